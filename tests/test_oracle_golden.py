@@ -1,0 +1,160 @@
+"""The CPU oracle against every known-answer test the reference holds for the hot path.
+
+Each case restates one Boost test of the reference (file:line in the docstring) with the reference's
+default fixture (dims 89x123x74, 10000 points; GV/test/testing_fixtures.hpp:131-166) and checks the
+oracle reproduces the expected integers. No GPU needed.
+"""
+import numpy as np
+import pytest
+
+DIMS = (89, 123, 74)
+N = DIMS[0] * DIMS[1] * DIMS[2]
+NPTS = 10000
+BIT, PROB = 0, 4
+
+
+def test_offset(oracle):
+    """GV/test/testing_voxelmap.cu:58-92 (voxelmap/offset)"""
+    sdim = (15, 16, 17)
+    for off, truth in [((0, -2, 0), -30), ((1, 1, 1), 256), ((1, -2, -3), -749), ((3, -2, -1), -267),
+                       ((-1, -2, 3), 689)]:
+        assert oracle.voxel_index_signed(sdim, off) == truth
+
+
+def test_float_to_probability(oracle):
+    """GV/voxel/DefaultCollider.hpp:94-98: thr 1.0 -> 127, 0.5 -> 0, 0.1 -> -101 (truncation toward 0)"""
+    assert oracle.float_to_probability(1.0) == 127
+    assert oracle.float_to_probability(0.5) == 0
+    assert oracle.float_to_probability(0.1) == -101
+    assert oracle.float_to_probability(0.0) == -127
+
+
+def test_collision(oracle):
+    """GV/test/testing_voxelmap.cu:95-114 (voxelmap/collision): Prob x Prob, thr 0.1 -> 10000"""
+    pts = oracle.create_equidistant_points(NPTS, DIMS, 1.0)
+    assert len(pts) == NPTS
+    m1, m2 = oracle.new_map(PROB, DIMS), oracle.new_map(PROB, DIMS)
+    assert not oracle.insert_points(m1, PROB, DIMS, 1.0, pts, 1)
+    oracle.insert_points(m2, PROB, DIMS, 1.0, pts, 1)
+    assert oracle.collide_map_map(m1, PROB, m2, PROB, N, 0.1) == NPTS
+
+
+def test_collision_with_offset(oracle):
+    """GV/test/testing_voxelmap.cu:118-141: 8, then 18 with (-1,0,-1), 18 reversed with (1,0,1)"""
+    p1 = oracle.create_box_of_points((2.1, 2.1, 2.1), (4.1, 4.1, 4.1), 0.5)
+    p2 = oracle.create_box_of_points((3.1, 3.1, 3.1), (5.1, 5.1, 5.1), 0.5)
+    m1, m2 = oracle.new_map(PROB, DIMS), oracle.new_map(PROB, DIMS)
+    oracle.insert_points(m1, PROB, DIMS, 1.0, p1, 1)
+    oracle.insert_points(m2, PROB, DIMS, 1.0, p2, 1)
+    assert oracle.collide_map_map(m1, PROB, m2, PROB, N, 0.1) == 8
+    assert oracle.collide_map_map(m1, PROB, m2, PROB, N, 0.1, oracle.voxel_index_signed(DIMS, (-1, 0, -1))) == 18
+    assert oracle.collide_map_map(m2, PROB, m1, PROB, N, 0.1, oracle.voxel_index_signed(DIMS, (1, 0, 1))) == 18
+
+
+def test_no_collision(oracle):
+    """GV/test/testing_voxelmap.cu:143-167: 3-D checkerboard -> 0"""
+    black, white = oracle.create_equidistant_points(NPTS, DIMS, 1.0, checkerboard=True)
+    m1, m2 = oracle.new_map(PROB, DIMS), oracle.new_map(PROB, DIMS)
+    oracle.insert_points(m1, PROB, DIMS, 1.0, black, 1)
+    oracle.insert_points(m2, PROB, DIMS, 1.0, white, 1)
+    assert oracle.collide_map_map(m1, PROB, m2, PROB, N, 0.1) == 0
+
+
+CUBE8 = np.array([[x, y, z] for x in (2, 3) for y in (2, 3) for z in (2, 3)], np.float32)
+
+
+def test_collision_with_types_probab(oracle):
+    """GV/test/testing_voxelmap.cu:312-360: count 8, mask == exactly bits {14, 46, 103}"""
+    m1, m2 = oracle.new_map(BIT, DIMS), oracle.new_map(PROB, DIMS)
+    for mg in (4 + 10, 4 + 42, 4 + 99):
+        oracle.insert_points(m1, BIT, DIMS, 1.0, CUBE8, mg)
+    oracle.insert_points(m2, PROB, DIMS, 1.0, CUBE8, 1)
+    cnt, mask = oracle.collide_bit_prob_types(m1, m2, N, 1.0)
+    assert cnt == 8
+    assert oracle.bits_of(mask) == [14, 46, 103]
+    # side effect (VoxelMapOperations.hpp:211): colliding voxels of map_1 now carry eBVM_COLLISION
+    cnt2, mask2 = oracle.collide_bit_prob_types(m1, m2, N, 1.0)
+    assert cnt2 == 8 and oracle.bits_of(mask2) == [2, 14, 46, 103]
+
+
+def test_bit_layout(oracle):
+    """GV/test/testing_voxelmap.cu:364-398 + testing_bitvector.cu:48-51,109-112: bit k lives in byte k>>3 at k&7"""
+    m = oracle.new_map(BIT, (1, 1, 1))
+    for mg in (0, 2, 3, 4, 111, 254, 255):
+        oracle.insert_points(m, BIT, (1, 1, 1), 1.0, [[0.5, 0.5, 0.5]], mg)
+    assert m[0] == 29 and m[13] == 128 and m[31] == 192
+    assert oracle.bits_of(m) == [0, 2, 3, 4, 111, 254, 255]
+    truth = "10111" + "0" * 106 + "1" + "0" * 142 + "11"
+    assert "".join("1" if (m[k >> 3] >> (k & 7)) & 1 else "0" for k in range(256)) == truth
+
+
+def _two_boxes(oracle):
+    b1 = oracle.create_box_of_points((1.1, 1.1, 1.1), (3.9, 3.9, 3.9), 0.1)
+    b2 = oracle.create_box_of_points((2.1, 2.1, 2.1), (4.9, 4.9, 4.9), 0.1)
+    return np.concatenate([b1, b2]), [len(b1), len(b2)]
+
+
+def test_list_insert_metapointcloud(oracle):
+    """GV/test/testing_voxellist.cu:282-338: 46 unique voxels, 8 with both bits {11,12}, all in the centre"""
+    xyz, sizes = _two_boxes(oracle)
+    lst = oracle.VoxelList(DIMS, 1.0)
+    lst.insert_meta(xyz, sizes, [11, 12])
+    assert len(lst) == 46
+    assert np.all(np.diff(lst.ids.astype(np.int64)) > 0)
+    both = [i for i in range(46) if oracle.bits_of(lst.voxels[i]) == [11, 12]]
+    assert len(both) == 8
+    assert all(2 <= c <= 3 for i in both for c in lst.coords[i])
+
+
+@pytest.mark.parametrize("map_type", [PROB, BIT])
+def test_list_collide_with_map(oracle, map_type):
+    """GV/test/testing_voxellist.cu:109-145 (46), :149-236 (types: 46, mask == {11,12}) for both map types"""
+    xyz, sizes = _two_boxes(oracle)
+    lst = oracle.VoxelList(DIMS, 1.0)
+    lst.insert_meta(xyz, sizes, [11, 12])
+    m = oracle.new_map(map_type, DIMS)
+    oracle.insert_meta(m, map_type, DIMS, 1.0, xyz, sizes, [1])
+    cnt, mask, _ = lst.collide(1, m, map_type, 1.0, mark=False)
+    assert cnt == 46 and oracle.bits_of(mask) == [11, 12]
+    cnt, _, _ = lst.collide(0, m, map_type, 1.0)
+    assert cnt == 46
+    # per-meaning counts over the same colliding set: 27 voxels carry 11, 27 carry 12 (8 carry both);
+    # every entry also carries eBVM_COLLISION from the marking collide above
+    tot, _, per = lst.collide(3, m, map_type, 1.0, mark=False)
+    assert per[11] == 27 and per[12] == 27 and per[2] == 46 and tot == 100
+
+
+def test_list_collide_shifting(oracle):
+    """GV/test/testing_voxellist.cu:239-279: x-offset 0..3 -> 27, 18, 9, 0"""
+    b1 = oracle.create_box_of_points((1.1, 1.1, 1.1), (3.9, 3.9, 3.9), 0.1)
+    lst = oracle.VoxelList(DIMS, 1.0)
+    lst.insert_meta(b1, [len(b1)], [1])
+    m = oracle.new_map(PROB, DIMS)
+    oracle.insert_meta(m, PROB, DIMS, 1.0, b1, [len(b1)], [1])
+    shift = np.float32(0.0)
+    while shift < 4.0:
+        off = oracle.voxel_index_signed(DIMS, (int(shift), 0, 0))
+        cnt, _, _ = lst.collide(0, m, PROB, 1.0, off)
+        assert cnt == (27 if shift < 1 else 18 if shift < 2 else 9 if shift < 3 else 0)
+        shift = np.float32(shift + np.float32(0.5))
+
+
+def test_bitmasked_collision(oracle):
+    """GV/test/testing_voxellist.cu:739-864 (voxellists/bitmasked_collision), side 0.025"""
+    side = 0.025
+    lst = oracle.VoxelList(DIMS, side)
+    m = oracle.new_map(PROB, DIMS)
+    oracle.insert_points(m, PROB, DIMS, side, oracle.create_box_of_points((0.111, 0.111, 0.111), (0.799, 0.399, 0.399), 0.005), 1)
+    for mn, mx, mg in [((0.111, 0.311, 0.111), (0.399, 0.599, 0.399), 34),
+                       ((0.311, 0.311, 0.111), (0.599, 0.599, 0.399), 63),
+                       ((0.511, 0.311, 0.111), (0.799, 0.599, 0.399), 102)]:
+        lst.insert_points(oracle.create_box_of_points(mn, mx, 0.005), mg)
+    for off3, expect in [((0, 0, 0), (0, 0, 9, 15, 21)), ((0, -4, 0), (0, 0, 18, 30, 42)),
+                         ((0, -4, -4), (0, 0, 12, 20, 28))]:
+        off = oracle.voxel_index_signed(DIMS, off3)
+        mask = np.zeros(32, np.uint8)
+        got = [lst.collide(2, m, PROB, 1.0, off, mask_in=mask)[0]]
+        for bit in (33, 34, 63, 102):
+            mask[bit >> 3] |= 1 << (bit & 7)
+            got.append(lst.collide(2, m, PROB, 1.0, off, mask_in=mask)[0])
+        assert got == [e * 64 for e in expect]
