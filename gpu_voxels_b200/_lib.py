@@ -1,0 +1,88 @@
+"""ctypes binding of libgvx.so (the C ABI declared in include/gvx.h).
+
+The product path: there is NO CPU fallback. If the CUDA library is missing or no GPU is present,
+loading / gvx_init fails loudly.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgvx.so")
+
+GVX_OK = 0
+ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED, ERR_DIM_MISMATCH, ERR_NOT_INITIALIZED = 1, 2, 3, 4, 5, 6
+MEM_HOST, MEM_DEVICE = 0, 1
+
+u64, u32, i32, f32, vp = C.c_uint64, C.c_uint32, C.c_int32, C.c_float, C.c_void_p
+P = C.POINTER
+
+# name -> (restype, argtypes); must list every symbol include/gvx.h declares (checked by tests/test_abi.py)
+SIGNATURES = {
+    "gvx_init": (C.c_int, [C.c_int]),
+    "gvx_shutdown": (C.c_int, []),
+    "gvx_last_error": (C.c_char_p, []),
+    "gvx_set_stream": (C.c_int, [vp]),
+    "gvx_sync": (C.c_int, []),
+    "gvx_device_info": (C.c_int, [P(C.c_int), P(u64), P(u64), C.c_char_p]),
+    "gvx_launch_count": (u64, []),
+    "gvx_map_create": (C.c_int, [P(u64), C.c_int, u32, u32, u32, f32]),
+    "gvx_map_create_slab": (C.c_int, [P(u64), C.c_int, u32, u32, u32, f32, u32, u32]),
+    "gvx_map_wrap": (C.c_int, [P(u64), C.c_int, vp, u32, u32, u32, f32, u32, u32]),
+    "gvx_map_destroy": (C.c_int, [u64]),
+    "gvx_map_clear": (C.c_int, [u64]),
+    "gvx_map_clear_meaning": (C.c_int, [u64, C.c_int]),
+    "gvx_map_clear_bits": (C.c_int, [u64, vp]),
+    "gvx_map_device_ptr": (C.c_int, [u64, P(vp), P(u64), P(u64)]),
+    "gvx_map_info": (C.c_int, [u64, P(C.c_int), P(u32), P(f32), P(u32), P(u32), P(u64)]),
+    "gvx_map_download": (C.c_int, [u64, vp]),
+    "gvx_map_upload": (C.c_int, [u64, vp]),
+    "gvx_insert_points": (C.c_int, [u64, vp, u64, C.c_int, C.c_int, P(C.c_int)]),
+    "gvx_insert_meta": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, u32, vp, P(C.c_int)]),
+    "gvx_transform_points": (C.c_int, [vp, vp, u64, C.c_int, vp]),
+    "gvx_update_logodds": (C.c_int, [u64, vp, u64, C.c_int, vp, C.c_int]),
+    "gvx_collide_map_map": (C.c_int, [u64, u64, f32, vp, C.c_int, P(u64)]),
+    "gvx_collide_map_map_async": (C.c_int, [u64, u64, f32, vp, C.c_int, vp]),
+    "gvx_collide_map_map_any": (C.c_int, [u64, u64, f32, P(C.c_int)]),
+    "gvx_collide_map_map_types": (C.c_int, [u64, u64, f32, C.c_int, vp, P(u64)]),
+}
+
+
+class GvxError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("gvx error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+
+
+def load():
+    """dlopen libgvx.so and declare the signatures. No compute call is made."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("libgvx.so is not built (run `python -m gpu_voxels_b200.build`); "
+                              "there is no CPU fallback for this path")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != GVX_OK:
+        raise GvxError(rc, load().gvx_last_error().decode("utf-8", "replace"))
+
+
+_initialized = False
+
+
+def init(device=-1):
+    global _initialized
+    L = load()
+    if not _initialized:
+        check(L.gvx_init(int(device)))
+        _initialized = True
+    return L

@@ -1,0 +1,369 @@
+"""Host-side mirror of the reference's public API for the hot path, over the C ABI (libgvx.so).
+
+Same names, argument meaning and error behaviour as the reference's C++ classes so that the parity
+tests read like the reference's own Boost tests:
+
+  GpuVoxels            GV/GpuVoxels.h:91-415         (getInstance, initialize, addMap, delMap, getMap, clearMap,
+                                                      insertPointCloudIntoMap, insertMetaPointCloudIntoMap)
+  BitVectorVoxelMap    GV/voxelmap/BitVoxelMap.h     (collideWith, collideWithTypes, clearBit(s), ...)
+  ProbVoxelMap         GV/voxelmap/ProbVoxelMap.h    (collideWith, insertSensorData, ...)
+  MetaPointCloud       GV/helpers/MetaPointCloud.h   (host container of concatenated sub-clouds)
+
+Point clouds are numpy float32 (n,3) arrays (host memory) or torch CUDA tensors (device memory, zero copy).
+The C++ facade in include/gpu_voxels/ is the drop-in for C++ callers; this module is the same thing for the
+Python test and benchmark harness. Nothing here computes voxels on the CPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import GvxError, MEM_DEVICE, MEM_HOST
+
+# MapType, GV/helpers/common_defines.h:59-73
+MT_BITVECTOR_VOXELMAP, MT_BITVECTOR_VOXELLIST, MT_BITVECTOR_OCTREE, MT_BITVECTOR_MORTON_VOXELLIST = 0, 1, 2, 3
+MT_PROBAB_VOXELMAP, MT_PROBAB_VOXELLIST, MT_PROBAB_OCTREE, MT_PROBAB_MORTON_VOXELLIST = 4, 5, 6, 7
+MT_COUNTING_VOXELLIST, MT_DISTANCE_VOXELMAP = 8, 9
+# BitVoxelMeaning, GV/helpers/common_defines.h:50-58
+eBVM_FREE, eBVM_OCCUPIED, eBVM_COLLISION, eBVM_UNKNOWN = 0, 1, 2, 3
+eBVM_SWEPT_VOLUME_START, eBVM_SWEPT_VOLUME_END, eBVM_UNDEFINED = 4, 254, 255
+BIT_VECTOR_LENGTH = 256
+SSIZE_MAX = 2 ** 63 - 1
+GPU_VOXELS_MAP_TYPE_NOT_IMPLEMENTED = "THIS TYPE OF DATA STRUCTURE IS NOT YET IMPLEMENTED!"
+
+
+def _log_error(msg):
+    import sys
+    print("[gpu_voxels ERROR] " + msg, file=sys.stderr)
+
+
+def _points_arg(points):
+    """-> (pointer, n, mem_kind, keepalive)"""
+    if hasattr(points, "data_ptr") and hasattr(points, "is_cuda"):  # torch tensor
+        t = points
+        if not t.is_cuda:
+            t = t.detach().cpu().numpy()
+        else:
+            import torch
+            assert t.dtype == torch.float32 and t.is_contiguous()
+            n = t.numel() // 3
+            return C.c_void_p(t.data_ptr()), n, MEM_DEVICE, t
+        points = t
+    a = np.ascontiguousarray(points, dtype=np.float32).reshape(-1, 3)
+    return a.ctypes.data_as(C.c_void_p), len(a), MEM_HOST, a
+
+
+class BitVectorVoxel:
+    """256-bit meaning set (GV/voxel/BitVoxel.h:38-108); .bytes is the reference's uint8_t[32] layout."""
+
+    def __init__(self, data=None):
+        self.bytes = np.zeros(32, np.uint8) if data is None else np.array(data, np.uint8).reshape(32)
+
+    def setBit(self, k):
+        self.bytes[k >> 3] |= np.uint8(1 << (k & 7))
+
+    def clearBit(self, k):
+        self.bytes[k >> 3] &= np.uint8(~(1 << (k & 7)) & 0xFF)
+
+    def getBit(self, k):
+        return bool(self.bytes[k >> 3] & (1 << (k & 7)))
+
+    def clear(self):
+        self.bytes[:] = 0
+
+    def isZero(self):
+        return not self.bytes.any()
+
+    def noneButEmpty(self):
+        return not ((self.bytes[0] & 0xFE) or self.bytes[1:].any())
+
+    def bits(self):
+        return [k for k in range(256) if self.getBit(k)]
+
+    def bitVector(self):
+        return self
+
+
+class MetaPointCloud:
+    """Concatenated sub-clouds + sizes (GV/helpers/MetaPointCloud.h:41-241). Host-resident here; the library
+    stages it to the device in one copy per insert."""
+
+    def __init__(self, point_clouds):
+        self.clouds = [np.ascontiguousarray(c, np.float32).reshape(-1, 3) for c in point_clouds]
+
+    def getNumberOfPointclouds(self):
+        return len(self.clouds)
+
+    def getPointcloudSizes(self):
+        return [len(c) for c in self.clouds]
+
+    def getAccumulatedPointcloudSize(self):
+        return sum(len(c) for c in self.clouds)
+
+    def accumulated(self):
+        return np.concatenate(self.clouds) if self.clouds else np.zeros((0, 3), np.float32)
+
+    def syncToDevice(self):
+        pass
+
+
+class GpuVoxelsMap:
+    """Base of the dense maps (GV/GpuVoxelsMap.h:50-276, GV/voxelmap/TemplateVoxelMap.h)."""
+    map_type = None
+
+    def __init__(self, dim, voxel_side_length, map_type=None, slab=None, _wrap_ptr=None):
+        self._L = _lib.init()
+        self.m_dim = tuple(int(d) for d in dim)
+        self.m_voxel_side_length = float(voxel_side_length)
+        h = C.c_uint64(0)
+        z0, z1 = (0, self.m_dim[2]) if slab is None else (int(slab[0]), int(slab[1]))
+        self.slab = (z0, z1)
+        if _wrap_ptr is not None:
+            _lib.check(self._L.gvx_map_wrap(C.byref(h), self.map_type, C.c_void_p(_wrap_ptr), *self.m_dim,
+                                            self.m_voxel_side_length, z0, z1))
+        else:
+            _lib.check(self._L.gvx_map_create_slab(C.byref(h), self.map_type, *self.m_dim, self.m_voxel_side_length,
+                                                   z0, z1))
+        self.handle = h.value
+
+    # -- lifetime
+    def destroy(self):
+        if getattr(self, "handle", None):
+            self._L.gvx_map_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+    # -- introspection
+    def getMapType(self):
+        return self.map_type
+
+    def getDimensions(self):
+        return self.m_dim
+
+    def getVoxelSideLength(self):
+        return self.m_voxel_side_length
+
+    def getMetricDimensions(self):
+        return tuple(np.float32(d) * np.float32(self.m_voxel_side_length) for d in self.m_dim)
+
+    def numVoxels(self):
+        return self.m_dim[0] * self.m_dim[1] * (self.slab[1] - self.slab[0])
+
+    def getMemoryUsage(self):
+        return self.numVoxels() * (1 if self.map_type == MT_PROBAB_VOXELMAP else 32)
+
+    def getVoidDeviceDataPtr(self):
+        p = C.c_void_p()
+        _lib.check(self._L.gvx_map_device_ptr(self.handle, C.byref(p), None, None))
+        return p.value
+
+    def download(self):
+        """raw voxel bytes in the reference layout: int8[n] (Prob) or uint8[n,32] (BitVector)"""
+        if self.map_type == MT_PROBAB_VOXELMAP:
+            out = np.empty(self.numVoxels(), np.int8)
+        else:
+            out = np.empty((self.numVoxels(), 32), np.uint8)
+        _lib.check(self._L.gvx_map_download(self.handle, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def upload(self, data):
+        a = np.ascontiguousarray(data)
+        assert a.nbytes == self.getMemoryUsage()
+        _lib.check(self._L.gvx_map_upload(self.handle, a.ctypes.data_as(C.c_void_p)))
+
+    # -- clearing
+    def clearMap(self):
+        _lib.check(self._L.gvx_map_clear(self.handle))
+
+    def clearBitVoxelMeaning(self, voxel_meaning):
+        rc = self._L.gvx_map_clear_meaning(self.handle, int(voxel_meaning))
+        if rc == _lib.ERR_UNSUPPORTED:  # ProbVoxelMap: logged, nothing happens (GV/voxelmap/ProbVoxelMap.hpp:110-116)
+            _log_error(self._L.gvx_last_error().decode())
+            return
+        _lib.check(rc)
+
+    # -- voxelisation
+    def insertPointCloud(self, points, voxel_meaning, check_outside=True):
+        """returns True if any point was outside the map (the reference only logs a warning)"""
+        p, n, kind, keep = _points_arg(points)
+        flag = C.c_int(0)
+        rc = self._L.gvx_insert_points(self.handle, p, n, kind, int(voxel_meaning),
+                                       C.byref(flag) if check_outside else None)
+        if rc == _lib.ERR_UNSUPPORTED:  # logged no-op, GV/voxelmap/ProbVoxelMap.hpp:118-140
+            _log_error(self._L.gvx_last_error().decode())
+            return False
+        _lib.check(rc)
+        return bool(flag.value)
+
+    def insertMetaPointCloud(self, meta_point_cloud, voxel_meanings, transforms=None, check_outside=True):
+        """voxel_meanings: one BitVoxelMeaning or a list with one per sub-cloud (both reference overloads,
+        GV/voxelmap/TemplateVoxelMap.hpp:609-664). transforms (optional, n_clouds x 4 x 4): the per-link
+        transformSubCloud fused into the insert."""
+        mpc = meta_point_cloud
+        sizes = np.asarray(mpc.getPointcloudSizes(), np.uint32)
+        mg = np.atleast_1d(np.asarray(voxel_meanings, np.int32))
+        xyz = mpc.accumulated()
+        tr = None if transforms is None else np.ascontiguousarray(transforms, np.float32).reshape(len(sizes), 16)
+        flag = C.c_int(0)
+        rc = self._L.gvx_insert_meta(self.handle, xyz.ctypes.data_as(C.c_void_p), MEM_HOST,
+                                     sizes.ctypes.data_as(C.c_void_p), len(sizes), mg.ctypes.data_as(C.c_void_p),
+                                     len(mg), tr.ctypes.data_as(C.c_void_p) if tr is not None else None,
+                                     C.byref(flag) if check_outside else None)
+        if rc == _lib.ERR_UNSUPPORTED:
+            _log_error(self._L.gvx_last_error().decode())
+            return False
+        _lib.check(rc)
+        return bool(flag.value)
+
+    # -- collisions
+    @staticmethod
+    def _off(offset):
+        if offset is None:
+            return None, None
+        a = np.asarray(offset, np.int32).reshape(3)
+        return a.ctypes.data_as(C.c_void_p), a
+
+    def collideWith(self, other, coll_threshold=1.0, offset=None, mark=True):
+        """size_t collideWith(const Map*, float coll_threshold = 1.0, const Vector3i& offset = Vector3i())
+        (GV/helpers/CollisionInterfaces.h:46,75). mark=True keeps the reference's side effect."""
+        p, keep = self._off(offset)
+        cnt = C.c_uint64(0)
+        _lib.check(self._L.gvx_collide_map_map(self.handle, other.handle, coll_threshold, p, int(mark), C.byref(cnt)))
+        return cnt.value
+
+    def collisionCheck(self, other, coll_threshold=1.0):
+        flag = C.c_int(0)
+        _lib.check(self._L.gvx_collide_map_map_any(self.handle, other.handle, coll_threshold, C.byref(flag)))
+        return bool(flag.value)
+
+
+class BitVectorVoxelMap(GpuVoxelsMap):
+    map_type = MT_BITVECTOR_VOXELMAP
+
+    def clearBit(self, bit_index):
+        _lib.check(self._L.gvx_map_clear_meaning(self.handle, int(bit_index)))
+
+    def clearBits(self, bits):
+        b = np.ascontiguousarray(bits.bytes if isinstance(bits, BitVectorVoxel) else bits, np.uint8)
+        _lib.check(self._L.gvx_map_clear_bits(self.handle, b.ctypes.data_as(C.c_void_p)))
+
+    def collideWithTypes(self, other, types_in_collision, coll_threshold=1.0, offset=None, mark=True):
+        """GV/voxelmap/BitVoxelMap.hpp:205-217; types_in_collision (BitVectorVoxel) is OR-ed into; offset ignored
+        like in the reference."""
+        cnt = C.c_uint64(0)
+        _lib.check(self._L.gvx_collide_map_map_types(self.handle, other.handle, coll_threshold, int(mark),
+                                                     types_in_collision.bytes.ctypes.data_as(C.c_void_p),
+                                                     C.byref(cnt)))
+        return cnt.value
+
+
+class ProbVoxelMap(GpuVoxelsMap):
+    map_type = MT_PROBAB_VOXELMAP
+
+    def insertSensorData(self, points_sensor_frame, sensor_pose, delta_occupied=72):
+        """the log-odds update of GV/voxelmap/ProbVoxelMap.hpp:52-102 without ray casting.
+        sensor_pose: 3x4 (or 4x4) row-major [R|t]."""
+        p, n, kind, keep = _points_arg(points_sensor_frame)
+        pose = np.ascontiguousarray(np.asarray(sensor_pose, np.float32).reshape(-1)[:12])
+        _lib.check(self._L.gvx_update_logodds(self.handle, p, n, kind, pose.ctypes.data_as(C.c_void_p),
+                                              int(delta_occupied)))
+
+
+def transform_points(points, matrix4):
+    """PointCloud::transform (kernelTransformCloud, GV/helpers/kernels/MetaPointCloudOperations.cu:77-91)"""
+    L = _lib.init()
+    a = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+    out = np.empty_like(a)
+    M = np.ascontiguousarray(matrix4, np.float32).reshape(16)
+    _lib.check(L.gvx_transform_points(a.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), len(a), MEM_HOST,
+                                      M.ctypes.data_as(C.c_void_p)))
+    return out
+
+
+class GpuVoxels:
+    """The singleton facade (GV/GpuVoxels.h:91-415, GV/GpuVoxels.cpp:33-78,164-313,443-559)."""
+    _instance = None
+
+    def __init__(self):
+        self._L = _lib.init()
+        self.m_dim = None
+        self.m_voxel_side_length = None
+        self.m_managed_maps = {}
+
+    @classmethod
+    def getInstance(cls):
+        if cls._instance is None:
+            cls._instance = GpuVoxels()
+        return cls._instance
+
+    def initialize(self, dim_x, dim_y, dim_z, voxel_side_length):
+        if self.m_dim is not None:  # second call only warns, GV/GpuVoxels.cpp:52-65
+            _log_error("Do not try to initialize GpuVoxels multiple times. Parameters remain unchanged.")
+            return
+        self.m_dim = (int(dim_x), int(dim_y), int(dim_z))
+        self.m_voxel_side_length = float(voxel_side_length)
+
+    def addMap(self, map_type, map_name):
+        if map_name in self.m_managed_maps:  # duplicate name -> null shared_ptr, GV/GpuVoxels.cpp:169-176
+            _log_error("Map with name '%s' already exists." % map_name)
+            return None
+        if map_type == MT_BITVECTOR_VOXELMAP:
+            m = BitVectorVoxelMap(self.m_dim, self.m_voxel_side_length)
+        elif map_type == MT_PROBAB_VOXELMAP:
+            m = ProbVoxelMap(self.m_dim, self.m_voxel_side_length)
+        elif map_type == MT_BITVECTOR_VOXELLIST:
+            from .voxellist import BitVectorVoxelList
+            m = BitVectorVoxelList(self.m_dim, self.m_voxel_side_length)
+        else:  # the reference throws std::string for unimplemented types, GV/GpuVoxels.cpp:210-211
+            raise NotImplementedError(GPU_VOXELS_MAP_TYPE_NOT_IMPLEMENTED)
+        self.m_managed_maps[map_name] = m
+        return m
+
+    def delMap(self, map_name):
+        m = self.m_managed_maps.pop(map_name, None)
+        if m is None:
+            _log_error("Map with name '%s' not found." % map_name)
+            return False
+        m.destroy()
+        return True
+
+    def getMap(self, map_name):
+        m = self.m_managed_maps.get(map_name)
+        if m is None:
+            _log_error("Map with name '%s' not found." % map_name)
+        return m
+
+    def clearMap(self, map_name, voxel_meaning=None):
+        m = self.getMap(map_name)
+        if m is None:
+            return False
+        if voxel_meaning is None:
+            m.clearMap()
+        else:
+            m.clearBitVoxelMeaning(voxel_meaning)
+        return True
+
+    def insertPointCloudIntoMap(self, cloud, map_name, voxel_meaning):
+        m = self.getMap(map_name)
+        if m is None:
+            return False
+        m.insertPointCloud(cloud, voxel_meaning)
+        return True
+
+    def insertMetaPointCloudIntoMap(self, meta_point_cloud, map_name, voxel_meanings):
+        m = self.getMap(map_name)
+        if m is None:
+            return False
+        m.insertMetaPointCloud(meta_point_cloud, voxel_meanings)
+        return True
+
+    def getDimensions(self):
+        return self.m_dim
+
+    def getVoxelSideLength(self):
+        return self.m_voxel_side_length

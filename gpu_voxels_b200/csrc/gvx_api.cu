@@ -1,0 +1,525 @@
+// gvx_api.cu -- the C ABI (include/gvx.h): context, handle table, host glue. No torch types.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/gvx.h"
+#include "gvx_internal.h"
+
+namespace gvx {
+
+struct Map {
+  int type;
+  uint32_t dx, dy, dz, z0, z1;
+  float side;
+  void* data;
+  bool owned;
+  uint64_t n_voxels() const { return (uint64_t)dx * dy * (z1 - z0); }
+  uint64_t n_total() const { return (uint64_t)dx * dy * dz; }
+  bool sharded() const { return z0 != 0 || z1 != dz; }
+  size_t voxel_bytes() const { return type == kMapProb ? 1 : kBitVoxelBytes; }
+  size_t bytes() const { return n_voxels() * voxel_bytes(); }
+  MapView view() const { return MapView{data, type, dx, dy, dz, z0, z1, side}; }
+};
+
+struct Context {
+  bool ready = false;
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  ReduceScratch* scratch_d = nullptr;
+  ResultBlock* result_d = nullptr;
+  ResultBlock* result_h = nullptr;       // pinned, mapped
+  ResultBlock* result_hmap_d = nullptr;  // device alias of result_h
+  // staging: device buffer for host point clouds, pinned + device buffers for small descriptors
+  void* stage_d = nullptr; size_t stage_cap = 0;
+  void* desc_h = nullptr; void* desc_d = nullptr; size_t desc_cap = 0;
+  uint64_t launches = 0;
+  uint64_t next_handle = 1;
+  std::unordered_map<uint64_t, Map> maps;
+  std::mutex mu;
+};
+
+static Context g;
+static thread_local std::string t_err;
+
+static int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  t_err = buf;
+  return code;
+}
+#define GVX_CUDA(x)                                                                                   \
+  do {                                                                                                \
+    cudaError_t e_ = (x);                                                                             \
+    if (e_ != cudaSuccess) return fail(GVX_ERR_CUDA, "%s: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+#define GVX_NEED_INIT() \
+  do { if (!g.ready) return fail(GVX_ERR_NOT_INITIALIZED, "gvx_init has not been called"); } while (0)
+
+static LaunchCtx lctx() {
+  return LaunchCtx{g.stream, g.sm_count, g.scratch_d, g.result_d, g.result_hmap_d, &g.launches};
+}
+static Map* find_map(gvx_handle_t h) {
+  auto it = g.maps.find(h);
+  return it == g.maps.end() ? nullptr : &it->second;
+}
+static int ensure_stage(size_t bytes) {
+  if (bytes <= g.stage_cap) return GVX_OK;
+  if (g.stage_d) { GVX_CUDA(cudaStreamSynchronize(g.stream)); GVX_CUDA(cudaFree(g.stage_d)); g.stage_d = nullptr; g.stage_cap = 0; }
+  size_t cap = bytes + bytes / 4 + (1u << 20);
+  GVX_CUDA(cudaMalloc(&g.stage_d, cap));
+  g.stage_cap = cap;
+  return GVX_OK;
+}
+static int ensure_desc(size_t bytes) {
+  if (bytes <= g.desc_cap) return GVX_OK;
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (g.desc_h) cudaFreeHost(g.desc_h);
+  if (g.desc_d) cudaFree(g.desc_d);
+  g.desc_h = g.desc_d = nullptr; g.desc_cap = 0;
+  size_t cap = bytes * 2 + 4096;
+  GVX_CUDA(cudaHostAlloc(&g.desc_h, cap, cudaHostAllocDefault));
+  GVX_CUDA(cudaMalloc(&g.desc_d, cap));
+  g.desc_cap = cap;
+  return GVX_OK;
+}
+// Points to device: host clouds go through the staging buffer (one async H2D, no per-call cudaMalloc/cudaFree
+// as in TemplateVoxelMap::insertPointCloud(std::vector), GV/voxelmap/TemplateVoxelMap.hpp:563-576).
+static int points_to_device(const float* xyz, uint64_t n, int mem_kind, const float** out_d) {
+  if (mem_kind == GVX_MEM_DEVICE) { *out_d = xyz; return GVX_OK; }
+  if (mem_kind != GVX_MEM_HOST) return fail(GVX_ERR_INVALID, "bad mem_kind %d", mem_kind);
+  const size_t bytes = (size_t)n * 12;
+  int rc = ensure_stage(bytes);
+  if (rc) return rc;
+  if (bytes) GVX_CUDA(cudaMemcpyAsync(g.stage_d, xyz, bytes, cudaMemcpyHostToDevice, g.stream));
+  *out_d = (const float*)g.stage_d;
+  return GVX_OK;
+}
+// DefaultCollider::floatToProbability (GV/voxel/DefaultCollider.hpp:94-98), evaluated on the host like the
+// reference does: thr*254 - 127 in fp32, C truncation to int32, low 8 bits.
+static int8_t float_to_probability(float thr) {
+  const float tmp = (thr * (float(127) - float(-127))) + float(-127);
+  return (int8_t)(int32_t)tmp;
+}
+
+}  // namespace gvx
+
+using namespace gvx;
+
+extern "C" {
+
+int gvx_init(int device) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  if (g.ready) return GVX_OK;
+  int n_dev = 0;
+  cudaError_t e = cudaGetDeviceCount(&n_dev);
+  if (e != cudaSuccess || n_dev == 0)
+    return fail(GVX_ERR_CUDA, "no CUDA device available (%s)", e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device >= 0) GVX_CUDA(cudaSetDevice(device));
+  GVX_CUDA(cudaGetDevice(&g.device));
+  GVX_CUDA(cudaDeviceGetAttribute(&g.sm_count, cudaDevAttrMultiProcessorCount, g.device));
+  GVX_CUDA(cudaStreamCreateWithFlags(&g.own_stream, cudaStreamNonBlocking));
+  g.stream = g.own_stream;
+  GVX_CUDA(cudaMalloc(&g.scratch_d, sizeof(ReduceScratch)));
+  GVX_CUDA(cudaMemset(g.scratch_d, 0, sizeof(ReduceScratch)));
+  GVX_CUDA(cudaMalloc(&g.result_d, sizeof(ResultBlock)));
+  GVX_CUDA(cudaMemset(g.result_d, 0, sizeof(ResultBlock)));
+  GVX_CUDA(cudaHostAlloc(&g.result_h, sizeof(ResultBlock), cudaHostAllocMapped));
+  memset(g.result_h, 0, sizeof(ResultBlock));
+  GVX_CUDA(cudaHostGetDevicePointer((void**)&g.result_hmap_d, g.result_h, 0));
+  GVX_CUDA(cudaDeviceSynchronize());
+  g.ready = true;
+  return GVX_OK;
+}
+
+int gvx_shutdown(void) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  if (!g.ready) return GVX_OK;
+  cudaDeviceSynchronize();
+  for (auto& kv : g.maps) if (kv.second.owned && kv.second.data) cudaFree(kv.second.data);
+  g.maps.clear();
+  if (g.stage_d) cudaFree(g.stage_d);
+  if (g.desc_d) cudaFree(g.desc_d);
+  if (g.desc_h) cudaFreeHost(g.desc_h);
+  cudaFree(g.scratch_d); cudaFree(g.result_d); cudaFreeHost(g.result_h);
+  cudaStreamDestroy(g.own_stream);
+  g.stage_d = g.desc_d = g.desc_h = nullptr; g.stage_cap = g.desc_cap = 0;
+  g.ready = false;
+  return GVX_OK;
+}
+
+const char* gvx_last_error(void) { return t_err.c_str(); }
+
+int gvx_set_stream(void* cuda_stream) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  g.stream = cuda_stream ? (cudaStream_t)cuda_stream : g.own_stream;
+  return GVX_OK;
+}
+
+int gvx_sync(void) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  return GVX_OK;
+}
+
+int gvx_device_info(int* sm_count, uint64_t* free_bytes, uint64_t* total_bytes, char* name64) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  size_t f = 0, t = 0;
+  GVX_CUDA(cudaMemGetInfo(&f, &t));
+  if (sm_count) *sm_count = g.sm_count;
+  if (free_bytes) *free_bytes = f;
+  if (total_bytes) *total_bytes = t;
+  if (name64) {
+    cudaDeviceProp p;
+    GVX_CUDA(cudaGetDeviceProperties(&p, g.device));
+    strncpy(name64, p.name, 63);
+    name64[63] = 0;
+  }
+  return GVX_OK;
+}
+
+uint64_t gvx_launch_count(void) { return g.launches; }
+
+// ---- dense maps ---------------------------------------------------------------------------------------
+static int map_make(gvx_handle_t* h, int map_type, void* wrap, uint32_t dx, uint32_t dy, uint32_t dz, float side,
+                    uint32_t z0, uint32_t z1) {
+  GVX_NEED_INIT();
+  if (!h) return fail(GVX_ERR_INVALID, "null handle pointer");
+  if (map_type != GVX_MT_BITVECTOR_VOXELMAP && map_type != GVX_MT_PROBAB_VOXELMAP)
+    return fail(GVX_ERR_UNSUPPORTED, "map type %d is not a dense voxel map of this path", map_type);
+  if (!dx || !dy || !dz || !(side > 0.0f) || z0 >= z1 || z1 > dz)
+    return fail(GVX_ERR_INVALID, "bad map geometry %ux%ux%u side %g slab [%u,%u)", dx, dy, dz, side, z0, z1);
+  Map m{map_type, dx, dy, dz, z0, z1, side, wrap, wrap == nullptr};
+  if (wrap) {
+    if ((uintptr_t)wrap & 31) return fail(GVX_ERR_INVALID, "wrapped map pointer must be 32-byte aligned");
+  } else {
+    cudaError_t e = cudaMalloc(&m.data, m.bytes());
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(GVX_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", m.bytes(), cudaGetErrorString(e)); }
+    GVX_CUDA(cudaMemsetAsync(m.data, map_type == GVX_MT_PROBAB_VOXELMAP ? 0x80 : 0x00, m.bytes(), g.stream));
+  }
+  const uint64_t id = g.next_handle++;
+  g.maps.emplace(id, m);
+  *h = id;
+  return GVX_OK;
+}
+
+int gvx_map_create(gvx_handle_t* h, int map_type, uint32_t dx, uint32_t dy, uint32_t dz, float side) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  return map_make(h, map_type, nullptr, dx, dy, dz, side, 0, dz);
+}
+int gvx_map_create_slab(gvx_handle_t* h, int map_type, uint32_t dx, uint32_t dy, uint32_t dz, float side, uint32_t z0,
+                        uint32_t z1) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  return map_make(h, map_type, nullptr, dx, dy, dz, side, z0, z1);
+}
+int gvx_map_wrap(gvx_handle_t* h, int map_type, void* data_d, uint32_t dx, uint32_t dy, uint32_t dz, float side,
+                 uint32_t z0, uint32_t z1) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  if (!data_d) return fail(GVX_ERR_INVALID, "null device pointer");
+  return map_make(h, map_type, data_d, dx, dy, dz, side, z0, z1);
+}
+int gvx_map_destroy(gvx_handle_t h) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (m->owned) GVX_CUDA(cudaFree(m->data));
+  g.maps.erase(h);
+  return GVX_OK;
+}
+static int map_clear_locked(Map* m) {
+  GVX_CUDA(cudaMemsetAsync(m->data, m->type == kMapProb ? 0x80 : 0x00, m->bytes(), g.stream));
+  return GVX_OK;
+}
+int gvx_map_clear(gvx_handle_t h) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  return map_clear_locked(m);
+}
+int gvx_map_clear_bits(gvx_handle_t h, const uint8_t mask32[GVX_BITVOXEL_BYTES]) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m || !mask32) return fail(GVX_ERR_INVALID, "unknown map handle or null mask");
+  if (m->type != kMapBit) return fail(GVX_ERR_UNSUPPORTED, "clearBits needs a BitVectorVoxelMap");
+  uint32_t w[8];
+  memcpy(w, mask32, 32);
+  GVX_CUDA(launch_clear_bits(lctx(), m->data, m->n_voxels(), w));
+  return GVX_OK;
+}
+int gvx_map_clear_meaning(gvx_handle_t h, int meaning) {
+  {
+    std::lock_guard<std::mutex> lk(g.mu);
+    GVX_NEED_INIT();
+    Map* m = find_map(h);
+    if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+    if (meaning < 0 || meaning > 255) return fail(GVX_ERR_INVALID, "meaning %d out of range", meaning);
+    if (m->type == kMapProb) {
+      if (meaning != GVX_BVM_OCCUPIED) return fail(GVX_ERR_UNSUPPORTED, "ProbVoxelMap only supports eBVM_OCCUPIED");
+      return map_clear_locked(m);
+    }
+  }
+  uint8_t mask[32] = {0};
+  mask[meaning >> 3] = (uint8_t)(1u << (meaning & 7));
+  return gvx_map_clear_bits(h, mask);
+}
+int gvx_map_device_ptr(gvx_handle_t h, void** data_d, uint64_t* first_voxel, uint64_t* n_voxels) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (data_d) *data_d = m->data;
+  if (first_voxel) *first_voxel = (uint64_t)m->z0 * m->dx * m->dy;
+  if (n_voxels) *n_voxels = m->n_voxels();
+  return GVX_OK;
+}
+int gvx_map_info(gvx_handle_t h, int* map_type, uint32_t dims3[3], float* side, uint32_t* z0, uint32_t* z1,
+                 uint64_t* bytes) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (map_type) *map_type = m->type;
+  if (dims3) { dims3[0] = m->dx; dims3[1] = m->dy; dims3[2] = m->dz; }
+  if (side) *side = m->side;
+  if (z0) *z0 = m->z0;
+  if (z1) *z1 = m->z1;
+  if (bytes) *bytes = m->bytes();
+  return GVX_OK;
+}
+int gvx_map_download(gvx_handle_t h, void* host_buf) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m || !host_buf) return fail(GVX_ERR_INVALID, "unknown map handle or null buffer");
+  GVX_CUDA(cudaMemcpyAsync(host_buf, m->data, m->bytes(), cudaMemcpyDeviceToHost, g.stream));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  return GVX_OK;
+}
+int gvx_map_upload(gvx_handle_t h, const void* host_buf) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m || !host_buf) return fail(GVX_ERR_INVALID, "unknown map handle or null buffer");
+  GVX_CUDA(cudaMemcpyAsync(m->data, host_buf, m->bytes(), cudaMemcpyHostToDevice, g.stream));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  return GVX_OK;
+}
+
+// ---- voxelisation -------------------------------------------------------------------------------------
+static int read_flag(int* any_outside) {
+  if (!any_outside) return GVX_OK;
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  *any_outside = g.result_h->flag ? 1 : 0;
+  return GVX_OK;
+}
+
+int gvx_insert_points(gvx_handle_t h, const float* xyz, uint64_t n, int mem_kind, int meaning, int* any_outside) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (meaning < 0 || meaning > 255) return fail(GVX_ERR_INVALID, "meaning %d out of range", meaning);
+  if (m->type == kMapProb && meaning != GVX_BVM_OCCUPIED)
+    return fail(GVX_ERR_UNSUPPORTED, "ProbVoxelMap only supports eBVM_OCCUPIED");
+  if (any_outside) *any_outside = 0;
+  if (n == 0) return GVX_OK;
+  if (!xyz) return fail(GVX_ERR_INVALID, "null point pointer");
+  const float* xyz_d = nullptr;
+  int rc = points_to_device(xyz, n, mem_kind, &xyz_d);
+  if (rc) return rc;
+  GVX_CUDA(launch_insert_points(lctx(), m->view(), xyz_d, n, meaning, any_outside != nullptr));
+  return read_flag(any_outside);
+}
+
+int gvx_insert_meta(gvx_handle_t h, const float* xyz, int mem_kind, const uint32_t* cloud_sizes, uint32_t n_clouds,
+                    const int32_t* meanings, uint32_t n_meanings, const float* transforms, int* any_outside) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (!cloud_sizes || !meanings || n_clouds == 0) return fail(GVX_ERR_INVALID, "null/empty cloud description");
+  if (n_meanings != 1 && n_meanings != n_clouds)
+    return fail(GVX_ERR_INVALID, "number of meanings (%u) differs from number of sub-clouds (%u)", n_meanings, n_clouds);
+  for (uint32_t k = 0; k < n_meanings; ++k) {
+    if (meanings[k] < 0 || meanings[k] > 255) return fail(GVX_ERR_INVALID, "meaning %d out of range", meanings[k]);
+    if (m->type == kMapProb && meanings[k] != GVX_BVM_OCCUPIED)
+      return fail(GVX_ERR_UNSUPPORTED, "ProbVoxelMap only supports eBVM_OCCUPIED");
+  }
+  if (any_outside) *any_outside = 0;
+  // descriptor = prefix[n_clouds+1] | meanings[n_meanings] | transforms[n_clouds*16], one async H2D
+  const size_t off_mg = ((size_t)n_clouds + 1) * 4, off_tr = off_mg + (size_t)n_meanings * 4;
+  const size_t total = off_tr + (transforms ? (size_t)n_clouds * 64 : 0);
+  int rc = ensure_desc(total);
+  if (rc) return rc;
+  GVX_CUDA(cudaStreamSynchronize(g.stream));  // the pinned descriptor may still be read by an earlier async copy
+  uint32_t* prefix = (uint32_t*)g.desc_h;
+  uint64_t acc = 0;
+  for (uint32_t c = 0; c < n_clouds; ++c) { prefix[c] = (uint32_t)acc; acc += cloud_sizes[c]; }
+  if (acc > 0xFFFFFFFFull) return fail(GVX_ERR_INVALID, "MetaPointCloud larger than 2^32-1 points");
+  prefix[n_clouds] = (uint32_t)acc;
+  memcpy((char*)g.desc_h + off_mg, meanings, (size_t)n_meanings * 4);
+  if (transforms) memcpy((char*)g.desc_h + off_tr, transforms, (size_t)n_clouds * 64);
+  if (acc == 0) return GVX_OK;
+  if (!xyz) return fail(GVX_ERR_INVALID, "null point pointer");
+  GVX_CUDA(cudaMemcpyAsync(g.desc_d, g.desc_h, total, cudaMemcpyHostToDevice, g.stream));
+  const float* xyz_d = nullptr;
+  rc = points_to_device(xyz, acc, mem_kind, &xyz_d);
+  if (rc) return rc;
+  MetaDesc d;
+  d.prefix_d = (const uint32_t*)g.desc_d;
+  d.meanings_d = (const int32_t*)((char*)g.desc_d + off_mg);
+  d.transforms_d = transforms ? (const float*)((char*)g.desc_d + off_tr) : nullptr;
+  d.n_clouds = n_clouds;
+  d.n_meanings = n_meanings;
+  GVX_CUDA(launch_insert_meta(lctx(), m->view(), xyz_d, acc, d, any_outside != nullptr));
+  return read_flag(any_outside);
+}
+
+int gvx_transform_points(const float* in_xyz, float* out_xyz, uint64_t n, int mem_kind, const float M16[16]) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  if (n == 0) return GVX_OK;
+  if (!in_xyz || !out_xyz || !M16) return fail(GVX_ERR_INVALID, "null pointer");
+  int rc = ensure_desc(64);
+  if (rc) return rc;
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  memcpy(g.desc_h, M16, 64);
+  GVX_CUDA(cudaMemcpyAsync(g.desc_d, g.desc_h, 64, cudaMemcpyHostToDevice, g.stream));
+  if (mem_kind == GVX_MEM_DEVICE) {
+    GVX_CUDA(launch_transform(lctx(), in_xyz, out_xyz, n, (const float*)g.desc_d));
+    return GVX_OK;
+  }
+  const float* in_d = nullptr;
+  rc = points_to_device(in_xyz, n, mem_kind, &in_d);
+  if (rc) return rc;
+  GVX_CUDA(launch_transform(lctx(), in_d, (float*)g.stage_d, n, (const float*)g.desc_d));
+  GVX_CUDA(cudaMemcpyAsync(out_xyz, g.stage_d, (size_t)n * 12, cudaMemcpyDeviceToHost, g.stream));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  return GVX_OK;
+}
+
+int gvx_update_logodds(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int mem_kind, const float pose12[12],
+                       int delta_occ) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (m->type != kMapProb) return fail(GVX_ERR_UNSUPPORTED, "insertSensorData needs a ProbVoxelMap");
+  if (delta_occ < -127 || delta_occ > 127) return fail(GVX_ERR_INVALID, "delta %d outside int8 range", delta_occ);
+  if (n == 0) return GVX_OK;
+  if (!xyz_sensor || !pose12) return fail(GVX_ERR_INVALID, "null pointer");
+  int rc = ensure_desc(48);
+  if (rc) return rc;
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  memcpy(g.desc_h, pose12, 48);
+  GVX_CUDA(cudaMemcpyAsync(g.desc_d, g.desc_h, 48, cudaMemcpyHostToDevice, g.stream));
+  const float* xyz_d = nullptr;
+  rc = points_to_device(xyz_sensor, n, mem_kind, &xyz_d);
+  if (rc) return rc;
+  GVX_CUDA(launch_update_logodds(lctx(), m->view(), xyz_d, n, (const float*)g.desc_d, delta_occ));
+  return GVX_OK;
+}
+
+// ---- collision counting, map x map --------------------------------------------------------------------
+static int collide_prepare(gvx_handle_t ha, gvx_handle_t hb, const int32_t off3[3], Map** a, Map** b, int64_t* off,
+                           int64_t* i0, int64_t* i1) {
+  *a = find_map(ha);
+  *b = find_map(hb);
+  if (!*a || !*b) return fail(GVX_ERR_INVALID, "unknown map handle");
+  Map *A = *a, *B = *b;
+  if (A->dx != B->dx || A->dy != B->dy || A->dz != B->dz || A->z0 != B->z0 || A->z1 != B->z1)
+    return fail(GVX_ERR_DIM_MISMATCH, "maps differ in dimensions or slab");
+  int64_t o = 0;
+  if (off3) o = (int64_t)off3[2] * A->dx * A->dy + (int64_t)off3[1] * A->dx + (int64_t)off3[0];  // getVoxelIndexSigned
+  if (o != 0 && A->sharded())
+    return fail(GVX_ERR_UNSUPPORTED, "offset collide on a z-slab map needs a halo exchange (replicas only)");
+  const int64_t n = (int64_t)A->n_voxels();
+  *off = o;
+  *i0 = o < 0 ? -o : 0;
+  *i1 = o > 0 ? n - o : n;
+  if (*i1 < *i0) *i1 = *i0;
+  return GVX_OK;
+}
+
+int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32_t off3[3], int mark, uint64_t* count) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map *a, *b;
+  int64_t off, i0, i1;
+  int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1);
+  if (rc) return rc;
+  GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
+                                  mark != 0, false, nullptr));
+  if (count) {
+    GVX_CUDA(cudaStreamSynchronize(g.stream));
+    *count = g.result_h->count;
+  }
+  return GVX_OK;
+}
+
+int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32_t off3[3], int mark,
+                              uint64_t* count_d) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map *a, *b;
+  int64_t off, i0, i1;
+  int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1);
+  if (rc) return rc;
+  GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
+                                  mark != 0, false, (unsigned long long*)count_d));
+  return GVX_OK;
+}
+
+int gvx_collide_map_map_any(gvx_handle_t ha, gvx_handle_t hb, float thr, int* flag) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map *a, *b;
+  int64_t off, i0, i1;
+  int rc = collide_prepare(ha, hb, nullptr, &a, &b, &off, &i0, &i1);
+  if (rc) return rc;
+  GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, 0, float_to_probability(thr),
+                                  false, false, nullptr));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (flag) *flag = g.result_h->count != 0;
+  return GVX_OK;
+}
+
+int gvx_collide_map_map_types(gvx_handle_t ha, gvx_handle_t hb, float thr, int mark,
+                              uint8_t mask_inout32[GVX_BITVOXEL_BYTES], uint64_t* count) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map *a, *b;
+  int64_t off, i0, i1;
+  int rc = collide_prepare(ha, hb, nullptr, &a, &b, &off, &i0, &i1);
+  if (rc) return rc;
+  if (a->type != kMapBit || b->type != kMapProb)
+    return fail(GVX_ERR_UNSUPPORTED, "collideWithTypes is implemented for BitVectorVoxelMap x ProbVoxelMap");
+  GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, 0, float_to_probability(thr),
+                                  mark != 0, true, nullptr));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (count) *count = g.result_h->count;
+  if (mask_inout32) {
+    const uint8_t* m = (const uint8_t*)g.result_h->mask;
+    for (int k = 0; k < 32; ++k) mask_inout32[k] |= m[k];
+  }
+  return GVX_OK;
+}
+
+}  // extern "C"

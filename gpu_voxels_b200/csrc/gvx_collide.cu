@@ -1,0 +1,269 @@
+// gvx_collide.cu -- collideWith map x map for sm_100a.
+//
+// Replaces kernelCollideVoxelMapsDebug / kernelCollideVoxelMaps / kernelCollideVoxelMapsBitvector
+// (GV/voxelmap/kernels/VoxelMapOperations.hpp:78-239) and the host tail of
+// collisionCheckWithCounterRelativeTransform (GV/voxelmap/TemplateVoxelMap.hpp:486-519: 128 KiB D2H of
+// uint16 block counters + a 65k-iteration host sum).
+//
+// Shape: a pure HBM stream over two grids. One BitVectorVoxel = one 256-bit load (LDG.E.256, sm_100a), so a
+// warp reads 1 KiB contiguous per instruction; probabilistic voxels are byte loads of one 32-B sector per warp
+// (Bit x Prob) or 128-bit loads of 16 voxels per thread (Prob x Prob). Tests and popcounts stay in registers,
+// counts go warp-REDUX -> shared -> one partial per CTA; the last CTA to arrive (self-resetting ticket) sums
+// the partials and writes the 64-bit result to device memory and to a mapped pinned host word, so one launch
+// and one stream sync deliver the answer. Algorithmic traffic: 33 / 33 / 2 / 64 B per voxel
+// (Bit x Prob, Prob x Bit, Prob x Prob, Bit x Bit).
+#include "gvx_internal.h"
+
+namespace gvx {
+
+constexpr int kThreads = 256;
+constexpr int kUnroll = 4;
+constexpr int kCtasPerSm = 4;
+
+template <bool COHERENT>
+__device__ __forceinline__ BitVoxelWords load_bit(const uint8_t* p) {
+  if (COHERENT) {
+    BitVoxelWords r;
+    asm volatile("ld.global.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]),
+                   "=r"(r.w[7])
+                 : "l"(p));
+    return r;
+  }
+  return ld_voxel_stream(p);
+}
+
+// Block-level finish shared by all collide kernels: reduce (count, mask) over the CTA, publish the partial,
+// let the last CTA produce the final result.
+template <bool TYPES>
+__device__ __forceinline__ void finish_block(uint32_t my_count, const uint32_t (&acc)[8], ReduceScratch* s,
+                                             ResultBlock* out_d, ResultBlock* out_h,
+                                             unsigned long long* count_out_d) {
+  __shared__ unsigned long long sh_cnt[kThreads / 32];
+  __shared__ uint32_t sh_mask[8];
+  __shared__ bool sh_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (TYPES && threadIdx.x < 8) sh_mask[threadIdx.x] = 0u;
+  const unsigned long long wsum = warp_sum_u32(my_count);
+  if (lane == 0) sh_cnt[warp] = wsum;
+  __syncthreads();
+  if (TYPES) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t m = __reduce_or_sync(0xffffffffu, acc[k]);
+      if (lane == 0 && m) atomicOr(&sh_mask[k], m);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    unsigned long long c = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) c += sh_cnt[w];
+    s->partial_count[blockIdx.x] = c;
+    if (TYPES) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s->partial_mask[blockIdx.x][k] = sh_mask[k];
+    }
+    __threadfence();
+    const unsigned int t = atomicInc(&s->ticket, gridDim.x - 1);  // wraps to 0 on the last arrival
+    sh_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!sh_last) return;
+  __threadfence();
+  unsigned long long c = 0;
+  uint32_t m[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (unsigned int b = threadIdx.x; b < gridDim.x; b += kThreads) {
+    c += __ldcg(&s->partial_count[b]);
+    if (TYPES) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) m[k] |= __ldcg(&s->partial_mask[b][k]);
+    }
+  }
+  __syncthreads();  // everyone is done with sh_cnt / sh_mask of the first phase
+  if (TYPES && threadIdx.x < 8) sh_mask[threadIdx.x] = 0u;
+  // 64-bit warp sum via two 32-bit halves would overflow-carry wrongly; shuffle-add instead
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if (lane == 0) sh_cnt[warp] = c;
+  __syncthreads();
+  if (TYPES) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t r = __reduce_or_sync(0xffffffffu, m[k]);
+      if (lane == 0 && r) atomicOr(&sh_mask[k], r);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    unsigned long long tot = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) tot += sh_cnt[w];
+    out_d->count = tot;
+    out_h->count = tot;
+    out_d->flag = tot != 0;
+    out_h->flag = tot != 0;
+    if (count_out_d) *count_out_d = tot;
+    if (TYPES) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { out_d->mask[k] = sh_mask[k]; out_h->mask[k] = sh_mask[k]; }
+    }
+    __threadfence_system();
+  }
+}
+
+// ---- generic kernel: one voxel per thread per step, at least one side is a BitVectorVoxel map (or an
+// unaligned Prob x Prob fallback). AT/BT are MapType values. DefaultCollider::collide semantics
+// (GV/voxel/DefaultCollider.hpp:51-80); TYPES adds SVCollider's mask |= a (GV/voxel/SVCollider.hpp:96-106).
+template <int AT, int BT, bool MARK, bool TYPES>
+__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+k_collide_voxelwise(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long long i_begin, long long i_end,
+                    long long off, int thr, ReduceScratch* scratch, ResultBlock* out_d, ResultBlock* out_h,
+                    unsigned long long* count_out_d) {
+  constexpr int U = (AT == kMapBit && BT == kMapBit) ? 2 : kUnroll;  // 128 B in flight per thread either way
+  uint32_t cnt = 0;
+  uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const long long stride = (long long)gridDim.x * kThreads * U;
+  for (long long base = i_begin + (long long)blockIdx.x * kThreads * U; base < i_end; base += stride) {
+    BitVoxelWords va[U], vb[U];
+    int pa[U], pb[U];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = base + u * kThreads + threadIdx.x;
+      ok[u] = i < i_end;
+      if (ok[u]) {
+        if (AT == kMapBit) va[u] = load_bit<MARK>(a + (size_t)(i + off) * kBitVoxelBytes);
+        else pa[u] = MARK ? (int)((const volatile int8_t*)a)[i + off] : (int)ld_stream_i8(a + (i + off));
+        if (BT == kMapBit) vb[u] = ld_voxel_stream(b + (size_t)i * kBitVoxelBytes);
+        else pb[u] = (int)ld_stream_i8(b + i);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!ok[u]) continue;
+      const long long i = base + u * kThreads + threadIdx.x;
+      const bool occ_a = (AT == kMapBit) ? bit_occupied(va[u]) : (pa[u] >= thr);
+      const bool occ_b = (BT == kMapBit) ? bit_occupied(vb[u]) : (pb[u] >= thr);
+      if (occ_a && occ_b) {
+        ++cnt;
+        if (TYPES && AT == kMapBit) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] |= va[u].w[k];
+        }
+        if (MARK) {  // a[i].insert(eBVM_COLLISION): bit 2 / occupancy 127; write only when it changes something
+          if (AT == kMapBit) {
+            if (!(va[u].w[0] & 4u)) *(uint32_t*)(a + (size_t)(i + off) * kBitVoxelBytes) = va[u].w[0] | 4u;
+          } else {
+            if (pa[u] != 127) ((int8_t*)a)[i + off] = 127;
+          }
+        }
+      }
+    }
+  }
+  finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d);
+}
+
+// ---- Prob x Prob, 16 voxels per 128-bit load. Requires (a + off) and b 16-byte aligned for i % 16 == 0.
+// Byte-wise signed >= via the SIMD video instructions; popcount of the 0xFF lanes / 8.
+template <bool MARK>
+__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long long i_begin, long long i_end,
+                    long long off, int thr, ReduceScratch* scratch, ResultBlock* out_d, ResultBlock* out_h,
+                    unsigned long long* count_out_d) {
+  uint32_t cnt = 0;
+  const uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const uint32_t t4 = (uint32_t)(uint8_t)thr * 0x01010101u;
+  const long long vb = (i_begin + 15) & ~15ll, ve = i_end & ~15ll;
+  if (blockIdx.x == 0) {  // unaligned head and tail, at most 30 voxels
+    const long long head = (vb < i_end ? vb : i_end) - i_begin;
+    const long long tail = ve > vb ? i_end - ve : 0;
+    for (long long k = threadIdx.x; k < head + tail; k += kThreads) {
+      const long long i = k < head ? i_begin + k : ve + (k - head);
+      const int pa = a[i + off], pb = b[i];
+      if (pa >= thr && pb >= thr) {
+        ++cnt;
+        if (MARK && pa != 127) a[i + off] = 127;
+      }
+    }
+  }
+  const long long nvec = ve > vb ? (ve - vb) >> 4 : 0;
+  const uint4* av = reinterpret_cast<const uint4*>(a + vb + off);
+  const uint4* bv = reinterpret_cast<const uint4*>(b + vb);
+  const long long stride = (long long)gridDim.x * kThreads * kUnroll;
+  for (long long base = (long long)blockIdx.x * kThreads * kUnroll; base < nvec; base += stride) {
+    uint4 xa[kUnroll], xb[kUnroll];
+    bool ok[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long v = base + u * kThreads + threadIdx.x;
+      ok[u] = v < nvec;
+      if (ok[u]) {
+        xa[u] = MARK ? __ldcg(av + v) : ld_stream_u4(av + v);
+        xb[u] = ld_stream_u4(bv + v);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      if (!ok[u]) continue;
+      const long long v = base + u * kThreads + threadIdx.x;
+      uint32_t wa[4] = {xa[u].x, xa[u].y, xa[u].z, xa[u].w};
+      const uint32_t wb[4] = {xb[u].x, xb[u].y, xb[u].z, xb[u].w};
+      bool changed = false;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t hit = __vcmpges4(wa[k], t4) & __vcmpges4(wb[k], t4);  // 0xFF per colliding byte
+        cnt += __popc(hit) >> 3;
+        if (MARK) {
+          const uint32_t nw = (wa[k] & ~hit) | (0x7F7F7F7Fu & hit);
+          changed |= nw != wa[k];
+          wa[k] = nw;
+        }
+      }
+      if (MARK && changed)
+        *reinterpret_cast<uint4*>(a + vb + off + (v << 4)) = make_uint4(wa[0], wa[1], wa[2], wa[3]);
+    }
+  }
+  finish_block<false>(cnt, acc, scratch, out_d, out_h, count_out_d);
+}
+
+template <int AT, int BT>
+static cudaError_t launch_voxelwise(const LaunchCtx& c, int grid, uint8_t* a, const uint8_t* b, long long i0,
+                                    long long i1, long long off, int thr, bool mark, bool types,
+                                    unsigned long long* out) {
+#define GVX_GO(M, T) k_collide_voxelwise<AT, BT, M, T><<<grid, kThreads, 0, c.stream>>>( \
+      a, b, i0, i1, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, out)
+  if (types) { if (mark) GVX_GO(true, true); else GVX_GO(false, true); }
+  else       { if (mark) GVX_GO(true, false); else GVX_GO(false, false); }
+#undef GVX_GO
+  return cudaGetLastError();
+}
+
+cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, const void* b_, int b_type,
+                                   int64_t i_begin, int64_t i_end, int64_t off, int8_t thr, bool mark, bool types,
+                                   unsigned long long* count_out_d) {
+  uint8_t* a = (uint8_t*)a_;
+  const uint8_t* b = (const uint8_t*)b_;
+  if (i_end < i_begin) i_end = i_begin;
+  const long long n = i_end - i_begin;
+  const int max_grid = c.sm_count * kCtasPerSm < kMaxGrid ? c.sm_count * kCtasPerSm : kMaxGrid;
+  ++*c.launches;
+  if (a_type == kMapProb && b_type == kMapProb) {
+    const bool aligned = ((off & 15) == 0) && (((uintptr_t)a & 15) == 0) && (((uintptr_t)b & 15) == 0);
+    if (aligned) {
+      long long work = (n / 16 + kThreads * kUnroll - 1) / (kThreads * kUnroll);
+      int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));
+      if (mark) k_collide_prob_prob<true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d);
+      else k_collide_prob_prob<false><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d);
+      return cudaGetLastError();
+    }
+  }
+  long long work = (n + kThreads * kUnroll - 1) / (kThreads * kUnroll);
+  int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));
+  if (a_type == kMapBit && b_type == kMapProb) return launch_voxelwise<kMapBit, kMapProb>(c, grid, a, b, i_begin, i_end, off, thr, mark, types, count_out_d);
+  if (a_type == kMapProb && b_type == kMapBit) return launch_voxelwise<kMapProb, kMapBit>(c, grid, a, b, i_begin, i_end, off, thr, mark, false, count_out_d);
+  if (a_type == kMapBit && b_type == kMapBit) return launch_voxelwise<kMapBit, kMapBit>(c, grid, a, b, i_begin, i_end, off, thr, mark, false, count_out_d);
+  return launch_voxelwise<kMapProb, kMapProb>(c, grid, a, b, i_begin, i_end, off, thr, mark, false, count_out_d);
+}
+
+}  // namespace gvx

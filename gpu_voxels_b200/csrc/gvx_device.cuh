@@ -1,0 +1,90 @@
+// gvx_device.cuh -- device-side building blocks shared by the sm_100a kernels.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace gvx {
+
+constexpr int kBitVoxelBytes = 32;
+constexpr int kMapBit = 0;   // MT_BITVECTOR_VOXELMAP
+constexpr int kMapProb = 4;  // MT_PROBAB_VOXELMAP
+
+// One BitVectorVoxel (256 bits) as eight little-endian 32-bit words: bit k of the reference's
+// uint8_t[32] (byte k>>3, position k&7; GV/helpers/BitVector.h:223-228) is bit k&31 of word k>>5.
+struct __align__(32) BitVoxelWords {
+  uint32_t w[8];
+};
+
+// 256-bit streaming load (sm_100a: LDG.E.256), read-only path, no L1 allocation.
+__device__ __forceinline__ BitVoxelWords ld_voxel_stream(const void* p) {
+  BitVoxelWords r;
+  asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]),
+                 "=r"(r.w[7])
+               : "l"(p));
+  return r;
+}
+// 256-bit coherent load (for data this kernel may also write)
+__device__ __forceinline__ BitVoxelWords ld_voxel(const void* p) {
+  BitVoxelWords r;
+  asm volatile("ld.global.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]),
+                 "=r"(r.w[7])
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint4 ld_stream_u4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ int8_t ld_stream_i8(const void* p) {
+  int r;
+  asm volatile("ld.global.nc.L1::no_allocate.s8 %0, [%1];" : "=r"(r) : "l"(p));
+  return (int8_t)r;
+}
+
+// !BitVector::noneButEmpty(): any bit other than bit 0 (eBVM_FREE) set (GV/helpers/BitVector.h:183-198)
+__device__ __forceinline__ bool bit_occupied(const BitVoxelWords& v) {
+  return (((v.w[0] & 0xFFFFFFFEu) | v.w[1] | v.w[2] | v.w[3]) | (v.w[4] | v.w[5] | v.w[6] | v.w[7])) != 0u;
+}
+
+// float -> voxel coordinate, GV/voxelmap/kernels/VoxelMapOperations.h:123-133:
+// static_cast<uint32_t>(floor(c / side)). IEEE division (this file is never built with -use_fast_math), floor,
+// saturating convert (NaN and negatives -> 0); compiles to F2I.U32.FLOOR.NTZ like the reference kernel.
+__device__ __forceinline__ uint32_t coord_to_voxel(float c, float side) {
+  return static_cast<uint32_t>(floorf(__fdiv_rn(c, side)));
+}
+
+// Matrix4f * Vector3f (GV/helpers/cuda_matrices.h:740-746) with the exact contraction nvcc 12.9 emits for the
+// reference's kernelTransformCloud: fadd(a14, fma(a13, z, fma(a11, x, fmul(a12, y)))). The _rn intrinsics are
+// never re-associated or re-contracted by the compiler.
+__device__ __forceinline__ float affine_row(const float* __restrict__ a, float x, float y, float z) {
+  float t = __fmul_rn(a[1], y);
+  t = __fmaf_rn(a[0], x, t);
+  t = __fmaf_rn(a[2], z, t);
+  return __fadd_rn(a[3], t);
+}
+
+__device__ __forceinline__ uint64_t warp_sum_u32(uint32_t v) { return (uint64_t)__reduce_add_sync(0xffffffffu, v); }
+
+// Scratch shared by every reducing kernel of one context: per-CTA partials, a self-resetting ticket
+// (atomicInc wraps to 0 when the last CTA arrives, so no memset between launches) and the result block.
+struct ResultBlock {
+  unsigned long long count;
+  uint32_t mask[8];
+  uint32_t flag;
+  uint32_t pad;
+  unsigned long long per_meaning[256];
+};
+constexpr int kMaxGrid = 148 * 16;  // upper bound on CTAs of a reducing kernel
+struct ReduceScratch {
+  unsigned long long partial_count[kMaxGrid];
+  uint32_t partial_mask[kMaxGrid][8];
+  unsigned int ticket;
+  unsigned int flag_accum;
+};
+
+}  // namespace gvx

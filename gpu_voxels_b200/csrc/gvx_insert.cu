@@ -1,0 +1,249 @@
+// gvx_insert.cu -- point-cloud voxelisation for sm_100a.
+//
+// Replaces kernelInsertGlobalPointCloud / kernelInsertMetaPointCloud x2
+// (GV/voxelmap/kernels/VoxelMapOperations.hpp:241-264, 302-340, 386-437), kernelTransformCloud
+// (GV/helpers/kernels/MetaPointCloudOperations.cu:77-91), kernelTransformSensorData
+// (GV/voxelmap/kernels/VoxelMapOperations.cu:27-71), kernelInsertSensorData without ray casting
+// (GV/voxelmap/kernels/VoxelMapOperations.hpp:559-613) and kernelClearVoxelMap(bits) (:45-72).
+//
+// The fp32 point transform, the float->voxel index computation and the scatter are ONE kernel. The
+// reference's non-atomic byte read-modify-write (BitVector::setBit) loses bits when two meanings of the
+// same byte hit one voxel concurrently; here a BitVectorVoxel insert is an atomicOr on the 32-bit word
+// that holds the meaning bit, issued once per (voxel, meaning) group of a warp (__match_any_sync), and the
+// probabilistic log-odds update is a saturating add applied with one CAS per (voxel) group of a warp, so
+// results equal the sequential (race-free) semantics and are deterministic.
+#include "gvx_internal.h"
+
+namespace gvx {
+
+constexpr int kInsThreads = 256;
+
+__device__ __forceinline__ int8_t prob_insert_value(int meaning) {
+  // ProbabilisticVoxel::insert, GV/voxel/ProbabilisticVoxel.hpp:77-92
+  return meaning == 0 ? (int8_t)-127 : ((meaning == 1 || meaning == 2) ? (int8_t)127 : (int8_t)-128);
+}
+
+// Lower-bound search in the exclusive prefix of cloud sizes: cloud c with prefix[c] <= i < prefix[c+1].
+// (The reference walks cloud_sizes[] linearly from 0 in every thread, VoxelMapOperations.hpp:396-406.)
+__device__ __forceinline__ uint32_t find_cloud(const uint32_t* prefix, uint32_t n_clouds, uint32_t i) {
+  uint32_t lo = 0, hi = n_clouds;
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (prefix[mid] <= i) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// Publish the "points outside the map" flag: OR into flag_accum, last CTA moves it to the result block and
+// resets it (self-cleaning, no memset between launches).
+__device__ __forceinline__ void finish_flag(bool outside, ReduceScratch* s, ResultBlock* out_d, ResultBlock* out_h) {
+  __shared__ bool sh_last;
+  const bool any = __syncthreads_or(outside);
+  if (threadIdx.x == 0) {
+    if (any) atomicOr(&s->flag_accum, 1u);
+    __threadfence();
+    const unsigned int t = atomicInc(&s->ticket, gridDim.x - 1);
+    sh_last = (t == gridDim.x - 1);
+    if (sh_last) {
+      __threadfence();
+      const unsigned int v = atomicExch(&s->flag_accum, 0u);
+      out_d->flag = v;
+      out_h->flag = v;
+      __threadfence_system();
+    }
+  }
+}
+
+template <bool PROB, bool META>
+__global__ void __launch_bounds__(kInsThreads)
+k_insert(MapView m, const float* __restrict__ xyz, unsigned long long n, int meaning, MetaDesc d,
+         bool want_flag, ReduceScratch* s, ResultBlock* out_d, ResultBlock* out_h) {
+  extern __shared__ uint32_t sh_prefix[];  // META: n_clouds + 1 entries when they fit, else unused
+  const uint32_t* prefix = d.prefix_d;
+  if (META && d.n_clouds + 1 <= 1024) {
+    for (uint32_t k = threadIdx.x; k <= d.n_clouds; k += kInsThreads) sh_prefix[k] = d.prefix_d[k];
+    __syncthreads();
+    prefix = sh_prefix;
+  }
+  const uint64_t slab = (uint64_t)m.dx * m.dy;
+  bool outside = false;
+  const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
+  // uniform trip count per warp so the warp-collective match below is always convergent
+  const unsigned long long n_round = (n + 31ull) & ~31ull;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n_round; i += stride) {
+    bool live = i < n;
+    unsigned long long key = ~0ull - (threadIdx.x & 31);  // unique per lane => no peers
+    uint64_t idx = 0;
+    int mg = meaning;
+    if (live) {
+      float x = __ldg(xyz + 3 * i), y = __ldg(xyz + 3 * i + 1), z = __ldg(xyz + 3 * i + 2);
+      if (META) {
+        const uint32_t c = find_cloud(prefix, d.n_clouds, (uint32_t)i);
+        mg = d.meanings_d[d.n_meanings == 1 ? 0 : c];
+        if (d.transforms_d) {
+          const float* M = d.transforms_d + 16 * (size_t)c;
+          const float tx = affine_row(M, x, y, z), ty = affine_row(M + 4, x, y, z), tz = affine_row(M + 8, x, y, z);
+          x = tx; y = ty; z = tz;
+        }
+      }
+      const uint32_t cx = coord_to_voxel(x, m.side), cy = coord_to_voxel(y, m.side), cz = coord_to_voxel(z, m.side);
+      if (cx < m.dx && cy < m.dy && cz < m.dz) {
+        live = cz >= m.z0 && cz < m.z1;  // another slab's voxel: not outside, not ours
+        idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+        key = (idx << 8) | (uint32_t)(mg & 255);
+      } else {
+        outside = true;
+        live = false;
+      }
+    }
+    if (PROB) {
+      if (live) ((int8_t*)m.data)[idx] = prob_insert_value(mg);  // same value from every writer
+    } else {
+      const unsigned peers = __match_any_sync(0xffffffffu, key);
+      if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
+        const uint32_t bit = (uint32_t)(mg & 255);
+        atomicOr((uint32_t*)m.data + idx * 8 + (bit >> 5), 1u << (bit & 31));
+      }
+    }
+  }
+  if (want_flag) finish_flag(outside, s, out_d, out_h);
+}
+
+__global__ void __launch_bounds__(kInsThreads)
+k_transform(const float* __restrict__ in, float* __restrict__ out, unsigned long long n, const float* __restrict__ M16) {
+  __shared__ float M[12];
+  if (threadIdx.x < 12) M[threadIdx.x] = M16[threadIdx.x];
+  __syncthreads();
+  const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n; i += stride) {
+    const float x = in[3 * i], y = in[3 * i + 1], z = in[3 * i + 2];
+    const float tx = affine_row(M, x, y, z), ty = affine_row(M + 4, x, y, z), tz = affine_row(M + 8, x, y, z);
+    out[3 * i] = tx; out[3 * i + 1] = ty; out[3 * i + 2] = tz;
+  }
+}
+
+// Saturating int8 add on one byte of the map with a 32-bit CAS. For same-sign deltas,
+// clamp(occ + k*delta, -127, 127) equals k sequential ProbabilisticVoxel::updateOccupancy calls
+// (GV/voxel/ProbabilisticVoxel.hpp:51-57), so a warp's duplicates are folded into one update.
+__device__ __forceinline__ void logodds_add(int8_t* map, uint64_t idx, int total_delta) {
+  uint32_t* wp = reinterpret_cast<uint32_t*>(map + (idx & ~3ull));
+  const int shift = (int)(idx & 3ull) * 8;
+  uint32_t old = *wp, assumed;
+  do {
+    assumed = old;
+    int v = (int)(int8_t)((assumed >> shift) & 0xFFu) + total_delta;
+    v = v < -127 ? -127 : (v > 127 ? 127 : v);
+    const uint32_t nw = (assumed & ~(0xFFu << shift)) | (((uint32_t)v & 0xFFu) << shift);
+    if (nw == assumed) break;
+    old = atomicCAS(wp, assumed, nw);
+  } while (old != assumed);
+}
+
+// insertSensorData without ray casting: sensor-frame point -> world (pose = [R|t], re-projection onto z = 0
+// with the reference's double-precision factor when the world point is below the floor), NaN filter, bounds
+// test on the point and on the sensor origin, updateOccupancy(+delta) at the hit voxel.
+__global__ void __launch_bounds__(kInsThreads)
+k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n, const float* __restrict__ pose12,
+                 int delta) {
+  __shared__ float P[12];
+  if (threadIdx.x < 12) P[threadIdx.x] = pose12[threadIdx.x];
+  __syncthreads();
+  const uint32_t sx = coord_to_voxel(P[3], m.side), sy = coord_to_voxel(P[7], m.side), sz = coord_to_voxel(P[11], m.side);
+  const bool sensor_inside = sx < m.dx && sy < m.dy && sz < m.dz;
+  const uint64_t slab = (uint64_t)m.dx * m.dy;
+  const unsigned long long nvox = slab * m.dz;
+  if (n > nvox) n = nvox;  // the reference's loop bound, VoxelMapOperations.hpp:569
+  const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
+  const unsigned long long n_round = (n + 31ull) & ~31ull;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n_round; i += stride) {
+    bool live = false;
+    uint64_t idx = 0;
+    if (i < n) {
+      const float rx = __ldg(xyz + 3 * i), ry = __ldg(xyz + 3 * i + 1), rz = __ldg(xyz + 3 * i + 2);
+      float wx = affine_row(P, rx, ry, rz), wy = affine_row(P + 4, rx, ry, rz), wz = affine_row(P + 8, rx, ry, rz);
+      if (wz < 0.0f) {  // VoxelMapOperations.cu:56-64
+        const double factor = (double)__fdiv_rn(P[11], __fsub_rn(P[11], wz));
+        const float qx = (float)((double)rx * factor), qy = (float)((double)ry * factor), qz = (float)((double)rz * factor);
+        wx = affine_row(P, qx, qy, qz); wy = affine_row(P + 4, qx, qy, qz); wz = affine_row(P + 8, qx, qy, qz);
+      }
+      if (!(isnan(wx) || isnan(wy) || isnan(wz))) {
+        const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
+        if (cx < m.dx && cy < m.dy && cz < m.dz && sensor_inside && cz >= m.z0 && cz < m.z1) {
+          live = true;
+          idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+        }
+      }
+    }
+    const unsigned long long key = live ? idx : (~0ull - (threadIdx.x & 31));
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
+  }
+}
+
+// BitVoxelMap::clearBits / clearBit: voxel &= ~mask, written back only where it changes.
+__global__ void __launch_bounds__(kInsThreads)
+k_clear_bits(uint8_t* data, unsigned long long n, BitVoxelWords mask) {
+  const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n; i += stride) {
+    BitVoxelWords v = ld_voxel(data + i * kBitVoxelBytes);
+    uint32_t hit = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) hit |= v.w[k] & mask.w[k];
+    if (hit) {
+      uint4* p = reinterpret_cast<uint4*>(data + i * kBitVoxelBytes);
+      p[0] = make_uint4(v.w[0] & ~mask.w[0], v.w[1] & ~mask.w[1], v.w[2] & ~mask.w[2], v.w[3] & ~mask.w[3]);
+      p[1] = make_uint4(v.w[4] & ~mask.w[4], v.w[5] & ~mask.w[5], v.w[6] & ~mask.w[6], v.w[7] & ~mask.w[7]);
+    }
+  }
+}
+
+static int grid_for(const LaunchCtx& c, unsigned long long n, int per_sm) {
+  unsigned long long g = (n + kInsThreads - 1) / kInsThreads;
+  const unsigned long long cap = (unsigned long long)c.sm_count * per_sm;
+  if (g > cap) g = cap;
+  if (g > (unsigned long long)kMaxGrid) g = kMaxGrid;
+  return g < 1 ? 1 : (int)g;
+}
+
+cudaError_t launch_insert_points(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n, int meaning,
+                                 bool want_flag) {
+  const int grid = grid_for(c, n, 8);
+  MetaDesc d{};
+  ++*c.launches;
+  if (m.type == kMapProb) k_insert<true, false><<<grid, kInsThreads, 0, c.stream>>>(m, xyz_d, n, meaning, d, want_flag, c.scratch_d, c.result_d, c.result_hmap_d);
+  else k_insert<false, false><<<grid, kInsThreads, 0, c.stream>>>(m, xyz_d, n, meaning, d, want_flag, c.scratch_d, c.result_d, c.result_hmap_d);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_insert_meta(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n, const MetaDesc& d,
+                               bool want_flag) {
+  const int grid = grid_for(c, n, 8);
+  const size_t smem = d.n_clouds + 1 <= 1024 ? (d.n_clouds + 1) * sizeof(uint32_t) : 0;
+  ++*c.launches;
+  if (m.type == kMapProb) k_insert<true, true><<<grid, kInsThreads, smem, c.stream>>>(m, xyz_d, n, 0, d, want_flag, c.scratch_d, c.result_d, c.result_hmap_d);
+  else k_insert<false, true><<<grid, kInsThreads, smem, c.stream>>>(m, xyz_d, n, 0, d, want_flag, c.scratch_d, c.result_d, c.result_hmap_d);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_transform(const LaunchCtx& c, const float* in_d, float* out_d, uint64_t n, const float* M16_d) {
+  ++*c.launches;
+  k_transform<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(in_d, out_d, n, M16_d);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
+                                  const float* pose12_d, int delta) {
+  ++*c.launches;
+  k_update_logodds<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, n, pose12_d, delta);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8]) {
+  BitVoxelWords mk;
+  for (int k = 0; k < 8; ++k) mk.w[k] = mask8[k];
+  ++*c.launches;
+  k_clear_bits<<<grid_for(c, n_voxels, 8), kInsThreads, 0, c.stream>>>((uint8_t*)data, n_voxels, mk);
+  return cudaGetLastError();
+}
+
+}  // namespace gvx

@@ -1,0 +1,157 @@
+/* gvx.h -- C ABI of the B200-native gpu-voxels hot path (libgvx.so).
+ *
+ * This is the drop-in boundary. The reference (Changliu52/gpu-voxels) has no FFI: its boundary is the
+ * public C++ class API (GpuVoxels, voxelmap::BitVectorVoxelMap, voxelmap::ProbVoxelMap,
+ * voxellist::BitVectorVoxelList). include/gpu_voxels/ keeps that C++ surface source-compatible for
+ * the path; every method there is a few lines over the functions below. Each entry point cites the
+ * reference interface it replaces ("GV/" = packages/gpu_voxels/src/gpu_voxels/ in the reference).
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes, opaque 64-bit handles, int status (0 = GVX_OK). Nothing
+ *    throws, nothing calls exit(); gvx_last_error() returns the message of the last failure on the
+ *    calling thread.
+ *  - Pointer arguments are HOST pointers unless the name ends in _d or a mem_kind argument says otherwise
+ *    (GVX_MEM_HOST / GVX_MEM_DEVICE).
+ *  - Voxel layout is the reference's and is part of the contract (GV/voxelmap/TemplateVoxelMap.h:257-259):
+ *    linear index = z*dx*dy + y*dx + x; BitVectorVoxel = 32 bytes, bit k in byte k>>3 at position k&7
+ *    (GV/helpers/BitVector.h:223-228); ProbabilisticVoxel = 1 signed byte of log-odds
+ *    (GV/voxel/ProbabilisticVoxel.h:34-115). Indices are 64-bit, so maps beyond the reference's 4 GiB limit
+ *    (GV/voxelmap/TemplateVoxelMap.hpp:65-75) are allowed.
+ *  - All work is enqueued on ONE CUDA stream per process (gvx_set_stream lets the host share it, e.g. with
+ *    torch). Calls that return a host value synchronise that stream; calls whose result pointers are NULL, and
+ *    the *_async variants (results into device memory), do not.
+ *  - A map may be a z-slab [z0,z1) of a larger grid (multi-GPU sharding: one process per GPU, each owning a
+ *    slab; not in the reference). Slab maps hold voxels z0*dx*dy .. z1*dx*dy-1 only.
+ *  - One device per process. Thread-safe: a process-wide mutex serialises calls (the reference takes
+ *    per-map recursive mutexes around fully synchronous calls, GV/GpuVoxelsMap.h:267-269).
+ */
+#ifndef GVX_H_INCLUDED
+#define GVX_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef uint64_t gvx_handle_t;
+
+enum gvx_status {
+  GVX_OK = 0,
+  GVX_ERR_INVALID = 1,      /* bad argument / unknown handle */
+  GVX_ERR_CUDA = 2,         /* a CUDA runtime call failed (message in gvx_last_error) */
+  GVX_ERR_NOMEM = 3,
+  GVX_ERR_UNSUPPORTED = 4,  /* e.g. meaning != eBVM_OCCUPIED into a ProbVoxelMap, offset on a slab map */
+  GVX_ERR_DIM_MISMATCH = 5, /* list x map with different reference dimensions (reference returns SSIZE_MAX) */
+  GVX_ERR_NOT_INITIALIZED = 6
+};
+
+/* values of the reference's MapType enum (GV/helpers/common_defines.h:59-73); also the on-disk tag */
+enum gvx_map_type {
+  GVX_MT_BITVECTOR_VOXELMAP = 0,
+  GVX_MT_BITVECTOR_VOXELLIST = 1,
+  GVX_MT_PROBAB_VOXELMAP = 4
+};
+
+/* BitVoxelMeaning (GV/helpers/common_defines.h:50-58) */
+enum gvx_meaning {
+  GVX_BVM_FREE = 0, GVX_BVM_OCCUPIED = 1, GVX_BVM_COLLISION = 2, GVX_BVM_UNKNOWN = 3,
+  GVX_BVM_SWEPT_VOLUME_START = 4, GVX_BVM_SWEPT_VOLUME_END = 254, GVX_BVM_UNDEFINED = 255
+};
+
+enum gvx_mem_kind { GVX_MEM_HOST = 0, GVX_MEM_DEVICE = 1 };
+
+#define GVX_BITVOXEL_BYTES 32
+
+/* ---- runtime ------------------------------------------------------------------------------------------ */
+/* replaces GpuVoxels::GpuVoxels -> cuTestAndInitDevice (GV/GpuVoxels.cpp:33-42, GV/helpers/cuda_handling.cu:102-130).
+ * device < 0: use the current CUDA device. Idempotent. Fails (no exit(123)) when no GPU is present. */
+int gvx_init(int device);
+int gvx_shutdown(void);
+const char* gvx_last_error(void);
+/* cudaStream_t to enqueue on (NULL = the library's own non-blocking stream). */
+int gvx_set_stream(void* cuda_stream);
+int gvx_sync(void);
+/* getDeviceInfos / getDeviceMemoryInfo (GV/helpers/cuda_handling.cu:66-149) */
+int gvx_device_info(int* sm_count, uint64_t* free_bytes, uint64_t* total_bytes, char* name64);
+/* number of kernels this library has launched since gvx_init (bench.py reports it as gpu_launches) */
+uint64_t gvx_launch_count(void);
+
+/* ---- dense maps --------------------------------------------------------------------------------------- */
+/* GpuVoxels::addMap(MT_BITVECTOR_VOXELMAP | MT_PROBAB_VOXELMAP) -> TemplateVoxelMap ctor + clearMap
+ * (GV/GpuVoxels.cpp:164-290, GV/voxelmap/TemplateVoxelMap.hpp:54-138). */
+int gvx_map_create(gvx_handle_t* h, int map_type, uint32_t dx, uint32_t dy, uint32_t dz, float side);
+/* same, but this process holds only z in [z0,z1) of the dx*dy*dz grid */
+int gvx_map_create_slab(gvx_handle_t* h, int map_type, uint32_t dx, uint32_t dy, uint32_t dz, float side,
+                        uint32_t z0, uint32_t z1);
+/* non-owning ctor TemplateVoxelMap(Voxel* dev_data, ...) (GV/voxelmap/TemplateVoxelMap.hpp:139-148);
+ * data_d must be 32-byte aligned; not cleared */
+int gvx_map_wrap(gvx_handle_t* h, int map_type, void* data_d, uint32_t dx, uint32_t dy, uint32_t dz, float side,
+                 uint32_t z0, uint32_t z1);
+/* GpuVoxels::delMap (GV/GpuVoxels.cpp:292-302) / ~TemplateVoxelMap */
+int gvx_map_destroy(gvx_handle_t h);
+/* clearMap: memset 0x00 (Bit) / 0x80 (Prob) (GV/voxelmap/TemplateVoxelMap.hpp:205-246). Asynchronous. */
+int gvx_map_clear(gvx_handle_t h);
+/* clearBitVoxelMeaning: BitVoxelMap::clearBit (GV/voxelmap/BitVoxelMap.hpp:57-71,228-232); ProbVoxelMap accepts only
+ * eBVM_OCCUPIED and then clears the map (GV/voxelmap/ProbVoxelMap.hpp:110-116), else GVX_ERR_UNSUPPORTED */
+int gvx_map_clear_meaning(gvx_handle_t h, int meaning);
+/* BitVoxelMap::clearBits (GV/voxelmap/BitVoxelMap.hpp:73-81) */
+int gvx_map_clear_bits(gvx_handle_t h, const uint8_t mask32[GVX_BITVOXEL_BYTES]);
+/* getDeviceDataPtr / getVoidDeviceDataPtr, getDimensions, getVoxelSideLength, getMemoryUsage */
+int gvx_map_device_ptr(gvx_handle_t h, void** data_d, uint64_t* first_voxel, uint64_t* n_voxels);
+int gvx_map_info(gvx_handle_t h, int* map_type, uint32_t dims3[3], float* side, uint32_t* z0, uint32_t* z1,
+                 uint64_t* bytes);
+/* raw voxel bytes of this process's slab, reference layout (the payload of writeToDisk/readFromDisk,
+ * GV/voxelmap/TemplateVoxelMap.hpp:666-799) */
+int gvx_map_download(gvx_handle_t h, void* host_buf);
+int gvx_map_upload(gvx_handle_t h, const void* host_buf);
+
+/* ---- voxelisation ------------------------------------------------------------------------------------- */
+/* insertPointCloud (GV/voxelmap/TemplateVoxelMap.hpp:563-607, kernelInsertGlobalPointCloud
+ * GV/voxelmap/kernels/VoxelMapOperations.hpp:241-264). xyz = n packed Vector3f. ProbVoxelMap accepts only
+ * eBVM_OCCUPIED (GV/voxelmap/ProbVoxelMap.hpp:118-140) -> GVX_ERR_UNSUPPORTED otherwise, nothing inserted.
+ * any_outside (nullable): set to 1 if a point fell outside the whole grid (the reference's warning flag);
+ * NULL makes the call asynchronous. */
+int gvx_insert_points(gvx_handle_t h, const float* xyz, uint64_t n, int mem_kind, int meaning, int* any_outside);
+/* insertMetaPointCloud, both overloads (GV/voxelmap/TemplateVoxelMap.hpp:609-664, kernels
+ * GV/voxelmap/kernels/VoxelMapOperations.hpp:302-340,386-437), with the per-sub-cloud transform of
+ * MetaPointCloud::transformSubCloud (GV/helpers/MetaPointCloud.cu:624-649) optionally fused in.
+ * xyz: the concatenated clouds; cloud_sizes[n_clouds] (host); meanings[n_meanings] (host), n_meanings == 1 or
+ * n_clouds; transforms: NULL or n_clouds row-major 4x4 fp32 matrices (host). */
+int gvx_insert_meta(gvx_handle_t h, const float* xyz, int mem_kind, const uint32_t* cloud_sizes, uint32_t n_clouds,
+                    const int32_t* meanings, uint32_t n_meanings, const float* transforms, int* any_outside);
+/* PointCloud::transform / MetaPointCloud::transform (kernelTransformCloud,
+ * GV/helpers/kernels/MetaPointCloudOperations.cu:77-91); in and out are both of mem_kind; in == out allowed */
+int gvx_transform_points(const float* in_xyz, float* out_xyz, uint64_t n, int mem_kind, const float M16[16]);
+/* ProbVoxelMap::insertSensorData without ray casting / robot cut: the log-odds update
+ * (GV/voxelmap/ProbVoxelMap.hpp:52-102, kernelTransformSensorData GV/voxelmap/kernels/VoxelMapOperations.cu:27-71,
+ * kernelInsertSensorData GV/voxelmap/kernels/VoxelMapOperations.hpp:559-613). pose12 = row-major [R|t];
+ * delta_occ = cSENSOR_MODEL_OCCUPIED (72). Atomic and saturating, so no update is lost. Asynchronous. */
+int gvx_update_logodds(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int mem_kind, const float pose12[12],
+                       int delta_occ);
+
+/* ---- collision counting, map x map -------------------------------------------------------------------- */
+/* collideWith (BitVoxelMap::collideWith GV/voxelmap/BitVoxelMap.hpp:191-203, ProbVoxelMap::collideWith
+ * GV/voxelmap/ProbVoxelMap.hpp:144-155 -> collisionCheckWithCounterRelativeTransform
+ * GV/voxelmap/TemplateVoxelMap.hpp:486-519, kernelCollideVoxelMapsDebug
+ * GV/voxelmap/kernels/VoxelMapOperations.hpp:129-184). a is `this`, b is `other`; off3 (nullable) is the
+ * Vector3i offset applied to a's base pointer; voxels where the shifted index leaves a's allocation are
+ * skipped (the reference reads out of bounds there). mark != 0 reproduces the reference's side effect
+ * a[i].insert(eBVM_COLLISION) on every colliding voxel of a. */
+int gvx_collide_map_map(gvx_handle_t a, gvx_handle_t b, float thr, const int32_t off3[3], int mark, uint64_t* count);
+/* same, result (one uint64) written to device memory, no synchronisation */
+int gvx_collide_map_map_async(gvx_handle_t a, gvx_handle_t b, float thr, const int32_t off3[3], int mark,
+                              uint64_t* count_d);
+/* collisionCheck (boolean, no side effect; GV/voxelmap/TemplateVoxelMap.hpp:329-414) */
+int gvx_collide_map_map_any(gvx_handle_t a, gvx_handle_t b, float thr, int* flag);
+/* BitVoxelMap::collideWithTypes(ProbVoxelMap*) (GV/voxelmap/BitVoxelMap.hpp:212-217 -> collisionCheckBitvector :139-188,
+ * kernelCollideVoxelMapsBitvector GV/voxelmap/kernels/VoxelMapOperations.hpp:187-239, SVCollider::collide
+ * GV/voxel/SVCollider.hpp:96-106). mask_inout32 is OR-ed into (the reference does not reset it). */
+int gvx_collide_map_map_types(gvx_handle_t a, gvx_handle_t b, float thr, int mark,
+                              uint8_t mask_inout32[GVX_BITVOXEL_BYTES], uint64_t* count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GVX_H_INCLUDED */
