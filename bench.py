@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the hot path (BASELINE.json: collideWith voxels/s, % HBM peak; insert points/s).
+
+One step = one pass of the hot path over one batch: a 640x480 synthetic depth frame (307 200 points) is folded into
+the 512^3 ProbVoxelMap with the log-odds update, then that map is collided with the robot BitVectorVoxelMap
+(BASELINE.json configs[1]). value = voxels collided per second over the whole job.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+N > 1 (under torchrun, one rank per GPU, NCCL): the grid is 512 x 512 x (512*N), rank r owns z-slab r (weak scaling:
+per-GPU work fixed), every rank reads the whole N-frame cloud and voxelises only its slab, the collision counts are
+all-reduced (one int64) over NVLink.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+DX = DY = DZ = 512
+SIDE = 0.01
+FRAME_W, FRAME_H = 640, 480
+N_FRAME = FRAME_W * FRAME_H
+BYTES_PER_VOXEL = 33  # Prob (1 B) x BitVector (32 B): algorithmic bytes of the dominant kernel
+THR = 0.5
+
+
+# ---- synthetic inputs (seeded; SURVEY 8d "C2") ---------------------------------------------------------------
+def depth_frame(seed):
+    """640x480 pinhole depth image (fx=fy=525, cx=319.5, cy=239.5): back wall at 2.5 m + 3 boxes + +-1 cm noise,
+    2 % NaN pixels; points in the SENSOR frame (z forward)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    u, v = np.meshgrid(np.arange(FRAME_W, dtype=np.float32), np.arange(FRAME_H, dtype=np.float32))
+    z = np.full(u.shape, 2.5, np.float32)
+    for (u0, u1, v0, v1, d) in ((60, 220, 200, 420, 1.4), (300, 420, 120, 300, 1.9), (470, 600, 260, 470, 1.1)):
+        z[v0:v1, u0:u1] = d
+    z = (z + rng.uniform(-0.01, 0.01, size=z.shape)).astype(np.float32)
+    f = np.float32(525.0)
+    pts = np.stack([(u - np.float32(319.5)) * z / f, (v - np.float32(239.5)) * z / f, z], -1).reshape(-1, 3)
+    pts = pts.astype(np.float32)
+    pts[rng.uniform(size=len(pts)) < 0.02] = np.nan
+    return np.ascontiguousarray(pts)
+
+
+def sensor_pose(z_shift=0.0):
+    """sensor at (0.3, 2.56, 2.2 + shift) looking along +x, image-down = world -z; row-major [R|t]"""
+    return np.array([[0, 0, 1, 0.3], [-1, 0, 0, 2.56], [0, -1, 0, 2.2 + z_shift]], np.float32)
+
+
+def robot_clouds(seed=301, z_shift=0.0):
+    """7 link clouds of 50 000 surface points each (capsules, r 4-8 cm, l 10-40 cm) along an arm reaching into the
+    scene in front of the sensor; meanings 4..10 (SURVEY 8d "C3" arm, inserted once for C2)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    clouds, base = [], np.array([1.2, 2.56, 1.2 + z_shift], np.float32)
+    for k in range(7):
+        r, l = rng.uniform(0.04, 0.08), rng.uniform(0.10, 0.40)
+        t = rng.uniform(0, l, 50000); a = rng.uniform(0, 2 * np.pi, 50000)
+        d = rng.normal(size=3); d /= np.linalg.norm(d)
+        e1 = np.cross(d, [0, 0, 1.0]); e1 /= np.linalg.norm(e1); e2 = np.cross(d, e1)
+        p = base + np.outer(t, d) + r * (np.outer(np.cos(a), e1) + np.outer(np.sin(a), e2))
+        clouds.append(p.astype(np.float32))
+        base = (base + l * d * 0.9).astype(np.float32)
+        base[2] = min(max(base[2], 0.3 + z_shift), 4.5 + z_shift); base[0] = min(max(base[0], 0.8), 2.6)
+    return clouds
+
+
+# ---- clocks sampling during the timed region (B200_PROFILING.md) ---------------------------------------------
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        mhz = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(s[2 + k].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None,
+                "sm_max_mhz": int(self.samples[0][1]) if self.samples[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---- CPU arms (the ONLY places bench.py touches oracle/) ------------------------------------------------------
+SAMPLE_DZ = 32  # z sub-slab of the 512^3 grid used as the bounded CPU sample (8.4 M voxels, 277 MB of maps)
+
+
+def _cpu_sample_maps(orc):
+    """env/robot z-slab [96,128) of the same workload, built with the oracle (untimed)."""
+    dims, z0, z1 = (DX, DY, DZ), 96, 96 + SAMPLE_DZ
+    env = orc.new_map(orc.MAP_PROB, dims, z0, z1)
+    rob = orc.new_map(orc.MAP_BIT, dims, z0, z1)
+    clouds = robot_clouds()
+    orc.insert_meta(rob, orc.MAP_BIT, dims, SIDE, np.concatenate(clouds), [len(c) for c in clouds],
+                    list(range(4, 11)), None, z0, z1)
+    return dims, z0, z1, env, rob
+
+
+def cpu_arm(steps, warmup, use_ref_so=True, threads=None):
+    """One step on the host cores: log-odds update of one 307 200-point frame + collideWith (Prob x BitVector) on a
+    bounded z-sub-slab sample. Collide runs through oracle/_ref/libgvref_cpu.so (the reference's own voxel/collider
+    headers compiled with g++, OpenMP over all host threads) when it exists, else through the oracle port."""
+    from oracle import gvoracle as orc
+    dims, z0, z1, env, rob = _cpu_sample_maps(orc)
+    n_s = DX * DY * SAMPLE_DZ
+    ref = None
+    so = os.path.join(ROOT, "oracle", "_ref", "libgvref_cpu.so")
+    if use_ref_so and os.path.exists(so):
+        ref = C.CDLL(so)
+        ref.gvrefcpu_collide_map_map.restype = C.c_uint64
+        ref.gvrefcpu_collide_map_map.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_uint64, C.c_float,
+                                                 C.c_int64, C.c_int]
+        if threads:
+            ref.gvrefcpu_set_num_threads(threads)
+        cores = ref.gvrefcpu_num_threads()
+    else:
+        if threads:
+            orc.set_num_threads(threads)
+        cores = orc.num_threads()
+    frames = [depth_frame(201 + k) for k in range(2)]
+    pose = sensor_pose()
+
+    def step(k):
+        orc.update_logodds(env, dims, SIDE, frames[k % 2], pose, 72, z0, z1)
+        if ref is not None:
+            return ref.gvrefcpu_collide_map_map(env.ctypes.data, 4, rob.ctypes.data, 0, n_s, THR, 0, 1)
+        return orc.collide_map_map(env, orc.MAP_PROB, rob, orc.MAP_BIT, n_s, THR, 0, True)
+
+    for k in range(warmup):
+        step(k)
+    t0 = time.perf_counter()
+    for k in range(steps):
+        cnt = step(warmup + k)
+    dt = time.perf_counter() - t0
+    return {"value": n_s * steps / dt, "unit": "voxels/s", "cores": int(cores),
+            "kind": "reference" if ref is not None else "port",
+            "sample": "z-slab [96,128) of the 512^3 grid (%d voxels/step, Prob x BitVector collide + one 307200-point "
+                      "log-odds frame), %d steps; collide = %s" % (n_s, steps, "reference voxel/collider headers (g++ -O2 "
+                      "-fopenmp)" if ref is not None else "oracle C port (gcc -O2 -fopenmp)"),
+            "ms_per_step": dt / steps * 1e3, "last_count": int(cnt)}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    r = cpu_arm(args.steps, args.warmup)
+    line = {"impl": "reference", "metric": "collideWith voxels/s", "value": r["value"], "unit": "voxels/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": workload_config(args.gpus),
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": "voxels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "the reference has no CPU path and its library cannot be built here (Boost/icl_core absent); this arm "
+                    "runs the reference's own host-callable voxel/collider code in an OpenMP loop on the host cores"}
+    print(json.dumps(line))
+
+
+def workload_config(n_gpus):
+    return {"workload": "BASELINE.json configs[1]: 512^3 ProbVoxelMap @1cm, per step one 640x480 depth frame (307200 pts) "
+                        "log-odds insert then collideWith a 512^3 robot BitVectorVoxelMap (7 links, 350k pts)",
+            "grid": [DX, DY, DZ * n_gpus], "voxels_per_gpu": DX * DY * DZ, "points_per_step": N_FRAME * n_gpus,
+            "coll_threshold": THR, "mark_collisions": True,
+            "l2": "inputs larger than L2 (4.43 GB streamed per collide vs 126 MB L2)",
+            "parallelism": "z-slab x%d" % n_gpus if n_gpus > 1 else "single GPU"}
+
+
+# ---- the GPU arm ------------------------------------------------------------------------------------------------
+def run_gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    import gpu_voxels_b200 as gv
+    from gpu_voxels_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    L = _lib.init(local_rank)
+    stream = torch.cuda.current_stream()
+    _lib.check(L.gvx_set_stream(C.c_void_p(stream.cuda_stream)))  # torch events then time libgvx's kernels
+
+    n_vox = DX * DY * DZ
+    dims = (DX, DY, DZ * world)
+    slab = (DZ * rank, DZ * (rank + 1))
+    env = gv.ProbVoxelMap(dims, SIDE, slab=slab)
+    rob = gv.BitVectorVoxelMap(dims, SIDE, slab=slab)
+    # robot: every slab holds its own copy of the arm (inserted once, untimed); global cloud = all copies
+    rclouds = [np.concatenate([c for r in range(world) for c in [robot_clouds(z_shift=DZ * SIDE * r)[k]]]) for k in range(7)]
+    rob.insertMetaPointCloud(gv.MetaPointCloud(rclouds), list(range(4, 11)))
+    # frames: N sub-frames (one per slab) concatenated into one global cloud; every rank reads all of it
+    poses = [sensor_pose(DZ * SIDE * r) for r in range(world)]
+    frames_h = [[depth_frame(201 + 2 * r + k) for r in range(world)] for k in range(2)]  # [parity][slab] sensor frame
+    pinned = [[torch.from_numpy(f).pin_memory() for f in fr] for fr in frames_h]
+    frames_d = [[p.cuda(non_blocking=True) for p in fr] for fr in pinned]
+    count_d = torch.zeros(1, dtype=torch.int64, device="cuda")
+    pose_arr = [np.ascontiguousarray(p.reshape(-1)) for p in poses]
+
+    def step_device(k):
+        """inputs resident in HBM; result stays on the device (all-reduced when sharded)"""
+        for r in range(world):
+            f = frames_d[k % 2][r]
+            _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
+                                            pose_arr[r].ctypes.data_as(C.c_void_p), 72))
+        _lib.check(L.gvx_collide_map_map_async(env.handle, rob.handle, THR, None, 1, C.c_void_p(count_d.data_ptr())))
+        if world > 1:
+            dist.all_reduce(count_d)
+
+    def step_e2e(k):
+        """through the C ABI with HOST buffers: H2D of the frame inside, count read back to the host"""
+        for r in range(world):
+            f = pinned[k % 2][r]
+            _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_HOST,
+                                            pose_arr[r].ctypes.data_as(C.c_void_p), 72))
+        if world > 1:
+            _lib.check(L.gvx_collide_map_map_async(env.handle, rob.handle, THR, None, 1, C.c_void_p(count_d.data_ptr())))
+            dist.all_reduce(count_d)
+            return int(count_d.item())
+        cnt = C.c_uint64(0)
+        _lib.check(L.gvx_collide_map_map(env.handle, rob.handle, THR, None, 1, C.byref(cnt)))
+        return cnt.value
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, per_kernel=False):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ev0.record(stream)
+        for k in range(steps):
+            fn(k)
+        ev1.record(stream)
+        barrier()
+        ms = torch.tensor([ev0.elapsed_time(ev1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for k in range(max(args.warmup, 3)):
+        step_device(k)
+        step_e2e(k)
+    # dominant kernel alone (collide), CUDA events on the launching stream, same maps, inputs >> L2
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches0 = L.gvx_launch_count()
+    with ClockSampler(local_rank) as clk:
+        ms_total = timed(step_device, args.steps)
+        launches = L.gvx_launch_count() - launches0
+        ms_e2e = timed(step_e2e, args.steps)
+        barrier()
+        for e0, e1 in kev:
+            e0.record(stream)
+            _lib.check(L.gvx_collide_map_map_async(env.handle, rob.handle, THR, None, 1, C.c_void_p(count_d.data_ptr())))
+            e1.record(stream)
+        torch.cuda.synchronize()
+        # insertion alone: points/s of the log-odds frame update (atomic-bound; reported beside the headline)
+        evi0, evi1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        evi0.record(stream)
+        for k in range(args.steps):
+            f = frames_d[k % 2][rank]
+            _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
+                                            pose_arr[rank].ctypes.data_as(C.c_void_p), 72))
+        evi1.record(stream)
+        torch.cuda.synchronize()
+    k_ms = sorted(e0.elapsed_time(e1) for e0, e1 in kev)
+    k_avg = sum(k_ms) / len(k_ms)
+    ins_ms = evi0.elapsed_time(evi1) / args.steps
+    last_count = step_e2e(0)
+
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        achieved = BYTES_PER_VOXEL * n_vox / (k_avg * 1e-3) / 1e9
+        traffic = None
+        tfile = os.path.join(ROOT, "profiles", "collide_traffic.json")
+        if os.path.exists(tfile):
+            try:
+                traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        cpu = cpu_arm(2, 1) if world == 1 and not args.no_cpu_baseline else None
+        line = {
+            "metric": "collideWith voxels/s", "value": n_vox * world * args.steps / (ms_total * 1e-3), "unit": "voxels/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": workload_config(world),
+            "e2e": {"value": n_vox * world * args.steps / (ms_e2e * 1e-3), "unit": "voxels/s",
+                    "h2d_bytes_per_step": N_FRAME * 12 * world + 48 * world, "d2h_bytes_per_step": 8,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k_collide_voxelwise<Prob,Bit,mark>", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": BYTES_PER_VOXEL * n_vox, "kernel_ms_avg": k_avg,
+                         "kernel_ms_min": k_ms[0], "frac_of_8000_nominal": achieved / 8000.0},
+            "insert": {"metric": "insertSensorData (log-odds) points/s", "value": N_FRAME / (ins_ms * 1e-3),
+                       "unit": "points/s", "ms_per_frame": ins_ms, "points": N_FRAME},
+            "clocks": clk.summary(), "collisions_last_step": int(last_count),
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()
