@@ -57,19 +57,19 @@ def sensor_pose(z_shift=0.0):
 
 
 def robot_clouds(seed=301, z_shift=0.0):
-    """7 link clouds of 50 000 surface points each (capsules, r 4-8 cm, l 10-40 cm) along an arm reaching into the
-    scene in front of the sensor; meanings 4..10 (SURVEY 8d "C3" arm, inserted once for C2)."""
+    """7 link clouds of 50 000 surface points each (capsules, r 4-8 cm, l 10-40 cm): an arm that starts in front of
+    the sensor and reaches +x through the face of the first box of the depth scene (so there ARE collisions);
+    meanings 4..10 (SURVEY 8d "C3" arm, inserted once for C2)."""
     rng = np.random.Generator(np.random.PCG64(seed))
-    clouds, base = [], np.array([1.2, 2.56, 1.2 + z_shift], np.float32)
+    clouds, base = [], np.array([1.25, 3.0, 2.0 + z_shift])
     for k in range(7):
         r, l = rng.uniform(0.04, 0.08), rng.uniform(0.10, 0.40)
         t = rng.uniform(0, l, 50000); a = rng.uniform(0, 2 * np.pi, 50000)
-        d = rng.normal(size=3); d /= np.linalg.norm(d)
+        d = np.array([1.0, rng.uniform(-0.25, 0.25), rng.uniform(-0.25, 0.25)]); d /= np.linalg.norm(d)
         e1 = np.cross(d, [0, 0, 1.0]); e1 /= np.linalg.norm(e1); e2 = np.cross(d, e1)
         p = base + np.outer(t, d) + r * (np.outer(np.cos(a), e1) + np.outer(np.sin(a), e2))
-        clouds.append(p.astype(np.float32))
-        base = (base + l * d * 0.9).astype(np.float32)
-        base[2] = min(max(base[2], 0.3 + z_shift), 4.5 + z_shift); base[0] = min(max(base[0], 0.8), 2.6)
+        clouds.append(np.ascontiguousarray(p, dtype=np.float32))
+        base = base + l * d * 0.9
     return clouds
 
 
@@ -223,8 +223,11 @@ def run_gpu_arm(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     L = _lib.init(local_rank)
-    stream = torch.cuda.current_stream()
-    _lib.check(L.gvx_set_stream(C.c_void_p(stream.cuda_stream)))  # torch events then time libgvx's kernels
+    # one explicit (non-default) stream shared by libgvx, torch events and NCCL, so CUDA events time libgvx's kernels
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
+    _lib.check(L.gvx_set_stream(C.c_void_p(stream.cuda_stream)))
 
     n_vox = DX * DY * DZ
     dims = (DX, DY, DZ * world)

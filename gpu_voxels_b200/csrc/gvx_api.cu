@@ -38,7 +38,10 @@ struct Context {
   ResultBlock* result_hmap_d = nullptr;  // device alias of result_h
   // staging: device buffer for host point clouds, pinned + device buffers for small descriptors
   void* stage_d = nullptr; size_t stage_cap = 0;
-  void* desc_h = nullptr; void* desc_d = nullptr; size_t desc_cap = 0;
+  // ring of small descriptor slots (pinned host + device + "H2D done" event): no stream sync per call
+  static constexpr int kDescSlots = 8;
+  void* desc_h[kDescSlots] = {}; void* desc_d[kDescSlots] = {}; size_t desc_cap[kDescSlots] = {};
+  cudaEvent_t desc_ev[kDescSlots] = {}; int desc_next = 0;
   uint64_t launches = 0;
   uint64_t next_handle = 1;
   std::unordered_map<uint64_t, Map> maps;
@@ -80,16 +83,29 @@ static int ensure_stage(size_t bytes) {
   g.stage_cap = cap;
   return GVX_OK;
 }
-static int ensure_desc(size_t bytes) {
-  if (bytes <= g.desc_cap) return GVX_OK;
-  GVX_CUDA(cudaStreamSynchronize(g.stream));
-  if (g.desc_h) cudaFreeHost(g.desc_h);
-  if (g.desc_d) cudaFree(g.desc_d);
-  g.desc_h = g.desc_d = nullptr; g.desc_cap = 0;
-  size_t cap = bytes * 2 + 4096;
-  GVX_CUDA(cudaHostAlloc(&g.desc_h, cap, cudaHostAllocDefault));
-  GVX_CUDA(cudaMalloc(&g.desc_d, cap));
-  g.desc_cap = cap;
+// Acquire the next descriptor slot with room for `bytes`; waits only if that slot's previous H2D copy (8 calls
+// ago) has not finished. Fill *h, then call desc_commit to copy it to *d on the stream.
+static int desc_acquire(size_t bytes, int* slot, void** h, void** d) {
+  const int k = g.desc_next;
+  g.desc_next = (g.desc_next + 1) % Context::kDescSlots;
+  if (!g.desc_ev[k]) GVX_CUDA(cudaEventCreateWithFlags(&g.desc_ev[k], cudaEventDisableTiming));
+  GVX_CUDA(cudaEventSynchronize(g.desc_ev[k]));
+  if (bytes > g.desc_cap[k]) {
+    GVX_CUDA(cudaStreamSynchronize(g.stream));  // a kernel may still read the old device slot
+    if (g.desc_h[k]) cudaFreeHost(g.desc_h[k]);
+    if (g.desc_d[k]) cudaFree(g.desc_d[k]);
+    g.desc_h[k] = g.desc_d[k] = nullptr; g.desc_cap[k] = 0;
+    const size_t cap = bytes * 2 + 4096;
+    GVX_CUDA(cudaHostAlloc(&g.desc_h[k], cap, cudaHostAllocDefault));
+    GVX_CUDA(cudaMalloc(&g.desc_d[k], cap));
+    g.desc_cap[k] = cap;
+  }
+  *slot = k; *h = g.desc_h[k]; *d = g.desc_d[k];
+  return GVX_OK;
+}
+static int desc_commit(int slot, size_t bytes) {
+  GVX_CUDA(cudaMemcpyAsync(g.desc_d[slot], g.desc_h[slot], bytes, cudaMemcpyHostToDevice, g.stream));
+  GVX_CUDA(cudaEventRecord(g.desc_ev[slot], g.stream));
   return GVX_OK;
 }
 // Points to device: host clouds go through the staging buffer (one async H2D, no per-call cudaMalloc/cudaFree
@@ -148,11 +164,15 @@ int gvx_shutdown(void) {
   for (auto& kv : g.maps) if (kv.second.owned && kv.second.data) cudaFree(kv.second.data);
   g.maps.clear();
   if (g.stage_d) cudaFree(g.stage_d);
-  if (g.desc_d) cudaFree(g.desc_d);
-  if (g.desc_h) cudaFreeHost(g.desc_h);
+  for (int k = 0; k < Context::kDescSlots; ++k) {
+    if (g.desc_d[k]) cudaFree(g.desc_d[k]);
+    if (g.desc_h[k]) cudaFreeHost(g.desc_h[k]);
+    if (g.desc_ev[k]) cudaEventDestroy(g.desc_ev[k]);
+    g.desc_d[k] = g.desc_h[k] = nullptr; g.desc_cap[k] = 0; g.desc_ev[k] = nullptr;
+  }
   cudaFree(g.scratch_d); cudaFree(g.result_d); cudaFreeHost(g.result_h);
   cudaStreamDestroy(g.own_stream);
-  g.stage_d = g.desc_d = g.desc_h = nullptr; g.stage_cap = g.desc_cap = 0;
+  g.stage_d = nullptr; g.stage_cap = 0;
   g.ready = false;
   return GVX_OK;
 }
@@ -163,6 +183,8 @@ int gvx_set_stream(void* cuda_stream) {
   std::lock_guard<std::mutex> lk(g.mu);
   GVX_NEED_INIT();
   GVX_CUDA(cudaStreamSynchronize(g.stream));
+  // NULL selects the library's own non-blocking stream; pass cudaStreamLegacy / cudaStreamPerThread (or any created
+  // stream) explicitly to share a stream with the host program.
   g.stream = cuda_stream ? (cudaStream_t)cuda_stream : g.own_stream;
   return GVX_OK;
 }
@@ -366,26 +388,27 @@ int gvx_insert_meta(gvx_handle_t h, const float* xyz, int mem_kind, const uint32
   // descriptor = prefix[n_clouds+1] | meanings[n_meanings] | transforms[n_clouds*16], one async H2D
   const size_t off_mg = ((size_t)n_clouds + 1) * 4, off_tr = off_mg + (size_t)n_meanings * 4;
   const size_t total = off_tr + (transforms ? (size_t)n_clouds * 64 : 0);
-  int rc = ensure_desc(total);
+  int slot; void *dh, *dd;
+  int rc = desc_acquire(total, &slot, &dh, &dd);
   if (rc) return rc;
-  GVX_CUDA(cudaStreamSynchronize(g.stream));  // the pinned descriptor may still be read by an earlier async copy
-  uint32_t* prefix = (uint32_t*)g.desc_h;
+  uint32_t* prefix = (uint32_t*)dh;
   uint64_t acc = 0;
   for (uint32_t c = 0; c < n_clouds; ++c) { prefix[c] = (uint32_t)acc; acc += cloud_sizes[c]; }
   if (acc > 0xFFFFFFFFull) return fail(GVX_ERR_INVALID, "MetaPointCloud larger than 2^32-1 points");
   prefix[n_clouds] = (uint32_t)acc;
-  memcpy((char*)g.desc_h + off_mg, meanings, (size_t)n_meanings * 4);
-  if (transforms) memcpy((char*)g.desc_h + off_tr, transforms, (size_t)n_clouds * 64);
+  memcpy((char*)dh + off_mg, meanings, (size_t)n_meanings * 4);
+  if (transforms) memcpy((char*)dh + off_tr, transforms, (size_t)n_clouds * 64);
   if (acc == 0) return GVX_OK;
   if (!xyz) return fail(GVX_ERR_INVALID, "null point pointer");
-  GVX_CUDA(cudaMemcpyAsync(g.desc_d, g.desc_h, total, cudaMemcpyHostToDevice, g.stream));
+  rc = desc_commit(slot, total);
+  if (rc) return rc;
   const float* xyz_d = nullptr;
   rc = points_to_device(xyz, acc, mem_kind, &xyz_d);
   if (rc) return rc;
   MetaDesc d;
-  d.prefix_d = (const uint32_t*)g.desc_d;
-  d.meanings_d = (const int32_t*)((char*)g.desc_d + off_mg);
-  d.transforms_d = transforms ? (const float*)((char*)g.desc_d + off_tr) : nullptr;
+  d.prefix_d = (const uint32_t*)dd;
+  d.meanings_d = (const int32_t*)((char*)dd + off_mg);
+  d.transforms_d = transforms ? (const float*)((char*)dd + off_tr) : nullptr;
   d.n_clouds = n_clouds;
   d.n_meanings = n_meanings;
   GVX_CUDA(launch_insert_meta(lctx(), m->view(), xyz_d, acc, d, any_outside != nullptr));
@@ -397,19 +420,16 @@ int gvx_transform_points(const float* in_xyz, float* out_xyz, uint64_t n, int me
   GVX_NEED_INIT();
   if (n == 0) return GVX_OK;
   if (!in_xyz || !out_xyz || !M16) return fail(GVX_ERR_INVALID, "null pointer");
-  int rc = ensure_desc(64);
-  if (rc) return rc;
-  GVX_CUDA(cudaStreamSynchronize(g.stream));
-  memcpy(g.desc_h, M16, 64);
-  GVX_CUDA(cudaMemcpyAsync(g.desc_d, g.desc_h, 64, cudaMemcpyHostToDevice, g.stream));
+  Affine12 M;
+  memcpy(M.a, M16, 48);
   if (mem_kind == GVX_MEM_DEVICE) {
-    GVX_CUDA(launch_transform(lctx(), in_xyz, out_xyz, n, (const float*)g.desc_d));
+    GVX_CUDA(launch_transform(lctx(), in_xyz, out_xyz, n, M));
     return GVX_OK;
   }
   const float* in_d = nullptr;
-  rc = points_to_device(in_xyz, n, mem_kind, &in_d);
+  int rc = points_to_device(in_xyz, n, mem_kind, &in_d);
   if (rc) return rc;
-  GVX_CUDA(launch_transform(lctx(), in_d, (float*)g.stage_d, n, (const float*)g.desc_d));
+  GVX_CUDA(launch_transform(lctx(), in_d, (float*)g.stage_d, n, M));
   GVX_CUDA(cudaMemcpyAsync(out_xyz, g.stage_d, (size_t)n * 12, cudaMemcpyDeviceToHost, g.stream));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   return GVX_OK;
@@ -425,15 +445,12 @@ int gvx_update_logodds(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int 
   if (delta_occ < -127 || delta_occ > 127) return fail(GVX_ERR_INVALID, "delta %d outside int8 range", delta_occ);
   if (n == 0) return GVX_OK;
   if (!xyz_sensor || !pose12) return fail(GVX_ERR_INVALID, "null pointer");
-  int rc = ensure_desc(48);
-  if (rc) return rc;
-  GVX_CUDA(cudaStreamSynchronize(g.stream));
-  memcpy(g.desc_h, pose12, 48);
-  GVX_CUDA(cudaMemcpyAsync(g.desc_d, g.desc_h, 48, cudaMemcpyHostToDevice, g.stream));
+  Affine12 P;
+  memcpy(P.a, pose12, 48);
   const float* xyz_d = nullptr;
-  rc = points_to_device(xyz_sensor, n, mem_kind, &xyz_d);
+  int rc = points_to_device(xyz_sensor, n, mem_kind, &xyz_d);
   if (rc) return rc;
-  GVX_CUDA(launch_update_logodds(lctx(), m->view(), xyz_d, n, (const float*)g.desc_d, delta_occ));
+  GVX_CUDA(launch_update_logodds(lctx(), m->view(), xyz_d, n, P, delta_occ));
   return GVX_OK;
 }
 

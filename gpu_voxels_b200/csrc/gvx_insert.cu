@@ -110,10 +110,8 @@ k_insert(MapView m, const float* __restrict__ xyz, unsigned long long n, int mea
 }
 
 __global__ void __launch_bounds__(kInsThreads)
-k_transform(const float* __restrict__ in, float* __restrict__ out, unsigned long long n, const float* __restrict__ M16) {
-  __shared__ float M[12];
-  if (threadIdx.x < 12) M[threadIdx.x] = M16[threadIdx.x];
-  __syncthreads();
+k_transform(const float* __restrict__ in, float* __restrict__ out, unsigned long long n, const Affine12 Mv) {
+  const float* M = Mv.a;
   const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
   for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n; i += stride) {
     const float x = in[3 * i], y = in[3 * i + 1], z = in[3 * i + 2];
@@ -143,11 +141,8 @@ __device__ __forceinline__ void logodds_add(int8_t* map, uint64_t idx, int total
 // with the reference's double-precision factor when the world point is below the floor), NaN filter, bounds
 // test on the point and on the sensor origin, updateOccupancy(+delta) at the hit voxel.
 __global__ void __launch_bounds__(kInsThreads)
-k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n, const float* __restrict__ pose12,
-                 int delta) {
-  __shared__ float P[12];
-  if (threadIdx.x < 12) P[threadIdx.x] = pose12[threadIdx.x];
-  __syncthreads();
+k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n, const Affine12 pose, int delta) {
+  const float* P = pose.a;
   const uint32_t sx = coord_to_voxel(P[3], m.side), sy = coord_to_voxel(P[7], m.side), sz = coord_to_voxel(P[11], m.side);
   const bool sensor_inside = sx < m.dx && sy < m.dy && sz < m.dz;
   const uint64_t slab = (uint64_t)m.dx * m.dy;
@@ -225,16 +220,16 @@ cudaError_t launch_insert_meta(const LaunchCtx& c, const MapView& m, const float
   return cudaGetLastError();
 }
 
-cudaError_t launch_transform(const LaunchCtx& c, const float* in_d, float* out_d, uint64_t n, const float* M16_d) {
+cudaError_t launch_transform(const LaunchCtx& c, const float* in_d, float* out_d, uint64_t n, const Affine12& M) {
   ++*c.launches;
-  k_transform<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(in_d, out_d, n, M16_d);
+  k_transform<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(in_d, out_d, n, M);
   return cudaGetLastError();
 }
 
 cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
-                                  const float* pose12_d, int delta) {
+                                  const Affine12& pose, int delta) {
   ++*c.launches;
-  k_update_logodds<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, n, pose12_d, delta);
+  k_update_logodds<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, n, pose, delta);
   return cudaGetLastError();
 }
 

@@ -40,9 +40,10 @@ cudaError_t launch_insert_points(const LaunchCtx& c, const MapView& m, const flo
                                  bool want_flag);
 cudaError_t launch_insert_meta(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
                                const MetaDesc& d, bool want_flag);
-cudaError_t launch_transform(const LaunchCtx& c, const float* in_d, float* out_d, uint64_t n, const float* M16_d);
+struct Affine12 { float a[12]; };  // row-major [R|t], passed to kernels by value (no H2D copy, no sync)
+cudaError_t launch_transform(const LaunchCtx& c, const float* in_d, float* out_d, uint64_t n, const Affine12& M);
 cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
-                                  const float* pose12_d, int delta);
+                                  const Affine12& pose, int delta);
 cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8]);
 
 }  // namespace gvx
