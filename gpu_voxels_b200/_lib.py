@@ -44,6 +44,22 @@ SIGNATURES = {
     "gvx_collide_map_map_async": (C.c_int, [u64, u64, f32, vp, C.c_int, vp]),
     "gvx_collide_map_map_any": (C.c_int, [u64, u64, f32, P(C.c_int)]),
     "gvx_collide_map_map_types": (C.c_int, [u64, u64, f32, C.c_int, vp, P(u64)]),
+    "gvx_list_create": (C.c_int, [P(u64), u32, u32, u32, f32]),
+    "gvx_list_destroy": (C.c_int, [u64]),
+    "gvx_list_clear": (C.c_int, [u64]),
+    "gvx_list_size": (C.c_int, [u64, P(u64)]),
+    "gvx_list_insert_points": (C.c_int, [u64, vp, u64, C.c_int, C.c_int]),
+    "gvx_list_insert_meta": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, u32]),
+    "gvx_list_download": (C.c_int, [u64, vp, vp, vp]),
+    "gvx_list_upload": (C.c_int, [u64, vp, vp, vp, u64]),
+    "gvx_list_device_ptrs": (C.c_int, [u64, P(vp), P(vp), P(vp), P(u64)]),
+    "gvx_collide_list_map": (C.c_int, [u64, u64, f32, vp, C.c_int, P(u64)]),
+    "gvx_collide_list_map_async": (C.c_int, [u64, u64, f32, vp, C.c_int, vp]),
+    "gvx_collide_list_map_types": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),
+    "gvx_collide_list_map_mask": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),
+    "gvx_collide_list_map_per_meaning": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),
+    "gvx_batch_robot_collide": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, vp, u32, vp, f32, vp]),
+    "gvx_batch_set_scratch_budget": (C.c_int, [u64]),
 }
 
 

@@ -285,6 +285,28 @@ def transform_points(points, matrix4):
     return out
 
 
+def batch_robot_collide(env_map, meta_point_cloud, voxel_meanings, transforms, types_to_check=None, coll_threshold=1.0):
+    """counts[c] of the planner's state check (gvl_ompl_planning/gvl_ompl_planner_helper.cpp:169-202) for every
+    configuration c in ONE call: robot cleared, link clouds transformed by transforms[c] (n_cfg x n_links x 4 x 4),
+    inserted with per-link meanings, collided with env_map. types_to_check: optional BitVectorVoxel collision mask."""
+    L = _lib.init()
+    sizes = np.asarray(meta_point_cloud.getPointcloudSizes(), np.uint32)
+    mg = np.ascontiguousarray(np.broadcast_to(np.asarray(voxel_meanings, np.int32), (len(sizes),)))
+    xyz = meta_point_cloud.accumulated()
+    tr = np.ascontiguousarray(transforms, np.float32).reshape(-1, len(sizes), 16)
+    counts = np.zeros(tr.shape[0], np.uint64)
+    mk = None
+    if types_to_check is not None:
+        mk = np.ascontiguousarray(types_to_check.bytes if isinstance(types_to_check, BitVectorVoxel) else types_to_check,
+                                  np.uint8)
+    _lib.check(L.gvx_batch_robot_collide(env_map.handle, xyz.ctypes.data_as(C.c_void_p), MEM_HOST,
+                                         sizes.ctypes.data_as(C.c_void_p), len(sizes), mg.ctypes.data_as(C.c_void_p),
+                                         tr.ctypes.data_as(C.c_void_p), tr.shape[0],
+                                         mk.ctypes.data_as(C.c_void_p) if mk is not None else None,
+                                         coll_threshold, counts.ctypes.data_as(C.c_void_p)))
+    return counts
+
+
 class GpuVoxels:
     """The singleton facade (GV/GpuVoxels.h:91-415, GV/GpuVoxels.cpp:33-78,164-313,443-559)."""
     _instance = None

@@ -1,0 +1,322 @@
+// gvx_api_list.cu -- C ABI of the BitVectorVoxelList path (include/gvx.h, "voxel lists" section).
+#include "gvx_context.h"
+
+using namespace gvx;
+
+namespace {
+
+void list_free(VoxList& l) {
+  for (int k = 0; k < 2; ++k) {
+    if (l.ids[k]) cudaFree(l.ids[k]);
+    if (l.coords[k]) cudaFree(l.coords[k]);
+    if (l.voxels[k]) cudaFree(l.voxels[k]);
+    l.ids[k] = l.coords[k] = nullptr; l.voxels[k] = nullptr; l.cap[k] = 0;
+  }
+  if (l.keys_in) cudaFree(l.keys_in);
+  if (l.keys_out) cudaFree(l.keys_out);
+  if (l.vals_in) cudaFree(l.vals_in);
+  if (l.vals_out) cudaFree(l.vals_out);
+  if (l.new_meaning) cudaFree(l.new_meaning);
+  if (l.tmp) cudaFree(l.tmp);
+  l.keys_in = l.keys_out = l.vals_in = l.vals_out = nullptr; l.new_meaning = nullptr; l.tmp = nullptr;
+  l.tmp_bytes = 0; l.scratch_cap = l.meaning_cap = 0; l.size = 0;
+}
+
+// storage buffer `k` with room for `n` entries (contents are NOT preserved: only ever called on the non-current buffer
+// or on an empty list)
+int list_reserve(VoxList& l, int k, uint64_t n) {
+  if (n <= l.cap[k]) return GVX_OK;
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (l.ids[k]) cudaFree(l.ids[k]);
+  if (l.coords[k]) cudaFree(l.coords[k]);
+  if (l.voxels[k]) cudaFree(l.voxels[k]);
+  l.ids[k] = l.coords[k] = nullptr; l.voxels[k] = nullptr; l.cap[k] = 0;
+  const uint64_t cap = n + n / 4 + 1024;
+  GVX_CUDA(cudaMalloc(&l.ids[k], cap * 4));
+  GVX_CUDA(cudaMalloc(&l.coords[k], cap * 12));
+  GVX_CUDA(cudaMalloc(&l.voxels[k], cap * kBitVoxelBytes));
+  l.cap[k] = cap;
+  return GVX_OK;
+}
+
+int list_reserve_scratch(VoxList& l, uint64_t total, uint64_t n_new) {
+  if (total > l.scratch_cap) {
+    GVX_CUDA(cudaStreamSynchronize(g.stream));
+    if (l.keys_in) cudaFree(l.keys_in);
+    if (l.keys_out) cudaFree(l.keys_out);
+    if (l.vals_in) cudaFree(l.vals_in);
+    if (l.vals_out) cudaFree(l.vals_out);
+    if (l.tmp) cudaFree(l.tmp);
+    l.keys_in = l.keys_out = l.vals_in = l.vals_out = nullptr; l.tmp = nullptr; l.scratch_cap = 0;
+    const uint64_t cap = total + total / 4 + 1024;
+    GVX_CUDA(cudaMalloc(&l.keys_in, cap * 4));
+    GVX_CUDA(cudaMalloc(&l.keys_out, cap * 4));
+    GVX_CUDA(cudaMalloc(&l.vals_in, cap * 4));
+    GVX_CUDA(cudaMalloc(&l.vals_out, cap * 4));
+    l.tmp_bytes = list_sort_temp_bytes(cap) + 256;
+    GVX_CUDA(cudaMalloc(&l.tmp, l.tmp_bytes));
+    l.scratch_cap = cap;
+  }
+  if (n_new > l.meaning_cap) {
+    GVX_CUDA(cudaStreamSynchronize(g.stream));
+    if (l.new_meaning) cudaFree(l.new_meaning);
+    l.new_meaning = nullptr; l.meaning_cap = 0;
+    const uint64_t cap = n_new + n_new / 4 + 1024;
+    GVX_CUDA(cudaMalloc(&l.new_meaning, cap));
+    l.meaning_cap = cap;
+  }
+  return GVX_OK;
+}
+
+int list_insert(VoxList& l, const float* xyz_d, uint64_t n, const MetaDesc& meta, int single_meaning) {
+  const uint64_t total = l.size + n;
+  if (total >= 0xFFFFFFFFull) return fail(GVX_ERR_INVALID, "voxel list would exceed 2^32-1 entries");
+  const int nxt = l.cur ^ 1;
+  int rc = list_reserve(l, nxt, total);
+  if (rc) return rc;
+  rc = list_reserve_scratch(l, total, n);
+  if (rc) return rc;
+  ListBuild b{};
+  b.old_ids = l.ids[l.cur]; b.old_coords = l.coords[l.cur]; b.old_voxels = l.voxels[l.cur]; b.old_size = l.size;
+  b.xyz_d = xyz_d; b.n_new = n;
+  b.dx = l.dx; b.dy = l.dy; b.side = l.side;
+  b.meta = meta; b.single_meaning = single_meaning;
+  b.keys_in = l.keys_in; b.keys_out = l.keys_out; b.vals_in = l.vals_in; b.vals_out = l.vals_out;
+  b.new_meaning = l.new_meaning; b.tmp = l.tmp; b.tmp_bytes = l.tmp_bytes;
+  b.out_ids = l.ids[nxt]; b.out_coords = l.coords[nxt]; b.out_voxels = l.voxels[nxt];
+  GVX_CUDA(launch_list_build(lctx(), b));
+  // the list size is a host value in the reference too (make_unique resizes the vectors)
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  l.size = g.result_h->count;
+  l.cur = nxt;
+  return GVX_OK;
+}
+
+struct ListCollideArgs {
+  VoxList* l; Map* m; int64_t off;
+};
+int list_collide_prepare(gvx_handle_t hl, gvx_handle_t hm, const int32_t off3[3], ListCollideArgs* a) {
+  a->l = find_list(hl);
+  a->m = find_map(hm);
+  if (!a->l || !a->m) return fail(GVX_ERR_INVALID, "unknown list or map handle");
+  // TemplateVoxelList::collisionCheckWithCollider: differing reference dimensions -> SSIZE_MAX
+  // (GV/voxellist/TemplateVoxelList.hpp:737-742)
+  if (a->l->dx != a->m->dx || a->l->dy != a->m->dy || a->l->dz != a->m->dz)
+    return fail(GVX_ERR_DIM_MISMATCH, "list and map have different reference dimensions");
+  a->off = off3 ? (int64_t)off3[2] * a->m->dx * a->m->dy + (int64_t)off3[1] * a->m->dx + (int64_t)off3[0] : 0;
+  return GVX_OK;
+}
+
+int list_collide(int mode, gvx_handle_t hl, gvx_handle_t hm, float thr, const int32_t off3[3], int mark,
+                 const uint8_t* mask_in32, uint8_t* mask_out32, uint64_t* counts256, uint64_t* count) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  ListCollideArgs a;
+  int rc = list_collide_prepare(hl, hm, off3, &a);
+  if (rc) return rc;
+  if (mode == 2 && !mask_in32) return fail(GVX_ERR_INVALID, "null types_to_check mask");
+  uint32_t mk[8] = {0};
+  if (mask_in32) memcpy(mk, mask_in32, 32);
+  if (a.l->size == 0) {  // the reference launches nothing useful on an empty list; result is 0
+    if (count) *count = 0;
+    if (mode == 1 && mask_out32) memset(mask_out32, 0, 32);
+    if (mode == 3 && counts256) memset(counts256, 0, 256 * sizeof(uint64_t));
+    return GVX_OK;
+  }
+  GVX_CUDA(launch_collide_list_map(lctx(), mode, a.l->ids[a.l->cur], a.l->voxels[a.l->cur], a.l->size, a.m->data,
+                                   a.m->type, a.m->n_total(), (uint64_t)a.m->z0 * a.m->dx * a.m->dy, a.m->n_voxels(),
+                                   float_to_probability(thr), thr, a.off, mark != 0, mk, nullptr));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (count) *count = g.result_h->count;
+  if (mode == 1 && mask_out32) memcpy(mask_out32, g.result_h->mask, 32);  // cleared first, BitVoxelList.hpp:163
+  if (mode == 3 && counts256) memcpy(counts256, g.result_h->per_meaning, 256 * sizeof(uint64_t));
+  return GVX_OK;
+}
+
+}  // namespace
+
+namespace gvx {
+void lists_free_all() {
+  for (auto& kv : g.lists) list_free(kv.second);
+  g.lists.clear();
+}
+}  // namespace gvx
+
+extern "C" {
+
+int gvx_list_create(gvx_handle_t* h, uint32_t dx, uint32_t dy, uint32_t dz, float side) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  if (!h) return fail(GVX_ERR_INVALID, "null handle pointer");
+  if (!dx || !dy || !dz || !(side > 0.0f)) return fail(GVX_ERR_INVALID, "bad list geometry %ux%ux%u side %g", dx, dy, dz, side);
+  VoxList l;
+  l.dx = dx; l.dy = dy; l.dz = dz; l.side = side;
+  const uint64_t id = g.next_handle++;
+  g.lists.emplace(id, l);
+  *h = id;
+  return GVX_OK;
+}
+
+int gvx_list_destroy(gvx_handle_t h) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* l = find_list(h);
+  if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  list_free(*l);
+  g.lists.erase(h);
+  return GVX_OK;
+}
+
+int gvx_list_clear(gvx_handle_t h) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* l = find_list(h);
+  if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
+  l->size = 0;
+  return GVX_OK;
+}
+
+int gvx_list_size(gvx_handle_t h, uint64_t* size) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* l = find_list(h);
+  if (!l || !size) return fail(GVX_ERR_INVALID, "unknown list handle or null pointer");
+  *size = l->size;
+  return GVX_OK;
+}
+
+int gvx_list_insert_points(gvx_handle_t h, const float* xyz, uint64_t n, int mem_kind, int meaning) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* l = find_list(h);
+  if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
+  if (meaning < 0 || meaning > 255) return fail(GVX_ERR_INVALID, "meaning %d out of range", meaning);
+  if (n == 0) return GVX_OK;
+  if (!xyz) return fail(GVX_ERR_INVALID, "null point pointer");
+  const float* xyz_d = nullptr;
+  int rc = points_to_device(xyz, n, mem_kind, &xyz_d);
+  if (rc) return rc;
+  MetaDesc d{};
+  return list_insert(*l, xyz_d, n, d, meaning);
+}
+
+int gvx_list_insert_meta(gvx_handle_t h, const float* xyz, int mem_kind, const uint32_t* cloud_sizes, uint32_t n_clouds,
+                         const int32_t* meanings, uint32_t n_meanings) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* l = find_list(h);
+  if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
+  if (!cloud_sizes || !meanings || n_clouds == 0) return fail(GVX_ERR_INVALID, "null/empty cloud description");
+  if (n_meanings != 1 && n_meanings != n_clouds)
+    return fail(GVX_ERR_INVALID, "number of meanings (%u) differs from number of sub-clouds (%u)", n_meanings, n_clouds);
+  for (uint32_t k = 0; k < n_meanings; ++k)
+    if (meanings[k] < 0 || meanings[k] > 255) return fail(GVX_ERR_INVALID, "meaning %d out of range", meanings[k]);
+  const size_t off_mg = ((size_t)n_clouds + 1) * 4, total = off_mg + (size_t)n_meanings * 4;
+  int slot; void *dh, *dd;
+  int rc = desc_acquire(total, &slot, &dh, &dd);
+  if (rc) return rc;
+  uint32_t* prefix = (uint32_t*)dh;
+  uint64_t acc = 0;
+  for (uint32_t c = 0; c < n_clouds; ++c) { prefix[c] = (uint32_t)acc; acc += cloud_sizes[c]; }
+  if (acc > 0xFFFFFFFFull) return fail(GVX_ERR_INVALID, "MetaPointCloud larger than 2^32-1 points");
+  prefix[n_clouds] = (uint32_t)acc;
+  memcpy((char*)dh + off_mg, meanings, (size_t)n_meanings * 4);
+  if (acc == 0) return GVX_OK;
+  if (!xyz) return fail(GVX_ERR_INVALID, "null point pointer");
+  rc = desc_commit(slot, total);
+  if (rc) return rc;
+  const float* xyz_d = nullptr;
+  rc = points_to_device(xyz, acc, mem_kind, &xyz_d);
+  if (rc) return rc;
+  MetaDesc d{};
+  d.prefix_d = (const uint32_t*)dd;
+  d.meanings_d = (const int32_t*)((char*)dd + off_mg);
+  d.n_clouds = n_clouds;
+  d.n_meanings = n_meanings;
+  return list_insert(*l, xyz_d, acc, d, 0);
+}
+
+int gvx_list_download(gvx_handle_t h, uint32_t* ids, uint32_t* coords, uint8_t* voxels) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* l = find_list(h);
+  if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
+  if (l->size) {
+    if (ids) GVX_CUDA(cudaMemcpyAsync(ids, l->ids[l->cur], l->size * 4, cudaMemcpyDeviceToHost, g.stream));
+    if (coords) GVX_CUDA(cudaMemcpyAsync(coords, l->coords[l->cur], l->size * 12, cudaMemcpyDeviceToHost, g.stream));
+    if (voxels) GVX_CUDA(cudaMemcpyAsync(voxels, l->voxels[l->cur], l->size * kBitVoxelBytes, cudaMemcpyDeviceToHost, g.stream));
+  }
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  return GVX_OK;
+}
+
+int gvx_list_upload(gvx_handle_t h, const uint32_t* ids, const uint32_t* coords, const uint8_t* voxels, uint64_t n) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* l = find_list(h);
+  if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
+  if (n && (!ids || !voxels)) return fail(GVX_ERR_INVALID, "null ids/voxels");
+  if (n >= 0xFFFFFFFFull) return fail(GVX_ERR_INVALID, "voxel list would exceed 2^32-1 entries");
+  for (uint64_t i = 1; i < n; ++i)
+    if (ids[i] <= ids[i - 1]) return fail(GVX_ERR_INVALID, "ids must be strictly increasing (entry %llu)", (unsigned long long)i);
+  l->size = 0;
+  int rc = list_reserve(*l, l->cur, n);
+  if (rc) return rc;
+  if (n) {
+    GVX_CUDA(cudaMemcpyAsync(l->ids[l->cur], ids, n * 4, cudaMemcpyHostToDevice, g.stream));
+    if (coords) GVX_CUDA(cudaMemcpyAsync(l->coords[l->cur], coords, n * 12, cudaMemcpyHostToDevice, g.stream));
+    else GVX_CUDA(cudaMemsetAsync(l->coords[l->cur], 0, n * 12, g.stream));
+    GVX_CUDA(cudaMemcpyAsync(l->voxels[l->cur], voxels, n * kBitVoxelBytes, cudaMemcpyHostToDevice, g.stream));
+    GVX_CUDA(cudaStreamSynchronize(g.stream));
+  }
+  l->size = n;
+  return GVX_OK;
+}
+
+int gvx_list_device_ptrs(gvx_handle_t h, void** ids_d, void** coords_d, void** voxels_d, uint64_t* size) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* l = find_list(h);
+  if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
+  if (ids_d) *ids_d = l->ids[l->cur];
+  if (coords_d) *coords_d = l->coords[l->cur];
+  if (voxels_d) *voxels_d = l->voxels[l->cur];
+  if (size) *size = l->size;
+  return GVX_OK;
+}
+
+int gvx_collide_list_map(gvx_handle_t l, gvx_handle_t m, float thr, const int32_t off3[3], int mark, uint64_t* count) {
+  return list_collide(0, l, m, thr, off3, mark, nullptr, nullptr, nullptr, count);
+}
+int gvx_collide_list_map_types(gvx_handle_t l, gvx_handle_t m, float thr, const int32_t off3[3], int mark,
+                               uint8_t mask_out32[GVX_BITVOXEL_BYTES], uint64_t* count) {
+  return list_collide(1, l, m, thr, off3, mark, nullptr, mask_out32, nullptr, count);
+}
+int gvx_collide_list_map_mask(gvx_handle_t l, gvx_handle_t m, float thr, const int32_t off3[3], int mark,
+                              const uint8_t mask_in32[GVX_BITVOXEL_BYTES], uint64_t* count) {
+  return list_collide(2, l, m, thr, off3, mark, mask_in32, nullptr, nullptr, count);
+}
+int gvx_collide_list_map_per_meaning(gvx_handle_t l, gvx_handle_t m, float thr, const int32_t off3[3], int mark,
+                                     uint64_t counts256[256], uint64_t* total) {
+  return list_collide(3, l, m, thr, off3, mark, nullptr, nullptr, counts256, total);
+}
+int gvx_collide_list_map_async(gvx_handle_t hl, gvx_handle_t hm, float thr, const int32_t off3[3], int mark,
+                               uint64_t* count_d) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  ListCollideArgs a;
+  int rc = list_collide_prepare(hl, hm, off3, &a);
+  if (rc) return rc;
+  if (a.l->size == 0) {
+    if (count_d) GVX_CUDA(cudaMemsetAsync(count_d, 0, 8, g.stream));
+    return GVX_OK;
+  }
+  GVX_CUDA(launch_collide_list_map(lctx(), 0, a.l->ids[a.l->cur], a.l->voxels[a.l->cur], a.l->size, a.m->data,
+                                   a.m->type, a.m->n_total(), (uint64_t)a.m->z0 * a.m->dx * a.m->dy, a.m->n_voxels(),
+                                   float_to_probability(thr), thr, a.off, mark != 0, nullptr,
+                                   (unsigned long long*)count_d));
+  return GVX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,183 @@
+// gvx_context.h -- process-wide context, handle tables and error plumbing shared by the gvx_api*.cu files.
+#pragma once
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/gvx.h"
+#include "gvx_internal.h"
+
+namespace gvx {
+
+struct Map {
+  int type;
+  uint32_t dx, dy, dz, z0, z1;
+  float side;
+  void* data;
+  bool owned;
+  uint64_t n_voxels() const { return (uint64_t)dx * dy * (z1 - z0); }
+  uint64_t n_total() const { return (uint64_t)dx * dy * dz; }
+  bool sharded() const { return z0 != 0 || z1 != dz; }
+  size_t voxel_bytes() const { return type == kMapProb ? 1 : kBitVoxelBytes; }
+  size_t bytes() const { return n_voxels() * voxel_bytes(); }
+  MapView view() const { return MapView{data, type, dx, dy, dz, z0, z1, side}; }
+};
+
+// BitVectorVoxelList storage: SoA id / coord / voxel like the reference (GV/voxellist/TemplateVoxelList.h:250-252),
+// double-buffered so a build reads the old list and writes the merged one; plus the sort scratch.
+struct VoxList {
+  uint32_t dx = 0, dy = 0, dz = 0;
+  float side = 0;
+  uint64_t size = 0;
+  int cur = 0;
+  uint32_t* ids[2] = {nullptr, nullptr};
+  uint32_t* coords[2] = {nullptr, nullptr};
+  uint8_t* voxels[2] = {nullptr, nullptr};
+  uint64_t cap[2] = {0, 0};
+  uint32_t *keys_in = nullptr, *keys_out = nullptr, *vals_in = nullptr, *vals_out = nullptr;
+  uint8_t* new_meaning = nullptr;
+  void* tmp = nullptr;
+  size_t tmp_bytes = 0;
+  uint64_t scratch_cap = 0, meaning_cap = 0;
+  uint64_t n_total() const { return (uint64_t)dx * dy * dz; }
+};
+
+struct Context {
+  bool ready = false;
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  ReduceScratch* scratch_d = nullptr;
+  ResultBlock* result_d = nullptr;
+  ResultBlock* result_h = nullptr;       // pinned, mapped
+  ResultBlock* result_hmap_d = nullptr;  // device alias of result_h
+  // staging: device buffer for host point clouds, pinned + device buffers for small descriptors
+  void* stage_d = nullptr; size_t stage_cap = 0;
+  // ring of small descriptor slots (pinned host + device + "H2D done" event): no stream sync per call
+  static constexpr int kDescSlots = 8;
+  void* desc_h[kDescSlots] = {}; void* desc_d[kDescSlots] = {}; size_t desc_cap[kDescSlots] = {};
+  cudaEvent_t desc_ev[kDescSlots] = {}; int desc_next = 0;
+  // batch-collide scratch (gvx_api_batch.cu): env occupancy bitmap, per-configuration "seen" bitmaps, transforms,
+  // counts (device + pinned host)
+  void* bat_bits = nullptr; size_t bat_bits_cap = 0;
+  void* bat_seen = nullptr; size_t bat_seen_cap = 0;
+  void* bat_tr = nullptr; size_t bat_tr_cap = 0;
+  void* bat_tr_h = nullptr; size_t bat_tr_h_cap = 0;
+  void* bat_counts = nullptr; size_t bat_counts_cap = 0;
+  void* bat_counts_h = nullptr; size_t bat_counts_h_cap = 0;
+  size_t bat_seen_budget = (size_t)4 << 30;  // bytes of "seen" scratch per wave of configurations
+  uint64_t launches = 0;
+  uint64_t next_handle = 1;
+  std::unordered_map<uint64_t, Map> maps;
+  std::unordered_map<uint64_t, VoxList> lists;
+  std::mutex mu;
+};
+
+extern Context g;
+void lists_free_all();  // gvx_api_list.cu
+extern thread_local std::string t_err;
+
+inline int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  t_err = buf;
+  return code;
+}
+#define GVX_CUDA(x)                                                                                   \
+  do {                                                                                                \
+    cudaError_t e_ = (x);                                                                             \
+    if (e_ != cudaSuccess) return fail(GVX_ERR_CUDA, "%s: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+#define GVX_NEED_INIT() \
+  do { if (!g.ready) return fail(GVX_ERR_NOT_INITIALIZED, "gvx_init has not been called"); } while (0)
+
+inline LaunchCtx lctx() {
+  return LaunchCtx{g.stream, g.sm_count, g.scratch_d, g.result_d, g.result_hmap_d, &g.launches};
+}
+inline Map* find_map(gvx_handle_t h) {
+  auto it = g.maps.find(h);
+  return it == g.maps.end() ? nullptr : &it->second;
+}
+inline VoxList* find_list(gvx_handle_t h) {
+  auto it = g.lists.find(h);
+  return it == g.lists.end() ? nullptr : &it->second;
+}
+// grow-only device / pinned-host scratch buffers
+inline int ensure_dev(void** p, size_t* cap, size_t bytes) {
+  if (bytes <= *cap) return GVX_OK;
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (*p) { cudaFree(*p); *p = nullptr; *cap = 0; }
+  cudaError_t e = cudaMalloc(p, bytes);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(GVX_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e)); }
+  *cap = bytes;
+  return GVX_OK;
+}
+inline int ensure_pinned(void** p, size_t* cap, size_t bytes) {
+  if (bytes <= *cap) return GVX_OK;
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (*p) { cudaFreeHost(*p); *p = nullptr; *cap = 0; }
+  GVX_CUDA(cudaHostAlloc(p, bytes, cudaHostAllocDefault));
+  *cap = bytes;
+  return GVX_OK;
+}
+inline int ensure_stage(size_t bytes) {
+  if (bytes <= g.stage_cap) return GVX_OK;
+  if (g.stage_d) { GVX_CUDA(cudaStreamSynchronize(g.stream)); GVX_CUDA(cudaFree(g.stage_d)); g.stage_d = nullptr; g.stage_cap = 0; }
+  size_t cap = bytes + bytes / 4 + (1u << 20);
+  GVX_CUDA(cudaMalloc(&g.stage_d, cap));
+  g.stage_cap = cap;
+  return GVX_OK;
+}
+// Acquire the next descriptor slot with room for `bytes`; waits only if that slot's previous H2D copy (8 calls
+// ago) has not finished. Fill *h, then call desc_commit to copy it to *d on the stream.
+inline int desc_acquire(size_t bytes, int* slot, void** h, void** d) {
+  const int k = g.desc_next;
+  g.desc_next = (g.desc_next + 1) % Context::kDescSlots;
+  if (!g.desc_ev[k]) GVX_CUDA(cudaEventCreateWithFlags(&g.desc_ev[k], cudaEventDisableTiming));
+  GVX_CUDA(cudaEventSynchronize(g.desc_ev[k]));
+  if (bytes > g.desc_cap[k]) {
+    GVX_CUDA(cudaStreamSynchronize(g.stream));  // a kernel may still read the old device slot
+    if (g.desc_h[k]) cudaFreeHost(g.desc_h[k]);
+    if (g.desc_d[k]) cudaFree(g.desc_d[k]);
+    g.desc_h[k] = g.desc_d[k] = nullptr; g.desc_cap[k] = 0;
+    const size_t cap = bytes * 2 + 4096;
+    GVX_CUDA(cudaHostAlloc(&g.desc_h[k], cap, cudaHostAllocDefault));
+    GVX_CUDA(cudaMalloc(&g.desc_d[k], cap));
+    g.desc_cap[k] = cap;
+  }
+  *slot = k; *h = g.desc_h[k]; *d = g.desc_d[k];
+  return GVX_OK;
+}
+inline int desc_commit(int slot, size_t bytes) {
+  GVX_CUDA(cudaMemcpyAsync(g.desc_d[slot], g.desc_h[slot], bytes, cudaMemcpyHostToDevice, g.stream));
+  GVX_CUDA(cudaEventRecord(g.desc_ev[slot], g.stream));
+  return GVX_OK;
+}
+// Points to device: host clouds go through the staging buffer (one async H2D, no per-call cudaMalloc/cudaFree
+// as in TemplateVoxelMap::insertPointCloud(std::vector), GV/voxelmap/TemplateVoxelMap.hpp:563-576).
+inline int points_to_device(const float* xyz, uint64_t n, int mem_kind, const float** out_d) {
+  if (mem_kind == GVX_MEM_DEVICE) { *out_d = xyz; return GVX_OK; }
+  if (mem_kind != GVX_MEM_HOST) return fail(GVX_ERR_INVALID, "bad mem_kind %d", mem_kind);
+  const size_t bytes = (size_t)n * 12;
+  int rc = ensure_stage(bytes);
+  if (rc) return rc;
+  if (bytes) GVX_CUDA(cudaMemcpyAsync(g.stage_d, xyz, bytes, cudaMemcpyHostToDevice, g.stream));
+  *out_d = (const float*)g.stage_d;
+  return GVX_OK;
+}
+// DefaultCollider::floatToProbability (GV/voxel/DefaultCollider.hpp:94-98), evaluated on the host like the
+// reference does: thr*254 - 127 in fp32, C truncation to int32, low 8 bits.
+inline int8_t float_to_probability(float thr) {
+  const float tmp = (thr * (float(127) - float(-127))) + float(-127);
+  return (int8_t)(int32_t)tmp;
+}
+
+}  // namespace gvx

@@ -68,6 +68,17 @@ __device__ __forceinline__ float affine_row(const float* __restrict__ a, float x
   return __fadd_rn(a[3], t);
 }
 
+// Lower-bound search in the exclusive prefix of cloud sizes: cloud c with prefix[c] <= i < prefix[c+1].
+// (The reference walks cloud_sizes[] linearly from 0 in every thread, VoxelMapOperations.hpp:396-406.)
+__device__ __forceinline__ uint32_t find_cloud(const uint32_t* prefix, uint32_t n_clouds, uint32_t i) {
+  uint32_t lo = 0, hi = n_clouds;
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (prefix[mid] <= i) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
 __device__ __forceinline__ uint64_t warp_sum_u32(uint32_t v) { return (uint64_t)__reduce_add_sync(0xffffffffu, v); }
 
 // Scratch shared by every reducing kernel of one context: per-CTA partials, a self-resetting ticket

@@ -23,17 +23,6 @@ __device__ __forceinline__ int8_t prob_insert_value(int meaning) {
   return meaning == 0 ? (int8_t)-127 : ((meaning == 1 || meaning == 2) ? (int8_t)127 : (int8_t)-128);
 }
 
-// Lower-bound search in the exclusive prefix of cloud sizes: cloud c with prefix[c] <= i < prefix[c+1].
-// (The reference walks cloud_sizes[] linearly from 0 in every thread, VoxelMapOperations.hpp:396-406.)
-__device__ __forceinline__ uint32_t find_cloud(const uint32_t* prefix, uint32_t n_clouds, uint32_t i) {
-  uint32_t lo = 0, hi = n_clouds;
-  while (hi - lo > 1) {
-    const uint32_t mid = (lo + hi) >> 1;
-    if (prefix[mid] <= i) lo = mid; else hi = mid;
-  }
-  return lo;
-}
-
 // Publish the "points outside the map" flag: OR into flag_accum, last CTA moves it to the result block and
 // resets it (self-cleaning, no memset between launches).
 __device__ __forceinline__ void finish_flag(bool outside, ReduceScratch* s, ResultBlock* out_d, ResultBlock* out_h) {

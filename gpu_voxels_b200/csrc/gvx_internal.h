@@ -46,4 +46,40 @@ cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const fl
                                   const Affine12& pose, int delta);
 cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8]);
 
+
+// BitVectorVoxelList build (gvx_list.cu): old list (sorted, unique) + n_new points -> out_* (sorted, unique, OR-merged);
+// the number of entries lands in ResultBlock::count. All pointers are device pointers.
+struct ListBuild {
+  const uint32_t* old_ids; const uint32_t* old_coords; const uint8_t* old_voxels; uint64_t old_size;
+  const float* xyz_d; uint64_t n_new;
+  uint32_t dx, dy; float side;
+  MetaDesc meta;        // prefix_d == nullptr: every point gets single_meaning
+  int single_meaning;
+  uint32_t *keys_in, *keys_out, *vals_in, *vals_out;  // old_size + n_new entries each
+  uint8_t* new_meaning;                               // n_new bytes
+  void* tmp; size_t tmp_bytes;                        // >= list_sort_temp_bytes(old_size + n_new)
+  uint32_t* out_ids; uint32_t* out_coords; uint8_t* out_voxels;
+};
+size_t list_sort_temp_bytes(uint64_t n);
+cudaError_t launch_list_build(const LaunchCtx& c, const ListBuild& b);
+cudaError_t launch_collide_list_map(const LaunchCtx& c, int mode, const uint32_t* ids, void* voxels, uint64_t size,
+                                    const void* map, int map_type, uint64_t n_total, uint64_t map_first,
+                                    uint64_t map_n, int8_t thr_i, float thr_f, int64_t off, bool mark,
+                                    const uint32_t mask_in8[8], unsigned long long* count_out_d);
+
+// batch of robot configurations vs one environment map (gvx_batch.cu)
+struct BatchDesc {
+  const uint32_t* prefix_d;    // n_clouds + 1 exclusive prefix of the link cloud sizes
+  const uint8_t* eligible_d;   // n_clouds: 1 if the link's meaning passes the collision mask
+  const float* transforms_d;   // n_cfg x n_clouds x 16 (row-major Matrix4f)
+  uint32_t n_clouds;
+  uint32_t dx, dy, dz;
+  float side;
+};
+cudaError_t launch_env_bitmap(const LaunchCtx& c, const void* env, int env_type, uint64_t n, int8_t thr,
+                              uint32_t* bits_d);
+cudaError_t launch_batch_collide(const LaunchCtx& c, const float* xyz_d, const BatchDesc& d, uint32_t n_points,
+                                 const uint32_t* env_bits_d, uint32_t* seen_d, uint64_t seen_words, uint32_t cfg0,
+                                 uint32_t n_cfg_wave, unsigned long long* counts_d);
+
 }  // namespace gvx

@@ -1,0 +1,89 @@
+// gvx_reduce.cuh -- CTA-level finish shared by every counting kernel (map x map, list x map).
+#pragma once
+#include "gvx_device.cuh"
+
+namespace gvx {
+
+constexpr int kThreads = 256;  // block size of every reducing kernel
+
+// Block-level finish shared by all collide kernels: reduce (count, mask) over the CTA, publish the partial,
+// let the last CTA produce the final result.
+template <bool TYPES>
+__device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (&acc)[8], ReduceScratch* s,
+                                             ResultBlock* out_d, ResultBlock* out_h,
+                                             unsigned long long* count_out_d) {
+  __shared__ unsigned long long sh_cnt[kThreads / 32];
+  __shared__ uint32_t sh_mask[8];
+  __shared__ bool sh_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (TYPES && threadIdx.x < 8) sh_mask[threadIdx.x] = 0u;
+  const unsigned long long wsum = warp_sum_u32(my_count);
+  if (lane == 0) sh_cnt[warp] = wsum;
+  __syncthreads();
+  if (TYPES) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t m = __reduce_or_sync(0xffffffffu, acc[k]);
+      if (lane == 0 && m) atomicOr(&sh_mask[k], m);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    unsigned long long c = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) c += sh_cnt[w];
+    s->partial_count[blockIdx.x] = c;
+    if (TYPES) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s->partial_mask[blockIdx.x][k] = sh_mask[k];
+    }
+    __threadfence();
+    const unsigned int t = atomicInc(&s->ticket, gridDim.x - 1);  // wraps to 0 on the last arrival
+    sh_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!sh_last) return false;
+  __threadfence();
+  unsigned long long c = 0;
+  uint32_t m[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (unsigned int b = threadIdx.x; b < gridDim.x; b += kThreads) {
+    c += __ldcg(&s->partial_count[b]);
+    if (TYPES) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) m[k] |= __ldcg(&s->partial_mask[b][k]);
+    }
+  }
+  __syncthreads();  // everyone is done with sh_cnt / sh_mask of the first phase
+  if (TYPES && threadIdx.x < 8) sh_mask[threadIdx.x] = 0u;
+  // 64-bit warp sum via two 32-bit halves would overflow-carry wrongly; shuffle-add instead
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if (lane == 0) sh_cnt[warp] = c;
+  __syncthreads();
+  if (TYPES) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t r = __reduce_or_sync(0xffffffffu, m[k]);
+      if (lane == 0 && r) atomicOr(&sh_mask[k], r);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    unsigned long long tot = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) tot += sh_cnt[w];
+    out_d->count = tot;
+    out_h->count = tot;
+    out_d->flag = tot != 0;
+    out_h->flag = tot != 0;
+    if (count_out_d) *count_out_d = tot;
+    if (TYPES) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { out_d->mask[k] = sh_mask[k]; out_h->mask[k] = sh_mask[k]; }
+    }
+    __threadfence_system();
+  }
+  return true;
+}
+
+}  // namespace gvx

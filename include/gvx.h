@@ -151,6 +151,72 @@ int gvx_collide_map_map_any(gvx_handle_t a, gvx_handle_t b, float thr, int* flag
 int gvx_collide_map_map_types(gvx_handle_t a, gvx_handle_t b, float thr, int mark,
                               uint8_t mask_inout32[GVX_BITVOXEL_BYTES], uint64_t* count);
 
+/* ---- voxel lists (BitVectorVoxelList) ----------------------------------------------------------------- */
+/* GpuVoxels::addMap(MT_BITVECTOR_VOXELLIST) -> TemplateVoxelList ctor (GV/GpuVoxels.cpp:213-221,
+ * GV/voxellist/TemplateVoxelList.hpp:67-86). Storage is the reference's SoA: id[u32] = linear voxel index,
+ * coord[3 x u32], voxel[32 B] (GV/voxellist/TemplateVoxelList.h:250-252); always sorted by id and unique. */
+int gvx_list_create(gvx_handle_t* h, uint32_t dx, uint32_t dy, uint32_t dz, float side);
+int gvx_list_destroy(gvx_handle_t h);
+/* TemplateVoxelList::clearMap (GV/voxellist/TemplateVoxelList.hpp:405-416) */
+int gvx_list_clear(gvx_handle_t h);
+/* getDimensions().x of the reference's list = number of entries (GV/voxellist/TemplateVoxelList.hpp:418-422) */
+int gvx_list_size(gvx_handle_t h, uint64_t* size);
+/* TemplateVoxelList::insertPointCloud (GV/voxellist/TemplateVoxelList.hpp:284-341, kernelInsertGlobalPointCloud
+ * GV/voxellist/kernels/VoxelListOperations.hpp:41-61) followed by make_unique (:141-208): one entry per point with NO
+ * bounds check (outside points get wrapped uint32 ids), stable sort by id, OR-merge of equal ids, unique. */
+int gvx_list_insert_points(gvx_handle_t h, const float* xyz, uint64_t n, int mem_kind, int meaning);
+/* TemplateVoxelList::insertMetaPointCloud x2 (GV/voxellist/TemplateVoxelList.hpp:343-403, kernels
+ * GV/voxellist/kernels/VoxelListOperations.hpp:63-120); n_meanings == 1 or n_clouds */
+int gvx_list_insert_meta(gvx_handle_t h, const float* xyz, int mem_kind, const uint32_t* cloud_sizes, uint32_t n_clouds,
+                         const int32_t* meanings, uint32_t n_meanings);
+/* copyCoordsToHost / the payload of writeToDisk (GV/voxellist/TemplateVoxelList.hpp:227-282, 444-471); each output
+ * pointer may be NULL; buffers hold gvx_list_size entries */
+int gvx_list_download(gvx_handle_t h, uint32_t* ids, uint32_t* coords, uint8_t* voxels);
+/* readFromDisk's payload: replace the list by n host entries; ids must be strictly increasing; coords may be NULL */
+int gvx_list_upload(gvx_handle_t h, const uint32_t* ids, const uint32_t* coords, const uint8_t* voxels, uint64_t n);
+/* getDeviceIdPtr / getDeviceCoordPtr / getDeviceDataPtr (GV/voxellist/TemplateVoxelList.h:120-160) */
+int gvx_list_device_ptrs(gvx_handle_t h, void** ids_d, void** coords_d, void** voxels_d, uint64_t* size);
+
+/* ---- collision counting, list x map ------------------------------------------------------------------- */
+/* BitVoxelList::collideWith(ProbVoxelMap* | BitVectorVoxelMap*) (GV/voxellist/BitVoxelList.hpp:70-84 ->
+ * TemplateVoxelList::collisionCheckWithCollider GV/voxellist/TemplateVoxelList.hpp:731-774, kernelCollideWithVoxelMap
+ * GV/voxellist/kernels/VoxelListOperations.hpp:126-177). The map voxel of entry e is map[id_e + linear(off3)], used
+ * only if it lies inside the map. mark != 0: colliding LIST voxels get eBVM_COLLISION. The map may be a z-slab
+ * (entries of other slabs are skipped; sum the counts over ranks). Different reference dimensions ->
+ * GVX_ERR_DIM_MISMATCH (the reference returns SSIZE_MAX, TemplateVoxelList.hpp:737-742). */
+int gvx_collide_list_map(gvx_handle_t list, gvx_handle_t map, float thr, const int32_t off3[3], int mark,
+                         uint64_t* count);
+int gvx_collide_list_map_async(gvx_handle_t list, gvx_handle_t map, float thr, const int32_t off3[3], int mark,
+                               uint64_t* count_d);
+/* BitVoxelList::collideWithTypes (GV/voxellist/BitVoxelList.hpp:127-218, kernel VoxelListOperations.hpp:182-240):
+ * count + OR of the colliding list voxels; mask_out32 is cleared first (BitVoxelList.hpp:163); the map voxel is
+ * tested with isOccupied(thr) on the RAW float threshold (GV/voxel/ProbabilisticVoxel.hpp:94-98) */
+int gvx_collide_list_map_types(gvx_handle_t list, gvx_handle_t map, float thr, const int32_t off3[3], int mark,
+                               uint8_t mask_out32[GVX_BITVOXEL_BYTES], uint64_t* count);
+/* BitVoxelList::collideWithTypeMask (GV/voxellist/BitVoxelList.hpp:220-265, kernel VoxelListOperations.hpp:260-314):
+ * only entries with (types_to_check & list voxel) != 0 count -- the BitVoxelMeaning collision mask */
+int gvx_collide_list_map_mask(gvx_handle_t list, gvx_handle_t map, float thr, const int32_t off3[3], int mark,
+                              const uint8_t mask_in32[GVX_BITVOXEL_BYTES], uint64_t* count);
+/* Per-meaning counts with the semantics of BitVoxelList::collideCountingPerMeaning (GV/voxellist/BitVoxelList.hpp:300-344,
+ * list x list only in the reference, summed on the host) applied to collideWith's colliding set: every set bit j of a
+ * colliding list voxel adds 1 to counts256[j] and to *total. */
+int gvx_collide_list_map_per_meaning(gvx_handle_t list, gvx_handle_t map, float thr, const int32_t off3[3], int mark,
+                                     uint64_t counts256[256], uint64_t* total);
+
+/* ---- batch of robot configurations -------------------------------------------------------------------- */
+/* n_cfg times the planner's state check (gvl_ompl_planning/gvl_ompl_planner_helper.cpp:169-202): clearMap(robot);
+ * transformSubCloud per link (GV/helpers/MetaPointCloud.cu:624-649); insertMetaPointCloud(robot, meanings);
+ * counts[c] = robot.collideWith(env, thr) -- in ONE call, without a robot grid and without per-configuration
+ * launches or syncs. base_xyz: the concatenated link clouds in link frames; meanings[n_clouds];
+ * transforms: n_cfg x n_clouds row-major 4x4 fp32 (host). mask32 (nullable) is the BitVoxelMeaning collision mask:
+ * a robot voxel counts only if (mask & voxel) != 0; NULL = DefaultCollider (any meaning other than eBVM_FREE).
+ * No side effects on env. counts: n_cfg host uint64. */
+int gvx_batch_robot_collide(gvx_handle_t env, const float* base_xyz, int mem_kind, const uint32_t* cloud_sizes,
+                            uint32_t n_clouds, const int32_t* meanings, const float* transforms, uint32_t n_cfg,
+                            const uint8_t* mask32, float thr, uint64_t* counts);
+/* bytes of per-wave scratch the batch call may use for its per-configuration "seen" bitmaps (default 4 GiB) */
+int gvx_batch_set_scratch_budget(uint64_t bytes);
+
 #ifdef __cplusplus
 }
 #endif
