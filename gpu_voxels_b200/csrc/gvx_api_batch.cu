@@ -7,7 +7,7 @@ extern "C" {
 
 int gvx_batch_set_scratch_budget(uint64_t bytes) {
   std::lock_guard<std::mutex> lk(g.mu);
-  if (bytes < (1u << 20)) return fail(GVX_ERR_INVALID, "scratch budget below 1 MiB");
+  if (bytes < 4096) return fail(GVX_ERR_INVALID, "scratch budget below 4 KiB");
   g.bat_seen_budget = (size_t)bytes;
   return GVX_OK;
 }
