@@ -25,6 +25,11 @@ SIGNATURES = {
     "gvx_sync": (C.c_int, []),
     "gvx_device_info": (C.c_int, [P(C.c_int), P(u64), P(u64), C.c_char_p]),
     "gvx_launch_count": (u64, []),
+    "gvx_buffer_create": (C.c_int, [P(u64), u64]),
+    "gvx_buffer_destroy": (C.c_int, [u64]),
+    "gvx_buffer_upload": (C.c_int, [u64, u64, vp, u64]),
+    "gvx_buffer_download": (C.c_int, [u64, u64, vp, u64]),
+    "gvx_buffer_device_ptr": (C.c_int, [u64, P(vp), P(u64)]),
     "gvx_map_create": (C.c_int, [P(u64), C.c_int, u32, u32, u32, f32]),
     "gvx_map_create_slab": (C.c_int, [P(u64), C.c_int, u32, u32, u32, f32, u32, u32]),
     "gvx_map_wrap": (C.c_int, [P(u64), C.c_int, vp, u32, u32, u32, f32, u32, u32]),

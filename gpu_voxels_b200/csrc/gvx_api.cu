@@ -52,6 +52,8 @@ int gvx_shutdown(void) {
   for (auto& kv : g.maps) if (kv.second.owned && kv.second.data) cudaFree(kv.second.data);
   g.maps.clear();
   lists_free_all();
+  for (auto& kv : g.buffers) if (kv.second.p) cudaFree(kv.second.p);
+  g.buffers.clear();
   for (void** p : {&g.bat_bits, &g.bat_seen, &g.bat_tr, &g.bat_counts}) { if (*p) cudaFree(*p); *p = nullptr; }
   for (void** p : {&g.bat_tr_h, &g.bat_counts_h}) { if (*p) cudaFreeHost(*p); *p = nullptr; }
   g.bat_bits_cap = g.bat_seen_cap = g.bat_tr_cap = g.bat_tr_h_cap = g.bat_counts_cap = g.bat_counts_h_cap = 0;
@@ -106,6 +108,74 @@ int gvx_device_info(int* sm_count, uint64_t* free_bytes, uint64_t* total_bytes, 
 }
 
 uint64_t gvx_launch_count(void) { return g.launches; }
+
+// ---- device buffers (PointCloud / MetaPointCloud storage of the C++ facade) ---------------------------------
+int gvx_buffer_create(gvx_handle_t* h, uint64_t bytes) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  if (!h) return fail(GVX_ERR_INVALID, "null handle pointer");
+  Context::DevBuffer b{nullptr, bytes};
+  if (bytes) {
+    cudaError_t e = cudaMalloc(&b.p, bytes);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(GVX_ERR_NOMEM, "cudaMalloc(%llu) failed: %s", (unsigned long long)bytes, cudaGetErrorString(e)); }
+  }
+  const uint64_t id = g.next_handle++;
+  g.buffers.emplace(id, b);
+  *h = id;
+  return GVX_OK;
+}
+int gvx_buffer_destroy(gvx_handle_t h) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  auto it = g.buffers.find(h);
+  if (it == g.buffers.end()) return fail(GVX_ERR_INVALID, "unknown buffer handle %llu", (unsigned long long)h);
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (it->second.p) GVX_CUDA(cudaFree(it->second.p));
+  g.buffers.erase(it);
+  return GVX_OK;
+}
+static int buffer_range(gvx_handle_t h, uint64_t offset, uint64_t bytes, Context::DevBuffer** out) {
+  auto it = g.buffers.find(h);
+  if (it == g.buffers.end()) return fail(GVX_ERR_INVALID, "unknown buffer handle %llu", (unsigned long long)h);
+  if (offset > it->second.bytes || bytes > it->second.bytes - offset)
+    return fail(GVX_ERR_INVALID, "range [%llu,+%llu) outside the buffer (%llu bytes)", (unsigned long long)offset,
+                (unsigned long long)bytes, (unsigned long long)it->second.bytes);
+  *out = &it->second;
+  return GVX_OK;
+}
+int gvx_buffer_upload(gvx_handle_t h, uint64_t offset, const void* host, uint64_t bytes) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Context::DevBuffer* b;
+  int rc = buffer_range(h, offset, bytes, &b);
+  if (rc) return rc;
+  if (!bytes) return GVX_OK;
+  if (!host) return fail(GVX_ERR_INVALID, "null host pointer");
+  GVX_CUDA(cudaMemcpyAsync((char*)b->p + offset, host, bytes, cudaMemcpyHostToDevice, g.stream));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));  // pageable host memory may be reused by the caller right away
+  return GVX_OK;
+}
+int gvx_buffer_download(gvx_handle_t h, uint64_t offset, void* host, uint64_t bytes) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Context::DevBuffer* b;
+  int rc = buffer_range(h, offset, bytes, &b);
+  if (rc) return rc;
+  if (!bytes) return GVX_OK;
+  if (!host) return fail(GVX_ERR_INVALID, "null host pointer");
+  GVX_CUDA(cudaMemcpyAsync(host, (const char*)b->p + offset, bytes, cudaMemcpyDeviceToHost, g.stream));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  return GVX_OK;
+}
+int gvx_buffer_device_ptr(gvx_handle_t h, void** data_d, uint64_t* bytes) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  auto it = g.buffers.find(h);
+  if (it == g.buffers.end()) return fail(GVX_ERR_INVALID, "unknown buffer handle %llu", (unsigned long long)h);
+  if (data_d) *data_d = it->second.p;
+  if (bytes) *bytes = it->second.bytes;
+  return GVX_OK;
+}
 
 // ---- dense maps ---------------------------------------------------------------------------------------
 static int map_make(gvx_handle_t* h, int map_type, void* wrap, uint32_t dx, uint32_t dy, uint32_t dz, float side,

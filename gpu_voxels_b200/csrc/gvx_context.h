@@ -75,6 +75,8 @@ struct Context {
   uint64_t next_handle = 1;
   std::unordered_map<uint64_t, Map> maps;
   std::unordered_map<uint64_t, VoxList> lists;
+  struct DevBuffer { void* p; uint64_t bytes; };
+  std::unordered_map<uint64_t, DevBuffer> buffers;  // gvx_buffer_*: device-resident point clouds of the C++ facade
   std::mutex mu;
 };
 

@@ -78,6 +78,16 @@ int gvx_device_info(int* sm_count, uint64_t* free_bytes, uint64_t* total_bytes, 
 /* number of kernels this library has launched since gvx_init (bench.py reports it as gpu_launches) */
 uint64_t gvx_launch_count(void);
 
+/* ---- device buffers ----------------------------------------------------------------------------------- */
+/* Device-resident storage for point clouds: what PointCloud / MetaPointCloud hold in the reference
+ * (cudaMalloc + cudaMemcpy in GV/helpers/PointCloud.cu:32-120, GV/helpers/MetaPointCloud.cu:24-140). The device
+ * pointer can be passed wherever a mem_kind == GVX_MEM_DEVICE cloud is accepted. */
+int gvx_buffer_create(gvx_handle_t* h, uint64_t bytes);
+int gvx_buffer_destroy(gvx_handle_t h);
+int gvx_buffer_upload(gvx_handle_t h, uint64_t offset, const void* host, uint64_t bytes);
+int gvx_buffer_download(gvx_handle_t h, uint64_t offset, void* host, uint64_t bytes);
+int gvx_buffer_device_ptr(gvx_handle_t h, void** data_d, uint64_t* bytes);
+
 /* ---- dense maps --------------------------------------------------------------------------------------- */
 /* GpuVoxels::addMap(MT_BITVECTOR_VOXELMAP | MT_PROBAB_VOXELMAP) -> TemplateVoxelMap ctor + clearMap
  * (GV/GpuVoxels.cpp:164-290, GV/voxelmap/TemplateVoxelMap.hpp:54-138). */
