@@ -1,0 +1,217 @@
+// gpu_voxels/GpuVoxels.h -- the GpuVoxels singleton of the reference's API for the hot path
+// (GV/GpuVoxels.h:91-415, GV/GpuVoxels.cpp:33-78,164-313,443-559,594-609), header-only over the C ABI (include/gvx.h).
+// Source-compatible for: getInstance, initialize, addMap, delMap, getMap, clearMap x2, insertPointCloudIntoMap x2,
+// insertMetaPointCloudIntoMap x2, insertBoxIntoMap, getDimensions x2, getVoxelSideLength; the returned maps provide
+// collideWith / collideWithTypes / collideWithTypeMask. Visualisation, robots, octrees, distance maps, primitive arrays
+// and file loaders are outside this build.
+#ifndef GPU_VOXELS_B200_GPUVOXELS_H
+#define GPU_VOXELS_B200_GPUVOXELS_H
+
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <gpu_voxels/GpuVoxelsMap.h>
+#include <gpu_voxels/helpers/GeometryGeneration.h>
+#include <gpu_voxels/voxellist/VoxelList.h>
+#include <gpu_voxels/voxelmap/VoxelMap.h>
+
+namespace gpu_voxels {
+
+class GpuVoxels;
+typedef std::shared_ptr<GpuVoxels> GpuVoxelsSharedPtr;
+
+struct ManagedMap
+{
+  GpuVoxelsMapSharedPtr map_shared_ptr;
+};
+typedef std::map<std::string, ManagedMap> ManagedMaps;
+typedef ManagedMaps::iterator ManagedMapsIterator;
+
+class GpuVoxels
+{
+public:
+  ~GpuVoxels() { m_managed_maps.clear(); }
+
+  // one shared instance as long as somebody holds it (weak_ptr singleton, GV/GpuVoxels.cpp:67-78)
+  static GpuVoxelsSharedPtr getInstance()
+  {
+    static std::weak_ptr<GpuVoxels> master;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lk(mu);
+    GpuVoxelsSharedPtr p = master.lock();
+    if (!p)
+    {
+      p.reset(new GpuVoxels());
+      master = p;
+    }
+    return p;
+  }
+
+  void initialize(const uint32_t dim_x, const uint32_t dim_y, const uint32_t dim_z, const float voxel_side_length)
+  {
+    if (m_dim.x == 0 || m_dim.y == 0 || m_dim.z == 0 || m_voxel_side_length == 0)
+    {
+      m_dim = Vector3ui(dim_x, dim_y, dim_z);
+      m_voxel_side_length = voxel_side_length;
+    }
+    else  // GV/GpuVoxels.cpp:52-65
+    {
+      LOGGING_WARNING(Gpu_voxels, "Do not try to initialize GpuVoxels multiple times. Parameters remain unchanged." << endl);
+    }
+  }
+
+  GpuVoxelsMapSharedPtr addMap(const MapType map_type, const std::string& map_name)
+  {
+    if (m_managed_maps.find(map_name) != m_managed_maps.end())  // GV/GpuVoxels.cpp:169-176
+    {
+      LOGGING_ERROR_C(Gpu_voxels, GpuVoxels, "Map with name '" << map_name << "' already exists." << endl);
+      return GpuVoxelsMapSharedPtr();
+    }
+    GpuVoxelsMapSharedPtr map_shared_ptr;
+    switch (map_type)
+    {
+      case MT_BITVECTOR_VOXELMAP:
+        map_shared_ptr.reset(new voxelmap::BitVectorVoxelMap(m_dim, m_voxel_side_length, MT_BITVECTOR_VOXELMAP));
+        break;
+      case MT_PROBAB_VOXELMAP:
+        map_shared_ptr.reset(new voxelmap::ProbVoxelMap(m_dim, m_voxel_side_length, MT_PROBAB_VOXELMAP));
+        break;
+      case MT_BITVECTOR_VOXELLIST:
+        map_shared_ptr.reset(new voxellist::BitVectorVoxelList(m_dim, m_voxel_side_length, MT_BITVECTOR_VOXELLIST));
+        break;
+      default:  // the reference throws a std::string for unimplemented types (GV/GpuVoxels.cpp:210-211)
+        throw GPU_VOXELS_MAP_TYPE_NOT_IMPLEMENTED;
+    }
+    ManagedMap m;
+    m.map_shared_ptr = map_shared_ptr;
+    m_managed_maps.insert(std::make_pair(map_name, m));
+    return map_shared_ptr;
+  }
+
+  bool delMap(const std::string& map_name)
+  {
+    ManagedMapsIterator it = findMap(map_name);
+    if (it == m_managed_maps.end()) return false;
+    m_managed_maps.erase(it);
+    return true;
+  }
+
+  GpuVoxelsMapSharedPtr getMap(const std::string& map_name)
+  {
+    ManagedMapsIterator it = findMap(map_name);
+    return it == m_managed_maps.end() ? GpuVoxelsMapSharedPtr() : it->second.map_shared_ptr;
+  }
+
+  bool clearMap(const std::string& map_name)
+  {
+    ManagedMapsIterator it = findMap(map_name);
+    if (it == m_managed_maps.end()) return false;
+    it->second.map_shared_ptr->clearMap();
+    return true;
+  }
+  bool clearMap(const std::string& map_name, BitVoxelMeaning voxel_meaning)
+  {
+    ManagedMapsIterator it = findMap(map_name);
+    if (it == m_managed_maps.end()) return false;
+    it->second.map_shared_ptr->clearBitVoxelMeaning(voxel_meaning);
+    return true;
+  }
+
+  bool insertPointCloudIntoMap(const PointCloud& cloud, std::string map_name, const BitVoxelMeaning voxel_meaning)
+  {
+    ManagedMapsIterator it = findMap(map_name);
+    if (it == m_managed_maps.end()) return false;
+    it->second.map_shared_ptr->insertPointCloud(cloud, voxel_meaning);
+    return true;
+  }
+  bool insertPointCloudIntoMap(const std::vector<Vector3f>& cloud, std::string map_name, const BitVoxelMeaning voxel_meaning)
+  {
+    ManagedMapsIterator it = findMap(map_name);
+    if (it == m_managed_maps.end()) return false;
+    it->second.map_shared_ptr->insertPointCloud(cloud, voxel_meaning);
+    return true;
+  }
+  bool insertMetaPointCloudIntoMap(const MetaPointCloud& meta_point_cloud, std::string map_name,
+                                   const std::vector<BitVoxelMeaning>& voxel_meanings)
+  {
+    ManagedMapsIterator it = findMap(map_name);
+    if (it == m_managed_maps.end()) return false;
+    it->second.map_shared_ptr->insertMetaPointCloud(meta_point_cloud, voxel_meanings);
+    return true;
+  }
+  bool insertMetaPointCloudIntoMap(const MetaPointCloud& meta_point_cloud, std::string map_name,
+                                   const BitVoxelMeaning voxel_meaning)
+  {
+    ManagedMapsIterator it = findMap(map_name);
+    if (it == m_managed_maps.end()) return false;
+    it->second.map_shared_ptr->insertMetaPointCloud(meta_point_cloud, voxel_meaning);
+    return true;
+  }
+
+  // GV/GpuVoxels.cpp:519-535: a box sampled with delta = side / points_per_voxel
+  bool insertBoxIntoMap(const Vector3f& corner_min, const Vector3f& corner_max, std::string map_name,
+                        const BitVoxelMeaning voxel_meaning, uint16_t points_per_voxel = 1)
+  {
+    ManagedMapsIterator it = findMap(map_name);
+    if (it == m_managed_maps.end()) return false;
+    const float delta = m_voxel_side_length / points_per_voxel;
+    it->second.map_shared_ptr->insertPointCloud(geometry_generation::createBoxOfPoints(corner_min, corner_max, delta), voxel_meaning);
+    return true;
+  }
+
+  // Extension for planners (BASELINE.json configs[2]): the planner's per-state sequence clearMap(robot) /
+  // transformSubCloud per link / insertMetaPointCloud / collideWith(env) (gvl_ompl_planner_helper.cpp:169-202)
+  // for MANY states in one call. transforms[c * n_links + l] is link l's pose in state c.
+  bool collideRobotConfigurations(const MetaPointCloud& robot_links, const std::vector<BitVoxelMeaning>& link_meanings,
+                                  const std::vector<Matrix4f>& transforms, const std::string& env_map_name,
+                                  std::vector<size_t>& collisions_per_configuration, float coll_threshold = 1.0,
+                                  const BitVectorVoxel* types_to_check = NULL)
+  {
+    ManagedMapsIterator it = findMap(env_map_name);
+    if (it == m_managed_maps.end()) return false;
+    const uint32_t n_links = robot_links.getNumberOfPointclouds();
+    if (!n_links || link_meanings.size() != n_links || transforms.size() % n_links)
+    {
+      LOGGING_ERROR_C(Gpu_voxels, GpuVoxels, "Number of link meanings / transforms does not fit the robot" << endl);
+      return false;
+    }
+    const uint32_t n_cfg = uint32_t(transforms.size() / n_links);
+    const std::vector<int32_t> mg = detail::meaningsToInts(link_meanings);
+    std::vector<uint64_t> counts(n_cfg);
+    lock_guard guard(it->second.map_shared_ptr->m_mutex);
+    const int rc = gvx_batch_robot_collide(it->second.map_shared_ptr->getHandle(),
+                                           reinterpret_cast<const float*>(robot_links.getDeviceBasePointer()), GVX_MEM_DEVICE,
+                                           &robot_links.getPointcloudSizes()[0], n_links, &mg[0],
+                                           n_cfg ? transforms[0].data() : NULL, n_cfg,
+                                           types_to_check ? types_to_check->bitVector().bytes() : NULL, coll_threshold,
+                                           n_cfg ? &counts[0] : NULL);
+    if (!gvxCheck(rc, "collideRobotConfigurations")) return false;
+    collisions_per_configuration.assign(counts.begin(), counts.end());
+    return true;
+  }
+
+  void getDimensions(uint32_t& dim_x, uint32_t& dim_y, uint32_t& dim_z) { dim_x = m_dim.x; dim_y = m_dim.y; dim_z = m_dim.z; }
+  void getDimensions(Vector3ui& dim) { dim = m_dim; }
+  void getVoxelSideLength(float& voxel_side_length) { voxel_side_length = m_voxel_side_length; }
+
+protected:
+  GpuVoxels() : m_dim(0, 0, 0), m_voxel_side_length(0) { gvxEnsureInit(); }
+
+private:
+  ManagedMapsIterator findMap(const std::string& map_name)
+  {
+    ManagedMapsIterator it = m_managed_maps.find(map_name);
+    if (it == m_managed_maps.end())
+      LOGGING_ERROR_C(Gpu_voxels, GpuVoxels, "Could not find map '" << map_name << "'" << endl);
+    return it;
+  }
+
+  ManagedMaps m_managed_maps;
+  Vector3ui m_dim;
+  float m_voxel_side_length;
+};
+
+}  // namespace gpu_voxels
+#endif

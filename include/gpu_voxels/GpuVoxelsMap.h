@@ -1,0 +1,84 @@
+// gpu_voxels/GpuVoxelsMap.h -- abstract base of all maps, as in the reference (GV/GpuVoxelsMap.h:50-276).
+// std::shared_ptr / std::recursive_timed_mutex stand in for the boost types of the same role (Boost is not a
+// dependency of this build); names of the typedefs are the reference's.
+#ifndef GPU_VOXELS_B200_GPUVOXELSMAP_H
+#define GPU_VOXELS_B200_GPUVOXELSMAP_H
+
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include <gpu_voxels/helpers/GvxCall.h>
+#include <gpu_voxels/helpers/MetaPointCloud.h>
+#include <gpu_voxels/helpers/PointCloud.h>
+#include <gpu_voxels/helpers/common_defines.h>
+#include <gpu_voxels/helpers/cuda_datatypes.h>
+#include <gpu_voxels/logging/logging_gpu_voxels.h>
+#include <gpu_voxels/voxel/BitVoxel.h>
+
+namespace gpu_voxels {
+
+class GpuVoxelsMap;
+typedef std::shared_ptr<GpuVoxelsMap> GpuVoxelsMapSharedPtr;
+typedef std::unique_lock<std::recursive_timed_mutex> lock_guard;
+
+class GpuVoxelsMap
+{
+public:
+  GpuVoxelsMap() : m_map_type(MT_BITVECTOR_VOXELMAP) {}
+  virtual ~GpuVoxelsMap() {}
+
+  template <class T> const T* as() const { return static_cast<const T*>(this); }
+  template <class T> T* as() { return static_cast<T*>(this); }
+  template <class T> bool is() { return dynamic_cast<T*>(this) != NULL; }
+  template <class T> bool is() const { return dynamic_cast<const T*>(this) != NULL; }
+
+  MapType getMapType() const { return m_map_type; }
+
+  virtual void insertPointCloud(const std::vector<Vector3f>& point_cloud, const BitVoxelMeaning voxel_meaning) = 0;
+  virtual void insertPointCloud(const PointCloud& pointcloud, const BitVoxelMeaning voxel_meaning) = 0;
+  virtual void insertMetaPointCloud(const MetaPointCloud& meta_point_cloud, BitVoxelMeaning voxel_meaning) = 0;
+  virtual void insertMetaPointCloud(const MetaPointCloud& meta_point_cloud,
+                                    const std::vector<BitVoxelMeaning>& voxel_meanings) = 0;
+  virtual void clearMap() = 0;
+  virtual void clearBitVoxelMeaning(BitVoxelMeaning voxel_meaning) = 0;
+  virtual std::size_t getMemoryUsage() const = 0;
+  virtual Vector3ui getDimensions() const = 0;
+  virtual Vector3f getMetricDimensions() const = 0;
+
+  // the C-ABI handle behind this map (not in the reference)
+  virtual gvx_handle_t getHandle() const = 0;
+
+  // public so that callers can lock a map around several operations, as in the reference (GV/GpuVoxelsMap.h:267-269)
+  mutable std::recursive_timed_mutex m_mutex;
+
+protected:
+  MapType m_map_type;
+
+private:
+  GpuVoxelsMap(const GpuVoxelsMap&);
+  const GpuVoxelsMap& operator=(const GpuVoxelsMap&);
+};
+
+namespace detail {
+inline std::vector<int32_t> meaningsToInts(const std::vector<BitVoxelMeaning>& v)
+{
+  std::vector<int32_t> out(v.size());
+  for (size_t i = 0; i < v.size(); ++i) out[i] = int32_t(v[i]);
+  return out;
+}
+// lock two maps without deadlock, like boost::lock(a, b) in the reference's binary operations
+struct DualLock
+{
+  DualLock(std::recursive_timed_mutex& a, std::recursive_timed_mutex& b) : m_a(a), m_b(b), m_same(&a == &b)
+  {
+    if (m_same) m_a.lock(); else std::lock(m_a, m_b);
+  }
+  ~DualLock() { m_a.unlock(); if (!m_same) m_b.unlock(); }
+  std::recursive_timed_mutex& m_a; std::recursive_timed_mutex& m_b; bool m_same;
+};
+}  // namespace detail
+
+}  // namespace gpu_voxels
+#endif

@@ -1,0 +1,168 @@
+// gpu_voxels/voxellist/VoxelList.h -- voxellist::BitVectorVoxelList of the reference's API over the C ABI
+// (GV/voxellist/BitVoxelList.h:139-150, .hpp:70-265; GV/voxellist/TemplateVoxelList.h, .hpp:284-422, 731-774).
+#ifndef GPU_VOXELS_B200_VOXELLIST_VOXELLIST_H
+#define GPU_VOXELS_B200_VOXELLIST_VOXELLIST_H
+
+#include <climits>
+
+#include <gpu_voxels/GpuVoxelsMap.h>
+#include <gpu_voxels/voxelmap/VoxelMap.h>
+
+namespace gpu_voxels {
+namespace voxellist {
+
+template <std::size_t length>
+class BitVoxelList : public GpuVoxelsMap
+{
+public:
+  BitVoxelList(const Vector3ui ref_map_dim, const float voxel_side_length, const MapType map_type = MT_BITVECTOR_VOXELLIST)
+    : m_ref_map_dim(ref_map_dim), m_voxel_side_length(voxel_side_length), m_handle(0)
+  {
+    gvxEnsureInit();
+    this->m_map_type = map_type;
+    gvxCheck(gvx_list_create(&m_handle, ref_map_dim.x, ref_map_dim.y, ref_map_dim.z, voxel_side_length), "voxel list construction");
+  }
+  virtual ~BitVoxelList() { if (m_handle) gvx_list_destroy(m_handle); }
+
+  virtual void insertPointCloud(const std::vector<Vector3f>& points, const BitVoxelMeaning voxel_meaning)
+  {
+    lock_guard guard(this->m_mutex);
+    if (points.empty()) return;
+    gvxCheck(gvx_list_insert_points(m_handle, reinterpret_cast<const float*>(&points[0]), points.size(), GVX_MEM_HOST,
+                                    int(voxel_meaning)), "insertPointCloud");
+  }
+  virtual void insertPointCloud(const PointCloud& pointcloud, const BitVoxelMeaning voxel_meaning)
+  {
+    lock_guard guard(this->m_mutex);
+    if (!pointcloud.getPointCloudSize()) return;
+    gvxCheck(gvx_list_insert_points(m_handle, reinterpret_cast<const float*>(pointcloud.getConstDevicePointer()),
+                                    pointcloud.getPointCloudSize(), GVX_MEM_DEVICE, int(voxel_meaning)), "insertPointCloud");
+  }
+  virtual void insertMetaPointCloud(const MetaPointCloud& meta_point_cloud, BitVoxelMeaning voxel_meaning)
+  {
+    std::vector<BitVoxelMeaning> one(1, voxel_meaning);
+    insertMeta(meta_point_cloud, one);
+  }
+  virtual void insertMetaPointCloud(const MetaPointCloud& meta_point_cloud,
+                                    const std::vector<BitVoxelMeaning>& voxel_meanings)
+  {
+    if (voxel_meanings.size() != meta_point_cloud.getNumberOfPointclouds())
+    {
+      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, "Number of voxel meanings differs from number of sub-clouds" << endl);
+      return;
+    }
+    insertMeta(meta_point_cloud, voxel_meanings);
+  }
+  virtual void clearMap()
+  {
+    lock_guard guard(this->m_mutex);
+    gvxCheck(gvx_list_clear(m_handle), "clearMap");
+  }
+  virtual void clearBitVoxelMeaning(BitVoxelMeaning)
+  {
+    LOGGING_ERROR_C(VoxellistLog, BitVoxelList, GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+  }
+  // the reference reports (number of entries, 1, 1) (GV/voxellist/TemplateVoxelList.hpp:418-422)
+  virtual Vector3ui getDimensions() const { return Vector3ui(uint32_t(size()), 1, 1); }
+  virtual Vector3f getMetricDimensions() const
+  {
+    return Vector3f(float(m_ref_map_dim.x), float(m_ref_map_dim.y), float(m_ref_map_dim.z)) * m_voxel_side_length;
+  }
+  virtual std::size_t getMemoryUsage() const { return size() * (4 + 12 + 32); }
+  virtual gvx_handle_t getHandle() const { return m_handle; }
+  float getVoxelSideLength() const { return m_voxel_side_length; }
+  std::size_t size() const { uint64_t n = 0; gvx_list_size(m_handle, &n); return std::size_t(n); }
+  // copyCoordsToHost (GV/voxellist/TemplateVoxelList.hpp:444-471)
+  void copyCoordsToHost(std::vector<Vector3ui>& host_vec)
+  {
+    host_vec.resize(size());
+    if (!host_vec.empty()) gvxCheck(gvx_list_download(m_handle, NULL, &host_vec[0].x, NULL), "copyCoordsToHost");
+  }
+
+  // ids / coords / voxels of all entries (what extractCubes exposes in the reference, GV/voxellist/TemplateVoxelList.hpp)
+  void copyToHost(std::vector<uint32_t>& ids, std::vector<Vector3ui>& coords, std::vector<BitVectorVoxel>& voxels)
+  {
+    const std::size_t n = size();
+    ids.resize(n); coords.resize(n); voxels.resize(n);
+    if (n) gvxCheck(gvx_list_download(m_handle, &ids[0], &coords[0].x, voxels[0].bitVector().bytes()), "copyToHost");
+  }
+
+  // GV/voxellist/BitVoxelList.hpp:70-84
+  size_t collideWith(const voxelmap::ProbVoxelMap* map, float coll_threshold = 1.0, const Vector3i& offset = Vector3i())
+  {
+    return collide(0, map, coll_threshold, offset, NULL, NULL);
+  }
+  size_t collideWith(const voxelmap::BitVectorVoxelMap* map, float coll_threshold = 1.0, const Vector3i& offset = Vector3i())
+  {
+    return collide(0, map, coll_threshold, offset, NULL, NULL);
+  }
+  // GV/voxellist/BitVoxelList.hpp:127-218
+  size_t collideWithTypes(const voxelmap::ProbVoxelMap* map, BitVectorVoxel& types_in_collision, float coll_threshold = 1.0,
+                          const Vector3i& offset = Vector3i())
+  {
+    return collide(1, map, coll_threshold, offset, NULL, types_in_collision.bitVector().bytes());
+  }
+  size_t collideWithTypes(const voxelmap::BitVectorVoxelMap* map, BitVectorVoxel& types_in_collision, float coll_threshold = 1.0,
+                          const Vector3i& offset = Vector3i())
+  {
+    return collide(1, map, coll_threshold, offset, NULL, types_in_collision.bitVector().bytes());
+  }
+  // GV/voxellist/BitVoxelList.hpp:220-265
+  template <class MapT>
+  size_t collideWithTypeMask(const MapT* map, const BitVectorVoxel& types_to_check, float coll_threshold = 1.0,
+                             const Vector3i& offset = Vector3i())
+  {
+    return collide(2, map, coll_threshold, offset, types_to_check.bitVector().bytes(), NULL);
+  }
+  // list x map per-meaning counts with the semantics of collideCountingPerMeaning (GV/voxellist/BitVoxelList.hpp:300-344)
+  template <class MapT>
+  size_t collideCountingPerMeaning(const MapT* map, std::vector<size_t>& collisions_per_meaning, float coll_threshold = 1.0,
+                                   const Vector3i& offset = Vector3i())
+  {
+    detail::DualLock guard(this->m_mutex, map->m_mutex);
+    const int32_t off[3] = {offset.x, offset.y, offset.z};
+    uint64_t counts[256], total = 0;
+    const int rc = gvx_collide_list_map_per_meaning(m_handle, map->getHandle(), coll_threshold, off, 1, counts, &total);
+    if (rc != GVX_OK) { gvxCheck(rc, "collideCountingPerMeaning"); return SSIZE_MAX; }
+    collisions_per_meaning.assign(counts, counts + 256);
+    return size_t(total);
+  }
+
+private:
+  size_t collide(int mode, const GpuVoxelsMap* map, float thr, const Vector3i& offset, const uint8_t* mask_in, uint8_t* mask_out)
+  {
+    detail::DualLock guard(this->m_mutex, map->m_mutex);
+    const int32_t off[3] = {offset.x, offset.y, offset.z};
+    uint64_t n = 0;
+    int rc;
+    if (mode == 0) rc = gvx_collide_list_map(m_handle, map->getHandle(), thr, off, 1, &n);
+    else if (mode == 1) rc = gvx_collide_list_map_types(m_handle, map->getHandle(), thr, off, 1, mask_out, &n);
+    else rc = gvx_collide_list_map_mask(m_handle, map->getHandle(), thr, off, 1, mask_in, &n);
+    if (rc == GVX_ERR_DIM_MISMATCH)  // GV/voxellist/TemplateVoxelList.hpp:737-742
+    {
+      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, "The Voxellist reference map dimension differ from the map dimension!" << endl);
+      return SSIZE_MAX;
+    }
+    if (!gvxCheck(rc, "collideWith")) return SSIZE_MAX;
+    return size_t(n);
+  }
+  void insertMeta(const MetaPointCloud& mpc, const std::vector<BitVoxelMeaning>& meanings)
+  {
+    lock_guard guard(this->m_mutex);
+    if (mpc.getNumberOfPointclouds() == 0 || mpc.getAccumulatedPointcloudSize() == 0) return;
+    const std::vector<int32_t> mg = detail::meaningsToInts(meanings);
+    gvxCheck(gvx_list_insert_meta(m_handle, reinterpret_cast<const float*>(mpc.getDeviceBasePointer()), GVX_MEM_DEVICE,
+                                  &mpc.getPointcloudSizes()[0], mpc.getNumberOfPointclouds(), &mg[0], uint32_t(mg.size())),
+             "insertMetaPointCloud");
+  }
+
+  Vector3ui m_ref_map_dim;
+  float m_voxel_side_length;
+  gvx_handle_t m_handle;
+};
+
+typedef BitVoxelList<BIT_VECTOR_LENGTH> BitVectorVoxelList;  // GV/voxellist/VoxelList.h
+
+}  // namespace voxellist
+}  // namespace gpu_voxels
+#endif

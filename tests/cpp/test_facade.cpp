@@ -1,0 +1,336 @@
+// tests/cpp/test_facade.cpp -- the reference's own known-answer tests for the hot path, written against the
+// header-only C++ facade (include/gpu_voxels/) exactly as a user of the reference would write them:
+//   voxelmap suite   <- GV/test/testing_voxelmap.cu:95-167, 312-398
+//   voxellists suite <- GV/test/testing_voxellist.cu:109-338, 739-864
+//   facade suite     <- example_how_to_link/gvl_linkage_test_lib.cpp:20-39, GV/GpuVoxels.cpp error conventions
+// plus the planner-batch extension checked against the per-configuration call sequence.
+// Build: g++ -std=c++14 -Iinclude tests/cpp/test_facade.cpp -Lgpu_voxels_b200 -lgvx  (see tests/test_cpp_facade.py)
+#include <cmath>
+#include <sstream>
+
+#include <gpu_voxels/GpuVoxels.h>
+
+#include "mini_boost_test.h"
+
+using namespace gpu_voxels;
+using namespace gpu_voxels::voxelmap;
+using namespace gpu_voxels::voxellist;
+using namespace gpu_voxels::geometry_generation;
+
+// GV/test/testing_fixtures.hpp:131-166
+static const uint32_t dimX = 89, dimY = 123, dimZ = 74;
+static const int numberOfPoints = 10000;
+
+BOOST_AUTO_TEST_SUITE(voxelmap_tests)
+
+BOOST_AUTO_TEST_CASE(collision)
+{
+  const float side_length = 1.f;
+  ProbVoxelMap map_1(Vector3ui(dimX, dimY, dimZ), side_length, MT_PROBAB_VOXELMAP);
+  ProbVoxelMap map_2(Vector3ui(dimX, dimY, dimZ), side_length, MT_PROBAB_VOXELMAP);
+  std::vector<Vector3f> pts;
+  createEquidistantPointsInBox(numberOfPoints, Vector3ui(dimX, dimY, dimZ), side_length, pts);
+  map_1.insertPointCloud(pts, eBVM_OCCUPIED);
+  map_2.insertPointCloud(pts, eBVM_OCCUPIED);
+  BOOST_CHECK_MESSAGE(map_1.collideWith(&map_2, 0.1) == (size_t)numberOfPoints, "All collisions detected.");
+}
+
+BOOST_AUTO_TEST_CASE(collision_with_offset)
+{
+  ProbVoxelMap map_1(Vector3ui(dimX, dimY, dimZ), 1.f, MT_PROBAB_VOXELMAP);
+  ProbVoxelMap map_2(Vector3ui(dimX, dimY, dimZ), 1.f, MT_PROBAB_VOXELMAP);
+  map_1.insertPointCloud(createBoxOfPoints(Vector3f(2.1, 2.1, 2.1), Vector3f(4.1, 4.1, 4.1), 0.5), eBVM_OCCUPIED);
+  map_2.insertPointCloud(createBoxOfPoints(Vector3f(3.1, 3.1, 3.1), Vector3f(5.1, 5.1, 5.1), 0.5), eBVM_OCCUPIED);
+  BOOST_CHECK_MESSAGE(map_1.collideWith(&map_2, 0.1) == 8, "All collisions without offset detected.");
+  BOOST_CHECK_MESSAGE(map_1.collideWith(&map_2, 0.1, Vector3i(-1, 0, -1)) == 18, "negative offset");
+  BOOST_CHECK_MESSAGE(map_2.collideWith(&map_1, 0.1, Vector3i(1, 0, 1)) == 18, "positive offset");
+}
+
+BOOST_AUTO_TEST_CASE(no_collision)
+{
+  std::vector<Vector3f> black, white;
+  ProbVoxelMap map_1(Vector3ui(dimX, dimY, dimZ), 1.f, MT_PROBAB_VOXELMAP);
+  ProbVoxelMap map_2(Vector3ui(dimX, dimY, dimZ), 1.f, MT_PROBAB_VOXELMAP);
+  createNonOverlapping3dCheckerboard(numberOfPoints, Vector3ui(dimX, dimY, dimZ), 1.f, black, white);
+  map_1.insertPointCloud(black, eBVM_OCCUPIED);
+  map_2.insertPointCloud(white, eBVM_OCCUPIED);
+  BOOST_CHECK_MESSAGE(map_1.collideWith(&map_2, 0.1) == 0, "No collisions detected.");
+  BOOST_CHECK(!map_1.collisionCheck(&map_2, 0.1));
+}
+
+BOOST_AUTO_TEST_CASE(collision_with_types_probab)
+{
+  BitVectorVoxelMap map_1(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELMAP);
+  ProbVoxelMap map_2(Vector3ui(dimX, dimY, dimZ), 1.f, MT_PROBAB_VOXELMAP);
+  std::vector<Vector3f> points;
+  for (int x = 2; x <= 3; ++x)
+    for (int y = 2; y <= 3; ++y)
+      for (int z = 2; z <= 3; ++z) points.push_back(Vector3f(x, y, z));
+  map_1.insertPointCloud(points, BitVoxelMeaning(eBVM_SWEPT_VOLUME_START + 10));
+  map_1.insertPointCloud(points, BitVoxelMeaning(eBVM_SWEPT_VOLUME_START + 42));
+  map_1.insertPointCloud(points, BitVoxelMeaning(eBVM_SWEPT_VOLUME_START + 99));
+  map_2.insertPointCloud(points, eBVM_OCCUPIED);
+  BitVectorVoxel coll_types;
+  const size_t num_collisions = map_1.collideWithTypes(&map_2, coll_types);
+  BOOST_CHECK(num_collisions == points.size());
+  BOOST_CHECK(coll_types.bitVector().getBit(eBVM_SWEPT_VOLUME_START + 10));
+  BOOST_CHECK(coll_types.bitVector().getBit(eBVM_SWEPT_VOLUME_START + 42));
+  BOOST_CHECK(coll_types.bitVector().getBit(eBVM_SWEPT_VOLUME_START + 99));
+  coll_types.bitVector().clearBit(eBVM_SWEPT_VOLUME_START + 10);
+  coll_types.bitVector().clearBit(eBVM_SWEPT_VOLUME_START + 42);
+  coll_types.bitVector().clearBit(eBVM_SWEPT_VOLUME_START + 99);
+  BOOST_CHECK(coll_types.bitVector().noneButEmpty());
+}
+
+BOOST_AUTO_TEST_CASE(iostream_bitvoxel)
+{
+  BitVectorVoxel my_voxel;
+  my_voxel.insert(eBVM_FREE);
+  my_voxel.insert(eBVM_COLLISION);
+  my_voxel.insert(eBVM_UNKNOWN);
+  my_voxel.insert(eBVM_SWEPT_VOLUME_START);
+  my_voxel.insert(BitVoxelMeaning(111));
+  my_voxel.insert(eBVM_SWEPT_VOLUME_END);
+  my_voxel.insert(eBVM_UNDEFINED);
+  const std::string ground_truth = "10111" + std::string(106, '0') + "1" + std::string(142, '0') + "11";
+  std::stringstream ss;
+  ss << my_voxel;
+  BOOST_CHECK_MESSAGE(ss.str() == ground_truth, "Outstream");
+  BitVectorVoxel my_voxel2;
+  ss.str(ground_truth);
+  ss >> my_voxel2;
+  std::stringstream s2;
+  s2 << my_voxel2;
+  BOOST_CHECK_MESSAGE(s2.str() == ground_truth, "Instream");
+}
+
+BOOST_AUTO_TEST_CASE(prob_map_rejects_other_meanings_and_marks_collisions)
+{
+  ProbVoxelMap pm(Vector3ui(32, 32, 32), 1.f);
+  BitVectorVoxelMap bm(Vector3ui(32, 32, 32), 1.f);
+  std::vector<Vector3f> p(1, Vector3f(3.5f, 4.5f, 5.5f));
+  pm.insertPointCloud(p, eBVM_SWEPT_VOLUME_START);  // logged no-op (GV/voxelmap/ProbVoxelMap.hpp:118-140)
+  bm.insertPointCloud(p, BitVoxelMeaning(20));
+  BOOST_CHECK(bm.collideWith(&pm, 0.1) == 0);
+  pm.insertPointCloud(p, eBVM_OCCUPIED);
+  BOOST_CHECK(bm.collideWith(&pm, 0.1) == 1);
+  // collideWith marked the colliding voxel of `this` with eBVM_COLLISION: clearing meaning 20 leaves it occupied
+  bm.clearBitVoxelMeaning(BitVoxelMeaning(20));
+  BOOST_CHECK(bm.collideWith(&pm, 0.1) == 1);
+  bm.clearBitVoxelMeaning(eBVM_COLLISION);
+  BOOST_CHECK(bm.collideWith(&pm, 0.1) == 0);
+}
+
+BOOST_AUTO_TEST_SUITE_END()
+
+BOOST_AUTO_TEST_SUITE(voxellists)
+
+static MetaPointCloud twoBoxes()
+{
+  std::vector<std::vector<Vector3f> > box_clouds;
+  box_clouds.push_back(createBoxOfPoints(Vector3f(1.1, 1.1, 1.1), Vector3f(3.9, 3.9, 3.9), 0.1));
+  box_clouds.push_back(createBoxOfPoints(Vector3f(2.1, 2.1, 2.1), Vector3f(4.9, 4.9, 4.9), 0.1));
+  MetaPointCloud boxes(box_clouds);
+  boxes.syncToDevice();
+  return boxes;
+}
+static std::vector<BitVoxelMeaning> meanings1112()
+{
+  std::vector<BitVoxelMeaning> m;
+  m.push_back(BitVoxelMeaning(11));
+  m.push_back(BitVoxelMeaning(12));
+  return m;
+}
+
+BOOST_AUTO_TEST_CASE(collide_bitvoxellist_with_prob_voxelmap)
+{
+  BitVectorVoxelList* list = new BitVectorVoxelList(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELLIST);
+  MetaPointCloud boxes = twoBoxes();
+  list->insertMetaPointCloud(boxes, meanings1112());
+  GpuVoxelsMapSharedPtr map_2(new ProbVoxelMap(Vector3ui(dimX, dimY, dimZ), 1.f, MT_PROBAB_VOXELMAP));
+  map_2->insertMetaPointCloud(boxes, eBVM_OCCUPIED);
+  BOOST_CHECK_MESSAGE(list->collideWith(map_2->as<ProbVoxelMap>(), 1.0) == 46, "Number of Collisions == 46");
+  delete list;
+}
+
+BOOST_AUTO_TEST_CASE(bitvoxellist_collide_with_types_both_map_types)
+{
+  BitVectorVoxelList list(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELLIST);
+  MetaPointCloud boxes = twoBoxes();
+  list.insertMetaPointCloud(boxes, meanings1112());
+  ProbVoxelMap pmap(Vector3ui(dimX, dimY, dimZ), 1.f);
+  BitVectorVoxelMap bmap(Vector3ui(dimX, dimY, dimZ), 1.f);
+  pmap.insertMetaPointCloud(boxes, eBVM_OCCUPIED);
+  bmap.insertMetaPointCloud(boxes, eBVM_OCCUPIED);
+  BitVectorVoxel types;
+  BOOST_CHECK(list.collideWithTypes(&pmap, types, 1.0) == 46);
+  BOOST_CHECK(types.bitVector().getBit(11) && types.bitVector().getBit(12));
+  BitVectorVoxel types_b;
+  BOOST_CHECK(list.collideWithTypes(&bmap, types_b, 1.0) == 46);
+  BOOST_CHECK(types_b.bitVector().getBit(11) && types_b.bitVector().getBit(12));
+  std::vector<size_t> per_meaning;
+  const size_t total = list.collideCountingPerMeaning(&bmap, per_meaning);
+  BOOST_CHECK(per_meaning.size() == 256 && per_meaning[11] == 27 && per_meaning[12] == 27);
+  BOOST_CHECK(total == 27 + 27 + per_meaning[eBVM_COLLISION]);
+}
+
+BOOST_AUTO_TEST_CASE(collide_bitvoxellist_with_prob_voxelmap_shifting)
+{
+  BitVectorVoxelList list(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELLIST);
+  std::vector<std::vector<Vector3f> > box_cloud;
+  box_cloud.push_back(createBoxOfPoints(Vector3f(1.1, 1.1, 1.1), Vector3f(3.9, 3.9, 3.9), 0.1));
+  MetaPointCloud box(box_cloud);
+  box.syncToDevice();
+  list.insertMetaPointCloud(box, eBVM_OCCUPIED);
+  GpuVoxelsMapSharedPtr map_2(new ProbVoxelMap(Vector3ui(dimX, dimY, dimZ), 1.f, MT_PROBAB_VOXELMAP));
+  map_2->insertMetaPointCloud(box, eBVM_OCCUPIED);
+  for (float shift = 0.0; shift < 4.0; shift += 0.5)
+  {
+    const size_t num_colls = list.collideWith(map_2->as<ProbVoxelMap>(), 1.0, Vector3i(shift, 0, 0));
+    const size_t want = shift < 1.0 ? 27 : shift < 2.0 ? 18 : shift < 3.0 ? 9 : 0;
+    BOOST_CHECK_MESSAGE(num_colls == want, "shift " << shift << ": " << num_colls << " != " << want);
+  }
+}
+
+BOOST_AUTO_TEST_CASE(bitvoxellist_insert_metapointcloud)
+{
+  BitVectorVoxelList list(Vector3ui(dimX, dimY, dimZ), 1, MT_BITVECTOR_VOXELLIST);
+  MetaPointCloud boxes = twoBoxes();
+  list.insertMetaPointCloud(boxes, meanings1112());
+  std::vector<uint32_t> ids;
+  std::vector<Vector3ui> coords;
+  std::vector<BitVectorVoxel> voxels;
+  list.copyToHost(ids, coords, voxels);
+  BOOST_CHECK_MESSAGE(ids.size() == 46, "Number of reduced cubes == 46");
+  BOOST_CHECK(list.getDimensions().x == 46);
+  BitVector<BIT_VECTOR_LENGTH> ref_bv;
+  ref_bv.setBit(11);
+  ref_bv.setBit(12);
+  size_t both = 0;
+  for (size_t i = 0; i < ids.size(); i++)
+    if (voxels[i].bitVector() == ref_bv)
+    {
+      ++both;
+      const Vector3ui& c = coords[i];
+      BOOST_CHECK_MESSAGE(c.x >= 2 && c.x <= 3 && c.y >= 2 && c.y <= 3 && c.z >= 2 && c.z <= 3, "merged voxel in the centre");
+    }
+  BOOST_CHECK_MESSAGE(both == 8, "Detect 8 overlapping voxels.");
+}
+
+BOOST_AUTO_TEST_CASE(bitmasked_collision)
+{
+  // GV/test/testing_voxellist.cu:739-864: three boxes with meanings 34 / 63 / 102 against one obstacle, side 0.025
+  const float side = 0.025f;
+  BitVectorVoxelList list(Vector3ui(dimX, dimY, dimZ), side, MT_BITVECTOR_VOXELLIST);
+  ProbVoxelMap map(Vector3ui(dimX, dimY, dimZ), side, MT_PROBAB_VOXELMAP);
+  map.insertPointCloud(createBoxOfPoints(Vector3f(0.111, 0.111, 0.111), Vector3f(0.799, 0.399, 0.399), 0.005), eBVM_OCCUPIED);
+  list.insertPointCloud(createBoxOfPoints(Vector3f(0.111, 0.311, 0.111), Vector3f(0.399, 0.599, 0.399), 0.005), BitVoxelMeaning(34));
+  list.insertPointCloud(createBoxOfPoints(Vector3f(0.311, 0.311, 0.111), Vector3f(0.599, 0.599, 0.399), 0.005), BitVoxelMeaning(63));
+  list.insertPointCloud(createBoxOfPoints(Vector3f(0.511, 0.311, 0.111), Vector3f(0.799, 0.599, 0.399), 0.005), BitVoxelMeaning(102));
+  const Vector3i offs[3] = {Vector3i(0, 0, 0), Vector3i(0, -4, 0), Vector3i(0, -4, -4)};
+  const size_t expect[3][5] = {{0, 0, 9, 15, 21}, {0, 0, 18, 30, 42}, {0, 0, 12, 20, 28}};
+  const int bits[4] = {33, 34, 63, 102};
+  for (int o = 0; o < 3; ++o)
+  {
+    BitVectorVoxel mask;
+    BOOST_CHECK(list.collideWithTypeMask(&map, mask, 1.0, offs[o]) == expect[o][0] * 64);
+    for (int b = 0; b < 4; ++b)
+    {
+      mask.bitVector().setBit(bits[b]);
+      const size_t got = list.collideWithTypeMask(&map, mask, 1.0, offs[o]);
+      BOOST_CHECK_MESSAGE(got == expect[o][b + 1] * 64, "offset " << o << " bit " << bits[b] << ": " << got);
+    }
+  }
+}
+
+BOOST_AUTO_TEST_SUITE_END()
+
+BOOST_AUTO_TEST_SUITE(facade)
+
+BOOST_AUTO_TEST_CASE(linkage_example)
+{
+  // example_how_to_link/gvl_linkage_test_lib.cpp: two overlapping boxes in two ProbVoxelMaps
+  GpuVoxelsSharedPtr gvl = GpuVoxels::getInstance();
+  gvl->initialize(100, 100, 100, 0.01);
+  gvl->initialize(10, 10, 10, 1.0);  // warns, parameters remain unchanged
+  uint32_t dx, dy, dz;
+  gvl->getDimensions(dx, dy, dz);
+  BOOST_CHECK(dx == 100 && dy == 100 && dz == 100);
+  BOOST_CHECK(gvl->addMap(MT_PROBAB_VOXELMAP, "myFirstMap") != NULL);
+  BOOST_CHECK(gvl->addMap(MT_PROBAB_VOXELMAP, "mySecondMap") != NULL);
+  BOOST_CHECK(gvl->addMap(MT_PROBAB_VOXELMAP, "mySecondMap") == NULL);  // duplicate name
+  const Vector3f center(0.5, 0.5, 0.5), box_size(0.4, 0.4, 0.4), overlap(0.1, 0.1, 0.1);
+  const Vector3f c1 = center - overlap, c2 = c1 + box_size, c3 = center + overlap, c4 = c3 - box_size;
+  BOOST_CHECK(gvl->insertBoxIntoMap(c1, c2, "myFirstMap", eBVM_OCCUPIED, 1));
+  BOOST_CHECK(gvl->insertBoxIntoMap(c4, c3, "mySecondMap", eBVM_OCCUPIED, 1));
+  BOOST_CHECK(!gvl->insertBoxIntoMap(c4, c3, "noSuchMap", eBVM_OCCUPIED, 1));
+  const size_t n = gvl->getMap("myFirstMap")->as<ProbVoxelMap>()->collideWith(gvl->getMap("mySecondMap")->as<ProbVoxelMap>());
+  // overlap = [0.4, 0.6]^3 sampled at 1 cm: count the voxels both clouds touch with the same float accumulation
+  std::vector<Vector3f> a = createBoxOfPoints(c1, c2, 0.01f), b = createBoxOfPoints(c4, c3, 0.01f);
+  std::vector<char> va(100 * 100 * 100, 0), vb(100 * 100 * 100, 0);
+  for (size_t i = 0; i < a.size(); ++i) va[size_t(floorf(a[i].z / 0.01f)) * 10000 + size_t(floorf(a[i].y / 0.01f)) * 100 + size_t(floorf(a[i].x / 0.01f))] = 1;
+  for (size_t i = 0; i < b.size(); ++i) vb[size_t(floorf(b[i].z / 0.01f)) * 10000 + size_t(floorf(b[i].y / 0.01f)) * 100 + size_t(floorf(b[i].x / 0.01f))] = 1;
+  size_t want = 0;
+  for (size_t i = 0; i < va.size(); ++i) want += va[i] && vb[i];
+  BOOST_CHECK_MESSAGE(n == want && n > 0, n << " collisions, expected " << want);
+  BOOST_CHECK(gvl->clearMap("myFirstMap"));
+  BOOST_CHECK(gvl->getMap("myFirstMap")->as<ProbVoxelMap>()->collideWith(gvl->getMap("mySecondMap")->as<ProbVoxelMap>()) == 0);
+  BOOST_CHECK(!gvl->clearMap("nope"));
+  bool thrown = false;
+  try { gvl->addMap(MT_BITVECTOR_OCTREE, "tree"); } catch (const std::string&) { thrown = true; }
+  BOOST_CHECK(thrown);
+  BOOST_CHECK(gvl->delMap("myFirstMap") && !gvl->delMap("myFirstMap"));
+  BOOST_CHECK(gvl->getMap("mySecondMap")->is<ProbVoxelMap>() && !gvl->getMap("mySecondMap")->is<BitVectorVoxelMap>());
+}
+
+BOOST_AUTO_TEST_CASE(batch_equals_planner_sequence)
+{
+  GpuVoxelsSharedPtr gvl = GpuVoxels::getInstance();
+  gvl->initialize(100, 100, 100, 0.01);
+  gvl->addMap(MT_BITVECTOR_VOXELMAP, "env");
+  gvl->addMap(MT_BITVECTOR_VOXELMAP, "robot");
+  gvl->insertBoxIntoMap(Vector3f(0.3, 0.3, 0.3), Vector3f(0.6, 0.6, 0.6), "env", eBVM_OCCUPIED, 1);
+  std::vector<std::vector<Vector3f> > links;
+  links.push_back(createBoxOfPoints(Vector3f(-0.05, -0.05, 0), Vector3f(0.05, 0.05, 0.3), 0.004));
+  links.push_back(createBoxOfPoints(Vector3f(-0.03, -0.03, 0), Vector3f(0.03, 0.03, 0.2), 0.004));
+  MetaPointCloud robot(links);
+  robot.syncToDevice();
+  std::vector<BitVoxelMeaning> mg;
+  mg.push_back(BitVoxelMeaning(10));
+  mg.push_back(BitVoxelMeaning(11));
+  const int n_cfg = 9;
+  std::vector<Matrix4f> T;
+  for (int c = 0; c < n_cfg; ++c)
+  {
+    const Matrix4f base = Matrix4f::createFromRotationAndTranslation(Matrix3f::createFromRPY(0.1f * c, 0.2f * c, 0.3f * c),
+                                                                    Vector3f(0.1f + 0.08f * c, 0.45f, 0.2f));
+    const Matrix4f joint = Matrix4f::createFromRotationAndTranslation(Matrix3f::createFromRPY(0.5f, 0, 0), Vector3f(0, 0, 0.3f));
+    T.push_back(base);
+    T.push_back(base * joint);
+  }
+  std::vector<size_t> counts;
+  BOOST_CHECK(gvl->collideRobotConfigurations(robot, mg, T, "env", counts));
+  BOOST_CHECK(counts.size() == size_t(n_cfg));
+  BitVectorVoxelMap* rob = gvl->getMap("robot")->as<BitVectorVoxelMap>();
+  BitVectorVoxelMap* env = gvl->getMap("env")->as<BitVectorVoxelMap>();
+  size_t sum = 0;
+  for (int c = 0; c < n_cfg; ++c)
+  {
+    // the reference's sequence: clear, transform each link, insert, collide
+    gvl->clearMap("robot");
+    MetaPointCloud moved(robot);
+    moved.transformSubCloud(0, &T[2 * c], &moved);
+    moved.transformSubCloud(1, &T[2 * c + 1], &moved);
+    gvl->insertMetaPointCloudIntoMap(moved, "robot", mg);
+    const size_t want = rob->collideWith(env, 1.0);
+    BOOST_CHECK_MESSAGE(counts[c] == want, "configuration " << c << ": " << counts[c] << " != " << want);
+    sum += want;
+  }
+  BOOST_CHECK(sum > 0);
+  gvl->delMap("env");
+  gvl->delMap("robot");
+}
+
+BOOST_AUTO_TEST_SUITE_END()
+
+int main(int argc, char** argv) { return mini_test::run_all(argc > 1 ? argv[1] : NULL); }

@@ -1,0 +1,40 @@
+"""The header-only C++ facade (include/gpu_voxels/, the reference's class API over the C ABI): it must compile with a
+plain g++ and link against libgvx.so (CPU check), and the reference's known-answer tests written against it must pass
+on the GPU (tests/cpp/test_facade.cpp)."""
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = os.path.join(ROOT, "tests", "cpp", "test_facade.cpp")
+EXE = os.path.join(ROOT, "tests", "cpp", "test_facade")
+CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+
+
+def _build():
+    from gpu_voxels_b200 import build as gvx_build
+    gvx_build.build()
+    deps = [SRC, os.path.join(ROOT, "tests", "cpp", "mini_boost_test.h"), os.path.join(ROOT, "include", "gvx.h")]
+    for d, _, fs in os.walk(os.path.join(ROOT, "include", "gpu_voxels")):
+        deps += [os.path.join(d, f) for f in fs]
+    if os.path.exists(EXE) and all(os.path.getmtime(EXE) >= os.path.getmtime(d) for d in deps):
+        return
+    subprocess.check_call([CXX, "-std=c++14", "-O1", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                           SRC, "-L" + os.path.join(ROOT, "gpu_voxels_b200"), "-lgvx",
+                           "-Wl,-rpath," + os.path.join(ROOT, "gpu_voxels_b200"),
+                           "-Wl,-rpath,$ORIGIN/../../gpu_voxels_b200", "-lpthread", "-o", EXE])
+
+
+def test_facade_compiles_and_links_with_plain_gxx():
+    _build()
+    assert os.path.exists(EXE)
+
+
+@pytest.mark.gpu
+def test_reference_known_answer_tests_through_the_cpp_facade():
+    _build()
+    r = subprocess.run([EXE], capture_output=True, text=True, timeout=600)
+    print(r.stdout[-4000:], r.stderr[-4000:])
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert " 0 failures" in r.stdout
