@@ -1,0 +1,123 @@
+"""Multi-GPU plumbing of the hot path: one process per GPU, torch.distributed (NCCL over NVLink on the GPUs, gloo in
+the CPU tests) for the only exchange the path has -- the reduction of collision results.
+
+The reference is single-GPU. The partition:
+  * dense maps: z-slabs. The linear voxel index is z-major (GV/voxelmap/TemplateVoxelMap.h:257-259), so the slab
+    [z0,z1) is the contiguous range [z0*dx*dy, z1*dx*dy) and a rank's shard is byte-identical to that slice of the
+    unsharded map. Every rank sees the whole cloud and keeps the points of its slab (gvx_map_create_slab).
+  * collide map x map / list x map: purely local, then ONE all-reduce of (count | per-meaning counts | 256-bit mask).
+  * batch of robot configurations: the environment map is replicated, the BATCH is split; counts are all-gathered.
+  * a non-zero offset.z needs a halo from the neighbour slab: not supported on slab maps (GVX_ERR_UNSUPPORTED).
+No CUDA code here and no voxel arithmetic: only ranges and collectives.
+"""
+import numpy as np
+
+
+def slab_for_rank(dz, rank, world):
+    """z-range [z0, z1) of `rank`: dz split as evenly as possible, the first dz % world ranks get one more slice."""
+    if not (0 <= rank < world):
+        raise ValueError("rank %d outside world of %d" % (rank, world))
+    if world > dz:
+        raise ValueError("more ranks (%d) than z-slices (%d)" % (world, dz))
+    base, rem = divmod(int(dz), int(world))
+    z0 = rank * base + min(rank, rem)
+    return z0, z0 + base + (1 if rank < rem else 0)
+
+
+def voxel_range_for_rank(dims, rank, world):
+    """linear voxel indices [first, first + n) held by `rank`"""
+    z0, z1 = slab_for_rank(dims[2], rank, world)
+    plane = int(dims[0]) * int(dims[1])
+    return z0 * plane, (z1 - z0) * plane
+
+
+def batch_range_for_rank(n_cfg, rank, world):
+    """configurations [c0, c1) of a planner batch handled by `rank` (may be empty when n_cfg < world)"""
+    base, rem = divmod(int(n_cfg), int(world))
+    c0 = rank * base + min(rank, rem)
+    return c0, c0 + base + (1 if rank < rem else 0)
+
+
+def list_entries_for_rank(sorted_ids, dims, rank, world, offset=0):
+    """[i0, i1) of a sorted voxel-list id array whose map voxel id + offset falls into `rank`'s slab: two binary
+    searches, since list ids are sorted (GV/voxellist/TemplateVoxelList.hpp:141-208)."""
+    first, n = voxel_range_for_rank(dims, rank, world)
+    ids = np.asarray(sorted_ids).astype(np.int64)
+    return int(np.searchsorted(ids, first - offset, "left")), int(np.searchsorted(ids, first + n - offset, "left"))
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+def _device_for_backend():
+    import torch
+    dist = _dist()
+    if dist.is_initialized() and dist.get_backend() == "nccl":
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
+
+
+def allreduce_collision_result(count, mask32=None, per_meaning=None, group=None):
+    """Sum the per-rank collision counts (and per-meaning counts) and OR the 256-bit meaning masks over all ranks in
+    ONE collective: a single int64 tensor [count | 256 per-meaning counts | 256 mask-bit flags] under SUM (NCCL has
+    no bit-OR; bit j of the mask is set iff its summed flag is > 0).
+    Returns (count, mask32 or None, per_meaning or None) as python int / numpy arrays."""
+    import torch
+    dist = _dist()
+    buf = torch.zeros(1 + 256 + 256, dtype=torch.int64)
+    buf[0] = int(count)
+    if per_meaning is not None:
+        buf[1:257] = torch.from_numpy(np.asarray(per_meaning, np.uint64).astype(np.int64))
+    if mask32 is not None:
+        bits = np.unpackbits(np.asarray(mask32, np.uint8).reshape(32), bitorder="little")
+        buf[257:513] = torch.from_numpy(bits.astype(np.int64))
+    dev = _device_for_backend()
+    t = buf.to(dev)
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    out = t.cpu().numpy()
+    total = int(out[0])
+    pm = out[1:257].astype(np.uint64) if per_meaning is not None else None
+    mk = np.packbits((out[257:513] > 0).astype(np.uint8), bitorder="little") if mask32 is not None else None
+    return total, mk, pm
+
+
+def allreduce_count_tensor(count_d, group=None):
+    """in-place SUM of a device-resident int64 count (the *_async collide variants write it): no host round trip"""
+    dist = _dist()
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(count_d, op=dist.ReduceOp.SUM, group=group)
+    return count_d
+
+
+def allreduce_flag(flag, group=None):
+    """OR of the per-rank 'points outside the map' / 'any collision' flags"""
+    import torch
+    dist = _dist()
+    t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=_device_for_backend())
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    return bool(t.item())
+
+
+def allgather_batch_counts(local_counts, n_cfg, group=None):
+    """counts of all n_cfg configurations from the per-rank shares of batch_range_for_rank, in configuration order"""
+    import torch
+    dist = _dist()
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return np.asarray(local_counts, np.uint64)
+    width = -(-int(n_cfg) // world)  # equal-sized slots so a plain all_gather works
+    dev = _device_for_backend()
+    mine = torch.zeros(width, dtype=torch.int64, device=dev)
+    lc = np.asarray(local_counts, np.uint64).astype(np.int64)
+    mine[: len(lc)] = torch.from_numpy(lc).to(dev)
+    parts = [torch.zeros(width, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(parts, mine, group=group)
+    out = np.zeros(int(n_cfg), np.uint64)
+    for r in range(world):
+        c0, c1 = batch_range_for_rank(n_cfg, r, world)
+        out[c0:c1] = parts[r].cpu().numpy()[: c1 - c0].astype(np.uint64)
+    return out
