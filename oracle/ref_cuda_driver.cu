@@ -20,6 +20,9 @@
 #include <gpu_voxels/voxel/DefaultCollider.hpp>
 #include <gpu_voxels/voxel/SVCollider.hpp>
 #include <gpu_voxels/voxelmap/kernels/VoxelMapOperations.hpp>
+// VoxelListOperations.hpp:137 calls getHighestVoxelPtr unqualified from namespace voxellist (accepted by the CUDA 7.5
+// era front end); make the name visible there without touching the reference source.
+namespace gpu_voxels { namespace voxellist { using voxelmap::getHighestVoxelPtr; } }
 #include <gpu_voxels/voxellist/kernels/VoxelListOperations.hpp>
 
 using namespace gpu_voxels;
@@ -86,6 +89,122 @@ int gvref_transform_cloud(const float* M16_h, const float* in_xyz, float* out_xy
   CK(cudaGetLastError());
   CK(cudaDeviceSynchronize());
   CK(cudaFree(m_d));
+  return 0;
+}
+
+
+static uint32_t sum_block_counters(uint32_t blocks) {
+  // host tail of collisionCheckWithCounterRelativeTransform (GV/voxelmap/TemplateVoxelMap.hpp:507-518)
+  cudaMemcpy(g_results_h, g_results_d, cMAX_NR_OF_BLOCKS * sizeof(uint16_t), cudaMemcpyDeviceToHost);
+  uint32_t n = 0;
+  for (uint32_t i = 0; i < blocks; i++) n += g_results_h[i];
+  return n;
+}
+
+// collisionCheckWithCounterRelativeTransform, offset 0 (GV/voxelmap/TemplateVoxelMap.hpp:486-519):
+// kernelCollideVoxelMapsDebug + 128 KiB D2H + host sum. a/b types: 0 = BitVectorVoxel, 4 = ProbabilisticVoxel.
+// Marks a (the kernel always does). Returns the count or -1.
+long long gvref_collide_map_map(void* a, int a_type, void* b, int b_type, uint32_t n, float thr) {
+  if (ensure_scratch()) return -1;
+  uint32_t bl, t; linear_load(n, &bl, &t);
+  DefaultCollider col(thr);
+  CK(cudaDeviceSynchronize());
+  if (a_type == 0 && b_type == 4)
+    voxelmap::kernelCollideVoxelMapsDebug<<<bl, t>>>((BitVectorVoxel*)a, n, (ProbabilisticVoxel*)b, col, g_results_d);
+  else if (a_type == 4 && b_type == 0)
+    voxelmap::kernelCollideVoxelMapsDebug<<<bl, t>>>((ProbabilisticVoxel*)a, n, (BitVectorVoxel*)b, col, g_results_d);
+  else if (a_type == 4 && b_type == 4)
+    voxelmap::kernelCollideVoxelMapsDebug<<<bl, t>>>((ProbabilisticVoxel*)a, n, (ProbabilisticVoxel*)b, col, g_results_d);
+  else
+    voxelmap::kernelCollideVoxelMapsDebug<<<bl, t>>>((BitVectorVoxel*)a, n, (BitVectorVoxel*)b, col, g_results_d);
+  CK(cudaGetLastError());
+  CK(cudaDeviceSynchronize());
+  return (long long)sum_block_counters(bl);
+}
+
+// insertMetaPointCloud with per-cloud meanings (GV/voxelmap/TemplateVoxelMap.hpp:631-664): builds the
+// MetaPointCloudStruct the way MetaPointCloud.cu does (struct + cloud_sizes + base addresses in device memory) and
+// uploads the meanings array per call like the reference.
+int gvref_insert_meta(void* map, int is_prob, uint32_t dx, uint32_t dy, uint32_t dz, float side, const float* xyz,
+                      const uint32_t* cloud_sizes_h, uint32_t n_clouds, const int32_t* meanings_h, int* any_outside_h) {
+  if (ensure_scratch()) return -1;
+  std::vector<Vector3f*> bases(n_clouds);
+  uint32_t acc = 0;
+  for (uint32_t c = 0; c < n_clouds; ++c) { bases[c] = (Vector3f*)xyz + acc; acc += cloud_sizes_h[c]; }
+  MetaPointCloudStruct st;
+  st.num_clouds = (uint16_t)n_clouds;
+  st.accumulated_cloud_size = acc;
+  MetaPointCloudStruct* st_d; BitVoxelMeaning* mg_d;
+  CK(cudaMalloc(&st.cloud_sizes, n_clouds * sizeof(uint32_t)));
+  CK(cudaMalloc(&st.clouds_base_addresses, n_clouds * sizeof(Vector3f*)));
+  CK(cudaMalloc(&st_d, sizeof(MetaPointCloudStruct)));
+  CK(cudaMalloc(&mg_d, n_clouds * sizeof(BitVoxelMeaning)));
+  CK(cudaMemcpy(st.cloud_sizes, cloud_sizes_h, n_clouds * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(st.clouds_base_addresses, bases.data(), n_clouds * sizeof(Vector3f*), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(st_d, &st, sizeof(MetaPointCloudStruct), cudaMemcpyHostToDevice));
+  std::vector<BitVoxelMeaning> mg(n_clouds);
+  for (uint32_t c = 0; c < n_clouds; ++c) mg[c] = (BitVoxelMeaning)meanings_h[c];
+  CK(cudaMemcpy(mg_d, mg.data(), n_clouds * sizeof(BitVoxelMeaning), cudaMemcpyHostToDevice));
+  CK(cudaMemset(g_outside_d, 0, sizeof(bool)));
+  uint32_t b, t; linear_load(acc, &b, &t);
+  CK(cudaDeviceSynchronize());
+  if (is_prob)
+    voxelmap::kernelInsertMetaPointCloud<<<b, t>>>((ProbabilisticVoxel*)map, st_d, mg_d, Vector3ui(dx, dy, dz), side, g_outside_d);
+  else
+    voxelmap::kernelInsertMetaPointCloud<<<b, t>>>((BitVectorVoxel*)map, st_d, mg_d, Vector3ui(dx, dy, dz), side, g_outside_d);
+  CK(cudaGetLastError());
+  bool o = false;
+  CK(cudaMemcpy(&o, g_outside_d, sizeof(bool), cudaMemcpyDeviceToHost));
+  CK(cudaDeviceSynchronize());
+  if (any_outside_h) *any_outside_h = o ? 1 : 0;
+  cudaFree(st.cloud_sizes); cudaFree(st.clouds_base_addresses); cudaFree(st_d); cudaFree(mg_d);
+  return 0;
+}
+
+// ProbVoxelMap::insertSensorData without ray casting (GV/voxelmap/ProbVoxelMap.hpp:52-102): kernelTransformSensorData
+// + kernelInsertSensorData<DummyRayCaster>. pose12_h = row-major [R|t]; raw_d: n sensor-frame points (device);
+// tmp_d: n points of scratch (device).
+int gvref_insert_sensor_data(void* map, uint32_t dx, uint32_t dy, uint32_t dz, float side, const float* pose12_h,
+                             float* raw_d, float* tmp_d, uint32_t n) {
+  Sensor s(Vector3f(pose12_h[3], pose12_h[7], pose12_h[11]),
+           Matrix3f(pose12_h[0], pose12_h[1], pose12_h[2], pose12_h[4], pose12_h[5], pose12_h[6], pose12_h[8],
+                    pose12_h[9], pose12_h[10]), n, 1);
+  Sensor* s_d;
+  CK(cudaMalloc(&s_d, sizeof(Sensor)));
+  CK(cudaMemcpy(s_d, &s, sizeof(Sensor), cudaMemcpyHostToDevice));
+  uint32_t b, t; linear_load(n, &b, &t);
+  voxelmap::kernelTransformSensorData<<<b, t>>>(s_d, (Vector3f*)raw_d, (Vector3f*)tmp_d);
+  CK(cudaGetLastError());
+  voxelmap::kernelInsertSensorData<<<b, t>>>((ProbabilisticVoxel*)map, dx * dy * dz, Vector3ui(dx, dy, dz), side, s_d,
+                                            (const Vector3f*)tmp_d, false, (BitVoxel<BIT_VECTOR_LENGTH>*)NULL,
+                                            (uint32_t)eBVM_OCCUPIED, voxelmap::DummyRayCaster());
+  CK(cudaGetLastError());
+  CK(cudaDeviceSynchronize());
+  CK(cudaFree(s_d));
+  return 0;
+}
+
+// BitVoxelList::collideWith(map) (GV/voxellist/TemplateVoxelList.hpp:731-774): kernelCollideWithVoxelMap + D2H + host sum
+long long gvref_collide_list_map(const uint32_t* ids, void* voxels, uint32_t size, const void* map, int map_type,
+                                 uint32_t dx, uint32_t dy, uint32_t dz, float thr, int ox, int oy, int oz) {
+  if (ensure_scratch()) return -1;
+  uint32_t bl, t; linear_load(size, &bl, &t);
+  DefaultCollider col(thr);
+  CK(cudaDeviceSynchronize());
+  if (map_type == 4)
+    voxellist::kernelCollideWithVoxelMap<<<bl, t>>>((const MapVoxelID*)ids, (BitVectorVoxel*)voxels, size,
+        (const ProbabilisticVoxel*)map, Vector3ui(dx, dy, dz), col, Vector3i(ox, oy, oz), g_results_d);
+  else
+    voxellist::kernelCollideWithVoxelMap<<<bl, t>>>((const MapVoxelID*)ids, (BitVectorVoxel*)voxels, size,
+        (const BitVectorVoxel*)map, Vector3ui(dx, dy, dz), col, Vector3i(ox, oy, oz), g_results_d);
+  CK(cudaGetLastError());
+  CK(cudaDeviceSynchronize());
+  return (long long)sum_block_counters(bl);
+}
+
+// clearMap (GV/voxelmap/TemplateVoxelMap.hpp:205-246)
+int gvref_clear_map(void* map, int is_prob, uint64_t n) {
+  CK(cudaMemset(map, is_prob ? 0x80 : 0x00, n * (is_prob ? 1 : 32)));
   return 0;
 }
 
