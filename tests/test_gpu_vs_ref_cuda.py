@@ -34,6 +34,8 @@ def _p(t):
 
 
 def _specials(p):
+    if len(p) < 16:
+        return p
     p[5] = [np.nan, 0.5, 0.5]
     p[6] = [0.5, np.inf, 0.5]
     p[7] = [-np.inf, 0.5, 0.5]
