@@ -91,7 +91,7 @@ class ClockSampler:
                     self.samples.append(f)
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._stop.wait(0.05)
 
     def __enter__(self):
         self._t = threading.Thread(target=self._run, daemon=True)
@@ -221,7 +221,20 @@ def run_gpu_arm(args):
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # NCCL announces its version on STDOUT when the first communicator comes up; the contract is ONE JSON line on
+        # stdout, so fd 1 points at stderr until the communicator exists.
+        sys.stdout.flush()
+        saved_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            warm = torch.zeros(1, device="cuda")
+            dist.all_reduce(warm)
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_fd, 1)
+            os.close(saved_fd)
     L = _lib.init(local_rank)
     # one explicit (non-default) stream shared by libgvx, torch events and NCCL, so CUDA events time libgvx's kernels
     stream = torch.cuda.Stream()
@@ -245,26 +258,44 @@ def run_gpu_arm(args):
     count_d = torch.zeros(1, dtype=torch.int64, device="cuda")
     pose_arr = [np.ascontiguousarray(p.reshape(-1)) for p in poses]
 
+    sizes_arr = np.full(world, N_FRAME, np.uint32)
+    poses_arr = np.ascontiguousarray(np.stack(pose_arr))
+    # [parity] all sub-frames concatenated in HBM (device-resident arm) and the all-gather target of the e2e arm
+    cat_d = [torch.cat(fr).contiguous() for fr in frames_d]
+    gathered = torch.empty((world * N_FRAME, 3), dtype=torch.float32, device="cuda")
+    own_d = torch.empty((N_FRAME, 3), dtype=torch.float32, device="cuda")
+
+    def fold_frames(points_d):
+        """log-odds update of ALL sub-frames (each with its own pose) in one launch; this rank keeps its slab's points"""
+        if world == 1:
+            _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(points_d.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
+                                            pose_arr[0].ctypes.data_as(C.c_void_p), 72))
+        else:
+            _lib.check(L.gvx_update_logodds_multi(env.handle, C.c_void_p(points_d.data_ptr()), _lib.MEM_DEVICE,
+                                                  sizes_arr.ctypes.data_as(C.c_void_p), world,
+                                                  poses_arr.ctypes.data_as(C.c_void_p), 72))
+
     def step_device(k):
         """inputs resident in HBM; result stays on the device (all-reduced when sharded)"""
-        for r in range(world):
-            f = frames_d[k % 2][r]
-            _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
-                                            pose_arr[r].ctypes.data_as(C.c_void_p), 72))
+        fold_frames(cat_d[k % 2])
         _lib.check(L.gvx_collide_map_map_async(env.handle, rob.handle, THR, None, 1, C.c_void_p(count_d.data_ptr())))
         if world > 1:
             dist.all_reduce(count_d)
 
     def step_e2e(k):
-        """through the C ABI with HOST buffers: H2D of the frame inside, count read back to the host"""
-        for r in range(world):
-            f = pinned[k % 2][r]
-            _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_HOST,
-                                            pose_arr[r].ctypes.data_as(C.c_void_p), 72))
+        """through the C ABI with HOST buffers: H2D of the frame inside, count read back to the host. Sharded: every
+        rank uploads ITS sensor's frame from pinned host memory and the frames are all-gathered over NVLink (each
+        rank needs the whole cloud to find its slab's points), instead of N x the PCIe traffic per rank."""
         if world > 1:
+            own_d.copy_(pinned[k % 2][rank], non_blocking=True)
+            dist.all_gather_into_tensor(gathered, own_d)
+            fold_frames(gathered)
             _lib.check(L.gvx_collide_map_map_async(env.handle, rob.handle, THR, None, 1, C.c_void_p(count_d.data_ptr())))
             dist.all_reduce(count_d)
             return int(count_d.item())
+        f = pinned[k % 2][0]
+        _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_HOST,
+                                        pose_arr[0].ctypes.data_as(C.c_void_p), 72))
         cnt = C.c_uint64(0)
         _lib.check(L.gvx_collide_map_map(env.handle, rob.handle, THR, None, 1, C.byref(cnt)))
         return cnt.value
@@ -334,7 +365,9 @@ def run_gpu_arm(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": workload_config(world),
             "e2e": {"value": n_vox * world * args.steps / (ms_e2e * 1e-3), "unit": "voxels/s",
-                    "h2d_bytes_per_step": N_FRAME * 12 * world + 48 * world, "d2h_bytes_per_step": 8,
+                    "h2d_bytes_per_step": N_FRAME * 12 * world + 48 * world, "d2h_bytes_per_step": 8 * world,
+                    "note": "per step, summed over ranks: every rank uploads its own sensor frame (pinned -> HBM), frames "
+                            "are all-gathered over NVLink, the count is all-reduced and read back by every rank",
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "k_collide_voxelwise<Prob,Bit,mark>", "achieved": achieved, "peak": peak,

@@ -274,6 +274,26 @@ class ProbVoxelMap(GpuVoxelsMap):
                                               int(delta_occupied)))
 
 
+def _insert_sensor_data_multi(self, frames, sensor_poses, delta_occupied=72):
+    """several sensor frames with their own poses in one launch (gvx_update_logodds_multi). frames: list of (n_i,3)
+    arrays, or ONE concatenated array / CUDA tensor together with frame_sizes = (sizes list)."""
+    if isinstance(frames, tuple):  # (concatenated points, sizes)
+        pts, sizes = frames
+    else:
+        sizes = [len(f) for f in frames]
+        pts = np.concatenate([np.ascontiguousarray(f, np.float32).reshape(-1, 3) for f in frames]) if frames else \
+            np.zeros((0, 3), np.float32)
+    p, n, kind, keep = _points_arg(pts)
+    sz = np.asarray(sizes, np.uint32)
+    assert int(sz.sum()) == n
+    poses = np.ascontiguousarray(np.stack([np.asarray(q, np.float32).reshape(-1)[:12] for q in sensor_poses]))
+    _lib.check(self._L.gvx_update_logodds_multi(self.handle, p, kind, sz.ctypes.data_as(C.c_void_p), len(sz),
+                                                poses.ctypes.data_as(C.c_void_p), int(delta_occupied)))
+
+
+ProbVoxelMap.insertSensorDataMulti = _insert_sensor_data_multi
+
+
 def transform_points(points, matrix4):
     """PointCloud::transform (kernelTransformCloud, GV/helpers/kernels/MetaPointCloudOperations.cu:77-91)"""
     L = _lib.init()

@@ -416,6 +416,36 @@ int gvx_update_logodds(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int 
   return GVX_OK;
 }
 
+int gvx_update_logodds_multi(gvx_handle_t h, const float* xyz_sensor, int mem_kind, const uint32_t* frame_sizes,
+                             uint32_t n_frames, const float* poses12, int delta_occ) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (m->type != kMapProb) return fail(GVX_ERR_UNSUPPORTED, "insertSensorData needs a ProbVoxelMap");
+  if (delta_occ < -127 || delta_occ > 127) return fail(GVX_ERR_INVALID, "delta %d outside int8 range", delta_occ);
+  if (!n_frames) return GVX_OK;
+  if (!frame_sizes || !poses12) return fail(GVX_ERR_INVALID, "null pointer");
+  const size_t off_pose = ((size_t)n_frames + 1) * 4, total = off_pose + (size_t)n_frames * 48;
+  int slot; void *dh, *dd;
+  int rc = desc_acquire(total, &slot, &dh, &dd);
+  if (rc) return rc;
+  uint32_t* prefix = (uint32_t*)dh;
+  uint64_t acc = 0;
+  for (uint32_t f = 0; f < n_frames; ++f) { prefix[f] = (uint32_t)acc; acc += frame_sizes[f]; }
+  if (acc > 0xFFFFFFFFull) return fail(GVX_ERR_INVALID, "more than 2^32-1 sensor points in one call");
+  prefix[n_frames] = (uint32_t)acc;
+  memcpy((char*)dh + off_pose, poses12, (size_t)n_frames * 48);
+  if (acc == 0) return GVX_OK;
+  if (!xyz_sensor) return fail(GVX_ERR_INVALID, "null point pointer");
+  if ((rc = desc_commit(slot, total))) return rc;
+  const float* xyz_d = nullptr;
+  if ((rc = points_to_device(xyz_sensor, acc, mem_kind, &xyz_d))) return rc;
+  GVX_CUDA(launch_update_logodds_multi(lctx(), m->view(), xyz_d, acc, (const uint32_t*)dd,
+                                       (const float*)((const char*)dd + off_pose), n_frames, delta_occ));
+  return GVX_OK;
+}
+
 // ---- collision counting, map x map --------------------------------------------------------------------
 static int collide_prepare(gvx_handle_t ha, gvx_handle_t hb, const int32_t off3[3], Map** a, Map** b, int64_t* off,
                            int64_t* i0, int64_t* i1) {

@@ -164,6 +164,64 @@ k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n,
   }
 }
 
+// Several sensor frames (each with its own pose) in ONE launch: frame f owns points [prefix[f], prefix[f+1]).
+// Same per-point arithmetic as k_update_logodds. Used when a z-slab rank folds the whole multi-sensor cloud and keeps
+// only its slab's points: one launch instead of one per frame.
+constexpr int kMaxFramesSmem = 64;
+__global__ void __launch_bounds__(kInsThreads)
+k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t* __restrict__ prefix_g,
+                       const float* __restrict__ poses_g, uint32_t n_frames, int delta) {
+  __shared__ float sh_pose[kMaxFramesSmem * 12];
+  __shared__ uint32_t sh_prefix[kMaxFramesSmem + 1];
+  __shared__ uint8_t sh_inside[kMaxFramesSmem];
+  const bool in_smem = n_frames <= (uint32_t)kMaxFramesSmem;
+  if (in_smem) {
+    for (uint32_t k = threadIdx.x; k < n_frames * 12; k += kInsThreads) sh_pose[k] = poses_g[k];
+    for (uint32_t k = threadIdx.x; k <= n_frames; k += kInsThreads) sh_prefix[k] = prefix_g[k];
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k < n_frames; k += kInsThreads) {
+      const float* P = sh_pose + 12 * k;
+      sh_inside[k] = coord_to_voxel(P[3], m.side) < m.dx && coord_to_voxel(P[7], m.side) < m.dy &&
+                     coord_to_voxel(P[11], m.side) < m.dz;
+    }
+    __syncthreads();
+  }
+  const uint32_t* prefix = in_smem ? sh_prefix : prefix_g;
+  const float* poses = in_smem ? sh_pose : poses_g;
+  const uint64_t slab = (uint64_t)m.dx * m.dy;
+  const unsigned long long n = prefix[n_frames];
+  const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
+  const unsigned long long n_round = (n + 31ull) & ~31ull;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n_round; i += stride) {
+    bool live = false;
+    uint64_t idx = 0;
+    if (i < n) {
+      const uint32_t f = find_cloud(prefix, n_frames, (uint32_t)i);
+      const float* P = poses + 12 * (size_t)f;
+      const bool sensor_inside = in_smem ? (bool)sh_inside[f]
+                                         : (coord_to_voxel(P[3], m.side) < m.dx && coord_to_voxel(P[7], m.side) < m.dy &&
+                                            coord_to_voxel(P[11], m.side) < m.dz);
+      const float rx = __ldg(xyz + 3 * i), ry = __ldg(xyz + 3 * i + 1), rz = __ldg(xyz + 3 * i + 2);
+      float wx = affine_row(P, rx, ry, rz), wy = affine_row(P + 4, rx, ry, rz), wz = affine_row(P + 8, rx, ry, rz);
+      if (wz < 0.0f) {
+        const double factor = (double)__fdiv_rn(P[11], __fsub_rn(P[11], wz));
+        const float qx = (float)((double)rx * factor), qy = (float)((double)ry * factor), qz = (float)((double)rz * factor);
+        wx = affine_row(P, qx, qy, qz); wy = affine_row(P + 4, qx, qy, qz); wz = affine_row(P + 8, qx, qy, qz);
+      }
+      if (!(isnan(wx) || isnan(wy) || isnan(wz))) {
+        const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
+        if (cx < m.dx && cy < m.dy && cz < m.dz && sensor_inside && cz >= m.z0 && cz < m.z1) {
+          live = true;
+          idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+        }
+      }
+    }
+    const unsigned long long key = live ? idx : (~0ull - (threadIdx.x & 31));
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
+  }
+}
+
 // BitVoxelMap::clearBits / clearBit: voxel &= ~mask, written back only where it changes.
 __global__ void __launch_bounds__(kInsThreads)
 k_clear_bits(uint8_t* data, unsigned long long n, BitVoxelWords mask) {
@@ -219,6 +277,13 @@ cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const fl
                                   const Affine12& pose, int delta) {
   ++*c.launches;
   k_update_logodds<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, n, pose, delta);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
+                                        const uint32_t* prefix_d, const float* poses_d, uint32_t n_frames, int delta) {
+  ++*c.launches;
+  k_update_logodds_multi<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, prefix_d, poses_d, n_frames, delta);
   return cudaGetLastError();
 }
 

@@ -44,6 +44,8 @@ struct Affine12 { float a[12]; };  // row-major [R|t], passed to kernels by valu
 cudaError_t launch_transform(const LaunchCtx& c, const float* in_d, float* out_d, uint64_t n, const Affine12& M);
 cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
                                   const Affine12& pose, int delta);
+cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
+                                        const uint32_t* prefix_d, const float* poses_d, uint32_t n_frames, int delta);
 cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8]);
 
 

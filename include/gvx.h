@@ -141,6 +141,12 @@ int gvx_transform_points(const float* in_xyz, float* out_xyz, uint64_t n, int me
 int gvx_update_logodds(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int mem_kind, const float pose12[12],
                        int delta_occ);
 
+/* The same update for several sensor frames, each with its own pose, in ONE launch (multi-camera rigs; z-slab ranks
+ * that fold the whole rig's cloud and keep only their slab's points). xyz_sensor: the concatenated frames;
+ * frame_sizes[n_frames] (host); poses12: n_frames row-major [R|t] (host). Asynchronous. */
+int gvx_update_logodds_multi(gvx_handle_t h, const float* xyz_sensor, int mem_kind, const uint32_t* frame_sizes,
+                             uint32_t n_frames, const float* poses12, int delta_occ);
+
 /* ---- collision counting, map x map -------------------------------------------------------------------- */
 /* collideWith (BitVoxelMap::collideWith GV/voxelmap/BitVoxelMap.hpp:191-203, ProbVoxelMap::collideWith
  * GV/voxelmap/ProbVoxelMap.hpp:144-155 -> collisionCheckWithCounterRelativeTransform

@@ -176,6 +176,25 @@ def test_update_logodds_frames(gv, oracle):
 
 
 # ---- collisions --------------------------------------------------------------------------------------------
+def test_update_logodds_multi_frame_equals_sequence(gv, oracle):
+    """gvx_update_logodds_multi: several frames, each with its own pose, in one launch == the frames one by one"""
+    dims, side = (128, 96, 80), 0.02
+    frames = [_depth_frame(40 + k, 96, 64) for k in range(5)] + [np.zeros((0, 3), np.float32)]
+    poses = [np.array([[0, 0, 1, 0.05 * k], [-1, 0, 0, 0.5], [0, -1, 0, 0.4 + 0.02 * k]], np.float32) for k in range(5)]
+    poses.append(np.array([[1, 0, 0, 9.0], [0, 1, 0, 0], [0, 0, 1, 0]], np.float32))  # empty frame, sensor outside
+    poses[3][0, 3] = -0.5  # sensor origin outside the map: that frame must contribute nothing
+    for slab in (None, (17, 53)):
+        m = gv.ProbVoxelMap(dims, side, slab=slab)
+        z0, z1 = slab if slab else (0, dims[2])
+        r = oracle.new_map(PROB, dims, z0, z1)
+        for rep in range(2):
+            m.insertSensorDataMulti(frames, poses)
+            for f, q in zip(frames, poses):
+                oracle.update_logodds(r, dims, side, f, q, 72, z0, z1)
+        assert np.array_equal(m.download(), r)
+        assert (r != -128).sum() > 1000
+
+
 def _filled_pair(gv, oracle, ta, tb, dims, side, seed):
     hi = dims[0] * side
     pa = _cloud(seed, 60000, -0.05 * hi, 1.05 * hi)
