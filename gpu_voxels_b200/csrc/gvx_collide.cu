@@ -40,7 +40,7 @@ template <int AT, int BT, bool MARK, bool TYPES>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 k_collide_voxelwise(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long long i_begin, long long i_end,
                     long long off, int thr, ReduceScratch* scratch, ResultBlock* out_d, ResultBlock* out_h,
-                    unsigned long long* count_out_d) {
+                    unsigned long long* count_out_d, PeerReduce pr) {
   constexpr int U = (AT == kMapBit && BT == kMapBit) ? 2 : kUnroll;  // 128 B in flight per thread either way
   uint32_t cnt = 0;
   uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -82,7 +82,7 @@ k_collide_voxelwise(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long
       }
     }
   }
-  finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d);
+  finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
 }
 
 // ---- Prob x Prob, 16 voxels per 128-bit load. Requires (a + off) and b 16-byte aligned for i % 16 == 0.
@@ -91,7 +91,7 @@ template <bool MARK>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long long i_begin, long long i_end,
                     long long off, int thr, ReduceScratch* scratch, ResultBlock* out_d, ResultBlock* out_h,
-                    unsigned long long* count_out_d) {
+                    unsigned long long* count_out_d, PeerReduce pr) {
   uint32_t cnt = 0;
   const uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const uint32_t t4 = (uint32_t)(uint8_t)thr * 0x01010101u;
@@ -145,7 +145,7 @@ k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long l
         *reinterpret_cast<uint4*>(a + vb + off + (v << 4)) = make_uint4(wa[0], wa[1], wa[2], wa[3]);
     }
   }
-  finish_block<false>(cnt, acc, scratch, out_d, out_h, count_out_d);
+  finish_block<false>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
 }
 
 template <int AT, int BT>
@@ -153,7 +153,7 @@ static cudaError_t launch_voxelwise(const LaunchCtx& c, int grid, uint8_t* a, co
                                     long long i1, long long off, int thr, bool mark, bool types,
                                     unsigned long long* out) {
 #define GVX_GO(M, T) k_collide_voxelwise<AT, BT, M, T><<<grid, kThreads, 0, c.stream>>>( \
-      a, b, i0, i1, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, out)
+      a, b, i0, i1, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer)
   if (types) { if (mark) GVX_GO(true, true); else GVX_GO(false, true); }
   else       { if (mark) GVX_GO(true, false); else GVX_GO(false, false); }
 #undef GVX_GO
@@ -174,8 +174,8 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
     if (aligned) {
       long long work = (n / 16 + kThreads * kUnroll - 1) / (kThreads * kUnroll);
       int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));
-      if (mark) k_collide_prob_prob<true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d);
-      else k_collide_prob_prob<false><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d);
+      if (mark) k_collide_prob_prob<true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
+      else k_collide_prob_prob<false><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
       return cudaGetLastError();
     }
   }

@@ -90,6 +90,19 @@ struct ResultBlock {
   uint32_t pad;
   unsigned long long per_meaning[256];
 };
+// Fused all-reduce of a collision count over NVLink peer memory (one process per GPU): every rank owns a mailbox in
+// its HBM with 2 (epoch parity) x kMaxPeers slots of {value, epoch}; peers[r] is rank r's mailbox mapped into this
+// process (CUDA IPC). The last CTA of a counting kernel stores its rank's count into its slot of EVERY mailbox
+// (st.global on mapped peer pointers), then waits until all slots of its own mailbox carry the current epoch and
+// sums them -- the collective is part of the kernel, no NCCL launch follows. world <= 1 disables it.
+constexpr int kMaxPeers = 16;
+struct PeerSlot { unsigned long long value; unsigned long long epoch; };
+struct PeerReduce {
+  PeerSlot* peers[kMaxPeers];
+  int rank;
+  int world;
+  unsigned long long epoch;  // > 0, identical on all ranks for one collective, strictly increasing
+};
 constexpr int kMaxGrid = 148 * 16;  // upper bound on CTAs of a reducing kernel
 struct ReduceScratch {
   unsigned long long partial_count[kMaxGrid];

@@ -13,6 +13,7 @@ struct LaunchCtx {
   ResultBlock* result_d;      // device copy of the result block
   ResultBlock* result_hmap_d; // device alias of the pinned, mapped host result block
   uint64_t* launches;         // kernel launch counter (host)
+  PeerReduce peer;            // world <= 1: no fused all-reduce
 };
 
 // collideWith map x map. a/b: device base pointers of the voxel arrays; a is indexed at i + off.

@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(kThreads, 4)
 k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxels, unsigned long long size,
                    const uint8_t* __restrict__ map, long long n_total, long long map_first, long long map_n,
                    int thr_i, float thr_f, long long off, BitVoxelWords mask_in, ReduceScratch* scratch,
-                   ResultBlock* out_d, ResultBlock* out_h, unsigned long long* count_out_d) {
+                   ResultBlock* out_d, ResultBlock* out_h, unsigned long long* count_out_d, PeerReduce pr) {
   __shared__ uint32_t sh_hist[MODE == 3 ? 256 : 1];
   if (MODE == 3) {
     sh_hist[threadIdx.x] = 0u;  // kThreads == 256
@@ -212,7 +212,7 @@ k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxel
     __threadfence();
     __syncthreads();
   }
-  const bool last = finish_block<MODE == 1>(cnt, acc, scratch, out_d, out_h, count_out_d);
+  const bool last = finish_block<MODE == 1>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
   if (MODE == 3 && last) {
     out_h->per_meaning[threadIdx.x] = __ldcg(&out_d->per_meaning[threadIdx.x]);
     __threadfence_system();
@@ -224,9 +224,9 @@ static void go_list(const LaunchCtx& c, int grid, bool mark, const uint32_t* ids
                     const uint8_t* map, long long n_total, long long map_first, long long map_n, int thr_i, float thr_f,
                     long long off, const BitVoxelWords& mk, unsigned long long* out) {
   if (mark)
-    k_collide_list_map<MAPT, MODE, true><<<grid, kThreads, 0, c.stream>>>(ids, voxels, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, c.scratch_d, c.result_d, c.result_hmap_d, out);
+    k_collide_list_map<MAPT, MODE, true><<<grid, kThreads, 0, c.stream>>>(ids, voxels, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
   else
-    k_collide_list_map<MAPT, MODE, false><<<grid, kThreads, 0, c.stream>>>(ids, voxels, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, c.scratch_d, c.result_d, c.result_hmap_d, out);
+    k_collide_list_map<MAPT, MODE, false><<<grid, kThreads, 0, c.stream>>>(ids, voxels, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
 }
 
 cudaError_t launch_collide_list_map(const LaunchCtx& c, int mode, const uint32_t* ids, void* voxels, uint64_t size,

@@ -6,12 +6,39 @@ namespace gvx {
 
 constexpr int kThreads = 256;  // block size of every reducing kernel
 
+// One thread: publish `mine` to every rank's mailbox, wait for all ranks' values of this epoch, return the sum.
+// The wait is bounded (~4 s of SM clocks): a rank that never arrives yields ~0ull instead of a hung GPU.
+__device__ __forceinline__ unsigned long long peer_allreduce_sum(unsigned long long mine, const PeerReduce& pr) {
+  const int par = (int)(pr.epoch & 1ull);
+  for (int r = 0; r < pr.world; ++r) {
+    PeerSlot* s = pr.peers[r] + par * kMaxPeers + pr.rank;
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&s->value), "l"(mine) : "memory");
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&s->epoch), "l"(pr.epoch) : "memory");
+  }
+  unsigned long long sum = 0;
+  const long long t0 = clock64();
+  for (int r = 0; r < pr.world; ++r) {
+    const PeerSlot* s = pr.peers[pr.rank] + par * kMaxPeers + r;
+    unsigned long long e;
+    for (;;) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(e) : "l"(&s->epoch) : "memory");
+      if (e == pr.epoch) break;
+      if (clock64() - t0 > 8000000000ll) return ~0ull;
+      __nanosleep(100);
+    }
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(&s->value) : "memory");
+    sum += v;
+  }
+  return sum;
+}
+
 // Block-level finish shared by all collide kernels: reduce (count, mask) over the CTA, publish the partial,
 // let the last CTA produce the final result.
 template <bool TYPES>
 __device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (&acc)[8], ReduceScratch* s,
                                              ResultBlock* out_d, ResultBlock* out_h,
-                                             unsigned long long* count_out_d) {
+                                             unsigned long long* count_out_d, const PeerReduce& pr) {
   __shared__ unsigned long long sh_cnt[kThreads / 32];
   __shared__ uint32_t sh_mask[8];
   __shared__ bool sh_last;
@@ -72,6 +99,7 @@ __device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (
     unsigned long long tot = 0;
 #pragma unroll
     for (int w = 0; w < kThreads / 32; ++w) tot += sh_cnt[w];
+    if (pr.world > 1) tot = peer_allreduce_sum(tot, pr);
     out_d->count = tot;
     out_h->count = tot;
     out_d->flag = tot != 0;
