@@ -275,12 +275,26 @@ def run_gpu_arm(args):
                                                   sizes_arr.ctypes.data_as(C.c_void_p), world,
                                                   poses_arr.ctypes.data_as(C.c_void_p), 72))
 
-    def step_device(k):
-        """inputs resident in HBM; result stays on the device (all-reduced when sharded)"""
-        fold_frames(cat_d[k % 2])
+    # sharded: the count is all-reduced INSIDE the collide kernel over NVLink peer memory (CUDA IPC mailboxes); NCCL
+    # stays the fallback when the IPC mapping is refused
+    fused = False
+    if world > 1 and not args.nccl_count:
+        from gpu_voxels_b200 import sharding
+        fused = sharding.connect_peer_mailboxes()
+
+    def collide_global(host_count=None):
+        if fused:
+            _lib.check(L.gvx_collide_map_map_allreduce(env.handle, rob.handle, THR, 1, host_count,
+                                                       C.c_void_p(count_d.data_ptr())))
+            return
         _lib.check(L.gvx_collide_map_map_async(env.handle, rob.handle, THR, None, 1, C.c_void_p(count_d.data_ptr())))
         if world > 1:
             dist.all_reduce(count_d)
+
+    def step_device(k):
+        """inputs resident in HBM; result stays on the device (all-reduced when sharded)"""
+        fold_frames(cat_d[k % 2])
+        collide_global()
 
     def step_e2e(k):
         """through the C ABI with HOST buffers: H2D of the frame inside, count read back to the host. Sharded: every
@@ -290,8 +304,11 @@ def run_gpu_arm(args):
             own_d.copy_(pinned[k % 2][rank], non_blocking=True)
             dist.all_gather_into_tensor(gathered, own_d)
             fold_frames(gathered)
-            _lib.check(L.gvx_collide_map_map_async(env.handle, rob.handle, THR, None, 1, C.c_void_p(count_d.data_ptr())))
-            dist.all_reduce(count_d)
+            if fused:
+                cnt = C.c_uint64(0)
+                collide_global(C.byref(cnt))
+                return cnt.value
+            collide_global()
             return int(count_d.item())
         f = pinned[k % 2][0]
         _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_HOST,
@@ -377,6 +394,7 @@ def run_gpu_arm(args):
             "insert": {"metric": "insertSensorData (log-odds) points/s", "value": N_FRAME / (ins_ms * 1e-3),
                        "unit": "points/s", "ms_per_frame": ins_ms, "points": N_FRAME},
             "clocks": clk.summary(), "collisions_last_step": int(last_count),
+            "count_allreduce": ("in-kernel over NVLink peer memory" if fused else "nccl") if world > 1 else "none",
         }
         if cpu is not None:
             line["cpu_baseline"] = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -392,6 +410,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--nccl-count", action="store_true", help="all-reduce the count with NCCL instead of in-kernel")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

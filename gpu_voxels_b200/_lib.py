@@ -50,6 +50,11 @@ SIGNATURES = {
     "gvx_collide_map_map_async": (C.c_int, [u64, u64, f32, vp, C.c_int, vp]),
     "gvx_collide_map_map_any": (C.c_int, [u64, u64, f32, P(C.c_int)]),
     "gvx_collide_map_map_types": (C.c_int, [u64, u64, f32, C.c_int, vp, P(u64)]),
+    "gvx_peer_mailbox_create": (C.c_int, [vp]),
+    "gvx_peer_mailbox_connect": (C.c_int, [C.c_int, C.c_int, vp]),
+    "gvx_peer_mailbox_disconnect": (C.c_int, []),
+    "gvx_collide_map_map_allreduce": (C.c_int, [u64, u64, f32, C.c_int, P(u64), vp]),
+    "gvx_collide_list_map_allreduce": (C.c_int, [u64, u64, f32, C.c_int, P(u64), vp]),
     "gvx_list_create": (C.c_int, [P(u64), u32, u32, u32, f32]),
     "gvx_list_destroy": (C.c_int, [u64]),
     "gvx_list_clear": (C.c_int, [u64]),

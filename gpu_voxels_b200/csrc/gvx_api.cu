@@ -64,6 +64,11 @@ int gvx_shutdown(void) {
     if (g.desc_ev[k]) cudaEventDestroy(g.desc_ev[k]);
     g.desc_d[k] = g.desc_h[k] = nullptr; g.desc_cap[k] = 0; g.desc_ev[k] = nullptr;
   }
+  for (int r = 0; r < g.peer_world; ++r)
+    if (r != g.peer_rank && g.peer_ptr[r]) cudaIpcCloseMemHandle(g.peer_ptr[r]);
+  for (int r = 0; r < kMaxPeers; ++r) g.peer_ptr[r] = nullptr;
+  g.peer_world = 1; g.peer_rank = 0;
+  if (g.peer_mailbox) { cudaFree(g.peer_mailbox); g.peer_mailbox = nullptr; }
   cudaFree(g.scratch_d); cudaFree(g.result_d); cudaFreeHost(g.result_h);
   cudaStreamDestroy(g.own_stream);
   g.stage_d = nullptr; g.stage_cap = 0;
@@ -493,6 +498,72 @@ int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const
   if (rc) return rc;
   GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
                                   mark != 0, false, (unsigned long long*)count_d));
+  return GVX_OK;
+}
+
+// ---- fused all-reduce over peer memory ----------------------------------------------------------------
+int gvx_peer_mailbox_create(void* ipc_handle64) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is exchanged as 64 bytes");
+  if (!ipc_handle64) return fail(GVX_ERR_INVALID, "null handle buffer");
+  if (!g.peer_mailbox) {
+    GVX_CUDA(cudaMalloc((void**)&g.peer_mailbox, 2 * kMaxPeers * sizeof(PeerSlot)));
+    GVX_CUDA(cudaMemset(g.peer_mailbox, 0, 2 * kMaxPeers * sizeof(PeerSlot)));
+    GVX_CUDA(cudaDeviceSynchronize());
+  }
+  cudaIpcMemHandle_t h;
+  GVX_CUDA(cudaIpcGetMemHandle(&h, g.peer_mailbox));
+  memcpy(ipc_handle64, &h, 64);
+  return GVX_OK;
+}
+
+int gvx_peer_mailbox_connect(int rank, int world, const void* all_handles) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return fail(GVX_ERR_INVALID, "bad rank %d / world %d", rank, world);
+  if (!g.peer_mailbox) return fail(GVX_ERR_INVALID, "gvx_peer_mailbox_create has not been called");
+  if (world > 1 && !all_handles) return fail(GVX_ERR_INVALID, "null handles");
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) { g.peer_ptr[r] = g.peer_mailbox; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)all_handles + 64 * r, 64);
+    void* p = nullptr;
+    GVX_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    g.peer_ptr[r] = (PeerSlot*)p;
+  }
+  g.peer_rank = rank;
+  g.peer_world = world;
+  g.peer_epoch = 0;
+  return GVX_OK;
+}
+
+int gvx_peer_mailbox_disconnect(void) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  if (!g.ready) return GVX_OK;
+  cudaStreamSynchronize(g.stream);
+  for (int r = 0; r < g.peer_world; ++r)
+    if (r != g.peer_rank && g.peer_ptr[r]) cudaIpcCloseMemHandle(g.peer_ptr[r]);
+  for (int r = 0; r < kMaxPeers; ++r) g.peer_ptr[r] = nullptr;
+  g.peer_world = 1; g.peer_rank = 0;
+  return GVX_OK;
+}
+
+int gvx_collide_map_map_allreduce(gvx_handle_t ha, gvx_handle_t hb, float thr, int mark, uint64_t* count,
+                                  uint64_t* count_d) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map *a, *b;
+  int64_t off, i0, i1;
+  int rc = collide_prepare(ha, hb, nullptr, &a, &b, &off, &i0, &i1);
+  if (rc) return rc;
+  GVX_CUDA(launch_collide_map_map(lctx_allreduce(), a->data, a->type, b->data, b->type, i0, i1, 0,
+                                  float_to_probability(thr), mark != 0, false, (unsigned long long*)count_d));
+  if (count) {
+    GVX_CUDA(cudaStreamSynchronize(g.stream));
+    *count = g.result_h->count;
+    if (*count == ~0ull) return fail(GVX_ERR_CUDA, "peer all-reduce timed out: a rank did not arrive");
+  }
   return GVX_OK;
 }
 

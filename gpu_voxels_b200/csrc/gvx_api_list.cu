@@ -319,4 +319,23 @@ int gvx_collide_list_map_async(gvx_handle_t hl, gvx_handle_t hm, float thr, cons
   return GVX_OK;
 }
 
+int gvx_collide_list_map_allreduce(gvx_handle_t hl, gvx_handle_t hm, float thr, int mark, uint64_t* count,
+                                   uint64_t* count_d) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  ListCollideArgs a;
+  int rc = list_collide_prepare(hl, hm, nullptr, &a);
+  if (rc) return rc;
+  // an empty list still has to take part in the collective: launch with size 0
+  GVX_CUDA(launch_collide_list_map(lctx_allreduce(), 0, a.l->ids[a.l->cur], a.l->voxels[a.l->cur], a.l->size, a.m->data,
+                                   a.m->type, a.m->n_total(), (uint64_t)a.m->z0 * a.m->dx * a.m->dy, a.m->n_voxels(),
+                                   float_to_probability(thr), thr, 0, mark != 0, nullptr, (unsigned long long*)count_d));
+  if (count) {
+    GVX_CUDA(cudaStreamSynchronize(g.stream));
+    *count = g.result_h->count;
+    if (*count == ~0ull) return fail(GVX_ERR_CUDA, "peer all-reduce timed out: a rank did not arrive");
+  }
+  return GVX_OK;
+}
+
 }  // extern "C"

@@ -71,6 +71,12 @@ struct Context {
   void* bat_counts = nullptr; size_t bat_counts_cap = 0;
   void* bat_counts_h = nullptr; size_t bat_counts_h_cap = 0;
   size_t bat_seen_budget = (size_t)4 << 30;  // bytes of "seen" scratch per wave of configurations
+  // fused all-reduce over NVLink peer memory (gvx_peer_*): this rank's mailbox, the peers' mailboxes mapped through
+  // CUDA IPC, and the collective sequence number
+  PeerSlot* peer_mailbox = nullptr;
+  PeerSlot* peer_ptr[kMaxPeers] = {};
+  int peer_rank = 0, peer_world = 1;
+  unsigned long long peer_epoch = 0;
   uint64_t launches = 0;
   uint64_t next_handle = 1;
   std::unordered_map<uint64_t, Map> maps;
@@ -102,7 +108,20 @@ inline int fail(int code, const char* fmt, ...) {
   do { if (!g.ready) return fail(GVX_ERR_NOT_INITIALIZED, "gvx_init has not been called"); } while (0)
 
 inline LaunchCtx lctx() {
-  return LaunchCtx{g.stream, g.sm_count, g.scratch_d, g.result_d, g.result_hmap_d, &g.launches};
+  LaunchCtx c{g.stream, g.sm_count, g.scratch_d, g.result_d, g.result_hmap_d, &g.launches, PeerReduce{}};
+  c.peer.world = 1;
+  return c;
+}
+// launch context of a counting kernel that all-reduces its count over the connected peers (next epoch)
+inline LaunchCtx lctx_allreduce() {
+  LaunchCtx c = lctx();
+  if (g.peer_world > 1) {
+    for (int r = 0; r < g.peer_world; ++r) c.peer.peers[r] = g.peer_ptr[r];
+    c.peer.rank = g.peer_rank;
+    c.peer.world = g.peer_world;
+    c.peer.epoch = ++g.peer_epoch;
+  }
+  return c;
 }
 inline Map* find_map(gvx_handle_t h) {
   auto it = g.maps.find(h);

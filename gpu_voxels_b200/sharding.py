@@ -121,3 +121,36 @@ def allgather_batch_counts(local_counts, n_cfg, group=None):
         c0, c1 = batch_range_for_rank(n_cfg, r, world)
         out[c0:c1] = parts[r].cpu().numpy()[: c1 - c0].astype(np.uint64)
     return out
+
+
+def connect_peer_mailboxes(group=None):
+    """Set up the fused collide + all-reduce path (gvx_collide_*_allreduce): every rank creates its mailbox, the 64-byte
+    CUDA IPC handles are exchanged with one all_gather, every rank maps its peers. Returns True when connected; False
+    (and the caller keeps using NCCL for the count) when the process group is missing or the IPC mapping is refused."""
+    import ctypes as C
+    import torch
+    from . import _lib
+    dist = _dist()
+    if not dist.is_initialized() or dist.get_world_size(group) < 2:
+        return False
+    L = _lib.init()
+    mine = (C.c_ubyte * 64)()
+    rc = L.gvx_peer_mailbox_create(mine)
+    ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=_device_for_backend())
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+    if not ok.item():
+        return False
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = _device_for_backend()
+    t = torch.tensor(list(bytes(mine)), dtype=torch.uint8, device=dev)
+    parts = [torch.zeros(64, dtype=torch.uint8, device=dev) for _ in range(world)]
+    dist.all_gather(parts, t, group=group)
+    blob = b"".join(bytes(p.cpu().numpy().tobytes()) for p in parts)
+    rc = L.gvx_peer_mailbox_connect(rank, world, C.c_char_p(blob))
+    ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+    if not ok.item():
+        L.gvx_peer_mailbox_disconnect()
+        return False
+    dist.barrier(group=group)
+    return True

@@ -167,6 +167,22 @@ int gvx_collide_map_map_any(gvx_handle_t a, gvx_handle_t b, float thr, int* flag
 int gvx_collide_map_map_types(gvx_handle_t a, gvx_handle_t b, float thr, int mark,
                               uint8_t mask_inout32[GVX_BITVOXEL_BYTES], uint64_t* count);
 
+/* ---- multi-GPU: collision count all-reduced INSIDE the collide kernel over NVLink peer memory ------------- */
+/* One process per GPU (not in the reference). Every rank creates a small mailbox in its HBM and exports it as a
+ * 64-byte CUDA IPC handle; the host program exchanges the handles (any transport: torch.distributed, MPI, files)
+ * and every rank maps all peers' mailboxes. From then on the *_allreduce collide variants finish with the last CTA
+ * storing this rank's count into every peer's mailbox and summing all ranks' counts: compute + collective are ONE
+ * kernel, no NCCL launch follows. All ranks must issue the same sequence of *_allreduce calls. */
+int gvx_peer_mailbox_create(void* ipc_handle64_out);
+int gvx_peer_mailbox_connect(int rank, int world, const void* all_handles /* world x 64 bytes, rank order */);
+int gvx_peer_mailbox_disconnect(void);
+/* collideWith on this rank's z-slab (offset 0), result = sum over all ranks; count (host, nullable: NULL = no sync)
+ * and count_d (device, nullable) both receive the GLOBAL count */
+int gvx_collide_map_map_allreduce(gvx_handle_t a, gvx_handle_t b, float thr, int mark, uint64_t* count,
+                                  uint64_t* count_d);
+int gvx_collide_list_map_allreduce(gvx_handle_t list, gvx_handle_t map, float thr, int mark, uint64_t* count,
+                                   uint64_t* count_d);
+
 /* ---- voxel lists (BitVectorVoxelList) ----------------------------------------------------------------- */
 /* GpuVoxels::addMap(MT_BITVECTOR_VOXELLIST) -> TemplateVoxelList ctor (GV/GpuVoxels.cpp:213-221,
  * GV/voxellist/TemplateVoxelList.hpp:67-86). Storage is the reference's SoA: id[u32] = linear voxel index,

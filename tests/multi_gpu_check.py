@@ -1,0 +1,108 @@
+"""Multi-GPU check of the sharded path on REAL GPUs (one rank per GPU), run as
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tests/multi_gpu_check.py
+Not collected by pytest (the -m gpu tier runs on one GPU; kernels that wait on other ranks must never share a GPU).
+Checks, bit-exactly against the CPU oracle on the unsharded grid:
+  * z-slab shards of Prob and BitVector maps filled from the whole cloud,
+  * collideWith with the count all-reduced INSIDE the kernel over NVLink peer memory == NCCL all-reduce == oracle,
+    repeated (epoch parity double-buffering), map x map and list x map,
+  * batch of robot configurations split over ranks and all-gathered.
+"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import gpu_voxels_b200 as gv  # noqa: E402
+from gpu_voxels_b200 import _lib, sharding  # noqa: E402
+from oracle import gvoracle as orc  # noqa: E402
+
+BIT, PROB = 0, 4
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    sys.stdout.flush()
+    fd = os.dup(1); os.dup2(2, 1)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dist.all_reduce(torch.zeros(1, device="cuda")); torch.cuda.synchronize()
+    os.dup2(fd, 1); os.close(fd)
+    L = _lib.init(local)
+    stream = torch.cuda.Stream(); torch.cuda.set_stream(stream)
+    _lib.check(L.gvx_set_stream(C.c_void_p(stream.cuda_stream)))
+    fused = sharding.connect_peer_mailboxes()
+    assert fused, "CUDA IPC peer mailboxes could not be connected"
+
+    dims, side = (96, 80, 101), 0.01  # 101 slices: uneven slabs
+    n = dims[0] * dims[1] * dims[2]
+    rng = np.random.Generator(np.random.PCG64(5))
+    env_pts = rng.uniform(-0.01, 1.02, size=(200000, 3)).astype(np.float32)
+    rob_pts = np.concatenate([env_pts[:30000], rng.uniform(0, 1.0, size=(90000, 3)).astype(np.float32)])
+    slab = sharding.slab_for_rank(dims[2], rank, world)
+    env = gv.ProbVoxelMap(dims, side, slab=slab)
+    rob = gv.BitVectorVoxelMap(dims, side, slab=slab)
+    env.insertPointCloud(env_pts, 1)
+    rob.insertMetaPointCloud(gv.MetaPointCloud([rob_pts[:50000], rob_pts[50000:]]), [9, 70])
+    r_env, r_rob = orc.new_map(PROB, dims), orc.new_map(BIT, dims)
+    orc.insert_points(r_env, PROB, dims, side, env_pts, 1)
+    orc.insert_meta(r_rob, BIT, dims, side, rob_pts, [50000, 70000], [9, 70])
+    first, n_loc = sharding.voxel_range_for_rank(dims, rank, world)
+    assert np.array_equal(env.download(), r_env[first:first + n_loc]), "Prob shard differs from the slice of the full map"
+    assert np.array_equal(rob.download().reshape(-1), r_rob[first * 32:(first + n_loc) * 32]), "Bit shard differs"
+    want = orc.collide_map_map(r_rob.copy(), BIT, r_env, PROB, n, 1.0, 0, False)
+    assert want > 1000
+    cnt_d = torch.zeros(1, dtype=torch.int64, device="cuda")
+    for it in range(7):  # odd and even epochs
+        host = C.c_uint64(0)
+        _lib.check(L.gvx_collide_map_map_allreduce(rob.handle, env.handle, 1.0, 0, C.byref(host), C.c_void_p(cnt_d.data_ptr())))
+        assert host.value == want and int(cnt_d.item()) == want, (it, host.value, int(cnt_d.item()), want)
+    # back-to-back without host syncs in between, then one sync
+    for it in range(20):
+        _lib.check(L.gvx_collide_map_map_allreduce(rob.handle, env.handle, 1.0, 0, None, C.c_void_p(cnt_d.data_ptr())))
+    torch.cuda.synchronize()
+    assert int(cnt_d.item()) == want
+    # NCCL path gives the same
+    _lib.check(L.gvx_collide_map_map_async(rob.handle, env.handle, 1.0, None, 0, C.c_void_p(cnt_d.data_ptr())))
+    dist.all_reduce(cnt_d)
+    assert int(cnt_d.item()) == want
+    # list x map: replicated list, sharded map
+    lst = gv.BitVectorVoxelList(dims, side)
+    lst.insertMetaPointCloud(gv.MetaPointCloud([rob_pts[:50000], rob_pts[50000:]]), [9, 70])
+    r_lst = orc.VoxelList(dims, side)
+    r_lst.insert_meta(rob_pts, [50000, 70000], [9, 70])
+    l_want = r_lst.collide(0, r_env, PROB, 1.0, 0, False)[0]
+    host = C.c_uint64(0)
+    _lib.check(L.gvx_collide_list_map_allreduce(lst.handle, env.handle, 1.0, 0, C.byref(host), None))
+    assert host.value == l_want and l_want > 0, (host.value, l_want)
+    tot, per = lst.collideCountingPerMeaning(env, mark=False)
+    g_tot, _, g_per = sharding.allreduce_collision_result(tot, per_meaning=per)
+    w_tot, _, w_per = r_lst.collide(3, r_env, PROB, 1.0, 0, False)
+    assert g_tot == w_tot and np.array_equal(g_per, w_per)
+    # batch split over ranks (environment replicated)
+    full_env = gv.BitVectorVoxelMap(dims, side)
+    full_env.insertPointCloud(env_pts, 1)
+    links = [rob_pts[:4000] - 0.5, rob_pts[4000:7000] - 0.5]
+    T = np.tile(np.eye(4, dtype=np.float32), (13, 2, 1, 1))
+    T[:, :, :3, 3] = rng.uniform(0.3, 0.7, size=(13, 2, 3)).astype(np.float32)
+    c0, c1 = sharding.batch_range_for_rank(13, rank, world)
+    mine = gv.batch_robot_collide(full_env, gv.MetaPointCloud(links), [4, 5], T[c0:c1]) if c1 > c0 else np.zeros(0, np.uint64)
+    allc = sharding.allgather_batch_counts(mine, 13)
+    r_full = orc.new_map(BIT, dims)
+    orc.insert_points(r_full, BIT, dims, side, env_pts, 1)
+    w = orc.batch_robot_collide(r_full, BIT, dims, side, np.concatenate(links), [4000, 3000], [4, 5], T, None, 1.0)
+    assert np.array_equal(allc, w), (allc, w)
+    dist.barrier()
+    if rank == 0:
+        print("multi_gpu_check ok: world %d, fused in-kernel all-reduce == NCCL == oracle (%d, list %d), batch split ok" % (world, want, l_want))
+    _lib.check(L.gvx_peer_mailbox_disconnect())
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
