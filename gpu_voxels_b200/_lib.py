@@ -25,6 +25,7 @@ SIGNATURES = {
     "gvx_sync": (C.c_int, []),
     "gvx_device_info": (C.c_int, [P(C.c_int), P(u64), P(u64), C.c_char_p]),
     "gvx_launch_count": (u64, []),
+    "gvx_set_l2_fetch_granularity": (C.c_int, [C.c_int, P(C.c_int)]),
     "gvx_buffer_create": (C.c_int, [P(u64), u64]),
     "gvx_buffer_destroy": (C.c_int, [u64]),
     "gvx_buffer_upload": (C.c_int, [u64, u64, vp, u64]),

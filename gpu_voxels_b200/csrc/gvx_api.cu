@@ -114,6 +114,19 @@ int gvx_device_info(int* sm_count, uint64_t* free_bytes, uint64_t* total_bytes, 
 
 uint64_t gvx_launch_count(void) { return g.launches; }
 
+int gvx_set_l2_fetch_granularity(int bytes, int* previous) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  size_t cur = 0;
+  GVX_CUDA(cudaDeviceGetLimit(&cur, cudaLimitMaxL2FetchGranularity));
+  if (previous) *previous = (int)cur;
+  if (bytes == 0) return GVX_OK;
+  if (bytes != 32 && bytes != 64 && bytes != 128) return fail(GVX_ERR_INVALID, "granularity must be 32, 64 or 128");
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  GVX_CUDA(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)bytes));
+  return GVX_OK;
+}
+
 // ---- device buffers (PointCloud / MetaPointCloud storage of the C++ facade) ---------------------------------
 int gvx_buffer_create(gvx_handle_t* h, uint64_t bytes) {
   std::lock_guard<std::mutex> lk(g.mu);

@@ -78,6 +78,10 @@ int gvx_device_info(int* sm_count, uint64_t* free_bytes, uint64_t* total_bytes, 
 /* number of kernels this library has launched since gvx_init (bench.py reports it as gpu_launches) */
 uint64_t gvx_launch_count(void);
 
+/* cudaLimitMaxL2FetchGranularity (32 / 64 / 128 bytes; 0 = query only): how much DRAM the L2 fetches around a missing
+ * 32-byte sector. The gather kernels (list x map, random inserts) touch one sector per access. */
+int gvx_set_l2_fetch_granularity(int bytes, int* previous);
+
 /* ---- device buffers ----------------------------------------------------------------------------------- */
 /* Device-resident storage for point clouds: what PointCloud / MetaPointCloud hold in the reference
  * (cudaMalloc + cudaMemcpy in GV/helpers/PointCloud.cu:32-120, GV/helpers/MetaPointCloud.cu:24-140). The device
