@@ -176,6 +176,20 @@ class GpuVoxelsMap:
         assert a.nbytes == self.getMemoryUsage()
         _lib.check(self._L.gvx_map_upload(self.handle, a.ctypes.data_as(C.c_void_p)))
 
+    # -- occupancy summary (BitVectorVoxelMap): 1 bit per voxel kept in sync by the library
+    def refreshSummary(self):
+        _lib.check(self._L.gvx_map_refresh_summary(self.handle))
+
+    def summary(self):
+        """-> (bool array of this slab's voxels, valid flag); empty array for maps without a summary"""
+        n = self.numVoxels()
+        words = np.zeros((n + 31) // 32, np.uint32)
+        valid = C.c_int(0)
+        _lib.check(self._L.gvx_map_summary_download(self.handle, words.ctypes.data_as(C.c_void_p), len(words),
+                                                    C.byref(valid)))
+        bits = np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool)
+        return bits, bool(valid.value)
+
     # -- clearing
     def clearMap(self):
         _lib.check(self._L.gvx_map_clear(self.handle))
@@ -292,6 +306,14 @@ def _insert_sensor_data_multi(self, frames, sensor_poses, delta_occupied=72):
 
 
 ProbVoxelMap.insertSensorDataMulti = _insert_sensor_data_multi
+
+
+GVX_OPT_USE_SUMMARY = 1
+
+
+def set_option(option, value):
+    """gvx_set_option: GVX_OPT_USE_SUMMARY = 0 makes every collide stream the voxels (the reference's access pattern)"""
+    _lib.check(_lib.init().gvx_set_option(int(option), int(value)))
 
 
 def transform_points(points, matrix4):

@@ -49,7 +49,10 @@ int gvx_shutdown(void) {
   std::lock_guard<std::mutex> lk(g.mu);
   if (!g.ready) return GVX_OK;
   cudaDeviceSynchronize();
-  for (auto& kv : g.maps) if (kv.second.owned && kv.second.data) cudaFree(kv.second.data);
+  for (auto& kv : g.maps) {
+    if (kv.second.owned && kv.second.data) cudaFree(kv.second.data);
+    if (kv.second.occ) cudaFree(kv.second.occ);
+  }
   g.maps.clear();
   lists_free_all();
   for (auto& kv : g.buffers) if (kv.second.p) cudaFree(kv.second.p);
@@ -211,6 +214,12 @@ static int map_make(gvx_handle_t* h, int map_type, void* wrap, uint32_t dx, uint
     cudaError_t e = cudaMalloc(&m.data, m.bytes());
     if (e != cudaSuccess) { cudaGetLastError(); return fail(GVX_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", m.bytes(), cudaGetErrorString(e)); }
     GVX_CUDA(cudaMemsetAsync(m.data, map_type == GVX_MT_PROBAB_VOXELMAP ? 0x80 : 0x00, m.bytes(), g.stream));
+    if (map_type == GVX_MT_BITVECTOR_VOXELMAP) {  // occupancy summary, 1 bit per voxel
+      e = cudaMalloc((void**)&m.occ, m.occ_bytes());
+      if (e != cudaSuccess) { cudaGetLastError(); cudaFree(m.data); return fail(GVX_ERR_NOMEM, "cudaMalloc(summary) failed: %s", cudaGetErrorString(e)); }
+      GVX_CUDA(cudaMemsetAsync(m.occ, 0, m.occ_bytes(), g.stream));
+      m.occ_valid = true;
+    }
   }
   const uint64_t id = g.next_handle++;
   g.maps.emplace(id, m);
@@ -240,11 +249,16 @@ int gvx_map_destroy(gvx_handle_t h) {
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   if (m->owned) GVX_CUDA(cudaFree(m->data));
+  if (m->occ) GVX_CUDA(cudaFree(m->occ));
   g.maps.erase(h);
   return GVX_OK;
 }
 static int map_clear_locked(Map* m) {
   GVX_CUDA(cudaMemsetAsync(m->data, m->type == kMapProb ? 0x80 : 0x00, m->bytes(), g.stream));
+  if (m->occ) {  // an empty map has an empty summary: clearing also re-validates it
+    GVX_CUDA(cudaMemsetAsync(m->occ, 0, m->occ_bytes(), g.stream));
+    m->occ_valid = true;
+  }
   return GVX_OK;
 }
 int gvx_map_clear(gvx_handle_t h) {
@@ -262,7 +276,8 @@ int gvx_map_clear_bits(gvx_handle_t h, const uint8_t mask32[GVX_BITVOXEL_BYTES])
   if (m->type != kMapBit) return fail(GVX_ERR_UNSUPPORTED, "clearBits needs a BitVectorVoxelMap");
   uint32_t w[8];
   memcpy(w, mask32, 32);
-  GVX_CUDA(launch_clear_bits(lctx(), m->data, m->n_voxels(), w));
+  GVX_CUDA(launch_clear_bits(lctx(), m->data, m->n_voxels(), w, m->occ));
+  if (m->occ) m->occ_valid = true;  // the kernel re-derives every summary word
   return GVX_OK;
 }
 int gvx_map_clear_meaning(gvx_handle_t h, int meaning) {
@@ -286,7 +301,10 @@ int gvx_map_device_ptr(gvx_handle_t h, void** data_d, uint64_t* first_voxel, uin
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
-  if (data_d) *data_d = m->data;
+  if (data_d) {
+    *data_d = m->data;
+    m->occ_valid = false;  // the caller may write voxels behind the library's back: gvx_map_refresh_summary re-validates
+  }
   if (first_voxel) *first_voxel = (uint64_t)m->z0 * m->dx * m->dy;
   if (n_voxels) *n_voxels = m->n_voxels();
   return GVX_OK;
@@ -320,8 +338,45 @@ int gvx_map_upload(gvx_handle_t h, const void* host_buf) {
   Map* m = find_map(h);
   if (!m || !host_buf) return fail(GVX_ERR_INVALID, "unknown map handle or null buffer");
   GVX_CUDA(cudaMemcpyAsync(m->data, host_buf, m->bytes(), cudaMemcpyHostToDevice, g.stream));
+  if (m->occ) {
+    GVX_CUDA(launch_env_bitmap(lctx(), m->data, kMapBit, m->n_voxels(), 0, m->occ));
+    m->occ_valid = true;
+  }
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   return GVX_OK;
+}
+
+int gvx_map_refresh_summary(gvx_handle_t h) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (!m->occ) return GVX_OK;  // ProbVoxelMap or wrapped memory: nothing to refresh
+  GVX_CUDA(launch_env_bitmap(lctx(), m->data, kMapBit, m->n_voxels(), 0, m->occ));
+  m->occ_valid = true;
+  return GVX_OK;
+}
+
+int gvx_map_summary_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, int* valid) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (valid) *valid = m->occ_valid ? 1 : 0;
+  if (!m->occ || !words) return GVX_OK;
+  const uint64_t have = (m->n_voxels() + 31) / 32;
+  if (n_words > have) n_words = have;
+  GVX_CUDA(cudaMemcpyAsync(words, m->occ, n_words * 4, cudaMemcpyDeviceToHost, g.stream));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  return GVX_OK;
+}
+
+int gvx_set_option(int option, int value) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  switch (option) {
+    case GVX_OPT_USE_SUMMARY: g.use_summary = value != 0; return GVX_OK;
+    default: return fail(GVX_ERR_INVALID, "unknown option %d", option);
+  }
 }
 
 // ---- voxelisation -------------------------------------------------------------------------------------
@@ -493,7 +548,8 @@ int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32
   int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1);
   if (rc) return rc;
   GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
-                                  mark != 0, false, nullptr));
+                                  mark != 0, false, nullptr,
+                                  g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
   if (count) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
     *count = g.result_h->count;
@@ -510,7 +566,8 @@ int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const
   int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1);
   if (rc) return rc;
   GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
-                                  mark != 0, false, (unsigned long long*)count_d));
+                                  mark != 0, false, (unsigned long long*)count_d,
+                                  g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
   return GVX_OK;
 }
 
@@ -571,7 +628,8 @@ int gvx_collide_map_map_allreduce(gvx_handle_t ha, gvx_handle_t hb, float thr, i
   int rc = collide_prepare(ha, hb, nullptr, &a, &b, &off, &i0, &i1);
   if (rc) return rc;
   GVX_CUDA(launch_collide_map_map(lctx_allreduce(), a->data, a->type, b->data, b->type, i0, i1, 0,
-                                  float_to_probability(thr), mark != 0, false, (unsigned long long*)count_d));
+                                  float_to_probability(thr), mark != 0, false, (unsigned long long*)count_d,
+                                  g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
   if (count) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
     *count = g.result_h->count;
@@ -588,7 +646,8 @@ int gvx_collide_map_map_any(gvx_handle_t ha, gvx_handle_t hb, float thr, int* fl
   int rc = collide_prepare(ha, hb, nullptr, &a, &b, &off, &i0, &i1);
   if (rc) return rc;
   GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, 0, float_to_probability(thr),
-                                  false, false, nullptr));
+                                  false, false, nullptr,
+                                  g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   if (flag) *flag = g.result_h->count != 0;
   return GVX_OK;
@@ -605,7 +664,8 @@ int gvx_collide_map_map_types(gvx_handle_t ha, gvx_handle_t hb, float thr, int m
   if (a->type != kMapBit || b->type != kMapProb)
     return fail(GVX_ERR_UNSUPPORTED, "collideWithTypes is implemented for BitVectorVoxelMap x ProbVoxelMap");
   GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, 0, float_to_probability(thr),
-                                  mark != 0, true, nullptr));
+                                  mark != 0, true, nullptr,
+                                  g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   if (count) *count = g.result_h->count;
   if (mask_inout32) {

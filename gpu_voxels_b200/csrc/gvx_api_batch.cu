@@ -67,7 +67,12 @@ int gvx_batch_robot_collide(gvx_handle_t env, const float* base_xyz, int mem_kin
   const float* xyz_d = nullptr;
   if ((rc = points_to_device(base_xyz, n_pts, mem_kind, &xyz_d))) return rc;
 
-  GVX_CUDA(launch_env_bitmap(lctx(), m->data, m->type, n_vox, float_to_probability(thr), (uint32_t*)g.bat_bits));
+  // environment occupancy, 1 bit per voxel: a BitVectorVoxelMap's summary is exactly that; otherwise build it
+  const uint32_t* env_bits = (g.use_summary && m->type == kMapBit) ? m->occ_if_valid() : nullptr;
+  if (!env_bits) {
+    GVX_CUDA(launch_env_bitmap(lctx(), m->data, m->type, n_vox, float_to_probability(thr), (uint32_t*)g.bat_bits));
+    env_bits = (const uint32_t*)g.bat_bits;
+  }
   GVX_CUDA(cudaMemsetAsync(g.bat_counts, 0, (size_t)n_cfg * 8, g.stream));
   BatchDesc d;
   d.prefix_d = (const uint32_t*)g.bat_tr;
@@ -78,7 +83,7 @@ int gvx_batch_robot_collide(gvx_handle_t env, const float* base_xyz, int mem_kin
   for (uint32_t c0 = 0; c0 < n_cfg; c0 += (uint32_t)wave) {
     const uint32_t w = (uint32_t)(n_cfg - c0 < wave ? n_cfg - c0 : wave);
     GVX_CUDA(cudaMemsetAsync(g.bat_seen, 0, (size_t)w * words * 4, g.stream));
-    GVX_CUDA(launch_batch_collide(lctx(), xyz_d, d, (uint32_t)n_pts, (const uint32_t*)g.bat_bits, (uint32_t*)g.bat_seen,
+    GVX_CUDA(launch_batch_collide(lctx(), xyz_d, d, (uint32_t)n_pts, env_bits, (uint32_t*)g.bat_seen,
                                   words, c0, w, (unsigned long long*)g.bat_counts));
   }
   GVX_CUDA(cudaMemcpyAsync(g.bat_counts_h, g.bat_counts, (size_t)n_cfg * 8, cudaMemcpyDeviceToHost, g.stream));

@@ -148,6 +148,126 @@ k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long l
   finish_block<false>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
 }
 
+// ---- summary kernel: occupancy of a BitVectorVoxel side comes from its 1-bit-per-voxel summary (Map::occ) instead
+// of its 32-byte voxels; a ProbabilisticVoxel side is still streamed (1 B per voxel, 32 voxels per two 128-bit loads).
+// One thread handles a group of 32 consecutive voxels per step: mask_a & mask_b, popcount. The voxels themselves are
+// only touched where a collision needs a write-back (MARK) or its meaning bits (TYPES) -- sparse.
+// Traffic per voxel: Prob x Bit 1.125 B (vs 33), Bit x Bit 0.25 B (vs 64). Requires off == 0.
+__device__ __forceinline__ uint32_t prob_group_mask(const uint4& lo, const uint4& hi, uint32_t t4) {
+  const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+  uint32_t m = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t c = __vcmpges4(w[k], t4) & 0x01010101u;  // 1 per byte with occupancy >= threshold
+    m |= (((c * 0x01020408u) >> 24) & 0xFu) << (4 * k);    // gather the 4 flags into a nibble
+  }
+  return m;
+}
+
+template <int AT, int BT, bool MARK, bool TYPES>
+__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const uint32_t* __restrict__ occ_a,
+                  const uint32_t* __restrict__ occ_b, long long n, int thr, ReduceScratch* scratch, ResultBlock* out_d,
+                  ResultBlock* out_h, unsigned long long* count_out_d, PeerReduce pr) {
+  constexpr int U = 4;
+  uint32_t cnt = 0;
+  uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const uint32_t t4 = (uint32_t)(uint8_t)thr * 0x01010101u;
+  const long long n_full = n >> 5;  // complete 32-voxel groups
+  const long long stride = (long long)gridDim.x * kThreads * U;
+  for (long long base = (long long)blockIdx.x * kThreads * U; base < n_full; base += stride) {
+    uint4 alo[U], ahi[U], blo[U], bhi[U];
+    uint32_t ma[U], mb[U];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long g = base + u * kThreads + threadIdx.x;
+      ok[u] = g < n_full;
+      if (ok[u]) {
+        if (AT == kMapBit) ma[u] = __ldg(occ_a + g);
+        else {
+          const uint4* p = reinterpret_cast<const uint4*>(a + (g << 5));
+          if (MARK) { alo[u] = __ldcg(p); ahi[u] = __ldcg(p + 1); } else { alo[u] = ld_stream_u4(p); ahi[u] = ld_stream_u4(p + 1); }
+        }
+        if (BT == kMapBit) mb[u] = __ldg(occ_b + g);
+        else {
+          const uint4* p = reinterpret_cast<const uint4*>(b + (g << 5));
+          blo[u] = ld_stream_u4(p); bhi[u] = ld_stream_u4(p + 1);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!ok[u]) continue;
+      const long long g = base + u * kThreads + threadIdx.x;
+      if (AT != kMapBit) ma[u] = prob_group_mask(alo[u], ahi[u], t4);
+      if (BT != kMapBit) mb[u] = prob_group_mask(blo[u], bhi[u], t4);
+      uint32_t hit = ma[u] & mb[u];
+      cnt += __popc(hit);
+      if (MARK || TYPES) {
+        while (hit) {  // rare: colliding voxels only
+          const int j = __ffs(hit) - 1;
+          hit &= hit - 1;
+          const long long i = (g << 5) + j;
+          if (AT == kMapBit) {
+            uint32_t* vp = reinterpret_cast<uint32_t*>(a + (size_t)i * kBitVoxelBytes);
+            if (TYPES) {
+              const BitVoxelWords v = ld_voxel(vp);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) acc[k] |= v.w[k];
+              if (MARK && !(v.w[0] & 4u)) vp[0] = v.w[0] | 4u;
+            } else if (MARK) {
+              const uint32_t w0 = __ldcg(vp);
+              if (!(w0 & 4u)) vp[0] = w0 | 4u;  // insert(eBVM_COLLISION); occupancy (and the summary) unchanged
+            }
+          } else if (MARK) {
+            if (((const int8_t*)a)[i] != 127) ((int8_t*)a)[i] = 127;
+          }
+        }
+      }
+    }
+  }
+  // tail: fewer than 32 voxels, voxel-wise by the first warp of CTA 0
+  if (blockIdx.x == 0 && threadIdx.x < 32) {
+    const long long i = (n_full << 5) + threadIdx.x;
+    if (i < n) {
+      BitVoxelWords va;
+      bool oa, ob;
+      int pa = 0;
+      if (AT == kMapBit) oa = (__ldg(occ_a + (i >> 5)) >> (i & 31)) & 1u;
+      else { pa = ((const volatile int8_t*)a)[i]; oa = pa >= thr; }
+      if (BT == kMapBit) ob = (__ldg(occ_b + (i >> 5)) >> (i & 31)) & 1u;
+      else ob = (int)ld_stream_i8(b + i) >= thr;
+      if (oa && ob) {
+        ++cnt;
+        if (AT == kMapBit && (MARK || TYPES)) {
+          va = ld_voxel(a + (size_t)i * kBitVoxelBytes);
+          if (TYPES) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] |= va.w[k];
+          }
+          if (MARK && !(va.w[0] & 4u)) *(uint32_t*)(a + (size_t)i * kBitVoxelBytes) = va.w[0] | 4u;
+        } else if (MARK && AT != kMapBit) {
+          if (pa != 127) ((int8_t*)a)[i] = 127;
+        }
+      }
+    }
+  }
+  finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
+}
+
+template <int AT, int BT>
+static cudaError_t launch_summary(const LaunchCtx& c, int grid, uint8_t* a, const uint8_t* b, const uint32_t* occ_a,
+                                  const uint32_t* occ_b, long long n, int thr, bool mark, bool types,
+                                  unsigned long long* out) {
+#define GVX_GO(M, T) k_collide_summary<AT, BT, M, T><<<grid, kThreads, 0, c.stream>>>( \
+      a, b, occ_a, occ_b, n, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer)
+  if (types) { if (mark) GVX_GO(true, true); else GVX_GO(false, true); }
+  else       { if (mark) GVX_GO(true, false); else GVX_GO(false, false); }
+#undef GVX_GO
+  return cudaGetLastError();
+}
+
 template <int AT, int BT>
 static cudaError_t launch_voxelwise(const LaunchCtx& c, int grid, uint8_t* a, const uint8_t* b, long long i0,
                                     long long i1, long long off, int thr, bool mark, bool types,
@@ -162,13 +282,23 @@ static cudaError_t launch_voxelwise(const LaunchCtx& c, int grid, uint8_t* a, co
 
 cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, const void* b_, int b_type,
                                    int64_t i_begin, int64_t i_end, int64_t off, int8_t thr, bool mark, bool types,
-                                   unsigned long long* count_out_d) {
+                                   unsigned long long* count_out_d, const uint32_t* occ_a, const uint32_t* occ_b) {
   uint8_t* a = (uint8_t*)a_;
   const uint8_t* b = (const uint8_t*)b_;
   if (i_end < i_begin) i_end = i_begin;
   const long long n = i_end - i_begin;
   const int max_grid = c.sm_count * kCtasPerSm < kMaxGrid ? c.sm_count * kCtasPerSm : kMaxGrid;
   ++*c.launches;
+  // summary path: every BitVectorVoxel side has a valid occupancy summary, no offset, full range
+  const bool a_ok = a_type == kMapProb || occ_a != nullptr, b_ok = b_type == kMapProb || occ_b != nullptr;
+  if (off == 0 && i_begin == 0 && a_ok && b_ok && !(a_type == kMapProb && b_type == kMapProb) &&
+      (((uintptr_t)a | (uintptr_t)b) & 15) == 0) {
+    long long work = ((n >> 5) + kThreads * 4 - 1) / (kThreads * 4);
+    const int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));
+    if (a_type == kMapBit && b_type == kMapProb) return launch_summary<kMapBit, kMapProb>(c, grid, a, b, occ_a, occ_b, n, thr, mark, types, count_out_d);
+    if (a_type == kMapProb && b_type == kMapBit) return launch_summary<kMapProb, kMapBit>(c, grid, a, b, occ_a, occ_b, n, thr, mark, false, count_out_d);
+    return launch_summary<kMapBit, kMapBit>(c, grid, a, b, occ_a, occ_b, n, thr, mark, false, count_out_d);
+  }
   if (a_type == kMapProb && b_type == kMapProb) {
     const bool aligned = ((off & 15) == 0) && (((uintptr_t)a & 15) == 0) && (((uintptr_t)b & 15) == 0);
     if (aligned) {

@@ -19,12 +19,20 @@ struct Map {
   float side;
   void* data;
   bool owned;
+  // Occupancy summary of a BitVectorVoxelMap: 1 bit per voxel = !noneButEmpty(voxel) (any meaning except eBVM_FREE),
+  // bit i&31 of word i>>5, kept in sync by every mutating entry point (inserts set bits, clears reset or recompute).
+  // 1/256 of the map's size; collide kernels read it instead of the 32-byte voxels. nullptr for ProbVoxelMaps and for
+  // wrapped (caller-owned) memory; occ_valid drops when the raw device pointer is handed out.
+  uint32_t* occ = nullptr;
+  bool occ_valid = false;
+  size_t occ_bytes() const { return ((n_voxels() + 31) / 32 + 3) / 4 * 16; }  // padded to 16 B
+  uint32_t* occ_if_valid() const { return occ_valid ? occ : nullptr; }
   uint64_t n_voxels() const { return (uint64_t)dx * dy * (z1 - z0); }
   uint64_t n_total() const { return (uint64_t)dx * dy * dz; }
   bool sharded() const { return z0 != 0 || z1 != dz; }
   size_t voxel_bytes() const { return type == kMapProb ? 1 : kBitVoxelBytes; }
   size_t bytes() const { return n_voxels() * voxel_bytes(); }
-  MapView view() const { return MapView{data, type, dx, dy, dz, z0, z1, side}; }
+  MapView view() const { return MapView{data, type, dx, dy, dz, z0, z1, side, occ_valid ? occ : nullptr}; }
 };
 
 // BitVectorVoxelList storage: SoA id / coord / voxel like the reference (GV/voxellist/TemplateVoxelList.h:250-252),
@@ -77,6 +85,7 @@ struct Context {
   PeerSlot* peer_ptr[kMaxPeers] = {};
   int peer_rank = 0, peer_world = 1;
   unsigned long long peer_epoch = 0;
+  bool use_summary = true;  // GVX_OPT_USE_SUMMARY: collide kernels may read occupancy summaries instead of voxels
   uint64_t launches = 0;
   uint64_t next_handle = 1;
   std::unordered_map<uint64_t, Map> maps;

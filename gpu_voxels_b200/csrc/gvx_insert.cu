@@ -92,6 +92,12 @@ k_insert(MapView m, const float* __restrict__ xyz, unsigned long long n, int mea
       if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
         const uint32_t bit = (uint32_t)(mg & 255);
         atomicOr((uint32_t*)m.data + idx * 8 + (bit >> 5), 1u << (bit & 31));
+        // occupancy summary: every meaning except eBVM_FREE (bit 0) makes the voxel occupied
+        if (m.occ && bit != 0u) {
+          uint32_t* w = m.occ + (idx >> 5);
+          const uint32_t ob = 1u << (idx & 31);
+          if (!(__ldcg(w) & ob)) atomicOr(w, ob);
+        }
       }
     }
   }
@@ -222,19 +228,30 @@ k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t*
   }
 }
 
-// BitVoxelMap::clearBits / clearBit: voxel &= ~mask, written back only where it changes.
+// BitVoxelMap::clearBits / clearBit: voxel &= ~mask, written back only where it changes. When the map carries an
+// occupancy summary the warp re-derives its 32 voxels' summary word from the result (warps cover aligned 32-voxel
+// groups: block size and stride are multiples of 32).
 __global__ void __launch_bounds__(kInsThreads)
-k_clear_bits(uint8_t* data, unsigned long long n, BitVoxelWords mask) {
+k_clear_bits(uint8_t* data, unsigned long long n, BitVoxelWords mask, uint32_t* occ) {
   const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
-  for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n; i += stride) {
-    BitVoxelWords v = ld_voxel(data + i * kBitVoxelBytes);
-    uint32_t hit = 0;
+  const unsigned long long n_round = (n + 31ull) & ~31ull;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n_round; i += stride) {
+    bool occupied = false;
+    if (i < n) {
+      BitVoxelWords v = ld_voxel(data + i * kBitVoxelBytes);
+      uint32_t hit = 0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) hit |= v.w[k] & mask.w[k];
-    if (hit) {
-      uint4* p = reinterpret_cast<uint4*>(data + i * kBitVoxelBytes);
-      p[0] = make_uint4(v.w[0] & ~mask.w[0], v.w[1] & ~mask.w[1], v.w[2] & ~mask.w[2], v.w[3] & ~mask.w[3]);
-      p[1] = make_uint4(v.w[4] & ~mask.w[4], v.w[5] & ~mask.w[5], v.w[6] & ~mask.w[6], v.w[7] & ~mask.w[7]);
+      for (int k = 0; k < 8; ++k) { hit |= v.w[k] & mask.w[k]; v.w[k] &= ~mask.w[k]; }
+      if (hit) {
+        uint4* p = reinterpret_cast<uint4*>(data + i * kBitVoxelBytes);
+        p[0] = make_uint4(v.w[0], v.w[1], v.w[2], v.w[3]);
+        p[1] = make_uint4(v.w[4], v.w[5], v.w[6], v.w[7]);
+      }
+      occupied = bit_occupied(v);
+    }
+    if (occ) {
+      const uint32_t w = __ballot_sync(0xffffffffu, occupied);
+      if ((threadIdx.x & 31) == 0) occ[i >> 5] = w;
     }
   }
 }
@@ -287,11 +304,11 @@ cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, co
   return cudaGetLastError();
 }
 
-cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8]) {
+cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8], uint32_t* occ) {
   BitVoxelWords mk;
   for (int k = 0; k < 8; ++k) mk.w[k] = mask8[k];
   ++*c.launches;
-  k_clear_bits<<<grid_for(c, n_voxels, 8), kInsThreads, 0, c.stream>>>((uint8_t*)data, n_voxels, mk);
+  k_clear_bits<<<grid_for(c, n_voxels, 8), kInsThreads, 0, c.stream>>>((uint8_t*)data, n_voxels, mk, occ);
   return cudaGetLastError();
 }
 

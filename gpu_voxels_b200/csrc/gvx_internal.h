@@ -21,7 +21,8 @@ struct LaunchCtx {
 // destination for the 64-bit count (async API), may be nullptr.
 cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a, int a_type, const void* b, int b_type,
                                    int64_t i_begin, int64_t i_end, int64_t off, int8_t thr, bool mark,
-                                   bool types, unsigned long long* count_out_d);
+                                   bool types, unsigned long long* count_out_d, const uint32_t* occ_a = nullptr,
+                                   const uint32_t* occ_b = nullptr);
 
 // voxelisation
 struct MetaDesc {             // device-resident description of a MetaPointCloud insert
@@ -36,6 +37,7 @@ struct MapView {
   int type;
   uint32_t dx, dy, dz, z0, z1;
   float side;
+  uint32_t* occ;  // occupancy summary to keep in sync (BitVectorVoxelMap with a valid summary), else nullptr
 };
 cudaError_t launch_insert_points(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n, int meaning,
                                  bool want_flag);
@@ -47,7 +49,8 @@ cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const fl
                                   const Affine12& pose, int delta);
 cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
                                         const uint32_t* prefix_d, const float* poses_d, uint32_t n_frames, int delta);
-cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8]);
+// voxel &= ~mask for all voxels; occ (nullable): summary words rewritten from the result
+cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8], uint32_t* occ);
 
 
 // BitVectorVoxelList build (gvx_list.cu): old list (sorted, unique) + n_new points -> out_* (sorted, unique, OR-merged);
@@ -68,7 +71,8 @@ cudaError_t launch_list_build(const LaunchCtx& c, const ListBuild& b);
 cudaError_t launch_collide_list_map(const LaunchCtx& c, int mode, const uint32_t* ids, void* voxels, uint64_t size,
                                     const void* map, int map_type, uint64_t n_total, uint64_t map_first,
                                     uint64_t map_n, int8_t thr_i, float thr_f, int64_t off, bool mark,
-                                    const uint32_t mask_in8[8], unsigned long long* count_out_d);
+                                    const uint32_t mask_in8[8], unsigned long long* count_out_d,
+                                    const uint32_t* occ = nullptr);
 
 // batch of robot configurations vs one environment map (gvx_batch.cu)
 struct BatchDesc {

@@ -149,7 +149,8 @@ template <int MAPT, int MODE, bool MARK>
 __global__ void __launch_bounds__(kThreads, 4)
 k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxels, unsigned long long size,
                    const uint8_t* __restrict__ map, long long n_total, long long map_first, long long map_n,
-                   int thr_i, float thr_f, long long off, BitVoxelWords mask_in, ReduceScratch* scratch,
+                   int thr_i, float thr_f, long long off, BitVoxelWords mask_in, const uint32_t* __restrict__ occ,
+                   ReduceScratch* scratch,
                    ResultBlock* out_d, ResultBlock* out_h, unsigned long long* count_out_d, PeerReduce pr) {
   __shared__ uint32_t sh_hist[MODE == 3 ? 256 : 1];
   if (MODE == 3) {
@@ -163,14 +164,17 @@ k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxel
     const long long j = (long long)__ldg(ids + i) + off;
     if (j < 0 || j >= n_total) continue;                   // pointer range test of the reference (:139-140)
     if (j < map_first || j >= map_first + map_n) continue;  // another z-slab's voxel
-    bool occ;
+    bool hit_map;
     if (MAPT == kMapProb) {
       const int p = (int)ld_stream_i8(map + (j - map_first));
-      occ = (MODE == 0 || MODE == 3) ? (p >= thr_i) : ((float)p >= thr_f);
+      hit_map = (MODE == 0 || MODE == 3) ? (p >= thr_i) : ((float)p >= thr_f);
+    } else if (occ != nullptr) {  // occupancy summary of the map: one bit instead of a 32-byte voxel
+      const long long v = j - map_first;
+      hit_map = (__ldg(occ + (v >> 5)) >> (v & 31)) & 1u;
     } else {
-      occ = bit_occupied(ld_voxel_stream(map + (size_t)(j - map_first) * kBitVoxelBytes));
+      hit_map = bit_occupied(ld_voxel_stream(map + (size_t)(j - map_first) * kBitVoxelBytes));
     }
-    if (!occ) continue;
+    if (!hit_map) continue;
     uint8_t* lp = voxels + (size_t)i * kBitVoxelBytes;
     const BitVoxelWords lv = ld_voxel(lp);
     bool hit;
@@ -222,17 +226,17 @@ k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxel
 template <int MAPT, int MODE>
 static void go_list(const LaunchCtx& c, int grid, bool mark, const uint32_t* ids, uint8_t* voxels, uint64_t size,
                     const uint8_t* map, long long n_total, long long map_first, long long map_n, int thr_i, float thr_f,
-                    long long off, const BitVoxelWords& mk, unsigned long long* out) {
+                    long long off, const BitVoxelWords& mk, const uint32_t* occ, unsigned long long* out) {
   if (mark)
-    k_collide_list_map<MAPT, MODE, true><<<grid, kThreads, 0, c.stream>>>(ids, voxels, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
+    k_collide_list_map<MAPT, MODE, true><<<grid, kThreads, 0, c.stream>>>(ids, voxels, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, occ, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
   else
-    k_collide_list_map<MAPT, MODE, false><<<grid, kThreads, 0, c.stream>>>(ids, voxels, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
+    k_collide_list_map<MAPT, MODE, false><<<grid, kThreads, 0, c.stream>>>(ids, voxels, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, occ, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
 }
 
 cudaError_t launch_collide_list_map(const LaunchCtx& c, int mode, const uint32_t* ids, void* voxels, uint64_t size,
                                     const void* map_, int map_type, uint64_t n_total, uint64_t map_first,
                                     uint64_t map_n, int8_t thr_i, float thr_f, int64_t off, bool mark,
-                                    const uint32_t mask_in8[8], unsigned long long* count_out_d) {
+                                    const uint32_t mask_in8[8], unsigned long long* count_out_d, const uint32_t* occ) {
   BitVoxelWords mk;
   for (int k = 0; k < 8; ++k) mk.w[k] = mask_in8 ? mask_in8[k] : 0u;
   unsigned long long work = (size + kThreads * 4 - 1) / (kThreads * 4);
@@ -247,10 +251,10 @@ cudaError_t launch_collide_list_map(const LaunchCtx& c, int mode, const uint32_t
   ++*c.launches;
 #define GVX_LM(MT)                                                                                                      \
   switch (mode) {                                                                                                       \
-    case 0: go_list<MT, 0>(c, grid, mark, ids, vx, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, count_out_d); break; \
-    case 1: go_list<MT, 1>(c, grid, mark, ids, vx, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, count_out_d); break; \
-    case 2: go_list<MT, 2>(c, grid, mark, ids, vx, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, count_out_d); break; \
-    default: go_list<MT, 3>(c, grid, mark, ids, vx, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, count_out_d); break; \
+    case 0: go_list<MT, 0>(c, grid, mark, ids, vx, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, occ, count_out_d); break; \
+    case 1: go_list<MT, 1>(c, grid, mark, ids, vx, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, occ, count_out_d); break; \
+    case 2: go_list<MT, 2>(c, grid, mark, ids, vx, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, occ, count_out_d); break; \
+    default: go_list<MT, 3>(c, grid, mark, ids, vx, size, map, n_total, map_first, map_n, thr_i, thr_f, off, mk, occ, count_out_d); break; \
   }
   if (map_type == kMapProb) { GVX_LM(kMapProb) } else { GVX_LM(kMapBit) }
 #undef GVX_LM

@@ -121,6 +121,18 @@ int gvx_map_info(gvx_handle_t h, int* map_type, uint32_t dims3[3], float* side, 
 int gvx_map_download(gvx_handle_t h, void* host_buf);
 int gvx_map_upload(gvx_handle_t h, const void* host_buf);
 
+/* Occupancy summary. Every library-owned BitVectorVoxelMap carries 1 bit per voxel = "any meaning except eBVM_FREE
+ * set" (BitVector::noneButEmpty negated, GV/helpers/BitVector.h:183-198), 1/256 of the map's size, kept in sync by
+ * every mutating call of this API. Collision kernels read it instead of the 32-byte voxels whenever occupancy is all
+ * they need; results are identical. Handing out the raw device pointer (gvx_map_device_ptr with data_d != NULL)
+ * invalidates it, because the caller may then write voxels directly: call gvx_map_refresh_summary afterwards
+ * (one streaming pass) or the kernels fall back to reading the voxels. Wrapped maps have no summary. */
+int gvx_map_refresh_summary(gvx_handle_t h);
+/* test / debug: the summary words of this process's slab (bit i&31 of word i>>5 = voxel i) and whether it is valid */
+int gvx_map_summary_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, int* valid);
+enum gvx_option { GVX_OPT_USE_SUMMARY = 1 /* 0: always stream the voxels (the reference's access pattern) */ };
+int gvx_set_option(int option, int value);
+
 /* ---- voxelisation ------------------------------------------------------------------------------------- */
 /* insertPointCloud (GV/voxelmap/TemplateVoxelMap.hpp:563-607, kernelInsertGlobalPointCloud
  * GV/voxelmap/kernels/VoxelMapOperations.hpp:241-264). xyz = n packed Vector3f. ProbVoxelMap accepts only
