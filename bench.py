@@ -30,6 +30,7 @@ DX = DY = DZ = 512
 SIDE = 0.01
 FRAME_W, FRAME_H = 640, 480
 N_FRAME = FRAME_W * FRAME_H
+BYTES_PER_VOXEL_SUMMARY = 1.125  # default path: Prob (1 B) + 1 bit of the BitVector map's occupancy summary
 BYTES_PER_VOXEL = 33  # Prob (1 B) x BitVector (32 B): algorithmic bytes of the dominant kernel
 THR = 0.5
 
@@ -202,7 +203,9 @@ def workload_config(n_gpus):
                         "log-odds insert then collideWith a 512^3 robot BitVectorVoxelMap (7 links, 350k pts)",
             "grid": [DX, DY, DZ * n_gpus], "voxels_per_gpu": DX * DY * DZ, "points_per_step": N_FRAME * n_gpus,
             "coll_threshold": THR, "mark_collisions": True,
-            "l2": "inputs larger than L2 (4.43 GB streamed per collide vs 126 MB L2)",
+            "l2": "inputs larger than L2: two (env, robot) map pairs used alternately, 2 x 151 MB on the summary path "
+                  "(2 x 4.43 GB when streaming) vs 126 MB L2",
+            "collide_path": "occupancy summary of the BitVectorVoxelMap (maintained at insert time) + streamed ProbVoxelMap",
             "parallelism": "z-slab x%d" % n_gpus if n_gpus > 1 else "single GPU"}
 
 
@@ -245,11 +248,14 @@ def run_gpu_arm(args):
     n_vox = DX * DY * DZ
     dims = (DX, DY, DZ * world)
     slab = (DZ * rank, DZ * (rank + 1))
-    env = gv.ProbVoxelMap(dims, SIDE, slab=slab)
-    rob = gv.BitVectorVoxelMap(dims, SIDE, slab=slab)
+    # TWO (environment, robot) map pairs used alternately, so that consecutive steps never find the previous step's
+    # grids in the 126 MB L2 (one pair's collide reads 151 MB; both pairs: 302 MB)
+    envs = [gv.ProbVoxelMap(dims, SIDE, slab=slab) for _ in range(2)]
+    robs = [gv.BitVectorVoxelMap(dims, SIDE, slab=slab) for _ in range(2)]
     # robot: every slab holds its own copy of the arm (inserted once, untimed); global cloud = all copies
     rclouds = [np.concatenate([c for r in range(world) for c in [robot_clouds(z_shift=DZ * SIDE * r)[k]]]) for k in range(7)]
-    rob.insertMetaPointCloud(gv.MetaPointCloud(rclouds), list(range(4, 11)))
+    for rob in robs:
+        rob.insertMetaPointCloud(gv.MetaPointCloud(rclouds), list(range(4, 11)))
     # frames: N sub-frames (one per slab) concatenated into one global cloud; every rank reads all of it
     poses = [sensor_pose(DZ * SIDE * r) for r in range(world)]
     frames_h = [[depth_frame(201 + 2 * r + k) for r in range(world)] for k in range(2)]  # [parity][slab] sensor frame
@@ -265,13 +271,13 @@ def run_gpu_arm(args):
     gathered = torch.empty((world * N_FRAME, 3), dtype=torch.float32, device="cuda")
     own_d = torch.empty((N_FRAME, 3), dtype=torch.float32, device="cuda")
 
-    def fold_frames(points_d):
+    def fold_frames(points_d, k):
         """log-odds update of ALL sub-frames (each with its own pose) in one launch; this rank keeps its slab's points"""
         if world == 1:
-            _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(points_d.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
+            _lib.check(L.gvx_update_logodds(envs[k % 2].handle, C.c_void_p(points_d.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
                                             pose_arr[0].ctypes.data_as(C.c_void_p), 72))
         else:
-            _lib.check(L.gvx_update_logodds_multi(env.handle, C.c_void_p(points_d.data_ptr()), _lib.MEM_DEVICE,
+            _lib.check(L.gvx_update_logodds_multi(envs[k % 2].handle, C.c_void_p(points_d.data_ptr()), _lib.MEM_DEVICE,
                                                   sizes_arr.ctypes.data_as(C.c_void_p), world,
                                                   poses_arr.ctypes.data_as(C.c_void_p), 72))
 
@@ -282,7 +288,8 @@ def run_gpu_arm(args):
         from gpu_voxels_b200 import sharding
         fused = sharding.connect_peer_mailboxes()
 
-    def collide_global(host_count=None):
+    def collide_global(k, host_count=None):
+        env, rob = envs[k % 2], robs[k % 2]
         if fused:
             _lib.check(L.gvx_collide_map_map_allreduce(env.handle, rob.handle, THR, 1, host_count,
                                                        C.c_void_p(count_d.data_ptr())))
@@ -293,8 +300,8 @@ def run_gpu_arm(args):
 
     def step_device(k):
         """inputs resident in HBM; result stays on the device (all-reduced when sharded)"""
-        fold_frames(cat_d[k % 2])
-        collide_global()
+        fold_frames(cat_d[k % 2], k)
+        collide_global(k)
 
     def step_e2e(k):
         """through the C ABI with HOST buffers: H2D of the frame inside, count read back to the host. Sharded: every
@@ -303,18 +310,18 @@ def run_gpu_arm(args):
         if world > 1:
             own_d.copy_(pinned[k % 2][rank], non_blocking=True)
             dist.all_gather_into_tensor(gathered, own_d)
-            fold_frames(gathered)
+            fold_frames(gathered, k)
             if fused:
                 cnt = C.c_uint64(0)
-                collide_global(C.byref(cnt))
+                collide_global(k, C.byref(cnt))
                 return cnt.value
-            collide_global()
+            collide_global(k)
             return int(count_d.item())
         f = pinned[k % 2][0]
-        _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_HOST,
+        _lib.check(L.gvx_update_logodds(envs[k % 2].handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_HOST,
                                         pose_arr[0].ctypes.data_as(C.c_void_p), 72))
         cnt = C.c_uint64(0)
-        _lib.check(L.gvx_collide_map_map(env.handle, rob.handle, THR, None, 1, C.byref(cnt)))
+        _lib.check(L.gvx_collide_map_map(envs[k % 2].handle, robs[k % 2].handle, THR, None, 1, C.byref(cnt)))
         return cnt.value
 
     def barrier():
@@ -340,23 +347,39 @@ def run_gpu_arm(args):
         step_e2e(k)
     # dominant kernel alone (collide), CUDA events on the launching stream, same maps, inputs >> L2
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kev_stream = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                  for _ in range(min(args.steps, 50))]
     launches0 = L.gvx_launch_count()
     with ClockSampler(local_rank) as clk:
         ms_total = timed(step_device, args.steps)
         launches = L.gvx_launch_count() - launches0
         ms_e2e = timed(step_e2e, args.steps)
         barrier()
-        for e0, e1 in kev:
+        # the collide kernel alone: (1) the default path (robot map's occupancy summary + streamed ProbVoxelMap) and
+        # (2) the voxel-streaming kernel (GVX_OPT_USE_SUMMARY = 0: both grids read in full, the reference's pattern)
+        def collide_alone(k):
+            _lib.check(L.gvx_collide_map_map_async(envs[k % 2].handle, robs[k % 2].handle, THR, None, 1,
+                                                   C.c_void_p(count_d.data_ptr())))
+        for k, (e0, e1) in enumerate(kev):
             e0.record(stream)
-            _lib.check(L.gvx_collide_map_map_async(env.handle, rob.handle, THR, None, 1, C.c_void_p(count_d.data_ptr())))
+            collide_alone(k)
             e1.record(stream)
         torch.cuda.synchronize()
+        _lib.check(L.gvx_set_option(1, 0))
+        for k in range(3):
+            collide_alone(k)
+        for k, (e0, e1) in enumerate(kev_stream):
+            e0.record(stream)
+            collide_alone(k)
+            e1.record(stream)
+        torch.cuda.synchronize()
+        _lib.check(L.gvx_set_option(1, 1))
         # insertion alone: points/s of the log-odds frame update (atomic-bound; reported beside the headline)
         evi0, evi1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         evi0.record(stream)
         for k in range(args.steps):
             f = frames_d[k % 2][rank]
-            _lib.check(L.gvx_update_logodds(env.handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
+            _lib.check(L.gvx_update_logodds(envs[k % 2].handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
                                             pose_arr[rank].ctypes.data_as(C.c_void_p), 72))
         evi1.record(stream)
         torch.cuda.synchronize()
@@ -367,14 +390,17 @@ def run_gpu_arm(args):
 
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
-        achieved = BYTES_PER_VOXEL * n_vox / (k_avg * 1e-3) / 1e9
-        traffic = None
-        tfile = os.path.join(ROOT, "profiles", "collide_traffic.json")
-        if os.path.exists(tfile):
+        ks_ms = sorted(e0.elapsed_time(e1) for e0, e1 in kev_stream)
+        ks_avg = sum(ks_ms) / len(ks_ms)
+        achieved = BYTES_PER_VOXEL_SUMMARY * n_vox / (k_avg * 1e-3) / 1e9
+        achieved_stream = BYTES_PER_VOXEL * n_vox / (ks_avg * 1e-3) / 1e9
+
+        def _traffic(name):
             try:
-                traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
+                return json.load(open(os.path.join(ROOT, "profiles", name))).get("dram_bytes_per_launch")
             except Exception:
-                traffic = None
+                return None
+        traffic, traffic_stream = _traffic("collide_summary_traffic.json"), _traffic("collide_traffic.json")
         cpu = cpu_arm(2, 1) if world == 1 and not args.no_cpu_baseline else None
         line = {
             "metric": "collideWith voxels/s", "value": n_vox * world * args.steps / (ms_total * 1e-3), "unit": "voxels/s",
@@ -387,10 +413,20 @@ def run_gpu_arm(args):
                             "are all-gathered over NVLink, the count is all-reduced and read back by every rank",
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_collide_voxelwise<Prob,Bit,mark>", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "k_collide_summary<Prob,Bit,mark>", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": BYTES_PER_VOXEL * n_vox, "kernel_ms_avg": k_avg,
-                         "kernel_ms_min": k_ms[0], "frac_of_8000_nominal": achieved / 8000.0},
+                         "algorithmic_bytes_per_launch": BYTES_PER_VOXEL_SUMMARY * n_vox,
+                         "algorithmic_bytes_per_voxel": BYTES_PER_VOXEL_SUMMARY, "kernel_ms_avg": k_avg,
+                         "kernel_ms_min": k_ms[0], "frac_of_8000_nominal": achieved / 8000.0,
+                         "note": "default path: 1 B ProbabilisticVoxel + 1 summary bit of the BitVectorVoxel per voxel "
+                                 "(DESIGN.md 3.1); the 33 B/voxel figure of SURVEY 8d belongs to roofline_streaming"},
+            "roofline_streaming": {"bound": "hbm", "kernel": "k_collide_voxelwise<Prob,Bit,mark>", "achieved": achieved_stream,
+                                   "peak": peak, "unit": "GB/s", "frac": achieved_stream / peak, "traffic": traffic_stream,
+                                   "algorithmic_bytes_per_launch": BYTES_PER_VOXEL * n_vox,
+                                   "algorithmic_bytes_per_voxel": BYTES_PER_VOXEL, "kernel_ms_avg": ks_avg,
+                                   "kernel_ms_min": ks_ms[0], "frac_of_8000_nominal": achieved_stream / 8000.0,
+                                   "voxels_per_s": n_vox / (ks_avg * 1e-3),
+                                   "note": "GVX_OPT_USE_SUMMARY=0: both grids streamed in full like the reference"},
             "insert": {"metric": "insertSensorData (log-odds) points/s", "value": N_FRAME / (ins_ms * 1e-3),
                        "unit": "points/s", "ms_per_frame": ins_ms, "points": N_FRAME},
             "clocks": clk.summary(), "collisions_last_step": int(last_count),
