@@ -214,7 +214,7 @@ static int map_make(gvx_handle_t* h, int map_type, void* wrap, uint32_t dx, uint
     cudaError_t e = cudaMalloc(&m.data, m.bytes());
     if (e != cudaSuccess) { cudaGetLastError(); return fail(GVX_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", m.bytes(), cudaGetErrorString(e)); }
     GVX_CUDA(cudaMemsetAsync(m.data, map_type == GVX_MT_PROBAB_VOXELMAP ? 0x80 : 0x00, m.bytes(), g.stream));
-    if (map_type == GVX_MT_BITVECTOR_VOXELMAP) {  // occupancy summary, 1 bit per voxel
+    {  // summary, 1 bit per voxel: "occupied" for BitVectorVoxels, "known" (!= UNKNOWN) for ProbabilisticVoxels
       e = cudaMalloc((void**)&m.occ, m.occ_bytes());
       if (e != cudaSuccess) { cudaGetLastError(); cudaFree(m.data); return fail(GVX_ERR_NOMEM, "cudaMalloc(summary) failed: %s", cudaGetErrorString(e)); }
       GVX_CUDA(cudaMemsetAsync(m.occ, 0, m.occ_bytes(), g.stream));
@@ -339,7 +339,8 @@ int gvx_map_upload(gvx_handle_t h, const void* host_buf) {
   if (!m || !host_buf) return fail(GVX_ERR_INVALID, "unknown map handle or null buffer");
   GVX_CUDA(cudaMemcpyAsync(m->data, host_buf, m->bytes(), cudaMemcpyHostToDevice, g.stream));
   if (m->occ) {
-    GVX_CUDA(launch_env_bitmap(lctx(), m->data, kMapBit, m->n_voxels(), 0, m->occ));
+    // Bit: bit = !noneButEmpty; Prob: bit = occupancy >= -127, i.e. anything but UNKNOWN (-128)
+    GVX_CUDA(launch_env_bitmap(lctx(), m->data, m->type, m->n_voxels(), -127, m->occ));
     m->occ_valid = true;
   }
   GVX_CUDA(cudaStreamSynchronize(g.stream));
@@ -351,8 +352,8 @@ int gvx_map_refresh_summary(gvx_handle_t h) {
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
-  if (!m->occ) return GVX_OK;  // ProbVoxelMap or wrapped memory: nothing to refresh
-  GVX_CUDA(launch_env_bitmap(lctx(), m->data, kMapBit, m->n_voxels(), 0, m->occ));
+  if (!m->occ) return GVX_OK;  // wrapped memory: no summary
+  GVX_CUDA(launch_env_bitmap(lctx(), m->data, m->type, m->n_voxels(), -127, m->occ));
   m->occ_valid = true;
   return GVX_OK;
 }

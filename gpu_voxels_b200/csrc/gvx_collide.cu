@@ -164,11 +164,17 @@ __device__ __forceinline__ uint32_t prob_group_mask(const uint4& lo, const uint4
   return m;
 }
 
-template <int AT, int BT, bool MARK, bool TYPES>
+// ASUM / BSUM: that side's summary is available. A BitVectorVoxel side always needs it (bit = occupied, exact); for a
+// ProbabilisticVoxel side the summary bit means "known" (occupancy != UNKNOWN), a superset of "occupancy >= threshold":
+// groups with candidate bits fetch their 32 Prob bytes and apply the threshold, groups without candidates (almost
+// all of a sparse map) cost 1 bit per voxel. Without a summary the Prob side's bytes are streamed for every group.
+template <int AT, int BT, bool MARK, bool TYPES, bool ASUM, bool BSUM>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const uint32_t* __restrict__ occ_a,
                   const uint32_t* __restrict__ occ_b, long long n, int thr, ReduceScratch* scratch, ResultBlock* out_d,
                   ResultBlock* out_h, unsigned long long* count_out_d, PeerReduce pr) {
+  static_assert(AT == kMapProb || ASUM, "a BitVectorVoxel side needs its occupancy summary");
+  static_assert(BT == kMapProb || BSUM, "a BitVectorVoxel side needs its occupancy summary");
   constexpr int U = 4;
   uint32_t cnt = 0;
   uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -184,12 +190,12 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
       const long long g = base + u * kThreads + threadIdx.x;
       ok[u] = g < n_full;
       if (ok[u]) {
-        if (AT == kMapBit) ma[u] = __ldg(occ_a + g);
+        if (ASUM) ma[u] = __ldg(occ_a + g);
         else {
           const uint4* p = reinterpret_cast<const uint4*>(a + (g << 5));
           if (MARK) { alo[u] = __ldcg(p); ahi[u] = __ldcg(p + 1); } else { alo[u] = ld_stream_u4(p); ahi[u] = ld_stream_u4(p + 1); }
         }
-        if (BT == kMapBit) mb[u] = __ldg(occ_b + g);
+        if (BSUM) mb[u] = __ldg(occ_b + g);
         else {
           const uint4* p = reinterpret_cast<const uint4*>(b + (g << 5));
           blo[u] = ld_stream_u4(p); bhi[u] = ld_stream_u4(p + 1);
@@ -200,12 +206,23 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
     for (int u = 0; u < U; ++u) {
       if (!ok[u]) continue;
       const long long g = base + u * kThreads + threadIdx.x;
-      if (AT != kMapBit) ma[u] = prob_group_mask(alo[u], ahi[u], t4);
-      if (BT != kMapBit) mb[u] = prob_group_mask(blo[u], bhi[u], t4);
+      if (!ASUM) ma[u] = prob_group_mask(alo[u], ahi[u], t4);
+      if (!BSUM) mb[u] = prob_group_mask(blo[u], bhi[u], t4);
       uint32_t hit = ma[u] & mb[u];
+      if (hit == 0u) continue;
+      if (AT == kMapProb && ASUM) {  // candidates: apply the threshold to this group's bytes
+        const uint4* p = reinterpret_cast<const uint4*>(a + (g << 5));
+        const uint4 lo = __ldcg(p), hi = __ldcg(p + 1);
+        hit &= prob_group_mask(lo, hi, t4);
+      }
+      if (BT == kMapProb && BSUM && hit) {
+        const uint4* p = reinterpret_cast<const uint4*>(b + (g << 5));
+        const uint4 lo = __ldg(p), hi = __ldg(p + 1);
+        hit &= prob_group_mask(lo, hi, t4);
+      }
       cnt += __popc(hit);
       if (MARK || TYPES) {
-        while (hit) {  // rare: colliding voxels only
+        while (hit) {  // colliding voxels only
           const int j = __ffs(hit) - 1;
           hit &= hit - 1;
           const long long i = (g << 5) + j;
@@ -221,7 +238,7 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
               if (!(w0 & 4u)) vp[0] = w0 | 4u;  // insert(eBVM_COLLISION); occupancy (and the summary) unchanged
             }
           } else if (MARK) {
-            if (((const int8_t*)a)[i] != 127) ((int8_t*)a)[i] = 127;
+            if (((const volatile int8_t*)a)[i] != 127) ((int8_t*)a)[i] = 127;  // stays "known"
           }
         }
       }
@@ -231,7 +248,6 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
   if (blockIdx.x == 0 && threadIdx.x < 32) {
     const long long i = (n_full << 5) + threadIdx.x;
     if (i < n) {
-      BitVoxelWords va;
       bool oa, ob;
       int pa = 0;
       if (AT == kMapBit) oa = (__ldg(occ_a + (i >> 5)) >> (i & 31)) & 1u;
@@ -241,7 +257,7 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
       if (oa && ob) {
         ++cnt;
         if (AT == kMapBit && (MARK || TYPES)) {
-          va = ld_voxel(a + (size_t)i * kBitVoxelBytes);
+          const BitVoxelWords va = ld_voxel(a + (size_t)i * kBitVoxelBytes);
           if (TYPES) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) acc[k] |= va.w[k];
@@ -256,14 +272,14 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
   finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
 }
 
-template <int AT, int BT>
+template <int AT, int BT, bool ASUM, bool BSUM>
 static cudaError_t launch_summary(const LaunchCtx& c, int grid, uint8_t* a, const uint8_t* b, const uint32_t* occ_a,
                                   const uint32_t* occ_b, long long n, int thr, bool mark, bool types,
                                   unsigned long long* out) {
-#define GVX_GO(M, T) k_collide_summary<AT, BT, M, T><<<grid, kThreads, 0, c.stream>>>( \
+#define GVX_GO(M, T) k_collide_summary<AT, BT, M, T, ASUM, BSUM><<<grid, kThreads, 0, c.stream>>>( \
       a, b, occ_a, occ_b, n, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer)
-  if (types) { if (mark) GVX_GO(true, true); else GVX_GO(false, true); }
-  else       { if (mark) GVX_GO(true, false); else GVX_GO(false, false); }
+  if (types && AT == kMapBit) { if (mark) GVX_GO(true, (AT == kMapBit)); else GVX_GO(false, (AT == kMapBit)); }
+  else                        { if (mark) GVX_GO(true, false); else GVX_GO(false, false); }
 #undef GVX_GO
   return cudaGetLastError();
 }
@@ -289,15 +305,20 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
   const long long n = i_end - i_begin;
   const int max_grid = c.sm_count * kCtasPerSm < kMaxGrid ? c.sm_count * kCtasPerSm : kMaxGrid;
   ++*c.launches;
-  // summary path: every BitVectorVoxel side has a valid occupancy summary, no offset, full range
-  const bool a_ok = a_type == kMapProb || occ_a != nullptr, b_ok = b_type == kMapProb || occ_b != nullptr;
-  if (off == 0 && i_begin == 0 && a_ok && b_ok && !(a_type == kMapProb && b_type == kMapProb) &&
+  // summary path (no offset, full range): every BitVectorVoxel side has a valid occupancy summary; a ProbabilisticVoxel
+  // side uses its "known" summary when it has one and is streamed byte-wise otherwise (Prob x Prob needs both).
+  const bool a_bit = a_type == kMapBit, b_bit = b_type == kMapBit;
+  const bool a_sum = occ_a != nullptr, b_sum = occ_b != nullptr;
+  if (off == 0 && i_begin == 0 && (!a_bit || a_sum) && (!b_bit || b_sum) && (a_bit || b_bit || (a_sum && b_sum)) &&
       (((uintptr_t)a | (uintptr_t)b) & 15) == 0) {
     long long work = ((n >> 5) + kThreads * 4 - 1) / (kThreads * 4);
     const int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));
-    if (a_type == kMapBit && b_type == kMapProb) return launch_summary<kMapBit, kMapProb>(c, grid, a, b, occ_a, occ_b, n, thr, mark, types, count_out_d);
-    if (a_type == kMapProb && b_type == kMapBit) return launch_summary<kMapProb, kMapBit>(c, grid, a, b, occ_a, occ_b, n, thr, mark, false, count_out_d);
-    return launch_summary<kMapBit, kMapBit>(c, grid, a, b, occ_a, occ_b, n, thr, mark, false, count_out_d);
+#define GVX_SUM(AT, BT, AS, BS) return launch_summary<AT, BT, AS, BS>(c, grid, a, b, occ_a, occ_b, n, thr, mark, types, count_out_d)
+    if (a_bit && b_bit) GVX_SUM(kMapBit, kMapBit, true, true);
+    if (a_bit) { if (b_sum) GVX_SUM(kMapBit, kMapProb, true, true); GVX_SUM(kMapBit, kMapProb, true, false); }
+    if (b_bit) { if (a_sum) GVX_SUM(kMapProb, kMapBit, true, true); GVX_SUM(kMapProb, kMapBit, false, true); }
+    GVX_SUM(kMapProb, kMapProb, true, true);
+#undef GVX_SUM
   }
   if (a_type == kMapProb && b_type == kMapProb) {
     const bool aligned = ((off & 15) == 0) && (((uintptr_t)a & 15) == 0) && (((uintptr_t)b & 15) == 0);

@@ -19,10 +19,12 @@ struct Map {
   float side;
   void* data;
   bool owned;
-  // Occupancy summary of a BitVectorVoxelMap: 1 bit per voxel = !noneButEmpty(voxel) (any meaning except eBVM_FREE),
-  // bit i&31 of word i>>5, kept in sync by every mutating entry point (inserts set bits, clears reset or recompute).
-  // 1/256 of the map's size; collide kernels read it instead of the 32-byte voxels. nullptr for ProbVoxelMaps and for
-  // wrapped (caller-owned) memory; occ_valid drops when the raw device pointer is handed out.
+  // Summary: 1 bit per voxel, bit i&31 of word i>>5, kept in sync by every mutating entry point (inserts set bits,
+  // clears reset or recompute). BitVectorVoxelMap: bit = !noneButEmpty(voxel) (any meaning except eBVM_FREE), exact
+  // occupancy, 1/256 of the map. ProbVoxelMap: bit = "known" (occupancy != UNKNOWN_PROBABILITY), a superset of
+  // "occupancy >= threshold" for every threshold, 1/8 of the map. Collide kernels read summaries first and touch voxels
+  // only where they must. nullptr for wrapped (caller-owned) memory; occ_valid drops when the raw device pointer is
+  // handed out.
   uint32_t* occ = nullptr;
   bool occ_valid = false;
   size_t occ_bytes() const { return ((n_voxels() + 31) / 32 + 3) / 4 * 16; }  // padded to 16 B

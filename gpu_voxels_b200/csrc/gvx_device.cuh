@@ -79,6 +79,13 @@ __device__ __forceinline__ uint32_t find_cloud(const uint32_t* prefix, uint32_t 
   return lo;
 }
 
+// set voxel idx's bit in a map summary (skips the atomic when the bit is already there)
+__device__ __forceinline__ void summary_set(uint32_t* occ, uint64_t idx) {
+  uint32_t* w = occ + (idx >> 5);
+  const uint32_t b = 1u << (idx & 31);
+  if (!(__ldcg(w) & b)) atomicOr(w, b);
+}
+
 __device__ __forceinline__ uint64_t warp_sum_u32(uint32_t v) { return (uint64_t)__reduce_add_sync(0xffffffffu, v); }
 
 // Scratch shared by every reducing kernel of one context: per-CTA partials, a self-resetting ticket

@@ -86,18 +86,18 @@ k_insert(MapView m, const float* __restrict__ xyz, unsigned long long n, int mea
       }
     }
     if (PROB) {
-      if (live) ((int8_t*)m.data)[idx] = prob_insert_value(mg);  // same value from every writer
+      if (live) {
+        const int8_t v = prob_insert_value(mg);
+        ((int8_t*)m.data)[idx] = v;  // same value from every writer
+        if (m.occ && v != (int8_t)-128) summary_set(m.occ, idx);  // "known" summary
+      }
     } else {
       const unsigned peers = __match_any_sync(0xffffffffu, key);
       if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
         const uint32_t bit = (uint32_t)(mg & 255);
         atomicOr((uint32_t*)m.data + idx * 8 + (bit >> 5), 1u << (bit & 31));
         // occupancy summary: every meaning except eBVM_FREE (bit 0) makes the voxel occupied
-        if (m.occ && bit != 0u) {
-          uint32_t* w = m.occ + (idx >> 5);
-          const uint32_t ob = 1u << (idx & 31);
-          if (!(__ldcg(w) & ob)) atomicOr(w, ob);
-        }
+        if (m.occ && bit != 0u) summary_set(m.occ, idx);
       }
     }
   }
@@ -166,7 +166,10 @@ k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n,
     }
     const unsigned long long key = live ? idx : (~0ull - (threadIdx.x & 31));
     const unsigned peers = __match_any_sync(0xffffffffu, key);
-    if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
+    if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
+      logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
+      if (m.occ) summary_set(m.occ, idx);  // clamp(.., -127, 127) never returns to UNKNOWN: the voxel is "known"
+    }
   }
 }
 
@@ -224,7 +227,10 @@ k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t*
     }
     const unsigned long long key = live ? idx : (~0ull - (threadIdx.x & 31));
     const unsigned peers = __match_any_sync(0xffffffffu, key);
-    if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
+    if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
+      logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
+      if (m.occ) summary_set(m.occ, idx);  // clamp(.., -127, 127) never returns to UNKNOWN: the voxel is "known"
+    }
   }
 }
 

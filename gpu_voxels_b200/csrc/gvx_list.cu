@@ -166,6 +166,10 @@ k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxel
     if (j < map_first || j >= map_first + map_n) continue;  // another z-slab's voxel
     bool hit_map;
     if (MAPT == kMapProb) {
+      if (occ != nullptr) {  // "known" summary: an UNKNOWN voxel never collides, skip its byte
+        const long long v = j - map_first;
+        if (!((__ldg(occ + (v >> 5)) >> (v & 31)) & 1u)) continue;
+      }
       const int p = (int)ld_stream_i8(map + (j - map_first));
       hit_map = (MODE == 0 || MODE == 3) ? (p >= thr_i) : ((float)p >= thr_f);
     } else if (occ != nullptr) {  // occupancy summary of the map: one bit instead of a 32-byte voxel

@@ -79,7 +79,39 @@ def test_summary_tracks_every_mutation(gv, oracle, slab):
     _check(m)
 
 
-@pytest.mark.parametrize("ta,tb", [(BIT, PROB), (PROB, BIT), (BIT, BIT)])
+def test_prob_known_summary_tracks_every_mutation(gv, oracle):
+    """ProbVoxelMap: summary bit = "known" (occupancy != UNKNOWN); a clear bit must always mean UNKNOWN"""
+    dims, side = (50, 37, 41), 0.01
+    pose = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, 0.001]], np.float32)
+    for slab in (None, (5, 33)):
+        m = gv.ProbVoxelMap(dims, side, slab=slab)
+
+        def check():
+            bits, valid = m.summary()
+            assert valid and np.array_equal(bits, m.download() != -128)
+        check()
+        m.insertPointCloud(_cloud(1, 20000, 0.5), 1)
+        check()
+        m.insertSensorData(_cloud(2, 30000, 0.5), pose)
+        m.insertSensorDataMulti([_cloud(3, 5000, 0.5), _cloud(4, 5000, 0.5)], [pose, pose], delta_occupied=-10)
+        check()
+        b = gv.BitVectorVoxelMap(dims, side, slab=slab)
+        b.insertPointCloud(_cloud(2, 30000, 0.5)[:8000], 5)
+        assert m.collideWith(b, 0.3) > 0   # marks 127
+        check()
+        up = np.full(m.numVoxels(), -128, np.int8); up[::5] = -127; up[::9] = 40
+        m.upload(up)
+        check()
+        m.clearMap()
+        check()
+        assert not m.summary()[0].any()
+        m.getVoidDeviceDataPtr()
+        assert not m.summary()[1]
+        m.refreshSummary()
+        check()
+
+
+@pytest.mark.parametrize("ta,tb", [(BIT, PROB), (PROB, BIT), (BIT, BIT), (PROB, PROB)])
 def test_summary_and_streaming_paths_agree_with_the_oracle(gv, oracle, ta, tb):
     dims, side = (70, 45, 53), 0.01  # 166950 voxels, tail group of 6
     n = dims[0] * dims[1] * dims[2]
