@@ -30,7 +30,8 @@ DX = DY = DZ = 512
 SIDE = 0.01
 FRAME_W, FRAME_H = 640, 480
 N_FRAME = FRAME_W * FRAME_H
-BYTES_PER_VOXEL_SUMMARY = 1.125  # default path: Prob (1 B) + 1 bit of the BitVector map's occupancy summary
+BYTES_PER_VOXEL_SUMMARY = 0.25  # default path: 1 summary bit per voxel and side ("known" bit of the ProbVoxelMap,
+#                                  occupancy bit of the BitVectorVoxelMap); Prob bytes only for candidate groups
 BYTES_PER_VOXEL = 33  # Prob (1 B) x BitVector (32 B): algorithmic bytes of the dominant kernel
 THR = 0.5
 
@@ -203,9 +204,11 @@ def workload_config(n_gpus):
                         "log-odds insert then collideWith a 512^3 robot BitVectorVoxelMap (7 links, 350k pts)",
             "grid": [DX, DY, DZ * n_gpus], "voxels_per_gpu": DX * DY * DZ, "points_per_step": N_FRAME * n_gpus,
             "coll_threshold": THR, "mark_collisions": True,
-            "l2": "inputs larger than L2: two (env, robot) map pairs used alternately, 2 x 151 MB on the summary path "
-                  "(2 x 4.43 GB when streaming) vs 126 MB L2",
-            "collide_path": "occupancy summary of the BitVectorVoxelMap (maintained at insert time) + streamed ProbVoxelMap",
+            "l2": "L2 flushed between timed iterations of the collide kernel alone (a 256 MB buffer is rewritten); the step "
+                  "loop alternates two (env, robot) map pairs (2 x 33.5 MB of summaries on the default path, "
+                  "2 x 4.43 GB when streaming, vs 126 MB L2)",
+            "collide_path": "summaries: 'known' bits of the ProbVoxelMap x occupancy bits of the BitVectorVoxelMap "
+                            "(both maintained by the insert kernels), Prob bytes only for candidate groups",
             "parallelism": "z-slab x%d" % n_gpus if n_gpus > 1 else "single GPU"}
 
 
@@ -360,11 +363,14 @@ def run_gpu_arm(args):
         def collide_alone(k):
             _lib.check(L.gvx_collide_map_map_async(envs[k % 2].handle, robs[k % 2].handle, THR, None, 1,
                                                    C.c_void_p(count_d.data_ptr())))
+        l2_flush = torch.zeros(256 << 20, dtype=torch.uint8, device="cuda")
         for k, (e0, e1) in enumerate(kev):
+            l2_flush.add_(1)  # 2 x 256 MB of traffic: nothing of the 33.5 MB of summaries survives in the 126 MB L2
             e0.record(stream)
             collide_alone(k)
             e1.record(stream)
         torch.cuda.synchronize()
+        del l2_flush
         _lib.check(L.gvx_set_option(1, 0))
         for k in range(3):
             collide_alone(k)
@@ -413,13 +419,14 @@ def run_gpu_arm(args):
                             "are all-gathered over NVLink, the count is all-reduced and read back by every rank",
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_collide_summary<Prob,Bit,mark>", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "k_collide_summary<Prob,Bit,mark,sum,sum>", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": BYTES_PER_VOXEL_SUMMARY * n_vox,
                          "algorithmic_bytes_per_voxel": BYTES_PER_VOXEL_SUMMARY, "kernel_ms_avg": k_avg,
                          "kernel_ms_min": k_ms[0], "frac_of_8000_nominal": achieved / 8000.0,
-                         "note": "default path: 1 B ProbabilisticVoxel + 1 summary bit of the BitVectorVoxel per voxel "
-                                 "(DESIGN.md 3.1); the 33 B/voxel figure of SURVEY 8d belongs to roofline_streaming"},
+                         "note": "default path: one summary bit per voxel and side (2 x 16.8 MB for 512^3) + the Prob bytes of "
+                                 "candidate groups (DESIGN.md 3.1): a 33.5 MB problem, launch-latency territory; the "
+                                 "33 B/voxel figure of SURVEY 8d belongs to roofline_streaming"},
             "roofline_streaming": {"bound": "hbm", "kernel": "k_collide_voxelwise<Prob,Bit,mark>", "achieved": achieved_stream,
                                    "peak": peak, "unit": "GB/s", "frac": achieved_stream / peak, "traffic": traffic_stream,
                                    "algorithmic_bytes_per_launch": BYTES_PER_VOXEL * n_vox,
