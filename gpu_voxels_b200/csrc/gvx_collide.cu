@@ -164,6 +164,119 @@ __device__ __forceinline__ uint32_t prob_group_mask(const uint4& lo, const uint4
   return m;
 }
 
+// Candidate bits of one 32-voxel group -> exact collisions: a ProbabilisticVoxel side that was represented by its
+// "known" summary gets its threshold applied to the group's 32 bytes; then count, and touch the voxels themselves
+// only for the write-back (MARK) or the meaning bits (TYPES) of colliding voxels.
+template <int AT, int BT, bool MARK, bool TYPES, bool ASUM, bool BSUM>
+__device__ __forceinline__ void resolve_group(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long long g,
+                                              uint32_t hit, uint32_t t4, uint32_t& cnt, uint32_t (&acc)[8]) {
+  if (AT == kMapProb && ASUM) {
+    const uint4* p = reinterpret_cast<const uint4*>(a + (g << 5));
+    const uint4 lo = __ldcg(p), hi = __ldcg(p + 1);
+    hit &= prob_group_mask(lo, hi, t4);
+  }
+  if (BT == kMapProb && BSUM && hit) {
+    const uint4* p = reinterpret_cast<const uint4*>(b + (g << 5));
+    const uint4 lo = __ldg(p), hi = __ldg(p + 1);
+    hit &= prob_group_mask(lo, hi, t4);
+  }
+  cnt += __popc(hit);
+  if (MARK || TYPES) {
+    while (hit) {  // colliding voxels only
+      const int j = __ffs(hit) - 1;
+      hit &= hit - 1;
+      const long long i = (g << 5) + j;
+      if (AT == kMapBit) {
+        uint32_t* vp = reinterpret_cast<uint32_t*>(a + (size_t)i * kBitVoxelBytes);
+        if (TYPES) {
+          const BitVoxelWords v = ld_voxel(vp);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] |= v.w[k];
+          if (MARK && !(v.w[0] & 4u)) vp[0] = v.w[0] | 4u;
+        } else if (MARK) {
+          const uint32_t w0 = __ldcg(vp);
+          if (!(w0 & 4u)) vp[0] = w0 | 4u;  // insert(eBVM_COLLISION); occupancy (and the summary) unchanged
+        }
+      } else if (MARK) {
+        if (((const volatile int8_t*)a)[i] != 127) ((int8_t*)a)[i] = 127;  // stays "known"
+      }
+    }
+  }
+}
+
+// voxel-wise handling of the last (n & 31) voxels by the first warp of CTA 0
+template <int AT, int BT, bool MARK, bool TYPES>
+__device__ __forceinline__ void summary_tail(uint8_t* __restrict__ a, const uint8_t* __restrict__ b,
+                                             const uint32_t* __restrict__ occ_a, const uint32_t* __restrict__ occ_b,
+                                             long long n, int thr, uint32_t& cnt, uint32_t (&acc)[8]) {
+  if (blockIdx.x != 0 || threadIdx.x >= 32) return;
+  const long long i = ((n >> 5) << 5) + threadIdx.x;
+  if (i >= n) return;
+  bool oa, ob;
+  int pa = 0;
+  if (AT == kMapBit) oa = (__ldg(occ_a + (i >> 5)) >> (i & 31)) & 1u;
+  else { pa = ((const volatile int8_t*)a)[i]; oa = pa >= thr; }
+  if (BT == kMapBit) ob = (__ldg(occ_b + (i >> 5)) >> (i & 31)) & 1u;
+  else ob = (int)ld_stream_i8(b + i) >= thr;
+  if (!(oa && ob)) return;
+  ++cnt;
+  if (AT == kMapBit && (MARK || TYPES)) {
+    const BitVoxelWords va = ld_voxel(a + (size_t)i * kBitVoxelBytes);
+    if (TYPES) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] |= va.w[k];
+    }
+    if (MARK && !(va.w[0] & 4u)) *(uint32_t*)(a + (size_t)i * kBitVoxelBytes) = va.w[0] | 4u;
+  } else if (MARK && AT != kMapBit) {
+    if (pa != 127) ((int8_t*)a)[i] = 127;
+  }
+}
+
+// Both sides represented by summaries: 128-bit loads, 128 voxels per load pair and thread.
+template <int AT, int BT, bool MARK, bool TYPES>
+__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const uint32_t* __restrict__ occ_a,
+                   const uint32_t* __restrict__ occ_b, long long n, int thr, ReduceScratch* scratch, ResultBlock* out_d,
+                   ResultBlock* out_h, unsigned long long* count_out_d, PeerReduce pr) {
+  constexpr int U = 4;
+  uint32_t cnt = 0;
+  uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const uint32_t t4 = (uint32_t)(uint8_t)thr * 0x01010101u;
+  const long long n_full = n >> 5;     // complete 32-voxel groups
+  const long long n_quad = n_full >> 2;  // complete 4-group quads (summaries are 16-byte padded and aligned)
+  const uint4* qa = reinterpret_cast<const uint4*>(occ_a);
+  const uint4* qb = reinterpret_cast<const uint4*>(occ_b);
+  const long long stride = (long long)gridDim.x * kThreads * U;
+  for (long long base = (long long)blockIdx.x * kThreads * U; base < n_quad; base += stride) {
+    uint4 ma[U], mb[U];
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long q = base + u * kThreads + threadIdx.x;
+      ok[u] = q < n_quad;
+      if (ok[u]) { ma[u] = ld_stream_u4(qa + q); mb[u] = ld_stream_u4(qb + q); }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!ok[u]) continue;
+      const long long q = base + u * kThreads + threadIdx.x;
+      const uint32_t h[4] = {ma[u].x & mb[u].x, ma[u].y & mb[u].y, ma[u].z & mb[u].z, ma[u].w & mb[u].w};
+      if ((h[0] | h[1] | h[2] | h[3]) == 0u) continue;
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (h[k]) resolve_group<AT, BT, MARK, TYPES, true, true>(a, b, (q << 2) + k, h[k], t4, cnt, acc);
+    }
+  }
+  // up to 3 complete groups after the last quad
+  if (blockIdx.x == 0 && threadIdx.x < (n_full & 3)) {
+    const long long g = (n_quad << 2) + threadIdx.x;
+    const uint32_t hit = __ldg(occ_a + g) & __ldg(occ_b + g);
+    if (hit) resolve_group<AT, BT, MARK, TYPES, true, true>(a, b, g, hit, t4, cnt, acc);
+  }
+  summary_tail<AT, BT, MARK, TYPES>(a, b, occ_a, occ_b, n, thr, cnt, acc);
+  finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
+}
+
 // ASUM / BSUM: that side's summary is available. A BitVectorVoxel side always needs it (bit = occupied, exact); for a
 // ProbabilisticVoxel side the summary bit means "known" (occupancy != UNKNOWN), a superset of "occupancy >= threshold":
 // groups with candidate bits fetch their 32 Prob bytes and apply the threshold, groups without candidates (almost
@@ -208,67 +321,11 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
       const long long g = base + u * kThreads + threadIdx.x;
       if (!ASUM) ma[u] = prob_group_mask(alo[u], ahi[u], t4);
       if (!BSUM) mb[u] = prob_group_mask(blo[u], bhi[u], t4);
-      uint32_t hit = ma[u] & mb[u];
-      if (hit == 0u) continue;
-      if (AT == kMapProb && ASUM) {  // candidates: apply the threshold to this group's bytes
-        const uint4* p = reinterpret_cast<const uint4*>(a + (g << 5));
-        const uint4 lo = __ldcg(p), hi = __ldcg(p + 1);
-        hit &= prob_group_mask(lo, hi, t4);
-      }
-      if (BT == kMapProb && BSUM && hit) {
-        const uint4* p = reinterpret_cast<const uint4*>(b + (g << 5));
-        const uint4 lo = __ldg(p), hi = __ldg(p + 1);
-        hit &= prob_group_mask(lo, hi, t4);
-      }
-      cnt += __popc(hit);
-      if (MARK || TYPES) {
-        while (hit) {  // colliding voxels only
-          const int j = __ffs(hit) - 1;
-          hit &= hit - 1;
-          const long long i = (g << 5) + j;
-          if (AT == kMapBit) {
-            uint32_t* vp = reinterpret_cast<uint32_t*>(a + (size_t)i * kBitVoxelBytes);
-            if (TYPES) {
-              const BitVoxelWords v = ld_voxel(vp);
-#pragma unroll
-              for (int k = 0; k < 8; ++k) acc[k] |= v.w[k];
-              if (MARK && !(v.w[0] & 4u)) vp[0] = v.w[0] | 4u;
-            } else if (MARK) {
-              const uint32_t w0 = __ldcg(vp);
-              if (!(w0 & 4u)) vp[0] = w0 | 4u;  // insert(eBVM_COLLISION); occupancy (and the summary) unchanged
-            }
-          } else if (MARK) {
-            if (((const volatile int8_t*)a)[i] != 127) ((int8_t*)a)[i] = 127;  // stays "known"
-          }
-        }
-      }
+      const uint32_t hit = ma[u] & mb[u];
+      if (hit) resolve_group<AT, BT, MARK, TYPES, ASUM, BSUM>(a, b, g, hit, t4, cnt, acc);
     }
   }
-  // tail: fewer than 32 voxels, voxel-wise by the first warp of CTA 0
-  if (blockIdx.x == 0 && threadIdx.x < 32) {
-    const long long i = (n_full << 5) + threadIdx.x;
-    if (i < n) {
-      bool oa, ob;
-      int pa = 0;
-      if (AT == kMapBit) oa = (__ldg(occ_a + (i >> 5)) >> (i & 31)) & 1u;
-      else { pa = ((const volatile int8_t*)a)[i]; oa = pa >= thr; }
-      if (BT == kMapBit) ob = (__ldg(occ_b + (i >> 5)) >> (i & 31)) & 1u;
-      else ob = (int)ld_stream_i8(b + i) >= thr;
-      if (oa && ob) {
-        ++cnt;
-        if (AT == kMapBit && (MARK || TYPES)) {
-          const BitVoxelWords va = ld_voxel(a + (size_t)i * kBitVoxelBytes);
-          if (TYPES) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) acc[k] |= va.w[k];
-          }
-          if (MARK && !(va.w[0] & 4u)) *(uint32_t*)(a + (size_t)i * kBitVoxelBytes) = va.w[0] | 4u;
-        } else if (MARK && AT != kMapBit) {
-          if (pa != 127) ((int8_t*)a)[i] = 127;
-        }
-      }
-    }
-  }
+  summary_tail<AT, BT, MARK, TYPES>(a, b, occ_a, occ_b, n, thr, cnt, acc);
   finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
 }
 
@@ -276,12 +333,28 @@ template <int AT, int BT, bool ASUM, bool BSUM>
 static cudaError_t launch_summary(const LaunchCtx& c, int grid, uint8_t* a, const uint8_t* b, const uint32_t* occ_a,
                                   const uint32_t* occ_b, long long n, int thr, bool mark, bool types,
                                   unsigned long long* out) {
-#define GVX_GO(M, T) k_collide_summary<AT, BT, M, T, ASUM, BSUM><<<grid, kThreads, 0, c.stream>>>( \
-      a, b, occ_a, occ_b, n, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer)
+#define GVX_GO(M, T)                                                                                       \
+  do {                                                                                                     \
+    if (ASUM && BSUM)                                                                                      \
+      k_collide_summary2<AT, BT, M, T><<<grid, kThreads, 0, c.stream>>>(                                   \
+          a, b, occ_a, occ_b, n, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);              \
+    else                                                                                                   \
+      k_collide_summary<AT, BT, M, T, ASUM, BSUM><<<grid, kThreads, 0, c.stream>>>(                        \
+          a, b, occ_a, occ_b, n, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);              \
+  } while (0)
   if (types && AT == kMapBit) { if (mark) GVX_GO(true, (AT == kMapBit)); else GVX_GO(false, (AT == kMapBit)); }
   else                        { if (mark) GVX_GO(true, false); else GVX_GO(false, false); }
 #undef GVX_GO
   return cudaGetLastError();
+}
+
+// CTAs for `work` CTA-iterations when at most max_grid CTAs are resident: every CTA gets the same number of
+// iterations (no half-empty last wave)
+static int balanced_grid(long long work, int max_grid) {
+  if (work < 1) return 1;
+  if (work <= max_grid) return (int)work;
+  const long long iters = (work + max_grid - 1) / max_grid;
+  return (int)((work + iters - 1) / iters);
 }
 
 template <int AT, int BT>
@@ -311,8 +384,8 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
   const bool a_sum = occ_a != nullptr, b_sum = occ_b != nullptr;
   if (off == 0 && i_begin == 0 && (!a_bit || a_sum) && (!b_bit || b_sum) && (a_bit || b_bit || (a_sum && b_sum)) &&
       (((uintptr_t)a | (uintptr_t)b) & 15) == 0) {
-    long long work = ((n >> 5) + kThreads * 4 - 1) / (kThreads * 4);
-    const int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));
+    const long long units = (a_sum && b_sum) ? (n >> 7) : (n >> 5);  // quads of groups when both sides are summaries
+    const int grid = balanced_grid((units + kThreads * 4 - 1) / (kThreads * 4), max_grid);
 #define GVX_SUM(AT, BT, AS, BS) return launch_summary<AT, BT, AS, BS>(c, grid, a, b, occ_a, occ_b, n, thr, mark, types, count_out_d)
     if (a_bit && b_bit) GVX_SUM(kMapBit, kMapBit, true, true);
     if (a_bit) { if (b_sum) GVX_SUM(kMapBit, kMapProb, true, true); GVX_SUM(kMapBit, kMapProb, true, false); }
@@ -323,15 +396,15 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
   if (a_type == kMapProb && b_type == kMapProb) {
     const bool aligned = ((off & 15) == 0) && (((uintptr_t)a & 15) == 0) && (((uintptr_t)b & 15) == 0);
     if (aligned) {
-      long long work = (n / 16 + kThreads * kUnroll - 1) / (kThreads * kUnroll);
-      int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));
+      const int grid = balanced_grid((n / 16 + kThreads * kUnroll - 1) / (kThreads * kUnroll), max_grid);
       if (mark) k_collide_prob_prob<true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
       else k_collide_prob_prob<false><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
       return cudaGetLastError();
     }
   }
-  long long work = (n + kThreads * kUnroll - 1) / (kThreads * kUnroll);
-  int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));
+  // Bit x Bit advances 2 voxels per thread and step, the other pairs 4
+  const int per_step = kThreads * ((a_type == kMapBit && b_type == kMapBit) ? 2 : kUnroll);
+  const int grid = balanced_grid((n + per_step - 1) / per_step, max_grid);
   if (a_type == kMapBit && b_type == kMapProb) return launch_voxelwise<kMapBit, kMapProb>(c, grid, a, b, i_begin, i_end, off, thr, mark, types, count_out_d);
   if (a_type == kMapProb && b_type == kMapBit) return launch_voxelwise<kMapProb, kMapBit>(c, grid, a, b, i_begin, i_end, off, thr, mark, false, count_out_d);
   if (a_type == kMapBit && b_type == kMapBit) return launch_voxelwise<kMapBit, kMapBit>(c, grid, a, b, i_begin, i_end, off, thr, mark, false, count_out_d);

@@ -88,8 +88,9 @@ __device__ __forceinline__ void summary_set(uint32_t* occ, uint64_t idx) {
 
 __device__ __forceinline__ uint64_t warp_sum_u32(uint32_t v) { return (uint64_t)__reduce_add_sync(0xffffffffu, v); }
 
-// Scratch shared by every reducing kernel of one context: per-CTA partials, a self-resetting ticket
-// (atomicInc wraps to 0 when the last CTA arrives, so no memset between launches) and the result block.
+// Scratch shared by every reducing kernel of one context: accumulators the CTAs add into with one atomic each, and a
+// self-resetting ticket (atomicInc wraps to 0 when the last CTA arrives). The last CTA takes the accumulators with
+// atomicExch(.., 0), so no memset is needed between launches.
 struct ResultBlock {
   unsigned long long count;
   uint32_t mask[8];
@@ -112,9 +113,9 @@ struct PeerReduce {
 };
 constexpr int kMaxGrid = 148 * 16;  // upper bound on CTAs of a reducing kernel
 struct ReduceScratch {
-  unsigned long long partial_count[kMaxGrid];
-  uint32_t partial_mask[kMaxGrid][8];
-  unsigned int ticket;
+  unsigned long long total;  // sum of the CTAs' counts; taken (and zeroed) by the last CTA
+  uint32_t mask[8];          // OR of the CTAs' meaning masks; same protocol
+  unsigned int ticket;       // atomicInc wraps to 0 when the last CTA arrives
   unsigned int flag_accum;
 };
 

@@ -33,8 +33,10 @@ __device__ __forceinline__ unsigned long long peer_allreduce_sum(unsigned long l
   return sum;
 }
 
-// Block-level finish shared by all collide kernels: reduce (count, mask) over the CTA, publish the partial,
-// let the last CTA produce the final result.
+// Block-level finish shared by all counting kernels: reduce (count, mask) over the CTA, add it into the context's
+// accumulators with one atomic per CTA (8 more for a mask), take a ticket; the last CTA to arrive takes the totals,
+// optionally all-reduces the count over the peers, and publishes the result to device memory and to the mapped pinned
+// host block. Returns true in the last CTA.
 template <bool TYPES>
 __device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (&acc)[8], ReduceScratch* s,
                                              ResultBlock* out_d, ResultBlock* out_h,
@@ -59,59 +61,37 @@ __device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (
     unsigned long long c = 0;
 #pragma unroll
     for (int w = 0; w < kThreads / 32; ++w) c += sh_cnt[w];
-    s->partial_count[blockIdx.x] = c;
+    if (c) atomicAdd(&s->total, c);
     if (TYPES) {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) s->partial_mask[blockIdx.x][k] = sh_mask[k];
+      for (int k = 0; k < 8; ++k)
+        if (sh_mask[k]) atomicOr(&s->mask[k], sh_mask[k]);
     }
     __threadfence();
     const unsigned int t = atomicInc(&s->ticket, gridDim.x - 1);  // wraps to 0 on the last arrival
     sh_last = (t == gridDim.x - 1);
+    if (sh_last) {
+      __threadfence();
+      unsigned long long tot = atomicExch(&s->total, 0ull);
+      if (pr.world > 1) tot = peer_allreduce_sum(tot, pr);
+      out_d->count = tot;
+      out_h->count = tot;
+      out_d->flag = tot != 0;
+      out_h->flag = tot != 0;
+      if (count_out_d) *count_out_d = tot;
+      if (TYPES) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint32_t m = atomicExch(&s->mask[k], 0u);
+          out_d->mask[k] = m;
+          out_h->mask[k] = m;
+        }
+      }
+      __threadfence_system();
+    }
   }
   __syncthreads();
-  if (!sh_last) return false;
-  __threadfence();
-  unsigned long long c = 0;
-  uint32_t m[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  for (unsigned int b = threadIdx.x; b < gridDim.x; b += kThreads) {
-    c += __ldcg(&s->partial_count[b]);
-    if (TYPES) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) m[k] |= __ldcg(&s->partial_mask[b][k]);
-    }
-  }
-  __syncthreads();  // everyone is done with sh_cnt / sh_mask of the first phase
-  if (TYPES && threadIdx.x < 8) sh_mask[threadIdx.x] = 0u;
-  // 64-bit warp sum via two 32-bit halves would overflow-carry wrongly; shuffle-add instead
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-  if (lane == 0) sh_cnt[warp] = c;
-  __syncthreads();
-  if (TYPES) {
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const uint32_t r = __reduce_or_sync(0xffffffffu, m[k]);
-      if (lane == 0 && r) atomicOr(&sh_mask[k], r);
-    }
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) {
-    unsigned long long tot = 0;
-#pragma unroll
-    for (int w = 0; w < kThreads / 32; ++w) tot += sh_cnt[w];
-    if (pr.world > 1) tot = peer_allreduce_sum(tot, pr);
-    out_d->count = tot;
-    out_h->count = tot;
-    out_d->flag = tot != 0;
-    out_h->flag = tot != 0;
-    if (count_out_d) *count_out_d = tot;
-    if (TYPES) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) { out_d->mask[k] = sh_mask[k]; out_h->mask[k] = sh_mask[k]; }
-    }
-    __threadfence_system();
-  }
-  return true;
+  return sh_last;
 }
 
 }  // namespace gvx
