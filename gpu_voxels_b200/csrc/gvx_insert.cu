@@ -217,11 +217,15 @@ k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t*
         const float qx = (float)((double)rx * factor), qy = (float)((double)ry * factor), qz = (float)((double)rz * factor);
         wx = affine_row(P, qx, qy, qz); wy = affine_row(P + 4, qx, qy, qz); wz = affine_row(P + 8, qx, qy, qz);
       }
-      if (!(isnan(wx) || isnan(wy) || isnan(wz))) {
-        const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
-        if (cx < m.dx && cy < m.dy && cz < m.dz && sensor_inside && cz >= m.z0 && cz < m.z1) {
-          live = true;
-          idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+      if (sensor_inside && !(isnan(wx) || isnan(wy) || isnan(wz))) {
+        // z first: on a z-slab rank most points of the rig's cloud belong to other slabs and skip two divisions
+        const uint32_t cz = coord_to_voxel(wz, m.side);
+        if (cz >= m.z0 && cz < m.z1) {
+          const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side);
+          if (cx < m.dx && cy < m.dy) {
+            live = true;
+            idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+          }
         }
       }
     }
