@@ -34,6 +34,7 @@ BYTES_PER_VOXEL_SUMMARY = 0.25  # default path: 1 summary bit per voxel and side
 #                                  occupancy bit of the BitVectorVoxelMap); Prob bytes only for candidate groups
 BYTES_PER_VOXEL = 33  # Prob (1 B) x BitVector (32 B): algorithmic bytes of the dominant kernel
 THR = 0.5
+N_PAIRS = 8  # rotating (environment, robot) pairs and frames: 8 x 33.5 MB of summaries per rotation vs 126 MB of L2
 
 
 # ---- synthetic inputs (seeded; SURVEY 8d "C2") ---------------------------------------------------------------
@@ -204,9 +205,10 @@ def workload_config(n_gpus):
                         "log-odds insert then collideWith a 512^3 robot BitVectorVoxelMap (7 links, 350k pts)",
             "grid": [DX, DY, DZ * n_gpus], "voxels_per_gpu": DX * DY * DZ, "points_per_step": N_FRAME * n_gpus,
             "coll_threshold": THR, "mark_collisions": True,
-            "l2": "L2 flushed between timed iterations of the collide kernel alone (a 256 MB buffer is rewritten); the step "
-                  "loop alternates two (env, robot) map pairs (2 x 33.5 MB of summaries on the default path, "
-                  "2 x 4.43 GB when streaming, vs 126 MB L2)",
+            "l2": "inputs larger than L2: every timed loop rotates over %d (env, robot) map pairs and %d sensor frames, "
+                  "%d x 33.5 MB of summaries (default path) or %d x 4.43 GB of grids (streaming) per rotation vs 126 MB "
+                  "of L2; the single-launch figure flushes L2 (rewrites a 256 MB buffer) before every launch"
+                  % (N_PAIRS, N_PAIRS, N_PAIRS, N_PAIRS),
             "collide_path": "summaries: 'known' bits of the ProbVoxelMap x occupancy bits of the BitVectorVoxelMap "
                             "(both maintained by the insert kernels), Prob bytes only for candidate groups",
             "parallelism": "z-slab x%d" % n_gpus if n_gpus > 1 else "single GPU"}
@@ -251,17 +253,19 @@ def run_gpu_arm(args):
     n_vox = DX * DY * DZ
     dims = (DX, DY, DZ * world)
     slab = (DZ * rank, DZ * (rank + 1))
-    # TWO (environment, robot) map pairs used alternately, so that consecutive steps never find the previous step's
-    # grids in the 126 MB L2 (one pair's collide reads 151 MB; both pairs: 302 MB)
-    envs = [gv.ProbVoxelMap(dims, SIDE, slab=slab) for _ in range(2)]
-    robs = [gv.BitVectorVoxelMap(dims, SIDE, slab=slab) for _ in range(2)]
+    # N_PAIRS (environment, robot) map pairs and as many sensor frames used in rotation, so that a step never finds its
+    # inputs in the 126 MB L2: one pair's summaries are 33.5 MB, so a full rotation touches 8 x 33.5 MB = 268 MB of
+    # summaries (+ 8 frames, + the scattered voxels) before a pair comes round again. 8 x 4.43 GB = 35 GB of grids.
+    P = N_PAIRS
+    envs = [gv.ProbVoxelMap(dims, SIDE, slab=slab) for _ in range(P)]
+    robs = [gv.BitVectorVoxelMap(dims, SIDE, slab=slab) for _ in range(P)]
     # robot: every slab holds its own copy of the arm (inserted once, untimed); global cloud = all copies
     rclouds = [np.concatenate([c for r in range(world) for c in [robot_clouds(z_shift=DZ * SIDE * r)[k]]]) for k in range(7)]
     for rob in robs:
         rob.insertMetaPointCloud(gv.MetaPointCloud(rclouds), list(range(4, 11)))
     # frames: N sub-frames (one per slab) concatenated into one global cloud; every rank reads all of it
     poses = [sensor_pose(DZ * SIDE * r) for r in range(world)]
-    frames_h = [[depth_frame(201 + 2 * r + k) for r in range(world)] for k in range(2)]  # [parity][slab] sensor frame
+    frames_h = [[depth_frame(201 + P * r + k) for r in range(world)] for k in range(P)]  # [rotation][slab] sensor frame
     pinned = [[torch.from_numpy(f).pin_memory() for f in fr] for fr in frames_h]
     frames_d = [[p.cuda(non_blocking=True) for p in fr] for fr in pinned]
     count_d = torch.zeros(1, dtype=torch.int64, device="cuda")
@@ -277,10 +281,10 @@ def run_gpu_arm(args):
     def fold_frames(points_d, k):
         """log-odds update of ALL sub-frames (each with its own pose) in one launch; this rank keeps its slab's points"""
         if world == 1:
-            _lib.check(L.gvx_update_logodds(envs[k % 2].handle, C.c_void_p(points_d.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
+            _lib.check(L.gvx_update_logodds(envs[k % P].handle, C.c_void_p(points_d.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
                                             pose_arr[0].ctypes.data_as(C.c_void_p), 72))
         else:
-            _lib.check(L.gvx_update_logodds_multi(envs[k % 2].handle, C.c_void_p(points_d.data_ptr()), _lib.MEM_DEVICE,
+            _lib.check(L.gvx_update_logodds_multi(envs[k % P].handle, C.c_void_p(points_d.data_ptr()), _lib.MEM_DEVICE,
                                                   sizes_arr.ctypes.data_as(C.c_void_p), world,
                                                   poses_arr.ctypes.data_as(C.c_void_p), 72))
 
@@ -292,7 +296,7 @@ def run_gpu_arm(args):
         fused = sharding.connect_peer_mailboxes()
 
     def collide_global(k, host_count=None):
-        env, rob = envs[k % 2], robs[k % 2]
+        env, rob = envs[k % P], robs[k % P]
         if fused:
             _lib.check(L.gvx_collide_map_map_allreduce(env.handle, rob.handle, THR, 1, host_count,
                                                        C.c_void_p(count_d.data_ptr())))
@@ -303,7 +307,7 @@ def run_gpu_arm(args):
 
     def step_device(k):
         """inputs resident in HBM; result stays on the device (all-reduced when sharded)"""
-        fold_frames(cat_d[k % 2], k)
+        fold_frames(cat_d[k % P], k)
         collide_global(k)
 
     def step_e2e(k):
@@ -311,7 +315,7 @@ def run_gpu_arm(args):
         rank uploads ITS sensor's frame from pinned host memory and the frames are all-gathered over NVLink (each
         rank needs the whole cloud to find its slab's points), instead of N x the PCIe traffic per rank."""
         if world > 1:
-            own_d.copy_(pinned[k % 2][rank], non_blocking=True)
+            own_d.copy_(pinned[k % P][rank], non_blocking=True)
             dist.all_gather_into_tensor(gathered, own_d)
             fold_frames(gathered, k)
             if fused:
@@ -320,11 +324,11 @@ def run_gpu_arm(args):
                 return cnt.value
             collide_global(k)
             return int(count_d.item())
-        f = pinned[k % 2][0]
-        _lib.check(L.gvx_update_logodds(envs[k % 2].handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_HOST,
+        f = pinned[k % P][0]
+        _lib.check(L.gvx_update_logodds(envs[k % P].handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_HOST,
                                         pose_arr[0].ctypes.data_as(C.c_void_p), 72))
         cnt = C.c_uint64(0)
-        _lib.check(L.gvx_collide_map_map(envs[k % 2].handle, robs[k % 2].handle, THR, None, 1, C.byref(cnt)))
+        _lib.check(L.gvx_collide_map_map(envs[k % P].handle, robs[k % P].handle, THR, None, 1, C.byref(cnt)))
         return cnt.value
 
     def barrier():
@@ -361,8 +365,9 @@ def run_gpu_arm(args):
         # the collide kernel alone: (1) the default path (robot map's occupancy summary + streamed ProbVoxelMap) and
         # (2) the voxel-streaming kernel (GVX_OPT_USE_SUMMARY = 0: both grids read in full, the reference's pattern)
         def collide_alone(k):
-            _lib.check(L.gvx_collide_map_map_async(envs[k % 2].handle, robs[k % 2].handle, THR, None, 1,
+            _lib.check(L.gvx_collide_map_map_async(envs[k % P].handle, robs[k % P].handle, THR, None, 1,
                                                    C.c_void_p(count_d.data_ptr())))
+        # (1a) one event pair per launch, L2 flushed before each: includes the event pair's own ~2-3 us
         l2_flush = torch.zeros(256 << 20, dtype=torch.uint8, device="cuda")
         for k, (e0, e1) in enumerate(kev):
             l2_flush.add_(1)  # 2 x 256 MB of traffic: nothing of the 33.5 MB of summaries survives in the 126 MB L2
@@ -371,6 +376,15 @@ def run_gpu_arm(args):
             e1.record(stream)
         torch.cuda.synchronize()
         del l2_flush
+        # (1b) `steps` launches back to back over the rotating pairs (268 MB of summaries per rotation > L2), one event
+        # pair around all of them: the average launch duration without per-launch event overhead
+        evb0, evb1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        evb0.record(stream)
+        for k in range(args.steps):
+            collide_alone(k)
+        evb1.record(stream)
+        torch.cuda.synchronize()
+        k_b2b = evb0.elapsed_time(evb1) / args.steps
         _lib.check(L.gvx_set_option(1, 0))
         for k in range(3):
             collide_alone(k)
@@ -384,8 +398,8 @@ def run_gpu_arm(args):
         evi0, evi1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         evi0.record(stream)
         for k in range(args.steps):
-            f = frames_d[k % 2][rank]
-            _lib.check(L.gvx_update_logodds(envs[k % 2].handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
+            f = frames_d[k % P][rank]
+            _lib.check(L.gvx_update_logodds(envs[k % P].handle, C.c_void_p(f.data_ptr()), N_FRAME, _lib.MEM_DEVICE,
                                             pose_arr[rank].ctypes.data_as(C.c_void_p), 72))
         evi1.record(stream)
         torch.cuda.synchronize()
@@ -398,7 +412,7 @@ def run_gpu_arm(args):
         peak, peak_src = measured_peak_gbs()
         ks_ms = sorted(e0.elapsed_time(e1) for e0, e1 in kev_stream)
         ks_avg = sum(ks_ms) / len(ks_ms)
-        achieved = BYTES_PER_VOXEL_SUMMARY * n_vox / (k_avg * 1e-3) / 1e9
+        achieved = BYTES_PER_VOXEL_SUMMARY * n_vox / (k_b2b * 1e-3) / 1e9
         achieved_stream = BYTES_PER_VOXEL * n_vox / (ks_avg * 1e-3) / 1e9
 
         def _traffic(name):
@@ -419,11 +433,14 @@ def run_gpu_arm(args):
                             "are all-gathered over NVLink, the count is all-reduced and read back by every rank",
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_collide_summary<Prob,Bit,mark,sum,sum>", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "k_collide_summary2<Prob,Bit,mark>", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": BYTES_PER_VOXEL_SUMMARY * n_vox,
-                         "algorithmic_bytes_per_voxel": BYTES_PER_VOXEL_SUMMARY, "kernel_ms_avg": k_avg,
-                         "kernel_ms_min": k_ms[0], "frac_of_8000_nominal": achieved / 8000.0,
+                         "algorithmic_bytes_per_voxel": BYTES_PER_VOXEL_SUMMARY, "kernel_ms_avg": k_b2b,
+                         "kernel_ms_avg_how": "%d launches back to back over %d rotating map pairs (268 MB of summaries per "
+                                              "rotation > L2), one CUDA event pair around all of them" % (args.steps, N_PAIRS),
+                         "kernel_ms_single_launch_l2_flushed": k_avg, "kernel_ms_single_launch_min": k_ms[0],
+                         "frac_of_8000_nominal": achieved / 8000.0,
                          "note": "default path: one summary bit per voxel and side (2 x 16.8 MB for 512^3) + the Prob bytes of "
                                  "candidate groups (DESIGN.md 3.1): a 33.5 MB problem, launch-latency territory; the "
                                  "33 B/voxel figure of SURVEY 8d belongs to roofline_streaming"},

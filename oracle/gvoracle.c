@@ -498,3 +498,45 @@ uint64_t gvo_create_equidistant_points(uint64_t max_points, const uint32_t* max_
       }
   return n;
 }
+
+/* ---- batched forward kinematics of a DH chain ---------------------------------------------------
+ * DHParameters::convertDHtoM, GV/robot/dh_robot/KinematicLink.cu:30-84: sin/cos are evaluated in DOUBLE on the
+ * float angle and rounded to float; every product/sum after that is float with one rounding per operation
+ * (host g++, no FMA contraction); b == 0 is kept as written ("a * ct - b * st").
+ * KinematicChain::setConfiguration, GV/robot/dh_robot/KinematicChain.cu:104-124: link i's cloud is transformed by
+ * the product of the DH matrices of links 0..i-1 (identity for link 0): out[cfg][i] = T_0 * ... * T_{i-1}, with
+ * Matrix4f operator* (GV/helpers/cuda_matrices.h:772-803) summing left to right.
+ * dh4: n_links x {d, theta, a, alpha}; joint_types: 0 REVOLUTE, 1 PRISMATIC (KinematicLink.h:37-41);
+ * joint_values: n_cfg x n_links; out: n_cfg x n_links x 16 row-major. */
+static void dh_to_m(const float* p, int joint_type, float value, float* m) {
+  float d_current = p[0], theta_current = p[1];
+  const float a = p[2], alpha = p[3], b = 0;
+  if (joint_type == 1) d_current = p[0] + value;
+  else if (joint_type == 0) theta_current = p[1] + value;
+  const float ca = (float)cos((double)alpha), sa = (float)sin((double)alpha);
+  const float ct = (float)cos((double)theta_current), st = (float)sin((double)theta_current);
+  m[0] = ct;   m[1] = -st * ca; m[2] = st * sa;   m[3] = a * ct - b * st;
+  m[4] = st;   m[5] = ct * ca;  m[6] = -ct * sa;  m[7] = a * st + b * ct;
+  m[8] = 0.0f; m[9] = sa;       m[10] = ca;       m[11] = d_current;
+  m[12] = 0.0f; m[13] = 0.0f;   m[14] = 0.0f;     m[15] = 1.0f;
+}
+
+static void mat4_mul(const float* x, const float* y, float* r) {
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j)
+      r[4 * i + j] = x[4 * i + 0] * y[0 + j] + x[4 * i + 1] * y[4 + j] + x[4 * i + 2] * y[8 + j] + x[4 * i + 3] * y[12 + j];
+}
+
+int gvo_dh_chain(const float* dh4, const int32_t* joint_types, uint32_t n_links, const float* joint_values,
+                 uint32_t n_cfg, float* out) {
+  for (uint32_t c = 0; c < n_cfg; ++c) {
+    float acc[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}, m[16], t[16];
+    for (uint32_t l = 0; l < n_links; ++l) {
+      memcpy(out + ((size_t)c * n_links + l) * 16, acc, sizeof acc);
+      dh_to_m(dh4 + 4 * l, joint_types[l], joint_values[(size_t)c * n_links + l], m);
+      mat4_mul(acc, m, t);
+      memcpy(acc, t, sizeof acc);
+    }
+  }
+  return 0;
+}

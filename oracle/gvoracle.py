@@ -206,6 +206,16 @@ def batch_robot_collide(env, env_type, dims, side, base_xyz, cloud_sizes, meanin
     return counts
 
 
+def dh_chain(dh4, joint_types, joint_values):
+    """per-link transforms of a DH chain for a batch of configurations: (n_cfg, n_links, 4, 4) float32"""
+    dh4 = _f32(dh4).reshape(-1, 4)
+    jt = np.ascontiguousarray(joint_types, np.int32)
+    jv = _f32(joint_values).reshape(-1, len(dh4))
+    out = np.empty((jv.shape[0], len(dh4), 4, 4), np.float32)
+    assert lib().gvo_dh_chain(_ptr(dh4), _ptr(jt), C.c_uint32(len(dh4)), _ptr(jv), C.c_uint32(jv.shape[0]), _ptr(out)) == 0
+    return out
+
+
 def create_box_of_points(mn, mx, delta):
     mn, mx = _f32(mn), _f32(mx)
     n = lib().gvo_create_box_of_points(_ptr(mn), _ptr(mx), C.c_float(delta), None, C.c_uint64(0))

@@ -25,6 +25,10 @@
 #include <gpu_voxels/voxel/SVCollider.hpp>
 #include <gpu_voxels/voxelmap/kernels/VoxelMapOperations.h>
 
+// DHParameters::convertDHtoM: the reference's own translation unit, compiled for the host as it is there (nvcc hands
+// it to the same g++); no FMA contraction (-ffp-contract=off and no -mfma, like the reference's x86-64 build)
+#include <gpu_voxels/robot/dh_robot/KinematicLink.cu>
+
 using namespace gpu_voxels;
 static_assert(sizeof(BitVectorVoxel) == 32, "BitVectorVoxel layout");
 static_assert(sizeof(ProbabilisticVoxel) == 1, "ProbabilisticVoxel layout");
@@ -148,6 +152,24 @@ int gvrefcpu_list_entry_hit(int mode, const uint8_t* list_voxel32, const void* m
   if (mode == 1) return occ;
   BitVectorVoxel m; memcpy(&m, mask32, 32);
   return occ && !(m.bitVector() & lv.bitVector()).isZero();
+}
+
+// KinematicChain::setConfiguration's loop, GV/robot/dh_robot/KinematicChain.cu:104-124, with the reference's
+// DHParameters::convertDHtoM and Matrix4f operator*; out[cfg][link] = the matrix handed to transformSubCloud
+void gvrefcpu_dh_chain(const float* dh4, const int32_t* joint_types, uint32_t n_links, const float* joint_values,
+                       uint32_t n_cfg, float* out) {
+  for (uint32_t c = 0; c < n_cfg; ++c) {
+    Matrix4f transformation = gpu_voxels::Matrix4f::createIdentity();
+    for (uint32_t l = 0; l < n_links; ++l) {
+      memcpy(out + ((size_t)c * n_links + l) * 16, &transformation, 64);
+      robot::KinematicLink link(robot::DHParameters(dh4[4 * l], dh4[4 * l + 1], dh4[4 * l + 2], dh4[4 * l + 3], 0.0f,
+                                                    (robot::DHJointType)joint_types[l]));
+      link.setJointValue(joint_values[(size_t)c * n_links + l]);
+      Matrix4f m;
+      link.getMatrixRepresentation(m);
+      transformation = transformation * m;
+    }
+  }
 }
 
 } // extern "C"
