@@ -74,6 +74,8 @@ SIGNATURES = {
     "gvx_collide_list_map_mask": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),
     "gvx_collide_list_map_per_meaning": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),
     "gvx_batch_robot_collide": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, vp, u32, vp, f32, vp]),
+    "gvx_batch_robot_collide_dh": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, vp, vp, u32, vp, vp, u32, vp, f32, vp]),
+    "gvx_dh_chain_transforms": (C.c_int, [vp, vp, u32, vp, u32, vp, vp]),
     "gvx_batch_set_scratch_budget": (C.c_int, [u64]),
 }
 

@@ -309,6 +309,8 @@ ProbVoxelMap.insertSensorDataMulti = _insert_sensor_data_multi
 
 
 GVX_OPT_USE_SUMMARY = 1
+GVX_OPT_DH_CHECK_BITS = 2
+REVOLUTE, PRISMATIC = 0, 1  # robot::DHJointType, GV/robot/dh_robot/KinematicLink.h:37-41
 
 
 def set_option(option, value):
@@ -346,6 +348,52 @@ def batch_robot_collide(env_map, meta_point_cloud, voxel_meanings, transforms, t
                                          tr.ctypes.data_as(C.c_void_p), tr.shape[0],
                                          mk.ctypes.data_as(C.c_void_p) if mk is not None else None,
                                          coll_threshold, counts.ctypes.data_as(C.c_void_p)))
+    return counts
+
+
+def _dh_args(dh_params, joint_values):
+    """dh_params: per link (d, theta, a, alpha, joint_type) -- robot::DHParameters without the joint value"""
+    dh = np.asarray(dh_params, np.float64).reshape(-1, 5)
+    dh4 = np.ascontiguousarray(dh[:, :4], np.float32)
+    jt = np.ascontiguousarray(dh[:, 4], np.int32)
+    jv = np.ascontiguousarray(joint_values, np.float32).reshape(-1, len(dh4))
+    return dh4, jt, jv
+
+
+def dh_chain_transforms(dh_params, joint_values, return_ambiguous=False):
+    """KinematicChain::setConfiguration for a batch (GV/robot/dh_robot/KinematicChain.cu:93-126): the matrix each link's
+    cloud is transformed by, (n_cfg, n_links, 4, 4) float32, bit-identical to the reference's host arithmetic."""
+    L = _lib.init()
+    dh4, jt, jv = _dh_args(dh_params, joint_values)
+    out = np.empty((jv.shape[0], len(dh4), 4, 4), np.float32)
+    amb = C.c_uint32(0)
+    _lib.check(L.gvx_dh_chain_transforms(dh4.ctypes.data_as(C.c_void_p), jt.ctypes.data_as(C.c_void_p), len(dh4),
+                                         jv.ctypes.data_as(C.c_void_p), jv.shape[0], out.ctypes.data_as(C.c_void_p),
+                                         C.byref(amb)))
+    return (out, amb.value) if return_ambiguous else out
+
+
+def batch_robot_collide_dh(env_map, meta_point_cloud, voxel_meanings, dh_params, joint_values, link_cloud=None,
+                           types_to_check=None, coll_threshold=1.0):
+    """batch_robot_collide with the DH forward kinematics done on the device: joint_values (n_cfg, n_links)"""
+    L = _lib.init()
+    sizes = np.asarray(meta_point_cloud.getPointcloudSizes(), np.uint32)
+    mg = np.ascontiguousarray(np.broadcast_to(np.asarray(voxel_meanings, np.int32), (len(sizes),)))
+    xyz = meta_point_cloud.accumulated()
+    dh4, jt, jv = _dh_args(dh_params, joint_values)
+    lc = np.ascontiguousarray(link_cloud, np.int32) if link_cloud is not None else None
+    counts = np.zeros(jv.shape[0], np.uint64)
+    mk = None
+    if types_to_check is not None:
+        mk = np.ascontiguousarray(types_to_check.bytes if isinstance(types_to_check, BitVectorVoxel) else types_to_check,
+                                  np.uint8)
+    _lib.check(L.gvx_batch_robot_collide_dh(env_map.handle, xyz.ctypes.data_as(C.c_void_p), MEM_HOST,
+                                            sizes.ctypes.data_as(C.c_void_p), len(sizes), mg.ctypes.data_as(C.c_void_p),
+                                            dh4.ctypes.data_as(C.c_void_p), jt.ctypes.data_as(C.c_void_p), len(dh4),
+                                            lc.ctypes.data_as(C.c_void_p) if lc is not None else None,
+                                            jv.ctypes.data_as(C.c_void_p), jv.shape[0],
+                                            mk.ctypes.data_as(C.c_void_p) if mk is not None else None,
+                                            coll_threshold, counts.ctypes.data_as(C.c_void_p)))
     return counts
 
 

@@ -58,8 +58,10 @@ int gvx_shutdown(void) {
   for (auto& kv : g.buffers) if (kv.second.p) cudaFree(kv.second.p);
   g.buffers.clear();
   for (void** p : {&g.bat_bits, &g.bat_seen, &g.bat_tr, &g.bat_counts}) { if (*p) cudaFree(*p); *p = nullptr; }
-  for (void** p : {&g.bat_tr_h, &g.bat_counts_h}) { if (*p) cudaFreeHost(*p); *p = nullptr; }
+  for (void** p : {&g.bat_tr_h, &g.bat_counts_h, &g.bat_fk_h}) { if (*p) cudaFreeHost(*p); *p = nullptr; }
+  if (g.bat_fk) { cudaFree(g.bat_fk); g.bat_fk = nullptr; }
   g.bat_bits_cap = g.bat_seen_cap = g.bat_tr_cap = g.bat_tr_h_cap = g.bat_counts_cap = g.bat_counts_h_cap = 0;
+  g.bat_fk_cap = g.bat_fk_h_cap = 0;
   if (g.stage_d) cudaFree(g.stage_d);
   for (int k = 0; k < Context::kDescSlots; ++k) {
     if (g.desc_d[k]) cudaFree(g.desc_d[k]);
@@ -376,6 +378,9 @@ int gvx_set_option(int option, int value) {
   std::lock_guard<std::mutex> lk(g.mu);
   switch (option) {
     case GVX_OPT_USE_SUMMARY: g.use_summary = value != 0; return GVX_OK;
+    case GVX_OPT_DH_CHECK_BITS:
+      if (value < 8 || value > 52) return fail(GVX_ERR_INVALID, "GVX_OPT_DH_CHECK_BITS must be in [8, 52]");
+      g.dh_check_bits = value; return GVX_OK;
     default: return fail(GVX_ERR_INVALID, "unknown option %d", option);
   }
 }

@@ -80,6 +80,9 @@ struct Context {
   void* bat_tr_h = nullptr; size_t bat_tr_h_cap = 0;
   void* bat_counts = nullptr; size_t bat_counts_cap = 0;
   void* bat_counts_h = nullptr; size_t bat_counts_h_cap = 0;
+  void* bat_fk = nullptr; size_t bat_fk_cap = 0;      // DH links | joint values | ambiguous list (device)
+  void* bat_fk_h = nullptr; size_t bat_fk_h_cap = 0;  // the same, pinned
+  int dh_check_bits = 50;  // GVX_OPT_DH_CHECK_BITS: bracket of the double sin/cos before rounding to float
   size_t bat_seen_budget = (size_t)4 << 30;  // bytes of "seen" scratch per wave of configurations
   // fused all-reduce over NVLink peer memory (gvx_peer_*): this rank's mailbox, the peers' mailboxes mapped through
   // CUDA IPC, and the collective sequence number

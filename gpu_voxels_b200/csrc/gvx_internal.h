@@ -89,4 +89,19 @@ cudaError_t launch_batch_collide(const LaunchCtx& c, const float* xyz_d, const B
                                  const uint32_t* env_bits_d, uint32_t* seen_d, uint64_t seen_words, uint32_t cfg0,
                                  uint32_t n_cfg_wave, unsigned long long* counts_d);
 
+// batched DH forward kinematics (gvx_kinematics.cu)
+struct DhLinkDev {
+  float d, theta, a, ca, sa;  // ca/sa = (float)cos/sin((double)alpha), evaluated once per link on the host with libm
+  int32_t joint_type;         // 0 REVOLUTE, 1 PRISMATIC (GV/robot/dh_robot/KinematicLink.h:37-41)
+  int32_t out_slot;           // index of the link's cloud in the output row, < 0: none
+  int32_t pad_;
+};
+DhLinkDev dh_link_prepare(float d, float theta, float a, float alpha, int joint_type, int out_slot);
+// one configuration on the host with the reference's arithmetic; out: out_stride x 16 (rows addressed by out_slot)
+void dh_chain_host(const DhLinkDev* links, uint32_t n_links, const float* joint_values, float* out);
+// ambiguous_d: [0] = number of configurations whose float rounding could not be proven, [1..amb_cap] = their indices
+cudaError_t launch_dh_chain(const LaunchCtx& c, const DhLinkDev* links_d, uint32_t n_links, const float* joint_values_d,
+                            uint32_t n_cfg, float* out_d, uint32_t out_stride, int check_bits, uint32_t* ambiguous_d,
+                            uint32_t amb_cap);
+
 }  // namespace gvx

@@ -130,7 +130,11 @@ int gvx_map_upload(gvx_handle_t h, const void* host_buf);
 int gvx_map_refresh_summary(gvx_handle_t h);
 /* test / debug: the summary words of this process's slab (bit i&31 of word i>>5 = voxel i) and whether it is valid */
 int gvx_map_summary_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, int* valid);
-enum gvx_option { GVX_OPT_USE_SUMMARY = 1 /* 0: always stream the voxels (the reference's access pattern) */ };
+enum gvx_option {
+  GVX_OPT_USE_SUMMARY = 1,   /* 0: always stream the voxels (the reference's access pattern) */
+  GVX_OPT_DH_CHECK_BITS = 2  /* forward kinematics: sin/cos brackets of |v| * 2^-bits (default 50); smaller values send
+                                more configurations through the host re-computation (tests) */
+};
 int gvx_set_option(int option, int value);
 
 /* ---- voxelisation ------------------------------------------------------------------------------------- */
@@ -262,6 +266,24 @@ int gvx_collide_list_map_per_meaning(gvx_handle_t list, gvx_handle_t map, float 
 int gvx_batch_robot_collide(gvx_handle_t env, const float* base_xyz, int mem_kind, const uint32_t* cloud_sizes,
                             uint32_t n_clouds, const int32_t* meanings, const float* transforms, uint32_t n_cfg,
                             const uint8_t* mask32, float thr, uint64_t* counts);
+/* The same check with the forward kinematics of a DH chain done on the device: replaces, per configuration,
+ * KinematicChain::setConfiguration (GV/robot/dh_robot/KinematicChain.cu:93-126: DHParameters::convertDHtoM,
+ * GV/robot/dh_robot/KinematicLink.cu:30-84, and the host Matrix4f product, GV/helpers/cuda_matrices.h:772-803).
+ * dh4: n_links x {d, theta, a, alpha}; joint_types[n_links]: 0 REVOLUTE, 1 PRISMATIC; joint_values: n_cfg x n_links
+ * (host). link_cloud[n_links] (nullable): index of the sub-cloud that moves with link l, or -1 (the reference matches
+ * them by name; a link without a cloud still enters the chain, a cloud without a link is not transformed);
+ * NULL = link l moves cloud l. The cloud of link l is transformed by T_0 * ... * T_(l-1), as in the reference. */
+int gvx_batch_robot_collide_dh(gvx_handle_t env, const float* base_xyz, int mem_kind, const uint32_t* cloud_sizes,
+                               uint32_t n_clouds, const int32_t* meanings, const float* dh4,
+                               const int32_t* joint_types, uint32_t n_links, const int32_t* link_cloud,
+                               const float* joint_values, uint32_t n_cfg, const uint8_t* mask32, float thr,
+                               uint64_t* counts);
+/* The per-link matrices alone: transforms_out (host) n_cfg x n_links row-major 4x4 fp32, bit-identical to the
+ * reference's host arithmetic (double libm sin/cos rounded to float, float products without FMA): the device result is
+ * used where its rounding is provably the same, the few other configurations (*n_ambiguous, nullable; ~1e-8 per
+ * value) are recomputed on the host. */
+int gvx_dh_chain_transforms(const float* dh4, const int32_t* joint_types, uint32_t n_links, const float* joint_values,
+                            uint32_t n_cfg, float* transforms_out, uint32_t* n_ambiguous);
 /* bytes of per-wave scratch the batch call may use for its per-configuration "seen" bitmaps (default 4 GiB) */
 int gvx_batch_set_scratch_budget(uint64_t bytes);
 

@@ -122,3 +122,20 @@ def test_list_entry_predicates(oracle, ref):
                 vb = 1 if mt == PROB else 32
                 want = sum(ref.gvrefcpu_list_entry_hit(mode, bitl[32 * i:].ctypes.data, m[vb * i:].ctypes.data, mt, thr, mask.ctypes.data) for i in range(n))
                 assert cnt == want, (mt, thr, mode)
+
+
+def test_dh_chain_against_reference_kinematic_link(oracle, ref):
+    """DHParameters::convertDHtoM + KinematicChain's accumulation: the reference's own KinematicLink.cu and
+    Matrix4f operator*, compiled for the host, against the restatement -- bit for bit, incl. huge / tiny / -0 angles"""
+    rng = np.random.Generator(np.random.PCG64(21))
+    nl, nc = 9, 30000
+    dh = rng.uniform(-1, 1, size=(nl, 4)).astype(np.float32)
+    dh[:, 3] = rng.choice(np.array([0, np.pi / 2, -np.pi / 2, np.pi, 1.1], np.float32), nl)
+    jt = rng.integers(0, 2, nl).astype(np.int32)
+    jv = rng.uniform(-7, 7, size=(nc, nl)).astype(np.float32)
+    jv[:8, :] = np.array([0.0, -0.0, np.pi / 2, 1e-30, 1e5, -12345.678, 3e38, 1e-45], np.float32)[:, None]
+    got = oracle.dh_chain(dh, jt, jv)
+    want = np.empty_like(got)
+    ref.gvrefcpu_dh_chain(dh.ctypes.data_as(C.c_void_p), jt.ctypes.data_as(C.c_void_p), nl,
+                          jv.ctypes.data_as(C.c_void_p), nc, want.ctypes.data_as(C.c_void_p))
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
