@@ -54,6 +54,8 @@ SIGNATURES = {
     "gvx_collide_map_map_async": (C.c_int, [u64, u64, f32, vp, C.c_int, vp]),
     "gvx_collide_map_map_any": (C.c_int, [u64, u64, f32, P(C.c_int)]),
     "gvx_collide_map_map_types": (C.c_int, [u64, u64, f32, C.c_int, vp, P(u64)]),
+    "gvx_collide_map_map_bitcheck": (C.c_int, [u64, u64, u32, u32, C.c_int, vp, P(u64)]),
+    "gvx_map_shift_sv_ids": (C.c_int, [u64, u32]),
     "gvx_peer_mailbox_create": (C.c_int, [vp]),
     "gvx_peer_mailbox_connect": (C.c_int, [C.c_int, C.c_int, vp]),
     "gvx_peer_mailbox_disconnect": (C.c_int, []),

@@ -266,9 +266,23 @@ class BitVectorVoxelMap(GpuVoxelsMap):
         b = np.ascontiguousarray(bits.bytes if isinstance(bits, BitVectorVoxel) else bits, np.uint8)
         _lib.check(self._L.gvx_map_clear_bits(self.handle, b.ctypes.data_as(C.c_void_p)))
 
+    def collisionCheckBitvector(self, other, window_size, types_in_collision, sv_offset=0, mark=True):
+        """collisionCheckBitvector(other, SVCollider(1.0, window_size), types, sv_offset), GV/voxelmap/BitVoxelMap.hpp:91-135"""
+        cnt = C.c_uint64(0)
+        _lib.check(self._L.gvx_collide_map_map_bitcheck(self.handle, other.handle, int(window_size), int(sv_offset),
+                                                        int(mark), types_in_collision.bytes.ctypes.data_as(C.c_void_p),
+                                                        C.byref(cnt)))
+        return cnt.value
+
+    def shiftLeftSweptVolumeIDs(self, shift_size):
+        """GV/voxelmap/BitVoxelMap.hpp:234-246"""
+        _lib.check(self._L.gvx_map_shift_sv_ids(self.handle, int(shift_size)))
+
     def collideWithTypes(self, other, types_in_collision, coll_threshold=1.0, offset=None, mark=True):
         """GV/voxelmap/BitVoxelMap.hpp:205-217; types_in_collision (BitVectorVoxel) is OR-ed into; offset ignored
-        like in the reference."""
+        like in the reference. Against a BitVectorVoxelMap this is the bit-window check with window 0."""
+        if isinstance(other, BitVectorVoxelMap):
+            return self.collisionCheckBitvector(other, 0, types_in_collision, 0, mark)
         cnt = C.c_uint64(0)
         _lib.check(self._L.gvx_collide_map_map_types(self.handle, other.handle, coll_threshold, int(mark),
                                                      types_in_collision.bytes.ctypes.data_as(C.c_void_p),

@@ -681,4 +681,47 @@ int gvx_collide_map_map_types(gvx_handle_t ha, gvx_handle_t hb, float thr, int m
   return GVX_OK;
 }
 
+int gvx_collide_map_map_bitcheck(gvx_handle_t ha, gvx_handle_t hb, uint32_t margin, uint32_t sv_offset, int mark,
+                                 uint8_t types_inout32[GVX_BITVOXEL_BYTES], uint64_t* count) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map *a, *b;
+  int64_t off, i0, i1;
+  int rc = collide_prepare(ha, hb, nullptr, &a, &b, &off, &i0, &i1);
+  if (rc) return rc;
+  if (a->type != kMapBit || b->type != kMapBit)
+    return fail(GVX_ERR_UNSUPPORTED, "the bit-window check needs two BitVectorVoxelMaps");
+  // the reference prints an error for a window above 32 and then shifts by a negative amount; 32 itself shifts a
+  // 64-bit word by 64. Both are undefined there and refused here. The same for an offset that shifts by >= 64.
+  if (margin > 31) return fail(GVX_ERR_INVALID, "window size %u: the reference's 64-bit window supports at most 31", margin);
+  if (sv_offset > 0xFFFFu) return fail(GVX_ERR_INVALID, "sv_offset %u exceeds the kernel's uint16", sv_offset);
+  const uint32_t high = (sv_offset >> 3) & 0xFFu;
+  if (high >= 32 + margin) return fail(GVX_ERR_INVALID, "sv_offset %u shifts the 64-bit window by 64 or more", sv_offset);
+  // candidate filters: `other` contributes only swept-volume bits, a subset of its occupancy summary; `this` also
+  // contributes bits 0..3, and eBVM_FREE (not in the summary) reaches a swept-volume bit when margin + high >= 4
+  const uint32_t* occ_b = g.use_summary ? b->occ_if_valid() : nullptr;
+  const uint32_t* occ_a = (g.use_summary && occ_b && margin + high < 4) ? a->occ_if_valid() : nullptr;
+  GVX_CUDA(launch_collide_bitcheck(lctx(), a->data, b->data, i1 - i0, margin, sv_offset, mark != 0, occ_a, occ_b,
+                                   a->occ_valid ? a->occ : nullptr, nullptr));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (count) *count = g.result_h->count;
+  if (types_inout32) {
+    const uint8_t* m = (const uint8_t*)g.result_h->mask;
+    for (int k = 0; k < 32; ++k) types_inout32[k] |= m[k];
+  }
+  return GVX_OK;
+}
+
+int gvx_map_shift_sv_ids(gvx_handle_t h, uint32_t shift) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (m->type != kMapBit) return fail(GVX_ERR_UNSUPPORTED, "shiftLeftSweptVolumeIDs needs a BitVectorVoxelMap");
+  if (shift > 56) return fail(GVX_ERR_INVALID, "Maximum shift size is 56! Higher shift number requested. Not performing shift operation.");
+  GVX_CUDA(launch_shift_sv_ids(lctx(), m->data, m->n_voxels(), shift, m->occ));
+  if (m->occ) m->occ_valid = true;  // the kernel re-derives every summary word
+  return GVX_OK;
+}
+
 }  // extern "C"

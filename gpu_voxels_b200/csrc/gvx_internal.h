@@ -89,6 +89,13 @@ cudaError_t launch_batch_collide(const LaunchCtx& c, const float* xyz_d, const B
                                  const uint32_t* env_bits_d, uint32_t* seen_d, uint64_t seen_words, uint32_t cfg0,
                                  uint32_t n_cfg_wave, unsigned long long* counts_d);
 
+// swept-volume window check and ID shift (gvx_sweptvolume.cu). occ_a/occ_b: summaries usable as candidate filters
+// (nullable), occ_a_mark: summary of `a` to keep in sync when a voxel is marked (nullable)
+cudaError_t launch_collide_bitcheck(const LaunchCtx& c, void* a, const void* b, int64_t n, uint32_t margin,
+                                    uint32_t sv_offset, bool mark, const uint32_t* occ_a, const uint32_t* occ_b,
+                                    uint32_t* occ_a_mark, unsigned long long* count_out_d);
+cudaError_t launch_shift_sv_ids(const LaunchCtx& c, void* data, uint64_t n_voxels, uint32_t shift, uint32_t* occ);
+
 // batched DH forward kinematics (gvx_kinematics.cu)
 struct DhLinkDev {
   float d, theta, a, ca, sa;  // ca/sa = (float)cos/sin((double)alpha), evaluated once per link on the host with libm

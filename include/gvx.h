@@ -186,6 +186,20 @@ int gvx_collide_map_map_any(gvx_handle_t a, gvx_handle_t b, float thr, int* flag
  * GV/voxel/SVCollider.hpp:96-106). mask_inout32 is OR-ed into (the reference does not reset it). */
 int gvx_collide_map_map_types(gvx_handle_t a, gvx_handle_t b, float thr, int mark,
                               uint8_t mask_inout32[GVX_BITVOXEL_BYTES], uint64_t* count);
+/* Swept-volume check with a bit window: BitVoxelMap::collisionCheckBitvector(BitVoxelMap* other,
+ * SVCollider(thr, margin), types, sv_offset) (GV/voxelmap/BitVoxelMap.hpp:91-135; SVCollider::collide(Bit, Bit, ...)
+ * GV/voxel/SVCollider.hpp:87-93; bitMarginCollisionCheck GV/helpers/BitVector.h:416-471; reference tests
+ * GV/test/testing_voxelmap.cu:173-229). A voxel collides if a swept-volume bit of b lies within +-margin bits of a
+ * bit of a (after moving a by sv_offset); *count = such voxels, types_inout32 |= their colliding bits of a, and with
+ * mark != 0 they receive eBVM_COLLISION. BitVoxelMap::collideWithTypes(BitVectorVoxelMap*) (BitVoxelMap.hpp:205-210)
+ * is margin 0, sv_offset 0. margin <= 31 and sv_offset / 8 < 32 + margin (beyond that the reference shifts a
+ * 64-bit word by >= 64: undefined there, refused here). */
+int gvx_collide_map_map_bitcheck(gvx_handle_t a, gvx_handle_t b, uint32_t margin, uint32_t sv_offset, int mark,
+                                 uint8_t types_inout32[GVX_BITVOXEL_BYTES], uint64_t* count);
+/* BitVoxelMap::shiftLeftSweptVolumeIDs (GV/voxelmap/BitVoxelMap.hpp:234-246; performLeftShift
+ * GV/helpers/BitVector.h:361-402; reference test GV/test/testing_voxelmap.cu:238-304): every voxel's bit vector moves
+ * `shift` bits towards bit 0 and loses its four non-swept-volume bits. shift > 56 is an error (no change), as there. */
+int gvx_map_shift_sv_ids(gvx_handle_t h, uint32_t shift);
 
 /* ---- multi-GPU: collision count all-reduced INSIDE the collide kernel over NVLink peer memory ------------- */
 /* One process per GPU (not in the reference). Every rank creates a small mailbox in its HBM and exports it as a

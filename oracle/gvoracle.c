@@ -540,3 +540,75 @@ int gvo_dh_chain(const float* dh4, const int32_t* joint_types, uint32_t n_links,
   }
   return 0;
 }
+
+/* ---- swept-volume window check and ID shift ----------------------------------------------------
+ * bitMarginCollisionCheck, GV/helpers/BitVector.h:416-471, restated with the same 64-bit window arithmetic:
+ * the window holds 4 bytes of v2 above bit 32 and whatever has been shifted down below it; byte 0 of v2 loses its
+ * four non-swept-volume bits, byte 0 of v1 does NOT. `low` = sv_offset % 8 moves the first visited bit (and so can
+ * skip byte 0 and de-synchronise the refill), `high` = sv_offset / 8 is a bit shift of v1 -- the reference names
+ * them the other way round. Every visited byte of `collisions` is overwritten, the others are left alone. */
+int gvo_bit_margin_check(const uint8_t* v1, const uint8_t* v2, uint8_t* collisions, uint32_t margin, uint32_t sv_offset) {
+  uint64_t window = 0;
+  for (int k = 0; k < 4; ++k) window += (uint64_t)(k == 0 ? (v2[0] & 0xF0) : v2[k]) << (32 + 8 * k);
+  const uint32_t low = (uint8_t)(sv_offset % 8), high = (uint8_t)(sv_offset / 8);
+  for (uint32_t i = 4 /* eBVM_SWEPT_VOLUME_START */ + low; i < 254 /* eBVM_SWEPT_VOLUME_END, GV/helpers/common_defines.h:57 */; i += 8) {
+    uint8_t out = 0;
+    uint64_t probe = (uint64_t)v1[i >> 3] << (32 - margin + high);
+    for (uint32_t s = 0; s <= 2 * margin; ++s) {
+      out |= (uint8_t)((probe & window) >> (32 - margin + s));
+      probe <<= 1;
+    }
+    collisions[i >> 3] = out;
+    window >>= 8;
+    if (i < 256 - 32) window += (uint64_t)v2[(i + 32) >> 3] << 56;
+  }
+  for (int k = 0; k < GVO_BITVOXEL_BYTES; ++k) if (collisions[k]) return 1;
+  return 0;
+}
+
+/* performLeftShift, GV/helpers/BitVector.h:361-402: the vector moves `shift` (<= 56) bits towards bit 0 through a
+ * 64-bit window; the four non-swept-volume bits of byte 0 are cleared */
+void gvo_shift_left(uint8_t* v, uint32_t shift) {
+  uint64_t window = 0;
+  for (int k = 0; k < 8; ++k) window += (uint64_t)v[k] << (8 * k);
+  for (int k = 0; k < GVO_BITVOXEL_BYTES; ++k) {
+    uint8_t nb = (uint8_t)(window >> shift);
+    if (k == 0) nb &= 0xF0;
+    v[k] = nb;
+    window >>= 8;
+    if (k + 8 < GVO_BITVOXEL_BYTES) window += (uint64_t)v[k + 8] << 56;
+  }
+}
+
+/* BitVoxelMap::collisionCheckBitvector(BitVoxelMap*, SVCollider(thr, margin), types, sv_offset),
+ * GV/voxelmap/BitVoxelMap.hpp:91-135 + kernelCollideVoxelMapsBitvector, VoxelMapOperations.hpp:187-239, launched
+ * with one thread per voxel (ceil(n/1024) blocks of 1024), so every thread's `temp` starts empty and the block
+ * reduction ORs all of them: types32 |= union of the per-voxel collision bits, count = voxels with any.
+ * collideWithTypes(BitVectorVoxelMap*) is this with margin 0, sv_offset 0 (BitVoxelMap.hpp:205-210). */
+int gvo_collide_bitcheck(uint8_t* a, const uint8_t* b, uint64_t n, uint32_t margin, uint32_t sv_offset, int mark,
+                         uint8_t* types32, uint64_t* count) {
+  uint64_t cnt = 0;
+  for (uint64_t i = 0; i < n; ++i) {
+    uint8_t temp[GVO_BITVOXEL_BYTES] = {0};
+    /* shortcut (keeps the CPU suite fast, changes nothing): an empty v1 probes with zeros, an empty v2 gives an empty
+     * window -- every visited byte is then written as 0 */
+    const uint64_t* qa = (const uint64_t*)(a + i * GVO_BITVOXEL_BYTES);
+    const uint64_t* qb = (const uint64_t*)(b + i * GVO_BITVOXEL_BYTES);
+    if ((qa[0] | qa[1] | qa[2] | qa[3]) == 0 || ((qb[0] & ~(uint64_t)0xF) | qb[1] | qb[2] | qb[3]) == 0) continue;
+    if (gvo_bit_margin_check(a + i * GVO_BITVOXEL_BYTES, b + i * GVO_BITVOXEL_BYTES, temp, margin, sv_offset)) {
+      if (mark) bit_set(a + i * GVO_BITVOXEL_BYTES, GVO_EBVM_COLLISION);
+      for (int k = 0; k < GVO_BITVOXEL_BYTES; ++k) types32[k] |= temp[k];
+      ++cnt;
+    }
+  }
+  *count = cnt;
+  return 0;
+}
+
+/* BitVoxelMap::shiftLeftSweptVolumeIDs, GV/voxelmap/BitVoxelMap.hpp:234-246 (kernelShiftBitVector,
+ * VoxelMapOperations.hpp:615-624); shift > 56 is refused there with an error message and no change */
+int gvo_shift_map(uint8_t* a, uint64_t n, uint32_t shift) {
+  if (shift > 56) return 1;
+  for (uint64_t i = 0; i < n; ++i) gvo_shift_left(a + i * GVO_BITVOXEL_BYTES, shift);
+  return 0;
+}

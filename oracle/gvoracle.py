@@ -206,6 +206,32 @@ def batch_robot_collide(env, env_type, dims, side, base_xyz, cloud_sizes, meanin
     return counts
 
 
+def bit_margin_check(v1, v2, margin, sv_offset=0, collisions=None):
+    v1, v2 = np.ascontiguousarray(v1, np.uint8), np.ascontiguousarray(v2, np.uint8)
+    out = np.zeros(32, np.uint8) if collisions is None else collisions
+    r = lib().gvo_bit_margin_check(_ptr(v1), _ptr(v2), _ptr(out), C.c_uint32(margin), C.c_uint32(sv_offset))
+    return bool(r), out
+
+
+def shift_left(v32, shift):
+    v = np.ascontiguousarray(v32, np.uint8).copy()
+    lib().gvo_shift_left(_ptr(v), C.c_uint32(shift))
+    return v
+
+
+def collide_bitcheck(a, b, n, margin=0, sv_offset=0, mark=True, types=None):
+    """collisionCheckBitvector(BitVoxelMap*, SVCollider(1.0, margin), types, sv_offset): (count, types32)"""
+    types = np.zeros(32, np.uint8) if types is None else types
+    cnt = C.c_uint64(0)
+    assert lib().gvo_collide_bitcheck(_ptr(a), _ptr(b), C.c_uint64(n), C.c_uint32(margin), C.c_uint32(sv_offset),
+                                      int(mark), _ptr(types), C.byref(cnt)) == 0
+    return cnt.value, types
+
+
+def shift_map(a, n, shift):
+    return lib().gvo_shift_map(_ptr(a), C.c_uint64(n), C.c_uint32(shift)) == 0
+
+
 def dh_chain(dh4, joint_types, joint_values):
     """per-link transforms of a DH chain for a batch of configurations: (n_cfg, n_links, 4, 4) float32"""
     dh4 = _f32(dh4).reshape(-1, 4)

@@ -158,3 +158,40 @@ def test_bitmasked_collision(oracle):
             mask[bit >> 3] |= 1 << (bit & 7)
             got.append(lst.collide(2, m, PROB, 1.0, off, mask_in=mask)[0])
         assert got == [e * 64 for e in expect]
+
+
+SV_START = 4  # eBVM_SWEPT_VOLUME_START
+
+
+def test_collision_bitshift(oracle):
+    """GV/test/testing_voxelmap.cu:173-229 (voxelmap/collision_bitshift): 8 voxels of meaning SV_START+40 against the
+    same voxels of meaning i, window 20: collisions (all 8, only bit type_1) iff |i - type_1| <= 20"""
+    pts = np.array([[x, y, z] for x in (2, 3) for y in (2, 3) for z in (2, 3)], np.float32)
+    type_1, window = SV_START + 40, 20
+    m1 = oracle.new_map(BIT, DIMS)
+    oracle.insert_points(m1, BIT, DIMS, 1.0, pts, type_1)
+    types = np.zeros(32, np.uint8)  # the reference never resets types_voxel between iterations
+    for i in range(type_1 - window - 9, type_1 + window + 10):
+        m2 = oracle.new_map(BIT, DIMS)
+        oracle.insert_points(m2, BIT, DIMS, 1.0, pts, i)
+        cnt, types = oracle.collide_bitcheck(m1, m2, N, window, 0, True, types)
+        if cnt > 0:
+            types[type_1 >> 3] &= ~np.uint8(1 << (type_1 & 7))
+            assert not types.any()
+        assert cnt == (0 if abs(i - type_1) > window else len(pts)), i
+
+
+def test_bitvoxelmap_bitshift(oracle):
+    """GV/test/testing_voxelmap.cu:238-304 (voxelmap/bitvoxelmap_bitshift): map_2 holds SV_START+50, map_1 holds
+    SV_START+50-shift; after shifting map_2 by `shift` all 4 voxels collide (window 1) iff shift <= 50"""
+    pts = np.array([[0.3] * 3, [1.3] * 3, [2.3] * 3, [3.3] * 3], np.float32)
+    shift_start = 50
+    type_int = SV_START + shift_start
+    for shift in range(0, shift_start + SV_START - 5):
+        m1, m2 = oracle.new_map(BIT, DIMS), oracle.new_map(BIT, DIMS)
+        oracle.insert_points(m2, BIT, DIMS, 1.0, pts, type_int)
+        oracle.insert_points(m1, BIT, DIMS, 1.0, pts, type_int - shift)
+        assert oracle.shift_map(m2, N, shift)
+        cnt, _ = oracle.collide_bitcheck(m1, m2, N, 1, 0, True)
+        assert cnt == (len(pts) if shift <= shift_start else 0), shift
+    assert not oracle.shift_map(m2, N, 57)

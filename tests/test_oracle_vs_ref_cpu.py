@@ -139,3 +139,25 @@ def test_dh_chain_against_reference_kinematic_link(oracle, ref):
     ref.gvrefcpu_dh_chain(dh.ctypes.data_as(C.c_void_p), jt.ctypes.data_as(C.c_void_p), nl,
                           jv.ctypes.data_as(C.c_void_p), nc, want.ctypes.data_as(C.c_void_p))
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def test_bit_margin_check_and_shift_against_reference_bitvector_h(oracle, ref):
+    """bitMarginCollisionCheck / performLeftShift (GV/helpers/BitVector.h:361-471) on random vectors, windows and
+    offsets -- including the result vector's untouched bytes (it is not reset by the reference)"""
+    rng = np.random.Generator(np.random.PCG64(31))
+    for it in range(20000):
+        dens = rng.choice([0.02, 0.1, 0.5])
+        v1 = np.packbits(rng.uniform(size=256) < dens, bitorder="little")
+        v2 = np.packbits(rng.uniform(size=256) < dens, bitorder="little")
+        margin = int(rng.integers(0, 32))
+        svo = int(rng.integers(0, 8 * (32 + margin))) if it % 3 == 0 else int(rng.integers(0, 24))
+        c1 = rng.integers(0, 256, 32).astype(np.uint8)
+        c2 = c1.copy()
+        r1, _ = oracle.bit_margin_check(v1, v2, margin, svo, c1)
+        r2 = ref.gvrefcpu_bit_margin_check(v1.ctypes.data_as(C.c_void_p), v2.ctypes.data_as(C.c_void_p),
+                                           c2.ctypes.data_as(C.c_void_p), margin, svo)
+        assert r1 == bool(r2) and np.array_equal(c1, c2), (margin, svo)
+        sh = int(rng.integers(0, 57))
+        s2 = v1.copy()
+        ref.gvrefcpu_shift_left(s2.ctypes.data_as(C.c_void_p), sh)
+        assert np.array_equal(oracle.shift_left(v1, sh), s2), sh
