@@ -49,6 +49,7 @@ SIGNATURES = {
     "gvx_insert_meta": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, u32, vp, P(C.c_int)]),
     "gvx_transform_points": (C.c_int, [vp, vp, u64, C.c_int, vp]),
     "gvx_update_logodds": (C.c_int, [u64, vp, u64, C.c_int, vp, C.c_int]),
+    "gvx_insert_sensor_data": (C.c_int, [u64, vp, u64, C.c_int, vp, C.c_int, u64, C.c_int, C.c_int, C.c_int]),
     "gvx_update_logodds_multi": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, C.c_int]),
     "gvx_collide_map_map": (C.c_int, [u64, u64, f32, vp, C.c_int, P(u64)]),
     "gvx_collide_map_map_async": (C.c_int, [u64, u64, f32, vp, C.c_int, vp]),

@@ -293,13 +293,21 @@ class BitVectorVoxelMap(GpuVoxelsMap):
 class ProbVoxelMap(GpuVoxelsMap):
     map_type = MT_PROBAB_VOXELMAP
 
-    def insertSensorData(self, points_sensor_frame, sensor_pose, delta_occupied=72):
-        """the log-odds update of GV/voxelmap/ProbVoxelMap.hpp:52-102 without ray casting.
-        sensor_pose: 3x4 (or 4x4) row-major [R|t]."""
+    def insertSensorData(self, points_sensor_frame, sensor_pose, delta_occupied=72, enable_raycasting=False,
+                         cut_real_robot=False, robot_voxel_meaning=eBVM_OCCUPIED, robot_map=None, delta_free=-10):
+        """ProbVoxelMap::insertSensorData (GV/voxelmap/ProbVoxelMap.hpp:52-102): the log-odds update of the hit
+        voxels, optionally with the free-space ray casting and the robot cut. sensor_pose: 3x4 (or 4x4) row-major
+        [R|t]."""
         p, n, kind, keep = _points_arg(points_sensor_frame)
         pose = np.ascontiguousarray(np.asarray(sensor_pose, np.float32).reshape(-1)[:12])
-        _lib.check(self._L.gvx_update_logodds(self.handle, p, n, kind, pose.ctypes.data_as(C.c_void_p),
-                                              int(delta_occupied)))
+        if not enable_raycasting and not cut_real_robot:
+            _lib.check(self._L.gvx_update_logodds(self.handle, p, n, kind, pose.ctypes.data_as(C.c_void_p),
+                                                  int(delta_occupied)))
+            return
+        rh = robot_map.handle if cut_real_robot else 0
+        _lib.check(self._L.gvx_insert_sensor_data(self.handle, p, n, kind, pose.ctypes.data_as(C.c_void_p),
+                                                  int(enable_raycasting), rh, int(robot_voxel_meaning),
+                                                  int(delta_free), int(delta_occupied)))
 
 
 def _insert_sensor_data_multi(self, frames, sensor_poses, delta_occupied=72):

@@ -495,6 +495,40 @@ int gvx_update_logodds(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int 
   return GVX_OK;
 }
 
+int gvx_insert_sensor_data(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int mem_kind, const float pose12[12],
+                           int enable_raycasting, gvx_handle_t robot_map, int robot_bit, int delta_free,
+                           int delta_occ) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (m->type != kMapProb) return fail(GVX_ERR_UNSUPPORTED, "insertSensorData needs a ProbVoxelMap");
+  if (delta_occ < 0 || delta_occ > 127) return fail(GVX_ERR_INVALID, "delta_occ %d outside [0, 127]", delta_occ);
+  if (delta_free > 0 || delta_free < -127) return fail(GVX_ERR_INVALID, "delta_free %d outside [-127, 0]", delta_free);
+  const void* robot_d = nullptr;
+  if (robot_map) {
+    Map* r = find_map(robot_map);
+    if (!r) return fail(GVX_ERR_INVALID, "unknown robot map handle %llu", (unsigned long long)robot_map);
+    if (r->type != kMapBit) return fail(GVX_ERR_UNSUPPORTED, "cut_real_robot needs a BitVectorVoxelMap of the robot");
+    if (r->dx != m->dx || r->dy != m->dy || r->dz != m->dz) return fail(GVX_ERR_DIM_MISMATCH, "robot map dimensions differ");
+    if (r->sharded()) return fail(GVX_ERR_UNSUPPORTED, "the robot map of cut_real_robot must be whole on every rank (a ray's hit voxel may lie in another slab)");
+    if (robot_bit < 0 || robot_bit > 255) return fail(GVX_ERR_INVALID, "robot bit %d out of range", robot_bit);
+    robot_d = r->data;
+  }
+  if (n == 0) return GVX_OK;
+  if (!xyz_sensor || !pose12) return fail(GVX_ERR_INVALID, "null pointer");
+  Affine12 P;
+  memcpy(P.a, pose12, 48);
+  const float* xyz_d = nullptr;
+  int rc = points_to_device(xyz_sensor, n, mem_kind, &xyz_d);
+  if (rc) return rc;
+  // defined order: all free-space decrements of the frame, then all hits (two launches = the barrier between them)
+  if (enable_raycasting && delta_free != 0)
+    GVX_CUDA(launch_raycast_free(lctx(), m->view(), xyz_d, n, P, delta_free, robot_d, (uint32_t)robot_bit));
+  GVX_CUDA(launch_update_logodds(lctx(), m->view(), xyz_d, n, P, delta_occ, robot_d, (uint32_t)robot_bit));
+  return GVX_OK;
+}
+
 int gvx_update_logodds_multi(gvx_handle_t h, const float* xyz_sensor, int mem_kind, const uint32_t* frame_sizes,
                              uint32_t n_frames, const float* poses12, int delta_occ) {
   std::lock_guard<std::mutex> lk(g.mu);

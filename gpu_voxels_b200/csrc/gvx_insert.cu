@@ -132,11 +132,28 @@ __device__ __forceinline__ void logodds_add(int8_t* map, uint64_t idx, int total
   } while (old != assumed);
 }
 
+// kernelTransformSensorData, GV/voxelmap/kernels/VoxelMapOperations.cu:27-71: pose * raw point; a point that lands below
+// z = 0 is pulled back along its ray onto the floor with a DOUBLE factor
+__device__ __forceinline__ void sensor_to_world(const float* __restrict__ P, float rx, float ry, float rz, float& wx,
+                                                float& wy, float& wz) {
+  wx = affine_row(P, rx, ry, rz); wy = affine_row(P + 4, rx, ry, rz); wz = affine_row(P + 8, rx, ry, rz);
+  if (wz < 0.0f) {
+    const double factor = (double)__fdiv_rn(P[11], __fsub_rn(P[11], wz));
+    const float qx = (float)((double)rx * factor), qy = (float)((double)ry * factor), qz = (float)((double)rz * factor);
+    wx = affine_row(P, qx, qy, qz); wy = affine_row(P + 4, qx, qy, qz); wz = affine_row(P + 8, qx, qy, qz);
+  }
+}
+
+__device__ __forceinline__ bool robot_bit_set(const uint8_t* __restrict__ robot, uint64_t voxel, uint32_t bit) {
+  return (__ldg(robot + voxel * kBitVoxelBytes + (bit >> 3)) >> (bit & 7)) & 1u;
+}
+
 // insertSensorData without ray casting: sensor-frame point -> world (pose = [R|t], re-projection onto z = 0
 // with the reference's double-precision factor when the world point is below the floor), NaN filter, bounds
 // test on the point and on the sensor origin, updateOccupancy(+delta) at the hit voxel.
 __global__ void __launch_bounds__(kInsThreads)
-k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n, const Affine12 pose, int delta) {
+k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n, const Affine12 pose, int delta,
+                 const uint8_t* __restrict__ robot, uint32_t robot_bit) {
   const float* P = pose.a;
   const uint32_t sx = coord_to_voxel(P[3], m.side), sy = coord_to_voxel(P[7], m.side), sz = coord_to_voxel(P[11], m.side);
   const bool sensor_inside = sx < m.dx && sy < m.dy && sz < m.dz;
@@ -150,17 +167,15 @@ k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n,
     uint64_t idx = 0;
     if (i < n) {
       const float rx = __ldg(xyz + 3 * i), ry = __ldg(xyz + 3 * i + 1), rz = __ldg(xyz + 3 * i + 2);
-      float wx = affine_row(P, rx, ry, rz), wy = affine_row(P + 4, rx, ry, rz), wz = affine_row(P + 8, rx, ry, rz);
-      if (wz < 0.0f) {  // VoxelMapOperations.cu:56-64
-        const double factor = (double)__fdiv_rn(P[11], __fsub_rn(P[11], wz));
-        const float qx = (float)((double)rx * factor), qy = (float)((double)ry * factor), qz = (float)((double)rz * factor);
-        wx = affine_row(P, qx, qy, qz); wy = affine_row(P + 4, qx, qy, qz); wz = affine_row(P + 8, qx, qy, qz);
-      }
+      float wx, wy, wz;
+      sensor_to_world(P, rx, ry, rz, wx, wy, wz);
       if (!(isnan(wx) || isnan(wy) || isnan(wz))) {
         const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
         if (cx < m.dx && cy < m.dy && cz < m.dz && sensor_inside && cz >= m.z0 && cz < m.z1) {
           live = true;
           idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+          // cut_real_robot, VoxelMapOperations.hpp:578-592: the sensor sees the robot there, no update
+          if (robot) live = !robot_bit_set(robot, (uint64_t)cz * slab + (uint64_t)cy * m.dx + cx, robot_bit);
         }
       }
     }
@@ -169,6 +184,75 @@ k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n,
     if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
       logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
       if (m.occ) summary_set(m.occ, idx);  // clamp(.., -127, 127) never returns to UNKNOWN: the voxel is "known"
+    }
+  }
+}
+
+// Free-space pass of insertSensorData with ray casting (RayCaster::rayCast, GV/voxelmap/kernels/VoxelMapOperations.h:
+// 199-323): every live point walks the integer line from the sensor's voxel to its hit voxel, 1 + |dx| + |dy| + |dz|
+// cells with both ends, and applies updateOccupancy(delta_free < 0) to each. This pass holds ONLY decrements, which
+// commute under the saturating clamp; the hits follow in k_update_logodds (the defined order).
+// The lanes of a warp are neighbouring pixels: their rays leave the sensor through the same voxels, so each step folds
+// equal voxels into one update (match_any), and a voxel already at MIN_PROBABILITY (-127) is skipped after one L2 read
+// -- the cone in front of the sensor saturates after a few frames and then costs no atomics at all.
+__global__ void __launch_bounds__(kInsThreads)
+k_raycast_free(MapView m, const float* __restrict__ xyz, unsigned long long n, const Affine12 pose, int delta_free,
+               const uint8_t* __restrict__ robot, uint32_t robot_bit) {
+  const float* P = pose.a;
+  const uint32_t sx = coord_to_voxel(P[3], m.side), sy = coord_to_voxel(P[7], m.side), sz = coord_to_voxel(P[11], m.side);
+  if (!(sx < m.dx && sy < m.dy && sz < m.dz)) return;
+  const uint64_t slab = (uint64_t)m.dx * m.dy;
+  const unsigned long long nvox = slab * m.dz;
+  if (n > nvox) n = nvox;
+  const unsigned lane = threadIdx.x & 31;
+  int8_t* map = (int8_t*)m.data;
+  const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
+  const unsigned long long n_round = (n + 31ull) & ~31ull;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n_round; i += stride) {
+    int32_t px = (int32_t)sx, py = (int32_t)sy, pz = (int32_t)sz, steps = 0;
+    int32_t dx2 = 0, dy2 = 0, dz2 = 0, ix = 0, iy = 0, iz = 0, e_xy = 0, e_xz = 0, e_yz = 0;
+    if (i < n) {
+      const float rx = __ldg(xyz + 3 * i), ry = __ldg(xyz + 3 * i + 1), rz = __ldg(xyz + 3 * i + 2);
+      float wx, wy, wz;
+      sensor_to_world(P, rx, ry, rz, wx, wy, wz);
+      if (!(isnan(wx) || isnan(wy) || isnan(wz))) {
+        const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
+        if (cx < m.dx && cy < m.dy && cz < m.dz &&
+            !(robot && robot_bit_set(robot, (uint64_t)cz * slab + (uint64_t)cy * m.dx + cx, robot_bit))) {
+          int32_t ddx, ddy, ddz;
+          if (cx > sx) { ddx = (int32_t)(cx - sx); ix = 1; } else { ddx = (int32_t)(sx - cx); ix = -1; }
+          if (cy > sy) { ddy = (int32_t)(cy - sy); iy = 1; } else { ddy = (int32_t)(sy - cy); iy = -1; }
+          if (cz > sz) { ddz = (int32_t)(cz - sz); iz = 1; } else { ddz = (int32_t)(sz - cz); iz = -1; }
+          steps = 1 + ddx + ddy + ddz;
+          e_xy = ddx - ddy; e_xz = ddx - ddz; e_yz = ddy - ddz;
+          dx2 = 2 * ddx; dy2 = 2 * ddy; dz2 = 2 * ddz;
+        }
+      }
+    }
+    const int32_t max_steps = __reduce_max_sync(0xffffffffu, steps);
+    for (int32_t s = 0; s < max_steps; ++s) {
+      const bool act = s < steps;
+      bool need = false;
+      uint64_t idx = 0;
+      int v = 0;
+      if (act && (uint32_t)pz >= m.z0 && (uint32_t)pz < m.z1) {
+        idx = (uint64_t)((uint32_t)pz - m.z0) * slab + (uint64_t)py * m.dx + (uint64_t)px;
+        v = (int)__ldcg(map + idx);
+        need = v != -127;  // at the floor already: further decrements change nothing
+      }
+      if (__any_sync(0xffffffffu, need)) {
+        const unsigned long long key = need ? idx : (~0ull - lane);
+        const unsigned peers = __match_any_sync(0xffffffffu, key);
+        if (need && lane == (unsigned)(__ffs(peers) - 1)) {
+          logodds_add(map, idx, delta_free * __popc(peers));
+          if (m.occ && v == -128) summary_set(m.occ, idx);  // first touch: the voxel becomes "known"
+        }
+      }
+      if (act) {
+        if (e_xy > 0 && e_xz > 0) { px += ix; e_xy -= dy2; e_xz -= dz2; }
+        else if (e_yz > 0)        { py += iy; e_xy += dx2; e_yz -= dz2; }
+        else                      { pz += iz; e_xz += dx2; e_yz += dy2; }
+      }
     }
   }
 }
@@ -301,9 +385,18 @@ cudaError_t launch_transform(const LaunchCtx& c, const float* in_d, float* out_d
 }
 
 cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
-                                  const Affine12& pose, int delta) {
+                                  const Affine12& pose, int delta, const void* robot_d, uint32_t robot_bit) {
   ++*c.launches;
-  k_update_logodds<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, n, pose, delta);
+  k_update_logodds<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, n, pose, delta, (const uint8_t*)robot_d,
+                                                                    robot_bit);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_raycast_free(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
+                                const Affine12& pose, int delta_free, const void* robot_d, uint32_t robot_bit) {
+  ++*c.launches;
+  k_raycast_free<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, n, pose, delta_free, (const uint8_t*)robot_d,
+                                                                  robot_bit);
   return cudaGetLastError();
 }
 

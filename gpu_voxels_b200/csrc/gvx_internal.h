@@ -45,8 +45,14 @@ cudaError_t launch_insert_meta(const LaunchCtx& c, const MapView& m, const float
                                const MetaDesc& d, bool want_flag);
 struct Affine12 { float a[12]; };  // row-major [R|t], passed to kernels by value (no H2D copy, no sync)
 cudaError_t launch_transform(const LaunchCtx& c, const float* in_d, float* out_d, uint64_t n, const Affine12& M);
+// robot_d (nullable): data of a WHOLE BitVectorVoxelMap of the same dimensions; points whose hit voxel has robot_bit
+// set there are dropped (cut_real_robot)
 cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
-                                  const Affine12& pose, int delta);
+                                  const Affine12& pose, int delta, const void* robot_d = nullptr,
+                                  uint32_t robot_bit = 0);
+// the free-space pass of the ray caster: delta_free (< 0) on every cell from the sensor's voxel to the hit voxel
+cudaError_t launch_raycast_free(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
+                                const Affine12& pose, int delta_free, const void* robot_d, uint32_t robot_bit);
 cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
                                         const uint32_t* prefix_d, const float* poses_d, uint32_t n_frames, int delta);
 // voxel &= ~mask for all voxels; occ (nullable): summary words rewritten from the result

@@ -161,6 +161,18 @@ int gvx_transform_points(const float* in_xyz, float* out_xyz, uint64_t n, int me
 int gvx_update_logodds(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int mem_kind, const float pose12[12],
                        int delta_occ);
 
+/* ProbVoxelMap::insertSensorData complete (GV/voxelmap/ProbVoxelMap.hpp:52-102): enable_raycasting != 0 adds the
+ * free-space update of RayCaster::rayCast (GV/voxelmap/kernels/VoxelMapOperations.h:199-323): every cell on the integer
+ * line from the sensor's voxel to the hit voxel (both included) receives delta_free (cSENSOR_MODEL_FREE = -10) before
+ * the hit voxel receives delta_occ. robot_map != 0 is cut_real_robot (VoxelMapOperations.hpp:578-592): points whose
+ * hit voxel has bit robot_bit set in that (whole) BitVectorVoxelMap are dropped. Order of updates: all decrements of
+ * the frame, then all hits -- deterministic, no lost updates; equal to the reference executed point by point wherever
+ * a voxel is not both crossed and hit by different rays (the reference's own result depends on its thread schedule).
+ * On a z-slab map every rank walks the rays and keeps its slab's cells. Asynchronous. */
+int gvx_insert_sensor_data(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int mem_kind, const float pose12[12],
+                           int enable_raycasting, gvx_handle_t robot_map, int robot_bit, int delta_free,
+                           int delta_occ);
+
 /* The same update for several sensor frames, each with its own pose, in ONE launch (multi-camera rigs; z-slab ranks
  * that fold the whole rig's cloud and keep only their slab's points). xyz_sensor: the concatenated frames;
  * frame_sizes[n_frames] (host); poses12: n_frames row-major [R|t] (host). Asynchronous. */

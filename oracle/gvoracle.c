@@ -612,3 +612,86 @@ int gvo_shift_map(uint8_t* a, uint64_t n, uint32_t shift) {
   for (uint64_t i = 0; i < n; ++i) gvo_shift_left(a + i * GVO_BITVOXEL_BYTES, shift);
   return 0;
 }
+
+/* ---- insertSensorData with ray casting and robot cut -------------------------------------------
+ * kernelInsertSensorData<RayCaster>, GV/voxelmap/kernels/VoxelMapOperations.hpp:559-613, and RayCaster::rayCast,
+ * GV/voxelmap/kernels/VoxelMapOperations.h:199-323: an integer line walk from the sensor's voxel to the hit voxel
+ * that visits 1 + |dx| + |dy| + |dz| cells (both ends included) and applies updateOccupancy(cSENSOR_MODEL_FREE = -10)
+ * to each, then updateOccupancy(cSENSOR_MODEL_OCCUPIED = +72) at the hit voxel. With cut_real_robot a point whose hit
+ * voxel has `robot_bit` set in the robot map is dropped altogether (:578-592).
+ *
+ * ORDER. The reference updates voxels with non-atomic read-modify-writes from one thread per point, so its result
+ * depends on the schedule (lost updates, and clamp(-128 - 10) = -127 vs clamp(-128 + 72) = -56 do not commute). The
+ * defined order here and in the CUDA path: ALL free-space decrements of the frame first, then ALL hits. Decrements
+ * commute among themselves and so do hits, so the result is min(max(v - 10*kf, -127) + 72*ko, 127) per voxel
+ * (v = -128 -> the first update clamps as in ProbabilisticVoxel::updateOccupancy). It equals the reference run
+ * sequentially wherever a voxel is not both crossed and hit by DIFFERENT rays (tests pin exactly that).
+ * kf / ko (nullable): per-voxel counts of decrements / hits of this call, for tests. */
+static void ray_walk(int8_t* map, const uint32_t* dims, uint32_t z0, uint32_t z1, const uint32_t* from,
+                     const uint32_t* to, int delta_free, uint32_t* kf) {
+  int32_t d[3], inc[3], p[3];
+  for (int k = 0; k < 3; ++k) {
+    if (to[k] > from[k]) { d[k] = (int32_t)(to[k] - from[k]); inc[k] = 1; }
+    else { d[k] = (int32_t)(from[k] - to[k]); inc[k] = -1; }
+    p[k] = (int32_t)from[k];
+  }
+  int32_t n = 1 + d[0] + d[1] + d[2];
+  int32_t e_xy = d[0] - d[1], e_xz = d[0] - d[2], e_yz = d[1] - d[2];
+  d[0] *= 2; d[1] *= 2; d[2] *= 2;
+  for (; n > 0; --n) {
+    if ((uint32_t)p[2] >= z0 && (uint32_t)p[2] < z1) {
+      const uint64_t idx = (uint64_t)((uint32_t)p[2] - z0) * dims[0] * dims[1] + (uint64_t)p[1] * dims[0] + (uint64_t)p[0];
+      map[idx] = prob_update(map[idx], delta_free);
+      if (kf) ++kf[idx];
+    }
+    if (e_xy > 0 && e_xz > 0) { p[0] += inc[0]; e_xy -= d[1]; e_xz -= d[2]; }
+    else if (e_yz > 0)        { p[1] += inc[1]; e_xy += d[0]; e_yz -= d[2]; }
+    else                      { p[2] += inc[2]; e_xz += d[0]; e_yz += d[1]; }
+  }
+}
+
+int gvo_insert_sensor_data(int8_t* map, const uint32_t* dims, uint32_t z0, uint32_t z1, float side,
+                           const float* xyz_sensor, uint64_t n, const float* pose12, int raycast,
+                           const uint8_t* robot_map /* whole BitVectorVoxelMap or NULL */, int robot_bit,
+                           int delta_free, int delta_occ, uint32_t* kf, uint32_t* ko) {
+  float M[16];
+  memcpy(M, pose12, 12 * sizeof(float));
+  M[12] = 0; M[13] = 0; M[14] = 0; M[15] = 1;
+  const float sensor_pos[3] = {pose12[3], pose12[7], pose12[11]};
+  uint32_t sc[3];
+  gvo_map_to_voxels(side, sensor_pos, sc);
+  if (!(sc[0] < dims[0] && sc[1] < dims[1] && sc[2] < dims[2])) return 0;
+  uint64_t nvox = (uint64_t)dims[0] * dims[1] * dims[2];
+  if (n > nvox) n = nvox;
+  for (int phase = raycast ? 0 : 1; phase < 2; ++phase) {
+    for (uint64_t i = 0; i < n; ++i) {
+      const float* raw = xyz_sensor + 3 * i;
+      float w[3];
+      xform(M, raw, w);
+      if (w[2] < 0) {
+        double factor = (double)((float)(sensor_pos[2] / (sensor_pos[2] - w[2])));
+        float r2[3];
+        r2[0] = (float)((double)raw[0] * factor);
+        r2[1] = (float)((double)raw[1] * factor);
+        r2[2] = (float)((double)raw[2] * factor);
+        xform(M, r2, w);
+      }
+      if (isnan(w[0]) || isnan(w[1]) || isnan(w[2])) continue;
+      uint32_t c[3];
+      gvo_map_to_voxels(side, w, c);
+      if (!(c[0] < dims[0] && c[1] < dims[1] && c[2] < dims[2])) continue;
+      if (robot_map) {
+        const uint64_t g = ((uint64_t)c[2] * dims[1] + c[1]) * dims[0] + c[0];
+        const uint8_t* rv = robot_map + g * GVO_BITVOXEL_BYTES;
+        if (rv[robot_bit >> 3] & (1u << (robot_bit & 7))) continue; /* the sensor sees the robot: no update */
+      }
+      if (phase == 0) ray_walk(map, dims, z0, z1, sc, c, delta_free, kf);
+      else if (c[2] >= z0 && c[2] < z1) {
+        const uint64_t idx = (uint64_t)(c[2] - z0) * dims[0] * dims[1] + (uint64_t)c[1] * dims[0] + c[0];
+        map[idx] = prob_update(map[idx], delta_occ);
+        if (ko) ++ko[idx];
+      }
+    }
+  }
+  return 0;
+}

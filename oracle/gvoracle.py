@@ -124,6 +124,23 @@ def update_logodds(m, dims, side, xyz_sensor, pose12, delta=72, z0=0, z1=None):
                              C.c_uint64(len(xyz)), _ptr(_f32(pose12).reshape(12)), int(delta))
 
 
+def insert_sensor_data(m, dims, side, xyz_sensor, pose12, raycast=True, robot_map=None, robot_bit=1, delta_free=-10,
+                       delta_occ=72, z0=0, z1=None, counts=False):
+    """insertSensorData with ray casting / robot cut in the defined order (all free-space updates, then all hits).
+    counts=True: also returns (kf, ko), the per-voxel numbers of decrements and hits."""
+    z1 = dims[2] if z1 is None else z1
+    xyz = _f32(xyz_sensor).reshape(-1, 3)
+    kf = np.zeros(len(m), np.uint32) if counts else None
+    ko = np.zeros(len(m), np.uint32) if counts else None
+    rc = lib().gvo_insert_sensor_data(_ptr(m), _ptr(_dims(dims)), C.c_uint32(z0), C.c_uint32(z1), C.c_float(side),
+                                      _ptr(xyz), C.c_uint64(len(xyz)), _ptr(_f32(pose12).reshape(-1)[:12].copy()),
+                                      int(raycast), _ptr(robot_map) if robot_map is not None else None, int(robot_bit),
+                                      int(delta_free), int(delta_occ), _ptr(kf) if counts else None,
+                                      _ptr(ko) if counts else None)
+    assert rc == 0
+    return (kf, ko) if counts else None
+
+
 def collide_map_map(a, a_type, b, b_type, n, thr=1.0, off=0, mark=True):
     cnt = C.c_uint64(0)
     lib().gvo_collide_map_map(_ptr(a), a_type, _ptr(b), b_type, C.c_uint64(n), C.c_float(thr), C.c_int64(off),

@@ -184,6 +184,38 @@ int gvref_insert_sensor_data(void* map, uint32_t dx, uint32_t dy, uint32_t dz, f
   return 0;
 }
 
+// ProbVoxelMap::insertSensorData complete (GV/voxelmap/ProbVoxelMap.hpp:52-102): raycast != 0 selects RayCaster,
+// robot_map_d != NULL enables cut_real_robot with bit `robot_bit`. serial != 0 launches <<<1, 1>>>: the reference's
+// kernel run by ONE thread walks the points in index order without races (its updates are non-atomic), which is the
+// deterministic result the parity tests compare against.
+int gvref_insert_sensor_data_full(void* map, uint32_t dx, uint32_t dy, uint32_t dz, float side, const float* pose12_h,
+                                  float* raw_d, float* tmp_d, uint32_t n, int raycast, void* robot_map_d,
+                                  uint32_t robot_bit, int serial) {
+  Sensor s(Vector3f(pose12_h[3], pose12_h[7], pose12_h[11]),
+           Matrix3f(pose12_h[0], pose12_h[1], pose12_h[2], pose12_h[4], pose12_h[5], pose12_h[6], pose12_h[8],
+                    pose12_h[9], pose12_h[10]), n, 1);
+  Sensor* s_d;
+  CK(cudaMalloc(&s_d, sizeof(Sensor)));
+  CK(cudaMemcpy(s_d, &s, sizeof(Sensor), cudaMemcpyHostToDevice));
+  uint32_t b, t; linear_load(n, &b, &t);
+  voxelmap::kernelTransformSensorData<<<b, t>>>(s_d, (Vector3f*)raw_d, (Vector3f*)tmp_d);
+  CK(cudaGetLastError());
+  if (serial) { b = 1; t = 1; }
+  const bool cut = robot_map_d != NULL;
+  if (raycast)
+    voxelmap::kernelInsertSensorData<<<b, t>>>((ProbabilisticVoxel*)map, dx * dy * dz, Vector3ui(dx, dy, dz), side, s_d,
+                                              (const Vector3f*)tmp_d, cut, (BitVoxel<BIT_VECTOR_LENGTH>*)robot_map_d,
+                                              robot_bit, voxelmap::RayCaster());
+  else
+    voxelmap::kernelInsertSensorData<<<b, t>>>((ProbabilisticVoxel*)map, dx * dy * dz, Vector3ui(dx, dy, dz), side, s_d,
+                                              (const Vector3f*)tmp_d, cut, (BitVoxel<BIT_VECTOR_LENGTH>*)robot_map_d,
+                                              robot_bit, voxelmap::DummyRayCaster());
+  CK(cudaGetLastError());
+  CK(cudaDeviceSynchronize());
+  CK(cudaFree(s_d));
+  return 0;
+}
+
 // BitVoxelList::collideWith(map) (GV/voxellist/TemplateVoxelList.hpp:731-774): kernelCollideWithVoxelMap + D2H + host sum
 long long gvref_collide_list_map(const uint32_t* ids, void* voxels, uint32_t size, const void* map, int map_type,
                                  uint32_t dx, uint32_t dy, uint32_t dz, float thr, int ox, int oy, int oz) {
