@@ -143,7 +143,7 @@ def config_c1():
            "insert_device_ms": ins[0], "insert_points_per_s": 1e5 / (ins[0] * 1e-3),
            "insert_host_cloud_sync_ms": host_ins[0],
            "collide_L2_resident_ms": hot[0], "collide_L2_flushed_ms": cold[0],
-           "collide_voxels_per_s_flushed": n / (cold[0] * 1e-3), "roofline_flushed": roof(33 * n, cold[0]),
+           "collide_voxels_per_s_flushed": n / (cold[0] * 1e-3), "roofline_flushed": roof(0.25 * n, cold[0]),
            "collide_sync_call_latency_ms": sync_call[0]}
     if REF is not None:
         ra = torch.zeros(n * 32, dtype=torch.uint8, device="cuda")
@@ -291,7 +291,10 @@ def config_c4(dz=2048):
     out = {"config": "C4 2048x2048x%d slab of the 2048^3 ProbVoxelMap, 8 x 1M-point clouds per frame, Prob x Prob collide thr 0.5" % dz,
            "voxels": n, "frame_insert_ms": ins[0], "insert_points_per_s": 8e6 / (ins[0] * 1e-3),
            "collide_ms": ms[0], "collide_ms_min": ms[1], "collide_voxels_per_s": n / (ms[0] * 1e-3),
-           "roofline": roof(2 * n, ms[0]), "clearMap_ms": clr[0], "clearMap_GBs": n / (clr[0] * 1e-3) / 1e9,
+           "roofline": roof(0.25 * n, ms[0]),
+           "roofline_note": "default path: the two 'known' summaries (2 x 1 bit per voxel) + the Prob bytes of candidate "
+                            "groups; the reference's streaming pattern would read 2 B per voxel (%.2f GB)" % (2 * n / 1e9),
+           "clearMap_ms": clr[0], "clearMap_GBs": n / (clr[0] * 1e-3) / 1e9,
            "collisions": int(cnt_d.item()), "reference_cuda": "not representable in the reference (uint32 voxel count, 4 GiB map limit)"}
     env.destroy(); rob.destroy()
     return out
@@ -348,14 +351,52 @@ def config_c5(n_list=10_000_000):
     return out
 
 
+# ---- C2r: configs[1]'s frame with the complete sensor model (free-space ray casting) ---------------------------
+def config_c2_raycast():
+    import bench as B
+    dims, side = (512, 512, 512), 0.01
+    frames = [torch.from_numpy(B.depth_frame(201 + k)).cuda() for k in range(4)]
+    pose = np.ascontiguousarray(B.sensor_pose().reshape(-1))
+    m = gv.ProbVoxelMap(dims, side)
+    k = [0]
+
+    def frame(raycast):
+        f = frames[k[0] % 4]; k[0] += 1
+        _lib.check(L.gvx_insert_sensor_data(m.handle, p_(f), f.shape[0], _lib.MEM_DEVICE, pose.ctypes.data_as(C.c_void_p),
+                                            int(raycast), 0, 1, -10, 72))
+    first = time_gpu(lambda: frame(1), 1, warmup=0)   # unknown map: every cell of every ray is a first touch
+    steady = time_gpu(lambda: frame(1), 30)           # the cone is saturated at -127: reads only
+    hits = time_gpu(lambda: frame(0), 30)
+    mm = m.download()
+    out = {"config": "C2r 512^3 ProbVoxelMap, 640x480 frame, insertSensorData WITH ray casting",
+           "points": int(frames[0].shape[0]), "first_frame_ms": first[0], "steady_state_ms": steady[0],
+           "hits_only_ms": hits[0], "known_voxels": int((mm != -128).sum()), "free_voxels": int((mm == -127).sum()),
+           "rays_per_s_steady": frames[0].shape[0] / (steady[0] * 1e-3)}
+    if REF is not None:
+        n = dims[0] * dims[1] * dims[2]
+        rmap = torch.full((n,), -128, dtype=torch.int8, device="cuda")
+        tmp = torch.empty_like(frames[0])
+
+        def ref_frame():
+            f = frames[k[0] % 4]; k[0] += 1
+            REF.gvref_insert_sensor_data_full(p_(rmap), *dims, C.c_float(side), pose.ctypes.data_as(C.c_void_p), p_(f),
+                                              p_(tmp), f.shape[0], 1, None, 1, 0)
+        r = time_wall(ref_frame, 10, warmup=2)
+        out["reference_cuda"] = {"frame_call_ms": r[0], "speedup_steady": r[0] / steady[0],
+                                 "note": "the reference's kernelTransformSensorData + kernelInsertSensorData<RayCaster> "
+                                         "(non-atomic, racy) rebuilt for sm_100a, same frames"}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--configs", default="c1,c3,c4,c4s,c5")
+    ap.add_argument("--configs", default="c1,c2r,c3,c4,c4s,c5")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "configs.json"))
     args = ap.parse_args()
     setup()
     res = {"gpu": torch.cuda.get_device_name(0), "peak_GBs_measured": PEAK_GBS, "results": []}
-    fns = {"c1": config_c1, "c3": config_c3, "c4": config_c4, "c4s": lambda: config_c4(256), "c5": config_c5}
+    fns = {"c1": config_c1, "c3": config_c3, "c4": config_c4, "c4s": lambda: config_c4(256), "c5": config_c5,
+           "c2r": config_c2_raycast}
     for name in args.configs.split(","):
         t0 = time.time()
         try:

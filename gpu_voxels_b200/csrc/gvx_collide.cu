@@ -232,13 +232,43 @@ __device__ __forceinline__ void summary_tail(uint8_t* __restrict__ a, const uint
   }
 }
 
-// Both sides represented by summaries: 128-bit loads, 128 voxels per load pair and thread.
+// One queued candidate group: both sides' Prob bytes are requested together (no load depends on the other side's
+// threshold mask), then the colliding voxels are counted / marked like in resolve_group.
+template <int AT, int BT, bool MARK, bool TYPES>
+__device__ __forceinline__ void resolve_entry(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long long g,
+                                              uint32_t hit, uint32_t t4, uint32_t& cnt, uint32_t (&acc)[8]) {
+  uint4 alo, ahi, blo, bhi;
+  if (AT == kMapProb) {
+    const uint4* p = reinterpret_cast<const uint4*>(a + (g << 5));
+    alo = __ldcg(p); ahi = __ldcg(p + 1);
+  }
+  if (BT == kMapProb) {
+    const uint4* p = reinterpret_cast<const uint4*>(b + (g << 5));
+    blo = __ldg(p); bhi = __ldg(p + 1);
+  }
+  if (AT == kMapProb) hit &= prob_group_mask(alo, ahi, t4);
+  if (BT == kMapProb) hit &= prob_group_mask(blo, bhi, t4);
+  if (hit) resolve_group<AT, BT, MARK, TYPES, false, false>(a, b, g, hit, t4, cnt, acc);  // count + write-back only
+}
+
+// Both sides represented by summaries: 128-bit loads, 128 voxels per load pair and thread. Candidate groups (both
+// summaries have a common bit) are NOT resolved where they are found -- that would put two dependent ~1 us voxel
+// loads into the streaming loop of one lane while its 31 neighbours wait. Each warp appends them to a small queue in
+// shared memory and resolves 32 at a time, one per lane, all loads in flight together.
+constexpr int kQueuePerWarp = 64;
 template <int AT, int BT, bool MARK, bool TYPES>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const uint32_t* __restrict__ occ_a,
                    const uint32_t* __restrict__ occ_b, long long n, int thr, ReduceScratch* scratch, ResultBlock* out_d,
                    ResultBlock* out_h, unsigned long long* count_out_d, PeerReduce pr) {
   constexpr int U = 4;
+  __shared__ long long sh_g[kThreads / 32][kQueuePerWarp];
+  __shared__ uint32_t sh_h[kThreads / 32][kQueuePerWarp];
+  long long* qg = sh_g[threadIdx.x >> 5];
+  uint32_t* qh = sh_h[threadIdx.x >> 5];
+  const unsigned lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  int qn = 0;  // warp-uniform number of queued groups
   uint32_t cnt = 0;
   uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const uint32_t t4 = (uint32_t)(uint8_t)thr * 0x01010101u;
@@ -246,8 +276,14 @@ k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const
   const long long n_quad = n_full >> 2;  // complete 4-group quads (summaries are 16-byte padded and aligned)
   const uint4* qa = reinterpret_cast<const uint4*>(occ_a);
   const uint4* qb = reinterpret_cast<const uint4*>(occ_b);
+  auto drain = [&](int m) {  // the last m (<= 32) queued groups, one per lane
+    __syncwarp();
+    if ((int)lane < m) resolve_entry<AT, BT, MARK, TYPES>(a, b, qg[qn - m + lane], qh[qn - m + lane], t4, cnt, acc);
+    qn -= m;
+    __syncwarp();
+  };
   const long long stride = (long long)gridDim.x * kThreads * U;
-  for (long long base = (long long)blockIdx.x * kThreads * U; base < n_quad; base += stride) {
+  for (long long base = (long long)blockIdx.x * kThreads * U; base < n_quad; base += stride) {  // CTA-uniform trip count
     uint4 ma[U], mb[U];
     bool ok[U];
 #pragma unroll
@@ -258,15 +294,27 @@ k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      if (!ok[u]) continue;
       const long long q = base + u * kThreads + threadIdx.x;
-      const uint32_t h[4] = {ma[u].x & mb[u].x, ma[u].y & mb[u].y, ma[u].z & mb[u].z, ma[u].w & mb[u].w};
-      if ((h[0] | h[1] | h[2] | h[3]) == 0u) continue;
+      uint32_t h[4] = {0u, 0u, 0u, 0u};
+      if (ok[u]) { h[0] = ma[u].x & mb[u].x; h[1] = ma[u].y & mb[u].y; h[2] = ma[u].z & mb[u].z; h[3] = ma[u].w & mb[u].w; }
+      if (!__any_sync(0xffffffffu, (h[0] | h[1] | h[2] | h[3]) != 0u)) continue;
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (h[k]) resolve_group<AT, BT, MARK, TYPES, true, true>(a, b, (q << 2) + k, h[k], t4, cnt, acc);
+      for (int k = 0; k < 4; ++k) {
+        const bool has = h[k] != 0u;
+        const unsigned bal = __ballot_sync(0xffffffffu, has);
+        if (!bal) continue;
+        if (qn > kQueuePerWarp - 32) drain(32);
+        if (has) {
+          const int pos = qn + __popc(bal & lt);
+          qg[pos] = (q << 2) + k;
+          qh[pos] = h[k];
+        }
+        qn += __popc(bal);
+      }
     }
+    while (qn >= 32) drain(32);
   }
+  while (qn > 0) drain(qn < 32 ? qn : 32);
   // up to 3 complete groups after the last quad
   if (blockIdx.x == 0 && threadIdx.x < (n_full & 3)) {
     const long long g = (n_quad << 2) + threadIdx.x;
