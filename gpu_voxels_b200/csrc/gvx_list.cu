@@ -159,59 +159,81 @@ k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxel
   }
   uint32_t cnt = 0;
   uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  const unsigned long long stride = (unsigned long long)gridDim.x * kThreads;
-  for (unsigned long long i = (unsigned long long)blockIdx.x * kThreads + threadIdx.x; i < size; i += stride) {
-    const long long j = (long long)__ldg(ids + i) + off;
-    if (j < 0 || j >= n_total) continue;                   // pointer range test of the reference (:139-140)
-    if (j < map_first || j >= map_first + map_n) continue;  // another z-slab's voxel
-    bool hit_map;
-    if (MAPT == kMapProb) {
-      if (occ != nullptr) {  // "known" summary: an UNKNOWN voxel never collides, skip its byte
-        const long long v = j - map_first;
-        if (!((__ldg(occ + (v >> 5)) >> (v & 31)) & 1u)) continue;
+  // U entries per thread and step in three stages -- ids, then the map probe of every entry, then the (rare) hits --
+  // so that a thread has U independent gathers in flight instead of one dependent id -> map -> list-voxel chain
+  constexpr int U = 8;
+  const unsigned long long stride = (unsigned long long)gridDim.x * kThreads * U;
+  for (unsigned long long base = (unsigned long long)blockIdx.x * kThreads * U; base < size; base += stride) {
+    long long v[U];  // index into this slab's part of the map, < 0: skip
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const unsigned long long i = base + (unsigned long long)u * kThreads + threadIdx.x;
+      v[u] = -1;
+      if (i < size) {
+        const long long j = (long long)__ldg(ids + i) + off;
+        // pointer range test of the reference (:139-140); then: another z-slab's voxel
+        if (j >= 0 && j < n_total && j >= map_first && j < map_first + map_n) v[u] = j - map_first;
       }
-      const int p = (int)ld_stream_i8(map + (j - map_first));
-      hit_map = (MODE == 0 || MODE == 3) ? (p >= thr_i) : ((float)p >= thr_f);
-    } else if (occ != nullptr) {  // occupancy summary of the map: one bit instead of a 32-byte voxel
-      const long long v = j - map_first;
-      hit_map = (__ldg(occ + (v >> 5)) >> (v & 31)) & 1u;
-    } else {
-      hit_map = bit_occupied(ld_voxel_stream(map + (size_t)(j - map_first) * kBitVoxelBytes));
     }
-    if (!hit_map) continue;
-    uint8_t* lp = voxels + (size_t)i * kBitVoxelBytes;
-    const BitVoxelWords lv = ld_voxel(lp);
-    bool hit;
-    if (MODE == 0 || MODE == 3) {
-      hit = bit_occupied(lv);
-    } else if (MODE == 2) {
-      uint32_t any = 0;
+    uint32_t sw[U];
+    if (occ != nullptr) {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) any |= lv.w[k] & mask_in.w[k];
-      hit = any != 0u;
-    } else {
-      hit = true;
+      for (int u = 0; u < U; ++u) sw[u] = v[u] >= 0 ? __ldg(occ + (v[u] >> 5)) : 0u;
     }
-    if (!hit) continue;
-    if (MODE == 1) {
+    bool hit_map[U];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) acc[k] |= lv.w[k];
+    for (int u = 0; u < U; ++u) {
+      hit_map[u] = false;
+      if (v[u] < 0) continue;
+      if (MAPT == kMapProb) {
+        // "known" summary: an UNKNOWN voxel never collides, skip its byte
+        if (occ != nullptr && !((sw[u] >> (v[u] & 31)) & 1u)) continue;
+        const int p = (int)ld_stream_i8(map + v[u]);
+        hit_map[u] = (MODE == 0 || MODE == 3) ? (p >= thr_i) : ((float)p >= thr_f);
+      } else if (occ != nullptr) {  // occupancy summary of the map: one bit instead of a 32-byte voxel
+        hit_map[u] = (sw[u] >> (v[u] & 31)) & 1u;
+      } else {
+        hit_map[u] = bit_occupied(ld_voxel_stream(map + (size_t)v[u] * kBitVoxelBytes));
+      }
     }
-    if (MODE == 3) {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        uint32_t w = lv.w[k];
-        cnt += __popc(w);
-        while (w) {
-          const int b = __ffs(w) - 1;
-          w &= w - 1;
-          atomicAdd(&sh_hist[k * 32 + b], 1u);
+    for (int u = 0; u < U; ++u) {
+      if (!hit_map[u]) continue;
+      const unsigned long long i = base + (unsigned long long)u * kThreads + threadIdx.x;
+      uint8_t* lp = voxels + (size_t)i * kBitVoxelBytes;
+      const BitVoxelWords lv = ld_voxel(lp);
+      bool hit;
+      if (MODE == 0 || MODE == 3) {
+        hit = bit_occupied(lv);
+      } else if (MODE == 2) {
+        uint32_t any = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) any |= lv.w[k] & mask_in.w[k];
+        hit = any != 0u;
+      } else {
+        hit = true;
+      }
+      if (!hit) continue;
+      if (MODE == 1) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] |= lv.w[k];
+      }
+      if (MODE == 3) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          uint32_t w = lv.w[k];
+          cnt += __popc(w);
+          while (w) {
+            const int b = __ffs(w) - 1;
+            w &= w - 1;
+            atomicAdd(&sh_hist[k * 32 + b], 1u);
+          }
         }
+      } else {
+        ++cnt;
       }
-    } else {
-      ++cnt;
+      if (MARK && !(lv.w[0] & 4u)) *(uint32_t*)lp = lv.w[0] | 4u;  // list voxel .insert(eBVM_COLLISION)
     }
-    if (MARK && !(lv.w[0] & 4u)) *(uint32_t*)lp = lv.w[0] | 4u;  // list voxel .insert(eBVM_COLLISION)
   }
   if (MODE == 3) {
     __syncthreads();
@@ -243,7 +265,7 @@ cudaError_t launch_collide_list_map(const LaunchCtx& c, int mode, const uint32_t
                                     const uint32_t mask_in8[8], unsigned long long* count_out_d, const uint32_t* occ) {
   BitVoxelWords mk;
   for (int k = 0; k < 8; ++k) mk.w[k] = mask_in8 ? mask_in8[k] : 0u;
-  unsigned long long work = (size + kThreads * 4 - 1) / (kThreads * 4);
+  unsigned long long work = (size + kThreads * 8 - 1) / (kThreads * 8);
   const unsigned long long max_grid = (unsigned long long)(c.sm_count * 4 < kMaxGrid ? c.sm_count * 4 : kMaxGrid);
   const int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));
   const uint8_t* map = (const uint8_t*)map_;
