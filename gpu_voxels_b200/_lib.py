@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgvx.so")
 
 GVX_OK = 0
-ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED, ERR_DIM_MISMATCH, ERR_NOT_INITIALIZED = 1, 2, 3, 4, 5, 6
+ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED, ERR_DIM_MISMATCH, ERR_NOT_INITIALIZED, ERR_IO = 1, 2, 3, 4, 5, 6, 7
 MEM_HOST, MEM_DEVICE = 0, 1
 
 u64, u32, i32, f32, vp = C.c_uint64, C.c_uint32, C.c_int32, C.c_float, C.c_void_p
@@ -76,6 +76,17 @@ SIGNATURES = {
     "gvx_collide_list_map_types": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),
     "gvx_collide_list_map_mask": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),
     "gvx_collide_list_map_per_meaning": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),
+    "gvx_collide_list_list": (C.c_int, [u64, u64, P(u64)]),
+    "gvx_collide_list_list_types": (C.c_int, [u64, u64, vp, P(u64)]),
+    "gvx_collide_list_list_bitcheck": (C.c_int, [u64, u64, u32, P(u64)]),
+    "gvx_collide_list_list_per_meaning": (C.c_int, [u64, u64, vp, P(u64)]),
+    "gvx_list_subtract": (C.c_int, [u64, u64]),
+    "gvx_list_equals": (C.c_int, [u64, u64, P(C.c_int)]),
+    "gvx_list_shift_sv_ids": (C.c_int, [u64, u32]),
+    "gvx_map_write_file": (C.c_int, [u64, C.c_char_p]),
+    "gvx_map_read_file": (C.c_int, [u64, C.c_char_p]),
+    "gvx_list_write_file": (C.c_int, [u64, C.c_char_p]),
+    "gvx_list_read_file": (C.c_int, [u64, C.c_char_p]),
     "gvx_batch_robot_collide": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, vp, u32, vp, f32, vp]),
     "gvx_batch_robot_collide_dh": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, vp, vp, u32, vp, vp, u32, vp, f32, vp]),
     "gvx_dh_chain_transforms": (C.c_int, [vp, vp, u32, vp, u32, vp, vp]),

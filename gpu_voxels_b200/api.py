@@ -190,6 +190,19 @@ class GpuVoxelsMap:
         bits = np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool)
         return bits, bool(valid.value)
 
+    # -- files (GV/voxelmap/TemplateVoxelMap.hpp:666-799): False + a logged error on failure, like the reference
+    def writeToDisk(self, path):
+        rc = self._L.gvx_map_write_file(self.handle, str(path).encode())
+        if rc != 0:
+            _log_error(self._L.gvx_last_error().decode())
+        return rc == 0
+
+    def readFromDisk(self, path):
+        rc = self._L.gvx_map_read_file(self.handle, str(path).encode())
+        if rc != 0:
+            _log_error(self._L.gvx_last_error().decode())
+        return rc == 0
+
     # -- clearing
     def clearMap(self):
         _lib.check(self._L.gvx_map_clear(self.handle))

@@ -134,6 +134,38 @@ int list_collide(int mode, gvx_handle_t hl, gvx_handle_t hm, float thr, const in
   return GVX_OK;
 }
 
+// list x list: both handles, same reference dimensions, no offset (the reference refuses offsets between lists:
+// "Offset for VoxelList operation not supported", BitVoxelList.hpp:413-417)
+int list_list_prepare(gvx_handle_t ha, gvx_handle_t hb, VoxList** a, VoxList** b) {
+  *a = find_list(ha);
+  *b = find_list(hb);
+  if (!*a || !*b) return fail(GVX_ERR_INVALID, "unknown list handle");
+  if ((*a)->dx != (*b)->dx || (*a)->dy != (*b)->dy || (*a)->dz != (*b)->dz)
+    return fail(GVX_ERR_DIM_MISMATCH, "lists have different reference dimensions");
+  return GVX_OK;
+}
+
+int list_list(int mode, gvx_handle_t ha, gvx_handle_t hb, uint32_t margin, uint8_t* types_out32, uint64_t* counts256,
+              uint64_t* count) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList *a, *b;
+  int rc = list_list_prepare(ha, hb, &a, &b);
+  if (rc) return rc;
+  if (margin > 31) return fail(GVX_ERR_INVALID, "window size %u: the reference's 64-bit window supports at most 31", margin);
+  if (count) *count = 0;
+  if (mode == 1 && types_out32) memset(types_out32, 0, 32);  // types_in_collision is assigned, not OR-ed (:122)
+  if (mode == 3 && counts256) memset(counts256, 0, 256 * sizeof(uint64_t));
+  if (a->size == 0 || b->size == 0) return GVX_OK;
+  GVX_CUDA(launch_list_list(lctx(), mode, a->ids[a->cur], a->voxels[a->cur], a->size, b->ids[b->cur], b->voxels[b->cur],
+                            b->size, margin, nullptr));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (count) *count = g.result_h->count;
+  if (mode == 1 && types_out32) memcpy(types_out32, g.result_h->mask, 32);
+  if (mode == 3 && counts256) memcpy(counts256, g.result_h->per_meaning, 256 * sizeof(uint64_t));
+  return GVX_OK;
+}
+
 }  // namespace
 
 namespace gvx {
@@ -338,6 +370,68 @@ int gvx_collide_list_map_allreduce(gvx_handle_t hl, gvx_handle_t hm, float thr, 
     *count = g.result_h->count;
     if (*count == ~0ull) return fail(GVX_ERR_CUDA, "peer all-reduce timed out: a rank did not arrive");
   }
+  return GVX_OK;
+}
+
+int gvx_collide_list_list(gvx_handle_t a, gvx_handle_t b, uint64_t* count) {
+  return list_list(0, a, b, 0, nullptr, nullptr, count);
+}
+int gvx_collide_list_list_types(gvx_handle_t a, gvx_handle_t b, uint8_t types_out32[GVX_BITVOXEL_BYTES], uint64_t* count) {
+  return list_list(1, a, b, 0, types_out32, nullptr, count);
+}
+int gvx_collide_list_list_bitcheck(gvx_handle_t a, gvx_handle_t b, uint32_t margin, uint64_t* count) {
+  return list_list(2, a, b, margin, nullptr, nullptr, count);
+}
+int gvx_collide_list_list_per_meaning(gvx_handle_t a, gvx_handle_t b, uint64_t counts256[256], uint64_t* total) {
+  return list_list(3, a, b, 0, nullptr, counts256, total);
+}
+
+int gvx_list_subtract(gvx_handle_t ha, gvx_handle_t hb) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList *a, *b;
+  int rc = list_list_prepare(ha, hb, &a, &b);
+  if (rc) return rc;
+  if (a->size == 0 || b->size == 0) return GVX_OK;
+  if (a == b) { a->size = 0; return GVX_OK; }
+  const int nxt = a->cur ^ 1;
+  if ((rc = list_reserve(*a, nxt, a->size))) return rc;
+  if ((rc = list_reserve_scratch(*a, a->size, 0))) return rc;
+  GVX_CUDA(launch_list_list(lctx(), 4, a->ids[a->cur], a->voxels[a->cur], a->size, b->ids[b->cur], b->voxels[b->cur],
+                            b->size, 0, a->keys_in));
+  GVX_CUDA(launch_exclusive_sum(lctx(), a->keys_in, a->keys_out, a->size, a->tmp, a->tmp_bytes));
+  GVX_CUDA(launch_list_compact(lctx(), a->ids[a->cur], a->coords[a->cur], a->voxels[a->cur], a->size, a->keys_in,
+                               a->keys_out, a->ids[nxt], a->coords[nxt], a->voxels[nxt]));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  a->size -= g.result_h->count;  // the stencil kernel counted the overlapping entries
+  a->cur = nxt;
+  return GVX_OK;
+}
+
+int gvx_list_equals(gvx_handle_t ha, gvx_handle_t hb, int* equal) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* a = find_list(ha);
+  VoxList* b = find_list(hb);
+  if (!a || !b || !equal) return fail(GVX_ERR_INVALID, "unknown list handle or null result");
+  *equal = 0;
+  if (a->dx != b->dx || a->dy != b->dy || a->dz != b->dz || a->side != b->side || a->size != b->size) return GVX_OK;
+  if (a->size == 0 || a == b) { *equal = 1; return GVX_OK; }
+  GVX_CUDA(launch_list_diff(lctx(), a->ids[a->cur], a->coords[a->cur], a->voxels[a->cur], b->ids[b->cur],
+                            b->coords[b->cur], b->voxels[b->cur], a->size));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  *equal = g.result_h->count == 0;
+  return GVX_OK;
+}
+
+int gvx_list_shift_sv_ids(gvx_handle_t h, uint32_t shift) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* l = find_list(h);
+  if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
+  if (shift > 56) return fail(GVX_ERR_INVALID, "Maximum shift size is 56! Higher shift number requested. Not performing shift operation.");
+  if (l->size == 0) return GVX_OK;
+  GVX_CUDA(launch_shift_sv_ids(lctx(), l->voxels[l->cur], l->size, shift, nullptr));
   return GVX_OK;
 }
 

@@ -80,6 +80,18 @@ cudaError_t launch_collide_list_map(const LaunchCtx& c, int mode, const uint32_t
                                     const uint32_t mask_in8[8], unsigned long long* count_out_d,
                                     const uint32_t* occ = nullptr);
 
+// list x list (gvx_listlist.cu): mode 0 count of common ids, 1 + OR of both voxels, 2 bit check with margin,
+// 3 per-meaning histogram of a's voxels, 4 keep_d[i] = (a's id i is NOT in b). Results in the result block.
+cudaError_t launch_list_list(const LaunchCtx& c, int mode, const uint32_t* a_ids, const void* a_vox, uint64_t na,
+                             const uint32_t* b_ids, const void* b_vox, uint64_t nb, uint32_t margin, uint32_t* keep_d);
+cudaError_t launch_exclusive_sum(const LaunchCtx& c, const uint32_t* in_d, uint32_t* out_d, uint64_t n, void* tmp,
+                                 size_t tmp_bytes);
+cudaError_t launch_list_compact(const LaunchCtx& c, const uint32_t* ids, const uint32_t* coords, const void* vox,
+                                uint64_t n, const uint32_t* keep_d, const uint32_t* pos_d, uint32_t* o_ids,
+                                uint32_t* o_coords, void* o_vox);
+cudaError_t launch_list_diff(const LaunchCtx& c, const uint32_t* a_ids, const uint32_t* a_co, const void* a_vox,
+                             const uint32_t* b_ids, const uint32_t* b_co, const void* b_vox, uint64_t n);
+
 // batch of robot configurations vs one environment map (gvx_batch.cu)
 struct BatchDesc {
   const uint32_t* prefix_d;    // n_clouds + 1 exclusive prefix of the link cloud sizes

@@ -113,6 +113,13 @@ size_t list_sort_temp_bytes(uint64_t n) {
   return a > b ? a : b;
 }
 
+// out[i] = sum of in[0, i) (CUB, library), tmp >= list_sort_temp_bytes(n)
+cudaError_t launch_exclusive_sum(const LaunchCtx& c, const uint32_t* in_d, uint32_t* out_d, uint64_t n, void* tmp,
+                                 size_t tmp_bytes) {
+  ++*c.launches;
+  return cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, in_d, out_d, (long long)n, c.stream);
+}
+
 cudaError_t launch_list_build(const LaunchCtx& c, const ListBuild& b) {
   const unsigned long long total = b.old_size + b.n_new;
   if (total == 0) return cudaSuccess;

@@ -100,11 +100,65 @@ class BitVectorVoxelList:
         _lib.check(rc)
         return cnt.value
 
+    # -- list x list (GV/voxellist/BitVoxelList.hpp:86-125,267-344; offsets between lists are not supported there)
+    def _list_call(self, fn, other, offset, *extra):
+        if offset is not None and any(int(v) != 0 for v in offset):
+            _log_error("Offset for VoxelList collision not supported! Not performing collision check.")
+            return 0
+        cnt = C.c_uint64(0)
+        rc = fn(self.handle, other.handle, *extra, C.byref(cnt))
+        if rc == _lib.ERR_DIM_MISMATCH:
+            _log_error(self._L.gvx_last_error().decode())
+            return SSIZE_MAX
+        _lib.check(rc)
+        return cnt.value
+
+    def collideWithBitcheck(self, other, margin=0, offset=None):
+        """BitVoxelList::collideWithBitcheck(BitVectorVoxelList*, margin), GV/voxellist/BitVoxelList.hpp:267-296"""
+        return self._list_call(self._L.gvx_collide_list_list_bitcheck, other, offset, int(margin))
+
+    def subtract(self, other):
+        """TemplateVoxelList::subtract, GV/voxellist/TemplateVoxelList.hpp:609-641"""
+        _lib.check(self._L.gvx_list_subtract(self.handle, other.handle))
+        return True
+
+    def equals(self, other):
+        eq = C.c_int(0)
+        _lib.check(self._L.gvx_list_equals(self.handle, other.handle, C.byref(eq)))
+        return bool(eq.value)
+
+    def shiftLeftSweptVolumeIDs(self, shift_size):
+        """GV/voxellist/BitVoxelList.hpp:560-582: more than 56 bits is logged and nothing happens"""
+        rc = self._L.gvx_list_shift_sv_ids(self.handle, int(shift_size))
+        if rc == _lib.ERR_INVALID and shift_size > 56:
+            _log_error(self._L.gvx_last_error().decode())
+            return
+        _lib.check(rc)
+
+    def writeToDisk(self, path):
+        """GV/voxellist/TemplateVoxelList.hpp:444-478"""
+        rc = self._L.gvx_list_write_file(self.handle, str(path).encode())
+        if rc != 0:
+            _log_error(self._L.gvx_last_error().decode())
+        return rc == 0
+
+    def readFromDisk(self, path):
+        """GV/voxellist/TemplateVoxelList.hpp:480-526"""
+        rc = self._L.gvx_list_read_file(self.handle, str(path).encode())
+        if rc != 0:
+            _log_error(self._L.gvx_last_error().decode())
+        return rc == 0
+
     def collideWith(self, other, coll_threshold=1.0, offset=None, mark=True):
+        if isinstance(other, BitVectorVoxelList):
+            return self._list_call(self._L.gvx_collide_list_list, other, offset)
         return self._call(self._L.gvx_collide_list_map, other, coll_threshold, offset, mark)
 
     def collideWithTypes(self, other, types_in_collision, coll_threshold=1.0, offset=None, mark=True):
         """types_in_collision (BitVectorVoxel) is cleared, then receives the OR of the colliding list voxels"""
+        if isinstance(other, BitVectorVoxelList):
+            return self._list_call(self._L.gvx_collide_list_list_types, other, offset,
+                                   types_in_collision.bytes.ctypes.data_as(C.c_void_p))
         return self._call(self._L.gvx_collide_list_map_types, other, coll_threshold, offset, mark,
                           types_in_collision.bytes.ctypes.data_as(C.c_void_p))
 
@@ -117,8 +171,12 @@ class BitVectorVoxelList:
     def collideCountingPerMeaning(self, other, collisions_per_meaning=None, coll_threshold=1.0, offset=None, mark=True):
         """-> (total, counts[256]); semantics of GV/voxellist/BitVoxelList.hpp:300-344 for list x map"""
         counts = np.zeros(256, np.uint64)
-        total = self._call(self._L.gvx_collide_list_map_per_meaning, other, coll_threshold, offset, mark,
-                           counts.ctypes.data_as(C.c_void_p))
+        if isinstance(other, BitVectorVoxelList):
+            total = self._list_call(self._L.gvx_collide_list_list_per_meaning, other, offset,
+                                    counts.ctypes.data_as(C.c_void_p))
+        else:
+            total = self._call(self._L.gvx_collide_list_map_per_meaning, other, coll_threshold, offset, mark,
+                               counts.ctypes.data_as(C.c_void_p))
         if collisions_per_meaning is not None:
             collisions_per_meaning[:] = counts
         return total, counts

@@ -44,7 +44,8 @@ enum gvx_status {
   GVX_ERR_NOMEM = 3,
   GVX_ERR_UNSUPPORTED = 4,  /* e.g. meaning != eBVM_OCCUPIED into a ProbVoxelMap, offset on a slab map */
   GVX_ERR_DIM_MISMATCH = 5, /* list x map with different reference dimensions (reference returns SSIZE_MAX) */
-  GVX_ERR_NOT_INITIALIZED = 6
+  GVX_ERR_NOT_INITIALIZED = 6,
+  GVX_ERR_IO = 7            /* file cannot be opened, is truncated, or the write was short */
 };
 
 /* values of the reference's MapType enum (GV/helpers/common_defines.h:59-73); also the on-disk tag */
@@ -280,6 +281,39 @@ int gvx_collide_list_map_mask(gvx_handle_t list, gvx_handle_t map, float thr, co
  * colliding list voxel adds 1 to counts256[j] and to *total. */
 int gvx_collide_list_map_per_meaning(gvx_handle_t list, gvx_handle_t map, float thr, const int32_t off3[3], int mark,
                                      uint64_t counts256[256], uint64_t* total);
+
+/* ---- list x list (offsets between lists are refused by the reference, BitVoxelList.hpp:413-417; none here) ---- */
+/* BitVoxelList::collideWith(BitVectorVoxelList*) (GV/voxellist/BitVoxelList.hpp:86-99 -> collideVoxellists,
+ * GV/voxellist/TemplateVoxelList.hpp:227-282): the number of entries of `a` whose voxel id is also in `b` */
+int gvx_collide_list_list(gvx_handle_t a, gvx_handle_t b, uint64_t* count);
+/* collideWithTypes(BitVectorVoxelList*) (BitVoxelList.hpp:101-125): types_out32 = OR over the matching pairs of
+ * (a's voxel | b's voxel) -- assigned, not accumulated -- and the number of matching entries */
+int gvx_collide_list_list_types(gvx_handle_t a, gvx_handle_t b, uint8_t types_out32[GVX_BITVOXEL_BYTES], uint64_t* count);
+/* collideWithBitcheck(BitVectorVoxelList*, margin) (BitVoxelList.hpp:267-296): matching pairs with a common bit
+ * (margin 0: BitvectorCollision, ALL bits) or passing bitMarginCollisionCheck(a, b, margin, 0) (margin 1..31);
+ * reference test GV/test/testing_voxellist.cu:412-460 */
+int gvx_collide_list_list_bitcheck(gvx_handle_t a, gvx_handle_t b, uint32_t margin, uint64_t* count);
+/* collideCountingPerMeaning(list) (BitVoxelList.hpp:299-344; tests testing_voxellist.cu:44-107,341-410): every set bit j
+ * of a matching entry OF `a` adds one to counts256[j] and to *total */
+int gvx_collide_list_list_per_meaning(gvx_handle_t a, gvx_handle_t b, uint64_t counts256[256], uint64_t* total);
+/* TemplateVoxelList::subtract (GV/voxellist/TemplateVoxelList.hpp:609-641; test testing_voxellist.cu:541-572): removes
+ * from `a` every entry whose voxel id is in `b` */
+int gvx_list_subtract(gvx_handle_t a, gvx_handle_t b);
+/* TemplateVoxelList::equals (TemplateVoxelList.hpp:806-825): same dimensions, side, size, ids, coordinates and voxels */
+int gvx_list_equals(gvx_handle_t a, gvx_handle_t b, int* equal);
+/* BitVoxelList::shiftLeftSweptVolumeIDs (GV/voxellist/BitVoxelList.hpp:560-582) */
+int gvx_list_shift_sv_ids(gvx_handle_t list, uint32_t shift);
+
+/* ---- files: the reference's binary formats, readable and writable both ways ------------------------------------ */
+/* TemplateVoxelMap::writeToDisk / readFromDisk (GV/voxelmap/TemplateVoxelMap.hpp:666-799): int32 MapType, float side,
+ * 3 x uint32 dims, raw voxels. Reading checks type and dimensions (a different side length is only a warning there
+ * and is accepted here). Whole maps only. */
+int gvx_map_write_file(gvx_handle_t h, const char* path);
+int gvx_map_read_file(gvx_handle_t h, const char* path);
+/* TemplateVoxelList::writeToDisk / readFromDisk (GV/voxellist/TemplateVoxelList.hpp:444-526; test
+ * testing_voxellist.cu:503-539): int32 MapType, 3 x uint32 dims, float side, uint32 n, ids, coords, voxels */
+int gvx_list_write_file(gvx_handle_t h, const char* path);
+int gvx_list_read_file(gvx_handle_t h, const char* path);
 
 /* ---- batch of robot configurations -------------------------------------------------------------------- */
 /* n_cfg times the planner's state check (gvl_ompl_planning/gvl_ompl_planner_helper.cpp:169-202): clearMap(robot);

@@ -206,6 +206,70 @@ class VoxelList:
         return cnt.value, mask_out, per
 
 
+# ---- list x list (numpy restatement) --------------------------------------------------------------------------
+def _matching(a, b):
+    """findMatchingVoxels, GV/voxellist/BitVoxelList.hpp:408-508: indices (into a, into b) of the entries whose voxel id
+    is in both lists (ids are sorted and unique in each list)"""
+    _, ia, ib = np.intersect1d(a.ids, b.ids, assume_unique=True, return_indices=True)
+    return ia, ib
+
+
+def list_collide_list(a, b):
+    """BitVoxelList::collideWith(BitVectorVoxelList*), BitVoxelList.hpp:86-99: ids of a found in b"""
+    return int(np.isin(a.ids, b.ids, assume_unique=True).sum())
+
+
+def list_collide_list_types(a, b):
+    """collideWithTypes(list), BitVoxelList.hpp:101-125 -> (count, OR over matching pairs of (va | vb))"""
+    ia, ib = _matching(a, b)
+    t = np.zeros(32, np.uint8)
+    if len(ia):
+        t = np.bitwise_or.reduce(a.voxels[ia] | b.voxels[ib], axis=0)
+    return len(ia), t
+
+
+def list_collide_list_bitcheck(a, b, margin):
+    """collideWithBitcheck(list, margin), BitVoxelList.hpp:267-296: BitvectorCollision (margin 0, all bits) or
+    BitvectorCollisionWithBitshift(margin, 0) (BitVoxelList.h:40-73) on every matching pair"""
+    ia, ib = _matching(a, b)
+    if margin == 0:
+        return int((a.voxels[ia] & b.voxels[ib]).any(axis=1).sum())
+    return sum(bit_margin_check(a.voxels[i], b.voxels[j], margin, 0)[0] for i, j in zip(ia, ib))
+
+
+def list_collide_list_per_meaning(a, b):
+    """collideCountingPerMeaning(list), BitVoxelList.hpp:299-344 -> (total, counts[256]) over a's matching voxels"""
+    ia, _ = _matching(a, b)
+    bits = np.unpackbits(a.voxels[ia], axis=1, bitorder="little") if len(ia) else np.zeros((0, 256), np.uint8)
+    counts = bits.sum(axis=0).astype(np.uint64)
+    return int(counts.sum()), counts
+
+
+def list_subtract(a, b):
+    """TemplateVoxelList::subtract, TemplateVoxelList.hpp:609-641: a loses the entries whose id is in b"""
+    keep = ~np.isin(a.ids, b.ids, assume_unique=True)
+    a.ids, a.coords, a.voxels = a.ids[keep].copy(), a.coords[keep].copy(), a.voxels[keep].copy()
+
+
+def list_shift(a, shift):
+    """BitVoxelList::shiftLeftSweptVolumeIDs, BitVoxelList.hpp:560-582"""
+    for k in range(len(a.voxels)):
+        a.voxels[k] = shift_left(a.voxels[k], shift)
+
+
+def list_file_bytes(a):
+    """TemplateVoxelList::writeToDisk, TemplateVoxelList.hpp:444-478, as bytes"""
+    import struct
+    return (struct.pack("<i3IfI", 1, int(a.dims[0]), int(a.dims[1]), int(a.dims[2]), np.float32(a.side), len(a.ids))
+            + a.ids.astype("<u4").tobytes() + a.coords.astype("<u4").tobytes() + a.voxels.tobytes())
+
+
+def map_file_bytes(m, map_type, dims, side):
+    """TemplateVoxelMap::writeToDisk (bin_mode), GV/voxelmap/TemplateVoxelMap.hpp:666-716, as bytes"""
+    import struct
+    return struct.pack("<if3I", int(map_type), np.float32(side), int(dims[0]), int(dims[1]), int(dims[2])) + m.tobytes()
+
+
 def batch_robot_collide(env, env_type, dims, side, base_xyz, cloud_sizes, meanings, transforms, mask=None, thr=1.0):
     base_xyz = _f32(base_xyz).reshape(-1, 3)
     cs = np.asarray(cloud_sizes, np.uint32)

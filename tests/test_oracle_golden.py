@@ -195,3 +195,52 @@ def test_bitvoxelmap_bitshift(oracle):
         cnt, _ = oracle.collide_bitcheck(m1, m2, N, 1, 0, True)
         assert cnt == (len(pts) if shift <= shift_start else 0), shift
     assert not oracle.shift_map(m2, N, 57)
+
+
+def _olist(oracle, side=1.0):
+    return oracle.VoxelList(DIMS, side)
+
+
+def test_list_list_countingpermeaning(oracle):
+    """GV/test/testing_voxellist.cu:44-107: "(14|1) (15|8) (16|8) (17|27) (18|27) (19|27) (20|8) (21|1) (22|1)", 108"""
+    obstacle, swept = _olist(oracle), _olist(oracle)
+    obstacle.insert_points(oracle.create_box_of_points((8, 8, 8), (11, 11, 11), 0.1), 1)
+    clouds, meanings = [], []
+    for i in range(50):
+        p = np.float32(np.float32(np.float32(30) * np.float32(0.02)) * np.float32(i)) + np.float32(0)
+        clouds.append(oracle.create_box_of_points((p, p, p), (np.float32(p + np.float32(2.5)),) * 3, 0.1))
+        meanings.append(SV_START + i)
+    swept.insert_meta(np.concatenate(clouds), [len(c) for c in clouds], meanings)
+    total, counts = oracle.list_collide_list_per_meaning(swept, obstacle)
+    got = " ".join("(%d|%d)" % (i, counts[i]) for i in range(256) if counts[i] > 0)
+    assert got == "(14|1) (15|8) (16|8) (17|27) (18|27) (19|27) (20|8) (21|1) (22|1)" and total == 108
+
+
+def test_list_list_find_matching_voxels(oracle):
+    """GV/test/testing_voxellist.cu:341-410"""
+    l1, l2 = _olist(oracle, 0.01), _olist(oracle, 0.01)
+    cp = [np.array([[np.float32(j / float(n) * 5.0), y, 1.0] for j in range(n)], np.float32) for n, y in ((40, 1.0), (30, 2.0), (20, 3.0))]
+    l1.insert_points(oracle.create_box_of_points((2.1, 0.1, 5.1), (4.9, 4.9, 9.9), 0.02), 10)
+    l2.insert_points(oracle.create_box_of_points((5.1, 5.1, 10.1), (9.9, 9.9, 14.9), 0.3), 20)
+    for c, m1, m2 in zip(cp, (11, 12, 13), (21, 22, 23)):
+        l1.insert_points(c, m1); l2.insert_points(c, m2)
+    n, c = oracle.list_collide_list_per_meaning(l1, l2)
+    assert n == 90 and (c[11], c[12], c[13]) == (40, 30, 20) and c[21] == c[10] == 0
+    n, c = oracle.list_collide_list_per_meaning(l2, l1)
+    assert n == 90 and (c[21], c[22], c[23]) == (40, 30, 20) and c[11] == c[20] == 0
+
+
+def test_list_list_bitshift_collision_and_subtract(oracle):
+    """GV/test/testing_voxellist.cu:412-460 (window 1 after shifting) and :541-572 (27 + 27 boxes, 8 shared -> 19)"""
+    pts = np.array([[0.3, 0.3, 0.3]], np.float32)
+    for shift in range(0, 50 + SV_START - 5):
+        m1, m2 = _olist(oracle), _olist(oracle)
+        m2.insert_points(pts, SV_START + 50)
+        m1.insert_points(pts, SV_START + 50 - shift)
+        oracle.list_shift(m2, shift)
+        assert oracle.list_collide_list_bitcheck(m1, m2, 1) == (1 if shift <= 50 else 0), shift
+    l1, l2 = _olist(oracle), _olist(oracle)
+    l1.insert_points(oracle.create_box_of_points((1.1, 1.1, 1.1), (3.9, 3.9, 3.9), 0.1), 11)
+    l2.insert_points(oracle.create_box_of_points((2.1, 2.1, 2.1), (4.9, 4.9, 4.9), 0.1), 12)
+    oracle.list_subtract(l1, l2)
+    assert len(l1) == 19
