@@ -2,8 +2,10 @@
 // (GV/GpuVoxels.h:91-415, GV/GpuVoxels.cpp:33-78,164-313,443-559,594-609), header-only over the C ABI (include/gvx.h).
 // Source-compatible for: getInstance, initialize, addMap, delMap, getMap, clearMap x2, insertPointCloudIntoMap x2,
 // insertMetaPointCloudIntoMap x2, insertBoxIntoMap, getDimensions x2, getVoxelSideLength; the returned maps provide
-// collideWith / collideWithTypes / collideWithTypeMask. Visualisation, robots, octrees, distance maps, primitive arrays
-// and file loaders are outside this build.
+// collideWith / collideWithTypes / collideWithTypeMask / collideWithBitcheck, the swept-volume shift and the file
+// formats; DH-chain robots (addRobot with a MetaPointCloud, setRobotConfiguration, insertRobotIntoMap). Visualisation,
+// URDF robots, octrees, distance maps, primitive arrays and point-cloud file loaders are outside this build
+// (SURVEY.md section 8).
 #ifndef GPU_VOXELS_B200_GPUVOXELS_H
 #define GPU_VOXELS_B200_GPUVOXELS_H
 
@@ -14,6 +16,7 @@
 
 #include <gpu_voxels/GpuVoxelsMap.h>
 #include <gpu_voxels/helpers/GeometryGeneration.h>
+#include <gpu_voxels/robot/dh_robot/KinematicChain.h>
 #include <gpu_voxels/voxellist/VoxelList.h>
 #include <gpu_voxels/voxelmap/VoxelMap.h>
 
@@ -32,7 +35,7 @@ typedef ManagedMaps::iterator ManagedMapsIterator;
 class GpuVoxels
 {
 public:
-  ~GpuVoxels() { m_managed_maps.clear(); }
+  ~GpuVoxels() { m_managed_robots.clear(); m_managed_maps.clear(); }
 
   // one shared instance as long as somebody holds it (weak_ptr singleton, GV/GpuVoxels.cpp:67-78)
   static GpuVoxelsSharedPtr getInstance()
@@ -192,6 +195,101 @@ public:
     return true;
   }
 
+  // ---- robots (DH chains; GV/GpuVoxels.cpp addRobot / getRobot / setRobotConfiguration / insertRobotIntoMap) ----
+  bool addRobot(const std::string& robot_name, const std::vector<std::string>& link_names,
+                const std::vector<robot::DHParameters>& dh_params, const MetaPointCloud& pointclouds)
+  {
+    if (m_managed_robots.find(robot_name) != m_managed_robots.end())
+    {
+      LOGGING_ERROR_C(Gpu_voxels, GpuVoxels, "Robot with name '" << robot_name << "' already exists." << endl);
+      return false;
+    }
+    m_managed_robots[robot_name] = RobotInterfaceSharedPtr(new robot::KinematicChain(link_names, dh_params, pointclouds));
+    return true;
+  }
+  RobotInterfaceSharedPtr getRobot(const std::string& rob_name)
+  {
+    ManagedRobots::iterator it = m_managed_robots.find(rob_name);
+    if (it == m_managed_robots.end())
+    {
+      LOGGING_ERROR_C(Gpu_voxels, GpuVoxels, "Could not find robot '" << rob_name << "'" << endl);
+      return RobotInterfaceSharedPtr();
+    }
+    return it->second;
+  }
+  bool setRobotConfiguration(std::string robot_name, const robot::JointValueMap& jointmap)
+  {
+    RobotInterfaceSharedPtr r = getRobot(robot_name);
+    if (!r) return false;
+    r->setConfiguration(jointmap);
+    return true;
+  }
+  bool getRobotConfiguration(const std::string& robot_name, robot::JointValueMap& jointmap)
+  {
+    RobotInterfaceSharedPtr r = getRobot(robot_name);
+    if (!r) return false;
+    r->getConfiguration(jointmap);
+    return true;
+  }
+  bool updateRobotPart(std::string robot_name, const std::string& link_name, const std::vector<Vector3f> pointcloud)
+  {
+    RobotInterfaceSharedPtr r = getRobot(robot_name);
+    if (!r) return false;
+    r->updatePointcloud(link_name, pointcloud);
+    return true;
+  }
+  bool insertRobotIntoMap(std::string robot_name, std::string map_name, const BitVoxelMeaning voxel_meaning)
+  {
+    RobotInterfaceSharedPtr r = getRobot(robot_name);
+    if (!r) return false;
+    ManagedMapsIterator it = findMap(map_name);
+    if (it == m_managed_maps.end()) return false;
+    it->second.map_shared_ptr->insertMetaPointCloud(*r->getTransformedClouds(), voxel_meaning);
+    return true;
+  }
+  // Extension: collideRobotConfigurations with the forward kinematics of a managed DH robot done on the device.
+  // joint_values[c * n_links + l] is the joint value of link l (in link_names order) in state c.
+  bool collideRobotConfigurations(const std::string& robot_name, const std::vector<BitVoxelMeaning>& link_meanings,
+                                  const std::vector<float>& joint_values, const std::string& env_map_name,
+                                  std::vector<size_t>& collisions_per_configuration, float coll_threshold = 1.0,
+                                  const BitVectorVoxel* types_to_check = NULL)
+  {
+    RobotInterfaceSharedPtr r = getRobot(robot_name);
+    robot::KinematicChain* chain = r ? dynamic_cast<robot::KinematicChain*>(r.get()) : NULL;
+    ManagedMapsIterator it = findMap(env_map_name);
+    if (!chain || it == m_managed_maps.end()) return false;
+    const MetaPointCloud& clouds = *chain->getLinkClouds();
+    const std::vector<std::string>& names = chain->getLinkNames();
+    const uint32_t n_links = uint32_t(names.size()), n_clouds = clouds.getNumberOfPointclouds();
+    if (!n_links || !n_clouds || link_meanings.size() != n_clouds || joint_values.size() % n_links)
+    {
+      LOGGING_ERROR_C(Gpu_voxels, GpuVoxels, "Number of link meanings / joint values does not fit the robot" << endl);
+      return false;
+    }
+    std::vector<float> dh4(4 * n_links);
+    std::vector<int32_t> types(n_links), link_cloud(n_links);
+    for (uint32_t i = 0; i < n_links; i++)
+    {
+      const robot::DHParameters p = chain->getLink(names[i])->getDHParam();
+      dh4[4 * i] = p.d; dh4[4 * i + 1] = p.theta; dh4[4 * i + 2] = p.a; dh4[4 * i + 3] = p.alpha;
+      types[i] = int32_t(p.joint_type);
+      link_cloud[i] = clouds.getCloudNumber(names[i]);
+    }
+    const uint32_t n_cfg = uint32_t(joint_values.size() / n_links);
+    const std::vector<int32_t> mg = detail::meaningsToInts(link_meanings);
+    std::vector<uint64_t> counts(n_cfg);
+    lock_guard guard(it->second.map_shared_ptr->m_mutex);
+    const int rc = gvx_batch_robot_collide_dh(it->second.map_shared_ptr->getHandle(),
+                                              reinterpret_cast<const float*>(clouds.getDeviceBasePointer()), GVX_MEM_DEVICE,
+                                              &clouds.getPointcloudSizes()[0], n_clouds, &mg[0], &dh4[0], &types[0], n_links,
+                                              &link_cloud[0], n_cfg ? &joint_values[0] : NULL, n_cfg,
+                                              types_to_check ? types_to_check->bitVector().bytes() : NULL, coll_threshold,
+                                              n_cfg ? &counts[0] : NULL);
+    if (!gvxCheck(rc, "collideRobotConfigurations")) return false;
+    collisions_per_configuration.assign(counts.begin(), counts.end());
+    return true;
+  }
+
   void getDimensions(uint32_t& dim_x, uint32_t& dim_y, uint32_t& dim_z) { dim_x = m_dim.x; dim_y = m_dim.y; dim_z = m_dim.z; }
   void getDimensions(Vector3ui& dim) { dim = m_dim; }
   void getVoxelSideLength(float& voxel_side_length) { voxel_side_length = m_voxel_side_length; }
@@ -208,7 +306,9 @@ private:
     return it;
   }
 
+  typedef std::map<std::string, RobotInterfaceSharedPtr> ManagedRobots;
   ManagedMaps m_managed_maps;
+  ManagedRobots m_managed_robots;
   Vector3ui m_dim;
   float m_voxel_side_length;
 };

@@ -11,6 +11,7 @@ static const GvLogStream Gpu_voxels = {"GpuVoxels"};
 static const GvLogStream Gpu_voxels_helpers = {"GpuVoxelsHelpers"};
 static const GvLogStream VoxelmapLog = {"Voxelmap"};
 static const GvLogStream VoxellistLog = {"Voxellist"};
+static const GvLogStream RobotLog = {"Robot"};
 static const char endl = '\n';
 }  // namespace gpu_voxels
 

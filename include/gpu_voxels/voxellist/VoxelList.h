@@ -4,6 +4,7 @@
 #define GPU_VOXELS_B200_VOXELLIST_VOXELLIST_H
 
 #include <climits>
+#include <cmath>
 
 #include <gpu_voxels/GpuVoxelsMap.h>
 #include <gpu_voxels/voxelmap/VoxelMap.h>
@@ -128,7 +129,110 @@ public:
     return size_t(total);
   }
 
+  // ---- list x list (GV/voxellist/BitVoxelList.hpp:86-125, 267-344; offsets between lists are refused there) ----
+  size_t collideWith(const BitVoxelList<length>* other, float coll_threshold = 1.0, const Vector3i& offset = Vector3i())
+  {
+    (void)coll_threshold;
+    uint64_t n = 0;
+    const int rc = gvx_collide_list_list(m_handle, other->m_handle, &n);
+    return listList(other, offset, rc, n);
+  }
+  size_t collideWithTypes(const BitVoxelList<length>* other, BitVectorVoxel& types_in_collision, float coll_threshold = 1.0,
+                          const Vector3i& offset = Vector3i())
+  {
+    (void)coll_threshold;
+    uint64_t n = 0;
+    const int rc = gvx_collide_list_list_types(m_handle, other->m_handle, types_in_collision.bitVector().bytes(), &n);
+    return listList(other, offset, rc, n);
+  }
+  size_t collideWithBitcheck(const BitVoxelList<length>* other, const uint8_t margin = 0, const Vector3i& offset = Vector3i())
+  {
+    uint64_t n = 0;
+    const int rc = gvx_collide_list_list_bitcheck(m_handle, other->m_handle, margin, &n);
+    return listList(other, offset, rc, n);
+  }
+  size_t collideCountingPerMeaning(const GpuVoxelsMapSharedPtr other, std::vector<size_t>& collisions_per_meaning,
+                                   const Vector3i& offset = Vector3i())
+  {
+    if (other->getMapType() != MT_BITVECTOR_VOXELLIST)
+    {
+      LOGGING_ERROR_C(VoxellistLog, BitVoxelList, GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+      return SSIZE_MAX;
+    }
+    uint64_t counts[256], total = 0;
+    const int rc = gvx_collide_list_list_per_meaning(m_handle, other->getHandle(), counts, &total);
+    const size_t r = listList(other.get(), offset, rc, total);
+    if (r != SSIZE_MAX && offset == Vector3i())
+    {
+      if (collisions_per_meaning.size() < 256) collisions_per_meaning.resize(256, 0);
+      for (int k = 0; k < 256; ++k) collisions_per_meaning[k] += size_t(counts[k]);  // the reference increments
+    }
+    return r;
+  }
+  // GV/voxellist/TemplateVoxelList.hpp:609-641
+  bool subtract(const BitVoxelList<length>* other, const Vector3i& voxel_offset = Vector3i())
+  {
+    if (!(voxel_offset == Vector3i()))
+    {
+      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, "Offset for VoxelList collision not supported! Not performing collision check." << endl);
+      return true;  // the reference removes nothing and still returns true
+    }
+    detail::DualLock guard(this->m_mutex, other->m_mutex);
+    return gvxCheck(gvx_list_subtract(m_handle, other->m_handle), "subtract");
+  }
+  bool subtract(const BitVoxelList<length>* other, const Vector3f& metric_offset)
+  {
+    return subtract(other, Vector3i(int32_t(std::floor(metric_offset.x / m_voxel_side_length)),
+                                    int32_t(std::floor(metric_offset.y / m_voxel_side_length)),
+                                    int32_t(std::floor(metric_offset.z / m_voxel_side_length))));
+  }
+  // GV/voxellist/TemplateVoxelList.hpp:806-825
+  bool equals(const BitVoxelList<length>& other) const
+  {
+    int eq = 0;
+    gvxCheck(gvx_list_equals(m_handle, other.m_handle, &eq), "equals");
+    return eq != 0;
+  }
+  // GV/voxellist/BitVoxelList.hpp:560-582
+  void shiftLeftSweptVolumeIDs(uint8_t shift_size)
+  {
+    if (shift_size > 56)
+    {
+      LOGGING_ERROR_C(VoxellistLog, BitVoxelList, "Maximum shift size is 56! Higher shift number requested. Not performing shift operation." << endl);
+      return;
+    }
+    lock_guard guard(this->m_mutex);
+    gvxCheck(gvx_list_shift_sv_ids(m_handle, shift_size), "shiftLeftSweptVolumeIDs");
+  }
+  // GV/voxellist/TemplateVoxelList.hpp:444-526
+  virtual bool writeToDisk(const std::string path)
+  {
+    lock_guard guard(this->m_mutex);
+    return gvxCheck(gvx_list_write_file(m_handle, path.c_str()), "writeToDisk");
+  }
+  virtual bool readFromDisk(const std::string path)
+  {
+    lock_guard guard(this->m_mutex);
+    return gvxCheck(gvx_list_read_file(m_handle, path.c_str()), "readFromDisk");
+  }
+
 private:
+  size_t listList(const GpuVoxelsMap* other, const Vector3i& offset, int rc, uint64_t n)
+  {
+    (void)other;
+    if (!(offset == Vector3i()))
+    {
+      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, "Offset for VoxelList collision not supported! Not performing collision check." << endl);
+      return 0;
+    }
+    if (rc == GVX_ERR_DIM_MISMATCH)
+    {
+      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, "The Voxellist reference map dimensions differ!" << endl);
+      return SSIZE_MAX;
+    }
+    if (!gvxCheck(rc, "list x list")) return SSIZE_MAX;
+    return size_t(n);
+  }
   size_t collide(int mode, const GpuVoxelsMap* map, float thr, const Vector3i& offset, const uint8_t* mask_in, uint8_t* mask_out)
   {
     detail::DualLock guard(this->m_mutex, map->m_mutex);

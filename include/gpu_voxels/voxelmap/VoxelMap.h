@@ -9,6 +9,7 @@
 #include <climits>
 
 #include <gpu_voxels/GpuVoxelsMap.h>
+#include <gpu_voxels/voxel/SVCollider.h>
 
 namespace gpu_voxels {
 namespace voxelmap {
@@ -83,6 +84,18 @@ public:
   void* getVoidDeviceDataPtr() { void* p = NULL; gvx_map_device_ptr(m_handle, &p, NULL, NULL); return p; }
   const void* getConstVoidDeviceDataPtr() const { void* p = NULL; gvx_map_device_ptr(m_handle, &p, NULL, NULL); return p; }
   virtual gvx_handle_t getHandle() const { return m_handle; }
+
+  // the reference's binary file format (GV/voxelmap/TemplateVoxelMap.hpp:666-799)
+  virtual bool writeToDisk(const std::string path)
+  {
+    lock_guard guard(this->m_mutex);
+    return gvxCheck(gvx_map_write_file(m_handle, path.c_str()), "writeToDisk");
+  }
+  virtual bool readFromDisk(const std::string path)
+  {
+    lock_guard guard(this->m_mutex);
+    return gvxCheck(gvx_map_read_file(m_handle, path.c_str()), "readFromDisk");
+  }
 
   // collisionCheck: boolean, no side effect (GV/voxelmap/TemplateVoxelMap.hpp:329-414)
   bool collisionCheck(const AbstractVoxelMap* other, float coll_threshold = 1.0)
@@ -178,24 +191,31 @@ public:
     m_sensor.position = sensor.position;
     m_sensor.orientation = sensor.orientation;
   }
-  // the log-odds update (GV/voxelmap/ProbVoxelMap.hpp:52-102): points = sensor.data_size HOST points in the sensor
-  // frame. Ray casting (free-space update) and the robot cut are not part of this build yet: the
-  // occupied-endpoint update is applied and the request is logged.
+  // insertSensorData (GV/voxelmap/ProbVoxelMap.hpp:52-102): points = sensor.data_size HOST points in the sensor frame;
+  // enable_raycasting adds the free-space update along every ray (RayCaster, VoxelMapOperations.h:199-323);
+  // cut_real_robot drops points whose hit voxel has bit `voxel_meaning` set in robot_map (a DEVICE pointer to the
+  // voxels of a BitVectorVoxelMap of the same dimensions, as in the reference).
   template <std::size_t length>
   void insertSensorData(const Vector3f* points, const bool enable_raycasting, const bool cut_real_robot,
                         const BitVoxelMeaning voxel_meaning, BitVoxel<length>* robot_map = NULL)
   {
-    (void)voxel_meaning; (void)robot_map;
     lock_guard guard(this->m_mutex);
     if (!m_init_sensor) { LOGGING_ERROR_C(VoxelmapLog, EnvironmentMap, "Call initSensorSettings() first!" << endl); return; }
-    if (enable_raycasting || cut_real_robot)
-      LOGGING_WARNING_C(VoxelmapLog, ProbVoxelMap, "ray casting / robot cut are not available: endpoint update only" << endl);
     const Matrix3f& R = m_sensor.orientation;
     const float pose[12] = {R.a11, R.a12, R.a13, m_sensor.position.x, R.a21, R.a22, R.a23, m_sensor.position.y,
                             R.a31, R.a32, R.a33, m_sensor.position.z};
-    gvxCheck(gvx_update_logodds(m_handle, reinterpret_cast<const float*>(points), m_sensor.data_size, GVX_MEM_HOST, pose,
-                                cSENSOR_MODEL_OCCUPIED), "insertSensorData");
+    gvx_handle_t robot = 0;
+    if (cut_real_robot)
+    {
+      if (!robot_map) { LOGGING_ERROR_C(VoxelmapLog, ProbVoxelMap, "cut_real_robot needs the robot map" << endl); return; }
+      if (!gvxCheck(gvx_map_wrap(&robot, GVX_MT_BITVECTOR_VOXELMAP, robot_map, m_dim.x, m_dim.y, m_dim.z,
+                                 m_voxel_side_length, 0, m_dim.z), "insertSensorData (robot map)")) return;
+    }
+    gvxCheck(gvx_insert_sensor_data(m_handle, reinterpret_cast<const float*>(points), m_sensor.data_size, GVX_MEM_HOST, pose,
+                                    enable_raycasting ? 1 : 0, robot, int(voxel_meaning), cSENSOR_MODEL_FREE,
+                                    cSENSOR_MODEL_OCCUPIED), "insertSensorData");
     gvx_sync();  // the reference returns after cudaDeviceSynchronize; `points` may be reused by the caller
+    if (robot) gvx_map_destroy(robot);
   }
   void insertSensorData(const Vector3f* points, const bool enable_raycasting, const bool cut_real_robot,
                         const BitVoxelMeaning voxel_meaning)
@@ -246,6 +266,48 @@ public:
   {
     return collideMapMap(map, coll_threshold, offset);
   }
+  // GV/voxelmap/BitVoxelMap.hpp:91-135: swept-volume check with a bit window; colliding_meanings is OR-ed into
+  uint32_t collisionCheckBitvector(const BitVoxelMap<length>* other, const SVCollider& collider,
+                                   BitVector<length>& colliding_meanings, const uint16_t sv_offset = 0)
+  {
+    detail::DualLock guard(this->m_mutex, other->m_mutex);
+    uint64_t n = 0;
+    if (!gvxCheck(gvx_collide_map_map_bitcheck(m_handle, other->getHandle(), uint32_t(uint8_t(collider.getWindowSize())),
+                                               sv_offset, 1, colliding_meanings.bytes(), &n), "collisionCheckBitvector"))
+      return UINT_MAX;
+    return uint32_t(n);
+  }
+  // GV/voxelmap/BitVoxelMap.hpp:139-188 with a ProbVoxelMap: the SVCollider's threshold, no window
+  uint32_t collisionCheckBitvector(const ProbVoxelMap* other, const SVCollider& collider,
+                                   BitVector<length>& colliding_meanings, const uint16_t sv_offset = 0)
+  {
+    (void)sv_offset;
+    detail::DualLock guard(this->m_mutex, other->m_mutex);
+    uint64_t n = 0;
+    if (!gvxCheck(gvx_collide_map_map_types(m_handle, other->getHandle(), collider.getThreshold(), 1,
+                                            colliding_meanings.bytes(), &n), "collisionCheckBitvector"))
+      return UINT_MAX;
+    return uint32_t(n);
+  }
+  // GV/voxelmap/BitVoxelMap.hpp:205-210: SVCollider(coll_threshold), window 0
+  size_t collideWithTypes(const BitVoxelMap<length>* map, BitVoxel<length>& types_in_collision, float coll_threshold = 1.0,
+                          const Vector3i& offset = Vector3i())
+  {
+    (void)offset;
+    return collisionCheckBitvector(map, SVCollider(coll_threshold), types_in_collision.bitVector());
+  }
+  // GV/voxelmap/BitVoxelMap.hpp:234-246
+  void shiftLeftSweptVolumeIDs(uint8_t shift_size)
+  {
+    if (shift_size > 56)
+    {
+      LOGGING_ERROR_C(VoxelmapLog, BitVoxelMap, "Maximum shift size is 56! Higher shift number requested. Not performing shift operation." << endl);
+      return;
+    }
+    lock_guard guard(this->m_mutex);
+    gvxCheck(gvx_map_shift_sv_ids(m_handle, shift_size), "shiftLeftSweptVolumeIDs");
+  }
+
   // GV/voxelmap/BitVoxelMap.hpp:212-217: types_in_collision is OR-ed into; the offset is ignored by the reference too
   size_t collideWithTypes(const ProbVoxelMap* map, BitVoxel<length>& types_in_collision, float coll_threshold = 1.0,
                           const Vector3i& offset = Vector3i())

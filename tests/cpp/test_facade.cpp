@@ -333,4 +333,254 @@ BOOST_AUTO_TEST_CASE(batch_equals_planner_sequence)
 
 BOOST_AUTO_TEST_SUITE_END()
 
+// ---- swept volumes, list x list, files, robots ------------------------------------------------------
+BOOST_AUTO_TEST_SUITE(next_rows)
+
+// GV/test/testing_voxelmap.cu:173-229
+BOOST_AUTO_TEST_CASE(collision_bitshift)
+{
+  float side_length = 1.f;
+  BitVectorVoxelMap map_1(Vector3ui(dimX, dimY, dimZ), side_length, MT_BITVECTOR_VOXELMAP);
+  BitVectorVoxelMap map_2(Vector3ui(dimX, dimY, dimZ), side_length, MT_BITVECTOR_VOXELMAP);
+  std::vector<Vector3f> points;
+  for (int x = 2; x <= 3; ++x) for (int y = 2; y <= 3; ++y) for (int z = 2; z <= 3; ++z) points.push_back(Vector3f(x, y, z));
+  const BitVoxelMeaning type_1 = BitVoxelMeaning(eBVM_SWEPT_VOLUME_START + 40);
+  map_1.insertPointCloud(points, type_1);
+  size_t window_size = 20;
+  SVCollider collider(1.0, window_size);
+  BitVectorVoxel types_voxel;
+  for (size_t i = type_1 - window_size - 9; i <= type_1 + window_size + 9; ++i)
+  {
+    map_2.clearMap();
+    map_2.insertPointCloud(points, BitVoxelMeaning(i));
+    size_t num_collisions = map_1.collisionCheckBitvector(&map_2, collider, types_voxel.bitVector());
+    if (num_collisions > 0)
+    {
+      types_voxel.bitVector().clearBit(type_1);
+      BOOST_CHECK(types_voxel.bitVector().isZero());
+    }
+    if (i < type_1 - window_size || i > type_1 + window_size) BOOST_CHECK(num_collisions == 0);
+    else BOOST_CHECK(num_collisions == points.size());
+  }
+}
+
+// GV/test/testing_voxelmap.cu:238-304
+BOOST_AUTO_TEST_CASE(bitvoxelmap_bitshift)
+{
+  BitVectorVoxelMap map_1(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELMAP);
+  BitVectorVoxelMap map_2(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELMAP);
+  std::vector<Vector3f> points;
+  points.push_back(Vector3f(0.3, 0.3, 0.3)); points.push_back(Vector3f(1.3, 1.3, 1.3));
+  points.push_back(Vector3f(2.3, 2.3, 2.3)); points.push_back(Vector3f(3.3, 3.3, 3.3));
+  uint32_t shift_size = 0;
+  const uint32_t shift_start = 50;
+  const uint32_t type_int = eBVM_SWEPT_VOLUME_START + shift_start;
+  while (shift_size < shift_start + eBVM_SWEPT_VOLUME_START - 5)
+  {
+    map_1.clearMap(); map_2.clearMap();
+    map_2.insertPointCloud(points, BitVoxelMeaning(type_int));
+    map_1.insertPointCloud(points, BitVoxelMeaning(type_int - shift_size));
+    map_2.shiftLeftSweptVolumeIDs(shift_size);
+    BitVectorVoxel types_voxel;
+    SVCollider collider(1.0, 1);
+    size_t num_collisions = map_1.collisionCheckBitvector(&map_2, collider, types_voxel.bitVector());
+    if (shift_size <= shift_start) BOOST_CHECK(num_collisions == points.size());
+    else BOOST_CHECK(num_collisions == 0);
+    shift_size++;
+  }
+}
+
+// GV/test/testing_voxellist.cu:341-410
+BOOST_AUTO_TEST_CASE(bitvoxellist_findMatchingVoxels)
+{
+  float side_length = 0.01;
+  GpuVoxelsMapSharedPtr voxellist1_shrd_ptr(new BitVectorVoxelList(Vector3ui(dimX, dimY, dimZ), side_length, MT_BITVECTOR_VOXELLIST));
+  GpuVoxelsMapSharedPtr voxellist2_shrd_ptr(new BitVectorVoxelList(Vector3ui(dimX, dimY, dimZ), side_length, MT_BITVECTOR_VOXELLIST));
+  std::vector<Vector3f> box1 = createBoxOfPoints(Vector3f(2.1, 0.1, 5.1), Vector3f(4.9, 4.9, 9.9), 0.02f);
+  std::vector<Vector3f> box2 = createBoxOfPoints(Vector3f(5.1, 5.1, 10.1), Vector3f(9.9, 9.9, 14.9), 0.3f);
+  std::vector<Vector3f> cp1, cp2, cp3;
+  for (int j = 0; j < 40; j++) cp1.push_back(Vector3f(j / 40.0 * 5.0, 1.0, 1.0));
+  for (int j = 0; j < 30; j++) cp2.push_back(Vector3f(j / 30.0 * 5.0, 2.0, 1.0));
+  for (int j = 0; j < 20; j++) cp3.push_back(Vector3f(j / 20.0 * 5.0, 3.0, 1.0));
+  voxellist1_shrd_ptr->insertPointCloud(box1, BitVoxelMeaning(10));
+  voxellist1_shrd_ptr->insertPointCloud(cp1, BitVoxelMeaning(11));
+  voxellist1_shrd_ptr->insertPointCloud(cp2, BitVoxelMeaning(12));
+  voxellist1_shrd_ptr->insertPointCloud(cp3, BitVoxelMeaning(13));
+  voxellist2_shrd_ptr->insertPointCloud(box2, BitVoxelMeaning(20));
+  voxellist2_shrd_ptr->insertPointCloud(cp1, BitVoxelMeaning(21));
+  voxellist2_shrd_ptr->insertPointCloud(cp2, BitVoxelMeaning(22));
+  voxellist2_shrd_ptr->insertPointCloud(cp3, BitVoxelMeaning(23));
+  std::vector<size_t> collisions_per_meaning(BIT_VECTOR_LENGTH, 0);
+  size_t num_coll = voxellist1_shrd_ptr->as<BitVectorVoxelList>()->collideCountingPerMeaning(voxellist2_shrd_ptr, collisions_per_meaning);
+  BOOST_CHECK(num_coll == 90);
+  BOOST_CHECK(collisions_per_meaning[11] == 40 && collisions_per_meaning[12] == 30 && collisions_per_meaning[13] == 20);
+  BOOST_CHECK(collisions_per_meaning[21] == 0 && collisions_per_meaning[22] == 0 && collisions_per_meaning[23] == 0);
+  BOOST_CHECK(collisions_per_meaning[10] == 0 && collisions_per_meaning[20] == 0);
+  collisions_per_meaning.assign(BIT_VECTOR_LENGTH, 0);
+  num_coll = voxellist2_shrd_ptr->as<BitVectorVoxelList>()->collideCountingPerMeaning(voxellist1_shrd_ptr, collisions_per_meaning);
+  BOOST_CHECK(num_coll == 90);
+  BOOST_CHECK(collisions_per_meaning[21] == 40 && collisions_per_meaning[22] == 30 && collisions_per_meaning[23] == 20);
+  BOOST_CHECK(collisions_per_meaning[11] == 0 && collisions_per_meaning[12] == 0 && collisions_per_meaning[13] == 0);
+}
+
+// GV/test/testing_voxellist.cu:412-460
+BOOST_AUTO_TEST_CASE(bitvoxellist_bitshift_collision)
+{
+  BitVectorVoxelList map_1(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELLIST);
+  GpuVoxelsMapSharedPtr map_2(new BitVectorVoxelList(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELLIST));
+  BitVectorVoxelList* map2_base_ptr = map_2->as<BitVectorVoxelList>();
+  std::vector<Vector3f> points;
+  points.push_back(Vector3f(0.3, 0.3, 0.3));
+  uint32_t shift_size = 0;
+  const uint32_t shift_start = 50;
+  const uint32_t type_int = eBVM_SWEPT_VOLUME_START + shift_start;
+  while (shift_size < shift_start + eBVM_SWEPT_VOLUME_START - 5)
+  {
+    map_1.clearMap(); map_2->clearMap();
+    map_2->insertPointCloud(points, BitVoxelMeaning(type_int));
+    map_1.insertPointCloud(points, BitVoxelMeaning(type_int - shift_size));
+    map2_base_ptr->shiftLeftSweptVolumeIDs(shift_size);
+    size_t num_collisions = map_1.collideWithBitcheck(map_2->as<voxellist::BitVectorVoxelList>(), 1);
+    if (shift_size <= shift_start) BOOST_CHECK(num_collisions == 1);
+    else BOOST_CHECK(num_collisions == 0);
+    shift_size++;
+  }
+}
+
+// GV/test/testing_voxellist.cu:462-572: equals, disk io, subtract
+BOOST_AUTO_TEST_CASE(voxellist_equals_disk_io_subtract)
+{
+  BitVectorVoxelList list1(Vector3ui(dimX, dimY, dimZ), 1, MT_BITVECTOR_VOXELLIST);
+  BitVectorVoxelList list2(Vector3ui(dimX, dimY, dimZ), 1, MT_BITVECTOR_VOXELLIST);
+  std::vector<BitVoxelMeaning> voxel_meanings;
+  voxel_meanings.push_back(BitVoxelMeaning(11));
+  voxel_meanings.push_back(BitVoxelMeaning(12));
+  std::vector<std::vector<Vector3f> > box_clouds;
+  box_clouds.push_back(createBoxOfPoints(Vector3f(1.1, 1.1, 1.1), Vector3f(3.9, 3.9, 3.9), 0.1));
+  box_clouds.push_back(createBoxOfPoints(Vector3f(2.1, 2.1, 2.1), Vector3f(4.9, 4.9, 4.9), 0.1));
+  MetaPointCloud boxes(box_clouds);
+  boxes.syncToDevice();
+  list1.insertMetaPointCloud(boxes, voxel_meanings);
+  list2.insertMetaPointCloud(boxes, voxel_meanings);
+  BOOST_CHECK_MESSAGE(list1.equals(list2), "Lists are equal.");
+  BOOST_CHECK(list1.writeToDisk("/tmp/gvx_temp_list.lst"));
+  BitVectorVoxelList list3(Vector3ui(dimX, dimY, dimZ), 1, MT_BITVECTOR_VOXELLIST);
+  BOOST_CHECK(list3.readFromDisk("/tmp/gvx_temp_list.lst"));
+  BOOST_CHECK_MESSAGE(list1.equals(list3), "List from Disk equals original list.");
+  std::vector<Vector3f> outliers;
+  outliers.push_back(Vector3f(9.22, 9.22, 9.22));
+  list1.insertPointCloud(outliers, BitVoxelMeaning(11));
+  list2.insertPointCloud(outliers, BitVoxelMeaning(12));
+  BOOST_CHECK_MESSAGE(!list1.equals(list2), "Lists differ.");
+
+  BitVectorVoxelList a(Vector3ui(dimX, dimY, dimZ), 1, MT_BITVECTOR_VOXELLIST);
+  BitVectorVoxelList b(Vector3ui(dimX, dimY, dimZ), 1, MT_BITVECTOR_VOXELLIST);
+  a.insertPointCloud(box_clouds[0], BitVoxelMeaning(11));
+  b.insertPointCloud(box_clouds[1], BitVoxelMeaning(12));
+  a.subtract(&b, Vector3f());
+  BOOST_CHECK_MESSAGE(a.size() == 19, "Number of cubes after subtract == 19");
+}
+
+// TemplateVoxelMap::writeToDisk / readFromDisk (GV/voxelmap/TemplateVoxelMap.hpp:666-799)
+BOOST_AUTO_TEST_CASE(voxelmap_disk_io)
+{
+  ProbVoxelMap m1(Vector3ui(40, 30, 20), 0.5f, MT_PROBAB_VOXELMAP), m2(Vector3ui(40, 30, 20), 0.5f, MT_PROBAB_VOXELMAP);
+  BitVectorVoxelMap wrong(Vector3ui(40, 30, 20), 0.5f, MT_BITVECTOR_VOXELMAP);
+  m1.insertPointCloud(createBoxOfPoints(Vector3f(2.1, 2.1, 2.1), Vector3f(6.1, 6.1, 6.1), 0.25), eBVM_OCCUPIED);
+  BOOST_CHECK(m1.writeToDisk("/tmp/gvx_temp_map.bin"));
+  BOOST_CHECK(m2.readFromDisk("/tmp/gvx_temp_map.bin"));
+  BOOST_CHECK(!wrong.readFromDisk("/tmp/gvx_temp_map.bin"));
+  BOOST_CHECK(m1.collideWith(&m2, 0.5) == 9 * 9 * 9);
+}
+
+// ray casting through the reference's call: the cells between the sensor and a wall become free, the wall occupied
+BOOST_AUTO_TEST_CASE(insert_sensor_data_with_raycasting_and_robot_cut)
+{
+  const Vector3ui dim(64, 64, 32);
+  ProbVoxelMap env(dim, 0.1f, MT_PROBAB_VOXELMAP), probe(dim, 0.1f, MT_PROBAB_VOXELMAP);
+  BitVectorVoxelMap robot(dim, 0.1f, MT_BITVECTOR_VOXELMAP);
+  std::vector<Vector3f> wall;
+  for (int y = -10; y <= 10; ++y) for (int z = -5; z <= 5; ++z) wall.push_back(Vector3f(0.1f * y, 0.1f * z, 3.05f));  // sensor frame
+  // sensor at (0.55, 3.25, 1.65) looking along +x: sensor z -> world x, sensor x -> world y, sensor y -> world z
+  Sensor sensor(Vector3f(0.55f, 3.25f, 1.65f), Matrix3f(0, 0, 1, 1, 0, 0, 0, 1, 0), uint32_t(wall.size()), 1);
+  env.initSensorSettings(sensor);
+  env.insertSensorData(&wall[0], true, false, eBVM_OCCUPIED);
+  // the wall plane x = 36 is occupied, the cells in front of it on the central ray are free
+  std::vector<Vector3f> hit(1, Vector3f(3.65f, 3.25f, 1.65f)), mid(1, Vector3f(2.05f, 3.25f, 1.65f));
+  probe.insertPointCloud(hit, eBVM_OCCUPIED);
+  BOOST_CHECK(env.collideWith(&probe, 0.5) == 0);      // -127 -10 .. +72 = -55 < 0: one hit is not yet "occupied" at 0.5
+  BOOST_CHECK(env.collideWith(&probe, 0.2) == 1);      // but it is at threshold 0.2 (-76)
+  probe.clearMap();
+  probe.insertPointCloud(mid, eBVM_OCCUPIED);
+  BOOST_CHECK(env.collideWith(&probe, 0.01) == 0);     // free: -127 is below every threshold above 0
+  BOOST_CHECK(env.collideWith(&probe, 0.0) == 1);      // but known (-127 >= -127); this call marks the voxel (127)
+  // robot cut: the robot occupies the wall's central voxel -> that ray is dropped entirely
+  ProbVoxelMap env2(dim, 0.1f, MT_PROBAB_VOXELMAP);
+  robot.insertPointCloud(hit, eBVM_OCCUPIED);
+  env2.initSensorSettings(sensor);
+  env2.insertSensorData(&wall[0], true, true, eBVM_OCCUPIED,
+                        static_cast<BitVoxel<BIT_VECTOR_LENGTH>*>(robot.getVoidDeviceDataPtr()));
+  probe.clearMap();
+  probe.insertPointCloud(hit, eBVM_OCCUPIED);
+  BOOST_CHECK(env2.collideWith(&probe, 0.0) == 0);     // still unknown
+}
+
+// DH robot through the singleton: addRobot / setRobotConfiguration / insertRobotIntoMap, and the batch with device FK
+BOOST_AUTO_TEST_CASE(dh_robot_and_batched_fk)
+{
+  GpuVoxelsSharedPtr gvl = GpuVoxels::getInstance();
+  gvl->initialize(120, 120, 120, 0.01);
+  gvl->addMap(MT_BITVECTOR_VOXELMAP, "env");
+  gvl->addMap(MT_BITVECTOR_VOXELMAP, "rob");
+  gvl->insertBoxIntoMap(Vector3f(0.2, 0.2, 0.2), Vector3f(0.9, 0.9, 0.9), "env", eBVM_OCCUPIED, 1);
+  std::vector<std::string> names;
+  names.push_back("base"); names.push_back("upper"); names.push_back("lower");
+  std::vector<robot::DHParameters> dh;
+  dh.push_back(robot::DHParameters(0.3f, 0.f, 0.1f, 1.5707963f, 0.f, robot::REVOLUTE));
+  dh.push_back(robot::DHParameters(0.0f, 0.f, 0.3f, 0.f, 0.f, robot::REVOLUTE));
+  dh.push_back(robot::DHParameters(0.1f, 0.f, 0.2f, 0.f, 0.f, robot::PRISMATIC));
+  MetaPointCloud clouds;
+  clouds.addCloud(createBoxOfPoints(Vector3f(0.45, 0.45, 0.0), Vector3f(0.55, 0.55, 0.3), 0.004), false, "base");
+  clouds.addCloud(createBoxOfPoints(Vector3f(0.4, 0.4, 0.0), Vector3f(0.5, 0.5, 0.3), 0.004), false, "upper");
+  clouds.addCloud(createBoxOfPoints(Vector3f(0.3, 0.3, 0.0), Vector3f(0.4, 0.4, 0.2), 0.004), true, "lower");
+  BOOST_CHECK(gvl->addRobot("arm", names, dh, clouds));
+  BOOST_CHECK(!gvl->addRobot("arm", names, dh, clouds));
+  std::vector<BitVoxelMeaning> mg(3, eBVM_OCCUPIED);
+  const int n_cfg = 6;
+  std::vector<float> q;
+  std::vector<size_t> want;
+  BitVectorVoxelMap* rob = gvl->getMap("rob")->as<BitVectorVoxelMap>();
+  for (int c = 0; c < n_cfg; ++c)
+  {
+    robot::JointValueMap jm;
+    jm["base"] = 0.3f * c; jm["upper"] = -0.2f * c; jm["lower"] = 0.05f * c;
+    q.push_back(jm["base"]); q.push_back(jm["upper"]); q.push_back(jm["lower"]);
+    BOOST_CHECK(gvl->setRobotConfiguration("arm", jm));
+    gvl->clearMap("rob");
+    BOOST_CHECK(gvl->insertRobotIntoMap("arm", "rob", eBVM_OCCUPIED));
+    want.push_back(rob->collideWith(gvl->getMap("env")->as<BitVectorVoxelMap>(), 1.0));
+  }
+  std::vector<size_t> got;
+  BOOST_CHECK(gvl->collideRobotConfigurations("arm", mg, q, "env", got));
+  BOOST_CHECK(got.size() == want.size());
+  size_t sum = 0;
+  for (int c = 0; c < n_cfg; ++c)
+  {
+    BOOST_CHECK_MESSAGE(got[c] == want[c], "configuration " << c << ": " << got[c] << " != " << want[c]);
+    sum += want[c];
+  }
+  BOOST_CHECK(sum > 0);
+  robot::JointValueMap back;
+  BOOST_CHECK(gvl->getRobotConfiguration("arm", back) && back.size() == 3);
+  // one DH matrix: revolute, theta 0 + value, alpha pi/2 (KinematicLink.cu:30-84)
+  Matrix4f m;
+  robot::DHParameters(0.3f, 0.f, 0.1f, 1.5707963f, 0.5f, robot::REVOLUTE).convertDHtoM(m);
+  BOOST_CHECK(m.a11 == float(std::cos(0.5)) && m.a21 == float(std::sin(0.5)) && m.a34 == 0.3f && m.a44 == 1.f);
+  BOOST_CHECK(m.a14 == 0.1f * float(std::cos(0.5)) - 0.f * float(std::sin(0.5)));
+  gvl->delMap("env");
+  gvl->delMap("rob");
+}
+
+BOOST_AUTO_TEST_SUITE_END()
+
 int main(int argc, char** argv) { return mini_test::run_all(argc > 1 ? argv[1] : NULL); }
