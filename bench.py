@@ -403,6 +403,22 @@ def run_gpu_arm(args):
                                             pose_arr[rank].ctypes.data_as(C.c_void_p), 72))
         evi1.record(stream)
         torch.cuda.synchronize()
+    if args.diag:
+        # where a sharded step spends its time (stderr only): the fold alone, the collide alone without / with the
+        # in-kernel all-reduce, and an empty-kernel-free measure of the host's launch rate (the same calls, GPU idle)
+        def t_loop(fn):
+            return timed(fn, args.steps) / args.steps * 1e3
+        d = {"fold_us": t_loop(lambda k: fold_frames(cat_d[k % P], k)),
+             "collide_local_us": t_loop(lambda k: _lib.check(L.gvx_collide_map_map_async(
+                 envs[k % P].handle, robs[k % P].handle, THR, None, 1, C.c_void_p(count_d.data_ptr())))),
+             "collide_global_us": t_loop(lambda k: collide_global(k)),
+             "step_us": t_loop(step_device)}
+        t0 = time.perf_counter()
+        for k in range(args.steps):
+            step_device(k)
+        d["host_issue_us_per_step"] = (time.perf_counter() - t0) / args.steps * 1e6
+        barrier()
+        print("diag rank %d: %s" % (rank, json.dumps(d)), file=sys.stderr)
     k_ms = sorted(e0.elapsed_time(e1) for e0, e1 in kev)
     k_avg = sum(k_ms) / len(k_ms)
     ins_ms = evi0.elapsed_time(evi1) / args.steps
@@ -470,6 +486,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--diag", action="store_true", help="print a per-phase timing breakdown to stderr")
     ap.add_argument("--nccl-count", action="store_true", help="all-reduce the count with NCCL instead of in-kernel")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -539,6 +539,21 @@ int gvx_update_logodds_multi(gvx_handle_t h, const float* xyz_sensor, int mem_ki
   if (delta_occ < -127 || delta_occ > 127) return fail(GVX_ERR_INVALID, "delta %d outside int8 range", delta_occ);
   if (!n_frames) return GVX_OK;
   if (!frame_sizes || !poses12) return fail(GVX_ERR_INVALID, "null pointer");
+  if (n_frames <= (uint32_t)kMaxFramesByValue) {  // the usual case: everything travels in the kernel parameters
+    FramesByValue fv;
+    uint64_t acc = 0;
+    for (uint32_t f = 0; f < n_frames; ++f) { fv.prefix[f] = (uint32_t)acc; acc += frame_sizes[f]; }
+    if (acc > 0xFFFFFFFFull) return fail(GVX_ERR_INVALID, "more than 2^32-1 sensor points in one call");
+    fv.prefix[n_frames] = (uint32_t)acc;
+    memcpy(fv.poses, poses12, (size_t)n_frames * 48);
+    if (acc == 0) return GVX_OK;
+    if (!xyz_sensor) return fail(GVX_ERR_INVALID, "null point pointer");
+    const float* xyz_d = nullptr;
+    int rc = points_to_device(xyz_sensor, acc, mem_kind, &xyz_d);
+    if (rc) return rc;
+    GVX_CUDA(launch_update_logodds_multi(lctx(), m->view(), xyz_d, acc, nullptr, nullptr, n_frames, delta_occ, &fv));
+    return GVX_OK;
+  }
   const size_t off_pose = ((size_t)n_frames + 1) * 4, total = off_pose + (size_t)n_frames * 48;
   int slot; void *dh, *dd;
   int rc = desc_acquire(total, &slot, &dh, &dd);

@@ -322,6 +322,62 @@ k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t*
   }
 }
 
+// Up to kMaxFramesByValue frames with their poses in the kernel PARAMETERS (nothing for the host to stage): grid.y is
+// the frame, so a CTA works with one pose held in registers exactly like k_update_logodds. The world z of a point is
+// computed first: on a z-slab rank most points of a multi-sensor cloud belong to other slabs and are dropped after
+// three FMAs and one division.
+__global__ void __launch_bounds__(kInsThreads)
+k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_constant__ FramesByValue fv, int delta) {
+  const uint32_t f = blockIdx.y;
+  float P[12];
+#pragma unroll
+  for (int k = 0; k < 12; ++k) P[k] = fv.poses[12 * f + k];
+  if (!(coord_to_voxel(P[3], m.side) < m.dx && coord_to_voxel(P[7], m.side) < m.dy && coord_to_voxel(P[11], m.side) < m.dz))
+    return;  // sensor origin outside the map: the frame contributes nothing (VoxelMapOperations.hpp:577-580)
+  const unsigned long long first = fv.prefix[f], n = fv.prefix[f + 1] - fv.prefix[f];
+  const uint64_t slab = (uint64_t)m.dx * m.dy;
+  const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
+  const unsigned long long n_round = (n + 31ull) & ~31ull;
+  for (unsigned long long k = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; k < n_round; k += stride) {
+    bool live = false;
+    uint64_t idx = 0;
+    if (k < n) {
+      const unsigned long long i = first + k;
+      const float rx = __ldg(xyz + 3 * i), ry = __ldg(xyz + 3 * i + 1), rz = __ldg(xyz + 3 * i + 2);
+      float wz = affine_row(P + 8, rx, ry, rz);
+      if (wz < 0.0f) {  // re-projection onto the floor moves x and y too: the full path
+        float wx, wy;
+        sensor_to_world(P, rx, ry, rz, wx, wy, wz);
+        if (!(isnan(wx) || isnan(wy) || isnan(wz))) {
+          const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
+          if (cx < m.dx && cy < m.dy && cz >= m.z0 && cz < m.z1) {
+            live = true;
+            idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+          }
+        }
+      } else if (!isnan(wz)) {
+        const uint32_t cz = coord_to_voxel(wz, m.side);
+        if (cz >= m.z0 && cz < m.z1) {
+          const float wx = affine_row(P, rx, ry, rz), wy = affine_row(P + 4, rx, ry, rz);
+          if (!(isnan(wx) || isnan(wy))) {
+            const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side);
+            if (cx < m.dx && cy < m.dy) {
+              live = true;
+              idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+            }
+          }
+        }
+      }
+    }
+    const unsigned long long key = live ? idx : (~0ull - (threadIdx.x & 31));
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
+      logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
+      if (m.occ) summary_set(m.occ, idx);
+    }
+  }
+}
+
 // BitVoxelMap::clearBits / clearBit: voxel &= ~mask, written back only where it changes. When the map carries an
 // occupancy summary the warp re-derives its 32 voxels' summary word from the result (warps cover aligned 32-voxel
 // groups: block size and stride are multiples of 32).
@@ -401,9 +457,22 @@ cudaError_t launch_raycast_free(const LaunchCtx& c, const MapView& m, const floa
 }
 
 cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
-                                        const uint32_t* prefix_d, const float* poses_d, uint32_t n_frames, int delta) {
+                                        const uint32_t* prefix_d, const float* poses_d, uint32_t n_frames, int delta,
+                                        const FramesByValue* by_value) {
   ++*c.launches;
-  k_update_logodds_multi<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, prefix_d, poses_d, n_frames, delta);
+  if (by_value) {
+    uint32_t longest = 0;
+    for (uint32_t f = 0; f < n_frames; ++f) {
+      const uint32_t len = by_value->prefix[f + 1] - by_value->prefix[f];
+      if (len > longest) longest = len;
+    }
+    int gx = grid_for(c, longest, 8);
+    const int per_frame = (c.sm_count * 8 + (int)n_frames - 1) / (int)n_frames;  // the device holds sm_count * 8 CTAs
+    if (gx > per_frame) gx = per_frame;
+    k_update_logodds_frames<<<dim3((unsigned)gx, n_frames), kInsThreads, 0, c.stream>>>(m, xyz_d, *by_value, delta);
+  } else {
+    k_update_logodds_multi<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, prefix_d, poses_d, n_frames, delta);
+  }
   return cudaGetLastError();
 }
 

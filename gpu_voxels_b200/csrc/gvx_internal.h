@@ -53,8 +53,15 @@ cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const fl
 // the free-space pass of the ray caster: delta_free (< 0) on every cell from the sensor's voxel to the hit voxel
 cudaError_t launch_raycast_free(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
                                 const Affine12& pose, int delta_free, const void* robot_d, uint32_t robot_bit);
+constexpr int kMaxFramesByValue = 16;
+struct FramesByValue {  // a small multi-frame description passed in the kernel parameters
+  uint32_t prefix[kMaxFramesByValue + 1];
+  float poses[kMaxFramesByValue * 12];
+};
+// by_value != nullptr (n_frames <= kMaxFramesByValue): prefix_d / poses_d are ignored
 cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
-                                        const uint32_t* prefix_d, const float* poses_d, uint32_t n_frames, int delta);
+                                        const uint32_t* prefix_d, const float* poses_d, uint32_t n_frames, int delta,
+                                        const FramesByValue* by_value = nullptr);
 // voxel &= ~mask for all voxels; occ (nullable): summary words rewritten from the result
 cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8], uint32_t* occ);
 
