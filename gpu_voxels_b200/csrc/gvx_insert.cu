@@ -336,44 +336,119 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
     return;  // sensor origin outside the map: the frame contributes nothing (VoxelMapOperations.hpp:577-580)
   const unsigned long long first = fv.prefix[f], n = fv.prefix[f + 1] - fv.prefix[f];
   const uint64_t slab = (uint64_t)m.dx * m.dy;
-  const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
-  const unsigned long long n_round = (n + 31ull) & ~31ull;
-  for (unsigned long long k = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; k < n_round; k += stride) {
-    bool live = false;
-    uint64_t idx = 0;
-    if (k < n) {
-      const unsigned long long i = first + k;
-      const float rx = __ldg(xyz + 3 * i), ry = __ldg(xyz + 3 * i + 1), rz = __ldg(xyz + 3 * i + 2);
-      float wz = affine_row(P + 8, rx, ry, rz);
-      if (wz < 0.0f) {  // re-projection onto the floor moves x and y too: the full path
-        float wx, wy;
-        sensor_to_world(P, rx, ry, rz, wx, wy, wz);
-        if (!(isnan(wx) || isnan(wy) || isnan(wz))) {
-          const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
-          if (cx < m.dx && cy < m.dy && cz >= m.z0 && cz < m.z1) {
-            live = true;
-            idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
-          }
+  // U points per thread and step, their loads issued together: with several frames per launch a thread runs many steps,
+  // and one dependent load -> divide -> atomic chain per step would leave the SMs waiting on latency
+  constexpr int U = 4;
+  __shared__ __align__(16) float sh_xyz[kInsThreads * U * 3];
+  // staging needs 16-byte aligned chunks: the frame must start on a multiple of 4 points of a 16-byte aligned array
+  const bool staged = ((first & 3ull) == 0) && ((reinterpret_cast<uintptr_t>(xyz) & 15) == 0);
+  const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads * U;
+  for (unsigned long long base = (unsigned long long)blockIdx.x * kInsThreads * U; base < n; base += stride) {  // CTA-uniform
+    float rx[U], ry[U], rz[U];
+    bool have[U];
+    if (staged) {
+      // the CTA's U * 256 points (12 KB) come in as 768 coalesced 128-bit loads and are handed out from shared memory:
+      // a thread's own x/y/z sit 12 bytes apart, which as direct loads costs three 4-byte requests per point
+      const unsigned long long left = n - base;
+      const uint32_t n_floats = (uint32_t)(left < (unsigned long long)(kInsThreads * U) ? left : kInsThreads * U) * 3u;
+      const float4* src = reinterpret_cast<const float4*>(xyz + 3 * (first + base));
+      __syncthreads();  // the previous step's readers are done
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const uint32_t q = j * kInsThreads + threadIdx.x;  // float4 index inside the chunk
+        if (4 * q + 3 < n_floats) {
+          reinterpret_cast<float4*>(sh_xyz)[q] = __ldg(src + q);
+        } else {
+          for (uint32_t e = 4 * q; e < n_floats && e < 4 * q + 4; ++e) sh_xyz[e] = __ldg(xyz + 3 * (first + base) + e);
         }
-      } else if (!isnan(wz)) {
-        const uint32_t cz = coord_to_voxel(wz, m.side);
-        if (cz >= m.z0 && cz < m.z1) {
-          const float wx = affine_row(P, rx, ry, rz), wy = affine_row(P + 4, rx, ry, rz);
-          if (!(isnan(wx) || isnan(wy))) {
-            const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side);
-            if (cx < m.dx && cy < m.dy) {
+      }
+      __syncthreads();
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint32_t k = u * kInsThreads + threadIdx.x;
+        have[u] = base + k < n;
+        if (have[u]) { rx[u] = sh_xyz[3 * k]; ry[u] = sh_xyz[3 * k + 1]; rz[u] = sh_xyz[3 * k + 2]; }
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const unsigned long long k = base + (unsigned long long)u * kInsThreads + threadIdx.x;
+        have[u] = k < n;
+        if (have[u]) {
+          const float* p = xyz + 3 * (first + k);
+          rx[u] = __ldg(p); ry[u] = __ldg(p + 1); rz[u] = __ldg(p + 2);
+        }
+      }
+    }
+    bool lead[U];   // this lane applies the (warp-folded) update of point u
+    uint64_t idx[U];
+    int tot[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      bool live = false;
+      idx[u] = 0;
+      if (have[u]) {
+        float wz = affine_row(P + 8, rx[u], ry[u], rz[u]);
+        if (wz < 0.0f) {  // re-projection onto the floor moves x and y too: the full path
+          float wx, wy;
+          sensor_to_world(P, rx[u], ry[u], rz[u], wx, wy, wz);
+          if (!(isnan(wx) || isnan(wy) || isnan(wz))) {
+            const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
+            if (cx < m.dx && cy < m.dy && cz >= m.z0 && cz < m.z1) {
               live = true;
-              idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+              idx[u] = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+            }
+          }
+        } else if (!isnan(wz)) {
+          const uint32_t cz = coord_to_voxel(wz, m.side);
+          if (cz >= m.z0 && cz < m.z1) {
+            const float wx = affine_row(P, rx[u], ry[u], rz[u]), wy = affine_row(P + 4, rx[u], ry[u], rz[u]);
+            if (!(isnan(wx) || isnan(wy))) {
+              const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side);
+              if (cx < m.dx && cy < m.dy) {
+                live = true;
+                idx[u] = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+              }
             }
           }
         }
       }
+      lead[u] = false;
+      tot[u] = 0;
+      if (!__any_sync(0xffffffffu, live)) continue;  // a warp of another slab's points: nothing to fold
+      const unsigned long long key = live ? idx[u] : (~0ull - (threadIdx.x & 31));
+      const unsigned peers = __match_any_sync(0xffffffffu, key);
+      lead[u] = live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1);
+      tot[u] = delta * __popc(peers);
     }
-    const unsigned long long key = live ? idx : (~0ull - (threadIdx.x & 31));
-    const unsigned peers = __match_any_sync(0xffffffffu, key);
-    if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
-      logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
-      if (m.occ) summary_set(m.occ, idx);
+    // the U read-modify-writes of a thread go out together: loads of the old words, then the CAS of each, then (rare)
+    // the retry loop for a CAS that lost a race; the same for the summary bits. One latency chain instead of U.
+    int8_t* map = (int8_t*)m.data;
+    uint32_t oldw[U], neww[U], got[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (lead[u]) oldw[u] = __ldcg(reinterpret_cast<const uint32_t*>(map + (idx[u] & ~3ull)));
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!lead[u]) continue;
+      const int shift = (int)(idx[u] & 3ull) * 8;
+      int v = (int)(int8_t)((oldw[u] >> shift) & 0xFFu) + tot[u];
+      v = v < -127 ? -127 : (v > 127 ? 127 : v);
+      neww[u] = (oldw[u] & ~(0xFFu << shift)) | (((uint32_t)v & 0xFFu) << shift);
+      got[u] = oldw[u];
+      if (neww[u] != oldw[u]) got[u] = atomicCAS(reinterpret_cast<uint32_t*>(map + (idx[u] & ~3ull)), oldw[u], neww[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (lead[u] && got[u] != oldw[u]) logodds_add(map, idx[u], tot[u]);  // another update got in between: redo
+    if (m.occ) {
+      uint32_t sw[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (lead[u]) sw[u] = __ldcg(m.occ + (idx[u] >> 5));
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (lead[u] && !(sw[u] & (1u << (idx[u] & 31)))) atomicOr(m.occ + (idx[u] >> 5), 1u << (idx[u] & 31));
     }
   }
 }
@@ -466,7 +541,7 @@ cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, co
       const uint32_t len = by_value->prefix[f + 1] - by_value->prefix[f];
       if (len > longest) longest = len;
     }
-    int gx = grid_for(c, longest, 8);
+    int gx = grid_for(c, (longest + 3) / 4, 8);  // 4 points per thread and step
     const int per_frame = (c.sm_count * 8 + (int)n_frames - 1) / (int)n_frames;  // the device holds sm_count * 8 CTAs
     if (gx > per_frame) gx = per_frame;
     k_update_logodds_frames<<<dim3((unsigned)gx, n_frames), kInsThreads, 0, c.stream>>>(m, xyz_d, *by_value, delta);

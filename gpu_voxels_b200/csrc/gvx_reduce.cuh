@@ -6,31 +6,36 @@ namespace gvx {
 
 constexpr int kThreads = 256;  // block size of every reducing kernel
 
-// One thread: publish `mine` to every rank's mailbox, wait for all ranks' values of this epoch, return the sum.
+// One WARP: lane r publishes `mine` to rank r's mailbox and waits for rank r's value of this epoch in its own mailbox;
+// the lanes' values are then summed. Value (48 bits) and epoch (16 bits) travel in ONE 64-bit word, so a single relaxed
+// system-scope store per peer is enough -- nothing else written by this kernel is read through the mailbox -- and the
+// world - 1 NVLink stores and polls overlap instead of queueing behind one thread's release fences.
 // The wait is bounded (~4 s of SM clocks): a rank that never arrives yields ~0ull instead of a hung GPU.
 __device__ __forceinline__ unsigned long long peer_allreduce_sum(unsigned long long mine, const PeerReduce& pr) {
+  const int lane = threadIdx.x & 31;
   const int par = (int)(pr.epoch & 1ull);
-  for (int r = 0; r < pr.world; ++r) {
-    PeerSlot* s = pr.peers[r] + par * kMaxPeers + pr.rank;
-    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&s->value), "l"(mine) : "memory");
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(&s->epoch), "l"(pr.epoch) : "memory");
-  }
-  unsigned long long sum = 0;
-  const long long t0 = clock64();
-  for (int r = 0; r < pr.world; ++r) {
-    const PeerSlot* s = pr.peers[pr.rank] + par * kMaxPeers + r;
-    unsigned long long e;
+  const unsigned long long tag = (pr.epoch & 0xFFFFull) << 48;
+  unsigned long long v = 0;
+  bool ok = true;
+  if (lane < pr.world) {
+    PeerSlot* dst = pr.peers[lane] + par * kMaxPeers + pr.rank;
+    const unsigned long long word = tag | (mine & 0xFFFFFFFFFFFFull);
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&dst->value), "l"(word) : "memory");
+    const PeerSlot* src = pr.peers[pr.rank] + par * kMaxPeers + lane;
+    const long long t0 = clock64();
     for (;;) {
-      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(e) : "l"(&s->epoch) : "memory");
-      if (e == pr.epoch) break;
-      if (clock64() - t0 > 8000000000ll) return ~0ull;
-      __nanosleep(100);
+      asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(&src->value) : "memory");
+      if ((v >> 48) == (pr.epoch & 0xFFFFull)) break;
+      if (clock64() - t0 > 8000000000ll) { ok = false; break; }
     }
-    unsigned long long v;
-    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(&s->value) : "memory");
-    sum += v;
+    v &= 0xFFFFFFFFFFFFull;
   }
-  return sum;
+  const bool all_ok = __all_sync(0xffffffffu, ok);
+  unsigned int lo = (unsigned int)v, hi = (unsigned int)(v >> 32);
+  unsigned long long sum = 0;
+  for (int r = 0; r < pr.world; ++r)  // world <= 16: a handful of shuffles, no 64-bit warp reduce needed
+    sum += ((unsigned long long)__shfl_sync(0xffffffffu, hi, r) << 32) | __shfl_sync(0xffffffffu, lo, r);
+  return all_ok ? sum : ~0ull;
 }
 
 // Block-level finish shared by all counting kernels: reduce (count, mask) over the CTA, add it into the context's
@@ -44,6 +49,7 @@ __device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (
   __shared__ unsigned long long sh_cnt[kThreads / 32];
   __shared__ uint32_t sh_mask[8];
   __shared__ bool sh_last;
+  __shared__ unsigned long long sh_tot;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (TYPES && threadIdx.x < 8) sh_mask[threadIdx.x] = 0u;
   const unsigned long long wsum = warp_sum_u32(my_count);
@@ -72,8 +78,14 @@ __device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (
     sh_last = (t == gridDim.x - 1);
     if (sh_last) {
       __threadfence();
-      unsigned long long tot = atomicExch(&s->total, 0ull);
-      if (pr.world > 1) tot = peer_allreduce_sum(tot, pr);
+      sh_tot = atomicExch(&s->total, 0ull);
+    }
+  }
+  __syncthreads();
+  if (sh_last && threadIdx.x < 32) {  // block-uniform branch; the first warp publishes
+    unsigned long long tot = sh_tot;
+    if (pr.world > 1) tot = peer_allreduce_sum(tot, pr);
+    if (threadIdx.x == 0) {
       out_d->count = tot;
       out_h->count = tot;
       out_d->flag = tot != 0;

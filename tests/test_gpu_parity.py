@@ -181,6 +181,7 @@ def test_update_logodds_multi_frame_equals_sequence(gv, oracle, n_real):
     """gvx_update_logodds_multi: several frames, each with its own pose, in one launch == the frames one by one"""
     dims, side = (128, 96, 80), 0.02
     frames = [_depth_frame(40 + k, 96, 64) for k in range(n_real)] + [np.zeros((0, 3), np.float32)]
+    frames[1], frames[2] = frames[1][:-3], frames[2][:-1001]  # frames 2.. start off the 4-point grid: unstaged path
     poses = [np.array([[0, 0, 1, 0.05 * (k % 9)], [-1, 0, 0, 0.5], [0, -1, 0, 0.4 + 0.02 * (k % 7)]], np.float32) for k in range(n_real)]
     poses.append(np.array([[1, 0, 0, 9.0], [0, 1, 0, 0], [0, 0, 1, 0]], np.float32))  # empty frame, sensor outside
     poses[3][0, 3] = -0.5  # sensor origin outside the map: that frame must contribute nothing
