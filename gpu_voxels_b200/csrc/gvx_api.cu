@@ -547,6 +547,14 @@ int gvx_update_logodds_multi(gvx_handle_t h, const float* xyz_sensor, int mem_ki
     fv.prefix[n_frames] = (uint32_t)acc;
     memcpy(fv.poses, poses12, (size_t)n_frames * 48);
     if (acc == 0) return GVX_OK;
+    // scheduling hint only: a frame whose sensor stands inside this slab will do most of the atomics; its CTAs go first
+    uint32_t k = 0;
+    const float zlo = (float)m->z0 * m->side, zhi = (float)m->z1 * m->side;
+    for (int pass = 0; pass < 2; ++pass)
+      for (uint32_t f = 0; f < n_frames; ++f) {
+        const float sz = poses12[12 * f + 11];
+        if (((sz >= zlo && sz < zhi) ? 0 : 1) == pass) fv.order[k++] = (uint8_t)f;
+      }
     if (!xyz_sensor) return fail(GVX_ERR_INVALID, "null point pointer");
     const float* xyz_d = nullptr;
     int rc = points_to_device(xyz_sensor, acc, mem_kind, &xyz_d);

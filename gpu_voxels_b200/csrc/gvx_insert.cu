@@ -328,7 +328,7 @@ k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t*
 // three FMAs and one division.
 __global__ void __launch_bounds__(kInsThreads)
 k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_constant__ FramesByValue fv, int delta) {
-  const uint32_t f = blockIdx.y;
+  const uint32_t f = fv.order[blockIdx.y];
   float P[12];
 #pragma unroll
   for (int k = 0; k < 12; ++k) P[k] = fv.poses[12 * f + k];
@@ -541,9 +541,9 @@ cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, co
       const uint32_t len = by_value->prefix[f + 1] - by_value->prefix[f];
       if (len > longest) longest = len;
     }
-    int gx = grid_for(c, (longest + 3) / 4, 8);  // 4 points per thread and step
-    const int per_frame = (c.sm_count * 8 + (int)n_frames - 1) / (int)n_frames;  // the device holds sm_count * 8 CTAs
-    if (gx > per_frame) gx = per_frame;
+    // 4 points per thread and step. The grid is NOT divided among the frames: on a z-slab rank most frames belong to
+    // other slabs and their CTAs retire after one read, leaving the SMs to the frame(s) that do the atomics
+    int gx = grid_for(c, (longest + 3) / 4, 8);
     k_update_logodds_frames<<<dim3((unsigned)gx, n_frames), kInsThreads, 0, c.stream>>>(m, xyz_d, *by_value, delta);
   } else {
     k_update_logodds_multi<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, prefix_d, poses_d, n_frames, delta);

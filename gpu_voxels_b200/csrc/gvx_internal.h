@@ -57,6 +57,7 @@ constexpr int kMaxFramesByValue = 16;
 struct FramesByValue {  // a small multi-frame description passed in the kernel parameters
   uint32_t prefix[kMaxFramesByValue + 1];
   float poses[kMaxFramesByValue * 12];
+  uint8_t order[kMaxFramesByValue];  // blockIdx.y -> frame: frames whose sensor sits inside this slab are scheduled first
 };
 // by_value != nullptr (n_frames <= kMaxFramesByValue): prefix_d / poses_d are ignored
 cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
