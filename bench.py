@@ -291,6 +291,24 @@ def run_gpu_arm(args):
             p = ptr_of[t.data_ptr()] = C.c_void_p(t.data_ptr())
         return p
 
+    # sharded: every rank integrates ITS sensor's frame; hits are routed to the rank owning the voxel inside the
+    # update kernel over NVLink peer memory (gvx_update_logodds_dispatch). --fold multi: every rank reads all frames
+    # and keeps its slab's points (gvx_update_logodds_multi; the e2e arm then all-gathers the frames with NCCL)
+    dispatch = False
+    if world > 1 and args.fold != "multi":
+        from gpu_voxels_b200 import sharding
+        dispatch = sharding.connect_peer_dispatch(N_FRAME)
+        zb_arr = sharding.slab_bounds(DZ * world, world)
+        zb_p = zb_arr.ctypes.data_as(C.c_void_p)
+        own_pose_p = pose_arr[rank].ctypes.data_as(C.c_void_p)
+
+    # device-resident frames on 2 ranks: reading both frames (12.5 us) is cheaper than the exchange (14.9 us, measured);
+    # from 4 ranks on the exchange wins (22.9 us vs 15 us at 8). Host frames: the exchange always wins (no all-gather)
+    dispatch_resident = dispatch and (args.fold == "dispatch" or world > 2)
+
+    def fold_own(points, k, mem_kind):
+        _lib.check(L.gvx_update_logodds_dispatch(env_h[k % P], dev_ptr(points), N_FRAME, mem_kind, own_pose_p, 72, zb_p))
+
     def fold_frames(points_d, k):
         """log-odds update of ALL sub-frames (each with its own pose) in one launch; this rank keeps its slab's points"""
         if world == 1:
@@ -316,7 +334,10 @@ def run_gpu_arm(args):
 
     def step_device(k):
         """inputs resident in HBM; result stays on the device (all-reduced when sharded)"""
-        fold_frames(cat_d[k % P], k)
+        if dispatch_resident:
+            fold_own(frames_d[k % P][rank], k, _lib.MEM_DEVICE)
+        else:
+            fold_frames(cat_d[k % P], k)
         collide_global(k)
 
     def step_e2e(k):
@@ -324,9 +345,12 @@ def run_gpu_arm(args):
         rank uploads ITS sensor's frame from pinned host memory and the frames are all-gathered over NVLink (each
         rank needs the whole cloud to find its slab's points), instead of N x the PCIe traffic per rank."""
         if world > 1:
-            own_d.copy_(pinned[k % P][rank], non_blocking=True)
-            dist.all_gather_into_tensor(gathered, own_d)
-            fold_frames(gathered, k)
+            if dispatch:
+                fold_own(pinned[k % P][rank], k, _lib.MEM_HOST)
+            else:
+                own_d.copy_(pinned[k % P][rank], non_blocking=True)
+                dist.all_gather_into_tensor(gathered, own_d)
+                fold_frames(gathered, k)
             if fused:
                 cnt = C.c_uint64(0)
                 collide_global(k, C.byref(cnt))
@@ -417,7 +441,9 @@ def run_gpu_arm(args):
         # in-kernel all-reduce, and an empty-kernel-free measure of the host's launch rate (the same calls, GPU idle)
         def t_loop(fn):
             return timed(fn, args.steps) / args.steps * 1e3
-        d = {"fold_us": t_loop(lambda k: fold_frames(cat_d[k % P], k)),
+        d = {"fold": "dispatch" if dispatch_resident else "multi",
+             "fold_us": t_loop((lambda k: fold_own(frames_d[k % P][rank], k, _lib.MEM_DEVICE)) if dispatch_resident else
+                               (lambda k: fold_frames(cat_d[k % P], k))),
              "collide_local_us": t_loop(lambda k: _lib.check(L.gvx_collide_map_map_async(
                  envs[k % P].handle, robs[k % P].handle, THR, None, 1, C.c_void_p(count_d.data_ptr())))),
              "collide_global_us": t_loop(lambda k: collide_global(k)),
@@ -454,8 +480,10 @@ def run_gpu_arm(args):
             "config": workload_config(world),
             "e2e": {"value": n_vox * world * args.steps / (ms_e2e * 1e-3), "unit": "voxels/s",
                     "h2d_bytes_per_step": N_FRAME * 12 * world + 48 * world, "d2h_bytes_per_step": 8 * world,
-                    "note": "per step, summed over ranks: every rank uploads its own sensor frame (pinned -> HBM), frames "
-                            "are all-gathered over NVLink, the count is all-reduced and read back by every rank",
+                    "note": "per step, summed over ranks: every rank uploads its own sensor frame (pinned -> HBM); " +
+                            ("hits in other ranks' slabs are routed there inside the update kernel over NVLink peer memory, "
+                             if dispatch else "frames are all-gathered over NVLink (NCCL), ") +
+                            "the count is all-reduced and read back by every rank",
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "k_collide_summary2<Prob,Bit,mark>", "achieved": achieved, "peak": peak,
@@ -480,6 +508,10 @@ def run_gpu_arm(args):
                        "unit": "points/s", "ms_per_frame": ins_ms, "points": N_FRAME},
             "clocks": clk.summary(), "collisions_last_step": int(last_count),
             "count_allreduce": ("in-kernel over NVLink peer memory" if fused else "nccl") if world > 1 else "none",
+            "frame_exchange": ({"value": "in-kernel dispatch over NVLink peer memory" if dispatch_resident else
+                                         "every rank folds all frames",
+                                "e2e": "in-kernel dispatch over NVLink peer memory" if dispatch else
+                                       "NCCL all-gather of the frames, every rank folds all frames"} if world > 1 else "none"),
         }
         if cpu is not None:
             line["cpu_baseline"] = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -497,6 +529,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--diag", action="store_true", help="print a per-phase timing breakdown to stderr")
     ap.add_argument("--nccl-count", action="store_true", help="all-reduce the count with NCCL instead of in-kernel")
+    ap.add_argument("--fold", default="auto", choices=["auto", "dispatch", "multi"],
+                    help="sharded runs: route each rank's frame to the owning ranks in-kernel (dispatch), fold all frames on "
+                         "every rank (multi), or auto: dispatch for host frames and, from 4 ranks on, for resident frames")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

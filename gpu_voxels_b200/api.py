@@ -343,6 +343,20 @@ def _insert_sensor_data_multi(self, frames, sensor_poses, delta_occupied=72):
 ProbVoxelMap.insertSensorDataMulti = _insert_sensor_data_multi
 
 
+def _insert_sensor_data_dispatch(self, points_sensor_frame, sensor_pose, z_bounds, delta_occupied=72):
+    """COLLECTIVE (one process per GPU, z-slab maps, sharding.connect_peer_dispatch done): this rank's sensor frame;
+    hits are routed to the rank owning the voxel inside the kernel over NVLink peer memory
+    (gvx_update_logodds_dispatch). z_bounds: sharding.slab_bounds(dz, world)."""
+    p, n, kind, keep = _points_arg(points_sensor_frame)
+    pose = np.ascontiguousarray(np.asarray(sensor_pose, np.float32).reshape(-1)[:12])
+    zb = np.ascontiguousarray(z_bounds, np.uint32)
+    _lib.check(self._L.gvx_update_logodds_dispatch(self.handle, p, n, kind, pose.ctypes.data_as(C.c_void_p),
+                                                   int(delta_occupied), zb.ctypes.data_as(C.c_void_p)))
+
+
+ProbVoxelMap.insertSensorDataDispatch = _insert_sensor_data_dispatch
+
+
 GVX_OPT_USE_SUMMARY = 1
 GVX_OPT_DH_CHECK_BITS = 2
 REVOLUTE, PRISMATIC = 0, 1  # robot::DHJointType, GV/robot/dh_robot/KinematicLink.h:37-41

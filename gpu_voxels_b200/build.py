@@ -10,7 +10,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgvx.so")
 SOURCES = ["gvx_api.cu", "gvx_api_list.cu", "gvx_api_batch.cu", "gvx_collide.cu", "gvx_insert.cu", "gvx_list.cu",
-           "gvx_batch.cu", "gvx_kinematics.cu", "gvx_sweptvolume.cu", "gvx_listlist.cu", "gvx_api_io.cu"]
+           "gvx_batch.cu", "gvx_kinematics.cu", "gvx_sweptvolume.cu", "gvx_listlist.cu", "gvx_api_io.cu",
+           "gvx_dispatch.cu", "gvx_api_dispatch.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--ftz=false", "--prec-div=true", "--prec-sqrt=true", "--fmad=true"]
 

@@ -55,6 +55,7 @@ int gvx_shutdown(void) {
   }
   g.maps.clear();
   lists_free_all();
+  dispatch_free_all();
   for (auto& kv : g.buffers) if (kv.second.p) cudaFree(kv.second.p);
   g.buffers.clear();
   for (void** p : {&g.bat_bits, &g.bat_seen, &g.bat_tr, &g.bat_counts}) { if (*p) cudaFree(*p); *p = nullptr; }

@@ -90,6 +90,15 @@ struct Context {
   PeerSlot* peer_ptr[kMaxPeers] = {};
   int peer_rank = 0, peer_world = 1;
   unsigned long long peer_epoch = 0;
+  // sensor-frame dispatch over NVLink peer memory (gvx_peer_dispatch_*, gvx_dispatch.cu): this rank's head + inboxes,
+  // the peers' allocations mapped through CUDA IPC, the collective sequence number, a mapped host word for time-outs
+  unsigned char* disp_mem = nullptr;
+  unsigned char* disp_ptr[kMaxPeers] = {};
+  uint32_t disp_capacity = 0;
+  int disp_world_alloc = 0, disp_rank = 0, disp_world = 1;
+  bool disp_connected = false;
+  unsigned long long disp_epoch = 0;
+  uint32_t* disp_err_h = nullptr; uint32_t* disp_err_hmap_d = nullptr;
   bool use_summary = true;  // GVX_OPT_USE_SUMMARY: collide kernels may read occupancy summaries instead of voxels
   uint64_t launches = 0;
   uint64_t next_handle = 1;
@@ -102,6 +111,7 @@ struct Context {
 
 extern Context g;
 void lists_free_all();  // gvx_api_list.cu
+void dispatch_free_all();  // gvx_api_dispatch.cu
 extern thread_local std::string t_err;
 
 inline int fail(int code, const char* fmt, ...) {

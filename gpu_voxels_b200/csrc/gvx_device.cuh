@@ -111,6 +111,31 @@ struct PeerReduce {
   int world;
   unsigned long long epoch;  // > 0, identical on all ranks for one collective, strictly increasing
 };
+// Sensor-frame dispatch over NVLink peer memory (gvx_update_logodds_dispatch, gvx_dispatch.cu; one process per GPU,
+// z-slab maps). Every rank owns ONE allocation, mapped into all peers through CUDA IPC: a DispatchHead followed by
+// the inboxes, uint32 entries[2 (epoch parity)][world (source rank)][capacity]. An entry is the slab-local linear
+// index of a voxel that receives one log-odds hit.
+//   ready[p][s]  written by source s into the DESTINATION's head: epoch16 << 48 | number of entries s stored into
+//                inbox[p][s] for this epoch (a release after the entries);
+//   ack[d]       written by destination d into the SOURCE's head: the last epoch whose entries d has consumed; the
+//                source must see ack[d] + 2 >= epoch before it overwrites inbox[epoch & 1] at d (credit);
+//   counters, ticket: local bookkeeping of the owner's kernel, self-resetting.
+struct DispatchHead {
+  unsigned long long ready[2][kMaxPeers];
+  unsigned long long ack[kMaxPeers];
+  unsigned int counters[kMaxPeers];
+  unsigned int ticket_sent, pad_[3];
+};
+constexpr size_t kDispatchHeadBytes = 1024;
+static_assert(sizeof(DispatchHead) <= kDispatchHeadBytes, "dispatch head grew beyond its slot");
+struct PeerDispatch {
+  unsigned char* base[kMaxPeers];  // rank r's allocation as mapped into this process
+  uint32_t z_bounds[kMaxPeers + 1];  // rank r owns global z in [z_bounds[r], z_bounds[r + 1])
+  uint32_t capacity;               // entries per (parity, source) inbox
+  int rank;
+  int world;
+  unsigned long long epoch;        // > 0, identical on all ranks for one collective call, strictly increasing
+};
 constexpr int kMaxGrid = 148 * 16;  // upper bound on CTAs of a reducing kernel
 struct ReduceScratch {
   unsigned long long total;  // sum of the CTAs' counts; taken (and zeroed) by the last CTA

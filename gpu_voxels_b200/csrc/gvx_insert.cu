@@ -13,10 +13,9 @@
 // probabilistic log-odds update is a saturating add applied with one CAS per (voxel) group of a warp, so
 // results equal the sequential (race-free) semantics and are deterministic.
 #include "gvx_internal.h"
+#include "gvx_sensor.cuh"
 
 namespace gvx {
-
-constexpr int kInsThreads = 256;
 
 __device__ __forceinline__ int8_t prob_insert_value(int meaning) {
   // ProbabilisticVoxel::insert, GV/voxel/ProbabilisticVoxel.hpp:77-92
@@ -112,35 +111,6 @@ k_transform(const float* __restrict__ in, float* __restrict__ out, unsigned long
     const float x = in[3 * i], y = in[3 * i + 1], z = in[3 * i + 2];
     const float tx = affine_row(M, x, y, z), ty = affine_row(M + 4, x, y, z), tz = affine_row(M + 8, x, y, z);
     out[3 * i] = tx; out[3 * i + 1] = ty; out[3 * i + 2] = tz;
-  }
-}
-
-// Saturating int8 add on one byte of the map with a 32-bit CAS. For same-sign deltas,
-// clamp(occ + k*delta, -127, 127) equals k sequential ProbabilisticVoxel::updateOccupancy calls
-// (GV/voxel/ProbabilisticVoxel.hpp:51-57), so a warp's duplicates are folded into one update.
-__device__ __forceinline__ void logodds_add(int8_t* map, uint64_t idx, int total_delta) {
-  uint32_t* wp = reinterpret_cast<uint32_t*>(map + (idx & ~3ull));
-  const int shift = (int)(idx & 3ull) * 8;
-  uint32_t old = *wp, assumed;
-  do {
-    assumed = old;
-    int v = (int)(int8_t)((assumed >> shift) & 0xFFu) + total_delta;
-    v = v < -127 ? -127 : (v > 127 ? 127 : v);
-    const uint32_t nw = (assumed & ~(0xFFu << shift)) | (((uint32_t)v & 0xFFu) << shift);
-    if (nw == assumed) break;
-    old = atomicCAS(wp, assumed, nw);
-  } while (old != assumed);
-}
-
-// kernelTransformSensorData, GV/voxelmap/kernels/VoxelMapOperations.cu:27-71: pose * raw point; a point that lands below
-// z = 0 is pulled back along its ray onto the floor with a DOUBLE factor
-__device__ __forceinline__ void sensor_to_world(const float* __restrict__ P, float rx, float ry, float rz, float& wx,
-                                                float& wy, float& wz) {
-  wx = affine_row(P, rx, ry, rz); wy = affine_row(P + 4, rx, ry, rz); wz = affine_row(P + 8, rx, ry, rz);
-  if (wz < 0.0f) {
-    const double factor = (double)__fdiv_rn(P[11], __fsub_rn(P[11], wz));
-    const float qx = (float)((double)rx * factor), qy = (float)((double)ry * factor), qz = (float)((double)rz * factor);
-    wx = affine_row(P, qx, qy, qz); wy = affine_row(P + 4, qx, qy, qz); wz = affine_row(P + 8, qx, qy, qz);
   }
 }
 

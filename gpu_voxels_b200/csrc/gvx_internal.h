@@ -63,6 +63,10 @@ struct FramesByValue {  // a small multi-frame description passed in the kernel 
 cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
                                         const uint32_t* prefix_d, const float* poses_d, uint32_t n_frames, int delta,
                                         const FramesByValue* by_value = nullptr);
+// one frame per rank on a z-slab map; hits are routed to the owning rank inside the kernel (gvx_dispatch.cu)
+cudaError_t launch_update_logodds_dispatch(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
+                                           const Affine12& pose, int delta, const PeerDispatch& pd,
+                                           uint32_t* error_hmap_d);
 // voxel &= ~mask for all voxels; occ (nullable): summary words rewritten from the result
 cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8], uint32_t* occ);
 

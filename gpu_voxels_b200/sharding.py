@@ -24,6 +24,12 @@ def slab_for_rank(dz, rank, world):
     return z0, z0 + base + (1 if rank < rem else 0)
 
 
+def slab_bounds(dz, world):
+    """world + 1 slab boundaries: rank r owns z in [bounds[r], bounds[r + 1]) (the z_bounds argument of
+    gvx_update_logodds_dispatch)"""
+    return np.asarray([slab_for_rank(dz, r, world)[0] for r in range(world)] + [int(dz)], np.uint32)
+
+
 def voxel_range_for_rank(dims, rank, world):
     """linear voxel indices [first, first + n) held by `rank`"""
     z0, z1 = slab_for_rank(dims[2], rank, world)
@@ -121,6 +127,54 @@ def allgather_batch_counts(local_counts, n_cfg, group=None):
         c0, c1 = batch_range_for_rank(n_cfg, r, world)
         out[c0:c1] = parts[r].cpu().numpy()[: c1 - c0].astype(np.uint64)
     return out
+
+
+def _exchange_ipc(create, connect, disconnect, group=None):
+    """create() -> (rc, 64-byte handle); handles all-gathered; connect(rank, world, blob) -> rc. True when every rank
+    succeeded; on any failure every rank disconnects and the caller keeps the NCCL path."""
+    import torch
+    dist = _dist()
+    if not dist.is_initialized() or dist.get_world_size(group) < 2:
+        return False
+    dev = _device_for_backend()
+    rc, mine = create()
+    ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+    if not ok.item():
+        return False
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    t = torch.tensor(list(bytes(mine)), dtype=torch.uint8, device=dev)
+    parts = [torch.zeros(64, dtype=torch.uint8, device=dev) for _ in range(world)]
+    dist.all_gather(parts, t, group=group)
+    blob = b"".join(bytes(p.cpu().numpy().tobytes()) for p in parts)
+    rc = connect(rank, world, blob)
+    ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+    if not ok.item():
+        disconnect()
+        return False
+    dist.barrier(group=group)
+    return True
+
+
+def connect_peer_dispatch(capacity_points, group=None):
+    """Set up the sensor-frame dispatch (gvx_update_logodds_dispatch / ProbVoxelMap.insertSensorDataDispatch): every rank
+    allocates its inboxes (world sources x capacity_points hits, double-buffered), the CUDA IPC handles are exchanged
+    with one all_gather, every rank maps its peers. Returns True when connected."""
+    import ctypes as C
+    from . import _lib
+    dist = _dist()
+    if not dist.is_initialized():
+        return False
+    L = _lib.init()
+    world = dist.get_world_size(group)
+
+    def create():
+        mine = (C.c_ubyte * 64)()
+        return L.gvx_peer_dispatch_create(world, int(capacity_points), mine), mine
+
+    return _exchange_ipc(create, lambda r, w, blob: L.gvx_peer_dispatch_connect(r, w, C.c_char_p(blob)),
+                         L.gvx_peer_dispatch_disconnect, group)
 
 
 def connect_peer_mailboxes(group=None):

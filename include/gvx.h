@@ -230,6 +230,26 @@ int gvx_collide_map_map_allreduce(gvx_handle_t a, gvx_handle_t b, float thr, int
 int gvx_collide_list_map_allreduce(gvx_handle_t list, gvx_handle_t map, float thr, int mark, uint64_t* count,
                                    uint64_t* count_d);
 
+/* ---- multi-GPU: sensor frames routed to the rank that owns the voxel, INSIDE the update kernel ---------------- */
+/* insertSensorData (log-odds hits, ProbVoxelMap::insertSensorData GV/voxelmap/ProbVoxelMap.hpp:52-102 without ray
+ * casting) on a map cut into z-slabs, one sensor per rank: every rank transforms and voxelises only ITS frame; hits
+ * inside its slab are applied at once, a hit in another rank's slab is stored as a 32-bit slab-local voxel index into
+ * an inbox in that rank's HBM (CUDA IPC mapping, NVLink), and the same kernel then applies what the other ranks sent.
+ * The all-to-all is part of the kernel: no all-gather of the frames, no second launch, work per rank independent of
+ * the number of ranks. The slab ends up byte-identical to that slice of the map the reference builds from all frames
+ * (equal-sign saturating updates commute).
+ * create: this rank's inboxes for `world` sources of up to capacity_points hits each (double-buffered), exported as
+ * a 64-byte CUDA IPC handle; connect: map all peers (handles in rank order); collective calls from then on. */
+int gvx_peer_dispatch_create(int world, uint64_t capacity_points, void* ipc_handle64_out);
+int gvx_peer_dispatch_connect(int rank, int world, const void* all_handles /* world x 64 bytes, rank order */);
+int gvx_peer_dispatch_disconnect(void);
+/* COLLECTIVE: every connected rank calls it, in the same order, also with n == 0. xyz_sensor: this rank's frame
+ * (n <= capacity_points) in the sensor frame, pose12 its row-major [R|t]; z_bounds (host, world + 1 entries): rank r
+ * owns global z in [z_bounds[r], z_bounds[r + 1]). Not connected: the plain gvx_update_logodds.
+ * Asynchronous; a rank that does not arrive within ~4 s makes the NEXT dispatch call return GVX_ERR_CUDA. */
+int gvx_update_logodds_dispatch(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int mem_kind,
+                                const float pose12[12], int delta_occ, const uint32_t* z_bounds);
+
 /* ---- voxel lists (BitVectorVoxelList) ----------------------------------------------------------------- */
 /* GpuVoxels::addMap(MT_BITVECTOR_VOXELLIST) -> TemplateVoxelList ctor (GV/GpuVoxels.cpp:213-221,
  * GV/voxellist/TemplateVoxelList.hpp:67-86). Storage is the reference's SoA: id[u32] = linear voxel index,

@@ -5,7 +5,8 @@ Checks, bit-exactly against the CPU oracle on the unsharded grid:
   * z-slab shards of Prob and BitVector maps filled from the whole cloud,
   * collideWith with the count all-reduced INSIDE the kernel over NVLink peer memory == NCCL all-reduce == oracle,
     repeated (epoch parity double-buffering), map x map and list x map,
-  * batch of robot configurations split over ranks and all-gathered.
+  * batch of robot configurations split over ranks and all-gathered,
+  * sensor frames routed to the owning rank inside the update kernel (dispatch over peer memory) == multi-frame fold.
 """
 import ctypes as C
 import os
@@ -97,9 +98,52 @@ def main():
     orc.insert_points(r_full, BIT, dims, side, env_pts, 1)
     w = orc.batch_robot_collide(r_full, BIT, dims, side, np.concatenate(links), [4000, 3000], [4, 5], T, None, 1.0)
     assert np.array_equal(allc, w), (allc, w)
+    # sensor frames routed to the owning rank inside the update kernel (gvx_update_logodds_dispatch): one frame per
+    # rank per step, most hits land in OTHER ranks' slabs; 6 steps (both inbox parities, credits, saturation at 127),
+    # ragged frame sizes incl. an empty frame; result == the slab of the oracle's unsharded map == the multi-frame fold
+    n_max = 60000
+    assert sharding.connect_peer_dispatch(n_max), "CUDA IPC dispatch inboxes could not be connected"
+    zb = sharding.slab_bounds(dims[2], world)
+    d_env = gv.ProbVoxelMap(dims, side, slab=slab)
+    m_env = gv.ProbVoxelMap(dims, side, slab=slab)
+    o_env = orc.new_map(PROB, dims)
+    for step in range(6):
+        frames, poses = [], []
+        for r in range(world):
+            fr = np.random.Generator(np.random.PCG64(1000 + 31 * step + r))
+            k = 0 if (step == 2 and r == world - 1) else int(fr.integers(n_max // 2, n_max + 1))
+            pts = fr.uniform(-0.6, 0.6, size=(k, 3)).astype(np.float32)
+            pts[: k // 3] = (pts[: k // 3] * 0.05).astype(np.float32)  # a dense clump: many hits per voxel -> saturation
+            pts[k // 2: k // 2 + 50] = np.nan
+            pose = np.eye(4, dtype=np.float32)[:3].copy()
+            pose[:, 3] = (0.5, 0.4, 0.05 + 0.9 * (r + 0.5) / world)
+            if step == 4 and r == 0:
+                pose[:, 3] = (0.5, 0.4, 1.5)   # sensor outside the map: the whole frame is ignored
+            frames.append(pts); poses.append(pose)
+        d_env.insertSensorDataDispatch(frames[rank], poses[rank], zb)
+        m_env.insertSensorDataMulti(frames, poses)
+        for r in range(world):
+            orc.update_logodds(o_env, dims, side, frames[r], poses[r])
+    got_d, got_m = d_env.download(), m_env.download()
+    assert np.array_equal(got_m, o_env[first:first + n_loc]), "multi-frame fold differs from the oracle"
+    assert np.array_equal(got_d, o_env[first:first + n_loc]), "dispatch differs from the oracle: %d voxels" % int((got_d != o_env[first:first + n_loc]).sum())
+    assert (o_env == 127).sum() > 10 and (o_env != -128).sum() > 50000
+    # summaries stay in sync: the summary-path collide equals the voxel-streaming one
+    c_sum = d_env.collideWith(rob, 0.3, mark=False)
+    gv.set_option(gv.GVX_OPT_USE_SUMMARY, 0)
+    c_str = d_env.collideWith(rob, 0.3, mark=False)
+    gv.set_option(gv.GVX_OPT_USE_SUMMARY, 1)
+    assert c_sum == c_str
+    # back to back without host syncs, all ranks in lock step only through the kernels themselves
+    for step in range(25):
+        d_env.insertSensorDataDispatch(frames[rank][: 1000 * (1 + (step + rank) % 7)], poses[rank], zb)
+    _lib.check(L.gvx_sync())
+    d_env.insertSensorDataDispatch(frames[rank][:0], poses[rank], zb)   # reports a time-out of the run above, if any
+    _lib.check(L.gvx_sync())
+    _lib.check(L.gvx_peer_dispatch_disconnect())
     dist.barrier()
     if rank == 0:
-        print("multi_gpu_check ok: world %d, fused in-kernel all-reduce == NCCL == oracle (%d, list %d), batch split ok" % (world, want, l_want))
+        print("multi_gpu_check ok: world %d, fused in-kernel all-reduce == NCCL == oracle (%d, list %d), batch split ok, frame dispatch == multi-frame fold == oracle" % (world, want, l_want))
     _lib.check(L.gvx_peer_mailbox_disconnect())
     dist.destroy_process_group()
 

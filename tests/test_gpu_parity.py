@@ -321,3 +321,41 @@ def test_c2_full_size_properties(gv, oracle):
     assert rob.collideWith(env, 1.0, mark=False) == want  # only eBVM_COLLISION is left on the colliding voxels
     rob.clearMap()
     assert rob.collideWith(env, 1.0) == 0
+
+
+def test_dispatch_entry_point_on_one_rank(gv, oracle):
+    """gvx_update_logodds_dispatch without peers: unconnected it is the plain update; connected with world 1 the
+    dispatch kernel runs its local phase only. (The exchange itself needs one GPU per rank: tests/multi_gpu_check.py.)"""
+    import ctypes as C
+    from gpu_voxels_b200 import _lib
+    L = _lib.init()
+    dims, side = (64, 48, 40), 0.02
+    rng = np.random.Generator(np.random.PCG64(77))
+    pts = rng.uniform(-0.7, 0.7, size=(50000, 3)).astype(np.float32)
+    pts[:20000] *= np.float32(0.03)
+    pts[100:130] = np.nan
+    pose = np.eye(4, dtype=np.float32)[:3].copy()
+    pose[:, 3] = (0.6, 0.5, 0.4)
+    want = oracle.new_map(PROB, dims)
+    for _ in range(3):
+        oracle.update_logodds(want, dims, side, pts, pose)
+    zb = np.asarray([0, dims[2]], np.uint32)
+    a = gv.ProbVoxelMap(dims, side)
+    for _ in range(3):
+        a.insertSensorDataDispatch(pts, pose, zb)
+    assert np.array_equal(a.download(), want)
+    handle = (C.c_ubyte * 64)()
+    _lib.check(L.gvx_peer_dispatch_create(1, 50000, handle))
+    _lib.check(L.gvx_peer_dispatch_connect(0, 1, None))
+    try:
+        b = gv.ProbVoxelMap(dims, side)
+        for _ in range(3):
+            b.insertSensorDataDispatch(pts, pose, zb)
+        assert np.array_equal(b.download(), want)
+        assert b.collideWith(a, 0.9, mark=False) == oracle.collide_map_map(want.copy(), PROB, want, PROB, want.size, 0.9, 0, False)
+        with pytest.raises(gv.GvxError):   # more points than the inboxes hold
+            b.insertSensorDataDispatch(np.zeros((50001, 3), np.float32), pose, zb)
+        with pytest.raises(gv.GvxError):   # bounds that do not describe the map
+            b.insertSensorDataDispatch(pts, pose, np.asarray([0, dims[2] - 1], np.uint32))
+    finally:
+        _lib.check(L.gvx_peer_dispatch_disconnect())
