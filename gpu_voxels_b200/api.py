@@ -53,6 +53,45 @@ def _points_arg(points):
     return a.ctypes.data_as(C.c_void_p), len(a), MEM_HOST, a
 
 
+def _offset_arg(offset_XYZ):
+    if offset_XYZ is None:
+        return None, None
+    a = np.ascontiguousarray(offset_XYZ, dtype=np.float32).reshape(3)
+    return a.ctypes.data_as(C.c_void_p), a
+
+
+class PointcloudFileHandler:
+    """file_handling::PointcloudFileHandler (GV/helpers/PointcloudFileHandler.h:40-100, .cpp:64-137): .xyz / .pcd /
+    .binvox files -> points. Host only (no GPU, no gvx_init needed)."""
+    _instance = None
+
+    @classmethod
+    def Instance(cls):
+        if cls._instance is None:
+            cls._instance = cls()
+        return cls._instance
+
+    def loadPointCloud(self, path, use_model_path, points=None, shift_to_zero=False, offset_XYZ=None, scaling=1.0):
+        """-> (ok, float32 array n x 3). `points` (an n x 3 array or None) is what the reference's output vector held
+        before the call: the loaded points are appended to it and shift / scaling / offset apply to all of them."""
+        if points is not None and len(points):
+            raise NotImplementedError("appending to a non-empty vector is only offered by the C++ facade")
+        L = _lib.load()
+        out, n = C.c_void_p(), C.c_uint64()
+        off, keep = _offset_arg(offset_XYZ)
+        rc = L.gvx_pointcloud_file_load(str(path).encode(), int(bool(use_model_path)), int(bool(shift_to_zero)), off,
+                                        float(scaling), C.byref(out), C.byref(n))
+        if rc != 0:
+            _log_error(L.gvx_last_error().decode())
+            return False, np.zeros((0, 3), np.float32)
+        try:
+            a = np.ctypeslib.as_array(C.cast(out, C.POINTER(C.c_float)), shape=(n.value, 3)).copy() if n.value else \
+                np.zeros((0, 3), np.float32)
+        finally:
+            L.gvx_pointcloud_file_free(out)
+        return True, a
+
+
 class BitVectorVoxel:
     """256-bit meaning set (GV/voxel/BitVoxel.h:38-108); .bytes is the reference's uint8_t[32] layout."""
 
@@ -226,6 +265,23 @@ class GpuVoxelsMap:
             return False
         _lib.check(rc)
         return bool(flag.value)
+
+    def insertPointCloudFromFile(self, path, use_model_path, voxel_meaning, shift_to_zero=False, offset_XYZ=None,
+                                 scaling=1.0):
+        """GpuVoxelsMap::insertPointCloudFromFile (GV/GpuVoxelsMap.cpp:36-49): False if the file cannot be read"""
+        off, keep = _offset_arg(offset_XYZ)
+        flag = C.c_int(0)
+        rc = self._L.gvx_insert_pointcloud_file(self.handle, str(path).encode(), int(bool(use_model_path)),
+                                                int(voxel_meaning), int(bool(shift_to_zero)), off, float(scaling),
+                                                C.byref(flag))
+        if rc in (_lib.ERR_IO, _lib.ERR_INVALID):
+            _log_error(self._L.gvx_last_error().decode())
+            return False
+        if rc == _lib.ERR_UNSUPPORTED:  # loaded, but the ProbVoxelMap insert is a logged no-op: still true there
+            _log_error(self._L.gvx_last_error().decode())
+            return True
+        _lib.check(rc)
+        return True
 
     def insertMetaPointCloud(self, meta_point_cloud, voxel_meanings, transforms=None, check_outside=True):
         """voxel_meanings: one BitVoxelMeaning or a list with one per sub-cloud (both reference overloads,
@@ -515,6 +571,14 @@ class GpuVoxels:
             return False
         m.insertPointCloud(cloud, voxel_meaning)
         return True
+
+    def insertPointCloudFromFile(self, map_name, path, use_model_path, voxel_meaning, shift_to_zero=False,
+                                 offset_XYZ=None, scaling=1.0):
+        """GpuVoxels::insertPointCloudFromFile (GV/GpuVoxels.cpp:427-440)"""
+        m = self.getMap(map_name)
+        if m is None:
+            return False
+        return m.insertPointCloudFromFile(path, use_model_path, voxel_meaning, shift_to_zero, offset_XYZ, scaling)
 
     def insertMetaPointCloudIntoMap(self, meta_point_cloud, map_name, voxel_meanings):
         m = self.getMap(map_name)

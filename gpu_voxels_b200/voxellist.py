@@ -10,7 +10,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from .api import (BitVectorVoxel, GpuVoxelsMap, MT_BITVECTOR_VOXELLIST, SSIZE_MAX, _log_error, _points_arg)
+from .api import (BitVectorVoxel, GpuVoxelsMap, MT_BITVECTOR_VOXELLIST, SSIZE_MAX, _log_error, _offset_arg, _points_arg)
 from ._lib import MEM_HOST
 
 
@@ -80,6 +80,18 @@ class BitVectorVoxelList:
     def insertPointCloud(self, points, voxel_meaning):
         p, n, kind, keep = _points_arg(points)
         _lib.check(self._L.gvx_list_insert_points(self.handle, p, n, kind, int(voxel_meaning)))
+
+    def insertPointCloudFromFile(self, path, use_model_path, voxel_meaning, shift_to_zero=False, offset_XYZ=None,
+                                 scaling=1.0):
+        """GpuVoxelsMap::insertPointCloudFromFile (GV/GpuVoxelsMap.cpp:36-49) on a list"""
+        off, keep = _offset_arg(offset_XYZ)
+        rc = self._L.gvx_list_insert_pointcloud_file(self.handle, str(path).encode(), int(bool(use_model_path)),
+                                                     int(voxel_meaning), int(bool(shift_to_zero)), off, float(scaling))
+        if rc in (_lib.ERR_IO, _lib.ERR_INVALID):
+            _log_error(self._L.gvx_last_error().decode())
+            return False
+        _lib.check(rc)
+        return True
 
     def insertMetaPointCloud(self, meta_point_cloud, voxel_meanings):
         sizes = np.asarray(meta_point_cloud.getPointcloudSizes(), np.uint32)

@@ -1,10 +1,10 @@
 // gpu_voxels/GpuVoxels.h -- the GpuVoxels singleton of the reference's API for the hot path
 // (GV/GpuVoxels.h:91-415, GV/GpuVoxels.cpp:33-78,164-313,443-559,594-609), header-only over the C ABI (include/gvx.h).
 // Source-compatible for: getInstance, initialize, addMap, delMap, getMap, clearMap x2, insertPointCloudIntoMap x2,
-// insertMetaPointCloudIntoMap x2, insertBoxIntoMap, getDimensions x2, getVoxelSideLength; the returned maps provide
+// insertMetaPointCloudIntoMap x2, insertPointCloudFromFile, insertBoxIntoMap, getDimensions x2, getVoxelSideLength; the returned maps provide
 // collideWith / collideWithTypes / collideWithTypeMask / collideWithBitcheck, the swept-volume shift and the file
 // formats; DH-chain robots (addRobot with a MetaPointCloud, setRobotConfiguration, insertRobotIntoMap). Visualisation,
-// URDF robots, octrees, distance maps, primitive arrays and point-cloud file loaders are outside this build
+// URDF robots, octrees, distance maps and primitive arrays are outside this build
 // (SURVEY.md section 8).
 #ifndef GPU_VOXELS_B200_GPUVOXELS_H
 #define GPU_VOXELS_B200_GPUVOXELS_H
@@ -136,6 +136,16 @@ public:
     it->second.map_shared_ptr->insertPointCloud(cloud, voxel_meaning);
     return true;
   }
+  // GV/GpuVoxels.cpp:427-440
+  bool insertPointCloudFromFile(const std::string map_name, const std::string path, const bool use_model_path,
+                                const BitVoxelMeaning voxel_meaning, const bool shift_to_zero = false,
+                                const Vector3f& offset_XYZ = Vector3f(), const float scaling = 1.0)
+  {
+    ManagedMapsIterator it = findMap(map_name);
+    if (it == m_managed_maps.end()) return false;
+    return it->second.map_shared_ptr->insertPointCloudFromFile(path, use_model_path, voxel_meaning, shift_to_zero,
+                                                               offset_XYZ, scaling);
+  }
   bool insertMetaPointCloudIntoMap(const MetaPointCloud& meta_point_cloud, std::string map_name,
                                    const std::vector<BitVoxelMeaning>& voxel_meanings)
   {
@@ -205,6 +215,20 @@ public:
       return false;
     }
     m_managed_robots[robot_name] = RobotInterfaceSharedPtr(new robot::KinematicChain(link_names, dh_params, pointclouds));
+    return true;
+  }
+  // link clouds loaded from files (GV/GpuVoxels.cpp:316-336)
+  bool addRobot(const std::string& robot_name, const std::vector<std::string>& link_names,
+                const std::vector<robot::DHParameters>& dh_params, const std::vector<std::string>& paths_to_pointclouds,
+                const bool use_model_path)
+  {
+    if (m_managed_robots.find(robot_name) != m_managed_robots.end())
+    {
+      LOGGING_ERROR_C(Gpu_voxels, GpuVoxels, "Robot with name '" << robot_name << "' already exists." << endl);
+      return false;
+    }
+    m_managed_robots[robot_name] =
+      RobotInterfaceSharedPtr(new robot::KinematicChain(link_names, dh_params, paths_to_pointclouds, use_model_path));
     return true;
   }
   RobotInterfaceSharedPtr getRobot(const std::string& rob_name)

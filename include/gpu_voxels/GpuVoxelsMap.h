@@ -41,6 +41,18 @@ public:
   virtual void insertMetaPointCloud(const MetaPointCloud& meta_point_cloud, BitVoxelMeaning voxel_meaning) = 0;
   virtual void insertMetaPointCloud(const MetaPointCloud& meta_point_cloud,
                                     const std::vector<BitVoxelMeaning>& voxel_meanings) = 0;
+  // GV/GpuVoxelsMap.cpp:36-49: load (.xyz / .pcd / .binvox), then insertPointCloud; false if the file cannot be read
+  bool insertPointCloudFromFile(const std::string path, const bool use_model_path, const BitVoxelMeaning voxel_meaning,
+                                const bool shift_to_zero = false, const Vector3f& offset_XYZ = Vector3f(),
+                                const float scaling = 1.0)
+  {
+    std::vector<Vector3f> points;
+    if (!file_handling::PointcloudFileHandler::Instance()->loadPointCloud(path, use_model_path, points, shift_to_zero,
+                                                                         offset_XYZ, scaling))
+      return false;
+    insertPointCloud(points, voxel_meaning);
+    return true;
+  }
   virtual void clearMap() = 0;
   virtual void clearBitVoxelMeaning(BitVoxelMeaning voxel_meaning) = 0;
   virtual std::size_t getMemoryUsage() const = 0;

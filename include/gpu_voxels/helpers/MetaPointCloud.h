@@ -4,12 +4,14 @@
 #ifndef GPU_VOXELS_B200_HELPERS_METAPOINTCLOUD_H
 #define GPU_VOXELS_B200_HELPERS_METAPOINTCLOUD_H
 
+#include <iostream>
 #include <map>
 #include <string>
 #include <vector>
 
 #include <gpu_voxels/helpers/GvxCall.h>
 #include <gpu_voxels/helpers/PointCloud.h>
+#include <gpu_voxels/helpers/PointcloudFileHandler.h>
 #include <gpu_voxels/helpers/cuda_datatypes.h>
 #include <gpu_voxels/logging/logging_gpu_voxels.h>
 
@@ -19,6 +21,40 @@ class MetaPointCloud
 {
 public:
   MetaPointCloud() : m_buf(0), m_dev(NULL), m_cap(0) { gvxEnsureInit(); }
+  // sub-clouds from .xyz / .pcd / .binvox files (GV/helpers/MetaPointCloud.cu:115-171)
+  explicit MetaPointCloud(const std::vector<std::string>& point_cloud_files, bool use_model_path)
+    : m_buf(0), m_dev(NULL), m_cap(0)
+  {
+    gvxEnsureInit();
+    addClouds(point_cloud_files, use_model_path);
+  }
+  explicit MetaPointCloud(const std::vector<std::string>& point_cloud_files,
+                          const std::vector<std::string>& point_cloud_names, bool use_model_path)
+    : m_buf(0), m_dev(NULL), m_cap(0)
+  {
+    gvxEnsureInit();
+    addClouds(point_cloud_files, use_model_path);
+    if (point_cloud_files.size() == point_cloud_names.size())
+    {
+      if (m_sizes.size() == point_cloud_names.size())
+        for (size_t i = 0; i < point_cloud_names.size(); ++i) m_names[uint16_t(i)] = point_cloud_names[i];
+    }
+    else
+      std::cerr << "<Error MetaPointCloud> Number of names differs to number of pointcloud files!" << std::endl;
+  }
+  // all files or none: the first unreadable file aborts and leaves the MetaPointCloud as it was
+  void addClouds(const std::vector<std::string>& point_cloud_files, bool use_model_path)
+  {
+    std::vector<std::vector<Vector3f> > clouds(point_cloud_files.size());
+    for (size_t i = 0; i < point_cloud_files.size(); ++i)
+      if (!file_handling::PointcloudFileHandler::Instance()->loadPointCloud(point_cloud_files[i], use_model_path, clouds[i]))
+      {
+        std::cerr << "<Error MetaPointCloud> Could not read file " << point_cloud_files[i] << std::endl;
+        return;
+      }
+    for (size_t i = 0; i < clouds.size(); ++i) addCloud(clouds[i], false);
+    syncToDevice();
+  }
   explicit MetaPointCloud(const std::vector<uint32_t>& point_cloud_sizes) : m_buf(0), m_dev(NULL), m_cap(0)
   {
     gvxEnsureInit();

@@ -4,9 +4,12 @@
 #ifndef GPU_VOXELS_B200_HELPERS_POINTCLOUD_H
 #define GPU_VOXELS_B200_HELPERS_POINTCLOUD_H
 
+#include <iostream>
+#include <string>
 #include <vector>
 
 #include <gpu_voxels/helpers/GvxCall.h>
+#include <gpu_voxels/helpers/PointcloudFileHandler.h>
 #include <gpu_voxels/helpers/cuda_datatypes.h>
 
 namespace gpu_voxels {
@@ -17,6 +20,18 @@ public:
   PointCloud() : m_buf(0), m_dev(NULL), m_cap(0) { gvxEnsureInit(); }
   explicit PointCloud(const std::vector<Vector3f>& points) : m_buf(0), m_dev(NULL), m_cap(0) { gvxEnsureInit(); update(points); }
   explicit PointCloud(const Vector3f* points, uint32_t size) : m_buf(0), m_dev(NULL), m_cap(0) { gvxEnsureInit(); update(points, size); }
+  // from a .xyz / .pcd / .binvox file (GV/helpers/PointCloud.cu:84-105); an unreadable file leaves the cloud empty
+  explicit PointCloud(const std::string& path_to_file, bool use_model_path = true) : m_buf(0), m_dev(NULL), m_cap(0)
+  {
+    gvxEnsureInit();
+    std::vector<Vector3f> points;
+    if (!file_handling::PointcloudFileHandler::Instance()->loadPointCloud(path_to_file, use_model_path, points))
+    {
+      std::cerr << "<Error PointCloud> Could not read file " << path_to_file << std::endl;
+      return;
+    }
+    update(points);
+  }
   PointCloud(const PointCloud& other) : m_buf(0), m_dev(NULL), m_cap(0) { update(&other); }
   PointCloud& operator=(const PointCloud& other) { if (this != &other) update(&other); return *this; }
   ~PointCloud() { if (m_buf) gvx_buffer_destroy(m_buf); }

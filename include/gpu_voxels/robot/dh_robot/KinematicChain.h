@@ -33,6 +33,20 @@ public:
       m_links[linknames[i]] = KinematicLinkSharedPtr(new KinematicLink(dh_params[i]));
     LOGGING_INFO_C(RobotLog, KinematicChain, "now handling " << m_links.size() << " links." << endl);
   }
+  // link clouds from .xyz / .pcd / .binvox files, each cloud NAMED BY ITS PATH: a link moves the cloud whose path equals
+  // the link's name (GV/robot/dh_robot/KinematicChain.cu:35-43)
+  KinematicChain(const std::vector<std::string>& linknames, const std::vector<robot::DHParameters>& dh_params,
+                 const std::vector<std::string>& paths_to_pointclouds, const bool use_model_path)
+    : m_linknames(linknames),
+      m_links_meta_cloud(new MetaPointCloud(paths_to_pointclouds, paths_to_pointclouds, use_model_path)),
+      m_transformed_links_meta_cloud(new MetaPointCloud(*m_links_meta_cloud))
+  {
+    if (linknames.size() != dh_params.size())
+      LOGGING_ERROR_C(RobotLog, KinematicChain, "Number of linknames does not fit number of DH parameters. EXITING!" << endl);
+    for (size_t i = 0; i < dh_params.size() && i < linknames.size(); i++)
+      m_links[linknames[i]] = KinematicLinkSharedPtr(new KinematicLink(dh_params[i]));
+    LOGGING_INFO_C(RobotLog, KinematicChain, "now handling " << m_links.size() << " links." << endl);
+  }
   virtual ~KinematicChain()
   {
     delete m_links_meta_cloud;

@@ -335,6 +335,25 @@ int gvx_map_read_file(gvx_handle_t h, const char* path);
 int gvx_list_write_file(gvx_handle_t h, const char* path);
 int gvx_list_read_file(gvx_handle_t h, const char* path);
 
+/* ---- point-cloud files (.xyz, .pcd, .binvox) ------------------------------------------------------------------- */
+/* file_handling::PointcloudFileHandler::loadPointCloud (GV/helpers/PointcloudFileHandler.cpp:64-137) with its readers
+ * (GV/helpers/XyzFileReader.cpp:28-59, BinvoxFileReader.cpp:38-166, PcdFileReader.cpp:31-54): the format is chosen by the
+ * first of "xyz", "pcd", "binvox" found anywhere in the path; use_model_path prepends $GPU_VOXELS_MODEL_PATH
+ * (GV/helpers/common_defines.h:276-293); shift_to_zero moves the minimum corner to the origin; then every coordinate
+ * becomes scaling * c + offset (offset_xyz nullable = 0). Host only: works before gvx_init and without a GPU.
+ * *xyz_out receives n packed Vector3f allocated by the library (NULL for an empty cloud): release with
+ * gvx_pointcloud_file_free. GVX_ERR_IO: cannot be opened / truncated; GVX_ERR_INVALID: unknown or malformed format
+ * (the reference returns false for both). */
+int gvx_pointcloud_file_load(const char* path, int use_model_path, int shift_to_zero, const float* offset_xyz,
+                             float scaling, float** xyz_out, uint64_t* n_out);
+void gvx_pointcloud_file_free(float* xyz);
+/* GpuVoxelsMap::insertPointCloudFromFile (GV/GpuVoxelsMap.cpp:36-49; GpuVoxels::insertPointCloudFromFile,
+ * GV/GpuVoxels.cpp:427-440): load as above, then insertPointCloud into a map / a list */
+int gvx_insert_pointcloud_file(gvx_handle_t map, const char* path, int use_model_path, int meaning, int shift_to_zero,
+                               const float* offset_xyz, float scaling, int* any_outside);
+int gvx_list_insert_pointcloud_file(gvx_handle_t list, const char* path, int use_model_path, int meaning,
+                                    int shift_to_zero, const float* offset_xyz, float scaling);
+
 /* ---- batch of robot configurations -------------------------------------------------------------------- */
 /* n_cfg times the planner's state check (gvl_ompl_planning/gvl_ompl_planner_helper.cpp:169-202): clearMap(robot);
  * transformSubCloud per link (GV/helpers/MetaPointCloud.cu:624-649); insertMetaPointCloud(robot, meanings);

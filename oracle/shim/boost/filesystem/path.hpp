@@ -10,6 +10,14 @@ public:
   path(const char* s) : m_s(s) {}
   path(const std::string& s) : m_s(s) {}
   const std::string& string() const { return m_s; }
+  // boost semantics as far as the reference needs them: "" / p == p; a separator is inserted when the
+  // left side is non-empty and does not end in one; an absolute right side is appended as it is
+  path operator/(const path& r) const {
+    if (m_s.empty()) return r;
+    if (r.m_s.empty()) return *this;
+    if (m_s[m_s.size() - 1] == '/' || r.m_s[0] == '/') return path(m_s + r.m_s);
+    return path(m_s + "/" + r.m_s);
+  }
 private:
   std::string m_s;
 };

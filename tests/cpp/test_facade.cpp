@@ -493,6 +493,83 @@ BOOST_AUTO_TEST_CASE(voxelmap_disk_io)
   BOOST_CHECK(m1.collideWith(&m2, 0.5) == 9 * 9 * 9);
 }
 
+// PointcloudFileHandler / insertPointCloudFromFile / PointCloud(file) / MetaPointCloud(files)
+// (GV/helpers/PointcloudFileHandler.cpp:64-137, GV/GpuVoxelsMap.cpp:36-49, GV/helpers/PointCloud.cu:84-105,
+// GV/helpers/MetaPointCloud.cu:115-151); files of tests/golden/files, point counts as the reference's readers give them
+BOOST_AUTO_TEST_CASE(pointcloud_files)
+{
+  const char* dir = std::getenv("GVX_TEST_FILES");
+  BOOST_CHECK_MESSAGE(dir != NULL, "GVX_TEST_FILES names tests/golden/files");
+  if (!dir) return;
+  setenv("GPU_VOXELS_MODEL_PATH", dir, 1);
+  std::vector<Vector3f> pts;
+  file_handling::PointcloudFileHandler* fh = file_handling::PointcloudFileHandler::Instance();
+  BOOST_CHECK(fh->loadPointCloud("cube.binvox", true, pts));
+  BOOST_CHECK_MESSAGE(pts.size() == 52, "cube.binvox holds 52 voxels");
+  BOOST_CHECK(fh->loadPointCloud("messy.xyz", true, pts, true, Vector3f(1, 1, 1), 2.0f));  // appends, then post-processes all
+  BOOST_CHECK_MESSAGE(pts.size() == 52 + 11, "messy.xyz adds 11 points");
+  float lo = pts[0].x;
+  for (size_t i = 0; i < pts.size(); ++i) lo = std::min(lo, pts[i].x);
+  BOOST_CHECK_MESSAGE(lo == 1.0f, "shifted to zero, then scaled and offset by 1");
+  BOOST_CHECK(!fh->loadPointCloud("bad_magic.binvox", true, pts));
+  BOOST_CHECK(!fh->loadPointCloud("cloud.txt", true, pts));
+  BOOST_CHECK(pts.size() == 63);
+
+  PointCloud pc("grid32.binvox", true);
+  BOOST_CHECK(pc.getPointCloudSize() == 1697);
+  std::vector<std::string> files;
+  files.push_back("cube.binvox");
+  files.push_back("simple.xyz");
+  MetaPointCloud mpc(files, true);
+  BOOST_CHECK(mpc.getNumberOfPointclouds() == 2 && mpc.getPointcloudSize(0) == 52 && mpc.getPointcloudSize(1) == 200);
+  files.push_back("missing.xyz");
+  MetaPointCloud none(files, true);  // one unreadable file: nothing is added
+  BOOST_CHECK(none.getNumberOfPointclouds() == 0);
+
+  // grid32.binvox (0.77 / 32 per cell) scaled to one 1 cm voxel per cell: every one of its 1697 voxels is distinct
+  GpuVoxelsSharedPtr gvl = GpuVoxels::getInstance();
+  gvl->initialize(160, 160, 160, 0.01f);
+  gvl->addMap(MT_BITVECTOR_VOXELMAP, "from_file");
+  gvl->addMap(MT_BITVECTOR_VOXELLIST, "list_from_file");
+  BOOST_CHECK(gvl->insertPointCloudFromFile("from_file", "grid32.binvox", true, eBVM_OCCUPIED, true, Vector3f(0.005f, 0.005f, 0.005f), 0.415584f));
+  BOOST_CHECK(gvl->insertPointCloudFromFile("list_from_file", "grid32.binvox", true, eBVM_OCCUPIED, true, Vector3f(0.005f, 0.005f, 0.005f), 0.415584f));
+  BOOST_CHECK(!gvl->insertPointCloudFromFile("no_such_map", "grid32.binvox", true, eBVM_OCCUPIED));
+  BOOST_CHECK(!gvl->insertPointCloudFromFile("from_file", "no_dim.binvox", true, eBVM_OCCUPIED));
+  voxellist::BitVectorVoxelList* list = gvl->getMap("list_from_file")->as<voxellist::BitVectorVoxelList>();
+  BOOST_CHECK_MESSAGE(list->size() == 1697, "one list entry per binvox voxel");
+  BOOST_CHECK(list->collideWith(gvl->getMap("from_file")->as<voxelmap::BitVectorVoxelMap>(), 1.0f) == 1697);
+
+  // a DH robot whose link clouds come from files (GV/GpuVoxels.cpp:316-336): the clouds are named by their paths and
+  // a link moves the cloud of its own name -- it must equal the same robot built from the loaded clouds
+  std::vector<std::string> paths;
+  paths.push_back("simple.xyz");
+  paths.push_back("cube.binvox");
+  std::vector<robot::DHParameters> dh;
+  dh.push_back(robot::DHParameters(0.3f, 0.f, 0.1f, 1.5707963f, 0.f, robot::REVOLUTE));
+  dh.push_back(robot::DHParameters(0.0f, 0.f, 0.3f, 0.f, 0.f, robot::REVOLUTE));
+  BOOST_CHECK(gvl->addRobot("file_arm", paths, dh, paths, true));
+  BOOST_CHECK(!gvl->addRobot("file_arm", paths, dh, paths, true));
+  MetaPointCloud loaded(paths, paths, true);
+  BOOST_CHECK(gvl->addRobot("cloud_arm", paths, dh, loaded));
+  gvl->addMap(MT_BITVECTOR_VOXELMAP, "rob_a");
+  gvl->addMap(MT_BITVECTOR_VOXELMAP, "rob_b");
+  robot::JointValueMap jm;
+  jm["simple.xyz"] = 0.4f;
+  jm["cube.binvox"] = -0.7f;
+  BOOST_CHECK(gvl->setRobotConfiguration("file_arm", jm) && gvl->setRobotConfiguration("cloud_arm", jm));
+  BOOST_CHECK(gvl->insertRobotIntoMap("file_arm", "rob_a", eBVM_OCCUPIED));
+  BOOST_CHECK(gvl->insertRobotIntoMap("cloud_arm", "rob_b", eBVM_OCCUPIED));
+  voxelmap::BitVectorVoxelMap* ra = gvl->getMap("rob_a")->as<voxelmap::BitVectorVoxelMap>();
+  voxelmap::BitVectorVoxelMap* rb = gvl->getMap("rob_b")->as<voxelmap::BitVectorVoxelMap>();
+  const size_t occupied = ra->collideWith(ra, 1.0f);
+  BOOST_CHECK_MESSAGE(occupied > 20, "the robot occupies voxels: " << occupied);
+  BOOST_CHECK(ra->collideWith(rb, 1.0f) == occupied && rb->collideWith(rb, 1.0f) == occupied);
+  gvl->delMap("rob_a");
+  gvl->delMap("rob_b");
+  gvl->delMap("from_file");
+  gvl->delMap("list_from_file");
+}
+
 // ray casting through the reference's call: the cells between the sensor and a wall become free, the wall occupied
 BOOST_AUTO_TEST_CASE(insert_sensor_data_with_raycasting_and_robot_cut)
 {
