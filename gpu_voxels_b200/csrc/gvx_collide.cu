@@ -441,6 +441,8 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
     GVX_SUM(kMapProb, kMapProb, true, true);
 #undef GVX_SUM
   }
+  if (c.tma > 0 && collide_tma_applicable(a, a_type, b, b_type, i_begin, off, types))
+    return launch_collide_tma(c, a, a_type, b, b_type, n, thr, mark, count_out_d);
   if (a_type == kMapProb && b_type == kMapProb) {
     const bool aligned = ((off & 15) == 0) && (((uintptr_t)a & 15) == 0) && (((uintptr_t)b & 15) == 0);
     if (aligned) {

@@ -99,6 +99,7 @@ struct Context {
   bool disp_connected = false;
   unsigned long long disp_epoch = 0;
   uint32_t* disp_err_h = nullptr; uint32_t* disp_err_hmap_d = nullptr;
+  int collide_tma = 0;  // GVX_OPT_COLLIDE_TMA: streaming collide kernels read TMA bulk tiles instead of LDG.256
   bool use_summary = true;  // GVX_OPT_USE_SUMMARY: collide kernels may read occupancy summaries instead of voxels
   uint64_t launches = 0;
   uint64_t next_handle = 1;
@@ -134,6 +135,7 @@ inline int fail(int code, const char* fmt, ...) {
 inline LaunchCtx lctx() {
   LaunchCtx c{g.stream, g.sm_count, g.scratch_d, g.result_d, g.result_hmap_d, &g.launches, PeerReduce{}};
   c.peer.world = 1;
+  c.tma = g.collide_tma;
   return c;
 }
 // launch context of a counting kernel that all-reduces its count over the connected peers (next epoch)

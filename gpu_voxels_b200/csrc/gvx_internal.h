@@ -14,6 +14,7 @@ struct LaunchCtx {
   ResultBlock* result_hmap_d; // device alias of the pinned, mapped host result block
   uint64_t* launches;         // kernel launch counter (host)
   PeerReduce peer;            // world <= 1: no fused all-reduce
+  int tma = 0;                // GVX_OPT_COLLIDE_TMA: > 0 = voxel-streaming collide kernels fed by TMA bulk tiles (shape k)
 };
 
 // collideWith map x map. a/b: device base pointers of the voxel arrays; a is indexed at i + off.
@@ -23,6 +24,13 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a, int a_type, cons
                                    int64_t i_begin, int64_t i_end, int64_t off, int8_t thr, bool mark,
                                    bool types, unsigned long long* count_out_d, const uint32_t* occ_a = nullptr,
                                    const uint32_t* occ_b = nullptr);
+
+// the voxel-streaming collide fed by TMA bulk tiles (gvx_collide_tma.cu); applicable: off == 0, whole range, at least
+// one BitVectorVoxel side, 16-byte aligned bases, no meaning mask
+bool collide_tma_applicable(const void* a, int a_type, const void* b, int b_type, int64_t i_begin, int64_t off,
+                            bool types);
+cudaError_t launch_collide_tma(const LaunchCtx& c, void* a, int a_type, const void* b, int b_type, int64_t n,
+                               int8_t thr, bool mark, unsigned long long* count_out_d);
 
 // voxelisation
 struct MetaDesc {             // device-resident description of a MetaPointCloud insert

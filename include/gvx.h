@@ -133,8 +133,12 @@ int gvx_map_refresh_summary(gvx_handle_t h);
 int gvx_map_summary_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, int* valid);
 enum gvx_option {
   GVX_OPT_USE_SUMMARY = 1,   /* 0: always stream the voxels (the reference's access pattern) */
-  GVX_OPT_DH_CHECK_BITS = 2  /* forward kinematics: sin/cos brackets of |v| * 2^-bits (default 50); smaller values send
+  GVX_OPT_DH_CHECK_BITS = 2, /* forward kinematics: sin/cos brackets of |v| * 2^-bits (default 50); smaller values send
                                 more configurations through the host re-computation (tests) */
+  GVX_OPT_COLLIDE_TMA = 3    /* 1..5: the voxel-streaming collide kernels are fed by TMA bulk tiles (cp.async.bulk into a
+                                shared-memory ring; the value picks the tile x stages shape, 1 = 512 voxels x 4)
+                                instead of per-thread 256-bit loads; same results (default 0, see DESIGN.md 3.2 for
+                                the measurement that decides the default) */
 };
 int gvx_set_option(int option, int value);
 
