@@ -37,6 +37,7 @@ def main():
     torch.cuda.set_stream(stream)
     _lib.check(L.gvx_set_stream(C.c_void_p(stream.cuda_stream)))
     reps = int(sys.argv[1]) if len(sys.argv) > 1 else 40
+    only = sys.argv[2] if len(sys.argv) > 2 else None  # "bitprob": Bit x Prob with shapes 0 and 2 only (ncu captures)
     peak = 6448.1
     try:
         peak = float(json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"])
@@ -66,7 +67,9 @@ def main():
     results = []
     for name, (hs, bpv, mark) in pairs.items():
         base_counts = None
-        for shape in (0, 1, 2, 3, 4, 5):
+        if only == "bitprob" and name != "Bit x Prob":
+            continue
+        for shape in ((0, 2) if only else (0, 1, 2, 3, 4, 5)):
             if shape > 1 and name == "Bit x Bit":
                 continue  # one shape only for Bit x Bit (256 x 4)
             gv.set_option(gv.GVX_OPT_COLLIDE_TMA, shape)
@@ -97,10 +100,10 @@ def main():
                  "frac_of_8000": round(gbs / 8000, 3), "counts": counts}
             print(json.dumps(r), flush=True)
             results.append(r)
-    gv.set_option(gv.GVX_OPT_COLLIDE_TMA, 0)
+    gv.set_option(gv.GVX_OPT_COLLIDE_TMA, -1)
     gv.set_option(gv.GVX_OPT_USE_SUMMARY, 1)
     out = os.path.join(os.path.dirname(__file__), "..", "gpurun_out")
-    if os.path.isdir(out):
+    if os.path.isdir(out) and not only:
         json.dump({"grid": DIMS, "pairs_in_rotation": P, "reps": reps, "peak_gbs": peak, "results": results},
                   open(os.path.join(out, "tma_probe.json"), "w"), indent=1)
 

@@ -380,7 +380,7 @@ int gvx_set_option(int option, int value) {
   switch (option) {
     case GVX_OPT_USE_SUMMARY: g.use_summary = value != 0; return GVX_OK;
     case GVX_OPT_COLLIDE_TMA:
-      if (value < 0 || value > 5) return fail(GVX_ERR_INVALID, "GVX_OPT_COLLIDE_TMA must be in [0, 5]");
+      if (value < -1 || value > 5) return fail(GVX_ERR_INVALID, "GVX_OPT_COLLIDE_TMA must be in [-1, 5]");
       g.collide_tma = value; return GVX_OK;
     case GVX_OPT_DH_CHECK_BITS:
       if (value < 8 || value > 52) return fail(GVX_ERR_INVALID, "GVX_OPT_DH_CHECK_BITS must be in [8, 52]");

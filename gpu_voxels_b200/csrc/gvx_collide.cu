@@ -441,8 +441,15 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
     GVX_SUM(kMapProb, kMapProb, true, true);
 #undef GVX_SUM
   }
-  if (c.tma > 0 && collide_tma_applicable(a, a_type, b, b_type, i_begin, off, types))
-    return launch_collide_tma(c, a, a_type, b, b_type, n, thr, mark, count_out_d);
+  // TMA bulk tiles "where they beat plain loads" (north_star; benchmarks/tma_probe.py): measured at 512^3,
+  // Bit x Prob gains 5 % (7.15 vs 6.79 TB/s, tiles of 1024 voxels x 3 stages), Prob x Bit and Bit x Bit do not
+  // (7.08 vs 7.15, 7.20 vs 7.23 TB/s) -- so auto (-1) feeds only Bit x Prob through TMA; k > 0 forces shape k everywhere.
+  if (c.tma != 0 && collide_tma_applicable(a, a_type, b, b_type, i_begin, off, types) &&
+      (c.tma > 0 || (a_bit && !b_bit && n >= (1ll << 22)))) {
+    LaunchCtx ct = c;
+    if (ct.tma < 0) ct.tma = 2;
+    return launch_collide_tma(ct, a, a_type, b, b_type, n, thr, mark, count_out_d);
+  }
   if (a_type == kMapProb && b_type == kMapProb) {
     const bool aligned = ((off & 15) == 0) && (((uintptr_t)a & 15) == 0) && (((uintptr_t)b & 15) == 0);
     if (aligned) {

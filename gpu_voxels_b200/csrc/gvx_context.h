@@ -99,7 +99,7 @@ struct Context {
   bool disp_connected = false;
   unsigned long long disp_epoch = 0;
   uint32_t* disp_err_h = nullptr; uint32_t* disp_err_hmap_d = nullptr;
-  int collide_tma = 0;  // GVX_OPT_COLLIDE_TMA: streaming collide kernels read TMA bulk tiles instead of LDG.256
+  int collide_tma = -1;  // GVX_OPT_COLLIDE_TMA: -1 auto (TMA where it measured faster), 0 never, 1..5 always (shape k)
   bool use_summary = true;  // GVX_OPT_USE_SUMMARY: collide kernels may read occupancy summaries instead of voxels
   uint64_t launches = 0;
   uint64_t next_handle = 1;

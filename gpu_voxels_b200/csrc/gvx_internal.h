@@ -14,7 +14,7 @@ struct LaunchCtx {
   ResultBlock* result_hmap_d; // device alias of the pinned, mapped host result block
   uint64_t* launches;         // kernel launch counter (host)
   PeerReduce peer;            // world <= 1: no fused all-reduce
-  int tma = 0;                // GVX_OPT_COLLIDE_TMA: > 0 = voxel-streaming collide kernels fed by TMA bulk tiles (shape k)
+  int tma = 0;                // GVX_OPT_COLLIDE_TMA: -1 auto, 0 never, k > 0 = TMA bulk tiles of shape k for every pair
 };
 
 // collideWith map x map. a/b: device base pointers of the voxel arrays; a is indexed at i + off.

@@ -14,7 +14,7 @@ def gv():
     import gpu_voxels_b200 as g
     g._lib.init()
     yield g
-    g.set_option(g.GVX_OPT_COLLIDE_TMA, 0)
+    g.set_option(g.GVX_OPT_COLLIDE_TMA, -1)
     g.set_option(g.GVX_OPT_USE_SUMMARY, 1)
 
 
@@ -81,5 +81,23 @@ def test_tma_option_leaves_unsupported_calls_on_the_plain_kernels(gv, oracle):
     w1 = q0.copy()
     assert p1.collideWith(b, 0.5) == oracle.collide_map_map(w1, PROB, b0, PROB, n, 0.5, 0, True)
     assert gv._lib.load().gvx_set_option(gv.GVX_OPT_COLLIDE_TMA, 9) != 0
+    gv.set_option(gv.GVX_OPT_COLLIDE_TMA, -1)
+    gv.set_option(gv.GVX_OPT_USE_SUMMARY, 1)
+
+
+def test_auto_mode_feeds_large_bit_x_prob_through_tma_with_the_same_result(gv, oracle):
+    """default (-1): Bit x Prob on >= 4 M voxels takes the TMA kernel; count and marks as the oracle's"""
+    dims = (256, 192, 96)  # 4.7 M voxels, 151 MB of BitVectorVoxels
+    n = dims[0] * dims[1] * dims[2]
+    gv.set_option(gv.GVX_OPT_USE_SUMMARY, 0)
+    gv.set_option(gv.GVX_OPT_COLLIDE_TMA, -1)
+    a, a0 = _random_map(gv, BIT, dims, 41, 0.2)
+    b, b0 = _random_map(gv, PROB, dims, 42, 0.3)
+    want_a = a0.copy()
+    want = oracle.collide_map_map(want_a, BIT, b0, PROB, n, 0.5, 0, True)
+    assert a.collideWith(b, 0.5) == want
+    assert np.array_equal(a.download().reshape(-1).view(np.uint8), want_a)
     gv.set_option(gv.GVX_OPT_COLLIDE_TMA, 0)
+    assert a.collideWith(b, 0.5, mark=False) == want
+    gv.set_option(gv.GVX_OPT_COLLIDE_TMA, -1)
     gv.set_option(gv.GVX_OPT_USE_SUMMARY, 1)

@@ -32,8 +32,8 @@ def _golden(name, shift, scaling):
     raise KeyError(name)
 
 
-@pytest.mark.parametrize("name,shift,scaling,side", [("cube.binvox", True, 0.01, 0.001), ("grid32.binvox", True, 0.04, 0.01),
-                                                      ("simple.xyz", True, 0.5, 0.05), ("messy.xyz", False, 1.0, 1.0)])
+@pytest.mark.parametrize("name,shift,scaling,side", [("cube.binvox", True, 0.01, 0.01), ("grid32.binvox", True, 0.04, 0.01),
+                                                      ("simple.xyz", True, 0.5, 0.1), ("messy.xyz", False, 1.0, 1.0)])
 @pytest.mark.parametrize("map_type", [BIT, PROB])
 def test_insert_from_file_equals_reference_points_through_the_oracle(gv, oracle, monkeypatch, name, shift, scaling, side, map_type):
     monkeypatch.chdir(FILES)  # the format is detected by substring of the whole path: keep it the bare name
