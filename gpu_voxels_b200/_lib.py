@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(_HERE, "libgvx.so")
 
 GVX_OK = 0
 ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED, ERR_DIM_MISMATCH, ERR_NOT_INITIALIZED, ERR_IO = 1, 2, 3, 4, 5, 6, 7
-MEM_HOST, MEM_DEVICE = 0, 1
+MEM_HOST, MEM_DEVICE, MEM_HOST_PINNED = 0, 1, 2
 
 u64, u32, i32, f32, vp = C.c_uint64, C.c_uint32, C.c_int32, C.c_float, C.c_void_p
 P = C.POINTER

@@ -64,6 +64,16 @@ int gvx_shutdown(void) {
   g.bat_bits_cap = g.bat_seen_cap = g.bat_tr_cap = g.bat_tr_h_cap = g.bat_counts_cap = g.bat_counts_h_cap = 0;
   g.bat_fk_cap = g.bat_fk_h_cap = 0;
   if (g.stage_d) cudaFree(g.stage_d);
+  if (g.copy_stream) {
+    cudaStreamSynchronize(g.copy_stream);
+    for (int k = 0; k < 2; ++k) {
+      if (g.pipe_d[k]) cudaFree(g.pipe_d[k]);
+      cudaEventDestroy(g.pipe_ready[k]); cudaEventDestroy(g.pipe_consumed[k]);
+      g.pipe_d[k] = nullptr; g.pipe_cap[k] = 0; g.pipe_ready[k] = g.pipe_consumed[k] = nullptr;
+    }
+    cudaStreamDestroy(g.copy_stream);
+    g.copy_stream = nullptr; g.pipe_next = 0; g.pipe_pending = -1;
+  }
   for (int k = 0; k < Context::kDescSlots; ++k) {
     if (g.desc_d[k]) cudaFree(g.desc_d[k]);
     if (g.desc_h[k]) cudaFreeHost(g.desc_h[k]);
@@ -472,7 +482,8 @@ int gvx_transform_points(const float* in_xyz, float* out_xyz, uint64_t n, int me
     return GVX_OK;
   }
   const float* in_d = nullptr;
-  int rc = points_to_device(in_xyz, n, mem_kind, &in_d);
+  // host in, host out, synchronous: the staging buffer doubles as the output, so no pipelined upload here
+  int rc = points_to_device(in_xyz, n, mem_kind == GVX_MEM_HOST_PINNED ? GVX_MEM_HOST : mem_kind, &in_d);
   if (rc) return rc;
   GVX_CUDA(launch_transform(lctx(), in_d, (float*)g.stage_d, n, M));
   GVX_CUDA(cudaMemcpyAsync(out_xyz, g.stage_d, (size_t)n * 12, cudaMemcpyDeviceToHost, g.stream));

@@ -68,6 +68,12 @@ struct Context {
   ResultBlock* result_hmap_d = nullptr;  // device alias of result_h
   // staging: device buffer for host point clouds, pinned + device buffers for small descriptors
   void* stage_d = nullptr; size_t stage_cap = 0;
+  // GVX_MEM_HOST_PINNED: two device slots filled on a copy stream; ready = "slot holds the cloud" (copy stream),
+  // consumed = "everything that read the slot has been enqueued before this mark" (main stream)
+  cudaStream_t copy_stream = nullptr;
+  void* pipe_d[2] = {}; size_t pipe_cap[2] = {};
+  cudaEvent_t pipe_ready[2] = {}; cudaEvent_t pipe_consumed[2] = {};
+  int pipe_next = 0, pipe_pending = -1;
   // ring of small descriptor slots (pinned host + device + "H2D done" event): no stream sync per call
   static constexpr int kDescSlots = 8;
   void* desc_h[kDescSlots] = {}; void* desc_d[kDescSlots] = {}; size_t desc_cap[kDescSlots] = {};
@@ -212,8 +218,37 @@ inline int desc_commit(int slot, size_t bytes) {
 // as in TemplateVoxelMap::insertPointCloud(std::vector), GV/voxelmap/TemplateVoxelMap.hpp:563-576).
 inline int points_to_device(const float* xyz, uint64_t n, int mem_kind, const float** out_d) {
   if (mem_kind == GVX_MEM_DEVICE) { *out_d = xyz; return GVX_OK; }
-  if (mem_kind != GVX_MEM_HOST) return fail(GVX_ERR_INVALID, "bad mem_kind %d", mem_kind);
   const size_t bytes = (size_t)n * 12;
+  if (mem_kind == GVX_MEM_HOST_PINNED) {
+    if (!g.copy_stream) {
+      GVX_CUDA(cudaStreamCreateWithFlags(&g.copy_stream, cudaStreamNonBlocking));
+      for (int k = 0; k < 2; ++k) {
+        GVX_CUDA(cudaEventCreateWithFlags(&g.pipe_ready[k], cudaEventDisableTiming));
+        GVX_CUDA(cudaEventCreateWithFlags(&g.pipe_consumed[k], cudaEventDisableTiming));
+      }
+    }
+    // the kernels that read the slot filled by the previous call are on g.stream by now: mark the slot reusable
+    if (g.pipe_pending >= 0) { GVX_CUDA(cudaEventRecord(g.pipe_consumed[g.pipe_pending], g.stream)); g.pipe_pending = -1; }
+    const int k = g.pipe_next;
+    g.pipe_next ^= 1;
+    if (bytes > g.pipe_cap[k]) {
+      GVX_CUDA(cudaStreamSynchronize(g.copy_stream));
+      GVX_CUDA(cudaStreamSynchronize(g.stream));
+      if (g.pipe_d[k]) { cudaFree(g.pipe_d[k]); g.pipe_d[k] = nullptr; g.pipe_cap[k] = 0; }
+      const size_t cap = bytes + bytes / 4 + (1u << 20);
+      cudaError_t e = cudaMalloc(&g.pipe_d[k], cap);
+      if (e != cudaSuccess) { cudaGetLastError(); return fail(GVX_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", cap, cudaGetErrorString(e)); }
+      g.pipe_cap[k] = cap;
+    }
+    GVX_CUDA(cudaStreamWaitEvent(g.copy_stream, g.pipe_consumed[k], 0));  // never recorded yet = nothing to wait for
+    if (bytes) GVX_CUDA(cudaMemcpyAsync(g.pipe_d[k], xyz, bytes, cudaMemcpyHostToDevice, g.copy_stream));
+    GVX_CUDA(cudaEventRecord(g.pipe_ready[k], g.copy_stream));
+    GVX_CUDA(cudaStreamWaitEvent(g.stream, g.pipe_ready[k], 0));
+    g.pipe_pending = k;
+    *out_d = (const float*)g.pipe_d[k];
+    return GVX_OK;
+  }
+  if (mem_kind != GVX_MEM_HOST) return fail(GVX_ERR_INVALID, "bad mem_kind %d", mem_kind);
   int rc = ensure_stage(bytes);
   if (rc) return rc;
   if (bytes) GVX_CUDA(cudaMemcpyAsync(g.stage_d, xyz, bytes, cudaMemcpyHostToDevice, g.stream));

@@ -61,7 +61,15 @@ enum gvx_meaning {
   GVX_BVM_SWEPT_VOLUME_START = 4, GVX_BVM_SWEPT_VOLUME_END = 254, GVX_BVM_UNDEFINED = 255
 };
 
-enum gvx_mem_kind { GVX_MEM_HOST = 0, GVX_MEM_DEVICE = 1 };
+enum gvx_mem_kind {
+  GVX_MEM_HOST = 0,   /* any host memory; the call has consumed or staged it when it returns */
+  GVX_MEM_DEVICE = 1,
+  /* page-locked host memory that the caller leaves untouched until the work has completed (gvx_sync, a synchronous call,
+   * or an event of its own on the stream): the upload runs on a separate copy stream into one of two device staging
+   * slots, so the copy of call k+1 overlaps the kernels of call k (the reference stages every host cloud with a
+   * synchronous cudaMalloc + cudaMemcpy + cudaFree, GV/voxelmap/TemplateVoxelMap.hpp:563-576) */
+  GVX_MEM_HOST_PINNED = 2
+};
 
 #define GVX_BITVOXEL_BYTES 32
 

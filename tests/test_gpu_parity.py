@@ -175,6 +175,39 @@ def test_update_logodds_frames(gv, oracle):
     assert ref.max() == 127
 
 
+def test_pinned_host_frames_pipelined_upload(gv, oracle):
+    """GVX_MEM_HOST_PINNED: frames of different sizes from page-locked memory go up on the copy stream into alternating
+    staging slots while earlier kernels run; no sync between the calls. Maps and counts equal the oracle's sequence."""
+    import ctypes as C
+    import torch
+    from gpu_voxels_b200 import _lib
+    L = _lib.load()
+    dims, side = (128, 128, 64), 0.02
+    pose = np.ascontiguousarray(np.array([[0, 0, 1, 0.1], [-1, 0, 0, 1.28], [0, -1, 0, 0.5]], np.float32))
+    m, bm = _mk(gv, PROB, dims, side), _mk(gv, BIT, dims, side)
+    ref, ref_b = oracle.new_map(PROB, dims), oracle.new_map(BIT, dims)
+    frames = [_depth_frame(300 + f)[: 19200 - 3000 * (f % 3)] for f in range(7)]
+    pinned = [torch.from_numpy(np.ascontiguousarray(f)).pin_memory() for f in frames]
+    count_d = torch.zeros(7, dtype=torch.int64, device="cuda")
+    for f, t in enumerate(pinned):
+        _lib.check(L.gvx_update_logodds(m.handle, C.c_void_p(t.data_ptr()), len(t), _lib.MEM_HOST_PINNED,
+                                        pose.ctypes.data_as(C.c_void_p), 72))
+        # a second consumer of the same kind of upload, other map type, asynchronous (any_outside = NULL)
+        _lib.check(L.gvx_insert_points(bm.handle, C.c_void_p(t.data_ptr()), len(t), _lib.MEM_HOST_PINNED, 9 + f, None))
+        _lib.check(L.gvx_collide_map_map_async(m.handle, bm.handle, 0.5, None, 0, C.c_void_p(count_d.data_ptr() + 8 * f)))
+    _lib.check(L.gvx_sync())
+    want = []
+    for f, pts in enumerate(frames):
+        oracle.update_logodds(ref, dims, side, pts, pose)
+        oracle.insert_points(ref_b, BIT, dims, side, pts, 9 + f)
+        want.append(oracle.collide_map_map(ref, PROB, ref_b, BIT, dims[0] * dims[1] * dims[2], 0.5, 0, False))
+    assert np.array_equal(m.download(), ref)
+    assert np.array_equal(_flat(bm), ref_b.reshape(-1).view(np.uint8))
+    assert count_d.cpu().tolist() == want and max(want) > 0
+    # a mem_kind nobody defined is refused
+    assert L.gvx_insert_points(bm.handle, C.c_void_p(pinned[0].data_ptr()), 10, 7, 9, None) == _lib.ERR_INVALID
+
+
 # ---- collisions --------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("n_real", [5, 15, 16, 70])  # <= 16 frames travel in the kernel parameters, more in a descriptor
 def test_update_logodds_multi_frame_equals_sequence(gv, oracle, n_real):
