@@ -188,19 +188,23 @@ def test_pinned_host_frames_pipelined_upload(gv, oracle):
     ref, ref_b = oracle.new_map(PROB, dims), oracle.new_map(BIT, dims)
     frames = [_depth_frame(300 + f)[: 19200 - 3000 * (f % 3)] for f in range(7)]
     pinned = [torch.from_numpy(np.ascontiguousarray(f)).pin_memory() for f in frames]
+    # the BitVector map receives the same surface in world coordinates (NaN pixels -> voxel 0), so the maps do collide
+    M = np.vstack([pose, np.array([[0, 0, 0, 1]], np.float32)])
+    world = [np.ascontiguousarray(oracle.transform_points(M, f)) for f in frames]
+    pinned_w = [torch.from_numpy(w).pin_memory() for w in world]
     count_d = torch.zeros(7, dtype=torch.int64, device="cuda")
     for f, t in enumerate(pinned):
         _lib.check(L.gvx_update_logodds(m.handle, C.c_void_p(t.data_ptr()), len(t), _lib.MEM_HOST_PINNED,
                                         pose.ctypes.data_as(C.c_void_p), 72))
         # a second consumer of the same kind of upload, other map type, asynchronous (any_outside = NULL)
-        _lib.check(L.gvx_insert_points(bm.handle, C.c_void_p(t.data_ptr()), len(t), _lib.MEM_HOST_PINNED, 9 + f, None))
-        _lib.check(L.gvx_collide_map_map_async(m.handle, bm.handle, 0.5, None, 0, C.c_void_p(count_d.data_ptr() + 8 * f)))
+        _lib.check(L.gvx_insert_points(bm.handle, C.c_void_p(pinned_w[f].data_ptr()), len(t), _lib.MEM_HOST_PINNED, 9 + f, None))
+        _lib.check(L.gvx_collide_map_map_async(m.handle, bm.handle, 0.1, None, 0, C.c_void_p(count_d.data_ptr() + 8 * f)))
     _lib.check(L.gvx_sync())
     want = []
     for f, pts in enumerate(frames):
         oracle.update_logodds(ref, dims, side, pts, pose)
-        oracle.insert_points(ref_b, BIT, dims, side, pts, 9 + f)
-        want.append(oracle.collide_map_map(ref, PROB, ref_b, BIT, dims[0] * dims[1] * dims[2], 0.5, 0, False))
+        oracle.insert_points(ref_b, BIT, dims, side, world[f], 9 + f)
+        want.append(oracle.collide_map_map(ref, PROB, ref_b, BIT, dims[0] * dims[1] * dims[2], 0.1, 0, False))
     assert np.array_equal(m.download(), ref)
     assert np.array_equal(_flat(bm), ref_b.reshape(-1).view(np.uint8))
     assert count_d.cpu().tolist() == want and max(want) > 0
