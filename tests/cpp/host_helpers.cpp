@@ -1,0 +1,61 @@
+// tests/cpp/host_helpers.cpp -- host-only part of the C++ facade (no GPU, no gvx_init): prints what
+// gpu_voxels::computeLinearLoad / interpolateLinear (include/gpu_voxels/helpers/MathHelpers.h) return for the cases on
+// its command line, one per line, floats as raw bit patterns; tests/test_host_helpers.py compares the lines with
+// tests/golden/math_helpers.npz (produced by the reference's MathHelpers.cpp compiled for the host).
+//   host_helpers load <n>...            -> "<blocks> <threads>"
+//   host_helpers lerpf <a> <b> <r> ...  (uint32 bit patterns)  -> "<bits>"
+//   host_helpers lerpd <a> <b> <r> ...  (uint64 bit patterns)  -> "<bits>"
+#include <cinttypes>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include <gpu_voxels/helpers/MathHelpers.h>
+
+template <class T, class U> static T bits_to(U u) { T t; static_assert(sizeof(T) == sizeof(U), "size"); std::memcpy(&t, &u, sizeof t); return t; }
+
+int main(int argc, char** argv)
+{
+  if (argc < 2) return 2;
+  const std::string mode = argv[1];
+  if (mode == "load")
+    for (int i = 2; i < argc; ++i)
+    {
+      uint32_t blocks = 0, threads = 0;
+      gpu_voxels::computeLinearLoad(uint32_t(std::strtoul(argv[i], NULL, 10)), &blocks, &threads);
+      std::printf("%u %u\n", blocks, threads);
+    }
+  else if (mode == "lerpf")
+    for (int i = 2; i + 2 < argc; i += 3)
+    {
+      const float a = bits_to<float>(uint32_t(std::strtoul(argv[i], NULL, 10)));
+      const float b = bits_to<float>(uint32_t(std::strtoul(argv[i + 1], NULL, 10)));
+      const float r = bits_to<float>(uint32_t(std::strtoul(argv[i + 2], NULL, 10)));
+      std::printf("%u\n", bits_to<uint32_t>(gpu_voxels::interpolateLinear(a, b, r)));
+    }
+  else if (mode == "lerpd")
+    for (int i = 2; i + 2 < argc; i += 3)
+    {
+      const double a = bits_to<double>(uint64_t(std::strtoull(argv[i], NULL, 10)));
+      const double b = bits_to<double>(uint64_t(std::strtoull(argv[i + 1], NULL, 10)));
+      const double r = bits_to<double>(uint64_t(std::strtoull(argv[i + 2], NULL, 10)));
+      std::printf("%" PRIu64 "\n", bits_to<uint64_t>(gpu_voxels::interpolateLinear(a, b, r)));
+    }
+  else if (mode == "vec")
+  {  // the vector and map overloads against the scalar one
+    std::vector<float> a(3), b(3);
+    a[0] = 0.1f; a[1] = -2.f; a[2] = 3.5f; b[0] = 1.1f; b[1] = 4.f; b[2] = -3.5f;
+    std::vector<float> v = gpu_voxels::interpolateLinear(a, b, 0.3f);
+    std::map<std::string, float> ma, mb;
+    ma["j0"] = a[0]; ma["j1"] = a[1]; mb["j0"] = b[0]; mb["j1"] = b[1];
+    std::map<std::string, float> m = gpu_voxels::interpolateLinear(ma, mb, 0.3f);
+    bool ok = v.size() == 3 && m.size() == 2;
+    for (int k = 0; k < 3 && ok; ++k) ok = v[k] == gpu_voxels::interpolateLinear(a[k], b[k], 0.3f);
+    ok = ok && m["j0"] == v[0] && m["j1"] == v[1];
+    std::vector<double> da(1, 0.25), db(1, 0.75);
+    ok = ok && gpu_voxels::interpolateLinear(da, db, 0.5)[0] == 0.5;
+    std::printf("%s\n", ok ? "ok" : "MISMATCH");
+  }
+  else return 2;
+  return 0;
+}

@@ -182,5 +182,34 @@ def main():
     print("wrote", len(names), "files and", len(CASES), "cases")
 
 
+def math_helpers():
+    """computeLinearLoad / interpolateLinear of the reference (GV/helpers/MathHelpers.cpp compiled for the host into
+    oracle/_ref/libgvref_files.so) -> tests/golden/math_helpers.npz"""
+    L = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libgvref_files.so"))
+    L.gvrefio_lerp_f.restype, L.gvrefio_lerp_f.argtypes = C.c_float, [C.c_float] * 3
+    L.gvrefio_lerp_d.restype, L.gvrefio_lerp_d.argtypes = C.c_double, [C.c_double] * 3
+    rng = np.random.Generator(np.random.PCG64(99))
+    n = np.concatenate([[0, 1, 2, 1023, 1024, 1025, 2047, 2048, 65535 * 1024 - 1, 65535 * 1024, 65535 * 1024 + 1, 2 ** 31, 2 ** 32 - 1],
+                        rng.integers(0, 2 ** 32, size=200)]).astype(np.uint32)
+    load = np.zeros((len(n), 2), np.uint32)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(2)
+    os.dup2(devnull, 2)  # the n == 0 case logs an error
+    for i, v in enumerate(n):
+        b, t = C.c_uint32(), C.c_uint32()
+        L.gvrefio_linear_load(C.c_uint32(int(v)), C.byref(b), C.byref(t))
+        load[i] = (b.value, t.value)
+    os.dup2(saved, 2)
+    f = (rng.normal(size=(400, 3)) * 10.0 ** rng.integers(-3, 4, size=(400, 1))).astype(np.float32)
+    f[:, 2] = rng.uniform(-0.5, 1.5, size=400).astype(np.float32)
+    f[0] = (1, 2, 0); f[1] = (1, 2, 1); f[2] = (0.1, 0.2, 0.5); f[3] = (3.4e38, 3.4e38, 0.5); f[4] = (1e-45, 1e-45, 0.5)
+    lf = np.array([L.gvrefio_lerp_f(*[float(x) for x in row]) for row in f], np.float32)
+    d = f.astype(np.float64) * rng.uniform(0.9, 1.1, size=(400, 3))
+    ld = np.array([L.gvrefio_lerp_d(*[float(x) for x in row]) for row in d], np.float64)
+    np.savez_compressed(os.path.join(HERE, "math_helpers.npz"), n=n, load=load, f=f, lerp_f=lf, d=d, lerp_d=ld)
+    print("math helpers:", len(n), "launch shapes,", len(f), "+", len(d), "interpolations")
+
+
 if __name__ == "__main__":
     main()
+    math_helpers()

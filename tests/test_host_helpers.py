@@ -1,0 +1,50 @@
+"""Host-side helpers of the C++ facade that need no GPU: computeLinearLoad / interpolateLinear
+(include/gpu_voxels/helpers/MathHelpers.h; SURVEY 8 row a9, GV/helpers/MathHelpers.cpp:29-160). A small C++ program
+built with plain g++ prints the facade's results; they must equal tests/golden/math_helpers.npz bit for bit -- the
+output of the reference's own MathHelpers.cpp compiled for the host (tests/golden/make_golden_files.py)."""
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = os.path.join(ROOT, "tests", "cpp", "host_helpers.cpp")
+EXE = os.path.join(ROOT, "tests", "cpp", "host_helpers")
+CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+
+
+def _exe():
+    hdr = os.path.join(ROOT, "include", "gpu_voxels", "helpers", "MathHelpers.h")
+    if not (os.path.exists(EXE) and os.path.getmtime(EXE) >= max(os.path.getmtime(SRC), os.path.getmtime(hdr))):
+        subprocess.check_call([CXX, "-std=c++14", "-O2", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                               SRC, "-o", EXE])
+    return EXE
+
+
+def _run(mode, args):
+    out = []
+    args = [str(int(a)) for a in args]
+    for i in range(0, len(args), 600):  # keep the command line short
+        r = subprocess.run([_exe(), mode] + args[i:i + 600], capture_output=True, text=True, check=True)
+        out += r.stdout.split("\n")[:-1]
+    return out
+
+
+def test_compute_linear_load_equals_reference():
+    g = np.load(os.path.join(ROOT, "tests", "golden", "math_helpers.npz"))
+    lines = _run("load", g["n"])
+    got = np.array([[int(v) for v in ln.split()] for ln in lines], np.uint32)
+    assert np.array_equal(got, g["load"])
+    # the properties callers rely on: enough threads for every item up to the grid limit, never an empty launch
+    n = g["n"].astype(np.uint64)
+    small = n <= 65535 * 1024
+    assert (got[small, 0].astype(np.uint64) * got[small, 1] >= n[small]).all() and (got >= 1).all() and got[:, 0].max() == 65535
+
+
+def test_interpolate_linear_equals_reference():
+    g = np.load(os.path.join(ROOT, "tests", "golden", "math_helpers.npz"))
+    got = np.array([int(v) for v in _run("lerpf", g["f"].view(np.uint32).reshape(-1))], np.uint32)
+    assert np.array_equal(got, g["lerp_f"].view(np.uint32))
+    gotd = np.array([int(v) for v in _run("lerpd", g["d"].view(np.uint64).reshape(-1))], np.uint64)
+    assert np.array_equal(gotd, g["lerp_d"].view(np.uint64))
+    assert subprocess.run([_exe(), "vec"], capture_output=True, text=True, check=True).stdout.strip() == "ok"
