@@ -1,8 +1,9 @@
-# round-1 closing run: all GPU tests, smoke, the default bench, the TMA A/B probe, ncu of the TMA kernel
+# round-1 closing run (N=1): all GPU tests, smoke, both bench arms, launch list of the bench under ncu
 set -x
-( time timeout 1500 python -m pytest tests -m gpu -q ) > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"
-timeout 600 python benchmarks/tma_probe.py 40 > gpurun_out/tma_probe.log 2>&1; echo "probe rc=$?"
-timeout 600 python benchmarks/tma_probe.py 4 bitprob > gpurun_out/tma_probe_short.log 2>&1 && \
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_collide_tma -s 6 -c 1 -f -o gpurun_out/r1_collide_tma python benchmarks/tma_probe.py 4 bitprob > gpurun_out/ncu_tma.log 2>&1; echo "ncu rc=$?"
-tail -5 gpurun_out/pytest_gpu.log; tail -3 gpurun_out/smoke.log; tail -20 gpurun_out/tma_probe.log; ls -la gpurun_out
+( time timeout 900 python -m pytest tests -m gpu -q ) > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"
+timeout 600 python bench.py --steps 100 --warmup 3 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "bench rc=$?"
+timeout 600 python bench.py --impl reference --steps 100 --warmup 3 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
+timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_plain_bench.log 2>&1 && \
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file gpurun_out/r1_launches_bench_summary.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_bench.log 2>&1; echo "ncu rc=$?"
+tail -4 gpurun_out/pytest_gpu.log; cat gpurun_out/smoke.log | tail -2; cat gpurun_out/bench_ref.json | cut -c1-400
