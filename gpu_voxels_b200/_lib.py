@@ -91,6 +91,7 @@ SIGNATURES = {
     "gvx_map_read_file": (C.c_int, [u64, C.c_char_p]),
     "gvx_list_write_file": (C.c_int, [u64, C.c_char_p]),
     "gvx_list_read_file": (C.c_int, [u64, C.c_char_p]),
+    "gvx_list_merge": (C.c_int, [u64, u64, vp, C.c_int]),
     "gvx_pointcloud_file_load": (C.c_int, [C.c_char_p, C.c_int, C.c_int, vp, f32, P(vp), P(u64)]),
     "gvx_pointcloud_file_free": (None, [vp]),
     "gvx_insert_pointcloud_file": (C.c_int, [u64, C.c_char_p, C.c_int, C.c_int, C.c_int, vp, f32, P(C.c_int)]),

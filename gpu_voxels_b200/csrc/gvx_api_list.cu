@@ -92,6 +92,38 @@ int list_insert(VoxList& l, const float* xyz_d, uint64_t n, const MetaDesc& meta
   return GVX_OK;
 }
 
+// TemplateVoxelList<BitVoxel>::merge (GV/voxellist/TemplateVoxelList.hpp:548-600): append the other list's entries
+// (ids + getVoxelIndexSigned(offset), coordinates + offset, voxels or the single new meaning), then make_unique
+int list_merge(VoxList& l, const VoxList& o, const int32_t off3[3], int new_meaning) {
+  const uint64_t n = o.size, total = l.size + n;
+  if (total >= 0xFFFFFFFFull) return fail(GVX_ERR_INVALID, "voxel list would exceed 2^32-1 entries");
+  if (n == 0) return GVX_OK;
+  const int nxt = l.cur ^ 1;
+  int rc = list_reserve(l, nxt, total);
+  if (rc) return rc;
+  rc = list_reserve_scratch(l, total, 0);
+  if (rc) return rc;
+  ListBuild b{};
+  b.old_ids = l.ids[l.cur]; b.old_coords = l.coords[l.cur]; b.old_voxels = l.voxels[l.cur]; b.old_size = l.size;
+  b.n_new = n;
+  b.add_ids = o.ids[o.cur]; b.add_coords = o.coords[o.cur]; b.add_voxels = o.voxels[o.cur];
+  // getVoxelIndexSigned (GV/voxelmap/kernels/VoxelMapOperations.h:61-74) in ptrdiff_t, truncated to the uint32 id
+  const int64_t lin = (int64_t)off3[2] * l.dx * l.dy + (int64_t)off3[1] * l.dx + (int64_t)off3[0];
+  b.add_id_off = (uint32_t)lin;
+  for (int k = 0; k < 3; ++k) b.add_coord_off[k] = off3[k];
+  b.add_meaning = new_meaning;
+  b.dx = l.dx; b.dy = l.dy; b.side = l.side;
+  b.single_meaning = 0;
+  b.keys_in = l.keys_in; b.keys_out = l.keys_out; b.vals_in = l.vals_in; b.vals_out = l.vals_out;
+  b.new_meaning = l.new_meaning; b.tmp = l.tmp; b.tmp_bytes = l.tmp_bytes;
+  b.out_ids = l.ids[nxt]; b.out_coords = l.coords[nxt]; b.out_voxels = l.voxels[nxt];
+  GVX_CUDA(launch_list_build(lctx(), b));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  l.size = g.result_h->count;
+  l.cur = nxt;
+  return GVX_OK;
+}
+
 struct ListCollideArgs {
   VoxList* l; Map* m; int64_t off;
 };
@@ -217,6 +249,22 @@ int gvx_list_size(gvx_handle_t h, uint64_t* size) {
   if (!l || !size) return fail(GVX_ERR_INVALID, "unknown list handle or null pointer");
   *size = l->size;
   return GVX_OK;
+}
+
+int gvx_list_merge(gvx_handle_t h, gvx_handle_t other, const int32_t voxel_offset[3], int new_meaning) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  VoxList* l = find_list(h);
+  VoxList* o = find_list(other);
+  if (!l || !o) return fail(GVX_ERR_INVALID, "unknown list handle");
+  if (new_meaning < -1 || new_meaning > 255) return fail(GVX_ERR_INVALID, "meaning %d out of range", new_meaning);
+  static const int32_t zero[3] = {0, 0, 0};
+  if (l == o) {  // merging a list into itself: the reference appends a copy of its own entries; with no offset and
+                 // no new meaning that changes nothing, otherwise the source would be overwritten while it is read
+    if ((!voxel_offset || (!voxel_offset[0] && !voxel_offset[1] && !voxel_offset[2])) && new_meaning < 0) return GVX_OK;
+    return fail(GVX_ERR_UNSUPPORTED, "merging a list into itself with an offset or a new meaning");
+  }
+  return list_merge(*l, *o, voxel_offset ? voxel_offset : zero, new_meaning);
 }
 
 int gvx_list_insert_points(gvx_handle_t h, const float* xyz, uint64_t n, int mem_kind, int meaning) {

@@ -84,6 +84,11 @@ cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels,
 struct ListBuild {
   const uint32_t* old_ids; const uint32_t* old_coords; const uint8_t* old_voxels; uint64_t old_size;
   const float* xyz_d; uint64_t n_new;
+  // merge (TemplateVoxelList::merge): n_new entries of ANOTHER list instead of points when add_ids != nullptr; their
+  // ids / coordinates are shifted by add_id_off / add_coord_off (uint32 wrap-around like the reference's operator),
+  // their voxels replaced by the single bit add_meaning when it is >= 0
+  const uint32_t* add_ids = nullptr; const uint32_t* add_coords = nullptr; const uint8_t* add_voxels = nullptr;
+  uint32_t add_id_off = 0; int32_t add_coord_off[3] = {0, 0, 0}; int add_meaning = -1;
   uint32_t dx, dy; float side;
   MetaDesc meta;        // prefix_d == nullptr: every point gets single_meaning
   int single_meaning;

@@ -27,12 +27,15 @@ namespace gvx {
 __global__ void __launch_bounds__(256)
 k_list_keys(const uint32_t* __restrict__ old_ids, unsigned long long s, const float* __restrict__ xyz,
             unsigned long long n, uint32_t dx, uint32_t dy, float side, MetaDesc d, int single_meaning,
-            uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint8_t* __restrict__ new_meaning) {
+            uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint8_t* __restrict__ new_meaning,
+            const uint32_t* __restrict__ add_ids, uint32_t add_id_off) {
   const unsigned long long stride = (unsigned long long)gridDim.x * 256;
   for (unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x; i < s + n; i += stride) {
     uint32_t id;
     if (i < s) {
       id = old_ids[i];
+    } else if (add_ids) {  // merge: entry of the other list, id + signed linear offset in uint32 arithmetic
+      id = add_ids[i - s] + add_id_off;
     } else {
       const unsigned long long p = i - s;
       const float x = __ldg(xyz + 3 * p), y = __ldg(xyz + 3 * p + 1), z = __ldg(xyz + 3 * p + 2);
@@ -62,7 +65,8 @@ k_list_merge(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ val
              const uint8_t* __restrict__ old_voxels, const float* __restrict__ xyz,
              const uint8_t* __restrict__ new_meaning, float side, uint32_t* __restrict__ out_ids,
              uint32_t* __restrict__ out_coords, uint32_t* __restrict__ out_voxels, ResultBlock* out_d,
-             ResultBlock* out_h) {
+             ResultBlock* out_h, const uint32_t* __restrict__ add_coords, const uint8_t* __restrict__ add_voxels,
+             int3 add_coord_off, int add_meaning) {
   const unsigned long long stride = (unsigned long long)gridDim.x * 256;
   for (unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x; i < total; i += stride) {
     const uint32_t key = keys[i], src = vals[i], slot = pos[i] - 1u;
@@ -78,6 +82,22 @@ k_list_merge(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ val
         out_coords[3 * (size_t)slot] = old_coords[3 * (size_t)src];
         out_coords[3 * (size_t)slot + 1] = old_coords[3 * (size_t)src + 1];
         out_coords[3 * (size_t)slot + 2] = old_coords[3 * (size_t)src + 2];
+      }
+    } else if (add_coords) {  // an entry of the merged list
+      const unsigned long long p = src - s;
+      if (add_meaning >= 0) {
+        atomicOr(ov + (add_meaning >> 5), 1u << (add_meaning & 31));
+      } else {
+        const BitVoxelWords v = ld_voxel_stream(add_voxels + (size_t)p * kBitVoxelBytes);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (v.w[k]) atomicOr(ov + k, v.w[k]);
+      }
+      if (head) {
+        out_ids[slot] = key;
+        out_coords[3 * (size_t)slot] = add_coords[3 * p] + (uint32_t)add_coord_off.x;
+        out_coords[3 * (size_t)slot + 1] = add_coords[3 * p + 1] + (uint32_t)add_coord_off.y;
+        out_coords[3 * (size_t)slot + 2] = add_coords[3 * p + 2] + (uint32_t)add_coord_off.z;
       }
     } else {
       const unsigned long long p = src - s;
@@ -126,7 +146,7 @@ cudaError_t launch_list_build(const LaunchCtx& c, const ListBuild& b) {
   const int grid = list_grid(c, total);
   *c.launches += 3;
   k_list_keys<<<grid, 256, 0, c.stream>>>(b.old_ids, b.old_size, b.xyz_d, b.n_new, b.dx, b.dy, b.side, b.meta,
-                                          b.single_meaning, b.keys_in, b.vals_in, b.new_meaning);
+                                          b.single_meaning, b.keys_in, b.vals_in, b.new_meaning, b.add_ids, b.add_id_off);
   size_t tmp = b.tmp_bytes;
   cudaError_t e = cub::DeviceRadixSort::SortPairs(b.tmp, tmp, b.keys_in, b.keys_out, b.vals_in, b.vals_out,
                                                   (long long)total, 0, 32, c.stream);
@@ -139,7 +159,9 @@ cudaError_t launch_list_build(const LaunchCtx& c, const ListBuild& b) {
   if (e != cudaSuccess) return e;
   k_list_merge<<<grid, 256, 0, c.stream>>>(b.keys_out, b.vals_out, b.vals_in, total, b.old_size, b.old_coords,
                                            b.old_voxels, b.xyz_d, b.new_meaning, b.side, b.out_ids, b.out_coords,
-                                           (uint32_t*)b.out_voxels, c.result_d, c.result_hmap_d);
+                                           (uint32_t*)b.out_voxels, c.result_d, c.result_hmap_d, b.add_coords, b.add_voxels,
+                                           make_int3(b.add_coord_off[0], b.add_coord_off[1], b.add_coord_off[2]),
+                                           b.add_meaning);
   return cudaGetLastError();
 }
 

@@ -134,6 +134,24 @@ class BitVectorVoxelList:
         _lib.check(self._L.gvx_list_subtract(self.handle, other.handle))
         return True
 
+    def merge(self, other, voxel_offset=None, new_meaning=None, metric_offset=None):
+        """TemplateVoxelList<BitVoxel>::merge (GV/voxellist/TemplateVoxelList.hpp:548-608): append `other`'s entries (ids
+        and coordinates shifted by voxel_offset, voxels replaced by the single bit new_meaning if given), make unique.
+        metric_offset is converted like mapToVoxelsSigned (floor(c / side) in fp32). Only lists can be merged."""
+        if not isinstance(other, BitVectorVoxelList):
+            _log_error("THIS OPERATION IS NOT YET SUPPORTED BY THE DATA STRUCTURE!")
+            return False
+        if metric_offset is not None:
+            m = np.asarray(metric_offset, np.float32)
+            voxel_offset = np.floor(m / np.float32(self.m_voxel_side_length)).astype(np.int32)
+        off = None
+        if voxel_offset is not None:
+            off = np.ascontiguousarray(voxel_offset, dtype=np.int32).reshape(3)
+        _lib.check(self._L.gvx_list_merge(self.handle, other.handle,
+                                          off.ctypes.data_as(C.c_void_p) if off is not None else None,
+                                          -1 if new_meaning is None else int(new_meaning)))
+        return True
+
     def equals(self, other):
         eq = C.c_int(0)
         _lib.check(self._L.gvx_list_equals(self.handle, other.handle, C.byref(eq)))

@@ -53,6 +53,11 @@ public:
     insertPointCloud(points, voxel_meaning);
     return true;
   }
+  // GV/GpuVoxelsMap.h:186-204: copy the other map's data into this one; lists merge lists, dense maps refuse
+  virtual bool merge(const GpuVoxelsMapSharedPtr other, const Vector3i& voxel_offset = Vector3i(),
+                     const BitVoxelMeaning* new_meaning = NULL) = 0;
+  virtual bool merge(const GpuVoxelsMapSharedPtr other, const Vector3f& metric_offset,
+                     const BitVoxelMeaning* new_meaning = NULL) = 0;
   virtual void clearMap() = 0;
   virtual void clearBitVoxelMeaning(BitVoxelMeaning voxel_meaning) = 0;
   virtual std::size_t getMemoryUsage() const = 0;

@@ -186,6 +186,27 @@ public:
                                     int32_t(std::floor(metric_offset.y / m_voxel_side_length)),
                                     int32_t(std::floor(metric_offset.z / m_voxel_side_length))));
   }
+  // GV/voxellist/TemplateVoxelList.hpp:548-608: only another BitVectorVoxelList can be merged; its entries are
+  // appended (shifted by voxel_offset, voxels replaced by *new_meaning if given) and the list is made unique again
+  virtual bool merge(const GpuVoxelsMapSharedPtr other, const Vector3i& voxel_offset = Vector3i(),
+                     const BitVoxelMeaning* new_meaning = NULL)
+  {
+    if (!other || other->getMapType() != MT_BITVECTOR_VOXELLIST)
+    {
+      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, GPU_VOXELS_MAP_OPERATION_NOT_YET_SUPPORTED << endl);
+      return false;
+    }
+    const BitVoxelList<length>* o = static_cast<const BitVoxelList<length>*>(other.get());
+    detail::DualLock guard(this->m_mutex, o->m_mutex);
+    const int32_t off[3] = {voxel_offset.x, voxel_offset.y, voxel_offset.z};
+    return gvxCheck(gvx_list_merge(m_handle, o->m_handle, off, new_meaning ? int(*new_meaning) : -1), "merge");
+  }
+  virtual bool merge(const GpuVoxelsMapSharedPtr other, const Vector3f& metric_offset, const BitVoxelMeaning* new_meaning = NULL)
+  {
+    return merge(other, Vector3i(int32_t(std::floor(metric_offset.x / m_voxel_side_length)),
+                                 int32_t(std::floor(metric_offset.y / m_voxel_side_length)),
+                                 int32_t(std::floor(metric_offset.z / m_voxel_side_length))), new_meaning);
+  }
   // GV/voxellist/TemplateVoxelList.hpp:806-825
   bool equals(const BitVoxelList<length>& other) const
   {

@@ -91,6 +91,17 @@ public:
     lock_guard guard(this->m_mutex);
     return gvxCheck(gvx_map_write_file(m_handle, path.c_str()), "writeToDisk");
   }
+  // TemplateVoxelMap::merge x2 (GV/voxelmap/TemplateVoxelMap.hpp:801-813): not supported by dense maps there either
+  virtual bool merge(const GpuVoxelsMapSharedPtr, const Vector3i& = Vector3i(), const BitVoxelMeaning* = NULL)
+  {
+    LOGGING_ERROR_C(VoxelmapLog, TemplateVoxelMap, GPU_VOXELS_MAP_OPERATION_NOT_YET_SUPPORTED << endl);
+    return false;
+  }
+  virtual bool merge(const GpuVoxelsMapSharedPtr, const Vector3f&, const BitVoxelMeaning* = NULL)
+  {
+    LOGGING_ERROR_C(VoxelmapLog, TemplateVoxelMap, GPU_VOXELS_MAP_OPERATION_NOT_YET_SUPPORTED << endl);
+    return false;
+  }
   virtual bool readFromDisk(const std::string path)
   {
     lock_guard guard(this->m_mutex);

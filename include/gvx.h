@@ -276,6 +276,12 @@ int gvx_list_size(gvx_handle_t h, uint64_t* size);
  * GV/voxellist/kernels/VoxelListOperations.hpp:41-61) followed by make_unique (:141-208): one entry per point with NO
  * bounds check (outside points get wrapped uint32 ids), stable sort by id, OR-merge of equal ids, unique. */
 int gvx_list_insert_points(gvx_handle_t h, const float* xyz, uint64_t n, int mem_kind, int meaning);
+/* TemplateVoxelList<BitVoxel>::merge (GV/voxellist/TemplateVoxelList.hpp:548-608; applyOffsetOperator :68-90): the
+ * entries of `other` are appended to `list` -- ids shifted by getVoxelIndexSigned(voxel_offset), coordinates by
+ * voxel_offset (both in uint32 arithmetic, no bounds check, as there), voxels replaced by the single bit new_meaning
+ * unless it is -1 -- and the list is made unique again (equal ids OR-merged, the list's own entry keeps its
+ * coordinates). voxel_offset nullable = 0. The reference does not compare the two lists' reference dimensions. */
+int gvx_list_merge(gvx_handle_t list, gvx_handle_t other, const int32_t voxel_offset[3], int new_meaning);
 /* TemplateVoxelList::insertMetaPointCloud x2 (GV/voxellist/TemplateVoxelList.hpp:343-403, kernels
  * GV/voxellist/kernels/VoxelListOperations.hpp:63-120); n_meanings == 1 or n_clouds */
 int gvx_list_insert_meta(gvx_handle_t h, const float* xyz, int mem_kind, const uint32_t* cloud_sizes, uint32_t n_clouds,

@@ -251,6 +251,33 @@ def list_subtract(a, b):
     a.ids, a.coords, a.voxels = a.ids[keep].copy(), a.coords[keep].copy(), a.voxels[keep].copy()
 
 
+def list_merge(a, b, voxel_offset=(0, 0, 0), new_meaning=None):
+    """TemplateVoxelList<BitVoxel>::merge, TemplateVoxelList.hpp:548-600: b's entries appended to a with
+    applyOffsetOperator (:68-90: coords + offset and id + getVoxelIndexSigned(offset), both truncated to uint32), their
+    voxels replaced by the single bit new_meaning if given; then make_unique (:141-208): stable sort by id, equal ids
+    OR-merged, the first entry (a's own, if any) keeps its coordinates"""
+    off = np.asarray(voxel_offset, np.int64)
+    dx, dy = int(a.dims[0]), int(a.dims[1])
+    lin = int(off[2]) * dx * dy + int(off[1]) * dx + int(off[0])
+    b_ids = ((b.ids.astype(np.int64) + lin) & 0xFFFFFFFF).astype(np.uint32)
+    b_coords = ((b.coords.astype(np.int64) + off) & 0xFFFFFFFF).astype(np.uint32)
+    b_vox = b.voxels.copy()
+    if new_meaning is not None:
+        b_vox[:] = 0
+        b_vox[:, new_meaning >> 3] = 1 << (new_meaning & 7)
+    ids = np.concatenate([a.ids, b_ids])
+    coords = np.concatenate([a.coords, b_coords])
+    vox = np.concatenate([a.voxels, b_vox])
+    order = np.argsort(ids, kind="stable")
+    ids, coords, vox = ids[order], coords[order], vox[order]
+    head = np.ones(len(ids), bool)
+    head[1:] = ids[1:] != ids[:-1]
+    slot = np.cumsum(head) - 1
+    out = np.zeros((int(head.sum()), 32), np.uint8)
+    np.bitwise_or.at(out, slot, vox)
+    a.ids, a.coords, a.voxels = ids[head].copy(), coords[head].copy(), out
+
+
 def list_shift(a, shift):
     """BitVoxelList::shiftLeftSweptVolumeIDs, BitVoxelList.hpp:560-582"""
     for k in range(len(a.voxels)):

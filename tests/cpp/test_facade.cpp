@@ -481,7 +481,31 @@ BOOST_AUTO_TEST_CASE(voxellist_equals_disk_io_subtract)
   BOOST_CHECK_MESSAGE(a.size() == 19, "Number of cubes after subtract == 19");
 }
 
-// TemplateVoxelMap::writeToDisk / readFromDisk (GV/voxelmap/TemplateVoxelMap.hpp:666-799)
+// TemplateVoxelList<BitVoxel>::merge (GV/voxellist/TemplateVoxelList.hpp:548-608): the two 27-voxel boxes of
+// bitvoxellist_insert_metapointcloud as two lists -> 46 entries; with an offset and a new meaning; maps are refused
+BOOST_AUTO_TEST_CASE(voxellist_merge)
+{
+  std::shared_ptr<BitVectorVoxelList> a(new BitVectorVoxelList(Vector3ui(dimX, dimY, dimZ), 1, MT_BITVECTOR_VOXELLIST));
+  std::shared_ptr<BitVectorVoxelList> b(new BitVectorVoxelList(Vector3ui(dimX, dimY, dimZ), 1, MT_BITVECTOR_VOXELLIST));
+  a->insertPointCloud(createBoxOfPoints(Vector3f(1.1, 1.1, 1.1), Vector3f(3.9, 3.9, 3.9), 0.1), BitVoxelMeaning(11));
+  b->insertPointCloud(createBoxOfPoints(Vector3f(2.1, 2.1, 2.1), Vector3f(4.9, 4.9, 4.9), 0.1), BitVoxelMeaning(12));
+  BOOST_CHECK(a->merge(b));
+  BOOST_CHECK_MESSAGE(a->size() == 46, "27 + 27 - 8 shared voxels");
+  BOOST_CHECK(b->size() == 27);
+  BitVectorVoxel types;
+  BOOST_CHECK(a->collideWithTypes(b.get(), types, 1.0) == 27);
+  BOOST_CHECK(types.bitVector().getBit(11) && types.bitVector().getBit(12));
+  // shifted by (10, 0, 0) with a new meaning: 27 new, disjoint voxels carrying only bit 40
+  const BitVoxelMeaning forty = BitVoxelMeaning(40);
+  BOOST_CHECK(a->merge(b, Vector3i(10, 0, 0), &forty));
+  BOOST_CHECK(a->size() == 46 + 27);
+  BOOST_CHECK(a->merge(b, Vector3f(10.5f, 0.f, 0.f), &forty));  // metric: floor(10.5 / 1) = 10 -> nothing new
+  BOOST_CHECK(a->size() == 46 + 27);
+  GpuVoxelsMapSharedPtr map(new ProbVoxelMap(Vector3ui(dimX, dimY, dimZ), 1.f, MT_PROBAB_VOXELMAP));
+  BOOST_CHECK(!a->merge(map));
+}
+
+// TemplateVoxelMap::writeToDisk / readFromDisk (GV/voxelmap/TemplateVoxelMap.hpp:666-799)// TemplateVoxelMap::writeToDisk / readFromDisk (GV/voxelmap/TemplateVoxelMap.hpp:666-799)
 BOOST_AUTO_TEST_CASE(voxelmap_disk_io)
 {
   ProbVoxelMap m1(Vector3ui(40, 30, 20), 0.5f, MT_PROBAB_VOXELMAP), m2(Vector3ui(40, 30, 20), 0.5f, MT_PROBAB_VOXELMAP);

@@ -156,6 +156,50 @@ def test_random_lists_match_oracle(gv, oracle, na, nb):
     assert len(a) == 0
 
 
+def _same(g, r):
+    ids, co, vx = g.download()
+    return np.array_equal(ids, r.ids) and np.array_equal(co, r.coords) and np.array_equal(vx, r.voxels)
+
+
+@pytest.mark.parametrize("na,nb", [(30000, 4000), (4000, 30000), (0, 5000), (5000, 0)])
+@pytest.mark.parametrize("off,new_meaning", [(None, None), ((3, -2, 5), None), ((-4, 1, 0), 77), ((0, 0, 0), 200),
+                                             ((-70, 0, 0), None)])
+def test_list_merge_matches_oracle(gv, oracle, na, nb, off, new_meaning):
+    """TemplateVoxelList<BitVoxel>::merge (GV/voxellist/TemplateVoxelList.hpp:548-608): ids, coordinates (kept from the
+    list's own entry for shared ids) and OR-merged voxels, with voxel offsets (incl. one that wraps ids below zero) and
+    a replacing meaning"""
+    dims, side = (64, 64, 40), 0.01
+    a, ra = _random_list(gv, oracle, 210 + na % 7, dims, side, na) if na else (gv.BitVectorVoxelList(dims, side), oracle.VoxelList(dims, side))
+    b, rb = _random_list(gv, oracle, 310 + nb % 7, dims, side, nb) if nb else (gv.BitVectorVoxelList(dims, side), oracle.VoxelList(dims, side))
+    assert a.merge(b, off, new_meaning)
+    oracle.list_merge(ra, rb, off if off is not None else (0, 0, 0), new_meaning)
+    assert _same(a, ra) and len(a) == len(ra.ids)
+    assert _same(b, rb)  # the merged list is untouched
+    # a second merge of the same list changes nothing but the (already present) bits
+    assert a.merge(b, off, new_meaning)
+    oracle.list_merge(ra, rb, off if off is not None else (0, 0, 0), new_meaning)
+    assert _same(a, ra)
+
+
+def test_list_merge_reference_boxes_and_metric_offset(gv, oracle):
+    """the reference's two 27-voxel boxes as two lists: 46 entries after the merge, 8 with both meanings; a metric offset
+    is floor(c / side) per axis like mapToVoxelsSigned; a map cannot be merged into a list"""
+    l1, l2 = gv.BitVectorVoxelList(DIMS, 1.0), gv.BitVectorVoxelList(DIMS, 1.0)
+    l1.insertPointCloud(_box(oracle, (1.1, 1.1, 1.1), (3.9, 3.9, 3.9), 0.1), 11)
+    l2.insertPointCloud(_box(oracle, (2.1, 2.1, 2.1), (4.9, 4.9, 4.9), 0.1), 12)
+    assert l1.merge(l2) and len(l1) == 46
+    bits = np.unpackbits(l1.download()[2], axis=1, bitorder="little")
+    assert int((bits[:, 11] & bits[:, 12]).sum()) == 8
+    l3 = gv.BitVectorVoxelList(DIMS, 1.0)
+    assert l3.merge(l2, metric_offset=(10.5, -0.5, 2.0))  # -> voxel offset (10, -1, 2)
+    r2, r3 = oracle.VoxelList(DIMS, 1.0), oracle.VoxelList(DIMS, 1.0)
+    r2.insert_points(_box(oracle, (2.1, 2.1, 2.1), (4.9, 4.9, 4.9), 0.1), 12)
+    oracle.list_merge(r3, r2, (10, -1, 2))
+    assert _same(l3, r3) and l3.download()[1].min(axis=0).tolist() == [12, 1, 4]
+    assert not l3.merge(gv.BitVectorVoxelMap(DIMS, 1.0))
+    assert l3.merge(l3) and _same(l3, r3)  # into itself without offset: nothing changes
+
+
 def test_list_list_edge_cases(gv, oracle):
     dims = (16, 16, 16)
     a, b = gv.BitVectorVoxelList(dims, 0.1), gv.BitVectorVoxelList(dims, 0.1)
