@@ -111,6 +111,30 @@ public:
     return -1;
   }
 
+  // sizes, names and bounding boxes of the sub-clouds on stdout (GV/helpers/MetaPointCloud.cu:543-590)
+  void debugPointCloud() const
+  {
+    std::cout << "================== hostMetaPointCloud DBG ==================" << std::endl;
+    std::cout << "hostDebugMetaPointCloud DBG: NumClouds: " << m_sizes.size() << std::endl;
+    size_t first = 0;
+    for (size_t c = 0; c < m_sizes.size(); first += m_sizes[c], ++c)
+    {
+      std::cout << "hostDebugMetaPointCloud DBG: '" << getCloudName(uint16_t(c)) << "' CloudSize[" << c << "]: "
+                << m_sizes[c] << std::endl;
+      if (m_sizes[c] == 0) continue;
+      Vector3f lo = m_points[first], hi = m_points[first];
+      for (size_t j = first + 1; j < first + m_sizes[c]; ++j)
+      {
+        const Vector3f& p = m_points[j];
+        lo.x = p.x < lo.x ? p.x : lo.x; lo.y = p.y < lo.y ? p.y : lo.y; lo.z = p.z < lo.z ? p.z : lo.z;
+        hi.x = hi.x < p.x ? p.x : hi.x; hi.y = hi.y < p.y ? p.y : hi.y; hi.z = hi.z < p.z ? p.z : hi.z;
+      }
+      std::cout << "hostDebugMetaPointCloud DBG: CloudSize[" << c << "] bounds: Min[" << lo.x << ", " << lo.y << ", "
+                << lo.z << "], Max[" << hi.x << ", " << hi.y << ", " << hi.z << "]" << std::endl;
+    }
+    std::cout << "================== END hostMetaPointCloud DBG ==================" << std::endl;
+  }
+
   void syncToDevice()
   {
     reserveDevice(m_points.size());

@@ -77,6 +77,14 @@ public:
   Vector3f* getPoints() const { return m_host.empty() ? NULL : const_cast<Vector3f*>(&m_host[0]); }
   const std::vector<Vector3f>& getPointVector() const { return m_host; }
 
+  // GV/helpers/PointCloud.cu:349-358
+  void print()
+  {
+    for (size_t i = 0; i < m_host.size(); i++)
+      std::cout << "Point " << i << ": (" << m_host[i].x << ", " << m_host[i].y << ", " << m_host[i].z << ")" << std::endl;
+    std::cout << std::endl << std::endl;
+  }
+
   void resize(uint32_t new_number_of_points)
   {
     m_host.resize(new_number_of_points);
