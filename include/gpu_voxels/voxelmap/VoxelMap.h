@@ -9,6 +9,7 @@
 #include <climits>
 
 #include <gpu_voxels/GpuVoxelsMap.h>
+#include <gpu_voxels/voxel/ProbabilisticVoxel.h>
 #include <gpu_voxels/voxel/SVCollider.h>
 
 namespace gpu_voxels {
@@ -184,6 +185,10 @@ public:
   ProbVoxelMap(int8_t* dev_data, const Vector3ui dim, const float voxel_side_length, const MapType map_type = MT_PROBAB_VOXELMAP)
     : AbstractVoxelMap(dim, voxel_side_length, map_type, dev_data), m_init_sensor(false) {}
 
+  // typed view of the raw voxel array (GV/voxelmap/TemplateVoxelMap.h:getDeviceDataPtr): one int8 log-odds byte per voxel
+  ProbabilisticVoxel* getDeviceDataPtr() { return static_cast<ProbabilisticVoxel*>(getVoidDeviceDataPtr()); }
+  const ProbabilisticVoxel* getConstDeviceDataPtr() const { return static_cast<const ProbabilisticVoxel*>(getConstVoidDeviceDataPtr()); }
+
   // ProbVoxelMap only knows eBVM_OCCUPIED; anything else is a logged no-op (GV/voxelmap/ProbVoxelMap.hpp:110-116)
   virtual void clearBitVoxelMeaning(BitVoxelMeaning voxel_meaning)
   {
@@ -250,6 +255,10 @@ template <std::size_t length>
 class BitVoxelMap : public AbstractVoxelMap
 {
 public:
+  // typed view of the raw voxel array (GV/voxelmap/TemplateVoxelMap.h:getDeviceDataPtr): 32 bytes per voxel
+  BitVoxel<length>* getDeviceDataPtr() { return static_cast<BitVoxel<length>*>(getVoidDeviceDataPtr()); }
+  const BitVoxel<length>* getConstDeviceDataPtr() const { return static_cast<const BitVoxel<length>*>(getConstVoidDeviceDataPtr()); }
+
   BitVoxelMap(const Vector3ui dim, const float voxel_side_length, const MapType map_type = MT_BITVECTOR_VOXELMAP)
     : AbstractVoxelMap(dim, voxel_side_length, map_type, NULL) {}
   BitVoxelMap(BitVoxel<length>* dev_data, const Vector3ui dim, const float voxel_side_length, const MapType map_type = MT_BITVECTOR_VOXELMAP)

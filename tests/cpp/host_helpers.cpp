@@ -5,12 +5,14 @@
 //   host_helpers load <n>...            -> "<blocks> <threads>"
 //   host_helpers lerpf <a> <b> <r> ...  (uint32 bit patterns)  -> "<bits>"
 //   host_helpers lerpd <a> <b> <r> ...  (uint64 bit patterns)  -> "<bits>"
+//   host_helpers prob                   -> 256 lines of updateOccupancy results, one line of insert results, "ok"
 #include <cinttypes>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
 #include <gpu_voxels/helpers/MathHelpers.h>
+#include <gpu_voxels/voxel/ProbabilisticVoxel.h>
 
 template <class T, class U> static T bits_to(U u) { T t; static_assert(sizeof(T) == sizeof(U), "size"); std::memcpy(&t, &u, sizeof t); return t; }
 
@@ -41,6 +43,31 @@ int main(int argc, char** argv)
       const double r = bits_to<double>(uint64_t(std::strtoull(argv[i + 2], NULL, 10)));
       std::printf("%" PRIu64 "\n", bits_to<uint64_t>(gpu_voxels::interpolateLinear(a, b, r)));
     }
+  else if (mode == "prob")
+  {  // ProbabilisticVoxel: updateOccupancy for every (occupancy, delta) pair, then insert for every meaning
+    for (int occ = -128; occ <= 127; ++occ)
+    {
+      for (int d = -128; d <= 127; ++d)
+      {
+        gpu_voxels::ProbabilisticVoxel v;
+        v.occupancy() = gpu_voxels::Probability(occ);
+        std::printf("%d ", int(v.updateOccupancy(gpu_voxels::Probability(d))));
+      }
+      std::printf("\n");
+    }
+    for (int m = 0; m < 256; ++m)
+    {
+      gpu_voxels::ProbabilisticVoxel v;
+      v.occupancy() = 5;
+      v.insert(gpu_voxels::BitVoxelMeaning(m));
+      std::printf("%d ", int(v.getOccupancy()));
+    }
+    gpu_voxels::ProbabilisticVoxel u, w;
+    w.occupancy() = 100;
+    const bool ok = u.getOccupancy() == -128 && !u.isOccupied(-127.5f) && u.isOccupied(-128.f) && w.isOccupied(99.5f) &&
+                    !w.isOccupied(100.5f) && gpu_voxels::ProbabilisticVoxel::reduce(w, w).getOccupancy() == 127;
+    std::printf("\n%s\n", ok ? "ok" : "MISMATCH");
+  }
   else if (mode == "vec")
   {  // the vector and map overloads against the scalar one
     std::vector<float> a(3), b(3);

@@ -210,6 +210,21 @@ def math_helpers():
     print("math helpers:", len(n), "launch shapes,", len(f), "+", len(d), "interpolations")
 
 
+def prob_voxel():
+    """ProbabilisticVoxel::updateOccupancy for all 256 x 256 (occupancy, delta) pairs and ::insert for all 256 meanings,
+    from the reference's own header (GV/voxel/ProbabilisticVoxel.hpp via oracle/_ref/libgvref_cpu.so)"""
+    L = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libgvref_cpu.so"))
+    upd = np.array([[L.gvrefcpu_update_occupancy(o, d) for d in range(-128, 128)] for o in range(-128, 128)], np.int8)
+    ins = np.zeros(256, np.int8)
+    for m in range(256):
+        cell = np.array([5], np.int8)
+        L.gvrefcpu_insert_at(C.c_void_p(cell.ctypes.data), 1, C.c_uint64(0), m)
+        ins[m] = cell[0]
+    np.savez_compressed(os.path.join(HERE, "prob_voxel.npz"), update=upd, insert=ins)
+    print("prob voxel: 65536 updates,", int((ins == 127).sum()), "meanings -> 127,", int((ins == -127).sum()), "-> -127")
+
+
 if __name__ == "__main__":
     main()
     math_helpers()
+    prob_voxel()

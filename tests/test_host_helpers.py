@@ -48,3 +48,17 @@ def test_interpolate_linear_equals_reference():
     gotd = np.array([int(v) for v in _run("lerpd", g["d"].view(np.uint64).reshape(-1))], np.uint64)
     assert np.array_equal(gotd, g["lerp_d"].view(np.uint64))
     assert subprocess.run([_exe(), "vec"], capture_output=True, text=True, check=True).stdout.strip() == "ok"
+
+
+def test_probabilistic_voxel_value_type_equals_reference():
+    """include/gpu_voxels/voxel/ProbabilisticVoxel.h against the reference's header for EVERY (occupancy, delta) pair and
+    every meaning (tests/golden/prob_voxel.npz, from GV/voxel/ProbabilisticVoxel.hpp compiled for the host)"""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "prob_voxel.npz"))
+    hdr = os.path.join(ROOT, "include", "gpu_voxels", "voxel", "ProbabilisticVoxel.h")
+    if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
+        os.remove(EXE)
+    lines = subprocess.run([_exe(), "prob"], capture_output=True, text=True, check=True).stdout.split("\n")
+    upd = np.array([[int(v) for v in ln.split()] for ln in lines[:256]], np.int8)
+    assert np.array_equal(upd, g["update"])
+    assert np.array_equal(np.array([int(v) for v in lines[256].split()], np.int8), g["insert"])
+    assert lines[257] == "ok"
