@@ -59,6 +59,56 @@ private:
   uint8_t m_bytes[(num_bits + 7) / 8];
 };
 
+// Swept-volume IDs move `shift_size` (<= 56) bits towards bit 0; the four non-swept-volume bits of byte 0 end up
+// cleared (performLeftShift, GV/helpers/BitVector.h:361-402). Host restatement of what gvx_map_shift_sv_ids /
+// gvx_list_shift_sv_ids do per voxel on the device.
+template <std::size_t num_bits>
+inline void performLeftShift(BitVector<num_bits>& bit_vector, const uint8_t shift_size)
+{
+  const uint32_t n_bytes = uint32_t((num_bits + 7) / 8);
+  uint8_t* v = bit_vector.bytes();
+  uint64_t window = 0;
+  for (uint32_t k = 0; k < 8 && k < n_bytes; ++k) window |= uint64_t(v[k]) << (8 * k);
+  for (uint32_t k = 0; k < n_bytes; ++k)
+  {
+    uint8_t shifted = uint8_t(window >> shift_size);
+    if (k == 0) shifted &= 0xF0;
+    window >>= 8;
+    if (k + 8 < n_bytes) window |= uint64_t(v[k + 8]) << 56;
+    v[k] = shifted;
+  }
+}
+
+// Do v1 and v2 share a swept-volume bit (4..253) within +-`bit_margin` positions, v1 displaced by `sv_offset`?
+// (bitMarginCollisionCheck, GV/helpers/BitVector.h:416-471.) A 64-bit window slides over v2 -- its byte 0 without the
+// four non-swept-volume bits -- and each visited byte of `collisions` (may be NULL) is OVERWRITTEN with the hits
+// found for that byte of v1; sv_offset % 8 moves the first visited bit, sv_offset / 8 shifts the probe. Host
+// restatement of the per-voxel test of gvx_collide_map_map_bitcheck; margins above 31 are undefined there.
+template <std::size_t num_bits>
+inline bool bitMarginCollisionCheck(const BitVector<num_bits>& v1, const BitVector<num_bits>& v2,
+                                    BitVector<num_bits>* collisions, const uint8_t bit_margin, const uint32_t sv_offset)
+{
+  const uint8_t* a = v1.bytes();
+  const uint8_t* b = v2.bytes();
+  uint64_t window = uint64_t(b[0] & 0xF0) << 32;
+  for (uint32_t k = 1; k < 4; ++k) window |= uint64_t(b[k]) << (32 + 8 * k);
+  const uint32_t first_bit = uint8_t(sv_offset % 8), probe_shift = uint8_t(sv_offset / 8);
+  bool any = false;
+  for (uint32_t bit = uint32_t(eBVM_SWEPT_VOLUME_START) + first_bit; bit < uint32_t(eBVM_SWEPT_VOLUME_END); bit += 8)
+  {
+    uint64_t probe = uint64_t(a[bit >> 3]) << (32 - bit_margin + probe_shift);
+    uint8_t hits = 0;
+    for (uint32_t step = 0; step <= 2u * bit_margin; ++step, probe <<= 1)
+      hits |= uint8_t((probe & window) >> (32 - bit_margin + step));
+    if (collisions) collisions->setByte(bit, hits);
+    any = any || hits != 0;
+    window >>= 8;
+    if (bit < num_bits - 32) window |= uint64_t(b[(bit + 32) >> 3]) << 56;
+  }
+  if (collisions) return !collisions->isZero();  // the reference looks at the whole output vector, old bytes included
+  return any;
+}
+
 template <std::size_t length>
 class BitVoxel
 {

@@ -12,6 +12,7 @@
 #include <cstring>
 
 #include <gpu_voxels/helpers/MathHelpers.h>
+#include <gpu_voxels/voxel/BitVoxel.h>
 #include <gpu_voxels/voxel/ProbabilisticVoxel.h>
 
 template <class T, class U> static T bits_to(U u) { T t; static_assert(sizeof(T) == sizeof(U), "size"); std::memcpy(&t, &u, sizeof t); return t; }
@@ -67,6 +68,36 @@ int main(int argc, char** argv)
     const bool ok = u.getOccupancy() == -128 && !u.isOccupied(-127.5f) && u.isOccupied(-128.f) && w.isOccupied(99.5f) &&
                     !w.isOccupied(100.5f) && gpu_voxels::ProbabilisticVoxel::reduce(w, w).getOccupancy() == 127;
     std::printf("\n%s\n", ok ? "ok" : "MISMATCH");
+  }
+  else if (mode == "sv")
+  {  // lines of hex on stdin: "m <v1> <v2> <coll_in> <margin> <sv_offset>" -> "<result> <coll_out>",
+     //                        "s <v> <shift>" -> "<shifted>"
+    char kind;
+    char h1[80], h2[80], h3[80];
+    unsigned p1, p2;
+    auto parse = [](const char* hex, gpu_voxels::BitVector<256>& v) {
+      for (int k = 0; k < 32; ++k) { unsigned byte; std::sscanf(hex + 2 * k, "%2x", &byte); v.bytes()[k] = uint8_t(byte); }
+    };
+    auto print = [](const gpu_voxels::BitVector<256>& v) { for (int k = 0; k < 32; ++k) std::printf("%02x", v.bytes()[k]); };
+    while (std::scanf(" %c", &kind) == 1)
+    {
+      if (kind == 'm')
+      {
+        if (std::scanf("%79s %79s %79s %u %u", h1, h2, h3, &p1, &p2) != 5) return 3;
+        gpu_voxels::BitVector<256> v1, v2, coll;
+        parse(h1, v1); parse(h2, v2); parse(h3, coll);
+        const bool r = gpu_voxels::bitMarginCollisionCheck(v1, v2, &coll, uint8_t(p1), p2);
+        std::printf("%d ", r ? 1 : 0); print(coll); std::printf("\n");
+      }
+      else
+      {
+        if (std::scanf("%79s %u", h1, &p1) != 2) return 3;
+        gpu_voxels::BitVector<256> v;
+        parse(h1, v);
+        gpu_voxels::performLeftShift(v, uint8_t(p1));
+        print(v); std::printf("\n");
+      }
+    }
   }
   else if (mode == "vec")
   {  // the vector and map overloads against the scalar one

@@ -62,3 +62,28 @@ def test_probabilistic_voxel_value_type_equals_reference():
     assert np.array_equal(upd, g["update"])
     assert np.array_equal(np.array([int(v) for v in lines[256].split()], np.int8), g["insert"])
     assert lines[257] == "ok"
+
+
+def test_bitvector_window_check_and_shift_equal_reference():
+    """bitMarginCollisionCheck / performLeftShift of the facade (include/gpu_voxels/voxel/BitVoxel.h) on the 1500 golden
+    vectors recorded from the reference's BitVector.h (tests/golden/sweptvolume.npz): results and every output byte"""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "sweptvolume.npz"))
+    hdr = os.path.join(ROOT, "include", "gpu_voxels", "voxel", "BitVoxel.h")
+    if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
+        os.remove(EXE)
+    hx = lambda v: bytes(v).hex()  # noqa: E731
+    n = len(g["v1"])
+    fresh = np.zeros(32, np.uint8)
+    lines = []
+    for k in range(n):
+        lines.append("m %s %s %s %d %d" % (hx(g["v1"][k]), hx(g["v2"][k]), hx(g["coll_in"][k]), g["margin"][k], g["sv_offset"][k]))
+        lines.append("m %s %s %s %d %d" % (hx(g["v1"][k]), hx(g["v2"][k]), hx(fresh), g["margin"][k], g["sv_offset"][k]))
+        lines.append("s %s %d" % (hx(g["v1"][k]), g["shift"][k]))
+    out = subprocess.run([_exe(), "sv"], input="\n".join(lines) + "\n", capture_output=True, text=True, check=True).stdout.split("\n")
+    assert len(out) >= 3 * n
+    for k in range(n):
+        r, c = out[3 * k].split()
+        assert int(r) == int(g["result"][k]) and c == hx(g["coll_out"][k]), k
+        r, c = out[3 * k + 1].split()
+        assert int(r) == int(g["result_fresh"][k]) and c == hx(g["coll_fresh"][k]), k
+        assert out[3 * k + 2] == hx(g["shifted"][k]), k
