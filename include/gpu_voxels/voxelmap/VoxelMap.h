@@ -9,6 +9,7 @@
 #include <climits>
 
 #include <gpu_voxels/GpuVoxelsMap.h>
+#include <gpu_voxels/voxel/DefaultCollider.h>
 #include <gpu_voxels/voxel/ProbabilisticVoxel.h>
 #include <gpu_voxels/voxel/SVCollider.h>
 
@@ -116,6 +117,25 @@ public:
     int flag = 0;
     gvxCheck(gvx_collide_map_map_any(m_handle, other->m_handle, coll_threshold, &flag), "collisionCheck");
     return flag != 0;
+  }
+
+  // TemplateVoxelMap::collisionCheckWithCounter / ...RelativeTransform (GV/voxelmap/TemplateVoxelMap.hpp:477-519) with
+  // a collider object: number of colliding voxels, `this` gets eBVM_COLLISION marks. A collider with two different
+  // thresholds is refused (the kernels apply one threshold to both sides, as every public collideWith does).
+  uint32_t collisionCheckWithCounter(AbstractVoxelMap* other, DefaultCollider collider = DefaultCollider())
+  {
+    return collisionCheckWithCounterRelativeTransform(other, collider);
+  }
+  uint32_t collisionCheckWithCounterRelativeTransform(AbstractVoxelMap* other, DefaultCollider collider = DefaultCollider(),
+                                                      const Vector3i& offset = Vector3i())
+  {
+    float thr = 0.f;
+    if (!collider.asFloatThreshold(&thr))
+    {
+      LOGGING_ERROR_C(VoxelmapLog, TemplateVoxelMap, "DefaultCollider with two different thresholds: " << GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+      return 0;
+    }
+    return uint32_t(collideMapMap(other, thr, offset));
   }
 
 protected:

@@ -13,6 +13,7 @@
 
 #include <gpu_voxels/helpers/MathHelpers.h>
 #include <gpu_voxels/voxel/BitVoxel.h>
+#include <gpu_voxels/voxel/DefaultCollider.h>
 #include <gpu_voxels/voxel/ProbabilisticVoxel.h>
 
 template <class T, class U> static T bits_to(U u) { T t; static_assert(sizeof(T) == sizeof(U), "size"); std::memcpy(&t, &u, sizeof t); return t; }
@@ -98,6 +99,31 @@ int main(int argc, char** argv)
         print(v); std::printf("\n");
       }
     }
+  }
+  else if (mode == "f2p")
+  {  // DefaultCollider::floatToProbability of float bit patterns, and the float the facade hands to the C ABI for a
+     // collider built from that Probability: "<probability> <round trip ok>"
+    for (int i = 2; i < argc; ++i)
+    {
+      const float thr = bits_to<float>(uint32_t(std::strtoul(argv[i], NULL, 10)));
+      const gpu_voxels::Probability p = gpu_voxels::DefaultCollider::floatToProbability(thr);
+      float back = 0.f;
+      const bool ok = gpu_voxels::DefaultCollider(p, p).asFloatThreshold(&back) &&
+                      gpu_voxels::DefaultCollider::floatToProbability(back) == p &&
+                      gpu_voxels::DefaultCollider(thr).getThreshold1() == p;
+      std::printf("%d %d\n", int(p), ok ? 1 : 0);
+    }
+    // predicates on value types
+    gpu_voxels::ProbabilisticVoxel lo, hi;
+    lo.occupancy() = -5; hi.occupancy() = 5;
+    gpu_voxels::BitVectorVoxel freeOnly, occ;
+    freeOnly.insert(gpu_voxels::eBVM_FREE); occ.insert(gpu_voxels::BitVoxelMeaning(77));
+    const gpu_voxels::DefaultCollider half(0.5f);  // threshold 0
+    const bool ok = !half.collide(lo, hi) && half.collide(hi, hi) && half.collide(hi) && !half.collide(lo) &&
+                    half.collide(hi, occ) && !half.collide(hi, freeOnly) && !half.collide(lo, occ) &&
+                    half.collide(occ, hi) && !half.collide(freeOnly, hi) && half.collide(occ, occ) &&
+                    !half.collide(occ, freeOnly) && !gpu_voxels::DefaultCollider(gpu_voxels::Probability(1), gpu_voxels::Probability(9)).asFloatThreshold(NULL);
+    std::printf("%s\n", ok ? "ok" : "MISMATCH");
   }
   else if (mode == "vec")
   {  // the vector and map overloads against the scalar one

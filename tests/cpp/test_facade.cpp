@@ -33,6 +33,12 @@ BOOST_AUTO_TEST_CASE(collision)
   map_1.insertPointCloud(pts, eBVM_OCCUPIED);
   map_2.insertPointCloud(pts, eBVM_OCCUPIED);
   BOOST_CHECK_MESSAGE(map_1.collideWith(&map_2, 0.1) == (size_t)numberOfPoints, "All collisions detected.");
+  // the same through the collider-object entry points (GV/voxelmap/TemplateVoxelMap.hpp:477-519)
+  BOOST_CHECK(map_1.collisionCheckWithCounter(&map_2, DefaultCollider(0.1f)) == (uint32_t)numberOfPoints);
+  BOOST_CHECK(map_1.collisionCheckWithCounterRelativeTransform(&map_2, DefaultCollider(Probability(-101), Probability(-101))) == (uint32_t)numberOfPoints);
+  BOOST_CHECK(map_1.collisionCheckWithCounter(&map_2, DefaultCollider(Probability(1), Probability(2))) == 0);  // refused
+  ProbabilisticVoxel* raw = map_1.getDeviceDataPtr();
+  BOOST_CHECK(raw != NULL && (const void*)raw == map_1.getConstVoidDeviceDataPtr());
 }
 
 BOOST_AUTO_TEST_CASE(collision_with_offset)

@@ -87,3 +87,20 @@ def test_bitvector_window_check_and_shift_equal_reference():
         r, c = out[3 * k + 1].split()
         assert int(r) == int(g["result_fresh"][k]) and c == hx(g["coll_fresh"][k]), k
         assert out[3 * k + 2] == hx(g["shifted"][k]), k
+
+
+def test_default_collider_thresholds_equal_reference():
+    """DefaultCollider::floatToProbability of the facade on the 406 golden thresholds recorded from the reference's
+    collider (tests/golden/conversions.npz), the Probability -> float round trip used for the C ABI, and the five
+    collide() predicates"""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "conversions.npz"))
+    hdr = os.path.join(ROOT, "include", "gpu_voxels", "voxel", "DefaultCollider.h")
+    if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
+        os.remove(EXE)
+    lines = _run("f2p", g["thr"].view(np.uint32))
+    got = np.array([[int(v) for v in ln.split()] for ln in lines if ln not in ("ok", "MISMATCH")])
+    want = g["f2p"].astype(np.int32).astype(np.int8).astype(np.int32)   # the reference keeps the low 8 bits
+    assert np.array_equal(got[:, 0], want)
+    inside = (g["thr"] >= 0) & (g["thr"] <= 1)
+    assert got[inside, 1].all()
+    assert "MISMATCH" not in lines and "ok" in lines
