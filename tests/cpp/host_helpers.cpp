@@ -15,6 +15,7 @@
 #include <gpu_voxels/voxel/BitVoxel.h>
 #include <gpu_voxels/voxel/DefaultCollider.h>
 #include <gpu_voxels/voxel/ProbabilisticVoxel.h>
+#include <gpu_voxels/voxel/SVCollider.h>
 
 template <class T, class U> static T bits_to(U u) { T t; static_assert(sizeof(T) == sizeof(U), "size"); std::memcpy(&t, &u, sizeof t); return t; }
 
@@ -123,7 +124,21 @@ int main(int argc, char** argv)
                     half.collide(hi, occ) && !half.collide(hi, freeOnly) && !half.collide(lo, occ) &&
                     half.collide(occ, hi) && !half.collide(freeOnly, hi) && half.collide(occ, occ) &&
                     !half.collide(occ, freeOnly) && !gpu_voxels::DefaultCollider(gpu_voxels::Probability(1), gpu_voxels::Probability(9)).asFloatThreshold(NULL);
-    std::printf("%s\n", ok ? "ok" : "MISMATCH");
+    // SVCollider (GV/voxel/SVCollider.hpp:54-116): the second Prob voxel is compared STRICTLY; the types variants
+    // OR the colliding voxel's meanings into the output vector; Bit x Bit is the windowed ID test
+    const gpu_voxels::SVCollider sv(0.5f, 1);  // thresholds 0, window 1
+    gpu_voxels::ProbabilisticVoxel zero;
+    zero.occupancy() = 0;
+    gpu_voxels::BitVector<256> seen;
+    gpu_voxels::BitVectorVoxel id20, id21, id23;
+    id20.insert(gpu_voxels::BitVoxelMeaning(20)); id21.insert(gpu_voxels::BitVoxelMeaning(21)); id23.insert(gpu_voxels::BitVoxelMeaning(23));
+    bool ok2 = sv.collide(zero, hi) && !sv.collide(hi, zero) && sv.collide(zero) && sv.collide(hi, occ) && sv.collide(occ, hi) &&
+               !sv.collide(freeOnly, hi) && sv.collide(occ, hi, &seen) && seen.getBit(77) && !sv.collide(occ, lo, &seen) &&
+               sv.collide(hi, id20, &seen) && seen.getBit(20);
+    gpu_voxels::BitVector<256> win;
+    ok2 = ok2 && sv.collide(id20, id21, &win) && !sv.collide(id20, id23, &win) && win.isZero() &&
+          gpu_voxels::SVCollider(gpu_voxels::Probability(3), gpu_voxels::Probability(3), std::size_t(2)).getWindowSize() == 2;
+    std::printf("%s\n", ok && ok2 ? "ok" : "MISMATCH");
   }
   else if (mode == "vec")
   {  // the vector and map overloads against the scalar one

@@ -388,7 +388,8 @@ BOOST_AUTO_TEST_CASE(bitvoxelmap_bitshift)
     map_1.insertPointCloud(points, BitVoxelMeaning(type_int - shift_size));
     map_2.shiftLeftSweptVolumeIDs(shift_size);
     BitVectorVoxel types_voxel;
-    SVCollider collider(1.0, 1);
+    const size_t window_size = 1;
+    SVCollider collider(1.0, window_size);  // as GV/test/testing_voxelmap.cu:197 writes it
     size_t num_collisions = map_1.collisionCheckBitvector(&map_2, collider, types_voxel.bitVector());
     if (shift_size <= shift_start) BOOST_CHECK(num_collisions == points.size());
     else BOOST_CHECK(num_collisions == 0);

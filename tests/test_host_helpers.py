@@ -94,9 +94,10 @@ def test_default_collider_thresholds_equal_reference():
     collider (tests/golden/conversions.npz), the Probability -> float round trip used for the C ABI, and the five
     collide() predicates"""
     g = np.load(os.path.join(ROOT, "tests", "golden", "conversions.npz"))
-    hdr = os.path.join(ROOT, "include", "gpu_voxels", "voxel", "DefaultCollider.h")
-    if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
-        os.remove(EXE)
+    for h in ("DefaultCollider.h", "SVCollider.h"):
+        hdr = os.path.join(ROOT, "include", "gpu_voxels", "voxel", h)
+        if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
+            os.remove(EXE)
     lines = _run("f2p", g["thr"].view(np.uint32))
     got = np.array([[int(v) for v in ln.split()] for ln in lines if ln not in ("ok", "MISMATCH")])
     want = g["f2p"].astype(np.int32).astype(np.int8).astype(np.int32)   # the reference keeps the low 8 bits
