@@ -453,8 +453,7 @@ def run_gpu_arm(args):
         # the collide kernel alone: (1) the default path (robot map's occupancy summary + streamed ProbVoxelMap) and
         # (2) the voxel-streaming kernel (GVX_OPT_USE_SUMMARY = 0: both grids read in full, the reference's pattern)
         def collide_alone(k):
-            _lib.check(L.gvx_collide_map_map_async(envs[k % P].handle, robs[k % P].handle, THR, None, 1,
-                                                   C.c_void_p(count_d.data_ptr())))
+            _lib.check(L.gvx_collide_map_map_async(env_h[k % P], rob_h[k % P], THR, None, 1, count_p))
         # (1a) one event pair per launch, L2 flushed before each: includes the event pair's own ~2-3 us
         l2_flush = torch.zeros(256 << 20, dtype=torch.uint8, device="cuda")
         for k, (e0, e1) in enumerate(kev):
@@ -465,8 +464,11 @@ def run_gpu_arm(args):
         torch.cuda.synchronize()
         del l2_flush
         # (1b) `steps` launches back to back over the rotating pairs (268 MB of summaries per rotation > L2), one event
-        # pair around all of them: the average launch duration without per-launch event overhead
+        # pair around all of them: the average launch duration without per-launch event overhead. A ~1 ms spin kernel
+        # in front lets the host queue the launches while the GPU is busy, so the figure is the device's
+        # launch-to-launch time and not the Python call rate.
         evb0, evb1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda._sleep(2_000_000)
         evb0.record(stream)
         for k in range(args.steps):
             collide_alone(k)
@@ -555,7 +557,7 @@ def run_gpu_arm(args):
                          "algorithmic_bytes_per_launch": BYTES_PER_VOXEL_SUMMARY * n_vox,
                          "algorithmic_bytes_per_voxel": BYTES_PER_VOXEL_SUMMARY, "kernel_ms_avg": k_b2b,
                          "kernel_ms_avg_how": "%d launches back to back over %d rotating map pairs (268 MB of summaries per "
-                                              "rotation > L2), one CUDA event pair around all of them" % (args.steps, N_PAIRS),
+                                              "rotation > L2), queued behind a 1 ms spin kernel, one CUDA event pair around all of them" % (args.steps, N_PAIRS),
                          "kernel_ms_single_launch_l2_flushed": k_avg, "kernel_ms_single_launch_min": k_ms[0],
                          "frac_of_8000_nominal": achieved / 8000.0,
                          "note": "default path: one summary bit per voxel and side (2 x 16.8 MB for 512^3) + the Prob bytes of "
