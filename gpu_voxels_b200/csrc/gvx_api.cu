@@ -643,7 +643,9 @@ int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const
   int64_t off, i0, i1;
   int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1);
   if (rc) return rc;
-  GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
+  LaunchCtx c = lctx();
+  if (count_d) c.result_hmap_d = nullptr;  // the result stays on the device: nothing is written to mapped host memory
+  GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
                                   mark != 0, false, (unsigned long long*)count_d,
                                   g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
   return GVX_OK;
@@ -705,7 +707,9 @@ int gvx_collide_map_map_allreduce(gvx_handle_t ha, gvx_handle_t hb, float thr, i
   int64_t off, i0, i1;
   int rc = collide_prepare(ha, hb, nullptr, &a, &b, &off, &i0, &i1);
   if (rc) return rc;
-  GVX_CUDA(launch_collide_map_map(lctx_allreduce(), a->data, a->type, b->data, b->type, i0, i1, 0,
+  LaunchCtx c = lctx_allreduce();
+  if (!count && count_d) c.result_hmap_d = nullptr;  // device-only result
+  GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, 0,
                                   float_to_probability(thr), mark != 0, false, (unsigned long long*)count_d,
                                   g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
   if (count) {

@@ -86,20 +86,21 @@ __device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (
     unsigned long long tot = sh_tot;
     if (pr.world > 1) tot = peer_allreduce_sum(tot, pr);
     if (threadIdx.x == 0) {
+      // out_h == nullptr: an asynchronous call whose result stays on the device -- no store into mapped host memory
+      // and no system-scope fence (a PCIe round trip) at the end of the kernel
       out_d->count = tot;
-      out_h->count = tot;
       out_d->flag = tot != 0;
-      out_h->flag = tot != 0;
+      if (out_h) { out_h->count = tot; out_h->flag = tot != 0; }
       if (count_out_d) *count_out_d = tot;
       if (TYPES) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const uint32_t m = atomicExch(&s->mask[k], 0u);
           out_d->mask[k] = m;
-          out_h->mask[k] = m;
+          if (out_h) out_h->mask[k] = m;
         }
       }
-      __threadfence_system();
+      if (out_h) __threadfence_system();
     }
   }
   __syncthreads();
