@@ -249,6 +249,8 @@ def run_gpu_arm(args):
     torch.cuda.set_stream(stream)
     assert stream.cuda_stream != 0
     _lib.check(L.gvx_set_stream(C.c_void_p(stream.cuda_stream)))
+    if args.pdl is not None:
+        _lib.check(L.gvx_set_option(4, args.pdl))
 
     n_vox = DX * DY * DZ
     dims = (DX, DY, DZ * world)
@@ -595,6 +597,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--diag", action="store_true", help="print a per-phase timing breakdown to stderr")
     ap.add_argument("--nccl-count", action="store_true", help="all-reduce the count with NCCL instead of in-kernel")
+    ap.add_argument("--pdl", type=int, default=None, choices=[0, 1],
+                    help="GVX_OPT_PDL: programmatic dependent launch for the per-step kernels (library default when absent)")
     ap.add_argument("--fold", default="auto", choices=["auto", "dispatch", "multi"],
                     help="sharded runs: route each rank's frame to the owning ranks in-kernel (dispatch), fold all frames on "
                          "every rank (multi), or auto: dispatch for host frames and, from 4 ranks on, for resident frames")

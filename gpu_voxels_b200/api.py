@@ -416,6 +416,7 @@ ProbVoxelMap.insertSensorDataDispatch = _insert_sensor_data_dispatch
 GVX_OPT_USE_SUMMARY = 1
 GVX_OPT_DH_CHECK_BITS = 2
 GVX_OPT_COLLIDE_TMA = 3
+GVX_OPT_PDL = 4
 REVOLUTE, PRISMATIC = 0, 1  # robot::DHJointType, GV/robot/dh_robot/KinematicLink.h:37-41
 
 

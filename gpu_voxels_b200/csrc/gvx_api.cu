@@ -389,6 +389,7 @@ int gvx_set_option(int option, int value) {
   std::lock_guard<std::mutex> lk(g.mu);
   switch (option) {
     case GVX_OPT_USE_SUMMARY: g.use_summary = value != 0; return GVX_OK;
+    case GVX_OPT_PDL: g.pdl = value != 0; return GVX_OK;
     case GVX_OPT_COLLIDE_TMA:
       if (value < -1 || value > 5) return fail(GVX_ERR_INVALID, "GVX_OPT_COLLIDE_TMA must be in [-1, 5]");
       g.collide_tma = value; return GVX_OK;

@@ -262,6 +262,8 @@ k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const
                    const uint32_t* __restrict__ occ_b, long long n, int thr, ReduceScratch* scratch, ResultBlock* out_d,
                    ResultBlock* out_h, unsigned long long* count_out_d, PeerReduce pr) {
   constexpr int U = 4;
+  pdl_wait();
+  pdl_launch_dependents();  // at most kCtasPerSm CTAs per SM, all resident: the next kernel's CTAs queue up behind
   __shared__ long long sh_g[kThreads / 32][kQueuePerWarp];
   __shared__ uint32_t sh_h[kThreads / 32][kQueuePerWarp];
   long long* qg = sh_g[threadIdx.x >> 5];
@@ -381,11 +383,12 @@ template <int AT, int BT, bool ASUM, bool BSUM>
 static cudaError_t launch_summary(const LaunchCtx& c, int grid, uint8_t* a, const uint8_t* b, const uint32_t* occ_a,
                                   const uint32_t* occ_b, long long n, int thr, bool mark, bool types,
                                   unsigned long long* out) {
+  cudaError_t err = cudaSuccess;
 #define GVX_GO(M, T)                                                                                       \
   do {                                                                                                     \
     if (ASUM && BSUM)                                                                                      \
-      k_collide_summary2<AT, BT, M, T><<<grid, kThreads, 0, c.stream>>>(                                   \
-          a, b, occ_a, occ_b, n, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);              \
+      err = pdl_launch(k_collide_summary2<AT, BT, M, T>, grid, kThreads, c.stream, c.pdl, a, b, occ_a, occ_b, n, thr, \
+                       c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);                             \
     else                                                                                                   \
       k_collide_summary<AT, BT, M, T, ASUM, BSUM><<<grid, kThreads, 0, c.stream>>>(                        \
           a, b, occ_a, occ_b, n, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);              \
@@ -393,7 +396,7 @@ static cudaError_t launch_summary(const LaunchCtx& c, int grid, uint8_t* a, cons
   if (types && AT == kMapBit) { if (mark) GVX_GO(true, (AT == kMapBit)); else GVX_GO(false, (AT == kMapBit)); }
   else                        { if (mark) GVX_GO(true, false); else GVX_GO(false, false); }
 #undef GVX_GO
-  return cudaGetLastError();
+  return err != cudaSuccess ? err : cudaGetLastError();
 }
 
 // CTAs for `work` CTA-iterations when at most max_grid CTAs are resident: every CTA gets the same number of

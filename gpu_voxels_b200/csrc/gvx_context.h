@@ -105,6 +105,7 @@ struct Context {
   bool disp_connected = false;
   unsigned long long disp_epoch = 0;
   uint32_t* disp_err_h = nullptr; uint32_t* disp_err_hmap_d = nullptr;
+  bool pdl = true;       // GVX_OPT_PDL
   int collide_tma = -1;  // GVX_OPT_COLLIDE_TMA: -1 auto (TMA where it measured faster), 0 never, 1..5 always (shape k)
   bool use_summary = true;  // GVX_OPT_USE_SUMMARY: collide kernels may read occupancy summaries instead of voxels
   uint64_t launches = 0;
@@ -142,6 +143,7 @@ inline LaunchCtx lctx() {
   LaunchCtx c{g.stream, g.sm_count, g.scratch_d, g.result_d, g.result_hmap_d, &g.launches, PeerReduce{}};
   c.peer.world = 1;
   c.tma = g.collide_tma;
+  c.pdl = g.pdl;
   return c;
 }
 // launch context of a counting kernel that all-reduces its count over the connected peers (next epoch)

@@ -5,6 +5,11 @@
 
 namespace gvx {
 
+// programmatic dependent launch (gvx_internal.h pdl_launch): no-ops in a kernel that was launched plainly
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+
 constexpr int kBitVoxelBytes = 32;
 constexpr int kMapBit = 0;   // MT_BITVECTOR_VOXELMAP
 constexpr int kMapProb = 4;  // MT_PROBAB_VOXELMAP

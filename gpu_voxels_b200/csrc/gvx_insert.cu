@@ -124,6 +124,8 @@ __device__ __forceinline__ bool robot_bit_set(const uint8_t* __restrict__ robot,
 __global__ void __launch_bounds__(kInsThreads)
 k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n, const Affine12 pose, int delta,
                  const uint8_t* __restrict__ robot, uint32_t robot_bit) {
+  pdl_wait();               // the kernel before this one (a collide on this map, as a rule) is complete
+  pdl_launch_dependents();  // every CTA of this grid is resident at once: the next kernel may move in behind it
   const float* P = pose.a;
   const uint32_t sx = coord_to_voxel(P[3], m.side), sy = coord_to_voxel(P[7], m.side), sz = coord_to_voxel(P[11], m.side);
   const bool sensor_inside = sx < m.dx && sy < m.dy && sz < m.dz;
@@ -488,9 +490,8 @@ cudaError_t launch_transform(const LaunchCtx& c, const float* in_d, float* out_d
 cudaError_t launch_update_logodds(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
                                   const Affine12& pose, int delta, const void* robot_d, uint32_t robot_bit) {
   ++*c.launches;
-  k_update_logodds<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, n, pose, delta, (const uint8_t*)robot_d,
-                                                                    robot_bit);
-  return cudaGetLastError();
+  return pdl_launch(k_update_logodds, grid_for(c, n, 8), kInsThreads, c.stream, c.pdl, m, xyz_d, n, pose, delta,
+                    (const uint8_t*)robot_d, robot_bit);
 }
 
 cudaError_t launch_raycast_free(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,

@@ -15,7 +15,28 @@ struct LaunchCtx {
   uint64_t* launches;         // kernel launch counter (host)
   PeerReduce peer;            // world <= 1: no fused all-reduce
   int tma = 0;                // GVX_OPT_COLLIDE_TMA: -1 auto, 0 never, k > 0 = TMA bulk tiles of shape k for every pair
+  bool pdl = false;           // GVX_OPT_PDL: programmatic dependent launch for the per-step kernels (pdl_launch)
 };
+
+// Programmatic dependent launch. A kernel started through pdl_launch with pdl = true may become resident while the
+// kernel before it in the stream is still in its tail (its CTAs have passed griddepcontrol.launch_dependents or left);
+// such a kernel executes pdl_wait() (gvx_reduce.cuh) before its first global access, which returns once the
+// predecessor grid has completed and its writes are visible -- stream order for memory, minus the launch ramp.
+// Only kernels that begin with pdl_wait() may be launched with pdl = true.
+template <typename... KArgs, typename... Args>
+inline cudaError_t pdl_launch(void (*kernel)(KArgs...), int grid, int block, cudaStream_t stream, bool pdl,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1u : 0u;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 
 // collideWith map x map. a/b: device base pointers of the voxel arrays; a is indexed at i + off.
 // [i_begin, i_end) is the range of i for which 0 <= i + off < n. count_out_d: optional extra device

@@ -143,10 +143,14 @@ enum gvx_option {
   GVX_OPT_USE_SUMMARY = 1,   /* 0: always stream the voxels (the reference's access pattern) */
   GVX_OPT_DH_CHECK_BITS = 2, /* forward kinematics: sin/cos brackets of |v| * 2^-bits (default 50); smaller values send
                                 more configurations through the host re-computation (tests) */
-  GVX_OPT_COLLIDE_TMA = 3    /* the voxel-streaming collide kernels can be fed by TMA bulk tiles (cp.async.bulk into a
+  GVX_OPT_COLLIDE_TMA = 3,   /* the voxel-streaming collide kernels can be fed by TMA bulk tiles (cp.async.bulk into a
                                 shared-memory ring) instead of per-thread 256-bit loads; same results. -1 (default):
                                 where that measured faster (Bit x Prob on grids of >= 4 M voxels),
                                 0: never, 1..5: always, the value picks the tile x stages shape (1 = 512 voxels x 4) */
+  GVX_OPT_PDL = 4            /* 1 (default): the per-step kernels (log-odds frame update, summary collide) are started
+                                with programmatic dependent launch, so the launch ramp of one overlaps the tail of the
+                                kernel before it; they wait for that kernel's completion before touching memory, so
+                                results and ordering are those of a plain stream. 0: plain launches */
 };
 int gvx_set_option(int option, int value);
 

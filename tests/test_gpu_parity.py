@@ -212,6 +212,48 @@ def test_pinned_host_frames_pipelined_upload(gv, oracle):
     assert L.gvx_insert_points(bm.handle, C.c_void_p(pinned[0].data_ptr()), 10, 7, 9, None) == _lib.ERR_INVALID
 
 
+def test_step_loop_programmatic_dependent_launch(gv, oracle):
+    """GVX_OPT_PDL: frame update -> collide -> frame update ... queued back to back from device-resident frames, the
+    launch of each kernel overlapping the tail of the one before it. Every step's count and the final map equal the
+    oracle's sequence, with the option on and off (the collide of step k must see all of update k, update k+1 must
+    not overtake collide k, which marks nothing here but reads the bytes update k+1 raises)."""
+    import ctypes as C
+    import torch
+    from gpu_voxels_b200 import _lib
+    L = _lib.load()
+    dims, side, steps = (128, 128, 64), 0.02, 36
+    pose = np.ascontiguousarray(np.array([[0, 0, 1, 0.1], [-1, 0, 0, 1.28], [0, -1, 0, 0.5]], np.float32))
+    M = np.vstack([pose, np.array([[0, 0, 0, 1]], np.float32)])
+    frames = [_depth_frame(500 + f) for f in range(3)]
+    frames_d = [torch.from_numpy(np.ascontiguousarray(f)).cuda() for f in frames]
+    ref_b = oracle.new_map(BIT, dims)
+    for f in frames:
+        oracle.insert_points(ref_b, BIT, dims, side, np.ascontiguousarray(oracle.transform_points(M, f)), 11)
+    ref, want = oracle.new_map(PROB, dims), []
+    for k in range(steps):
+        oracle.update_logodds(ref, dims, side, frames[k % 3], pose, 23)
+        want.append(oracle.collide_map_map(ref, PROB, ref_b, BIT, dims[0] * dims[1] * dims[2], 0.7, 0, False))
+    assert len(set(want)) > 3  # voxels cross the threshold step after step
+    try:
+        for pdl in (1, 0, 1):
+            _lib.check(L.gvx_set_option(gv.GVX_OPT_PDL, pdl))
+            m, bm = _mk(gv, PROB, dims, side), _mk(gv, BIT, dims, side)
+            for f in frames:
+                bm.insertPointCloud(np.ascontiguousarray(oracle.transform_points(M, f)), 11)
+            count_d = torch.zeros(steps, dtype=torch.int64, device="cuda")
+            _lib.check(L.gvx_sync())
+            for k in range(steps):
+                t = frames_d[k % 3]
+                _lib.check(L.gvx_update_logodds(m.handle, C.c_void_p(t.data_ptr()), len(t), _lib.MEM_DEVICE,
+                                                pose.ctypes.data_as(C.c_void_p), 23))
+                _lib.check(L.gvx_collide_map_map_async(m.handle, bm.handle, 0.7, None, 0, C.c_void_p(count_d.data_ptr() + 8 * k)))
+            _lib.check(L.gvx_sync())
+            assert count_d.cpu().tolist() == want, pdl
+            assert np.array_equal(m.download(), ref), pdl
+    finally:
+        _lib.check(L.gvx_set_option(gv.GVX_OPT_PDL, 1))
+
+
 # ---- collisions --------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("n_real", [5, 15, 16, 70])  # <= 16 frames travel in the kernel parameters, more in a descriptor
 def test_update_logodds_multi_frame_equals_sequence(gv, oracle, n_real):
