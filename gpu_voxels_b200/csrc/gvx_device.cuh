@@ -143,9 +143,9 @@ struct PeerDispatch {
 };
 constexpr int kMaxGrid = 148 * 16;  // upper bound on CTAs of a reducing kernel
 struct ReduceScratch {
-  unsigned long long total;  // sum of the CTAs' counts; taken (and zeroed) by the last CTA
+  unsigned long long total;  // low 48 bits: sum of the CTAs' counts, above: arrivals (finish_block); zeroed by the last CTA
   uint32_t mask[8];          // OR of the CTAs' meaning masks; same protocol
-  unsigned int ticket;       // atomicInc wraps to 0 when the last CTA arrives
+  unsigned int ticket;       // k_insert's flag protocol: atomicInc wraps to 0 when the last CTA arrives
   unsigned int flag_accum;
 };
 

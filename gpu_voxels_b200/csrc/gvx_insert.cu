@@ -239,6 +239,8 @@ k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t*
   __shared__ float sh_pose[kMaxFramesSmem * 12];
   __shared__ uint32_t sh_prefix[kMaxFramesSmem + 1];
   __shared__ uint8_t sh_inside[kMaxFramesSmem];
+  pdl_wait();
+  pdl_launch_dependents();
   const bool in_smem = n_frames <= (uint32_t)kMaxFramesSmem;
   if (in_smem) {
     for (uint32_t k = threadIdx.x; k < n_frames * 12; k += kInsThreads) sh_pose[k] = poses_g[k];
@@ -300,6 +302,8 @@ k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t*
 // three FMAs and one division.
 __global__ void __launch_bounds__(kInsThreads)
 k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_constant__ FramesByValue fv, int delta) {
+  pdl_wait();
+  pdl_launch_dependents();
   const uint32_t f = fv.order[blockIdx.y];
   float P[12];
 #pragma unroll
@@ -515,11 +519,11 @@ cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, co
     // 4 points per thread and step. The grid is NOT divided among the frames: on a z-slab rank most frames belong to
     // other slabs and their CTAs retire after one read, leaving the SMs to the frame(s) that do the atomics
     int gx = grid_for(c, (longest + 3) / 4, 8);
-    k_update_logodds_frames<<<dim3((unsigned)gx, n_frames), kInsThreads, 0, c.stream>>>(m, xyz_d, *by_value, delta);
-  } else {
-    k_update_logodds_multi<<<grid_for(c, n, 8), kInsThreads, 0, c.stream>>>(m, xyz_d, prefix_d, poses_d, n_frames, delta);
+    return pdl_launch(k_update_logodds_frames, dim3((unsigned)gx, n_frames), kInsThreads, c.stream, c.pdl, m, xyz_d,
+                      *by_value, delta);
   }
-  return cudaGetLastError();
+  return pdl_launch(k_update_logodds_multi, dim3((unsigned)grid_for(c, n, 8)), kInsThreads, c.stream, c.pdl, m, xyz_d,
+                    prefix_d, poses_d, n_frames, delta);
 }
 
 cudaError_t launch_clear_bits(const LaunchCtx& c, void* data, uint64_t n_voxels, const uint32_t mask8[8], uint32_t* occ) {

@@ -24,10 +24,10 @@ struct LaunchCtx {
 // predecessor grid has completed and its writes are visible -- stream order for memory, minus the launch ramp.
 // Only kernels that begin with pdl_wait() may be launched with pdl = true.
 template <typename... KArgs, typename... Args>
-inline cudaError_t pdl_launch(void (*kernel)(KArgs...), int grid, int block, cudaStream_t stream, bool pdl,
+inline cudaError_t pdl_launch(void (*kernel)(KArgs...), dim3 grid, int block, cudaStream_t stream, bool pdl,
                               Args&&... args) {
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)grid);
+  cfg.gridDim = grid;
   cfg.blockDim = dim3((unsigned)block);
   cfg.stream = stream;
   cudaLaunchAttribute at[1];

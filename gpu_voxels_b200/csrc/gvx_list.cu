@@ -273,6 +273,7 @@ k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxel
   }
   const bool last = finish_block<MODE == 1>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
   if (MODE == 3 && last) {
+    __threadfence();  // acquire side of the arrival ticket: the other CTAs' histogram adds are in L2
     out_h->per_meaning[threadIdx.x] = __ldcg(&out_d->per_meaning[threadIdx.x]);
     __threadfence_system();
   }

@@ -92,6 +92,7 @@ k_list_list(const uint32_t* __restrict__ a_ids, const uint8_t* __restrict__ a_vo
   }
   const bool last = finish_block<MODE == 1>(cnt, acc, scratch, out_d, out_h, nullptr, pr);
   if (MODE == 3 && last) {
+    __threadfence();  // acquire side of the arrival ticket: the other CTAs' histogram adds are in L2
     out_h->per_meaning[threadIdx.x] = __ldcg(&out_d->per_meaning[threadIdx.x]);
   }
 }

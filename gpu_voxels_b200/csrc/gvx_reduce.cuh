@@ -39,9 +39,12 @@ __device__ __forceinline__ unsigned long long peer_allreduce_sum(unsigned long l
 }
 
 // Block-level finish shared by all counting kernels: reduce (count, mask) over the CTA, add it into the context's
-// accumulators with one atomic per CTA (8 more for a mask), take a ticket; the last CTA to arrive takes the totals,
+// accumulator together with an arrival ticket, one atomic per CTA (8 more for a mask); the last CTA to arrive has the total,
 // optionally all-reduces the count over the peers, and publishes the result to device memory and to the mapped pinned
 // host block. Returns true in the last CTA.
+constexpr int kTicketShift = 48;
+constexpr unsigned long long kTicketOne = 1ull << kTicketShift;
+
 template <bool TYPES>
 __device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (&acc)[8], ReduceScratch* s,
                                              ResultBlock* out_d, ResultBlock* out_h,
@@ -67,18 +70,21 @@ __device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (
     unsigned long long c = 0;
 #pragma unroll
     for (int w = 0; w < kThreads / 32; ++w) c += sh_cnt[w];
-    if (c) atomicAdd(&s->total, c);
     if (TYPES) {
 #pragma unroll
       for (int k = 0; k < 8; ++k)
         if (sh_mask[k]) atomicOr(&s->mask[k], sh_mask[k]);
+      __threadfence();  // the mask bits are in L2 before this CTA's arrival is
     }
-    __threadfence();
-    const unsigned int t = atomicInc(&s->ticket, gridDim.x - 1);  // wraps to 0 on the last arrival
-    sh_last = (t == gridDim.x - 1);
+    // count and arrival ticket travel in ONE 64-bit atomic (count in the low 48 bits, arrivals above; grids are
+    // <= kMaxGrid CTAs, counts <= the voxels of a 180 GB map): the tail of a reducing kernel is one L2 round trip per
+    // CTA, and the last arrival already holds the total
+    const unsigned long long old = atomicAdd(&s->total, c + kTicketOne);
+    sh_last = (unsigned)(old >> kTicketShift) + 1u == gridDim.x;
     if (sh_last) {
-      __threadfence();
-      sh_tot = atomicExch(&s->total, 0ull);
+      sh_tot = (old & (kTicketOne - 1ull)) + c;
+      s->total = 0ull;  // nobody else arrives in this launch; the next launch starts behind a kernel boundary
+      if (TYPES) __threadfence();
     }
   }
   __syncthreads();
