@@ -559,7 +559,10 @@ def run_gpu_arm(args):
                          "algorithmic_bytes_per_launch": BYTES_PER_VOXEL_SUMMARY * n_vox,
                          "algorithmic_bytes_per_voxel": BYTES_PER_VOXEL_SUMMARY, "kernel_ms_avg": k_b2b,
                          "kernel_ms_avg_how": "%d launches back to back over %d rotating map pairs (268 MB of summaries per "
-                                              "rotation > L2), queued behind a 1 ms spin kernel, one CUDA event pair around all of them" % (args.steps, N_PAIRS),
+                                              "rotation > L2), queued behind a 1 ms spin kernel, one CUDA event pair around all of them; "
+                                              "launched with programmatic dependent launch unless --pdl 0, so the ramp of a "
+                                              "launch overlaps the tail of the one before it, as in the timed step" % (args.steps, N_PAIRS),
+                         "pdl": args.pdl if args.pdl is not None else 1,
                          "kernel_ms_single_launch_l2_flushed": k_avg, "kernel_ms_single_launch_min": k_ms[0],
                          "frac_of_8000_nominal": achieved / 8000.0,
                          "note": "default path: one summary bit per voxel and side (2 x 16.8 MB for 512^3) + the Prob bytes of "
