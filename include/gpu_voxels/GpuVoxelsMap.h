@@ -38,6 +38,8 @@ public:
 
   virtual void insertPointCloud(const std::vector<Vector3f>& point_cloud, const BitVoxelMeaning voxel_meaning) = 0;
   virtual void insertPointCloud(const PointCloud& pointcloud, const BitVoxelMeaning voxel_meaning) = 0;
+  // GV/GpuVoxelsMap.h:117: no map of the path implements it (each logs "not supported" and returns false)
+  virtual bool insertRobotConfiguration(const MetaPointCloud* robot_links, bool with_self_collision_test) = 0;
   virtual void insertMetaPointCloud(const MetaPointCloud& meta_point_cloud, BitVoxelMeaning voxel_meaning) = 0;
   virtual void insertMetaPointCloud(const MetaPointCloud& meta_point_cloud,
                                     const std::vector<BitVoxelMeaning>& voxel_meanings) = 0;
@@ -58,8 +60,24 @@ public:
                      const BitVoxelMeaning* new_meaning = NULL) = 0;
   virtual bool merge(const GpuVoxelsMapSharedPtr other, const Vector3f& metric_offset,
                      const BitVoxelMeaning* new_meaning = NULL) = 0;
+  // the reference's binary dumps (GV/GpuVoxelsMap.h:206-216)
+  virtual bool writeToDisk(const std::string path) = 0;
+  virtual bool readFromDisk(const std::string path) = 0;
+  void generateVisualizerData() {}  // GV/GpuVoxelsMap.cpp:50-52: empty there too; the visualizer is out of scope
   virtual void clearMap() = 0;
   virtual void clearBitVoxelMeaning(BitVoxelMeaning voxel_meaning) = 0;
+  // GV/GpuVoxelsMap.h:229-247, .cpp:54-63: only octrees fragment; dense maps and lists answer "not supported" / false
+  virtual bool needsRebuild() const = 0;
+  virtual bool rebuild() = 0;
+  virtual bool rebuildIfNeeded()
+  {
+    if (needsRebuild())
+    {
+      rebuild();
+      return true;
+    }
+    return false;
+  }
   virtual std::size_t getMemoryUsage() const = 0;
   virtual Vector3ui getDimensions() const = 0;
   virtual Vector3f getMetricDimensions() const = 0;

@@ -5,6 +5,7 @@
 
 #include <climits>
 #include <cmath>
+#include <iostream>
 
 #include <gpu_voxels/GpuVoxelsMap.h>
 #include <gpu_voxels/voxelmap/VoxelMap.h>
@@ -53,6 +54,78 @@ public:
       return;
     }
     insertMeta(meta_point_cloud, voxel_meanings);
+  }
+  // TemplateVoxelList::insertPointCloud(const Vector3f* points_d, uint32_t size, ...) (GV/voxellist/TemplateVoxelList.hpp:311-340)
+  virtual void insertPointCloud(const Vector3f* points_d, uint32_t size, const BitVoxelMeaning voxel_meaning)
+  {
+    lock_guard guard(this->m_mutex);
+    if (!size) return;
+    gvxCheck(gvx_list_insert_points(m_handle, reinterpret_cast<const float*>(points_d), size, GVX_MEM_DEVICE,
+                                    int(voxel_meaning)), "insertPointCloud");
+  }
+  // GV/voxellist/BitVoxelList.hpp:57-62, AbstractVoxelList.cu:26-36
+  virtual bool insertRobotConfiguration(const MetaPointCloud*, bool)
+  {
+    LOGGING_ERROR_C(VoxellistLog, BitVoxelList, GPU_VOXELS_MAP_OPERATION_NOT_YET_SUPPORTED << endl);
+    return false;
+  }
+  virtual bool needsRebuild() const
+  {
+    LOGGING_ERROR_C(VoxellistLog, AbstractVoxelList, GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+    return false;
+  }
+  virtual bool rebuild()
+  {
+    LOGGING_ERROR_C(VoxellistLog, AbstractVoxelList, GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+    return false;
+  }
+  virtual MapType getTemplateType() { return this->m_map_type; }
+  // the three device arrays of the list (GV/voxellist/TemplateVoxelList.h:95-116); they move when the list grows
+  BitVoxel<length>* getDeviceDataPtr() { void* p = NULL; gvx_list_device_ptrs(m_handle, NULL, NULL, &p, NULL); return static_cast<BitVoxel<length>*>(p); }
+  uint32_t* getDeviceIdPtr() { void* p = NULL; gvx_list_device_ptrs(m_handle, &p, NULL, NULL, NULL); return static_cast<uint32_t*>(p); }
+  Vector3ui* getDeviceCoordPtr() { void* p = NULL; gvx_list_device_ptrs(m_handle, NULL, &p, NULL, NULL); return static_cast<Vector3ui*>(p); }
+  virtual void* getVoidDeviceDataPtr() { return getDeviceDataPtr(); }
+  // entries are unique and sorted after every insert / merge here, and storage is sized exactly: nothing to do
+  void make_unique() {}
+  virtual void shrinkToFit() {}
+  // TemplateVoxelList::screendump (GV/voxellist/TemplateVoxelList.hpp:776-802)
+  virtual void screendump(bool with_voxel_content = true)
+  {
+    LOGGING_INFO_C(VoxellistLog, TemplateVoxelList, "Dumping VoxelList with " << getDimensions().x << " entries to screen: " << endl);
+    lock_guard guard(this->m_mutex);
+    std::vector<uint32_t> ids; std::vector<Vector3ui> coords; std::vector<BitVectorVoxel> voxels;
+    copyToHost(ids, coords, voxels);
+    for (std::size_t i = 0; i < ids.size(); ++i)
+    {
+      std::cout << "[" << i << "] ID = " << ids[i] << " Coords: " << coords[i];
+      if (with_voxel_content) std::cout << "Voxel: " << voxels[i];
+      std::cout << std::endl;
+    }
+    LOGGING_INFO_C(VoxellistLog, TemplateVoxelList, "Dumped " << ids.size() << " Voxels." << endl);
+  }
+  // TemplateVoxelList::collisionCheckWithCollider (GV/voxellist/TemplateVoxelList.hpp:690-774) with the default
+  // collider: what collideWith forwards to. A collider with two different thresholds is refused (see VoxelMap.h)
+  size_t collisionCheckWithCollider(const voxelmap::AbstractVoxelMap* other, DefaultCollider collider = DefaultCollider(),
+                                    const Vector3i& offset = Vector3i())
+  {
+    float thr = 0.f;
+    if (!collider.asFloatThreshold(&thr))
+    {
+      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, "DefaultCollider with two different thresholds: " << GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+      return 0;
+    }
+    return collide(0, other, thr, offset, NULL, NULL);
+  }
+  size_t collisionCheckWithCollider(const BitVoxelList<length>* other, DefaultCollider collider = DefaultCollider(),
+                                    const Vector3i& offset = Vector3i())
+  {
+    float thr = 0.f;
+    if (!collider.asFloatThreshold(&thr))
+    {
+      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, "DefaultCollider with two different thresholds: " << GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+      return 0;
+    }
+    return collideWith(other, thr, offset);
   }
   virtual void clearMap()
   {

@@ -7,6 +7,7 @@
 #define GPU_VOXELS_B200_VOXELMAP_VOXELMAP_H
 
 #include <climits>
+#include <iostream>
 
 #include <gpu_voxels/GpuVoxelsMap.h>
 #include <gpu_voxels/voxel/DefaultCollider.h>
@@ -86,6 +87,24 @@ public:
   void* getVoidDeviceDataPtr() { void* p = NULL; gvx_map_device_ptr(m_handle, &p, NULL, NULL); return p; }
   const void* getConstVoidDeviceDataPtr() const { void* p = NULL; gvx_map_device_ptr(m_handle, &p, NULL, NULL); return p; }
   virtual gvx_handle_t getHandle() const { return m_handle; }
+
+  // GV/voxelmap/AbstractVoxelMap.h:60-66, .cu:23-33; BitVoxelMap.hpp:220-226, ProbVoxelMap.hpp:104-108
+  virtual MapType getTemplateType() const = 0;
+  virtual bool needsRebuild() const
+  {
+    LOGGING_ERROR_C(VoxelmapLog, AbstractVoxelMap, GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+    return false;
+  }
+  virtual bool rebuild()
+  {
+    LOGGING_ERROR_C(VoxelmapLog, AbstractVoxelMap, GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+    return false;
+  }
+  virtual bool insertRobotConfiguration(const MetaPointCloud*, bool)
+  {
+    LOGGING_ERROR_C(VoxelmapLog, TemplateVoxelMap, GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+    return false;
+  }
 
   // the reference's binary file format (GV/voxelmap/TemplateVoxelMap.hpp:666-799)
   virtual bool writeToDisk(const std::string path)
@@ -209,6 +228,17 @@ public:
   ProbabilisticVoxel* getDeviceDataPtr() { return static_cast<ProbabilisticVoxel*>(getVoidDeviceDataPtr()); }
   const ProbabilisticVoxel* getConstDeviceDataPtr() const { return static_cast<const ProbabilisticVoxel*>(getConstVoidDeviceDataPtr()); }
 
+  virtual MapType getTemplateType() const { return MT_PROBAB_VOXELMAP; }
+  // TemplateVoxelMap::printVoxelMapData (GV/voxelmap/TemplateVoxelMap.hpp:281-286): every voxel, one per line
+  virtual void printVoxelMapData()
+  {
+    lock_guard guard(this->m_mutex);
+    std::vector<int8_t> host(getVoxelMapSize());
+    if (host.empty() || !gvxCheck(gvx_map_download(m_handle, &host[0]), "printVoxelMapData")) return;
+    std::cout << "VoxelMap dump: " << std::endl;
+    for (std::size_t i = 0; i < host.size(); ++i) std::cout << i << ": " << int(host[i]) << std::endl;
+  }
+
   // ProbVoxelMap only knows eBVM_OCCUPIED; anything else is a logged no-op (GV/voxelmap/ProbVoxelMap.hpp:110-116)
   virtual void clearBitVoxelMeaning(BitVoxelMeaning voxel_meaning)
   {
@@ -283,6 +313,16 @@ public:
     : AbstractVoxelMap(dim, voxel_side_length, map_type, NULL) {}
   BitVoxelMap(BitVoxel<length>* dev_data, const Vector3ui dim, const float voxel_side_length, const MapType map_type = MT_BITVECTOR_VOXELMAP)
     : AbstractVoxelMap(dim, voxel_side_length, map_type, dev_data) {}
+
+  virtual MapType getTemplateType() const { return MT_BITVECTOR_VOXELMAP; }
+  virtual void printVoxelMapData()
+  {
+    lock_guard guard(this->m_mutex);
+    std::vector<BitVoxel<length> > host(getVoxelMapSize());
+    if (host.empty() || !gvxCheck(gvx_map_download(m_handle, &host[0]), "printVoxelMapData")) return;
+    std::cout << "VoxelMap dump: " << std::endl;
+    for (std::size_t i = 0; i < host.size(); ++i) std::cout << i << ": " << host[i] << std::endl;
+  }
 
   // GV/voxelmap/BitVoxelMap.hpp:57-81, 228-232
   virtual void clearBitVoxelMeaning(BitVoxelMeaning voxel_meaning) { clearBit(uint32_t(voxel_meaning)); }

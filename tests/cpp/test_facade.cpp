@@ -524,6 +524,80 @@ BOOST_AUTO_TEST_CASE(voxelmap_disk_io)
   BOOST_CHECK(m1.collideWith(&m2, 0.5) == 9 * 9 * 9);
 }
 
+// the GpuVoxelsMap base interface as callers use it through GpuVoxelsMapSharedPtr (GV/GpuVoxelsMap.h:112-260), and the
+// raw-storage / collider entry points of the list (GV/voxellist/TemplateVoxelList.h:95-116, .hpp:690-774)
+BOOST_AUTO_TEST_CASE(base_class_interface)
+{
+  GpuVoxelsMapSharedPtr maps[3] = {
+    GpuVoxelsMapSharedPtr(new ProbVoxelMap(Vector3ui(dimX, dimY, dimZ), 1.f, MT_PROBAB_VOXELMAP)),
+    GpuVoxelsMapSharedPtr(new BitVectorVoxelMap(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELMAP)),
+    GpuVoxelsMapSharedPtr(new BitVectorVoxelList(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELLIST))};
+  MetaPointCloud boxes = voxellists::twoBoxes();
+  for (int k = 0; k < 3; ++k)
+  {
+    BOOST_CHECK(!maps[k]->needsRebuild());
+    BOOST_CHECK(!maps[k]->rebuild());
+    BOOST_CHECK(!maps[k]->rebuildIfNeeded());
+    BOOST_CHECK(!maps[k]->insertRobotConfiguration(&boxes, false));
+    maps[k]->generateVisualizerData();
+  }
+  BOOST_CHECK(maps[0]->as<ProbVoxelMap>()->getTemplateType() == MT_PROBAB_VOXELMAP);
+  BOOST_CHECK(maps[1]->as<BitVectorVoxelMap>()->getTemplateType() == MT_BITVECTOR_VOXELMAP);
+  BOOST_CHECK(maps[2]->as<BitVectorVoxelList>()->getTemplateType() == MT_BITVECTOR_VOXELLIST);
+
+  // disk I/O through the base pointer
+  maps[0]->insertMetaPointCloud(boxes, eBVM_OCCUPIED);
+  maps[2]->insertMetaPointCloud(boxes, voxellists::meanings1112());
+  BOOST_CHECK(maps[0]->writeToDisk("/tmp/gvx_temp_base_map.bin"));
+  BOOST_CHECK(maps[2]->writeToDisk("/tmp/gvx_temp_base_list.bin"));
+  GpuVoxelsMapSharedPtr map_copy(new ProbVoxelMap(Vector3ui(dimX, dimY, dimZ), 1.f, MT_PROBAB_VOXELMAP));
+  GpuVoxelsMapSharedPtr list_copy(new BitVectorVoxelList(Vector3ui(dimX, dimY, dimZ), 1.f, MT_BITVECTOR_VOXELLIST));
+  BOOST_CHECK(map_copy->readFromDisk("/tmp/gvx_temp_base_map.bin"));
+  BOOST_CHECK(list_copy->readFromDisk("/tmp/gvx_temp_base_list.bin"));
+  BitVectorVoxelList* list = maps[2]->as<BitVectorVoxelList>();
+  BOOST_CHECK(list->equals(*list_copy->as<BitVectorVoxelList>()));
+
+  // collider-object entry points of the list == collideWith (46 collisions, GV/test/testing_voxellist.cu:142)
+  BOOST_CHECK(list->collisionCheckWithCollider(map_copy->as<ProbVoxelMap>(), DefaultCollider(1.0f)) == 46);
+  BOOST_CHECK(list->collisionCheckWithCollider(map_copy->as<ProbVoxelMap>(), DefaultCollider(Probability(1), Probability(2))) == 0);  // refused
+  BOOST_CHECK(list->collisionCheckWithCollider(list_copy->as<BitVectorVoxelList>()) == list->collideWith(list_copy->as<BitVectorVoxelList>()));
+
+  // raw storage: three device arrays of size() entries; make_unique / shrinkToFit leave a list as it is
+  const size_t n = list->size();
+  BOOST_CHECK(n > 0 && list->getDeviceIdPtr() != NULL && list->getDeviceCoordPtr() != NULL && list->getDeviceDataPtr() != NULL);
+  BOOST_CHECK(list->getVoidDeviceDataPtr() == (void*)list->getDeviceDataPtr());
+  std::vector<Vector3ui> coords_before, coords_after;
+  list->copyCoordsToHost(coords_before);
+  list->make_unique();
+  list->shrinkToFit();
+  list->copyCoordsToHost(coords_after);
+  BOOST_CHECK(list->size() == n && coords_before.size() == n && coords_after.size() == n);
+  bool same = coords_before.size() == coords_after.size();
+  for (size_t i = 0; same && i < n; ++i) same = coords_before[i] == coords_after[i];
+  BOOST_CHECK(same);  // (the voxels now carry eBVM_COLLISION marks from the checks above, so no equals() here)
+  // device-pointer insert overload: the coordinates of the first box again, nothing new
+  PointCloud pc(createBoxOfPoints(Vector3f(2.1, 2.1, 2.1), Vector3f(4.1, 4.1, 4.1), 0.5));
+  list->insertPointCloud(pc.getConstDevicePointer(), pc.getPointCloudSize(), BitVoxelMeaning(11));
+  BOOST_CHECK(list->size() >= n);
+
+  // dumps print one line per entry / voxel
+  BitVectorVoxelList tiny(Vector3ui(4, 4, 4), 1.f, MT_BITVECTOR_VOXELLIST);
+  std::vector<Vector3f> two;
+  two.push_back(Vector3f(1.5f, 1.5f, 1.5f));
+  two.push_back(Vector3f(2.5f, 1.5f, 1.5f));
+  tiny.insertPointCloud(two, BitVoxelMeaning(7));
+  std::stringstream captured;
+  std::streambuf* old = std::cout.rdbuf(captured.rdbuf());
+  tiny.screendump(true);
+  ProbVoxelMap tiny_map(Vector3ui(2, 2, 2), 1.f, MT_PROBAB_VOXELMAP);
+  tiny_map.printVoxelMapData();
+  std::cout.rdbuf(old);
+  const std::string text = captured.str();
+  BOOST_CHECK(text.find("[0] ID = 21 Coords: ") != std::string::npos);
+  BOOST_CHECK(text.find("[1] ID = 22 Coords: ") != std::string::npos);
+  BOOST_CHECK(text.find("VoxelMap dump: ") != std::string::npos && text.find("7: -128") != std::string::npos);
+}
+
 // PointcloudFileHandler / insertPointCloudFromFile / PointCloud(file) / MetaPointCloud(files)
 // (GV/helpers/PointcloudFileHandler.cpp:64-137, GV/GpuVoxelsMap.cpp:36-49, GV/helpers/PointCloud.cu:84-105,
 // GV/helpers/MetaPointCloud.cu:115-151); files of tests/golden/files, point counts as the reference's readers give them
