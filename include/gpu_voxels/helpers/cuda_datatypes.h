@@ -25,6 +25,8 @@ struct Vec3T
   Vec3T operator/(T s) const { return Vec3T(x / s, y / s, z / s); }
   Vec3T& operator+=(const Vec3T& o) { x += o.x; y += o.y; z += o.z; return *this; }
   Vec3T& operator-=(const Vec3T& o) { x -= o.x; y -= o.y; z -= o.z; return *this; }
+  // GV/helpers/cuda_vectors.h:268-272
+  float length() const { return std::sqrt(float((x * x) + (y * y) + (z * z))); }
   bool operator==(const Vec3T& o) const { return x == o.x && y == o.y && z == o.z; }
   bool operator!=(const Vec3T& o) const { return !(*this == o); }
 };
@@ -45,13 +47,45 @@ struct Matrix3f
   Matrix3f(float b11, float b12, float b13, float b21, float b22, float b23, float b31, float b32, float b33)
     : a11(b11), a12(b12), a13(b13), a21(b21), a22(b22), a23(b23), a31(b31), a32(b32), a33(b33) {}
   static Matrix3f createIdentity() { return Matrix3f(1, 0, 0, 0, 1, 0, 0, 0, 1); }
+  // single-axis rotations and their products exactly as the reference's host code builds them
+  // (GV/helpers/cuda_matrices.h:185-277): float sin / cos of the float angle, every entry of a product is
+  // (x_i1*y_1j + x_i2*y_2j) + x_i3*y_3j in fp32 without contraction -- pinned by tests/golden/geometry.npz
+  static Matrix3f createFromRoll(float angle)
+  {
+    return Matrix3f(1, 0, 0, 0, cosf(angle), -sinf(angle), 0, sinf(angle), cosf(angle));
+  }
+  static Matrix3f createFromPitch(float angle)
+  {
+    return Matrix3f(cosf(angle), 0, sinf(angle), 0, 1, 0, -sinf(angle), 0, cosf(angle));
+  }
+  static Matrix3f createFromYaw(float angle)
+  {
+    return Matrix3f(cosf(angle), -sinf(angle), 0, sinf(angle), cosf(angle), 0, 0, 0, 1);
+  }
+  Matrix3f operator*(const Matrix3f& rhs) const
+  {
+    const float* x = &a11;
+    const float* y = &rhs.a11;
+    Matrix3f r;
+    float* o = &r.a11;
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j)
+      {
+        volatile float p0 = x[3 * i] * y[j], p1 = x[3 * i + 1] * y[3 + j], p2 = x[3 * i + 2] * y[6 + j];
+        volatile float sum = p0 + p1;
+        sum = sum + p2;
+        o[3 * i + j] = sum;
+      }
+    return r;
+  }
   // rotation about x by roll, then y by pitch, then z by yaw: R = Rz(yaw) * Ry(pitch) * Rx(roll)
   static Matrix3f createFromRPY(float roll, float pitch, float yaw)
   {
-    const float sr = sinf(roll), cr = cosf(roll), sp = sinf(pitch), cp = cosf(pitch), sy = sinf(yaw), cy = cosf(yaw);
-    return Matrix3f(cy * cp, cy * sp * sr - sy * cr, cy * sp * cr + sy * sr,
-                    sy * cp, sy * sp * sr + cy * cr, sy * sp * cr - cy * sr,
-                    -sp, cp * sr, cp * cr);
+    return createFromYaw(yaw) * createFromPitch(pitch) * createFromRoll(roll);
+  }
+  static Matrix3f createFromYPR(float roll, float pitch, float yaw)
+  {
+    return createFromRoll(roll) * createFromPitch(pitch) * createFromYaw(yaw);
   }
   static Matrix3f createFromRPY(const Vector3f& rpy) { return createFromRPY(rpy.x, rpy.y, rpy.z); }
 };
@@ -100,6 +134,14 @@ inline Matrix4f operator*(const Matrix4f& x, const Matrix4f& y)
     }
   return r;
 }
+
+// box given by centre, HALF side lengths and roll / pitch / yaw (GV/helpers/cuda_datatypes.h:92-97)
+struct OrientedBoxParams
+{
+  Vector3f dim;
+  Vector3f center;
+  Vector3f rot;
+};
 
 // depth sensor description (GV/helpers/cuda_datatypes.h:45-69)
 struct Sensor

@@ -5,12 +5,14 @@
 //   host_helpers load <n>...            -> "<blocks> <threads>"
 //   host_helpers lerpf <a> <b> <r> ...  (uint32 bit patterns)  -> "<bits>"
 //   host_helpers lerpd <a> <b> <r> ...  (uint64 bit patterns)  -> "<bits>"
+//   host_helpers geom <kind> <bits>...  -> binary: rotation matrices / generated clouds (tests/golden/geometry.npz)
 //   host_helpers prob                   -> 256 lines of updateOccupancy results, one line of insert results, "ok"
 #include <cinttypes>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
+#include <gpu_voxels/helpers/GeometryGeneration.h>
 #include <gpu_voxels/helpers/MathHelpers.h>
 #include <gpu_voxels/voxel/BitVoxel.h>
 #include <gpu_voxels/voxel/DefaultCollider.h>
@@ -154,6 +156,56 @@ int main(int argc, char** argv)
     std::vector<double> da(1, 0.25), db(1, 0.75);
     ok = ok && gpu_voxels::interpolateLinear(da, db, 0.5)[0] == 0.5;
     std::printf("%s\n", ok ? "ok" : "MISMATCH");
+  }
+  else if (mode == "geom")
+  {  // geom <kind> <float bit patterns...>: binary to stdout (uint64 counts, raw float32), see tests/test_host_helpers.py
+    using namespace gpu_voxels;
+    using namespace gpu_voxels::geometry_generation;
+    if (argc < 3) return 2;
+    const std::string kind = argv[2];
+    std::vector<float> f;
+    for (int i = 3; i < argc; ++i) f.push_back(bits_to<float>(uint32_t(std::strtoul(argv[i], NULL, 10))));
+    struct Out
+    {
+      static void cloud(const std::vector<Vector3f>& c)
+      {
+        const uint64_t n = c.size();
+        std::fwrite(&n, 8, 1, stdout);
+        if (n) std::fwrite(&c[0], 12, n, stdout);
+      }
+    };
+    if (kind == "rpy")
+      for (size_t i = 0; i + 2 < f.size(); i += 3)
+      {
+        const Matrix3f m = Matrix3f::createFromRPY(Vector3f(f[i], f[i + 1], f[i + 2]));
+        std::fwrite(&m, 36, 1, stdout);
+      }
+    else if (kind == "box" && f.size() == 7)
+      Out::cloud(createBoxOfPoints(Vector3f(f[0], f[1], f[2]), Vector3f(f[3], f[4], f[5]), f[6]));
+    else if (kind == "sphere" && f.size() == 5)
+      Out::cloud(createSphereOfPoints(Vector3f(f[0], f[1], f[2]), f[3], f[4]));
+    else if (kind == "cylinder" && f.size() == 6)
+      Out::cloud(createCylinderOfPoints(Vector3f(f[0], f[1], f[2]), f[3], f[4], f[5]));
+    else if (kind == "obox" && f.size() == 11)
+    {
+      OrientedBoxParams p;
+      p.dim = Vector3f(f[0], f[1], f[2]); p.center = Vector3f(f[3], f[4], f[5]); p.rot = Vector3f(f[6], f[7], f[8]);
+      const Matrix4f m = detail::orientedBoxTransform(p);
+      std::fwrite(&m, 64, 1, stdout);
+      Out::cloud(f[10] != 0.f ? detail::orientedBoxEdgesCloud(p, f[9]) : detail::orientedBoxCloud(p, f[9]));
+    }
+    else if (kind == "eq" && argc == 8)
+    {  // geom eq <max points> <dx> <dy> <dz> <side bits>: equidistant points, then the two checkerboard clouds
+      const size_t max_n = size_t(std::strtoull(argv[3], NULL, 10));
+      const Vector3ui dims(uint32_t(std::strtoul(argv[4], NULL, 10)), uint32_t(std::strtoul(argv[5], NULL, 10)),
+                           uint32_t(std::strtoul(argv[6], NULL, 10)));
+      const float side = bits_to<float>(uint32_t(std::strtoul(argv[7], NULL, 10)));
+      std::vector<Vector3f> pts, black, white;
+      createEquidistantPointsInBox(max_n, dims, side, pts);
+      createNonOverlapping3dCheckerboard(max_n, dims, side, black, white);
+      Out::cloud(pts); Out::cloud(black); Out::cloud(white);
+    }
+    else return 2;
   }
   else return 2;
   return 0;

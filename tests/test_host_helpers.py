@@ -105,3 +105,88 @@ def test_default_collider_thresholds_equal_reference():
     inside = (g["thr"] >= 0) & (g["thr"] <= 1)
     assert got[inside, 1].all()
     assert "MISMATCH" not in lines and "ok" in lines
+
+
+# ---- synthetic geometry and rotation matrices (GV/helpers/GeometryGeneration.cpp, cuda_matrices.h) ------------------
+def _geom(kind, args):
+    r = subprocess.run([_exe(), "geom", kind] + [str(int(a)) for a in args], capture_output=True, check=True)
+    return r.stdout
+
+
+def _clouds(buf, k):
+    out, pos = [], 0
+    for _ in range(k):
+        n = int(np.frombuffer(buf, np.uint64, 1, pos)[0])
+        out.append(np.frombuffer(buf, np.float32, 3 * n, pos + 8).reshape(n, 3))
+        pos += 8 + 12 * n
+    assert pos == len(buf)
+    return out
+
+
+def _split(g, name):
+    sizes = g[name + "_sizes"]
+    ends = np.cumsum(sizes)
+    return [g[name + "_points"][e - s:e] for s, e in zip(sizes, ends)]
+
+
+def _same_bits(a, b):
+    return a.shape == b.shape and np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+
+
+def _geometry_golden():
+    for h in ("GeometryGeneration.h", "cuda_datatypes.h"):
+        hdr = os.path.join(ROOT, "include", "gpu_voxels", "helpers", h)
+        if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
+            os.remove(EXE)
+    return np.load(os.path.join(ROOT, "tests", "golden", "geometry.npz"))
+
+
+def test_rotation_matrices_equal_reference():
+    """Matrix3f::createFromRPY of the facade == the reference's product of single-axis rotations, bit for bit, for 747
+    angle triples (special angles, tiny angles, random)"""
+    g = _geometry_golden()
+    rpy = g["rpy"]
+    got = []
+    for i in range(0, len(rpy), 150):
+        got.append(np.frombuffer(_geom("rpy", rpy[i:i + 150].view(np.uint32).reshape(-1)), np.float32).reshape(-1, 9))
+    got = np.concatenate(got)
+    assert _same_bits(got, g["rpy_m9"])
+    # they are rotations
+    m = got.reshape(-1, 3, 3).astype(np.float64)
+    assert np.allclose(m @ m.transpose(0, 2, 1), np.eye(3), atol=1e-6)
+
+
+def test_point_generators_equal_reference():
+    """createBoxOfPoints / createSphereOfPoints / createCylinderOfPoints: same points in the same order as the reference's
+    translation unit (the loops accumulate `x += delta` in float, so the point SET depends on the rounding)"""
+    g = _geometry_golden()
+    for kind in ("box", "sphere", "cylinder"):
+        want = _split(g, kind)
+        assert sum(len(w) for w in want) > 30000
+        for p, w in zip(g[kind + "_params"], want):
+            got, = _clouds(_geom(kind, p.view(np.uint32)), 1)
+            assert _same_bits(got, w), (kind, p)
+
+
+def test_oriented_boxes_equal_reference():
+    """createOrientedBox / createOrientedBoxEdges: the cloud handed to PointCloud::update and the Matrix4f handed to
+    transformSelf (roll / pitch / yaw + centre) equal the reference's; the transform itself is the device kernel"""
+    g = _geometry_golden()
+    want = _split(g, "obox")
+    for p, w, m in zip(g["obox_params"], want, g["obox_matrix"]):
+        buf = _geom("obox", p.view(np.uint32))
+        assert _same_bits(np.frombuffer(buf, np.float32, 16), m), p
+        got, = _clouds(buf[64:], 1)
+        assert _same_bits(got, w), p
+    assert {int(p[10]) for p in g["obox_params"]} == {0, 1}
+
+
+def test_equidistant_points_and_checkerboards_equal_reference():
+    g = _geometry_golden()
+    eq, black, white = _split(g, "eq"), _split(g, "cb_black"), _split(g, "cb_white")
+    for i, (p, s) in enumerate(zip(g["eq_params"], g["eq_side"])):
+        r = subprocess.run([_exe(), "geom", "eq"] + [str(int(v)) for v in p] + [str(int(np.float32(s).view(np.uint32)))],
+                           capture_output=True, check=True)
+        got = _clouds(r.stdout, 3)
+        assert _same_bits(got[0], eq[i]) and _same_bits(got[1], black[i]) and _same_bits(got[2], white[i]), p
+    assert len(eq[0]) == 10000  # the reference fixture: 10000 points in the 89 x 123 x 74 map
