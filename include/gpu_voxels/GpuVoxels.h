@@ -14,6 +14,7 @@
 #include <string>
 #include <vector>
 
+#include <gpu_voxels/helpers/MathHelpers.h>
 #include <gpu_voxels/GpuVoxelsMap.h>
 #include <gpu_voxels/helpers/GeometryGeneration.h>
 #include <gpu_voxels/robot/dh_robot/KinematicChain.h>
@@ -105,6 +106,16 @@ public:
   {
     ManagedMapsIterator it = findMap(map_name);
     return it == m_managed_maps.end() ? GpuVoxelsMapSharedPtr() : it->second.map_shared_ptr;
+  }
+
+  // GV/GpuVoxels.cpp:561-570. The visualizer (a separate OpenGL process fed through shared memory) is out of scope
+  // and unavailable on a headless box: the call keeps the reference's contract for the map name (false + error for an
+  // unknown map) and is otherwise a successful no-op, so sensor / planner loops written for the reference
+  // compile and run unchanged (there, too, the call succeeds whether or not a visualizer process is listening).
+  bool visualizeMap(const std::string& map_name, const bool force_repaint = true)
+  {
+    (void)force_repaint;
+    return findMap(map_name) != m_managed_maps.end();
   }
 
   bool clearMap(const std::string& map_name)

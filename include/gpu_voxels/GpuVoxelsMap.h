@@ -9,6 +9,7 @@
 #include <string>
 #include <vector>
 
+#include <gpu_voxels/helpers/BoostCompat.h>
 #include <gpu_voxels/helpers/GvxCall.h>
 #include <gpu_voxels/helpers/MetaPointCloud.h>
 #include <gpu_voxels/helpers/PointCloud.h>

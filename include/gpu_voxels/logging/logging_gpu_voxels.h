@@ -16,7 +16,11 @@ static const char endl = '\n';
 }  // namespace gpu_voxels
 
 namespace icl_core { namespace logging {
-inline void initialize(int&, char**) {}
+// the command line, kept for the option stand-in of include/icl_core_config/Config.h (icl_core parses its registered
+// options inside logging::initialize)
+struct CommandLine { int argc; char** argv; CommandLine() : argc(0), argv(0) {} };
+inline CommandLine& commandLine() { static CommandLine c; return c; }
+inline void initialize(int& argc, char** argv) { commandLine().argc = argc; commandLine().argv = argv; }
 inline void initialize() {}
 inline void shutdown() {}
 }}  // namespace icl_core::logging
