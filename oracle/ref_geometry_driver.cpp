@@ -15,6 +15,7 @@
 #include <cstdint>
 #include <cstring>
 #include <map>
+#include <sstream>
 #include <string>
 #include <vector>
 #include <gpu_voxels/helpers/GeometryGeneration.cpp>
@@ -91,6 +92,65 @@ void gvrefgeo_rot_trans(const float* m9, const float* t3, float* m16) {
   std::memcpy((void*)&r, m9, 36);
   const Matrix4f m = Matrix4f::createFromRotationAndTranslation(r, v3(t3));
   std::memcpy(m16, &m, 64);
+}
+
+// ---- value API of the vector / matrix types (GV/helpers/cuda_vectors.h:247-331, cuda_matrices.h:285-660) ----------
+static Matrix3f m3(const float* p) { Matrix3f m; std::memcpy((void*)&m, p, 36); return m; }
+static Matrix4f m4(const float* p) { Matrix4f m; std::memcpy((void*)&m, p, 64); return m; }
+static void put3(const Vector3f& v, float* o) { o[0] = v.x; o[1] = v.y; o[2] = v.z; }
+
+void gvrefgeo_to_rpy(const float* m9, unsigned solution, float* out3) { put3(m3(m9).toRPY(solution), out3); }
+void gvrefgeo_orientation_diff(const float* a9, const float* b9, float* out3) { put3(m3(a9).orientationMatrixDiff(m3(b9)), out3); }
+int gvrefgeo_inverse3(const float* m9, float* out9) {
+  Matrix3f inv;
+  const bool ok = m3(m9).invertMatrix(inv);
+  std::memcpy(out9, &inv, 36);
+  return ok ? 1 : 0;
+}
+int gvrefgeo_inverse4(const float* m16, float* out16) {
+  Matrix4f inv;
+  const bool ok = m4(m16).invertMatrix(inv);
+  std::memcpy(out16, &inv, 64);
+  return ok ? 1 : 0;
+}
+// out: length, dot, angleBetween, cross[3], a.normalized[3], a.abs[3], a normalised in place [3], M4*a [3], M3*a [3],
+// then flags as floats: compVec(a,b), apprx_equal(a,b,eps)
+void gvrefgeo_vector_ops(const float* a3, const float* b3, const float* m16, double eps, float* out20) {
+  Vector3f a = v3(a3), b = v3(b3);
+  out20[0] = a.length();
+  out20[1] = a.dot(b);
+  out20[2] = a.angleBetween(b);
+  put3(a.cross(b), out20 + 3);
+  put3(a.normalized(), out20 + 6);
+  put3(a.abs(), out20 + 9);
+  Vector3f n = a;
+  n.normalize();
+  put3(n, out20 + 12);
+  put3(m4(m16) * a, out20 + 15);
+  out20[18] = Vector3f::compVec(a, b) ? 1.f : 0.f;
+  out20[19] = a.apprx_equal(b, eps) ? 1.f : 0.f;
+}
+void gvrefgeo_matrix_ops(const float* a16, const float* b16, double eps, float* transpose16, float* minus16, float* prod16,
+                         float* rot_apply3, const float* v, int* approx) {
+  const Matrix4f a = m4(a16), b = m4(b16);
+  const Matrix4f t = a.transpose(), d = a - b, pr = a * b;
+  std::memcpy(transpose16, &t, 64);
+  std::memcpy(minus16, &d, 64);
+  std::memcpy(prod16, &pr, 64);
+  put3(a.getRotation() * v3(v), rot_apply3);
+  *approx = a.apprx_equal(b, eps) ? 1 : 0;
+}
+// operator<< of Vector3f / Matrix3f / Matrix4f into buf (NUL-terminated); returns the length
+int gvrefgeo_format(int what, const float* p, char* buf, int cap) {
+  std::stringstream ss;
+  if (what == 0) ss << v3(p);
+  else if (what == 1) ss << m3(p);
+  else ss << m4(p);
+  const std::string s = ss.str();
+  const int n = (int)s.size() < cap - 1 ? (int)s.size() : cap - 1;
+  std::memcpy(buf, s.data(), n);
+  buf[n] = 0;
+  return n;
 }
 
 }  // extern "C"

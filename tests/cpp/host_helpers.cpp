@@ -11,6 +11,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <sstream>
+#include <vector>
 
 #include <gpu_voxels/helpers/GeometryGeneration.h>
 #include <gpu_voxels/helpers/MathHelpers.h>
@@ -190,9 +192,9 @@ int main(int argc, char** argv)
     {
       OrientedBoxParams p;
       p.dim = Vector3f(f[0], f[1], f[2]); p.center = Vector3f(f[3], f[4], f[5]); p.rot = Vector3f(f[6], f[7], f[8]);
-      const Matrix4f m = detail::orientedBoxTransform(p);
+      const Matrix4f m = geometry_generation::detail::orientedBoxTransform(p);
       std::fwrite(&m, 64, 1, stdout);
-      Out::cloud(f[10] != 0.f ? detail::orientedBoxEdgesCloud(p, f[9]) : detail::orientedBoxCloud(p, f[9]));
+      Out::cloud(f[10] != 0.f ? geometry_generation::detail::orientedBoxEdgesCloud(p, f[9]) : geometry_generation::detail::orientedBoxCloud(p, f[9]));
     }
     else if (kind == "eq" && argc == 8)
     {  // geom eq <max points> <dx> <dy> <dz> <side bits>: equidistant points, then the two checkerboard clouds
@@ -205,6 +207,95 @@ int main(int argc, char** argv)
       createNonOverlapping3dCheckerboard(max_n, dims, side, black, white);
       Out::cloud(pts); Out::cloud(black); Out::cloud(white);
     }
+    else return 2;
+  }
+  else if (mode == "mathfile")
+  {  // mathfile <kind> <path>: raw float32 records in, raw float32 results out (value API of Vector3f / Matrix3f /
+     // Matrix4f against tests/golden/geometry.npz; record layouts in tests/test_host_helpers.py)
+    using namespace gpu_voxels;
+    if (argc < 4) return 2;
+    const std::string kind = argv[2];
+    std::vector<float> in;
+    {
+      FILE* fp = std::fopen(argv[3], "rb");
+      if (!fp) return 3;
+      float buf[4096];
+      size_t n;
+      while ((n = std::fread(buf, 4, 4096, fp)) > 0) in.insert(in.end(), buf, buf + n);
+      std::fclose(fp);
+    }
+    struct IO
+    {
+      static Matrix3f m3(const float* p) { Matrix3f m; std::memcpy(static_cast<void*>(&m), p, 36); return m; }
+      static Matrix4f m4(const float* p) { Matrix4f m; std::memcpy(static_cast<void*>(&m), p, 64); return m; }
+      static void put(const Vector3f& v) { std::fwrite(&v, 12, 1, stdout); }
+      static void put(float v) { std::fwrite(&v, 4, 1, stdout); }
+    };
+    if (kind == "torpy")
+      for (size_t i = 0; i + 9 <= in.size(); i += 9)
+        for (unsigned sol = 0; sol < 3; ++sol) IO::put(IO::m3(&in[i]).toRPY(sol));
+    else if (kind == "diff")
+    {
+      const size_t n = in.size() / 9;
+      for (size_t i = 0; i < n; ++i) IO::put(IO::m3(&in[9 * i]).orientationMatrixDiff(IO::m3(&in[9 * ((i + 1) % n)])));
+    }
+    else if (kind == "inv3")
+      for (size_t i = 0; i + 9 <= in.size(); i += 9)
+      {
+        Matrix3f inv;
+        const bool ok = IO::m3(&in[i]).invertMatrix(inv);
+        if (!ok) inv = Matrix3f();
+        IO::put(ok ? 1.f : 0.f);
+        std::fwrite(&inv, 36, 1, stdout);
+      }
+    else if (kind == "inv4")
+      for (size_t i = 0; i + 16 <= in.size(); i += 16)
+      {
+        Matrix4f inv;
+        const bool ok = IO::m4(&in[i]).invertMatrix(inv);
+        if (!ok) inv = Matrix4f();
+        IO::put(ok ? 1.f : 0.f);
+        std::fwrite(&inv, 64, 1, stdout);
+      }
+    else if (kind == "vec")
+      for (size_t i = 0; i + 22 <= in.size(); i += 22)
+      {
+        const Vector3f a(in[i], in[i + 1], in[i + 2]), b(in[i + 3], in[i + 4], in[i + 5]);
+        IO::put(a.length()); IO::put(a.dot(b)); IO::put(a.angleBetween(b));
+        IO::put(a.cross(b)); IO::put(a.normalized()); IO::put(a.abs());
+        Vector3f n = a;
+        n.normalize();
+        IO::put(n);
+        IO::put(IO::m4(&in[i + 6]) * a);
+        IO::put(Vector3f::compVec(a, b) ? 1.f : 0.f);
+        IO::put(a.apprx_equal(b, 1e-3) ? 1.f : 0.f);
+      }
+    else if (kind == "mat")
+      for (size_t i = 0; i + 35 <= in.size(); i += 35)
+      {
+        const Matrix4f a = IO::m4(&in[i]), b = IO::m4(&in[i + 16]);
+        const Matrix4f t = a.transpose(), d = a - b, pr = a * b;
+        Matrix4f lm = a;
+        lm.leftMultiply(b);
+        std::fwrite(&t, 64, 1, stdout); std::fwrite(&d, 64, 1, stdout); std::fwrite(&pr, 64, 1, stdout);
+        IO::put(a.getRotation() * Vector3f(in[i + 32], in[i + 33], in[i + 34]));
+        IO::put(a.apprx_equal(b, 1e-3) ? 1.f : 0.f);
+        Matrix4f back = Matrix4f::createIdentity();
+        back.setRotation(a.getRotation());
+        back.setTranslation(a.getTranslation());
+        const bool affine = a.a41 == 0.f && a.a42 == 0.f && a.a43 == 0.f && a.a44 == 1.f;
+        IO::put(lm == pr && (!affine || back == a) ? 1.f : 0.f);
+      }
+    else if (kind == "fmt")
+      for (size_t i = 0; i + 17 <= in.size(); i += 17)
+      {
+        std::stringstream ss;
+        if (in[i] == 0.f) ss << Vector3f(in[i + 1], in[i + 2], in[i + 3]);
+        else if (in[i] == 1.f) ss << IO::m3(&in[i + 1]);
+        else ss << IO::m4(&in[i + 1]);
+        const std::string text = ss.str();
+        std::fwrite(text.c_str(), 1, text.size() + 1, stdout);
+      }
     else return 2;
   }
   else return 2;

@@ -117,6 +117,82 @@ def main():
     out["cb_black_sizes"], out["cb_black_points"] = pack(black)
     out["cb_white_sizes"], out["cb_white_points"] = pack(white)
 
+    # ---- value API of Vector3f / Matrix3f / Matrix4f (cuda_vectors.h, cuda_matrices.h) ----
+    L.gvrefgeo_to_rpy.argtypes = [C.c_void_p, C.c_uint, C.c_void_p]
+    L.gvrefgeo_orientation_diff.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.gvrefgeo_inverse3.argtypes = [C.c_void_p, C.c_void_p]
+    L.gvrefgeo_inverse4.argtypes = [C.c_void_p, C.c_void_p]
+    L.gvrefgeo_vector_ops.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_void_p]
+    L.gvrefgeo_matrix_ops.argtypes = [C.c_void_p, C.c_void_p, C.c_double] + [C.c_void_p] * 6
+    L.gvrefgeo_format.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+    ptr = lambda a: a.ctypes.data_as(C.c_void_p)
+    rot = np.ascontiguousarray(m9[::2][:330])          # rotations incl. the pitch singularities of the special angles
+    to_rpy = np.zeros((len(rot), 3, 3), np.float32)     # solution_number 0, 1, 2
+    diff = np.zeros((len(rot), 3), np.float32)
+    for i in range(len(rot)):
+        for sol in range(3):
+            L.gvrefgeo_to_rpy(ptr(rot[i]), sol, ptr(to_rpy[i, sol]))
+        L.gvrefgeo_orientation_diff(ptr(rot[i]), ptr(rot[(i + 1) % len(rot)]), ptr(diff[i]))
+    out["rot"], out["rot_to_rpy"], out["rot_diff"] = rot, to_rpy, diff
+
+    m3s = [rot[k] for k in range(0, 60)] + [rng.normal(0, 2, 9).astype(np.float32) for _ in range(60)]
+    m3s += [np.zeros(9, np.float32), np.array([1, 2, 3, 2, 4, 6, 1, 0, 1], np.float32),   # singular
+            np.array([0, 1, 0, 1, 0, 0, 0, 0, 1], np.float32), np.array([0, 0, 2, 0, 3, 0, 4, 0, 0], np.float32),  # zero pivots
+            np.array([1, 2, 3, 1, 2, 4, 5, 6, 7], np.float32)]                              # zero pivot in the second step
+    m3s = np.stack(m3s)
+    inv3, ok3 = np.zeros_like(m3s), np.zeros(len(m3s), np.int32)
+    for i in range(len(m3s)):
+        ok3[i] = L.gvrefgeo_inverse3(ptr(m3s[i]), ptr(inv3[i]))
+        if not ok3[i]:
+            inv3[i] = 0
+    out["inv3_in"], out["inv3_out"], out["inv3_ok"] = m3s, inv3, ok3
+
+    m4s = [mats[k] for k in range(len(mats))] + [rng.normal(0, 2, 16).astype(np.float32) for _ in range(80)]
+    m4s += [np.array([0.9751700, -0.218711, -0.0347626, 10, 0.1976770, 0.930432, -0.3085770, 11,
+                      0.0998334, 0.294044, 0.9505640, 12, 0, 0, 0, 1], np.float32),            # GV/test/testing_cudaMath.cu fixture
+            np.zeros(16, np.float32), np.array([0, 0, 0, 1, 0, 0, 1, 0, 0, 1, 0, 0, 1, 0, 0, 0], np.float32),
+            np.array([1, 2, 3, 4, 2, 4, 6, 8, 1, 0, 1, 0, 0, 1, 0, 1], np.float32),
+            np.array([1, 2, 3, 4, 1, 2, 4, 5, 0, 0, 0, 7, 3, 1, 2, 2], np.float32)]
+    m4s = np.stack(m4s)
+    inv4, ok4 = np.zeros_like(m4s), np.zeros(len(m4s), np.int32)
+    for i in range(len(m4s)):
+        ok4[i] = L.gvrefgeo_inverse4(ptr(m4s[i]), ptr(inv4[i]))
+        if not ok4[i]:
+            inv4[i] = 0
+    out["inv4_in"], out["inv4_out"], out["inv4_ok"] = m4s, inv4, ok4
+
+    va = rng.normal(0, 3, (300, 3)).astype(np.float32)
+    vb = rng.normal(0, 3, (300, 3)).astype(np.float32)
+    vb[:20] = va[:20] * np.float32(2.5)      # parallel: the acos argument is clamped
+    vb[20:40] = -va[20:40]                   # antiparallel
+    vb[40:50] = va[40:50]                    # equal
+    vb[50:60] = va[50:60] + np.float32(1e-4)  # almost equal (apprx_equal, eps 1e-3)
+    vm = np.stack([m4s[i % 90] for i in range(300)])
+    vops = np.zeros((300, 20), np.float32)
+    for i in range(300):
+        L.gvrefgeo_vector_ops(ptr(va[i]), ptr(vb[i]), ptr(vm[i]), 1e-3, ptr(vops[i]))
+    out["vec_a"], out["vec_b"], out["vec_m"], out["vec_ops"] = va, vb, vm, vops
+
+    ma, mb = m4s[:90].copy(), np.roll(m4s[:90], 1, axis=0).copy()
+    mb[:10] = ma[:10] + np.float32(1e-5)
+    mops = np.zeros((90, 16 * 3 + 3), np.float32)
+    mapprox = np.zeros(90, np.int32)
+    for i in range(90):
+        ap = C.c_int(0)
+        L.gvrefgeo_matrix_ops(ptr(ma[i]), ptr(mb[i]), 1e-3, ptr(mops[i, 0:16]), ptr(mops[i, 16:32]), ptr(mops[i, 32:48]),
+                              ptr(mops[i, 48:51]), ptr(va[i]), C.byref(ap))
+        mapprox[i] = ap.value
+    out["mat_a"], out["mat_b"], out["mat_ops"], out["mat_approx"] = ma, mb, mops, mapprox
+
+    texts = []
+    buf = C.create_string_buffer(4096)
+    for what, arr in ((0, va[0]), (0, np.array([1, -2.5, 1e-7], np.float32)), (1, rot[5]), (1, m3s[70]), (2, m4s[3]), (2, m4s[94])):
+        L.gvrefgeo_format(what, ptr(np.ascontiguousarray(arr)), buf, 4096)
+        texts.append(buf.value.decode())
+    out["fmt_what"] = np.array([0, 0, 1, 1, 2, 2], np.int32)
+    out["fmt_in"] = np.stack([np.pad(a, (0, 16 - len(a))) for a in (va[0], np.array([1, -2.5, 1e-7], np.float32), rot[5], m3s[70], m4s[3], m4s[94])])
+    out["fmt_text"] = np.array(texts)
+
     path = os.path.join(ROOT, "tests", "golden", "geometry.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, {k: v.shape for k, v in out.items()}, os.path.getsize(path), "bytes")

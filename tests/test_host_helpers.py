@@ -190,3 +190,55 @@ def test_equidistant_points_and_checkerboards_equal_reference():
         got = _clouds(r.stdout, 3)
         assert _same_bits(got[0], eq[i]) and _same_bits(got[1], black[i]) and _same_bits(got[2], white[i]), p
     assert len(eq[0]) == 10000  # the reference fixture: 10000 points in the 89 x 123 x 74 map
+
+
+# ---- value API of Vector3f / Matrix3f / Matrix4f (GV/helpers/cuda_vectors.h:247-331, cuda_matrices.h:83-660) -------
+def _mathfile(kind, records, tmp_path):
+    path = str(tmp_path / (kind + ".f32"))
+    np.ascontiguousarray(records, np.float32).tofile(path)
+    return subprocess.run([_exe(), "mathfile", kind, path], capture_output=True, check=True).stdout
+
+
+def test_rotation_decomposition_equals_reference(tmp_path):
+    """Matrix3f::toRPY (solution numbers 0, 1, 2; 330 rotations incl. both pitch singularities) and
+    orientationMatrixDiff, bit for bit; and the reference's own property test (GV/test/testing_cudaMath.cu:148-195):
+    both decompositions rebuild the rotation to within 0.005"""
+    g = _geometry_golden()
+    got = np.frombuffer(_mathfile("torpy", g["rot"], tmp_path), np.float32).reshape(-1, 3, 3)
+    assert _same_bits(got, g["rot_to_rpy"])
+    assert _same_bits(np.frombuffer(_mathfile("diff", g["rot"], tmp_path), np.float32).reshape(-1, 3), g["rot_diff"])
+    # property: createFromRPY(toRPY(R)) is R again (both solutions)
+    for sol in (0, 1):
+        back = np.frombuffer(_geom("rpy", np.ascontiguousarray(got[:150, sol]).view(np.uint32).reshape(-1)), np.float32).reshape(-1, 9)
+        assert np.abs(back - g["rot"][:150]).max() < 0.005
+
+
+def test_matrix_inversion_equals_reference(tmp_path):
+    """Gauss-Jordan inversion of Matrix3f / Matrix4f: same result bits, same verdict for singular matrices and for the
+    zero-pivot cases that need a row swap; M * inverse(M) is the identity (GV/test/testing_cudaMath.cu:127-146)"""
+    g = _geometry_golden()
+    for n, kind in ((3, "inv3"), (4, "inv4")):
+        got = np.frombuffer(_mathfile(kind, g[kind + "_in"], tmp_path), np.float32).reshape(-1, 1 + n * n)
+        assert np.array_equal(got[:, 0] != 0, g[kind + "_ok"] != 0)
+        assert _same_bits(got[:, 1:], g[kind + "_out"])
+        assert 0 < (g[kind + "_ok"] == 0).sum() < 10
+    fixture = g["inv4_in"][90].reshape(4, 4).astype(np.float64)   # the matrix of the reference's test
+    inv = g["inv4_out"][90].reshape(4, 4).astype(np.float64)
+    assert np.abs(fixture @ inv - np.eye(4)).max() < 2e-6
+
+
+def test_vector_and_matrix_value_api_equals_reference(tmp_path):
+    """length / dot / angleBetween (clamped for parallel vectors) / cross / normalized / abs / normalize / Matrix4f * v /
+    compVec / apprx_equal; transpose / a - b / a * b / leftMultiply / getRotation * v / apprx_equal; operator<< texts"""
+    g = _geometry_golden()
+    rec = np.concatenate([g["vec_a"], g["vec_b"], g["vec_m"]], axis=1)
+    got = np.frombuffer(_mathfile("vec", rec, tmp_path), np.float32).reshape(-1, 20)
+    assert _same_bits(got, g["vec_ops"])
+    assert got[:20, 2].max() < 1e-3 and got[20:40, 2].min() > 3.14 and got[40:50, 19].min() == 1.0 and got[50:60, 19].min() == 1.0 and got[100:, 19].max() == 0.0
+    rec = np.concatenate([g["mat_a"], g["mat_b"], g["vec_a"][:90]], axis=1)
+    got = np.frombuffer(_mathfile("mat", rec, tmp_path), np.float32).reshape(-1, 53)
+    assert _same_bits(got[:, :51], g["mat_ops"])
+    assert np.array_equal(got[:, 51] != 0, g["mat_approx"] != 0) and (got[:, 52] == 1.0).all()
+    rec = np.concatenate([g["fmt_what"].astype(np.float32)[:, None], g["fmt_in"]], axis=1)
+    texts = _mathfile("fmt", rec, tmp_path).split(b"\0")[:-1]
+    assert [t.decode() for t in texts] == [str(t) for t in g["fmt_text"]]
