@@ -589,13 +589,13 @@ BOOST_AUTO_TEST_CASE(base_class_interface)
   std::stringstream captured;
   std::streambuf* old = std::cout.rdbuf(captured.rdbuf());
   tiny.screendump(true);
-  ProbVoxelMap tiny_map(Vector3ui(2, 2, 2), 1.f, MT_PROBAB_VOXELMAP);
+  ProbVoxelMap tiny_map(Vector3ui(16, 16, 16), 1.f, MT_PROBAB_VOXELMAP);
   tiny_map.printVoxelMapData();
   std::cout.rdbuf(old);
   const std::string text = captured.str();
   BOOST_CHECK(text.find("[0] ID = 21 Coords: ") != std::string::npos);
   BOOST_CHECK(text.find("[1] ID = 22 Coords: ") != std::string::npos);
-  BOOST_CHECK(text.find("VoxelMap dump: ") != std::string::npos && text.find("7: -128") != std::string::npos);
+  BOOST_CHECK(text.find("VoxelMap dump: ") != std::string::npos && text.find("4095: -128") != std::string::npos);
 }
 
 // PointcloudFileHandler / insertPointCloudFromFile / PointCloud(file) / MetaPointCloud(files)
