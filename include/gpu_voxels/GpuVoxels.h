@@ -15,6 +15,7 @@
 #include <vector>
 
 #include <gpu_voxels/helpers/MathHelpers.h>
+#include <gpu_voxels/helpers/cuda_handling.h>
 #include <gpu_voxels/GpuVoxelsMap.h>
 #include <gpu_voxels/helpers/GeometryGeneration.h>
 #include <gpu_voxels/robot/dh_robot/KinematicChain.h>

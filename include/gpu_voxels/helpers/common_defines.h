@@ -50,5 +50,9 @@ static const Probability MAX_PROBABILITY = Probability(127);
 static const Probability cSENSOR_MODEL_FREE = -10;
 static const Probability cSENSOR_MODEL_OCCUPIED = 72;
 
+// GV/helpers/common_defines.h:294-295
+const float cMBYTE2BYTE = 1024.0 * 1024.0;
+const float cBYTE2MBYTE = 1.0 / cMBYTE2BYTE;
+
 }  // namespace gpu_voxels
 #endif

@@ -580,6 +580,12 @@ BOOST_AUTO_TEST_CASE(base_class_interface)
   list->insertPointCloud(pc.getConstDevicePointer(), pc.getPointCloudSize(), BitVoxelMeaning(11));
   BOOST_CHECK(list->size() >= n);
 
+  // device reports of the helper library (GV/helpers/cuda_handling.cu:66-149)
+  BOOST_CHECK(getDeviceMemoryInfo().find("total memory (MB)  : ") != std::string::npos);
+  BOOST_CHECK(getDeviceInfos().find("Multi Processor Count: ") != std::string::npos);
+  int n_dev = 0;
+  BOOST_CHECK(cuGetNrOfDevices(&n_dev) && n_dev == 1);
+
   // dumps print one line per entry / voxel
   BitVectorVoxelList tiny(Vector3ui(4, 4, 4), 1.f, MT_BITVECTOR_VOXELLIST);
   std::vector<Vector3f> two;
