@@ -42,3 +42,23 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "gvoracle" not in src and "oracle." not in src and "libgvref" not in src, f
+
+
+def test_python_constants_equal_the_header():
+    """every enumerator of include/gvx.h that the Python binding names has the header's value (status codes, memory
+    kinds, map types, options)"""
+    from gpu_voxels_b200 import _lib, api
+    txt = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "gvx.h")).read(), flags=re.S)
+    enum = {k: int(v) for k, v in re.findall(r"\b(GVX_[A-Z0-9_]+)\s*=\s*(-?\d+)", txt)}
+    assert len(enum) >= 18
+    checked = 0
+    for name, value in enum.items():
+        short = name[4:]
+        for mod in (_lib, api):
+            for attr in (name, short):
+                if hasattr(mod, attr):
+                    assert getattr(mod, attr) == value, (mod.__name__, attr)
+                    checked += 1
+    assert checked >= 14
+    # the facade's map types are the reference's on-disk tags (GV/helpers/common_defines.h:53-74)
+    assert (enum["GVX_MT_BITVECTOR_VOXELMAP"], enum["GVX_MT_BITVECTOR_VOXELLIST"], enum["GVX_MT_PROBAB_VOXELMAP"]) == (0, 1, 4)
