@@ -40,6 +40,10 @@ enum MapType
 static const std::string GPU_VOXELS_MAP_TYPE_NOT_IMPLEMENTED = "THIS TYPE OF DATA STRUCTURE IS NOT YET IMPLEMENTED!";
 static const std::string GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED = "THIS OPERATION IS NOT SUPPORTED BY THE DATA STRUCTURE!";
 static const std::string GPU_VOXELS_MAP_OPERATION_NOT_YET_SUPPORTED = "THIS OPERATION IS NOT YET SUPPORTED BY THE DATA STRUCTURE!";
+static const std::string GPU_VOXELS_MAP_ONLY_SUPPORTS_BVM_OCCUPIED = "THIS DATA STRUCTURE ONLY SUPPORTS BITVOXEL MEANING eBVM_OCCUPIED!";
+static const std::string GPU_VOXELS_MAP_SWAP_FOR_COLLIDE = "TRY TO SWAP BOTH DATA STRUCTURES TO COLLIDE.";
+static const std::string GPU_VOXELS_MAP_OFFSET_ON_WRONG_DATA_STRUCTURE = "OFFSET ADDITION ONLY POSSIBLE WHEN COLLIDING WITH VOXELMAP/VOXELLIST";
+const uint32_t cMAX_NR_OF_DEVICES = 10;  // GV/helpers/common_defines.h:33 (unused there as well: one device per process)
 
 typedef int8_t Probability;  // GV/voxel/ProbabilisticVoxel.h
 static const Probability UNKNOWN_PROBABILITY = Probability(-128);

@@ -243,7 +243,7 @@ public:
   virtual void clearBitVoxelMeaning(BitVoxelMeaning voxel_meaning)
   {
     if (voxel_meaning != eBVM_OCCUPIED)
-      LOGGING_ERROR_C(VoxelmapLog, ProbVoxelMap, GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+      LOGGING_ERROR_C(VoxelmapLog, ProbVoxelMap, GPU_VOXELS_MAP_ONLY_SUPPORTS_BVM_OCCUPIED << endl);
     else
       this->clearMap();
   }
