@@ -209,6 +209,59 @@ int main(int argc, char** argv)
     }
     else return 2;
   }
+  else if (mode == "bitvector")
+  {  // the reference's host-side BitVector tests (GV/test/testing_bitvector.cu:36-194) against the facade's BitVector
+    using namespace gpu_voxels;
+    typedef BitVector<BIT_VECTOR_LENGTH> BV;
+    int failed = 0;
+#define GVX_EXPECT(cond) do { if (!(cond)) { ++failed; std::printf("FAILED: %s\n", #cond); } } while (0)
+    std::string a_bits(256, '0'), not_a_bits(256, '1');
+    const int set_bits[] = {0, 2, 3, 4, 111, 254, 255};  // FREE, COLLISION, UNKNOWN, SV_START, 111, SV_END, UNDEFINED
+    for (int k = 0; k < 7; ++k) { a_bits[set_bits[k]] = '1'; not_a_bits[set_bits[k]] = '0'; }
+    BV a, same_a, not_a, b, c, tmp;
+    { std::stringstream in(a_bits); in >> a; }
+    { std::stringstream in(a_bits); in >> same_a; }
+    { std::stringstream in(not_a_bits); in >> not_a; }
+    { std::stringstream in(a_bits); in >> b; }
+    { std::stringstream out; out << a; GVX_EXPECT(out.str() == a_bits); }
+    GVX_EXPECT(tmp.isZero()); GVX_EXPECT(!a.isZero()); GVX_EXPECT(a == same_a); GVX_EXPECT(!(not_a == a));
+    tmp = a; GVX_EXPECT(a == tmp);
+    tmp.clear(); GVX_EXPECT(tmp.isZero());
+    tmp = BV(a); GVX_EXPECT(a == tmp);
+    c = ~a; GVX_EXPECT(c == not_a);
+    GVX_EXPECT((a & not_a).isZero()); GVX_EXPECT((~(a | not_a)).isZero());
+    tmp.clear();
+    tmp.setBit(eBVM_FREE); tmp.setBit(eBVM_COLLISION); tmp.setBit(eBVM_UNKNOWN); tmp.setBit(eBVM_SWEPT_VOLUME_START);
+    tmp.setBit(BitVoxelMeaning(111)); tmp.setBit(eBVM_SWEPT_VOLUME_END); tmp.setBit(eBVM_UNDEFINED);
+    GVX_EXPECT(tmp == b);
+    for (uint32_t i = 0; i < BIT_VECTOR_LENGTH; ++i)
+    {
+      bool want = false;
+      for (int k = 0; k < 7; ++k) want = want || uint32_t(set_bits[k]) == i;
+      GVX_EXPECT(b.getBit(i) == want);
+    }
+    tmp.clear();
+    tmp.setByte(0 * 8, uint8_t(29)); tmp.setByte(13 * 8, uint8_t(128)); tmp.setByte(31 * 8, uint8_t(192));
+    GVX_EXPECT(tmp == b);
+    GVX_EXPECT(tmp.getByte(13 * 8) == 128);
+    b.clearBit(eBVM_COLLISION); GVX_EXPECT(!b.getBit(eBVM_COLLISION));
+    a |= not_a; GVX_EXPECT((~a).isZero());
+    tmp.clear(); GVX_EXPECT(tmp.noneButEmpty());
+    tmp.setBit(eBVM_FREE); GVX_EXPECT(tmp.noneButEmpty());
+    tmp.setBit(123); GVX_EXPECT(!tmp.noneButEmpty());
+    for (uint32_t shift = 3; shift < 20; shift += 10)  // bitvector_bitshift, :139-194
+    {
+      BV v;
+      const uint32_t bits[] = {0, 1, 2, 3, 4, 14, 24, 254, 255};
+      for (int k = 0; k < 9; ++k) v.setBit(bits[k]);
+      performLeftShift(v, uint8_t(shift));
+      for (int k = 0; k < 9; ++k) GVX_EXPECT(!v.getBit(bits[k]));
+      GVX_EXPECT(v.getBit(24 - shift) == (24 - shift > 3));
+      GVX_EXPECT(v.getBit(254 - shift)); GVX_EXPECT(v.getBit(255 - shift));
+    }
+#undef GVX_EXPECT
+    std::printf("%s\n", failed ? "MISMATCH" : "ok");
+  }
   else if (mode == "mathfile")
   {  // mathfile <kind> <path>: raw float32 records in, raw float32 results out (value API of Vector3f / Matrix3f /
      // Matrix4f against tests/golden/geometry.npz; record layouts in tests/test_host_helpers.py)

@@ -242,3 +242,13 @@ def test_vector_and_matrix_value_api_equals_reference(tmp_path):
     rec = np.concatenate([g["fmt_what"].astype(np.float32)[:, None], g["fmt_in"]], axis=1)
     texts = _mathfile("fmt", rec, tmp_path).split(b"\0")[:-1]
     assert [t.decode() for t in texts] == [str(t) for t in g["fmt_text"]]
+
+
+def test_reference_bitvector_host_tests_pass_on_the_facade():
+    """GV/test/testing_bitvector.cu:36-194 (logic operations, stream operators, setByte, noneButEmpty, left shift of the
+    swept-volume IDs) run against include/gpu_voxels/voxel/BitVoxel.h"""
+    hdr = os.path.join(ROOT, "include", "gpu_voxels", "voxel", "BitVoxel.h")
+    if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
+        os.remove(EXE)
+    r = subprocess.run([_exe(), "bitvector"], capture_output=True, text=True, check=True)
+    assert r.stdout.strip() == "ok", r.stdout
