@@ -4,6 +4,7 @@
 #ifndef GPU_VOXELS_B200_HELPERS_METAPOINTCLOUD_H
 #define GPU_VOXELS_B200_HELPERS_METAPOINTCLOUD_H
 
+#include <cstring>
 #include <iostream>
 #include <map>
 #include <string>
@@ -76,7 +77,14 @@ public:
   }
   ~MetaPointCloud() { if (m_buf) gvx_buffer_destroy(m_buf); }
 
-  bool operator==(const MetaPointCloud& other) const { return m_sizes == other.m_sizes && m_points == other.m_points; }
+  // GV/helpers/MetaPointCloud.cu:226-287: same accumulated size, same NUMBER of sub-clouds and the same bytes of the
+  // accumulated array (the individual sub-cloud sizes are not compared there; NaN bit patterns compare equal)
+  bool operator==(const MetaPointCloud& other) const
+  {
+    if (this == &other) return true;
+    if (m_points.size() != other.m_points.size() || m_sizes.size() != other.m_sizes.size()) return false;
+    return m_points.empty() || std::memcmp(&m_points[0], &other.m_points[0], m_points.size() * sizeof(Vector3f)) == 0;
+  }
 
   void addCloud(uint32_t cloud_size)
   {

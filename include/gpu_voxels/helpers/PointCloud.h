@@ -4,6 +4,7 @@
 #ifndef GPU_VOXELS_B200_HELPERS_POINTCLOUD_H
 #define GPU_VOXELS_B200_HELPERS_POINTCLOUD_H
 
+#include <cstring>
 #include <iostream>
 #include <string>
 #include <vector>
@@ -36,7 +37,14 @@ public:
   PointCloud& operator=(const PointCloud& other) { if (this != &other) update(&other); return *this; }
   ~PointCloud() { if (m_buf) gvx_buffer_destroy(m_buf); }
 
-  bool operator==(const PointCloud& other) const { return m_host == other.m_host; }
+  // equal = same number of points and the same BYTES (GV/helpers/PointCloud.cu:147-210 compares the device arrays with
+  // kernelCompareMem): NaN coordinates with equal bit patterns are equal, +0 and -0 are not
+  bool operator==(const PointCloud& other) const
+  {
+    if (this == &other) return true;
+    if (m_host.size() != other.m_host.size()) return false;
+    return m_host.empty() || std::memcmp(&m_host[0], &other.m_host[0], m_host.size() * sizeof(Vector3f)) == 0;
+  }
 
   void add(const PointCloud* cloud) { add(cloud->m_host); }
   void add(const std::vector<Vector3f>& points) { add(points.empty() ? NULL : &points[0], uint32_t(points.size())); }

@@ -524,6 +524,66 @@ BOOST_AUTO_TEST_CASE(voxelmap_disk_io)
   BOOST_CHECK(m1.collideWith(&m2, 0.5) == 9 * 9 * 9);
 }
 
+// GV/test/testing_pointclouds.cu:35-150: copies of (meta) point clouds stay equal through chains of copy construction
+// and assignment, a changed point is detected, transform and transformSelf agree. Equality is byte-wise, as the
+// reference's kernelCompareMem: point 0 is (0, 0, inf) and becomes NaN under the rotation, and still compares equal.
+BOOST_AUTO_TEST_CASE(pointclouds_equality_and_rotation)
+{
+  std::vector<Vector3f> testdata;
+  for (size_t i = 0; i < (size_t)numberOfPoints; i++) testdata.push_back(Vector3f(i, 0, 1.0 / i));
+  {
+    MetaPointCloud* orig = new MetaPointCloud();
+    for (size_t j = 0; j < 15; j++) orig->addCloud(testdata);
+    orig->syncToDevice();
+    MetaPointCloud* working_copy = new MetaPointCloud(*orig);
+    for (size_t k = 0; k < 100; k++)
+    {
+      MetaPointCloud* copy1 = new MetaPointCloud(*working_copy);
+      MetaPointCloud* copy2 = new MetaPointCloud(*copy1);
+      delete copy1;
+      *working_copy = *copy2;
+      delete copy2;
+    }
+    BOOST_CHECK_MESSAGE(*orig == *working_copy, "Point clouds are the same.");
+    std::vector<Vector3f> changed(testdata);
+    changed[100] = Vector3f(100, 0.33, 1.0 / 100);
+    working_copy->updatePointCloud(3, changed, true);
+    BOOST_CHECK_MESSAGE(!(*orig == *working_copy), "Point cloud difference detected.");
+    delete orig;
+    delete working_copy;
+  }
+  {
+    PointCloud* orig = new PointCloud();
+    orig->update(testdata);
+    PointCloud* working_copy = new PointCloud(*orig);
+    for (size_t k = 0; k < 100; k++)
+    {
+      PointCloud* copy1 = new PointCloud(*working_copy);
+      PointCloud* copy2 = new PointCloud(*copy1);
+      delete copy1;
+      *working_copy = *copy2;
+      delete copy2;
+    }
+    BOOST_CHECK_MESSAGE(*orig == *working_copy, "Point clouds are the same.");
+    std::vector<Vector3f> changed(testdata);
+    changed[100] = Vector3f(100, 0.33, 1.0 / 100);
+    working_copy->update(changed);
+    BOOST_CHECK_MESSAGE(!(*orig == *working_copy), "Point cloud difference detected.");
+    delete orig;
+    delete working_copy;
+  }
+  {
+    PointCloud orig, rotated;
+    orig.add(testdata);
+    Matrix4f transformation = Matrix4f::createFromRotationAndTranslation(Matrix3f::createFromRPY(Vector3f(12.0, 11.0, 56.0)),
+                                                                        Vector3f(2.2, 1.1, 3.3));
+    orig.transform(&transformation, &rotated);
+    orig.transformSelf(&transformation);
+    BOOST_CHECK_MESSAGE(orig == rotated, "Self rotation and copy rotation are equal.");
+    BOOST_CHECK(orig.getPointCloudSize() == (size_t)numberOfPoints);
+  }
+}
+
 // the GpuVoxelsMap base interface as callers use it through GpuVoxelsMapSharedPtr (GV/GpuVoxelsMap.h:112-260), and the
 // raw-storage / collider entry points of the list (GV/voxellist/TemplateVoxelList.h:95-116, .hpp:690-774)
 BOOST_AUTO_TEST_CASE(base_class_interface)
