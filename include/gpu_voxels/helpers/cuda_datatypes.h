@@ -286,7 +286,13 @@ struct Matrix4f
   }
   const float* data() const { return &a11; }
   float* data() { return &a11; }
-  bool operator==(const Matrix4f& o) const { return std::memcmp(this, &o, sizeof(*this)) == 0; }
+  // element-wise float comparison (GV/helpers/cuda_matrices.h:560-567): -0 equals +0, NaN equals nothing
+  bool operator==(const Matrix4f& o) const
+  {
+    for (int i = 0; i < 16; ++i)
+      if (!(data()[i] == o.data()[i])) return false;
+    return true;
+  }
 };
 
 // Matrix4f * Matrix4f as the reference's HOST code evaluates it (GV/helpers/cuda_matrices.h:772-803): every entry is

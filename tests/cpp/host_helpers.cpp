@@ -262,6 +262,49 @@ int main(int argc, char** argv)
 #undef GVX_EXPECT
     std::printf("%s\n", failed ? "MISMATCH" : "ok");
   }
+  else if (mode == "cudamath")
+  {  // the reference's host-side matrix tests (GV/test/testing_cudaMath.cu:33-195) against the facade's types
+    using namespace gpu_voxels;
+    int failed = 0;
+#define GVX_EXPECT(cond) do { if (!(cond)) { ++failed; std::printf("FAILED: %s\n", #cond); } } while (0)
+    const Matrix4f matrix(0.9751700, -0.218711, -0.0347626, 10, 0.1976770, 0.930432, -0.3085770, 11,
+                          0.0998334, 0.294044, 0.9505640, 12, 0, 0, 0, 1);
+    GVX_EXPECT(matrix == matrix);
+    { Matrix4f a = matrix, b = matrix; b.a13 += 0.0001; GVX_EXPECT(!(a == b)); }
+    { Matrix4f a = matrix, b = matrix; b.a22 -= 0.00001; GVX_EXPECT(a.apprx_equal(b, 0.000011)); }
+    { Matrix4f a = matrix, b = matrix; b.a22 += 0.00001; GVX_EXPECT(a.apprx_equal(b, 0.000011)); }
+    { Matrix4f a = matrix, b = matrix; b.a22 += 0.000013; GVX_EXPECT(!a.apprx_equal(b, 0.000011)); }
+    GVX_EXPECT(matrix.transpose() == Matrix4f(0.9751700, 0.1976770, 0.0998334, 0, -0.218711, 0.930432, 0.294044, 0,
+                                              -0.0347626, -0.3085770, 0.9505640, 0, 10, 11, 12, 1));
+    {
+      const Matrix4f a(1, 2, 3, 4, 4, 3, 2, 1, 2, 1, 3, 4, 2, 3, 1, 4), b(7, 4, 5, 6, 6, 5, 7, 4, 4, 6, 5, 7, 4, 5, 6, 7);
+      GVX_EXPECT(a * b == Matrix4f(47, 52, 58, 63, 58, 48, 57, 57, 48, 51, 56, 65, 52, 49, 60, 59));
+    }
+    {
+      Matrix4f inverse;
+      GVX_EXPECT(matrix.invertMatrix(inverse));
+      GVX_EXPECT(Matrix4f::createIdentity().apprx_equal(matrix * inverse, 0.00000011));
+    }
+    {  // matrix_rpy: both decompositions of 1000 random rotations rebuild the rotation (difference < 0.005)
+      uint64_t state = 88172645463325252ull;  // xorshift64: any fixed sequence of angles in [-2 pi, 2 pi) will do
+      for (int n = 0; n < 1000; ++n)
+      {
+        float ang[3];
+        for (int k = 0; k < 3; ++k)
+        {
+          state ^= state << 13; state ^= state >> 7; state ^= state << 17;
+          ang[k] = float((double(state >> 11) / 9007199254740992.0 * 4.0 - 2.0) * M_PI);
+        }
+        const Matrix3f a = Matrix3f::createFromRPY(Vector3f(ang[0], ang[1], ang[2]));
+        const Matrix3f b = Matrix3f::createFromRPY(a.toRPY(0)), c = Matrix3f::createFromRPY(a.toRPY(1));
+        GVX_EXPECT(a.orientationMatrixDiff(b).apprx_equal(Vector3f(0.0f), 0.005));
+        GVX_EXPECT(a.orientationMatrixDiff(c).apprx_equal(Vector3f(0.0f), 0.005));
+      }
+    }
+    { Matrix4f z, mz; mz.a12 = -0.0f; GVX_EXPECT(z == mz); z.a33 = mz.a33 = std::nanf(""); GVX_EXPECT(!(z == mz)); }
+#undef GVX_EXPECT
+    std::printf("%s\n", failed ? "MISMATCH" : "ok");
+  }
   else if (mode == "mathfile")
   {  // mathfile <kind> <path>: raw float32 records in, raw float32 results out (value API of Vector3f / Matrix3f /
      // Matrix4f against tests/golden/geometry.npz; record layouts in tests/test_host_helpers.py)

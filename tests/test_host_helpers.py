@@ -252,3 +252,11 @@ def test_reference_bitvector_host_tests_pass_on_the_facade():
         os.remove(EXE)
     r = subprocess.run([_exe(), "bitvector"], capture_output=True, text=True, check=True)
     assert r.stdout.strip() == "ok", r.stdout
+
+
+def test_reference_matrix_host_tests_pass_on_the_facade():
+    """GV/test/testing_cudaMath.cu:33-195 (equality, approximate equality, transpose, product, inverse, roll / pitch /
+    yaw round trips of 1000 random rotations) run against include/gpu_voxels/helpers/cuda_datatypes.h"""
+    _geometry_golden()  # rebuilds the helper if the headers are newer
+    r = subprocess.run([_exe(), "cudamath"], capture_output=True, text=True, check=True)
+    assert r.stdout.strip() == "ok", r.stdout[-2000:]
