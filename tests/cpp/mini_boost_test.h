@@ -18,7 +18,9 @@ inline int run_all(const char* filter)
   for (size_t i = 0; i < cases().size(); ++i)
   {
     const std::string full = std::string(cases()[i].suite) + "/" + cases()[i].name;
-    if (filter && full.find(filter) == std::string::npos) continue;
+    // "name": only cases whose suite/name contains it; "!name": all cases except those
+    if (filter && filter[0] != '!' && full.find(filter) == std::string::npos) continue;
+    if (filter && filter[0] == '!' && full.find(filter + 1) != std::string::npos) continue;
     const int before = failures();
     cases()[i].fn();
     std::printf("[%s] %s\n", failures() == before ? " OK " : "FAIL", full.c_str());
