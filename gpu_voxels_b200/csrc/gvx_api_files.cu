@@ -12,12 +12,15 @@
 // Parsing needs no GPU: gvx_pointcloud_file_load works before gvx_init. Numbers are read with the C++ stream
 // extractors the reference uses (so "1e50", "nan", "0x10", a trailing comma ... fail or succeed exactly as there),
 // arithmetic is single fp32 multiplies and adds in the reference's order (this file is compiled without FMA contraction).
+#include <algorithm>
 #include <cerrno>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <new>
 #include <sstream>
+#include <stdexcept>
 #include <string>
 #include <vector>
 #include "gvx_context.h"
@@ -95,9 +98,12 @@ int read_binvox(const std::string& path, Cloud* pts) {
   const long long cells = (long long)h.width * h.height * h.depth;
   if (cells < 0 || cells > 0x7fffffffLL)  // the reference computes this in int and allocates it
     return fail(GVX_ERR_INVALID, "Binvox: dimensions %d x %d x %d not representable", h.depth, h.height, h.width);
-  // cells the file does not cover stay empty (the reference leaves them uninitialised)
-  std::vector<unsigned char> grid((size_t)cells, 0);
+  // cells the file does not cover stay empty (the reference leaves them uninitialised): only the part of the grid the
+  // run-length data can reach (255 cells per byte pair) is materialised, whatever the header claims
   size_t at = in.good() ? (size_t)in.tellg() + 1 : raw.size();  // one byte after "data": the line feed
+  const long long reachable = at < raw.size() ? (long long)((raw.size() - at) / 2) * 255 : 0;
+  const size_t n_grid = (size_t)std::min(cells, reachable);
+  std::vector<unsigned char> grid(n_grid, 0);
   long long filled = 0;
   while (filled < cells && at + 1 < raw.size()) {
     const unsigned char value = (unsigned char)raw[at], count = (unsigned char)raw[at + 1];
@@ -110,7 +116,7 @@ int read_binvox(const std::string& path, Cloud* pts) {
   for (int x = 0; x < h.depth; ++x)
     for (int z = 0; z < h.height; ++z)
       for (int y = 0; y < h.width; ++y, ++cell)
-        if (grid[cell] == 1) {  // exactly 1: other non-zero run values are not voxels there either
+        if (cell < n_grid && grid[cell] == 1) {  // exactly 1: other non-zero run values are not voxels there either
           P3 p;
           p.x = h.scale * x; p.x = p.x + h.tx;
           p.y = h.scale * y; p.y = p.y + h.ty;
@@ -194,6 +200,13 @@ int read_pcd(const std::string& path, Cloud* pts) {
     if (want[a] < 0 || fields[want[a]].type != 'F' || fields[want[a]].size != 4 || fields[want[a]].count != 1)
       return fail(GVX_ERR_UNSUPPORTED, "PCD: %s needs float32 fields x, y and z", path.c_str());
   const size_t n = (size_t)points, first = pts->size();
+  // the header's point count is checked against the bytes that are there BEFORE anything of that size is allocated
+  const size_t left = pos < raw.size() ? raw.size() - pos : 0;
+  if (stride > (1u << 20)) return fail(GVX_ERR_INVALID, "PCD: bad field layout in %s", path.c_str());
+  if (mode == "ascii" && n > left / 2 + 1) return fail(GVX_ERR_IO, "PCD: %s holds fewer than the %zu points of its header", path.c_str(), n);
+  if (mode == "binary" && n * stride > left) return fail(GVX_ERR_IO, "PCD: truncated point data in %s", path.c_str());
+  if (mode == "binary_compressed" && n * stride > (left > 8 ? left - 8 : 0) * 90 + 64)  // LZF expands < 90 x
+    return fail(GVX_ERR_IO, "PCD: bad compressed block in %s", path.c_str());
   pts->resize(first + n);
   P3* out = pts->data() + first;
   if (mode == "ascii") {
@@ -269,10 +282,18 @@ int load_cloud(const char* path_in, int use_model_path, int shift_to_zero, const
   const std::string path = resolve(path_in, use_model_path);
   // the format is recognised by the FIRST of "xyz", "pcd", "binvox" found ANYWHERE in the full path (:84-122)
   int rc;
-  if (path.find("xyz") != std::string::npos) rc = read_xyz(path, pts);
-  else if (path.find("pcd") != std::string::npos) rc = read_pcd(path, pts);
-  else if (path.find("binvox") != std::string::npos) rc = read_binvox(path, pts);
-  else return fail(GVX_ERR_INVALID, "%s has no known file format.", path.c_str());
+  try {
+    if (path.find("xyz") != std::string::npos) rc = read_xyz(path, pts);
+    else if (path.find("pcd") != std::string::npos) rc = read_pcd(path, pts);
+    else if (path.find("binvox") != std::string::npos) rc = read_binvox(path, pts);
+    else return fail(GVX_ERR_INVALID, "%s has no known file format.", path.c_str());
+  } catch (const std::bad_alloc&) {  // no exception crosses the C ABI
+    pts->clear();
+    return fail(GVX_ERR_NOMEM, "out of host memory while reading %s", path.c_str());
+  } catch (const std::exception& e) {
+    pts->clear();
+    return fail(GVX_ERR_INVALID, "%s: %s", path.c_str(), e.what());
+  }
   if (rc) return rc;
   if (shift_to_zero && !pts->empty()) {  // (an empty cloud is undefined behaviour there: points[0])
     P3 lo = (*pts)[0];

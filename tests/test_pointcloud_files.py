@@ -282,3 +282,34 @@ def test_abi_rejects_null_arguments():
     L.gvx_pointcloud_file_free(None)
     # inserting needs an initialised library: loud failure, not a silent no-op
     assert L.gvx_insert_pointcloud_file(1, os.path.join(FILES, "cloud.txt").encode(), 0, 1, 0, None, 1.0, None) != 0
+
+
+def test_hostile_headers_cost_nothing(tmp_path, monkeypatch):
+    """A header may claim any size: the loaders check it against the bytes that are there before allocating, and no
+    exception crosses the C ABI. A .binvox grid of 2 * 10^9 cells with three runs of data yields those runs' voxels."""
+    import resource
+    import time
+    monkeypatch.chdir(tmp_path)
+    head = b"# .PCD v0.7\nVERSION 0.7\nFIELDS x y z\nSIZE 4 4 4\nTYPE F F F\nCOUNT 1 1 1\nWIDTH %d\nHEIGHT 1\nPOINTS %d\nDATA %s\n"
+    big = 2000000000
+    cases = {
+        "ascii_claims_2e9.pcd": head % (big, big, b"ascii") + b"1 2 3\n4 5 6\n",
+        "binary_claims_2e9.pcd": head % (big, big, b"binary") + b"\0" * 24,
+        "lzf_claims_2e9.pcd": head % (big, big, b"binary_compressed") + struct.pack("<II", 4, 0xFFFFFFF0) + b"\x01abc",
+        "huge_count.pcd": (head % (2, 2, b"binary")).replace(b"COUNT 1 1 1", b"COUNT 1 1 2000000000") + b"\0" * 24,
+    }
+    t0 = time.perf_counter()
+    rss0 = resource.getrusage(resource.RUSAGE_SELF).ru_maxrss
+    for name, data in cases.items():
+        with open(name, "wb") as f:
+            f.write(data)
+        ok, got = load(name)
+        assert not ok and len(got) == 0, name
+    # binvox: 2000 x 1000 x 1000 cells announced, 3 runs present: 5 voxels, 200 empty cells, 2 voxels
+    with open("huge_grid.binvox", "wb") as f:
+        f.write(b"#binvox 1\ndim 2000 1000 1000\ntranslate 0 0 0\nscale 1000\ndata\n" + bytes([1, 5, 0, 200, 1, 2]))
+    ok, got = load("huge_grid.binvox")
+    assert ok and len(got) == 7
+    assert np.array_equal(got[:, 1], np.array([0, 1, 2, 3, 4, 205, 206], np.float32)) and not got[:, [0, 2]].any()
+    assert time.perf_counter() - t0 < 5.0
+    assert resource.getrusage(resource.RUSAGE_SELF).ru_maxrss - rss0 < 200 * 1024  # KiB: nothing of header size was touched
