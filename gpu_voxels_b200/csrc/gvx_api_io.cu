@@ -9,6 +9,7 @@
 // GV/helpers/common_defines.h:61-75).
 #include <cstdio>
 #include <memory>
+#include <new>
 #include <vector>
 #include "gvx_context.h"
 
@@ -23,6 +24,14 @@ struct File {
   ~File() { if (f) fclose(f); }
   bool put(const void* p, size_t n) { return n == 0 || fwrite(p, 1, n, f) == n; }
   bool get(void* p, size_t n) { return n == 0 || fread(p, 1, n, f) == n; }
+  // bytes between the read position and the end of the file
+  uint64_t remaining() {
+    const long here = ftell(f);
+    if (here < 0 || fseek(f, 0, SEEK_END) != 0) return 0;
+    const long end = ftell(f);
+    fseek(f, here, SEEK_SET);
+    return end > here ? (uint64_t)(end - here) : 0;
+  }
 };
 
 struct MapInfo { int type; uint32_t dx, dy, dz; float side; uint64_t bytes; bool sharded; };
@@ -58,7 +67,8 @@ int gvx_map_write_file(gvx_handle_t h, const char* path) {
   if (mi.sharded) return fail_locked(GVX_ERR_UNSUPPORTED, "a z-slab map holds only part of the grid; not writing", path);
   File out(path, "wb");
   if (!out.f) return fail_locked(GVX_ERR_IO, "Write to file failed:", path);
-  std::unique_ptr<char[]> buf(new char[mi.bytes]);
+  std::unique_ptr<char[]> buf(new (std::nothrow) char[mi.bytes]);
+  if (!buf) return fail_locked(GVX_ERR_NOMEM, "no host memory for the voxels of", path);
   if ((rc = gvx_map_download(h, buf.get()))) return rc;
   const int32_t type = mi.type;
   const uint32_t dims[3] = {mi.dx, mi.dy, mi.dz};
@@ -80,7 +90,9 @@ int gvx_map_read_file(gvx_handle_t h, const char* path) {
   // a differing voxel side length is only a warning in the reference ("Continuing though...", :760-763)
   if (dims[0] != mi.dx || dims[1] != mi.dy || dims[2] != mi.dz)
     return fail_locked(GVX_ERR_DIM_MISMATCH, "Read from file failed: map dimension does not match current object:", path);
-  std::unique_ptr<char[]> buf(new char[mi.bytes]);
+  if (in.remaining() < mi.bytes) return fail_locked(GVX_ERR_IO, "truncated voxel data in", path);
+  std::unique_ptr<char[]> buf(new (std::nothrow) char[mi.bytes]);
+  if (!buf) return fail_locked(GVX_ERR_NOMEM, "no host memory for the voxels of", path);
   if (!in.get(buf.get(), mi.bytes)) return fail_locked(GVX_ERR_IO, "truncated voxel data in", path);
   return gvx_map_upload(h, buf.get());
 }
@@ -92,8 +104,10 @@ int gvx_list_write_file(gvx_handle_t h, const char* path) {
   File out(path, "wb");
   if (!out.f) return fail_locked(GVX_ERR_IO, "Write to file failed:", path);
   const size_t n = (size_t)li.size;
-  std::vector<uint32_t> ids(n), coords(3 * n);
-  std::vector<uint8_t> vox(32 * n);
+  std::vector<uint32_t> ids, coords;
+  std::vector<uint8_t> vox;
+  try { ids.resize(n); coords.resize(3 * n); vox.resize(32 * n); }
+  catch (const std::bad_alloc&) { return fail_locked(GVX_ERR_NOMEM, "no host memory for the entries of", path); }
   if (n && (rc = gvx_list_download(h, ids.data(), coords.data(), vox.data()))) return rc;
   const int32_t type = kFileBitVoxelList;
   const uint32_t dims[3] = {li.dx, li.dy, li.dz};
@@ -120,11 +134,17 @@ int gvx_list_read_file(gvx_handle_t h, const char* path) {
   if (side != li.side) return fail_locked(GVX_ERR_INVALID, "Read from file failed: Voxel side length does not match current object:", path);
   if (!in.get(&num, 4)) return fail_locked(GVX_ERR_IO, "truncated header in", path);
   const size_t n = num;
-  std::vector<uint32_t> ids(n), coords(3 * n);
-  std::vector<uint8_t> vox(32 * n);
-  if (!(in.get(ids.data(), 4 * n) && in.get(coords.data(), 12 * n) && in.get(vox.data(), 32 * n)))
-    return fail_locked(GVX_ERR_IO, "truncated list data in", path);
-  return gvx_list_upload(h, ids.data(), coords.data(), vox.data(), n);
+  // the entry count of the header is checked against the bytes that are there before anything is allocated for it
+  if (in.remaining() < (uint64_t)n * 48) return fail_locked(GVX_ERR_IO, "truncated list data in", path);
+  try {
+    std::vector<uint32_t> ids(n), coords(3 * n);
+    std::vector<uint8_t> vox(32 * n);
+    if (!(in.get(ids.data(), 4 * n) && in.get(coords.data(), 12 * n) && in.get(vox.data(), 32 * n)))
+      return fail_locked(GVX_ERR_IO, "truncated list data in", path);
+    return gvx_list_upload(h, ids.data(), coords.data(), vox.data(), n);
+  } catch (const std::bad_alloc&) {  // no exception crosses the C ABI
+    return fail_locked(GVX_ERR_NOMEM, "no host memory for the entries of", path);
+  }
 }
 
 }  // extern "C"

@@ -81,3 +81,28 @@ print("ok")
 ''' % ROOT
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout[-2000:] + r.stderr[-3000:]
+
+
+@pytest.mark.gpu
+def test_list_file_with_a_hostile_entry_count_is_refused_without_allocating(tmp_path):
+    """readFromDisk of a voxel list whose header announces 4 * 10^9 entries but carries two: GVX_ERR_IO, at once"""
+    import struct
+    import time
+    import gpu_voxels_b200 as gv
+    from gpu_voxels_b200 import _lib
+    L = _lib.init()
+    lst = gv.BitVectorVoxelList((64, 64, 64), 0.5)
+    path = str(tmp_path / "hostile.lst")
+    with open(path, "wb") as f:
+        f.write(struct.pack("<i3IfI", 1, 64, 64, 64, 0.5, 4000000000) + b"\0" * 96)
+    t0 = time.perf_counter()
+    assert L.gvx_list_read_file(lst.handle, path.encode()) == _lib.ERR_IO
+    assert time.perf_counter() - t0 < 1.0
+    # and a well-formed file of two entries still loads
+    with open(path, "wb") as f:
+        f.write(struct.pack("<i3IfI", 1, 64, 64, 64, 0.5, 2) + struct.pack("<2I", 5, 70) +
+                struct.pack("<6I", 5, 0, 0, 6, 1, 0) + (b"\x00\x08" + b"\0" * 30) * 2)
+    _lib.check(L.gvx_list_read_file(lst.handle, path.encode()))
+    n = _lib.C.c_uint64(0)
+    _lib.check(L.gvx_list_size(lst.handle, _lib.C.byref(n)))
+    assert n.value == 2
