@@ -14,6 +14,8 @@
 #include <sstream>
 #include <vector>
 
+#include <icl_core_config/Config.h>
+#include <gpu_voxels/helpers/BoostCompat.h>
 #include <gpu_voxels/helpers/GeometryGeneration.h>
 #include <gpu_voxels/helpers/MathHelpers.h>
 #include <gpu_voxels/voxel/BitVoxel.h>
@@ -261,6 +263,18 @@ int main(int argc, char** argv)
     }
 #undef GVX_EXPECT
     std::printf("%s\n", failed ? "MISMATCH" : "ok");
+  }
+  else if (mode == "compat")
+  {  // the icl_core option stand-in and the boost aliases: host_helpers compat [--device-identifier=X | -id X] [--flag]
+    icl_core::config::GetoptParameter ident("device-identifier:", "id", "Identifer of the kinect device");
+    icl_core::config::addParameter(ident);
+    icl_core::config::addParameter(icl_core::config::GetoptParameter("flag", "f", "a switch"));
+    icl_core::logging::initialize(argc, argv);
+    const std::string id = icl_core::config::Getopt::instance().paramOpt("device-identifier");
+    boost::shared_ptr<std::string> p = boost::make_shared<std::string>(id);
+    std::printf("%s|%d|%d|%d\n", p->c_str(), int(icl_core::config::Getopt::instance().paramOptPresent("device-identifier")),
+                int(icl_core::config::Getopt::instance().paramOptPresent("flag")),
+                int(icl_core::config::Getopt::instance().paramOptPresent("unknown")));
   }
   else if (mode == "cudamath")
   {  // the reference's host-side matrix tests (GV/test/testing_cudaMath.cu:33-195) against the facade's types

@@ -260,3 +260,16 @@ def test_reference_matrix_host_tests_pass_on_the_facade():
     _geometry_golden()  # rebuilds the helper if the headers are newer
     r = subprocess.run([_exe(), "cudamath"], capture_output=True, text=True, check=True)
     assert r.stdout.strip() == "ok", r.stdout[-2000:]
+
+
+def test_option_stand_in_and_boost_aliases():
+    """include/icl_core_config/Config.h (the option handling the reference's examples use) and helpers/BoostCompat.h"""
+    for h in (os.path.join(ROOT, "include", "icl_core_config", "Config.h"),
+              os.path.join(ROOT, "include", "gpu_voxels", "helpers", "BoostCompat.h")):
+        if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(h):
+            os.remove(EXE)
+    run = lambda *a: subprocess.run([_exe(), "compat"] + list(a), capture_output=True, text=True, check=True).stdout.strip()
+    assert run("--device-identifier=cam7", "--flag") == "cam7|1|1|0"
+    assert run("-id", "cam9") == "cam9|1|0|0"
+    assert run("--device-identifier", "cam1", "-f") == "cam1|1|1|0"
+    assert run() == "|0|0|0"
