@@ -35,7 +35,8 @@ def build(force=False, verbose=False):
         cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, s), "-o", o]
         subprocess.check_call(cmd)
         objs.append(o)
-    subprocess.check_call([nvcc, "-shared", "-o", LIB] + objs + ["-lcudart"])
+    # the arch on the link line too: without it nvcc adds an (empty) element for its default architecture to the fatbinary
+    subprocess.check_call([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + ["-lcudart"])
     return LIB
 
 
