@@ -23,6 +23,7 @@ SIGNATURES = {
     "gvx_last_error": (C.c_char_p, []),
     "gvx_set_stream": (C.c_int, [vp]),
     "gvx_sync": (C.c_int, []),
+    "gvx_wait_event": (C.c_int, [vp]),
     "gvx_device_info": (C.c_int, [P(C.c_int), P(u64), P(u64), C.c_char_p]),
     "gvx_launch_count": (u64, []),
     "gvx_set_l2_fetch_granularity": (C.c_int, [C.c_int, P(C.c_int)]),
@@ -39,6 +40,8 @@ SIGNATURES = {
     "gvx_map_clear_meaning": (C.c_int, [u64, C.c_int]),
     "gvx_map_clear_bits": (C.c_int, [u64, vp]),
     "gvx_map_device_ptr": (C.c_int, [u64, P(vp), P(u64), P(u64)]),
+    "gvx_map_device_ptr_const": (C.c_int, [u64, P(vp), P(u64), P(u64)]),
+    "gvx_summary_fallback_count": (u64, []),
     "gvx_map_info": (C.c_int, [u64, P(C.c_int), P(u32), P(f32), P(u32), P(u32), P(u64)]),
     "gvx_map_download": (C.c_int, [u64, vp]),
     "gvx_map_upload": (C.c_int, [u64, vp]),
@@ -133,6 +136,27 @@ def check(rc):
 
 
 _initialized = False
+_shared_stream = None  # cudaStream_t handed to gvx_set_stream through set_stream(), else None (the library's own stream)
+
+
+def set_stream(cuda_stream):
+    """gvx_set_stream, remembered so that order_after_torch() can skip the event when torch works on the same stream"""
+    global _shared_stream
+    check(init().gvx_set_stream(C.c_void_p(cuda_stream) if cuda_stream else None))
+    _shared_stream = int(cuda_stream) if cuda_stream else None
+
+
+def order_after_torch(tensor):
+    """A CUDA tensor is about to be handed over as GVX_MEM_DEVICE: libgvx enqueues on its own non-blocking stream, which
+    has no ordering against torch's streams, so the kernels that read the tensor are made to wait for everything torch
+    has queued on its current stream (one event record + one cudaStreamWaitEvent; nothing blocks on the host)."""
+    import torch
+    cur = torch.cuda.current_stream(tensor.device)
+    if _shared_stream is not None and cur.cuda_stream == _shared_stream:
+        return
+    ev = torch.cuda.Event()
+    ev.record(cur)
+    check(load().gvx_wait_event(C.c_void_p(ev.cuda_event)))
 
 
 def init(device=-1):

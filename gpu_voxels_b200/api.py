@@ -47,6 +47,7 @@ def _points_arg(points):
             import torch
             assert t.dtype == torch.float32 and t.is_contiguous()
             n = t.numel() // 3
+            _lib.order_after_torch(t)
             return C.c_void_p(t.data_ptr()), n, MEM_DEVICE, t
         points = t
     a = np.ascontiguousarray(points, dtype=np.float32).reshape(-1, 3)

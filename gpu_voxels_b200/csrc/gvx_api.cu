@@ -64,6 +64,7 @@ int gvx_shutdown(void) {
   g.bat_bits_cap = g.bat_seen_cap = g.bat_tr_cap = g.bat_tr_h_cap = g.bat_counts_cap = g.bat_counts_h_cap = 0;
   g.bat_fk_cap = g.bat_fk_h_cap = 0;
   if (g.stage_d) cudaFree(g.stage_d);
+  if (g.stage_ev) { cudaEventDestroy(g.stage_ev); g.stage_ev = nullptr; }
   if (g.copy_stream) {
     cudaStreamSynchronize(g.copy_stream);
     for (int k = 0; k < 2; ++k) {
@@ -104,6 +105,14 @@ int gvx_set_stream(void* cuda_stream) {
   return GVX_OK;
 }
 
+int gvx_wait_event(void* cuda_event) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  if (!cuda_event) return fail(GVX_ERR_INVALID, "null event");
+  GVX_CUDA(cudaStreamWaitEvent(g.stream, (cudaEvent_t)cuda_event, 0));
+  return GVX_OK;
+}
+
 int gvx_sync(void) {
   std::lock_guard<std::mutex> lk(g.mu);
   GVX_NEED_INIT();
@@ -129,6 +138,7 @@ int gvx_device_info(int* sm_count, uint64_t* free_bytes, uint64_t* total_bytes, 
 }
 
 uint64_t gvx_launch_count(void) { return g.launches; }
+uint64_t gvx_summary_fallback_count(void) { return g.summary_fallbacks; }
 
 int gvx_set_l2_fetch_granularity(int bytes, int* previous) {
   std::lock_guard<std::mutex> lk(g.mu);
@@ -268,9 +278,9 @@ int gvx_map_destroy(gvx_handle_t h) {
 }
 static int map_clear_locked(Map* m) {
   GVX_CUDA(cudaMemsetAsync(m->data, m->type == kMapProb ? 0x80 : 0x00, m->bytes(), g.stream));
-  if (m->occ) {  // an empty map has an empty summary: clearing also re-validates it
+  if (m->occ) {  // an empty map has an empty summary: clearing re-validates it (unless the raw pointer is out)
     GVX_CUDA(cudaMemsetAsync(m->occ, 0, m->occ_bytes(), g.stream));
-    m->occ_valid = true;
+    m->revalidate();
   }
   return GVX_OK;
 }
@@ -290,7 +300,7 @@ int gvx_map_clear_bits(gvx_handle_t h, const uint8_t mask32[GVX_BITVOXEL_BYTES])
   uint32_t w[8];
   memcpy(w, mask32, 32);
   GVX_CUDA(launch_clear_bits(lctx(), m->data, m->n_voxels(), w, m->occ));
-  if (m->occ) m->occ_valid = true;  // the kernel re-derives every summary word
+  m->revalidate();  // the kernel re-derives every summary word
   return GVX_OK;
 }
 int gvx_map_clear_meaning(gvx_handle_t h, int meaning) {
@@ -316,8 +326,21 @@ int gvx_map_device_ptr(gvx_handle_t h, void** data_d, uint64_t* first_voxel, uin
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
   if (data_d) {
     *data_d = m->data;
-    m->occ_valid = false;  // the caller may write voxels behind the library's back: gvx_map_refresh_summary re-validates
+    // the caller may write voxels behind the library's back, now or later: the summary stays untrusted -- also across
+    // clearMap / clearBits / upload -- until gvx_map_refresh_summary
+    m->occ_valid = false;
+    m->raw_exported = true;
   }
+  if (first_voxel) *first_voxel = (uint64_t)m->z0 * m->dx * m->dy;
+  if (n_voxels) *n_voxels = m->n_voxels();
+  return GVX_OK;
+}
+int gvx_map_device_ptr_const(gvx_handle_t h, const void** data_d, uint64_t* first_voxel, uint64_t* n_voxels) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  if (data_d) *data_d = m->data;  // read-only view: the summary stays valid
   if (first_voxel) *first_voxel = (uint64_t)m->z0 * m->dx * m->dy;
   if (n_voxels) *n_voxels = m->n_voxels();
   return GVX_OK;
@@ -354,7 +377,7 @@ int gvx_map_upload(gvx_handle_t h, const void* host_buf) {
   if (m->occ) {
     // Bit: bit = !noneButEmpty; Prob: bit = occupancy >= -127, i.e. anything but UNKNOWN (-128)
     GVX_CUDA(launch_env_bitmap(lctx(), m->data, m->type, m->n_voxels(), -127, m->occ));
-    m->occ_valid = true;
+    m->revalidate();
   }
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   return GVX_OK;
@@ -367,7 +390,9 @@ int gvx_map_refresh_summary(gvx_handle_t h) {
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
   if (!m->occ) return GVX_OK;  // wrapped memory: no summary
   GVX_CUDA(launch_env_bitmap(lctx(), m->data, m->type, m->n_voxels(), -127, m->occ));
+  m->raw_exported = false;  // the caller declares its direct writes finished
   m->occ_valid = true;
+  m->fallback_logged = false;
   return GVX_OK;
 }
 
@@ -628,7 +653,7 @@ int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32
   if (rc) return rc;
   GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
                                   mark != 0, false, nullptr,
-                                  g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
+                                  summary_for_collide(a), summary_for_collide(b)));
   if (count) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
     *count = g.result_h->count;
@@ -648,7 +673,7 @@ int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const
   if (count_d) c.result_hmap_d = nullptr;  // the result stays on the device: nothing is written to mapped host memory
   GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
                                   mark != 0, false, (unsigned long long*)count_d,
-                                  g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
+                                  summary_for_collide(a), summary_for_collide(b)));
   return GVX_OK;
 }
 
@@ -685,7 +710,9 @@ int gvx_peer_mailbox_connect(int rank, int world, const void* all_handles) {
   }
   g.peer_rank = rank;
   g.peer_world = world;
-  g.peer_epoch = 0;
+  // the epoch is NOT reset: the mailbox (allocated once per process) keeps the 16-bit tags of the previous session and
+  // a count restarted at 0 would match them after a disconnect + connect. Ranks of one session issue the same
+  // collectives, so they all hold the same epoch and simply continue the sequence.
   return GVX_OK;
 }
 
@@ -712,7 +739,7 @@ int gvx_collide_map_map_allreduce(gvx_handle_t ha, gvx_handle_t hb, float thr, i
   if (!count && count_d) c.result_hmap_d = nullptr;  // device-only result
   GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, 0,
                                   float_to_probability(thr), mark != 0, false, (unsigned long long*)count_d,
-                                  g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
+                                  summary_for_collide(a), summary_for_collide(b)));
   if (count) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
     *count = g.result_h->count;
@@ -728,9 +755,11 @@ int gvx_collide_map_map_any(gvx_handle_t ha, gvx_handle_t hb, float thr, int* fl
   int64_t off, i0, i1;
   int rc = collide_prepare(ha, hb, nullptr, &a, &b, &off, &i0, &i1);
   if (rc) return rc;
-  GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, 0, float_to_probability(thr),
+  LaunchCtx c = lctx();
+  c.any = true;  // the kernels leave as soon as one CTA has found a collision; the count is then a lower bound
+  GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, 0, float_to_probability(thr),
                                   false, false, nullptr,
-                                  g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
+                                  summary_for_collide(a), summary_for_collide(b)));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   if (flag) *flag = g.result_h->count != 0;
   return GVX_OK;
@@ -748,7 +777,7 @@ int gvx_collide_map_map_types(gvx_handle_t ha, gvx_handle_t hb, float thr, int m
     return fail(GVX_ERR_UNSUPPORTED, "collideWithTypes is implemented for BitVectorVoxelMap x ProbVoxelMap");
   GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, 0, float_to_probability(thr),
                                   mark != 0, true, nullptr,
-                                  g.use_summary ? a->occ_if_valid() : nullptr, g.use_summary ? b->occ_if_valid() : nullptr));
+                                  summary_for_collide(a), summary_for_collide(b)));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   if (count) *count = g.result_h->count;
   if (mask_inout32) {
@@ -776,7 +805,7 @@ int gvx_collide_map_map_bitcheck(gvx_handle_t ha, gvx_handle_t hb, uint32_t marg
   if (high >= 32 + margin) return fail(GVX_ERR_INVALID, "sv_offset %u shifts the 64-bit window by 64 or more", sv_offset);
   // candidate filters: `other` contributes only swept-volume bits, a subset of its occupancy summary; `this` also
   // contributes bits 0..3, and eBVM_FREE (not in the summary) reaches a swept-volume bit when margin + high >= 4
-  const uint32_t* occ_b = g.use_summary ? b->occ_if_valid() : nullptr;
+  const uint32_t* occ_b = summary_for_collide(b);
   const uint32_t* occ_a = (g.use_summary && occ_b && margin + high < 4) ? a->occ_if_valid() : nullptr;
   GVX_CUDA(launch_collide_bitcheck(lctx(), a->data, b->data, i1 - i0, margin, sv_offset, mark != 0, occ_a, occ_b,
                                    a->occ_valid ? a->occ : nullptr, nullptr));
@@ -797,7 +826,7 @@ int gvx_map_shift_sv_ids(gvx_handle_t h, uint32_t shift) {
   if (m->type != kMapBit) return fail(GVX_ERR_UNSUPPORTED, "shiftLeftSweptVolumeIDs needs a BitVectorVoxelMap");
   if (shift > 56) return fail(GVX_ERR_INVALID, "Maximum shift size is 56! Higher shift number requested. Not performing shift operation.");
   GVX_CUDA(launch_shift_sv_ids(lctx(), m->data, m->n_voxels(), shift, m->occ));
-  if (m->occ) m->occ_valid = true;  // the kernel re-derives every summary word
+  m->revalidate();  // the kernel re-derives every summary word
   return GVX_OK;
 }
 

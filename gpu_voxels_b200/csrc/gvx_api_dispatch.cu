@@ -86,7 +86,8 @@ int gvx_peer_dispatch_connect(int rank, int world, const void* all_handles) {
   }
   g.disp_rank = rank;
   g.disp_world = world;
-  g.disp_epoch = 0;
+  // disp_epoch continues (it restarts only with a fresh, zeroed allocation in dispatch_alloc): ready[] tags and ack[]
+  // credits of the previous session are still in the heads, and a restarted count would match them
   g.disp_connected = true;
   return GVX_OK;
 }
@@ -136,7 +137,7 @@ int gvx_update_logodds_dispatch(gvx_handle_t h, const float* xyz_sensor, uint64_
   }
   if (z_bounds[0] != 0 || z_bounds[world] != m->dz || z_bounds[g.disp_rank] != m->z0 || z_bounds[g.disp_rank + 1] != m->z1)
     return fail(GVX_ERR_DIM_MISMATCH, "z_bounds do not describe this map: rank %d holds [%u, %u) of %u", g.disp_rank, m->z0, m->z1, m->dz);
-  if ((uint64_t)m->dx * m->dy * widest > 0xFFFFFFFFull)
+  if ((uint64_t)m->dx * m->dy * widest > (1ull << 32))  // slab-local indices 0 .. 2^32 - 1
     return fail(GVX_ERR_UNSUPPORTED, "a slab of more than 2^32 voxels does not fit the 32-bit dispatch entries");
   for (int r = 0; r < world; ++r) pd.base[r] = g.disp_ptr[r];
   pd.capacity = g.disp_capacity;

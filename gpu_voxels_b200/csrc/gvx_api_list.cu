@@ -158,7 +158,7 @@ int list_collide(int mode, gvx_handle_t hl, gvx_handle_t hm, float thr, const in
   GVX_CUDA(launch_collide_list_map(lctx(), mode, a.l->ids[a.l->cur], a.l->voxels[a.l->cur], a.l->size, a.m->data,
                                    a.m->type, a.m->n_total(), (uint64_t)a.m->z0 * a.m->dx * a.m->dy, a.m->n_voxels(),
                                    float_to_probability(thr), thr, a.off, mark != 0, mk, nullptr,
-                                   g.use_summary ? a.m->occ_if_valid() : nullptr));
+                                   summary_for_collide(a.m)));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   if (count) *count = g.result_h->count;
   if (mode == 1 && mask_out32) memcpy(mask_out32, g.result_h->mask, 32);  // cleared first, BitVoxelList.hpp:163
@@ -397,7 +397,7 @@ int gvx_collide_list_map_async(gvx_handle_t hl, gvx_handle_t hm, float thr, cons
                                    a.m->type, a.m->n_total(), (uint64_t)a.m->z0 * a.m->dx * a.m->dy, a.m->n_voxels(),
                                    float_to_probability(thr), thr, a.off, mark != 0, nullptr,
                                    (unsigned long long*)count_d,
-                                   g.use_summary ? a.m->occ_if_valid() : nullptr));
+                                   summary_for_collide(a.m)));
   return GVX_OK;
 }
 
@@ -412,7 +412,7 @@ int gvx_collide_list_map_allreduce(gvx_handle_t hl, gvx_handle_t hm, float thr, 
   GVX_CUDA(launch_collide_list_map(lctx_allreduce(), 0, a.l->ids[a.l->cur], a.l->voxels[a.l->cur], a.l->size, a.m->data,
                                    a.m->type, a.m->n_total(), (uint64_t)a.m->z0 * a.m->dx * a.m->dy, a.m->n_voxels(),
                                    float_to_probability(thr), thr, 0, mark != 0, nullptr, (unsigned long long*)count_d,
-                                   g.use_summary ? a.m->occ_if_valid() : nullptr));
+                                   summary_for_collide(a.m)));
   if (count) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
     *count = g.result_h->count;

@@ -33,10 +33,23 @@ __device__ __forceinline__ BitVoxelWords load_bit(const uint8_t* p) {
   return ld_voxel_stream(p);
 }
 
+// Early exit of the boolean collisionCheck (kernelCollideVoxelMaps, GV/voxelmap/kernels/VoxelMapOperations.hpp:78-120:
+// any-collision flag, no write-back): the first thread that counts a collision raises ReduceScratch::any_flag, every
+// thread looks at it once per loop iteration and leaves. The count that reaches finish_block is then a lower bound
+// (> 0 iff there is a collision), which is all gvx_collide_map_map_any reports. The last CTA lowers the flag again.
+__device__ __forceinline__ bool any_raised(const ReduceScratch* s) {
+  unsigned int v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(&s->any_flag) : "memory");
+  return v != 0u;
+}
+__device__ __forceinline__ void any_raise(ReduceScratch* s) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(&s->any_flag), "r"(1u) : "memory");
+}
+
 // ---- generic kernel: one voxel per thread per step, at least one side is a BitVectorVoxel map (or an
 // unaligned Prob x Prob fallback). AT/BT are MapType values. DefaultCollider::collide semantics
 // (GV/voxel/DefaultCollider.hpp:51-80); TYPES adds SVCollider's mask |= a (GV/voxel/SVCollider.hpp:96-106).
-template <int AT, int BT, bool MARK, bool TYPES>
+template <int AT, int BT, bool MARK, bool TYPES, bool ANY = false>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 k_collide_voxelwise(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long long i_begin, long long i_end,
                     long long off, int thr, ReduceScratch* scratch, ResultBlock* out_d, ResultBlock* out_h,
@@ -46,6 +59,10 @@ k_collide_voxelwise(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long
   uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const long long stride = (long long)gridDim.x * kThreads * U;
   for (long long base = i_begin + (long long)blockIdx.x * kThreads * U; base < i_end; base += stride) {
+    if (ANY) {
+      if (cnt) { any_raise(scratch); break; }
+      if (any_raised(scratch)) break;
+    }
     BitVoxelWords va[U], vb[U];
     int pa[U], pb[U];
     bool ok[U];
@@ -82,12 +99,13 @@ k_collide_voxelwise(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long
       }
     }
   }
+  if (ANY && cnt) any_raise(scratch);
   finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
 }
 
 // ---- Prob x Prob, 16 voxels per 128-bit load. Requires (a + off) and b 16-byte aligned for i % 16 == 0.
 // Byte-wise signed >= via the SIMD video instructions; popcount of the 0xFF lanes / 8.
-template <bool MARK>
+template <bool MARK, bool ANY = false>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long long i_begin, long long i_end,
                     long long off, int thr, ReduceScratch* scratch, ResultBlock* out_d, ResultBlock* out_h,
@@ -98,7 +116,7 @@ k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long l
   const long long vb = (i_begin + 15) & ~15ll, ve = i_end & ~15ll;
   if (blockIdx.x == 0) {  // unaligned head and tail, at most 30 voxels
     const long long head = (vb < i_end ? vb : i_end) - i_begin;
-    const long long tail = ve > vb ? i_end - ve : 0;
+    const long long tail = ve >= vb ? i_end - ve : 0;  // ve == vb: an empty aligned middle still has a tail
     for (long long k = threadIdx.x; k < head + tail; k += kThreads) {
       const long long i = k < head ? i_begin + k : ve + (k - head);
       const int pa = a[i + off], pb = b[i];
@@ -113,6 +131,10 @@ k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long l
   const uint4* bv = reinterpret_cast<const uint4*>(b + vb);
   const long long stride = (long long)gridDim.x * kThreads * kUnroll;
   for (long long base = (long long)blockIdx.x * kThreads * kUnroll; base < nvec; base += stride) {
+    if (ANY) {
+      if (cnt) { any_raise(scratch); break; }
+      if (any_raised(scratch)) break;
+    }
     uint4 xa[kUnroll], xb[kUnroll];
     bool ok[kUnroll];
 #pragma unroll
@@ -145,6 +167,7 @@ k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long l
         *reinterpret_cast<uint4*>(a + vb + off + (v << 4)) = make_uint4(wa[0], wa[1], wa[2], wa[3]);
     }
   }
+  if (ANY && cnt) any_raise(scratch);
   finish_block<false>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
 }
 
@@ -256,7 +279,7 @@ __device__ __forceinline__ void resolve_entry(uint8_t* __restrict__ a, const uin
 // loads into the streaming loop of one lane while its 31 neighbours wait. Each warp appends them to a small queue in
 // shared memory and resolves 32 at a time, one per lane, all loads in flight together.
 constexpr int kQueuePerWarp = 64;
-template <int AT, int BT, bool MARK, bool TYPES>
+template <int AT, int BT, bool MARK, bool TYPES, bool ANY = false>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const uint32_t* __restrict__ occ_a,
                    const uint32_t* __restrict__ occ_b, long long n, int thr, ReduceScratch* scratch, ResultBlock* out_d,
@@ -286,6 +309,10 @@ k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const
   };
   const long long stride = (long long)gridDim.x * kThreads * U;
   for (long long base = (long long)blockIdx.x * kThreads * U; base < n_quad; base += stride) {  // CTA-uniform trip count
+    if (ANY) {  // warp-uniform exit: the loop body holds warp collectives
+      if (__any_sync(0xffffffffu, cnt != 0u)) { if (lane == 0) any_raise(scratch); break; }
+      if (__any_sync(0xffffffffu, any_raised(scratch))) break;
+    }
     uint4 ma[U], mb[U];
     bool ok[U];
 #pragma unroll
@@ -315,6 +342,7 @@ k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const
       }
     }
     while (qn >= 32) drain(32);
+    if (ANY) while (qn > 0) drain(qn < 32 ? qn : 32);  // find out now whether a candidate is a collision
   }
   while (qn > 0) drain(qn < 32 ? qn : 32);
   // up to 3 complete groups after the last quad
@@ -324,6 +352,7 @@ k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const
     if (hit) resolve_group<AT, BT, MARK, TYPES, true, true>(a, b, g, hit, t4, cnt, acc);
   }
   summary_tail<AT, BT, MARK, TYPES>(a, b, occ_a, occ_b, n, thr, cnt, acc);
+  if (ANY && cnt) any_raise(scratch);
   finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
 }
 
@@ -331,7 +360,7 @@ k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const
 // ProbabilisticVoxel side the summary bit means "known" (occupancy != UNKNOWN), a superset of "occupancy >= threshold":
 // groups with candidate bits fetch their 32 Prob bytes and apply the threshold, groups without candidates (almost
 // all of a sparse map) cost 1 bit per voxel. Without a summary the Prob side's bytes are streamed for every group.
-template <int AT, int BT, bool MARK, bool TYPES, bool ASUM, bool BSUM>
+template <int AT, int BT, bool MARK, bool TYPES, bool ASUM, bool BSUM, bool ANY = false>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const uint32_t* __restrict__ occ_a,
                   const uint32_t* __restrict__ occ_b, long long n, int thr, ReduceScratch* scratch, ResultBlock* out_d,
@@ -345,6 +374,10 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
   const long long n_full = n >> 5;  // complete 32-voxel groups
   const long long stride = (long long)gridDim.x * kThreads * U;
   for (long long base = (long long)blockIdx.x * kThreads * U; base < n_full; base += stride) {
+    if (ANY) {
+      if (cnt) { any_raise(scratch); break; }
+      if (any_raised(scratch)) break;
+    }
     uint4 alo[U], ahi[U], blo[U], bhi[U];
     uint32_t ma[U], mb[U];
     bool ok[U];
@@ -376,6 +409,7 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
     }
   }
   summary_tail<AT, BT, MARK, TYPES>(a, b, occ_a, occ_b, n, thr, cnt, acc);
+  if (ANY && cnt) any_raise(scratch);
   finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
 }
 
@@ -384,6 +418,15 @@ static cudaError_t launch_summary(const LaunchCtx& c, int grid, uint8_t* a, cons
                                   const uint32_t* occ_b, long long n, int thr, bool mark, bool types,
                                   unsigned long long* out) {
   cudaError_t err = cudaSuccess;
+  if (c.any) {  // boolean collisionCheck: no write-back, no meaning mask, early exit
+    if (ASUM && BSUM)
+      err = pdl_launch(k_collide_summary2<AT, BT, false, false, true>, grid, kThreads, c.stream, c.pdl, a, b, occ_a, occ_b, n,
+                       thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
+    else
+      k_collide_summary<AT, BT, false, false, ASUM, BSUM, true><<<grid, kThreads, 0, c.stream>>>(
+          a, b, occ_a, occ_b, n, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
+    return err != cudaSuccess ? err : cudaGetLastError();
+  }
 #define GVX_GO(M, T)                                                                                       \
   do {                                                                                                     \
     if (ASUM && BSUM)                                                                                      \
@@ -412,6 +455,11 @@ template <int AT, int BT>
 static cudaError_t launch_voxelwise(const LaunchCtx& c, int grid, uint8_t* a, const uint8_t* b, long long i0,
                                     long long i1, long long off, int thr, bool mark, bool types,
                                     unsigned long long* out) {
+  if (c.any) {
+    k_collide_voxelwise<AT, BT, false, false, true><<<grid, kThreads, 0, c.stream>>>(
+        a, b, i0, i1, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
+    return cudaGetLastError();
+  }
 #define GVX_GO(M, T) k_collide_voxelwise<AT, BT, M, T><<<grid, kThreads, 0, c.stream>>>( \
       a, b, i0, i1, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer)
   if (types) { if (mark) GVX_GO(true, true); else GVX_GO(false, true); }
@@ -432,6 +480,13 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
   // summary path (no offset, full range): every BitVectorVoxel side has a valid occupancy summary; a ProbabilisticVoxel
   // side uses its "known" summary when it has one and is streamed byte-wise otherwise (Prob x Prob needs both).
   const bool a_bit = a_type == kMapBit, b_bit = b_type == kMapBit;
+  // A ProbabilisticVoxel summary marks "known" voxels, a superset of "occupancy >= thr" only for thr >= -127. A float
+  // threshold that converts to -128 (DefaultCollider::floatToProbability truncates: thr in (-0.0079, -0.0039], or a
+  // wrapped value) makes UNKNOWN voxels collide in the reference (GV/voxel/DefaultCollider.hpp:51-80): stream those.
+  if (thr == -128) {
+    if (!a_bit) occ_a = nullptr;
+    if (!b_bit) occ_b = nullptr;
+  }
   const bool a_sum = occ_a != nullptr, b_sum = occ_b != nullptr;
   if (off == 0 && i_begin == 0 && (!a_bit || a_sum) && (!b_bit || b_sum) && (a_bit || b_bit || (a_sum && b_sum)) &&
       (((uintptr_t)a | (uintptr_t)b) & 15) == 0) {
@@ -447,7 +502,7 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
   // TMA bulk tiles "where they beat plain loads" (north_star; benchmarks/tma_probe.py): measured at 512^3,
   // Bit x Prob gains 5 % (7.15 vs 6.79 TB/s, tiles of 1024 voxels x 3 stages), Prob x Bit and Bit x Bit do not
   // (7.08 vs 7.15, 7.20 vs 7.23 TB/s) -- so auto (-1) feeds only Bit x Prob through TMA; k > 0 forces shape k everywhere.
-  if (c.tma != 0 && collide_tma_applicable(a, a_type, b, b_type, i_begin, off, types) &&
+  if (!c.any && c.tma != 0 && collide_tma_applicable(a, a_type, b, b_type, i_begin, off, types) &&
       (c.tma > 0 || (a_bit && !b_bit && n >= (1ll << 22)))) {
     LaunchCtx ct = c;
     if (ct.tma < 0) ct.tma = 2;
@@ -457,7 +512,8 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
     const bool aligned = ((off & 15) == 0) && (((uintptr_t)a & 15) == 0) && (((uintptr_t)b & 15) == 0);
     if (aligned) {
       const int grid = balanced_grid((n / 16 + kThreads * kUnroll - 1) / (kThreads * kUnroll), max_grid);
-      if (mark) k_collide_prob_prob<true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
+      if (c.any) k_collide_prob_prob<false, true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
+      else if (mark) k_collide_prob_prob<true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
       else k_collide_prob_prob<false><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
       return cudaGetLastError();
     }

@@ -27,6 +27,11 @@ struct Map {
   // handed out.
   uint32_t* occ = nullptr;
   bool occ_valid = false;
+  // the writable raw device pointer has been handed out (gvx_map_device_ptr): the caller may write voxels at any time,
+  // so NO library call re-validates the summary until gvx_map_refresh_summary says the writes are over
+  bool raw_exported = false;
+  void revalidate() { if (occ && !raw_exported) occ_valid = true; }
+  bool fallback_logged = false;
   size_t occ_bytes() const { return ((n_voxels() + 31) / 32 + 3) / 4 * 16; }  // padded to 16 B
   uint32_t* occ_if_valid() const { return occ_valid ? occ : nullptr; }
   uint64_t n_voxels() const { return (uint64_t)dx * dy * (z1 - z0); }
@@ -68,6 +73,7 @@ struct Context {
   ResultBlock* result_hmap_d = nullptr;  // device alias of result_h
   // staging: device buffer for host point clouds, pinned + device buffers for small descriptors
   void* stage_d = nullptr; size_t stage_cap = 0;
+  cudaEvent_t stage_ev = nullptr;  // "the H2D copy out of a page-locked GVX_MEM_HOST buffer is done"
   // GVX_MEM_HOST_PINNED: two device slots filled on a copy stream; ready = "slot holds the cloud" (copy stream),
   // consumed = "everything that read the slot has been enqueued before this mark" (main stream)
   cudaStream_t copy_stream = nullptr;
@@ -109,6 +115,7 @@ struct Context {
   int collide_tma = -1;  // GVX_OPT_COLLIDE_TMA: -1 auto (TMA where it measured faster), 0 never, 1..5 always (shape k)
   bool use_summary = true;  // GVX_OPT_USE_SUMMARY: collide kernels may read occupancy summaries instead of voxels
   uint64_t launches = 0;
+  uint64_t summary_fallbacks = 0;  // collides that streamed voxels because a library-owned map's summary was invalid
   uint64_t next_handle = 1;
   std::unordered_map<uint64_t, Map> maps;
   std::unordered_map<uint64_t, VoxList> lists;
@@ -156,6 +163,21 @@ inline LaunchCtx lctx_allreduce() {
     c.peer.epoch = ++g.peer_epoch;
   }
   return c;
+}
+// the summary a collide may use for map m; counts (and logs once per map) the silent cliff where a library-owned map is
+// streamed only because its raw pointer was handed out and gvx_map_refresh_summary has not been called since
+inline const uint32_t* summary_for_collide(Map* m) {
+  if (!g.use_summary) return nullptr;
+  if (m->occ && !m->occ_valid) {
+    ++g.summary_fallbacks;
+    if (!m->fallback_logged) {
+      m->fallback_logged = true;
+      fprintf(stderr, "[gvx] collide streams the voxels of a %ux%ux%u map: its summary is invalid since the raw device "
+                      "pointer was handed out (gvx_map_device_ptr); call gvx_map_refresh_summary after writing\n",
+              m->dx, m->dy, m->dz);
+    }
+  }
+  return m->occ_if_valid();
 }
 inline Map* find_map(gvx_handle_t h) {
   auto it = g.maps.find(h);
@@ -253,7 +275,19 @@ inline int points_to_device(const float* xyz, uint64_t n, int mem_kind, const fl
   if (mem_kind != GVX_MEM_HOST) return fail(GVX_ERR_INVALID, "bad mem_kind %d", mem_kind);
   int rc = ensure_stage(bytes);
   if (rc) return rc;
-  if (bytes) GVX_CUDA(cudaMemcpyAsync(g.stage_d, xyz, bytes, cudaMemcpyHostToDevice, g.stream));
+  if (bytes) {
+    GVX_CUDA(cudaMemcpyAsync(g.stage_d, xyz, bytes, cudaMemcpyHostToDevice, g.stream));
+    // GVX_MEM_HOST promises "consumed or staged when the call returns". From pageable memory the runtime has staged the
+    // bytes when cudaMemcpyAsync returns; from page-locked memory (cudaHostAlloc / cudaHostRegister / torch pinned) the
+    // DMA reads the caller's buffer later, so wait for it here. Callers that want the overlap say GVX_MEM_HOST_PINNED.
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, xyz) != cudaSuccess) { cudaGetLastError(); at.type = cudaMemoryTypeUnregistered; }
+    if (at.type == cudaMemoryTypeHost) {
+      if (!g.stage_ev) GVX_CUDA(cudaEventCreateWithFlags(&g.stage_ev, cudaEventDisableTiming));
+      GVX_CUDA(cudaEventRecord(g.stage_ev, g.stream));
+      GVX_CUDA(cudaEventSynchronize(g.stage_ev));
+    }
+  }
   *out_d = (const float*)g.stage_d;
   return GVX_OK;
 }

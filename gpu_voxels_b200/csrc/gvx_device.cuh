@@ -147,6 +147,9 @@ struct ReduceScratch {
   uint32_t mask[8];          // OR of the CTAs' meaning masks; same protocol
   unsigned int ticket;       // k_insert's flag protocol: atomicInc wraps to 0 when the last CTA arrives
   unsigned int flag_accum;
+  unsigned int any_flag;     // early exit of the boolean collisionCheck: raised by the first CTA that finds a collision,
+                             // lowered by the last CTA of that launch (finish_block)
+  unsigned int pad_[3];
 };
 
 }  // namespace gvx

@@ -104,7 +104,7 @@ k_insert(MapView m, const float* __restrict__ xyz, unsigned long long n, int mea
 }
 
 __global__ void __launch_bounds__(kInsThreads)
-k_transform(const float* __restrict__ in, float* __restrict__ out, unsigned long long n, const Affine12 Mv) {
+k_transform(const float* in, float* out, unsigned long long n, const Affine12 Mv) {  // in == out is allowed
   const float* M = Mv.a;
   const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads;
   for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n; i += stride) {

@@ -16,6 +16,7 @@ struct LaunchCtx {
   PeerReduce peer;            // world <= 1: no fused all-reduce
   int tma = 0;                // GVX_OPT_COLLIDE_TMA: -1 auto, 0 never, k > 0 = TMA bulk tiles of shape k for every pair
   bool pdl = false;           // GVX_OPT_PDL: programmatic dependent launch for the per-step kernels (pdl_launch)
+  bool any = false;           // boolean collisionCheck: kernels leave as soon as any CTA has found a collision
 };
 
 // Programmatic dependent launch. A kernel started through pdl_launch with pdl = true may become resident while the

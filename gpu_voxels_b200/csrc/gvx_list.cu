@@ -295,6 +295,11 @@ cudaError_t launch_collide_list_map(const LaunchCtx& c, int mode, const uint32_t
                                     const uint32_t mask_in8[8], unsigned long long* count_out_d, const uint32_t* occ) {
   BitVoxelWords mk;
   for (int k = 0; k < 8; ++k) mk.w[k] = mask_in8 ? mask_in8[k] : 0u;
+  // "known" is a superset of "occupied at the threshold" only while UNKNOWN (-128) fails the test: DefaultCollider's
+  // int8 threshold -128 (modes 0/3) or a raw float threshold <= -128 (modes 1/2, GV/voxel/ProbabilisticVoxel.hpp:94-98)
+  // make UNKNOWN voxels collide in the reference -- read the bytes then
+  if (map_type == kMapProb && (((mode == 0 || mode == 3) && thr_i == -128) || ((mode == 1 || mode == 2) && thr_f <= -128.0f)))
+    occ = nullptr;
   unsigned long long work = (size + kThreads * 8 - 1) / (kThreads * 8);
   const unsigned long long max_grid = (unsigned long long)(c.sm_count * 4 < kMaxGrid ? c.sm_count * 4 : kMaxGrid);
   const int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));

@@ -84,6 +84,7 @@ __device__ __forceinline__ bool finish_block(uint32_t my_count, const uint32_t (
     if (sh_last) {
       sh_tot = (old & (kTicketOne - 1ull)) + c;
       s->total = 0ull;  // nobody else arrives in this launch; the next launch starts behind a kernel boundary
+      s->any_flag = 0u; // every CTA has left its loop: nobody reads or raises the early-exit flag any more
       if (TYPES) __threadfence();
     }
   }

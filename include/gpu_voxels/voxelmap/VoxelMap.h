@@ -85,7 +85,7 @@ public:
   float getVoxelSideLength() const { return m_voxel_side_length; }
   uint32_t getVoxelMapSize() const { return m_dim.x * m_dim.y * m_dim.z; }
   void* getVoidDeviceDataPtr() { void* p = NULL; gvx_map_device_ptr(m_handle, &p, NULL, NULL); return p; }
-  const void* getConstVoidDeviceDataPtr() const { void* p = NULL; gvx_map_device_ptr(m_handle, &p, NULL, NULL); return p; }
+  const void* getConstVoidDeviceDataPtr() const { const void* p = NULL; gvx_map_device_ptr_const(m_handle, &p, NULL, NULL); return p; }
   virtual gvx_handle_t getHandle() const { return m_handle; }
 
   // GV/voxelmap/AbstractVoxelMap.h:60-66, .cu:23-33; BitVoxelMap.hpp:220-226, ProbVoxelMap.hpp:104-108

@@ -62,7 +62,10 @@ enum gvx_meaning {
 };
 
 enum gvx_mem_kind {
-  GVX_MEM_HOST = 0,   /* any host memory; the call has consumed or staged it when it returns */
+  GVX_MEM_HOST = 0,   /* any host memory; the call has consumed or staged it when it returns (for page-locked memory the
+                       * call waits for the upload; say GVX_MEM_HOST_PINNED to keep it asynchronous) */
+  /* device memory, read by kernels on the library's stream (gvx_set_stream): the data must be complete in that
+   * stream's order -- produced on the same stream, or the producing stream synchronised / joined by an event first */
   GVX_MEM_DEVICE = 1,
   /* page-locked host memory that the caller leaves untouched until the work has completed (gvx_sync, a synchronous call,
    * or an event of its own on the stream): the upload runs on a separate copy stream into one of two device staging
@@ -82,10 +85,16 @@ const char* gvx_last_error(void);
 /* cudaStream_t to enqueue on (NULL = the library's own non-blocking stream). */
 int gvx_set_stream(void* cuda_stream);
 int gvx_sync(void);
+/* Everything enqueued by later calls waits for cuda_event (a cudaEvent_t recorded on ANOTHER stream): how a
+ * GVX_MEM_DEVICE buffer produced on the caller's stream is ordered before the kernels that read it. */
+int gvx_wait_event(void* cuda_event);
 /* getDeviceInfos / getDeviceMemoryInfo (GV/helpers/cuda_handling.cu:66-149) */
 int gvx_device_info(int* sm_count, uint64_t* free_bytes, uint64_t* total_bytes, char* name64);
 /* number of kernels this library has launched since gvx_init (bench.py reports it as gpu_launches) */
 uint64_t gvx_launch_count(void);
+/* number of collide calls that streamed the voxels of a library-owned map only because its summary was invalid (raw
+ * pointer handed out and gvx_map_refresh_summary not called since); the first one per map also warns on stderr */
+uint64_t gvx_summary_fallback_count(void);
 
 /* cudaLimitMaxL2FetchGranularity (32 / 64 / 128 bytes; 0 = query only): how much DRAM the L2 fetches around a missing
  * 32-byte sector. The gather kernels (list x map, random inserts) touch one sector per access. */
@@ -123,6 +132,9 @@ int gvx_map_clear_meaning(gvx_handle_t h, int meaning);
 int gvx_map_clear_bits(gvx_handle_t h, const uint8_t mask32[GVX_BITVOXEL_BYTES]);
 /* getDeviceDataPtr / getVoidDeviceDataPtr, getDimensions, getVoxelSideLength, getMemoryUsage */
 int gvx_map_device_ptr(gvx_handle_t h, void** data_d, uint64_t* first_voxel, uint64_t* n_voxels);
+/* getConstVoidDeviceDataPtr / getConstDeviceDataPtr: a read-only view; unlike gvx_map_device_ptr it leaves the map's
+ * summary valid */
+int gvx_map_device_ptr_const(gvx_handle_t h, const void** data_d, uint64_t* first_voxel, uint64_t* n_voxels);
 int gvx_map_info(gvx_handle_t h, int* map_type, uint32_t dims3[3], float* side, uint32_t* z0, uint32_t* z1,
                  uint64_t* bytes);
 /* raw voxel bytes of this process's slab, reference layout (the payload of writeToDisk/readFromDisk,
@@ -134,8 +146,9 @@ int gvx_map_upload(gvx_handle_t h, const void* host_buf);
  * set" (BitVector::noneButEmpty negated, GV/helpers/BitVector.h:183-198), 1/256 of the map's size, kept in sync by
  * every mutating call of this API. Collision kernels read it instead of the 32-byte voxels whenever occupancy is all
  * they need; results are identical. Handing out the raw device pointer (gvx_map_device_ptr with data_d != NULL)
- * invalidates it, because the caller may then write voxels directly: call gvx_map_refresh_summary afterwards
- * (one streaming pass) or the kernels fall back to reading the voxels. Wrapped maps have no summary. */
+ * invalidates it, because the caller may then write voxels directly -- and keeps it invalid across every later call
+ * (clearMap included) until gvx_map_refresh_summary (one streaming pass) declares the direct writes finished; until
+ * then the kernels read the voxels. gvx_map_device_ptr_const does not invalidate. Wrapped maps have no summary. */
 int gvx_map_refresh_summary(gvx_handle_t h);
 /* test / debug: the summary words of this process's slab (bit i&31 of word i>>5 = voxel i) and whether it is valid */
 int gvx_map_summary_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, int* valid);
