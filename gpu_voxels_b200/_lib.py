@@ -80,6 +80,7 @@ SIGNATURES = {
     "gvx_list_device_ptrs": (C.c_int, [u64, P(vp), P(vp), P(vp), P(u64)]),
     "gvx_collide_list_map": (C.c_int, [u64, u64, f32, vp, C.c_int, P(u64)]),
     "gvx_collide_list_map_async": (C.c_int, [u64, u64, f32, vp, C.c_int, vp]),
+    "gvx_collide_list_map_per_meaning_async": (C.c_int, [u64, u64, f32, vp, C.c_int, vp]),
     "gvx_collide_list_map_types": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),
     "gvx_collide_list_map_mask": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),
     "gvx_collide_list_map_per_meaning": (C.c_int, [u64, u64, f32, vp, C.c_int, vp, P(u64)]),

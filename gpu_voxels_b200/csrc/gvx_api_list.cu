@@ -89,6 +89,7 @@ int list_insert(VoxList& l, const float* xyz_d, uint64_t n, const MetaDesc& meta
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   l.size = g.result_h->count;
   l.cur = nxt;
+  ++l.version;
   return GVX_OK;
 }
 
@@ -121,6 +122,7 @@ int list_merge(VoxList& l, const VoxList& o, const int32_t off3[3], int new_mean
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   l.size = g.result_h->count;
   l.cur = nxt;
+  ++l.version;
   return GVX_OK;
 }
 
@@ -136,6 +138,43 @@ int list_collide_prepare(gvx_handle_t hl, gvx_handle_t hm, const int32_t off3[3]
   if (a->l->dx != a->m->dx || a->l->dy != a->m->dy || a->l->dz != a->m->dz)
     return fail(GVX_ERR_DIM_MISMATCH, "list and map have different reference dimensions");
   a->off = off3 ? (int64_t)off3[2] * a->m->dx * a->m->dy + (int64_t)off3[1] * a->m->dx + (int64_t)off3[0] : 0;
+  return GVX_OK;
+}
+
+// Entries [i0, i1) of the sorted id array whose map voxel id + off lies inside the map's z-slab ("list ids
+// are sorted, so shard boundaries are two binary searches"): a rank then reads size / world ids instead of all of them.
+// Whole maps: the full list (the kernel's range test handles offsets). One tiny kernel + one sync per (list contents,
+// slab, offset), then cached.
+int list_slab_range(VoxList& l, const Map& m, int64_t off, uint64_t* i0, uint64_t* i1) {
+  *i0 = 0; *i1 = l.size;
+  if (!m.sharded() || l.size == 0) return GVX_OK;
+  const int64_t first = (int64_t)m.z0 * m.dx * m.dy, end = first + (int64_t)m.n_voxels();
+  // id + off in [first, end)  <=>  id in [first - off, end - off), clamped to the uint32 id range
+  const int64_t lo_s = first - off, hi_s = end - off;
+  const uint64_t lo = lo_s < 0 ? 0 : (uint64_t)lo_s, hi = hi_s < 0 ? 0 : (uint64_t)hi_s;
+  if (!l.ids_exported && l.range.version == l.version && l.range.lo == lo && l.range.hi == hi) {
+    *i0 = l.range.i0; *i1 = l.range.i1;
+    return GVX_OK;
+  }
+  GVX_CUDA(launch_list_bounds(lctx(), l.ids[l.cur], l.size, lo, hi));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  *i0 = g.result_h->count;
+  *i1 = g.result_h->per_meaning[0];
+  if (*i1 < *i0) *i1 = *i0;
+  l.range.version = l.version; l.range.lo = lo; l.range.hi = hi; l.range.i0 = *i0; l.range.i1 = *i1;
+  return GVX_OK;
+}
+
+// the one place that launches list x map: slab range of the list, summary of the map, launch
+int list_launch(const LaunchCtx& c, int mode, const ListCollideArgs& a, float thr, bool mark, const uint32_t* mask8,
+                unsigned long long* count_d) {
+  uint64_t i0, i1;
+  int rc = list_slab_range(*a.l, *a.m, a.off, &i0, &i1);
+  if (rc) return rc;
+  GVX_CUDA(launch_collide_list_map(c, mode, a.l->ids[a.l->cur] + i0, a.l->voxels[a.l->cur] + i0 * kBitVoxelBytes, i1 - i0,
+                                   a.m->data, a.m->type, a.m->n_total(), (uint64_t)a.m->z0 * a.m->dx * a.m->dy,
+                                   a.m->n_voxels(), float_to_probability(thr), thr, a.off, mark, mask8, count_d,
+                                   summary_for_collide(a.m)));
   return GVX_OK;
 }
 
@@ -155,10 +194,7 @@ int list_collide(int mode, gvx_handle_t hl, gvx_handle_t hm, float thr, const in
     if (mode == 3 && counts256) memset(counts256, 0, 256 * sizeof(uint64_t));
     return GVX_OK;
   }
-  GVX_CUDA(launch_collide_list_map(lctx(), mode, a.l->ids[a.l->cur], a.l->voxels[a.l->cur], a.l->size, a.m->data,
-                                   a.m->type, a.m->n_total(), (uint64_t)a.m->z0 * a.m->dx * a.m->dy, a.m->n_voxels(),
-                                   float_to_probability(thr), thr, a.off, mark != 0, mk, nullptr,
-                                   summary_for_collide(a.m)));
+  if ((rc = list_launch(lctx(), mode, a, thr, mark != 0, mk, nullptr))) return rc;
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   if (count) *count = g.result_h->count;
   if (mode == 1 && mask_out32) memcpy(mask_out32, g.result_h->mask, 32);  // cleared first, BitVoxelList.hpp:163
@@ -239,6 +275,7 @@ int gvx_list_clear(gvx_handle_t h) {
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
   l->size = 0;
+  ++l->version;
   return GVX_OK;
 }
 
@@ -342,6 +379,7 @@ int gvx_list_upload(gvx_handle_t h, const uint32_t* ids, const uint32_t* coords,
   for (uint64_t i = 1; i < n; ++i)
     if (ids[i] <= ids[i - 1]) return fail(GVX_ERR_INVALID, "ids must be strictly increasing (entry %llu)", (unsigned long long)i);
   l->size = 0;
+  ++l->version;
   int rc = list_reserve(*l, l->cur, n);
   if (rc) return rc;
   if (n) {
@@ -360,7 +398,7 @@ int gvx_list_device_ptrs(gvx_handle_t h, void** ids_d, void** coords_d, void** v
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
-  if (ids_d) *ids_d = l->ids[l->cur];
+  if (ids_d) { *ids_d = l->ids[l->cur]; l->ids_exported = true; }  // the caller may rewrite ids: no range caching
   if (coords_d) *coords_d = l->coords[l->cur];
   if (voxels_d) *voxels_d = l->voxels[l->cur];
   if (size) *size = l->size;
@@ -393,11 +431,26 @@ int gvx_collide_list_map_async(gvx_handle_t hl, gvx_handle_t hm, float thr, cons
     if (count_d) GVX_CUDA(cudaMemsetAsync(count_d, 0, 8, g.stream));
     return GVX_OK;
   }
-  GVX_CUDA(launch_collide_list_map(lctx(), 0, a.l->ids[a.l->cur], a.l->voxels[a.l->cur], a.l->size, a.m->data,
-                                   a.m->type, a.m->n_total(), (uint64_t)a.m->z0 * a.m->dx * a.m->dy, a.m->n_voxels(),
-                                   float_to_probability(thr), thr, a.off, mark != 0, nullptr,
-                                   (unsigned long long*)count_d,
-                                   summary_for_collide(a.m)));
+  if ((rc = list_launch(lctx(), 0, a, thr, mark != 0, nullptr, (unsigned long long*)count_d))) return rc;
+  return GVX_OK;
+}
+
+int gvx_collide_list_map_per_meaning_async(gvx_handle_t hl, gvx_handle_t hm, float thr, const int32_t off3[3], int mark,
+                                           uint64_t* counts257_d) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  if (!counts257_d) return fail(GVX_ERR_INVALID, "null result pointer");
+  ListCollideArgs a;
+  int rc = list_collide_prepare(hl, hm, off3, &a);
+  if (rc) return rc;
+  if (a.l->size == 0) {
+    GVX_CUDA(cudaMemsetAsync(counts257_d, 0, 257 * sizeof(uint64_t), g.stream));
+    return GVX_OK;
+  }
+  LaunchCtx c = lctx();
+  c.result_hmap_d = nullptr;  // the result stays on the device
+  if ((rc = list_launch(c, 3, a, thr, mark != 0, nullptr, (unsigned long long*)counts257_d))) return rc;
+  GVX_CUDA(cudaMemcpyAsync(counts257_d + 1, g.result_d->per_meaning, 256 * sizeof(uint64_t), cudaMemcpyDeviceToDevice, g.stream));
   return GVX_OK;
 }
 
@@ -409,10 +462,7 @@ int gvx_collide_list_map_allreduce(gvx_handle_t hl, gvx_handle_t hm, float thr, 
   int rc = list_collide_prepare(hl, hm, nullptr, &a);
   if (rc) return rc;
   // an empty list still has to take part in the collective: launch with size 0
-  GVX_CUDA(launch_collide_list_map(lctx_allreduce(), 0, a.l->ids[a.l->cur], a.l->voxels[a.l->cur], a.l->size, a.m->data,
-                                   a.m->type, a.m->n_total(), (uint64_t)a.m->z0 * a.m->dx * a.m->dy, a.m->n_voxels(),
-                                   float_to_probability(thr), thr, 0, mark != 0, nullptr, (unsigned long long*)count_d,
-                                   summary_for_collide(a.m)));
+  if ((rc = list_launch(lctx_allreduce(), 0, a, thr, mark != 0, nullptr, (unsigned long long*)count_d))) return rc;
   if (count) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
     *count = g.result_h->count;
@@ -441,7 +491,7 @@ int gvx_list_subtract(gvx_handle_t ha, gvx_handle_t hb) {
   int rc = list_list_prepare(ha, hb, &a, &b);
   if (rc) return rc;
   if (a->size == 0 || b->size == 0) return GVX_OK;
-  if (a == b) { a->size = 0; return GVX_OK; }
+  if (a == b) { a->size = 0; ++a->version; return GVX_OK; }
   const int nxt = a->cur ^ 1;
   if ((rc = list_reserve(*a, nxt, a->size))) return rc;
   if ((rc = list_reserve_scratch(*a, a->size, 0))) return rc;
@@ -453,6 +503,7 @@ int gvx_list_subtract(gvx_handle_t ha, gvx_handle_t hb) {
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   a->size -= g.result_h->count;  // the stencil kernel counted the overlapping entries
   a->cur = nxt;
+  ++a->version;
   return GVX_OK;
 }
 

@@ -58,6 +58,12 @@ struct VoxList {
   void* tmp = nullptr;
   size_t tmp_bytes = 0;
   uint64_t scratch_cap = 0, meaning_cap = 0;
+  // z-slab maps: the entries whose map voxel lies in a slab are ONE contiguous range of the sorted ids, found with two
+  // binary searches on the device and remembered per (list contents, slab, offset). `version` moves with every change
+  // of the entries; a list whose id array has been handed out (gvx_list_device_ptrs) is never cached.
+  uint64_t version = 1;
+  bool ids_exported = false;
+  struct { uint64_t version = 0, lo = 0, hi = 0, i0 = 0, i1 = 0; } range;
   uint64_t n_total() const { return (uint64_t)dx * dy * dz; }
 };
 

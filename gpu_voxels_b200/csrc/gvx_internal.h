@@ -127,6 +127,9 @@ cudaError_t launch_collide_list_map(const LaunchCtx& c, int mode, const uint32_t
                                     const uint32_t mask_in8[8], unsigned long long* count_out_d,
                                     const uint32_t* occ = nullptr);
 
+// i0 = lower_bound(ids, lo) -> ResultBlock::count, i1 = lower_bound(ids, hi) -> ResultBlock::per_meaning[0]
+cudaError_t launch_list_bounds(const LaunchCtx& c, const uint32_t* ids, uint64_t size, uint64_t lo, uint64_t hi);
+
 // list x list (gvx_listlist.cu): mode 0 count of common ids, 1 + OR of both voxels, 2 bit check with margin,
 // 3 per-meaning histogram of a's voxels, 4 keep_d[i] = (a's id i is NOT in b). Results in the result block.
 cudaError_t launch_list_list(const LaunchCtx& c, int mode, const uint32_t* a_ids, const void* a_vox, uint64_t na,

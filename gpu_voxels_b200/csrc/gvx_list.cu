@@ -272,11 +272,44 @@ k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxel
     __syncthreads();
   }
   const bool last = finish_block<MODE == 1>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
-  if (MODE == 3 && last) {
+  if (MODE == 3 && last && out_h) {
     __threadfence();  // acquire side of the arrival ticket: the other CTAs' histogram adds are in L2
     out_h->per_meaning[threadIdx.x] = __ldcg(&out_d->per_meaning[threadIdx.x]);
     __threadfence_system();
   }
+}
+
+// lower bounds of lo and hi in the sorted ids: lanes 0..15 search lo, lanes 16..31 search hi, 16-ary (each step narrows
+// the range 17-fold with ONE round of loads instead of a chain of dependent probes). Results: out->count = i0,
+// out->per_meaning[0] = i1 (device block and mapped host block).
+__global__ void k_list_bounds(const uint32_t* __restrict__ ids, unsigned long long size, unsigned long long lo,
+                              unsigned long long hi, ResultBlock* out_d, ResultBlock* out_h) {
+  const int lane = threadIdx.x & 31, half = lane >> 4, sub = lane & 15;
+  const unsigned long long key = half ? hi : lo;
+  unsigned long long a = 0, b = size;  // answer in [a, b]
+  while (a < b) {
+    const unsigned long long len = b - a, step = (len + 16) / 17;  // probes at a + (sub + 1) * step - 1
+    const unsigned long long pos = a + (unsigned long long)(sub + 1) * step - 1;
+    const bool valid = pos < b;
+    const bool less = valid && (unsigned long long)__ldg(ids + pos) < key;  // ids[pos] < key: the bound is right of pos
+    const unsigned m = __ballot_sync(0xffffffffu, less) >> (16 * half) & 0xFFFFu;
+    const int k = __popc(m);  // ids sorted: the probes below the bound are a prefix
+    const unsigned long long na = k ? a + (unsigned long long)k * step : a;
+    unsigned long long nb = k < 16 ? a + (unsigned long long)(k + 1) * step - 1 : b;  // nothing was probed beyond probe 15
+    if (nb > b) nb = b;
+    a = na; b = nb;
+  }
+  if (sub == 0) {
+    if (half == 0) { out_d->count = a; if (out_h) out_h->count = a; }
+    else { out_d->per_meaning[0] = a; if (out_h) out_h->per_meaning[0] = a; }
+    __threadfence_system();
+  }
+}
+
+cudaError_t launch_list_bounds(const LaunchCtx& c, const uint32_t* ids, uint64_t size, uint64_t lo, uint64_t hi) {
+  ++*c.launches;
+  k_list_bounds<<<1, 32, 0, c.stream>>>(ids, size, lo, hi, c.result_d, c.result_hmap_d);
+  return cudaGetLastError();
 }
 
 template <int MAPT, int MODE>

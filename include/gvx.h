@@ -322,6 +322,12 @@ int gvx_collide_list_map(gvx_handle_t list, gvx_handle_t map, float thr, const i
                          uint64_t* count);
 int gvx_collide_list_map_async(gvx_handle_t list, gvx_handle_t map, float thr, const int32_t off3[3], int mark,
                                uint64_t* count_d);
+/* gvx_collide_list_map_per_meaning (below) without the host round trip: counts257_d (device) receives the total in
+ * [0] and the 256 per-meaning counts in [1..256]; nothing synchronises. On z-slab maps every rank gets its slab's
+ * share -- sum the 257 words over the ranks (ncclAllReduce on the same stream: the path's one collective for
+ * BASELINE config 5; bit j of the meaning mask = count j > 0). */
+int gvx_collide_list_map_per_meaning_async(gvx_handle_t list, gvx_handle_t map, float thr, const int32_t off3[3],
+                                           int mark, uint64_t* counts257_d);
 /* BitVoxelList::collideWithTypes (GV/voxellist/BitVoxelList.hpp:127-218, kernel VoxelListOperations.hpp:182-240):
  * count + OR of the colliding list voxels; mask_out32 is cleared first (BitVoxelList.hpp:163); the map voxel is
  * tested with isOccupied(thr) on the RAW float threshold (GV/voxel/ProbabilisticVoxel.hpp:94-98) */

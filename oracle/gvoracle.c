@@ -187,6 +187,27 @@ int gvo_insert_points(uint8_t* map, int map_type, const uint32_t* dims, uint32_t
  * pose12 = row-major 3x4 [R | t] (Sensor::orientation, Sensor::position). delta = cSENSOR_MODEL_OCCUPIED (72,
  * GV/voxelmap/kernels/VoxelMapOperations.h:38-39). Sequential => no lost updates. n is the frame size
  * (the reference additionally caps at the voxel count, :569). */
+/* one sensor point -> slab-local voxel index of its hit, or -1 (NaN, outside the map, another slab) */
+static inline int64_t logodds_hit_index(const uint32_t* dims, uint32_t z0, uint32_t z1, float side, const float* M,
+                                        const float* sensor_pos, int sensor_inside, const float* raw) {
+  float w[3];
+  xform(M, raw, w);
+  if (w[2] < 0) { /* VoxelMapOperations.cu:56-64: re-project onto z=0 with a DOUBLE factor */
+    double factor = (double)((float)(sensor_pos[2] / (sensor_pos[2] - w[2])));
+    float r2[3];
+    r2[0] = (float)((double)raw[0] * factor);
+    r2[1] = (float)((double)raw[1] * factor);
+    r2[2] = (float)((double)raw[2] * factor);
+    xform(M, r2, w);
+  }
+  if (isnan(w[0]) || isnan(w[1]) || isnan(w[2])) return -1;
+  uint32_t c[3];
+  gvo_map_to_voxels(side, w, c);
+  if (!(c[0] < dims[0] && c[1] < dims[1] && c[2] < dims[2] && sensor_inside)) return -1;
+  if (!(c[2] >= z0 && c[2] < z1)) return -1;
+  return (int64_t)((uint64_t)(c[2] - z0) * dims[0] * dims[1] + (uint64_t)c[1] * dims[0] + c[0]);
+}
+
 int gvo_update_logodds(int8_t* map, const uint32_t* dims, uint32_t z0, uint32_t z1, float side,
                        const float* xyz_sensor, uint64_t n, const float* pose12, int delta) {
   float M[16];
@@ -199,25 +220,36 @@ int gvo_update_logodds(int8_t* map, const uint32_t* dims, uint32_t z0, uint32_t 
   uint64_t nvox = (uint64_t)dims[0] * dims[1] * dims[2];
   if (n > nvox) n = nvox;
   for (uint64_t i = 0; i < n; ++i) {
-    const float* raw = xyz_sensor + 3 * i;
-    float w[3];
-    xform(M, raw, w);
-    if (w[2] < 0) { /* VoxelMapOperations.cu:56-64: re-project onto z=0 with a DOUBLE factor */
-      double factor = (double)((float)(sensor_pos[2] / (sensor_pos[2] - w[2])));
-      float r2[3];
-      r2[0] = (float)((double)raw[0] * factor);
-      r2[1] = (float)((double)raw[1] * factor);
-      r2[2] = (float)((double)raw[2] * factor);
-      xform(M, r2, w);
-    }
-    if (isnan(w[0]) || isnan(w[1]) || isnan(w[2])) continue;
-    uint32_t c[3];
-    gvo_map_to_voxels(side, w, c);
-    if (c[0] < dims[0] && c[1] < dims[1] && c[2] < dims[2] && sensor_inside) {
-      if (c[2] >= z0 && c[2] < z1) {
-        uint64_t idx = (uint64_t)(c[2] - z0) * dims[0] * dims[1] + (uint64_t)c[1] * dims[0] + c[0];
-        map[idx] = prob_update(map[idx], delta);
-      }
+    const int64_t idx = logodds_hit_index(dims, z0, z1, side, M, sensor_pos, sensor_inside, xyz_sensor + 3 * i);
+    if (idx >= 0) map[idx] = prob_update(map[idx], delta);
+  }
+  return 0;
+}
+
+/* The same update as an OpenMP loop over the points on all host threads (the timed "straightforward OpenMP host loop of
+ * identical semantics" of bench.py's CPU baseline): the read-modify-write of a voxel is a compare-and-swap on its
+ * byte, so no update is lost, and equal-sign saturating adds commute (clamp is monotone), so the map is byte-identical
+ * to the sequential loop above for every thread schedule (tests/test_oracle_golden.py). */
+int gvo_update_logodds_omp(int8_t* map, const uint32_t* dims, uint32_t z0, uint32_t z1, float side,
+                           const float* xyz_sensor, uint64_t n, const float* pose12, int delta) {
+  float M[16];
+  memcpy(M, pose12, 12 * sizeof(float));
+  M[12] = 0; M[13] = 0; M[14] = 0; M[15] = 1;
+  const float sensor_pos[3] = {pose12[3], pose12[7], pose12[11]};
+  uint32_t sc[3];
+  gvo_map_to_voxels(side, sensor_pos, sc);
+  const int sensor_inside = sc[0] < dims[0] && sc[1] < dims[1] && sc[2] < dims[2];
+  uint64_t nvox = (uint64_t)dims[0] * dims[1] * dims[2];
+  if (n > nvox) n = nvox;
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < (int64_t)n; ++i) {
+    const int64_t idx = logodds_hit_index(dims, z0, z1, side, M, sensor_pos, sensor_inside, xyz_sensor + 3 * i);
+    if (idx < 0) continue;
+    int8_t old = __atomic_load_n(&map[idx], __ATOMIC_RELAXED);
+    for (;;) {
+      const int8_t nv = prob_update(old, delta);
+      if (nv == old) break;
+      if (__atomic_compare_exchange_n(&map[idx], &old, nv, 1, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) break;
     }
   }
   return 0;

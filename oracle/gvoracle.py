@@ -117,11 +117,13 @@ def insert_meta(m, map_type, dims, side, xyz, cloud_sizes, meanings, transforms=
     return bool(outside.value)
 
 
-def update_logodds(m, dims, side, xyz_sensor, pose12, delta=72, z0=0, z1=None):
+def update_logodds(m, dims, side, xyz_sensor, pose12, delta=72, z0=0, z1=None, parallel=False):
+    """parallel=True: the same update as an OpenMP loop over the points (byte CAS; identical result, see gvoracle.c)"""
     z1 = dims[2] if z1 is None else z1
     xyz = _f32(xyz_sensor).reshape(-1, 3)
-    lib().gvo_update_logodds(_ptr(m), _ptr(_dims(dims)), C.c_uint32(z0), C.c_uint32(z1), C.c_float(side), _ptr(xyz),
-                             C.c_uint64(len(xyz)), _ptr(_f32(pose12).reshape(12)), int(delta))
+    fn = lib().gvo_update_logodds_omp if parallel else lib().gvo_update_logodds
+    fn(_ptr(m), _ptr(_dims(dims)), C.c_uint32(z0), C.c_uint32(z1), C.c_float(side), _ptr(xyz),
+       C.c_uint64(len(xyz)), _ptr(_f32(pose12).reshape(12)), int(delta))
 
 
 def insert_sensor_data(m, dims, side, xyz_sensor, pose12, raycast=True, robot_map=None, robot_bit=1, delta_free=-10,

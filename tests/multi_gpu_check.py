@@ -85,6 +85,36 @@ def main():
     g_tot, _, g_per = sharding.allreduce_collision_result(tot, per_meaning=per)
     w_tot, _, w_per = r_lst.collide(3, r_env, PROB, 1.0, 0, False)
     assert g_tot == w_tot and np.array_equal(g_per, w_per)
+    # the same without a host round trip: 257 words stay on the device and are summed by ONE NCCL all-reduce (bench.py C5);
+    # every rank reads only the entries of its slab (two binary searches on the sorted ids, cached per list version)
+    out_d = torch.zeros(257, dtype=torch.int64, device="cuda")
+    for it in range(3):
+        _lib.check(L.gvx_collide_list_map_per_meaning_async(lst.handle, env.handle, 1.0, None, 0, C.c_void_p(out_d.data_ptr())))
+        dist.all_reduce(out_d)
+        got = out_d.cpu().numpy().astype(np.uint64)
+        assert int(got[0]) == w_tot and np.array_equal(got[1:], w_per), (it, int(got[0]), w_tot)
+    # an offset moves the slab boundaries inside the list: ids + off must fall into the slab
+    off = (3, -2, 5)
+    lin = off[2] * dims[0] * dims[1] + off[1] * dims[0] + off[0]
+    w_off = r_lst.collide(0, r_env, PROB, 1.0, lin, False)[0]
+    c_off = lst.collideWith(env, 1.0, off, mark=False)
+    t_off = torch.tensor([c_off], dtype=torch.int64, device="cuda")
+    dist.all_reduce(t_off)
+    assert int(t_off.item()) == w_off, (int(t_off.item()), w_off)
+    lst.insertPointCloud(env_pts[:5000], 33)   # the list changes: the cached slab range must not survive
+    r_lst.insert_points(env_pts[:5000], 33)
+    l_want2 = r_lst.collide(0, r_env, PROB, 1.0, 0, False)[0]
+    host = C.c_uint64(0)
+    _lib.check(L.gvx_collide_list_map_allreduce(lst.handle, env.handle, 1.0, 0, C.byref(host), None))
+    assert host.value == l_want2 and l_want2 > l_want, (host.value, l_want2, l_want)
+    # disconnect + connect in one process must not match the stale tags of the previous session
+    _lib.check(L.gvx_peer_mailbox_disconnect())
+    dist.barrier()
+    assert sharding.connect_peer_mailboxes()
+    for it in range(3):
+        host = C.c_uint64(0)
+        _lib.check(L.gvx_collide_map_map_allreduce(rob.handle, env.handle, 1.0, 0, C.byref(host), None))
+        assert host.value == want, ("after reconnect", it, host.value, want)
     # batch split over ranks (environment replicated)
     full_env = gv.BitVectorVoxelMap(dims, side)
     full_env.insertPointCloud(env_pts, 1)
@@ -139,6 +169,23 @@ def main():
         d_env.insertSensorDataDispatch(frames[rank][: 1000 * (1 + (step + rank) % 7)], poses[rank], zb)
     _lib.check(L.gvx_sync())
     d_env.insertSensorDataDispatch(frames[rank][:0], poses[rank], zb)   # reports a time-out of the run above, if any
+    _lib.check(L.gvx_sync())
+    _lib.check(L.gvx_peer_dispatch_disconnect())
+    dist.barrier()
+    # a second dispatch session in the same process (same world and capacity: the allocation, its ready[] tags
+    # and ack[] credits are reused) -- 3 more frames on top of the 6 + 26 of the first session
+    assert sharding.connect_peer_dispatch(n_max)
+    d2, o2 = gv.ProbVoxelMap(dims, side, slab=slab), orc.new_map(PROB, dims)
+    for step in range(3):
+        for r in range(world):
+            fr = np.random.Generator(np.random.PCG64(5000 + 17 * step + r))
+            pts = fr.uniform(-0.5, 0.5, size=(20000 + 1000 * r, 3)).astype(np.float32)
+            pose = np.eye(4, dtype=np.float32)[:3].copy()
+            pose[:, 3] = (0.5, 0.4, 0.05 + 0.9 * (r + 0.5) / world)
+            if r == rank:
+                d2.insertSensorDataDispatch(pts, pose, zb)
+            orc.update_logodds(o2, dims, side, pts, pose)
+    assert np.array_equal(d2.download(), o2[first:first + n_loc]), "dispatch after a reconnect differs from the oracle"
     _lib.check(L.gvx_sync())
     _lib.check(L.gvx_peer_dispatch_disconnect())
     dist.barrier()

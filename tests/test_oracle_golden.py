@@ -244,3 +244,29 @@ def test_list_list_bitshift_collision_and_subtract(oracle):
     l2.insert_points(oracle.create_box_of_points((2.1, 2.1, 2.1), (4.9, 4.9, 4.9), 0.1), 12)
     oracle.list_subtract(l1, l2)
     assert len(l1) == 19
+
+
+def test_update_logodds_openmp_loop_equals_the_sequential_loop(oracle):
+    """bench.py's CPU baseline folds frames with gvo_update_logodds_omp (all host threads, byte CAS): it has to be the
+    sequential restatement byte for byte -- dense clumps (saturation at 127), NaN points, the z < 0 re-projection branch,
+    negative deltas (saturation at -127), z-slabs, 1 and many threads."""
+    dims, side = (64, 48, 40), 0.02
+    rng = np.random.Generator(np.random.PCG64(9))
+    pts = rng.uniform(-0.7, 0.7, size=(120000, 3)).astype(np.float32)
+    pts[:50000] *= np.float32(0.03)
+    pts[1000:1100] = np.nan
+    pose = np.eye(4, dtype=np.float32)[:3].copy()
+    pose[:, 3] = (0.6, 0.5, 0.4)
+    before = oracle.num_threads()
+    try:
+        for threads in (1, 7, max(2, before)):
+            oracle.set_num_threads(threads)
+            for z0, z1 in ((0, 40), (11, 29)):
+                a, b = oracle.new_map(4, dims, z0, z1), oracle.new_map(4, dims, z0, z1)
+                for delta in (72, 72, -10, 72, -127, 30):
+                    oracle.update_logodds(a, dims, side, pts, pose, delta, z0, z1)
+                    oracle.update_logodds(b, dims, side, pts, pose, delta, z0, z1, parallel=True)
+                    assert np.array_equal(a, b), (threads, z0, delta)
+                assert (a == 127).sum() > 5 and (a == -128).sum() > 1000
+    finally:
+        oracle.set_num_threads(before)
