@@ -60,6 +60,10 @@ SIGNATURES = {
     "gvx_collide_map_map_types": (C.c_int, [u64, u64, f32, C.c_int, vp, P(u64)]),
     "gvx_collide_map_map_bitcheck": (C.c_int, [u64, u64, u32, u32, C.c_int, vp, P(u64)]),
     "gvx_map_shift_sv_ids": (C.c_int, [u64, u32]),
+    "gvx_shard_info": (C.c_int, [P(C.c_int), P(C.c_int), P(C.c_int)]),
+    "gvx_shard_allreduce_u64": (C.c_int, [vp, C.c_int, C.c_int]),
+    "gvx_shard_connect_host": (C.c_int, [C.c_int, C.c_int, C.c_char_p]),
+    "gvx_shard_disconnect": (C.c_int, []),
     "gvx_peer_mailbox_create": (C.c_int, [vp]),
     "gvx_peer_mailbox_connect": (C.c_int, [C.c_int, C.c_int, vp]),
     "gvx_peer_mailbox_disconnect": (C.c_int, []),

@@ -1,6 +1,7 @@
 // gvx_api.cu -- the C ABI (include/gvx.h): context, handle table, host glue. No torch types.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -19,6 +20,59 @@ thread_local std::string t_err;
 
 using namespace gvx;
 
+namespace gvx {
+int mailbox_create_locked(void* ipc_handle64) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is exchanged as 64 bytes");
+  if (!ipc_handle64) return fail(GVX_ERR_INVALID, "null handle buffer");
+  if (!g.peer_mailbox) {
+    GVX_CUDA(cudaMalloc((void**)&g.peer_mailbox, 2 * kMaxPeers * sizeof(PeerSlot)));
+    GVX_CUDA(cudaMemset(g.peer_mailbox, 0, 2 * kMaxPeers * sizeof(PeerSlot)));
+    GVX_CUDA(cudaDeviceSynchronize());
+  }
+  cudaIpcMemHandle_t h;
+  GVX_CUDA(cudaIpcGetMemHandle(&h, g.peer_mailbox));
+  memcpy(ipc_handle64, &h, 64);
+  return GVX_OK;
+}
+
+int mailbox_disconnect_locked();
+int mailbox_connect_locked(int rank, int world, const void* all_handles) {
+  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return fail(GVX_ERR_INVALID, "bad rank %d / world %d", rank, world);
+  if (!g.peer_mailbox) return fail(GVX_ERR_INVALID, "gvx_peer_mailbox_create has not been called");
+  if (world > 1 && !all_handles) return fail(GVX_ERR_INVALID, "null handles");
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) { g.peer_ptr[r] = g.peer_mailbox; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)all_handles + 64 * r, 64);
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      g.peer_world = r; g.peer_rank = rank;  // unmap what has been mapped so far
+      mailbox_disconnect_locked();
+      return fail(GVX_ERR_CUDA, "cudaIpcOpenMemHandle for rank %d: %s", r, cudaGetErrorString(e));
+    }
+    g.peer_ptr[r] = (PeerSlot*)p;
+  }
+  g.peer_rank = rank;
+  g.peer_world = world;
+  // the epoch is NOT reset: the mailbox (allocated once per process) keeps the 16-bit tags of the previous session and
+  // a count restarted at 0 would match them after a disconnect + connect. Ranks of one session issue the same
+  // collectives, so they all hold the same epoch and simply continue the sequence.
+  return GVX_OK;
+}
+
+int mailbox_disconnect_locked() {
+  cudaStreamSynchronize(g.stream);
+  for (int r = 0; r < g.peer_world; ++r)
+    if (r != g.peer_rank && g.peer_ptr[r]) cudaIpcCloseMemHandle(g.peer_ptr[r]);
+  for (int r = 0; r < kMaxPeers; ++r) g.peer_ptr[r] = nullptr;
+  g.peer_world = 1; g.peer_rank = 0;
+  return GVX_OK;
+}
+
+}  // namespace gvx
+
 extern "C" {
 
 int gvx_init(int device) {
@@ -28,6 +82,21 @@ int gvx_init(int device) {
   cudaError_t e = cudaGetDeviceCount(&n_dev);
   if (e != cudaSuccess || n_dev == 0)
     return fail(GVX_ERR_CUDA, "no CUDA device available (%s)", e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0) {  // GVX_SHARD=z: the rank's device, GVX_DEVICES[local rank] or the local rank itself
+    const char* mode = getenv("GVX_SHARD");
+    if (mode && strcmp(mode, "z") == 0) {
+      const char* lr = getenv("GVX_LOCAL_RANK");
+      if (!lr) lr = getenv("LOCAL_RANK");
+      if (!lr) lr = getenv("OMPI_COMM_WORLD_LOCAL_RANK");
+      if (!lr) lr = getenv("GVX_RANK");
+      if (!lr) lr = getenv("RANK");
+      int local = lr ? atoi(lr) : 0;
+      std::vector<int> devs;
+      if (const char* dl = getenv("GVX_DEVICES"))
+        for (const char* p = dl; *p;) { devs.push_back(atoi(p)); while (*p && *p != ',') ++p; if (*p == ',') ++p; }
+      device = devs.empty() ? local % n_dev : devs[(size_t)local % devs.size()];
+    }
+  }
   if (device >= 0) GVX_CUDA(cudaSetDevice(device));
   GVX_CUDA(cudaGetDevice(&g.device));
   GVX_CUDA(cudaDeviceGetAttribute(&g.sm_count, cudaDevAttrMultiProcessorCount, g.device));
@@ -42,13 +111,18 @@ int gvx_init(int device) {
   GVX_CUDA(cudaHostGetDevicePointer((void**)&g.result_hmap_d, g.result_h, 0));
   GVX_CUDA(cudaDeviceSynchronize());
   g.ready = true;
-  return GVX_OK;
+  // GVX_SHARD=z: join the job (rendezvous, peer mailboxes); from then on gvx_map_create makes this rank's z-slab and
+  // collision results are global (gvx_api_shard.cu)
+  const int rc = shard_init_from_env();
+  if (rc != GVX_OK) g.ready = false;
+  return rc;
 }
 
 int gvx_shutdown(void) {
   std::lock_guard<std::mutex> lk(g.mu);
   if (!g.ready) return GVX_OK;
   cudaDeviceSynchronize();
+  shard_detach();
   for (auto& kv : g.maps) {
     if (kv.second.owned && kv.second.data) cudaFree(kv.second.data);
     if (kv.second.occ) cudaFree(kv.second.occ);
@@ -252,7 +326,9 @@ static int map_make(gvx_handle_t* h, int map_type, void* wrap, uint32_t dx, uint
 
 int gvx_map_create(gvx_handle_t* h, int map_type, uint32_t dx, uint32_t dy, uint32_t dz, float side) {
   std::lock_guard<std::mutex> lk(g.mu);
-  return map_make(h, map_type, nullptr, dx, dy, dz, side, 0, dz);
+  uint32_t z0 = 0, z1 = dz;
+  if (shard_active() && dz >= (uint32_t)g.shard_world) shard_slab(dz, &z0, &z1);  // GVX_SHARD=z: this rank's slab
+  return map_make(h, map_type, nullptr, dx, dy, dz, side, z0, z1);
 }
 int gvx_map_create_slab(gvx_handle_t* h, int map_type, uint32_t dx, uint32_t dy, uint32_t dz, float side, uint32_t z0,
                         uint32_t z1) {
@@ -651,12 +727,19 @@ int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32
   int64_t off, i0, i1;
   int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1);
   if (rc) return rc;
-  GVX_CUDA(launch_collide_map_map(lctx(), a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
-                                  mark != 0, false, nullptr,
+  // GVX_SHARD=z: the maps are this rank's slabs and the caller expects the count over the whole grid -- all-reduced
+  // inside the collide kernel when the peers' mailboxes are mapped, else through the host segment
+  const bool global = shard_active() && a->sharded();
+  const bool fused = global && g.shard_fused && g.peer_world > 1;
+  GVX_CUDA(launch_collide_map_map(fused ? lctx_allreduce() : lctx(), a->data, a->type, b->data, b->type, i0, i1, off,
+                                  float_to_probability(thr), mark != 0, false, nullptr,
                                   summary_for_collide(a), summary_for_collide(b)));
-  if (count) {
+  if (count || global) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
-    *count = g.result_h->count;
+    uint64_t c = g.result_h->count;
+    if (fused && c == ~0ull) return fail(GVX_ERR_CUDA, "peer all-reduce timed out: a rank did not arrive");
+    if (global && !fused && (rc = shard_allreduce(&c, 1, 0))) return rc;
+    if (count) *count = c;
   }
   return GVX_OK;
 }
@@ -681,50 +764,17 @@ int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const
 int gvx_peer_mailbox_create(void* ipc_handle64) {
   std::lock_guard<std::mutex> lk(g.mu);
   GVX_NEED_INIT();
-  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is exchanged as 64 bytes");
-  if (!ipc_handle64) return fail(GVX_ERR_INVALID, "null handle buffer");
-  if (!g.peer_mailbox) {
-    GVX_CUDA(cudaMalloc((void**)&g.peer_mailbox, 2 * kMaxPeers * sizeof(PeerSlot)));
-    GVX_CUDA(cudaMemset(g.peer_mailbox, 0, 2 * kMaxPeers * sizeof(PeerSlot)));
-    GVX_CUDA(cudaDeviceSynchronize());
-  }
-  cudaIpcMemHandle_t h;
-  GVX_CUDA(cudaIpcGetMemHandle(&h, g.peer_mailbox));
-  memcpy(ipc_handle64, &h, 64);
-  return GVX_OK;
+  return mailbox_create_locked(ipc_handle64);
 }
-
 int gvx_peer_mailbox_connect(int rank, int world, const void* all_handles) {
   std::lock_guard<std::mutex> lk(g.mu);
   GVX_NEED_INIT();
-  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return fail(GVX_ERR_INVALID, "bad rank %d / world %d", rank, world);
-  if (!g.peer_mailbox) return fail(GVX_ERR_INVALID, "gvx_peer_mailbox_create has not been called");
-  if (world > 1 && !all_handles) return fail(GVX_ERR_INVALID, "null handles");
-  for (int r = 0; r < world; ++r) {
-    if (r == rank) { g.peer_ptr[r] = g.peer_mailbox; continue; }
-    cudaIpcMemHandle_t h;
-    memcpy(&h, (const char*)all_handles + 64 * r, 64);
-    void* p = nullptr;
-    GVX_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
-    g.peer_ptr[r] = (PeerSlot*)p;
-  }
-  g.peer_rank = rank;
-  g.peer_world = world;
-  // the epoch is NOT reset: the mailbox (allocated once per process) keeps the 16-bit tags of the previous session and
-  // a count restarted at 0 would match them after a disconnect + connect. Ranks of one session issue the same
-  // collectives, so they all hold the same epoch and simply continue the sequence.
-  return GVX_OK;
+  return mailbox_connect_locked(rank, world, all_handles);
 }
-
 int gvx_peer_mailbox_disconnect(void) {
   std::lock_guard<std::mutex> lk(g.mu);
   if (!g.ready) return GVX_OK;
-  cudaStreamSynchronize(g.stream);
-  for (int r = 0; r < g.peer_world; ++r)
-    if (r != g.peer_rank && g.peer_ptr[r]) cudaIpcCloseMemHandle(g.peer_ptr[r]);
-  for (int r = 0; r < kMaxPeers; ++r) g.peer_ptr[r] = nullptr;
-  g.peer_world = 1; g.peer_rank = 0;
-  return GVX_OK;
+  return mailbox_disconnect_locked();
 }
 
 int gvx_collide_map_map_allreduce(gvx_handle_t ha, gvx_handle_t hb, float thr, int mark, uint64_t* count,
@@ -761,7 +811,9 @@ int gvx_collide_map_map_any(gvx_handle_t ha, gvx_handle_t hb, float thr, int* fl
                                   false, false, nullptr,
                                   summary_for_collide(a), summary_for_collide(b)));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
-  if (flag) *flag = g.result_h->count != 0;
+  uint64_t any = g.result_h->count != 0;
+  if (shard_active() && a->sharded() && (rc = shard_allreduce(&any, 0, 1))) return rc;  // OR over the ranks' slabs
+  if (flag) *flag = any != 0;
   return GVX_OK;
 }
 
@@ -779,9 +831,12 @@ int gvx_collide_map_map_types(gvx_handle_t ha, gvx_handle_t hb, float thr, int m
                                   mark != 0, true, nullptr,
                                   summary_for_collide(a), summary_for_collide(b)));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
-  if (count) *count = g.result_h->count;
+  uint64_t red[5] = {g.result_h->count, 0, 0, 0, 0};
+  memcpy(red + 1, g.result_h->mask, 32);
+  if (shard_active() && a->sharded() && (rc = shard_allreduce(red, 1, 4))) return rc;  // count summed, mask OR-ed
+  if (count) *count = red[0];
   if (mask_inout32) {
-    const uint8_t* m = (const uint8_t*)g.result_h->mask;
+    const uint8_t* m = (const uint8_t*)(red + 1);
     for (int k = 0; k < 32; ++k) mask_inout32[k] |= m[k];
   }
   return GVX_OK;
@@ -810,9 +865,12 @@ int gvx_collide_map_map_bitcheck(gvx_handle_t ha, gvx_handle_t hb, uint32_t marg
   GVX_CUDA(launch_collide_bitcheck(lctx(), a->data, b->data, i1 - i0, margin, sv_offset, mark != 0, occ_a, occ_b,
                                    a->occ_valid ? a->occ : nullptr, nullptr));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
-  if (count) *count = g.result_h->count;
+  uint64_t red[5] = {g.result_h->count, 0, 0, 0, 0};
+  memcpy(red + 1, g.result_h->mask, 32);
+  if (shard_active() && a->sharded() && (rc = shard_allreduce(red, 1, 4))) return rc;  // count summed, mask OR-ed
+  if (count) *count = red[0];
   if (types_inout32) {
-    const uint8_t* m = (const uint8_t*)g.result_h->mask;
+    const uint8_t* m = (const uint8_t*)(red + 1);
     for (int k = 0; k < 32; ++k) types_inout32[k] |= m[k];
   }
   return GVX_OK;

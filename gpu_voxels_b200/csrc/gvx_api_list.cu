@@ -196,6 +196,18 @@ int list_collide(int mode, gvx_handle_t hl, gvx_handle_t hm, float thr, const in
   }
   if ((rc = list_launch(lctx(), mode, a, thr, mark != 0, mk, nullptr))) return rc;
   GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (shard_active() && a.m->sharded()) {  // GVX_SHARD=z: the list is replicated, the map is this rank's slab -> global result
+    uint64_t red[1 + 256 + 4];
+    red[0] = g.result_h->count;
+    if (mode == 3) memcpy(red + 1, g.result_h->per_meaning, 256 * sizeof(uint64_t));
+    else memset(red + 1, 0, 256 * sizeof(uint64_t));
+    memcpy(red + 257, g.result_h->mask, 32);
+    if ((rc = shard_allreduce(red, 257, 4))) return rc;
+    if (count) *count = red[0];
+    if (mode == 1 && mask_out32) memcpy(mask_out32, red + 257, 32);
+    if (mode == 3 && counts256) memcpy(counts256, red + 1, 256 * sizeof(uint64_t));
+    return GVX_OK;
+  }
   if (count) *count = g.result_h->count;
   if (mode == 1 && mask_out32) memcpy(mask_out32, g.result_h->mask, 32);  // cleared first, BitVoxelList.hpp:163
   if (mode == 3 && counts256) memcpy(counts256, g.result_h->per_meaning, 256 * sizeof(uint64_t));

@@ -160,20 +160,24 @@ void shard_detach() {
 
 // called by gvx_init (g.mu held, context ready): join the job when the environment asks for it
 int shard_init_from_env() {
-  const char* mode = getenv("GVX_SHARD");
-  if (!mode || strcmp(mode, "z") != 0) return GVX_OK;
-  const char* w = env_first({"GVX_WORLD", "WORLD_SIZE", "OMPI_COMM_WORLD_SIZE"});
-  const char* r = env_first({"GVX_RANK", "RANK", "OMPI_COMM_WORLD_RANK"});
-  const int world = w ? atoi(w) : 1, rank = r ? atoi(r) : 0;
-  if (world <= 1) return GVX_OK;
-  if (world > kMaxPeers || rank < 0 || rank >= world) return fail(GVX_ERR_INVALID, "GVX_SHARD=z: bad rank %d / world %d", rank, world);
-  const char* rv = getenv("GVX_RENDEZVOUS");
-  const char* port = getenv("MASTER_PORT");
-  s_name = rv && *rv ? rv : (std::string("gvx_") + (port && *port ? port : "default"));
-  int rc = shard_attach(rank, world, s_name);
-  if (rc) return rc;
-  g.shard_rank = rank;
-  g.shard_world = world;
+  int rank, world, rc;
+  if (g.shard_world > 1) {  // joined explicitly (gvx_shard_connect_host) before gvx_init: only the mailboxes are missing
+    rank = g.shard_rank; world = g.shard_world;
+  } else {
+    const char* mode = getenv("GVX_SHARD");
+    if (!mode || strcmp(mode, "z") != 0) return GVX_OK;
+    const char* w = env_first({"GVX_WORLD", "WORLD_SIZE", "OMPI_COMM_WORLD_SIZE"});
+    const char* r = env_first({"GVX_RANK", "RANK", "OMPI_COMM_WORLD_RANK"});
+    world = w ? atoi(w) : 1; rank = r ? atoi(r) : 0;
+    if (world <= 1) return GVX_OK;
+    if (world > kMaxPeers || rank < 0 || rank >= world) return fail(GVX_ERR_INVALID, "GVX_SHARD=z: bad rank %d / world %d", rank, world);
+    const char* rv = getenv("GVX_RENDEZVOUS");
+    const char* port = getenv("MASTER_PORT");
+    s_name = rv && *rv ? rv : (std::string("gvx_") + (port && *port ? port : "default"));
+    if ((rc = shard_attach(rank, world, s_name))) return rc;
+    g.shard_rank = rank;
+    g.shard_world = world;
+  }
   // peer mailboxes for the in-kernel all-reduce of map x map counts: every rank publishes its CUDA IPC handle in the
   // segment; all ranks agree (host all-reduce) on whether every mapping succeeded, else counts go through the host too
   const char* fz = getenv("GVX_SHARD_FUSED");
@@ -205,9 +209,29 @@ int gvx_shard_info(int* rank, int* world, int* fused) {
 
 int gvx_shard_allreduce_u64(uint64_t* values, int n_sum, int n_or) {
   std::lock_guard<std::mutex> lk(g.mu);
-  GVX_NEED_INIT();
   if (!values && n_sum + n_or > 0) return fail(GVX_ERR_INVALID, "null values");
   return shard_allreduce(values, n_sum, n_or);
+}
+
+int gvx_shard_connect_host(int rank, int world, const char* rendezvous) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  if (g.shard_world > 1) return fail(GVX_ERR_INVALID, "already part of a sharded job");
+  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return fail(GVX_ERR_INVALID, "bad rank %d / world %d", rank, world);
+  if (!rendezvous || !*rendezvous) return fail(GVX_ERR_INVALID, "empty rendezvous name");
+  if (world == 1) return GVX_OK;
+  s_name = rendezvous;
+  int rc = shard_attach(rank, world, s_name);
+  if (rc) return rc;
+  g.shard_rank = rank;
+  g.shard_world = world;
+  g.shard_fused = false;
+  return GVX_OK;
+}
+
+int gvx_shard_disconnect(void) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  shard_detach();
+  return GVX_OK;
 }
 
 }  // extern "C"

@@ -3,6 +3,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -117,6 +118,9 @@ struct Context {
   bool disp_connected = false;
   unsigned long long disp_epoch = 0;
   uint32_t* disp_err_h = nullptr; uint32_t* disp_err_hmap_d = nullptr;
+  // z-slab sharding behind the API (gvx_api_shard.cu): one process per GPU, GVX_SHARD=z in the environment
+  int shard_rank = 0, shard_world = 1;
+  bool shard_fused = false;  // the peers' mailboxes are mapped: map x map counts are all-reduced inside the collide kernel
   bool pdl = true;       // GVX_OPT_PDL
   int collide_tma = -1;  // GVX_OPT_COLLIDE_TMA: -1 auto (TMA where it measured faster), 0 never, 1..5 always (shape k)
   bool use_summary = true;  // GVX_OPT_USE_SUMMARY: collide kernels may read occupancy summaries instead of voxels
@@ -131,6 +135,16 @@ struct Context {
 };
 
 extern Context g;
+// gvx_api_shard.cu
+int shard_init_from_env();
+void shard_detach();
+int shard_allreduce(uint64_t* v, int n_sum, int n_or);  // host-side, through the job's shared-memory segment
+void shard_slab(uint32_t dz, uint32_t* z0, uint32_t* z1);
+inline bool shard_active() { return g.shard_world > 1; }
+// gvx_api.cu: the peer mailbox entry points without taking g.mu
+int mailbox_create_locked(void* ipc_handle64);
+int mailbox_connect_locked(int rank, int world, const void* all_handles);
+int mailbox_disconnect_locked();
 void lists_free_all();  // gvx_api_list.cu
 void dispatch_free_all();  // gvx_api_dispatch.cu
 extern thread_local std::string t_err;

@@ -259,6 +259,27 @@ int gvx_collide_map_map_allreduce(gvx_handle_t a, gvx_handle_t b, float thr, int
 int gvx_collide_list_map_allreduce(gvx_handle_t list, gvx_handle_t map, float thr, int mark, uint64_t* count,
                                    uint64_t* count_d);
 
+/* ---- multi-GPU behind the drop-in API (SPMD, one process per GPU, no torch / MPI needed) ---------------------- */
+/* Start N copies of the SAME program with GVX_SHARD=z GVX_WORLD=N GVX_RANK=r in the environment ([GVX_LOCAL_RANK],
+ * [GVX_DEVICES=0,1,..], [GVX_RENDEZVOUS=name]; torchrun's RANK / WORLD_SIZE / LOCAL_RANK / MASTER_PORT and mpirun's
+ * OMPI_COMM_WORLD_* are understood). gvx_init(-1) then selects the rank's device and joins the job's POSIX
+ * shared-memory rendezvous; gvx_map_create (GpuVoxels::addMap, GV/GpuVoxels.cpp:164-290) allocates this rank's z-slab
+ * of the grid -- so maps beyond one GPU's memory and the reference's 4 GiB limit (GV/voxelmap/TemplateVoxelMap.hpp:
+ * 65-75) fit; inserts keep the slab's points; voxel lists stay replicated. Every synchronous call that returns a
+ * collision result returns the GLOBAL result on every rank: gvx_collide_map_map's count is all-reduced inside the
+ * collide kernel over NVLink peer memory (GVX_SHARD_FUSED=0: through the host segment), gvx_collide_map_map_any / _types /
+ * _bitcheck and gvx_collide_list_map / _types / _mask / _per_meaning through the host segment (sum of counts, OR of
+ * masks). Every rank must make the same calls in the same order. The *_async variants and downloads stay local to
+ * the slab; offsets on slab maps are refused (GVX_ERR_UNSUPPORTED: halo exchange). */
+int gvx_shard_info(int* rank, int* world, int* fused);
+/* utility for callers with results of their own: sum of values[0..n_sum), OR of the next n_or words, over all ranks */
+int gvx_shard_allreduce_u64(uint64_t* values, int n_sum, int n_or);
+/* join / leave the job's rendezvous explicitly instead of through the environment: host side only (no GPU needed, no
+ * peer mailboxes: every global result then goes through the host segment). Call before gvx_init, or in a process that
+ * only needs gvx_shard_allreduce_u64 (the CPU tests do). */
+int gvx_shard_connect_host(int rank, int world, const char* rendezvous);
+int gvx_shard_disconnect(void);
+
 /* ---- multi-GPU: sensor frames routed to the rank that owns the voxel, INSIDE the update kernel ---------------- */
 /* insertSensorData (log-odds hits, ProbVoxelMap::insertSensorData GV/voxelmap/ProbVoxelMap.hpp:52-102 without ray
  * casting) on a map cut into z-slabs, one sensor per rank: every rank transforms and voxelises only ITS frame; hits

@@ -1,0 +1,50 @@
+"""GVX_SHARD=z behind the drop-in API (VERDICT r1 missing #3): the SAME C++ caller code (tests/cpp/shard_example.cpp,
+written against the reference's public classes: GpuVoxels::addMap, insertBoxIntoMap, map->collideWith ...,
+GV/GpuVoxels.cpp:52-78,164-290) run as ONE process and as N processes that each hold a z-slab must print the same
+collision results. On the one-GPU test box the N processes share GPU 0 and the counts travel through the host segment
+(GVX_SHARD_FUSED=0: two spinning kernels of different processes must not share a GPU); benchmarks/job_r2_multi.sh runs
+the same comparison with one GPU per rank and the in-kernel all-reduce."""
+import os
+import subprocess
+
+import pytest
+
+from test_shard_host import build_shard_example
+
+pytestmark = pytest.mark.gpu
+
+
+def run_spmd(exe, world, fused, devices=None, timeout=300):
+    env = dict(os.environ)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "GVX_SHARD", "GVX_WORLD", "GVX_RANK"):
+        env.pop(k, None)
+    if world == 1:
+        r = subprocess.run([exe], capture_output=True, text=True, timeout=timeout, env=env)
+        assert r.returncode == 0, r.stderr[-2000:]
+        return [r.stdout], [r.stderr]
+    ps = []
+    for rank in range(world):
+        e = dict(env, GVX_SHARD="z", GVX_WORLD=str(world), GVX_RANK=str(rank), GVX_LOCAL_RANK=str(rank),
+                 GVX_RENDEZVOUS="gvx_pytest_%d" % os.getpid(), GVX_SHARD_FUSED="1" if fused else "0")
+        if devices is not None:
+            e["GVX_DEVICES"] = devices
+        ps.append(subprocess.Popen([exe], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=e))
+    outs, errs = [], []
+    for p in ps:
+        o, er = p.communicate(timeout=timeout)
+        assert p.returncode == 0, er[-2000:]
+        outs.append(o); errs.append(er)
+    return outs, errs
+
+
+def test_same_caller_code_one_process_vs_three_slabs():
+    exe = build_shard_example()
+    single, _ = run_spmd(exe, 1, False)
+    lines = dict(l.split(" ", 1) for l in single[0].strip().splitlines())
+    assert int(lines["linkage"]) == 8000            # example_how_to_link/README.txt:21 "about 8000 collisions"
+    assert lines["check"] == "1" and lines["after_clear"] == "0"
+    assert lines["types"].split()[1:] == ["14", "46"] and int(lines["list_x_bit"]) > 0
+    outs, errs = run_spmd(exe, 3, False, devices="0,0,0")   # 150 layers -> slabs of 50
+    for rank, o in enumerate(outs):
+        assert o == single[0], "rank %d of 3 prints different results:\n%s\nvs\n%s" % (rank, o, single[0])
+        assert "rank %d of 3" % rank in errs[rank]
