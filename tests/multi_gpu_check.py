@@ -101,8 +101,8 @@ def main():
     t_off = torch.tensor([c_off], dtype=torch.int64, device="cuda")
     dist.all_reduce(t_off)
     assert int(t_off.item()) == w_off, (int(t_off.item()), w_off)
-    lst.insertPointCloud(env_pts[:5000], 33)   # the list changes: the cached slab range must not survive
-    r_lst.insert_points(env_pts[:5000], 33)
+    lst.insertPointCloud(env_pts[100000:105000], 33)   # the list changes (new voxels, all occupied in env): the cached
+    r_lst.insert_points(env_pts[100000:105000], 33)    # slab range must not survive
     l_want2 = r_lst.collide(0, r_env, PROB, 1.0, 0, False)[0]
     host = C.c_uint64(0)
     _lib.check(L.gvx_collide_list_map_allreduce(lst.handle, env.handle, 1.0, 0, C.byref(host), None))
