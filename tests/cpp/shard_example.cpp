@@ -33,7 +33,7 @@ int main()
   voxelmap::BitVectorVoxelMap* bits = gvl->getMap("myBitMap")->as<voxelmap::BitVectorVoxelMap>();
   bits->insertPointCloud(geometry_generation::createBoxOfPoints(Vector3f(0.2f, 0.2f, 0.1f), Vector3f(0.6f, 0.6f, 0.9f), 0.01f),
                          BitVoxelMeaning(14));
-  bits->insertPointCloud(geometry_generation::createBoxOfPoints(Vector3f(0.5f, 0.5f, 0.6f), Vector3f(0.9f, 0.9f, 1.4f), 0.01f),
+  bits->insertPointCloud(geometry_generation::createBoxOfPoints(Vector3f(0.5f, 0.5f, 0.4f), Vector3f(0.9f, 0.9f, 1.4f), 0.01f),
                          BitVoxelMeaning(46));
   BitVectorVoxel types;
   std::printf("types %zu", bits->collideWithTypes(second, types, 1.0f));
