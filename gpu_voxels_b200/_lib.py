@@ -107,6 +107,8 @@ SIGNATURES = {
     "gvx_batch_robot_collide": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, vp, u32, vp, f32, vp]),
     "gvx_batch_robot_collide_dh": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, vp, vp, u32, vp, vp, u32, vp, f32, vp]),
     "gvx_dh_chain_transforms": (C.c_int, [vp, vp, u32, vp, u32, vp, vp]),
+    "gvx_batch_robot_collide_noalloc": (C.c_int, [u64, vp, vp, u32, vp, vp, u32, vp, f32, vp]),
+    "gvx_noalloc_scratch_bytes": (u64, []),
     "gvx_batch_set_scratch_budget": (C.c_int, [u64]),
 }
 

@@ -447,6 +447,23 @@ int gvx_dh_chain_transforms(const float* dh4, const int32_t* joint_types, uint32
                             uint32_t n_cfg, float* transforms_out, uint32_t* n_ambiguous);
 /* bytes of per-wave scratch the batch call may use for its per-configuration "seen" bitmaps (default 4 GiB) */
 int gvx_batch_set_scratch_budget(uint64_t bytes);
+/* No counterpart in the reference. gvx_batch_robot_collide for callers
+ * that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): ALL
+ * scratch -- the environment's 1-bit-per-voxel bitmap and one "seen" bitmap per configuration -- lives in one static
+ * __device__ array of gvx_noalloc_scratch_bytes() = 16 MiB inside the library (every GPU that loads libgvx.so holds it
+ * until the process exits). Inputs and output are the caller's: xyz_d (device, packed Vector3f of all link clouds),
+ * cloud_sizes / meanings (host, n_clouds <= 16), transforms_d (device, n_cfg x n_clouds x 16 floats, row-major
+ * Matrix4f), mask32 (host, nullable), counts_d (device, n_cfg x uint64, written by the call). Same result as
+ * gvx_batch_robot_collide. Limits, refused with GVX_ERR_INVALID and a message: (1 + n_cfg) bitmaps of
+ * ceil(voxels / 2048) * 256 bytes must fit the 16 MiB (e.g. 63 configurations of a 128^3 grid, 7 of 256^3),
+ * n_clouds <= 16, n_cfg <= 65535. The call enqueues a memset, at most one bitmap kernel and one collide kernel on the
+ * library's stream and returns without synchronising; it calls no cudaMalloc / cudaFree / cudaHostAlloc and no
+ * allocating library routine. All calls share the array, which keeps the last call's contents (this call clears what
+ * must start at zero): calls that overlap on the GPU race -- keep them ordered on one stream. */
+int gvx_batch_robot_collide_noalloc(gvx_handle_t env_map, const float* xyz_d, const uint32_t* cloud_sizes,
+                                    uint32_t n_clouds, const int32_t* meanings, const float* transforms_d,
+                                    uint32_t n_cfg, const uint8_t* mask32, float thr, uint64_t* counts_d);
+uint64_t gvx_noalloc_scratch_bytes(void);
 
 #ifdef __cplusplus
 }
