@@ -5,13 +5,13 @@ N=${1:-2}
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
-timeout 600 $TR --nproc-per-node $N --master-port 29511 tests/multi_gpu_check.py > gpurun_out/m_check_n$N.log 2>&1
+[ "$3" = "nocheck" ] || timeout 600 $TR --nproc-per-node $N --master-port 29511 tests/multi_gpu_check.py > gpurun_out/m_check_n$N.log 2>&1
 echo "multi_gpu_check rc=$?" | tee -a gpurun_out/m_check_n$N.log
 tail -3 gpurun_out/m_check_n$N.log
-timeout 300 python benchmarks/shard_spmd_check.py $N > gpurun_out/m_spmd_n$N.log 2>&1
+[ "$3" = "nocheck" ] || timeout 300 python benchmarks/shard_spmd_check.py $N > gpurun_out/m_spmd_n$N.log 2>&1
 echo "shard_spmd_check rc=$?" | tee -a gpurun_out/m_spmd_n$N.log
 tail -3 gpurun_out/m_spmd_n$N.log
-LIST="$N"; [ "$2" = "scale" ] && LIST="1 2 4 8"
+LIST="$N"; [ "$2" = "scale" ] && LIST="1 2 4 8"; [ -n "$2" ] && [ "$2" != "scale" ] && LIST="$2"
 for K in $LIST; do
   [ $K -gt $N ] && continue
   if [ $K -eq 1 ]; then CMD="python bench.py --gpus 1"; else CMD="$TR --nproc-per-node $K --master-port 2952$K bench.py --gpus $K"; fi

@@ -720,6 +720,15 @@ static int collide_prepare(gvx_handle_t ha, gvx_handle_t hb, const int32_t off3[
   return GVX_OK;
 }
 
+// A marking collide at the int8 threshold -128 (a nonsense threshold that converts to it, see launch_collide_map_map)
+// lets UNKNOWN voxels of a ProbVoxelMap collide and writes 127 into them: they become known behind the summary's back.
+// Re-derive the "known" summary from the voxels on the stream (one pass; the threshold is an error case, not a path).
+static int fixup_summary_after_mark(Map* a, int8_t thr_i, bool mark) {
+  if (mark && thr_i == -128 && a->type == kMapProb && a->occ && a->occ_valid)
+    GVX_CUDA(launch_env_bitmap(lctx(), a->data, a->type, a->n_voxels(), -127, a->occ));
+  return GVX_OK;
+}
+
 int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32_t off3[3], int mark, uint64_t* count) {
   std::lock_guard<std::mutex> lk(g.mu);
   GVX_NEED_INIT();
@@ -734,6 +743,7 @@ int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32
   GVX_CUDA(launch_collide_map_map(fused ? lctx_allreduce() : lctx(), a->data, a->type, b->data, b->type, i0, i1, off,
                                   float_to_probability(thr), mark != 0, false, nullptr,
                                   summary_for_collide(a), summary_for_collide(b)));
+  if ((rc = fixup_summary_after_mark(a, float_to_probability(thr), mark != 0))) return rc;
   if (count || global) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
     uint64_t c = g.result_h->count;
@@ -757,7 +767,7 @@ int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const
   GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
                                   mark != 0, false, (unsigned long long*)count_d,
                                   summary_for_collide(a), summary_for_collide(b)));
-  return GVX_OK;
+  return fixup_summary_after_mark(a, float_to_probability(thr), mark != 0);
 }
 
 // ---- fused all-reduce over peer memory ----------------------------------------------------------------
@@ -790,6 +800,7 @@ int gvx_collide_map_map_allreduce(gvx_handle_t ha, gvx_handle_t hb, float thr, i
   GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, 0,
                                   float_to_probability(thr), mark != 0, false, (unsigned long long*)count_d,
                                   summary_for_collide(a), summary_for_collide(b)));
+  if ((rc = fixup_summary_after_mark(a, float_to_probability(thr), mark != 0))) return rc;
   if (count) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
     *count = g.result_h->count;

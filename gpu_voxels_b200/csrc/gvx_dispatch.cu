@@ -47,8 +47,8 @@ __device__ __forceinline__ void apply_hit(const MapView& m, bool live, uint64_t 
   const unsigned long long key = live ? idx : (~0ull - (threadIdx.x & 31));
   const unsigned peers = __match_any_sync(0xffffffffu, key);
   if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
-    logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
-    if (m.occ) summary_set(m.occ, idx);
+    const bool first = logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
+    if (m.occ && first) summary_set(m.occ, idx);  // a voxel that was known has its bit already
   }
 }
 

@@ -154,8 +154,8 @@ k_update_logodds(MapView m, const float* __restrict__ xyz, unsigned long long n,
     const unsigned long long key = live ? idx : (~0ull - (threadIdx.x & 31));
     const unsigned peers = __match_any_sync(0xffffffffu, key);
     if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
-      logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
-      if (m.occ) summary_set(m.occ, idx);  // clamp(.., -127, 127) never returns to UNKNOWN: the voxel is "known"
+      const bool first = logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
+      if (m.occ && first) summary_set(m.occ, idx);  // first touch: the voxel becomes "known" (and never UNKNOWN again)
     }
   }
 }
@@ -233,6 +233,7 @@ k_raycast_free(MapView m, const float* __restrict__ xyz, unsigned long long n, c
 // Same per-point arithmetic as k_update_logodds. Used when a z-slab rank folds the whole multi-sensor cloud and keeps
 // only its slab's points: one launch instead of one per frame.
 constexpr int kMaxFramesSmem = 64;
+constexpr int kFoldDrain = 128;  // k_update_logodds_frames: queued hits a warp applies at once (4 per lane)
 __global__ void __launch_bounds__(kInsThreads)
 k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t* __restrict__ prefix_g,
                        const float* __restrict__ poses_g, uint32_t n_frames, int delta) {
@@ -290,8 +291,8 @@ k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t*
     const unsigned long long key = live ? idx : (~0ull - (threadIdx.x & 31));
     const unsigned peers = __match_any_sync(0xffffffffu, key);
     if (live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1)) {
-      logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
-      if (m.occ) summary_set(m.occ, idx);  // clamp(.., -127, 127) never returns to UNKNOWN: the voxel is "known"
+      const bool first = logodds_add((int8_t*)m.data, idx, delta * __popc(peers));
+      if (m.occ && first) summary_set(m.occ, idx);  // first touch: the voxel becomes "known" (and never UNKNOWN again)
     }
   }
 }
@@ -318,6 +319,57 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
   __shared__ __align__(16) float sh_xyz[kInsThreads * U * 3];
   // staging needs 16-byte aligned chunks: the frame must start on a multiple of 4 points of a 16-byte aligned array
   const bool staged = ((first & 3ull) == 0) && ((reinterpret_cast<uintptr_t>(xyz) & 15) == 0);
+  __shared__ unsigned long long sh_q[kInsThreads / 32][kFoldDrain + 32];  // per warp: < kFoldDrain waiting + one append
+  unsigned long long* wq = sh_q[threadIdx.x >> 5];
+  const unsigned lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+  int qn = 0;  // warp-uniform number of queued hits
+  int8_t* map = (int8_t*)m.data;
+  auto drain = [&](int cnt) {  // the last cnt (<= kFoldDrain) queued hits: entry j * 32 + lane of them for j = 0..3
+    __syncwarp();
+    constexpr int J = kFoldDrain / 32;
+    bool lead[J];
+    uint64_t id[J];
+    int tot[J];
+    uint32_t oldw[J], got[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+      lead[j] = false; id[j] = 0; tot[j] = 0;
+      if (j * 32 >= cnt) continue;  // warp-uniform
+      const int k = j * 32 + (int)lane;
+      const bool have_k = k < cnt;
+      if (have_k) id[j] = wq[qn - cnt + k];
+      // equal voxels of one round fold into one saturating update (exact for same-sign deltas)
+      const unsigned peers = __match_any_sync(0xffffffffu, have_k ? id[j] : (~0ull - lane));
+      lead[j] = have_k && lane == (unsigned)(__ffs(peers) - 1);
+      tot[j] = delta * __popc(peers);
+    }
+    // the read-modify-writes of a lane go out together: loads of the old words, then the CAS of each, then (rare) the
+    // retry loop for a CAS that lost a race. One latency chain instead of J.
+#pragma unroll
+    for (int j = 0; j < J; ++j)
+      if (lead[j]) oldw[j] = __ldcg(reinterpret_cast<const uint32_t*>(map + (id[j] & ~3ull)));
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+      if (!lead[j]) continue;
+      const int shift = (int)(id[j] & 3ull) * 8;
+      int v = (int)(int8_t)((oldw[j] >> shift) & 0xFFu) + tot[j];
+      v = v < -127 ? -127 : (v > 127 ? 127 : v);
+      const uint32_t neww = (oldw[j] & ~(0xFFu << shift)) | (((uint32_t)v & 0xFFu) << shift);
+      got[j] = oldw[j];
+      if (neww != oldw[j]) got[j] = atomicCAS(reinterpret_cast<uint32_t*>(map + (id[j] & ~3ull)), oldw[j], neww);
+    }
+    // first touch of a voxel (its byte was UNKNOWN in the word this lane read): only then can the "known" bit be missing
+    // from the summary -- every other hit skips the summary word, the second random DRAM sector of an update
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+      if (!lead[j]) continue;
+      bool first_touch = ((oldw[j] >> ((int)(id[j] & 3ull) * 8)) & 0xFFu) == 0x80u;
+      if (got[j] != oldw[j]) first_touch |= logodds_add(map, id[j], tot[j]);  // another update got in between: redo
+      if (m.occ && first_touch) atomicOr(m.occ + (id[j] >> 5), 1u << (id[j] & 31));
+    }
+    qn -= cnt;
+    __syncwarp();
+  };
   const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads * U;
   for (unsigned long long base = (unsigned long long)blockIdx.x * kInsThreads * U; base < n; base += stride) {  // CTA-uniform
     float rx[U], ry[U], rz[U];
@@ -356,13 +408,14 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
         }
       }
     }
-    bool lead[U];   // this lane applies the (warp-folded) update of point u
-    uint64_t idx[U];
-    int tot[U];
+    // Live hits are not applied where they are found: on a z-slab rank most lanes of a warp hold points of OTHER slabs,
+    // and a read-modify-write chain (DRAM miss -> CAS -> maybe the summary word) costs a warp the same latency with 4 live
+    // lanes as with 32. Every warp appends its live voxel indices to a small queue in shared memory and drains it 128 at a
+    // time -- 4 per lane, their loads issued together -- so the number of latency chains follows the number of hits.
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       bool live = false;
-      idx[u] = 0;
+      uint64_t idx = 0;
       if (have[u]) {
         float wz = affine_row(P + 8, rx[u], ry[u], rz[u]);
         if (wz < 0.0f) {  // re-projection onto the floor moves x and y too: the full path
@@ -372,7 +425,7 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
             const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
             if (cx < m.dx && cy < m.dy && cz >= m.z0 && cz < m.z1) {
               live = true;
-              idx[u] = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+              idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
             }
           }
         } else if (!isnan(wz)) {
@@ -383,50 +436,20 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
               const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side);
               if (cx < m.dx && cy < m.dy) {
                 live = true;
-                idx[u] = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+                idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
               }
             }
           }
         }
       }
-      lead[u] = false;
-      tot[u] = 0;
-      if (!__any_sync(0xffffffffu, live)) continue;  // a warp of another slab's points: nothing to fold
-      const unsigned long long key = live ? idx[u] : (~0ull - (threadIdx.x & 31));
-      const unsigned peers = __match_any_sync(0xffffffffu, key);
-      lead[u] = live && (threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1);
-      tot[u] = delta * __popc(peers);
-    }
-    // the U read-modify-writes of a thread go out together: loads of the old words, then the CAS of each, then (rare)
-    // the retry loop for a CAS that lost a race; the same for the summary bits. One latency chain instead of U.
-    int8_t* map = (int8_t*)m.data;
-    uint32_t oldw[U], neww[U], got[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (lead[u]) oldw[u] = __ldcg(reinterpret_cast<const uint32_t*>(map + (idx[u] & ~3ull)));
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (!lead[u]) continue;
-      const int shift = (int)(idx[u] & 3ull) * 8;
-      int v = (int)(int8_t)((oldw[u] >> shift) & 0xFFu) + tot[u];
-      v = v < -127 ? -127 : (v > 127 ? 127 : v);
-      neww[u] = (oldw[u] & ~(0xFFu << shift)) | (((uint32_t)v & 0xFFu) << shift);
-      got[u] = oldw[u];
-      if (neww[u] != oldw[u]) got[u] = atomicCAS(reinterpret_cast<uint32_t*>(map + (idx[u] & ~3ull)), oldw[u], neww[u]);
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (lead[u] && got[u] != oldw[u]) logodds_add(map, idx[u], tot[u]);  // another update got in between: redo
-    if (m.occ) {
-      uint32_t sw[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u)
-        if (lead[u]) sw[u] = __ldcg(m.occ + (idx[u] >> 5));
-#pragma unroll
-      for (int u = 0; u < U; ++u)
-        if (lead[u] && !(sw[u] & (1u << (idx[u] & 31)))) atomicOr(m.occ + (idx[u] >> 5), 1u << (idx[u] & 31));
+      const unsigned bal = __ballot_sync(0xffffffffu, live);
+      if (!bal) continue;  // a warp of another slab's points
+      if (live) wq[qn + __popc(bal & lt)] = idx;
+      qn += __popc(bal);
+      if (qn >= kFoldDrain) drain(kFoldDrain);
     }
   }
+  while (qn > 0) drain(qn < kFoldDrain ? qn : kFoldDrain);
 }
 
 // BitVoxelMap::clearBits / clearBit: voxel &= ~mask, written back only where it changes. When the map carries an
@@ -518,7 +541,11 @@ cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, co
     }
     // 4 points per thread and step. The grid is NOT divided among the frames: on a z-slab rank most frames belong to
     // other slabs and their CTAs retire after one read, leaving the SMs to the frame(s) that do the atomics
+    // ... but the whole grid stays within ~one wave of co-resident CTAs, so that a CTA runs several chunks and its warps'
+    // hit queues fill up across them before they are drained
     int gx = grid_for(c, (longest + 3) / 4, 8);
+    const int per_frame = (c.sm_count * 8 + (int)n_frames - 1) / (int)n_frames;
+    if (gx > per_frame) gx = per_frame < 1 ? 1 : per_frame;
     return pdl_launch(k_update_logodds_frames, dim3((unsigned)gx, n_frames), kInsThreads, c.stream, c.pdl, m, xyz_d,
                       *by_value, delta);
   }

@@ -9,10 +9,15 @@ constexpr int kInsThreads = 256;
 // Saturating int8 add on one byte of the map with a 32-bit CAS. For same-sign deltas,
 // clamp(occ + k*delta, -127, 127) equals k sequential ProbabilisticVoxel::updateOccupancy calls
 // (GV/voxel/ProbabilisticVoxel.hpp:51-57), so a warp's duplicates are folded into one update.
-__device__ __forceinline__ void logodds_add(int8_t* map, uint64_t idx, int total_delta) {
+// Returns true when the voxel was UNKNOWN (-128) at the first read: only then can its bit be missing from a valid
+// "known" summary (bit == (occupancy != UNKNOWN), kept exact by every mutating kernel), so callers touch the summary
+// word -- a second random DRAM sector per point -- only on the first touch of a voxel. clamp(.., -127, 127) never
+// returns to -128, so an UNKNOWN voxel always changes and a known one stays known.
+__device__ __forceinline__ bool logodds_add(int8_t* map, uint64_t idx, int total_delta) {
   uint32_t* wp = reinterpret_cast<uint32_t*>(map + (idx & ~3ull));
   const int shift = (int)(idx & 3ull) * 8;
-  uint32_t old = *wp, assumed;
+  uint32_t old = __ldcg(wp), assumed;
+  const bool was_unknown = ((old >> shift) & 0xFFu) == 0x80u;
   do {
     assumed = old;
     int v = (int)(int8_t)((assumed >> shift) & 0xFFu) + total_delta;
@@ -21,6 +26,7 @@ __device__ __forceinline__ void logodds_add(int8_t* map, uint64_t idx, int total
     if (nw == assumed) break;
     old = atomicCAS(wp, assumed, nw);
   } while (old != assumed);
+  return was_unknown;
 }
 
 // kernelTransformSensorData, GV/voxelmap/kernels/VoxelMapOperations.cu:27-71: pose * raw point; a point that lands below

@@ -64,6 +64,13 @@ def test_map_map_threshold_minus_128(gv, oracle, pair, thr):
                 got = maps[0].collideWith(maps[1], thr, mark=mark)
                 assert got == want, (pair, thr, use_summary, mark, got, want)
                 assert np.array_equal(maps[0].download().reshape(-1).view(np.uint8), refs[0].view(np.uint8))
+                # the marks may have turned UNKNOWN voxels into known ones: the summary must have followed
+                bits, valid = maps[0].summary()
+                if valid and pair[0] == PROB:
+                    assert np.array_equal(bits, maps[0].download() != -128), (pair, thr, use_summary, mark)
+            if use_summary and pair[0] == PROB:   # and the summary path after the marks agrees with the oracle again
+                want2 = oracle.collide_map_map(refs[0].copy(), pair[0], refs[1], pair[1], n, 0.5, 0, False)
+                assert maps[0].collideWith(maps[1], 0.5, mark=False) == want2
             if ti == -128 and pair == (PROB, BIT):  # every occupied robot voxel collides, known environment or not
                 v = refs[1].reshape(-1, 32)
                 assert want == int((((v[:, 0] & 0xFE) != 0) | v[:, 1:].any(1)).sum())
