@@ -14,6 +14,7 @@
 // results equal the sequential (race-free) semantics and are deterministic.
 #include "gvx_internal.h"
 #include "gvx_sensor.cuh"
+#include "gvx_tma.cuh"
 
 namespace gvx {
 
@@ -233,6 +234,7 @@ k_raycast_free(MapView m, const float* __restrict__ xyz, unsigned long long n, c
 // Same per-point arithmetic as k_update_logodds. Used when a z-slab rank folds the whole multi-sensor cloud and keeps
 // only its slab's points: one launch instead of one per frame.
 constexpr int kMaxFramesSmem = 64;
+constexpr int kFoldStages = 3;  // k_update_logodds_frames: ring of 12 KB point chunks filled by bulk copies
 constexpr int kFoldDrain = 128;  // k_update_logodds_frames: queued hits a warp applies at once (4 per lane)
 __global__ void __launch_bounds__(kInsThreads)
 k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t* __restrict__ prefix_g,
@@ -316,9 +318,34 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
   // U points per thread and step, their loads issued together: with several frames per launch a thread runs many steps,
   // and one dependent load -> divide -> atomic chain per step would leave the SMs waiting on latency
   constexpr int U = 4;
-  __shared__ __align__(16) float sh_xyz[kInsThreads * U * 3];
-  // staging needs 16-byte aligned chunks: the frame must start on a multiple of 4 points of a 16-byte aligned array
+  // A CTA's chunk of U * 256 points (12 KB) arrives as ONE bulk copy (cp.async.bulk, SASS UBLKCP) into a ring of
+  // kFoldStages shared-memory stages, issued by one thread kFoldStages chunks ahead and counted by an mbarrier: HBM keeps
+  // streaming while the CTA classifies the chunk before (a load -> __syncthreads -> compute loop left it idle half the
+  // time: on a z-slab rank, where 7 of 8 points are only read and dropped, the frame was filtered at 1.7 TB/s).
+  // A thread's own x/y/z sit 12 bytes apart and are handed out from shared memory.
+  __shared__ __align__(128) float sh_xyz[kFoldStages][kInsThreads * U * 3];
+  __shared__ __align__(8) uint64_t sh_full[kFoldStages];
+  constexpr uint32_t kChunkPts = kInsThreads * U, kChunkBytes = kChunkPts * 12;
+  // bulk copies need 16-byte aligned source chunks: the frame must start on a multiple of 4 points of a 16-byte aligned array
   const bool staged = ((first & 3ull) == 0) && ((reinterpret_cast<uintptr_t>(xyz) & 15) == 0);
+  const unsigned long long n_chunks = (n + kChunkPts - 1) / kChunkPts, n_full = staged ? n / kChunkPts : 0;
+  uint64_t policy = 0;
+  if (threadIdx.x == 0) {
+    for (int st = 0; st < kFoldStages; ++st) mbar_init(&sh_full[st], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  }
+  __syncthreads();
+  auto issue = [&](unsigned long long chunk, int st) {  // thread 0 only; full chunks only
+    mbar_expect_tx(&sh_full[st], kChunkBytes);
+    bulk_load(sh_xyz[st], xyz + 3 * (first + chunk * kChunkPts), kChunkBytes, &sh_full[st], policy);
+  };
+  if (threadIdx.x == 0) {
+    for (int st = 0; st < kFoldStages; ++st) {
+      const unsigned long long chunk = blockIdx.x + (unsigned long long)st * gridDim.x;
+      if (chunk < n_full) issue(chunk, st);
+    }
+  }
   __shared__ unsigned long long sh_q[kInsThreads / 32][kFoldDrain + 32];  // per warp: < kFoldDrain waiting + one append
   unsigned long long* wq = sh_q[threadIdx.x >> 5];
   const unsigned lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
@@ -370,34 +397,27 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
     qn -= cnt;
     __syncwarp();
   };
-  const unsigned long long stride = (unsigned long long)gridDim.x * kInsThreads * U;
-  for (unsigned long long base = (unsigned long long)blockIdx.x * kInsThreads * U; base < n; base += stride) {  // CTA-uniform
+  unsigned long long it = 0;
+  for (unsigned long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x, ++it) {  // CTA-uniform
+    const unsigned long long base = chunk * kChunkPts;
     float rx[U], ry[U], rz[U];
     bool have[U];
-    if (staged) {
-      // the CTA's U * 256 points (12 KB) come in as 768 coalesced 128-bit loads and are handed out from shared memory:
-      // a thread's own x/y/z sit 12 bytes apart, which as direct loads costs three 4-byte requests per point
-      const unsigned long long left = n - base;
-      const uint32_t n_floats = (uint32_t)(left < (unsigned long long)(kInsThreads * U) ? left : kInsThreads * U) * 3u;
-      const float4* src = reinterpret_cast<const float4*>(xyz + 3 * (first + base));
-      __syncthreads();  // the previous step's readers are done
-#pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        const uint32_t q = j * kInsThreads + threadIdx.x;  // float4 index inside the chunk
-        if (4 * q + 3 < n_floats) {
-          reinterpret_cast<float4*>(sh_xyz)[q] = __ldg(src + q);
-        } else {
-          for (uint32_t e = 4 * q; e < n_floats && e < 4 * q + 4; ++e) sh_xyz[e] = __ldg(xyz + 3 * (first + base) + e);
-        }
-      }
-      __syncthreads();
+    if (chunk < n_full) {
+      const int st = (int)(it % kFoldStages);
+      mbar_wait(&sh_full[st], (uint32_t)((it / kFoldStages) & 1));
+      const float* sp = sh_xyz[st];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const uint32_t k = u * kInsThreads + threadIdx.x;
-        have[u] = base + k < n;
-        if (have[u]) { rx[u] = sh_xyz[3 * k]; ry[u] = sh_xyz[3 * k + 1]; rz[u] = sh_xyz[3 * k + 2]; }
+        have[u] = true;
+        rx[u] = sp[3 * k]; ry[u] = sp[3 * k + 1]; rz[u] = sp[3 * k + 2];
       }
-    } else {
+      __syncthreads();  // every thread holds its points in registers: the stage may be refilled
+      if (threadIdx.x == 0) {
+        const unsigned long long next = chunk + (unsigned long long)kFoldStages * gridDim.x;
+        if (next < n_full) issue(next, st);
+      }
+    } else {  // the partial last chunk of a frame, or an unaligned frame: plain loads
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const unsigned long long k = base + (unsigned long long)u * kInsThreads + threadIdx.x;
@@ -541,10 +561,10 @@ cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, co
     }
     // 4 points per thread and step. The grid is NOT divided among the frames: on a z-slab rank most frames belong to
     // other slabs and their CTAs retire after one read, leaving the SMs to the frame(s) that do the atomics
-    // ... but the whole grid stays within ~one wave of co-resident CTAs, so that a CTA runs several chunks and its warps'
-    // hit queues fill up across them before they are drained
-    int gx = grid_for(c, (longest + 3) / 4, 8);
-    const int per_frame = (c.sm_count * 8 + (int)n_frames - 1) / (int)n_frames;
+    // ... but the whole grid is ONE wave of co-resident CTAs (4 per SM: 62 registers, 46 KB of shared memory), so that a CTA
+    // runs many chunks: its bulk-copy ring stays full and its warps' hit queues fill up before they are drained
+    int gx = grid_for(c, (longest + 3) / 4, 4);
+    const int per_frame = (c.sm_count * 4 + (int)n_frames - 1) / (int)n_frames;
     if (gx > per_frame) gx = per_frame < 1 ? 1 : per_frame;
     return pdl_launch(k_update_logodds_frames, dim3((unsigned)gx, n_frames), kInsThreads, c.stream, c.pdl, m, xyz_d,
                       *by_value, delta);
