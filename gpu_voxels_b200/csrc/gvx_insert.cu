@@ -12,6 +12,8 @@
 // that holds the meaning bit, issued once per (voxel, meaning) group of a warp (__match_any_sync), and the
 // probabilistic log-odds update is a saturating add applied with one CAS per (voxel) group of a warp, so
 // results equal the sequential (race-free) semantics and are deterministic.
+#include <cmath>
+
 #include "gvx_internal.h"
 #include "gvx_sensor.cuh"
 #include "gvx_tma.cuh"
@@ -265,7 +267,7 @@ k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t*
   for (unsigned long long i = (unsigned long long)blockIdx.x * kInsThreads + threadIdx.x; i < n_round; i += stride) {
     bool live = false;
     uint64_t idx = 0;
-    if (i < n) {
+    if (i < n && i - prefix[find_cloud(prefix, n_frames, (uint32_t)i)] < slab * m.dz) {  // :569: a frame is cut at the voxel count
       const uint32_t f = find_cloud(prefix, n_frames, (uint32_t)i);
       const float* P = poses + 12 * (size_t)f;
       const bool sensor_inside = in_smem ? (bool)sh_inside[f]
@@ -304,7 +306,8 @@ k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t*
 // computed first: on a z-slab rank most points of a multi-sensor cloud belong to other slabs and are dropped after
 // three FMAs and one division.
 __global__ void __launch_bounds__(kInsThreads)
-k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_constant__ FramesByValue fv, int delta) {
+k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_constant__ FramesByValue fv, int delta,
+                        float z_lo, float z_hi) {
   pdl_wait();
   pdl_launch_dependents();
   const uint32_t f = fv.order[blockIdx.y];
@@ -313,8 +316,9 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
   for (int k = 0; k < 12; ++k) P[k] = fv.poses[12 * f + k];
   if (!(coord_to_voxel(P[3], m.side) < m.dx && coord_to_voxel(P[7], m.side) < m.dy && coord_to_voxel(P[11], m.side) < m.dz))
     return;  // sensor origin outside the map: the frame contributes nothing (VoxelMapOperations.hpp:577-580)
-  const unsigned long long first = fv.prefix[f], n = fv.prefix[f + 1] - fv.prefix[f];
   const uint64_t slab = (uint64_t)m.dx * m.dy;
+  const unsigned long long first = fv.prefix[f], n_frame = fv.prefix[f + 1] - fv.prefix[f], nvox = slab * m.dz;
+  const unsigned long long n = n_frame < nvox ? n_frame : nvox;  // the reference's loop bound, VoxelMapOperations.hpp:569
   // U points per thread and step, their loads issued together: with several frames per launch a thread runs many steps,
   // and one dependent load -> divide -> atomic chain per step would leave the SMs waiting on latency
   constexpr int U = 4;
@@ -448,9 +452,9 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
               idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
             }
           }
-        } else if (!isnan(wz)) {
-          const uint32_t cz = coord_to_voxel(wz, m.side);
-          if (cz >= m.z0 && cz < m.z1) {
+        } else if (wz >= z_lo && wz < z_hi) {  // == (cz >= m.z0 && cz < m.z1) for wz >= 0, exactly (fold_z_bound): the
+          const uint32_t cz = coord_to_voxel(wz, m.side);  // points of other slabs are dropped without a division
+          if (cz >= m.z0 && cz < m.z1) {  // always true (see above); kept so that no index can ever leave the slab
             const float wx = affine_row(P, rx[u], ry[u], rz[u]), wy = affine_row(P + 4, rx[u], ry[u], rz[u]);
             if (!(isnan(wx) || isnan(wy))) {
               const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side);
@@ -549,6 +553,20 @@ cudaError_t launch_raycast_free(const LaunchCtx& c, const MapView& m, const floa
   return cudaGetLastError();
 }
 
+// Smallest float w >= 0 whose voxel layer floor(w / side) is >= z. The device computes a layer as
+// (uint32)floorf(__fdiv_rn(w, side)) (coord_to_voxel); IEEE division, floorf and the conversion are all monotone in w, so
+// for every non-negative, non-NaN w:  layer(w) >= z  <=>  w >= fold_z_bound(z). The host's float division is the same
+// correctly rounded operation (this file is built with -ffp-contract=off, no fast-math), so the bound is found by
+// stepping single ulps around z * side. A z-slab rank tests lo <= wz < hi instead of dividing every point of the frame.
+static float fold_z_bound(uint32_t z, float side) {
+  if (z == 0) return 0.0f;
+  auto layer_ge = [&](float w) { return (double)floorf(w / side) >= (double)z; };
+  float w = (float)z * side;
+  for (int k = 0; k < 64 && layer_ge(w); ++k) w = nextafterf(w, -INFINITY);
+  for (int k = 0; k < 128 && !layer_ge(w); ++k) w = nextafterf(w, INFINITY);
+  return w;
+}
+
 cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, const float* xyz_d, uint64_t n,
                                         const uint32_t* prefix_d, const float* poses_d, uint32_t n_frames, int delta,
                                         const FramesByValue* by_value) {
@@ -567,7 +585,7 @@ cudaError_t launch_update_logodds_multi(const LaunchCtx& c, const MapView& m, co
     const int per_frame = (c.sm_count * 4 + (int)n_frames - 1) / (int)n_frames;
     if (gx > per_frame) gx = per_frame < 1 ? 1 : per_frame;
     return pdl_launch(k_update_logodds_frames, dim3((unsigned)gx, n_frames), kInsThreads, c.stream, c.pdl, m, xyz_d,
-                      *by_value, delta);
+                      *by_value, delta, fold_z_bound(m.z0, m.side), fold_z_bound(m.z1, m.side));
   }
   return pdl_launch(k_update_logodds_multi, dim3((unsigned)grid_for(c, n, 8)), kInsThreads, c.stream, c.pdl, m, xyz_d,
                     prefix_d, poses_d, n_frames, delta);

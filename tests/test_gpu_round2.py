@@ -291,3 +291,43 @@ def test_pinned_host_cloud_may_be_reused_when_the_call_returns(gv, oracle):
         m.insertPointCloud(pinned.numpy(), 7, check_outside=False)   # numpy view of pinned memory -> GVX_MEM_HOST
         pinned.fill_(float("nan"))                                   # the caller reuses its buffer at once
         assert np.array_equal(m.download().reshape(-1), want)
+
+
+# ---- the multi-frame fold's division-free slab test -----------------------------------------------------------------
+@pytest.mark.parametrize("side", [0.01, 0.025, 0.3, 1.0, 0.007])
+def test_fold_slab_filter_is_exact_at_layer_boundaries(gv, oracle, side):
+    """k_update_logodds_frames drops the points of other z-slabs with lo <= wz < hi (two floats found on the host by
+    stepping ulps, gvx_insert.cu fold_z_bound) instead of floor(wz / side): by monotonicity that is the same predicate.
+    Points a few ulps around EVERY layer boundary, slabs cut at awkward places: each slab must be byte-identical to its
+    slice of the oracle's unsharded map."""
+    dims = (8, 6, 37)
+    s32 = np.float32(side)
+    zs = []
+    for layer in range(0, dims[2] + 2):
+        w = np.float32(layer) * s32
+        cand = [w]
+        for _ in range(4):
+            cand.append(np.nextafter(cand[-1], np.float32(np.inf), dtype=np.float32))
+        lo = w
+        for _ in range(4):
+            lo = np.nextafter(lo, np.float32(-np.inf), dtype=np.float32)
+            cand.append(lo)
+        zs += cand
+    zs = np.asarray(zs, np.float32)
+    rng = np.random.Generator(np.random.PCG64(3))
+    pts = np.stack([rng.uniform(0, dims[0] * side, len(zs)), rng.uniform(0, dims[1] * side, len(zs)), zs], -1).astype(np.float32)
+    pts = np.concatenate([pts, rng.uniform(0, 1, size=(5000, 3)).astype(np.float32) * (np.asarray(dims) * side).astype(np.float32)])
+    pts[7] = np.nan
+    pose = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, 1, 0]], np.float32)   # world z == sensor z: bit-for-bit the values above
+    want = oracle.new_map(PROB, dims)
+    frames = [pts[: len(pts) // 2], pts[len(pts) // 2:]]
+    for f in frames:
+        oracle.update_logodds(want, dims, side, f, pose)
+    plane = dims[0] * dims[1]
+    for cuts in ([0, 37], [0, 1, 2, 36, 37], [0, 5, 11, 12, 20, 29, 37]):
+        for z0, z1 in zip(cuts[:-1], cuts[1:]):
+            m = gv.ProbVoxelMap(dims, side, slab=(z0, z1))
+            m.insertSensorDataMulti(frames, [pose, pose])
+            assert np.array_equal(m.download(), want[z0 * plane:z1 * plane]), (side, z0, z1)
+            bits, valid = m.summary()
+            assert valid and np.array_equal(bits, want[z0 * plane:z1 * plane] != -128)
