@@ -34,6 +34,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--dz", type=int, default=2048)
     ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--gran", type=int, default=0, help="cudaLimitMaxL2FetchGranularity (32/64/128; 0 = leave)")
+    ap.add_argument("--z0", type=int, default=0, help="first layer of the slab (z0 >= 2048: no point falls into it -> pure filter time)")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "prebin_probe.json"))
     a = ap.parse_args()
     torch.cuda.set_device(0)
@@ -41,12 +43,16 @@ def main():
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
     _lib.set_stream(stream.cuda_stream)
+    prev = C.c_int(0)
+    _lib.check(L.gvx_set_l2_fetch_granularity(a.gran, C.byref(prev)))
     dims = (B.C4_DIM,) * 3
     clouds = torch.from_numpy(np.concatenate([B.c4_cloud(k) for k in range(B.C4_CLOUDS)])).cuda()
     n = clouds.shape[0]
     sizes = np.full(B.C4_CLOUDS, B.C4_POINTS, np.uint32)
     poses = np.ascontiguousarray(np.tile(B.C4_POSE.reshape(-1), (B.C4_CLOUDS, 1)))
-    m = gv.ProbVoxelMap(dims, B.SIDE, slab=(0, a.dz))
+    if a.z0 >= B.C4_DIM:   # a slab ABOVE the cloud: every point is read, filtered and dropped
+        dims = (B.C4_DIM, B.C4_DIM, a.z0 + a.dz)
+    m = gv.ProbVoxelMap(dims, B.SIDE, slab=(a.z0, a.z0 + a.dz))
 
     def fold(pts):
         _lib.check(L.gvx_update_logodds_multi(m.handle, C.c_void_p(pts.data_ptr()), _lib.MEM_DEVICE,
@@ -70,7 +76,7 @@ def main():
         return {"median": ms[len(ms) // 2], "min": ms[0]}
 
     sorted_pts = bin_points(clouds)
-    res = {"points": n, "slab_layers": a.dz}
+    res = {"points": n, "slab_layers": a.dz, "l2_fetch_granularity": a.gran or prev.value, "l2_fetch_granularity_default": prev.value}
     for tag, pts in (("A_unsorted", clouds), ("B_presorted", sorted_pts)):
         m.clearMap()
         fold(pts); torch.cuda.synchronize()                      # first touch: every voxel still UNKNOWN
@@ -78,7 +84,16 @@ def main():
         res[tag + "_first_frame_ms"] = timed(lambda: fold(pts), 1)["median"]
         res[tag + "_steady_ms"] = timed(lambda: fold(pts), a.iters)   # later frames: the same voxels again
     res["S_binning_ms"] = timed(lambda: bin_points(clouds), a.iters)
+    # back to back: `iters` launches between ONE event pair (no per-launch event overhead)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(a.iters):
+        fold(clouds)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    res["A_unsorted_back_to_back_ms"] = e0.elapsed_time(e1) / a.iters
     # identical maps
+    dims = (B.C4_DIM,) * 3
     ma, mb = gv.ProbVoxelMap(dims, B.SIDE, slab=(0, 64)), gv.ProbVoxelMap(dims, B.SIDE, slab=(0, 64))
     for mm, pts in ((ma, clouds), (mb, sorted_pts)):
         for _ in range(3):

@@ -236,7 +236,7 @@ k_raycast_free(MapView m, const float* __restrict__ xyz, unsigned long long n, c
 // Same per-point arithmetic as k_update_logodds. Used when a z-slab rank folds the whole multi-sensor cloud and keeps
 // only its slab's points: one launch instead of one per frame.
 constexpr int kMaxFramesSmem = 64;
-constexpr int kFoldStages = 3;  // k_update_logodds_frames: ring of 12 KB point chunks filled by bulk copies
+constexpr int kFoldStages = 2;  // k_update_logodds_frames: per-warp ring of 1.5 KB point chunks filled by bulk copies
 constexpr int kFoldDrain = 128;  // k_update_logodds_frames: queued hits a warp applies at once (4 per lane)
 __global__ void __launch_bounds__(kInsThreads)
 k_update_logodds_multi(MapView m, const float* __restrict__ xyz, const uint32_t* __restrict__ prefix_g,
@@ -322,40 +322,50 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
   // U points per thread and step, their loads issued together: with several frames per launch a thread runs many steps,
   // and one dependent load -> divide -> atomic chain per step would leave the SMs waiting on latency
   constexpr int U = 4;
-  // A CTA's chunk of U * 256 points (12 KB) arrives as ONE bulk copy (cp.async.bulk, SASS UBLKCP) into a ring of
-  // kFoldStages shared-memory stages, issued by one thread kFoldStages chunks ahead and counted by an mbarrier: HBM keeps
-  // streaming while the CTA classifies the chunk before (a load -> __syncthreads -> compute loop left it idle half the
-  // time: on a z-slab rank, where 7 of 8 points are only read and dropped, the frame was filtered at 1.7 TB/s).
-  // A thread's own x/y/z sit 12 bytes apart and are handed out from shared memory.
-  __shared__ __align__(128) float sh_xyz[kFoldStages][kInsThreads * U * 3];
-  __shared__ __align__(8) uint64_t sh_full[kFoldStages];
-  constexpr uint32_t kChunkPts = kInsThreads * U, kChunkBytes = kChunkPts * 12;
+  // Every WARP owns a ring of kFoldStages shared-memory stages of 128 points (1.5 KB): lane 0 issues one bulk copy per
+  // stage (cp.async.bulk, SASS UBLKCP) kFoldStages chunks ahead, an mbarrier counts the bytes, the lanes then take their
+  // U points each (x/y/z sit 12 bytes apart: conflict-free stride-3 reads). HBM keeps streaming while the warp classifies
+  // the chunk before, and there is no __syncthreads anywhere: a warp that drains its hit queue (a multi-microsecond chain
+  // of DRAM misses) never stalls the other warps of its CTA. (A CTA-wide load -> __syncthreads -> compute loop filtered
+  // the frame at 1.7 TB/s on a z-slab rank, where 7 of 8 points are only read and dropped.)
+  constexpr int kWarps = kInsThreads / 32;
+  constexpr uint32_t kChunkPts = 32 * U, kChunkBytes = kChunkPts * 12;
+  __shared__ __align__(128) float sh_xyz[kWarps][kFoldStages][kChunkPts * 3];
+  __shared__ __align__(8) uint64_t sh_full[kWarps][kFoldStages];
+  const unsigned lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+  const int warp = threadIdx.x >> 5;
   // bulk copies need 16-byte aligned source chunks: the frame must start on a multiple of 4 points of a 16-byte aligned array
   const bool staged = ((first & 3ull) == 0) && ((reinterpret_cast<uintptr_t>(xyz) & 15) == 0);
   const unsigned long long n_chunks = (n + kChunkPts - 1) / kChunkPts, n_full = staged ? n / kChunkPts : 0;
+  const unsigned long long gw = (unsigned long long)blockIdx.x * kWarps + warp, n_warps = (unsigned long long)gridDim.x * kWarps;
   uint64_t policy = 0;
-  if (threadIdx.x == 0) {
-    for (int st = 0; st < kFoldStages; ++st) mbar_init(&sh_full[st], 1);
+  if (lane == 0) {
+    for (int st = 0; st < kFoldStages; ++st) mbar_init(&sh_full[warp][st], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
   }
-  __syncthreads();
-  auto issue = [&](unsigned long long chunk, int st) {  // thread 0 only; full chunks only
-    mbar_expect_tx(&sh_full[st], kChunkBytes);
-    bulk_load(sh_xyz[st], xyz + 3 * (first + chunk * kChunkPts), kChunkBytes, &sh_full[st], policy);
+  __syncwarp();
+  auto issue = [&](unsigned long long chunk, int st) {  // lane 0 only; full chunks only
+    mbar_expect_tx(&sh_full[warp][st], kChunkBytes);
+    bulk_load(sh_xyz[warp][st], xyz + 3 * (first + chunk * kChunkPts), kChunkBytes, &sh_full[warp][st], policy);
   };
-  if (threadIdx.x == 0) {
+  if (lane == 0) {
     for (int st = 0; st < kFoldStages; ++st) {
-      const unsigned long long chunk = blockIdx.x + (unsigned long long)st * gridDim.x;
+      const unsigned long long chunk = gw + (unsigned long long)st * n_warps;
       if (chunk < n_full) issue(chunk, st);
     }
   }
-  __shared__ unsigned long long sh_q[kInsThreads / 32][kFoldDrain + 32];  // per warp: < kFoldDrain waiting + one append
-  unsigned long long* wq = sh_q[threadIdx.x >> 5];
-  const unsigned lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
-  int qn = 0;  // warp-uniform number of queued hits
+  // Candidates are not classified where they are found. On a z-slab rank most lanes of a warp hold points of OTHER slabs:
+  // the cheap test (world z against the slab's two float bounds) runs for every point, but the rest -- two more IEEE
+  // divisions, bounds, index, and the read-modify-write chain (DRAM miss -> CAS -> maybe the summary word) -- costs a warp
+  // the same with 4 live lanes as with 32. Every warp appends its candidate POINTS to a small queue in shared memory and
+  // drains it 128 at a time, 4 per lane with all lanes busy and their loads issued together: instructions and latency
+  // chains follow the number of hits, not the number of points read.
+  __shared__ float sh_qx[kWarps][kFoldDrain + 32], sh_qy[kWarps][kFoldDrain + 32], sh_qz[kWarps][kFoldDrain + 32];
+  float *qx = sh_qx[warp], *qy = sh_qy[warp], *qz = sh_qz[warp];  // per warp: < kFoldDrain waiting + one append
+  int qn = 0;  // warp-uniform number of queued candidates
   int8_t* map = (int8_t*)m.data;
-  auto drain = [&](int cnt) {  // the last cnt (<= kFoldDrain) queued hits: entry j * 32 + lane of them for j = 0..3
+  auto drain = [&](int cnt) {  // the last cnt (<= kFoldDrain) queued candidates: entry j * 32 + lane of them for j = 0..3
     __syncwarp();
     constexpr int J = kFoldDrain / 32;
     bool lead[J];
@@ -367,11 +377,22 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
       lead[j] = false; id[j] = 0; tot[j] = 0;
       if (j * 32 >= cnt) continue;  // warp-uniform
       const int k = j * 32 + (int)lane;
-      const bool have_k = k < cnt;
-      if (have_k) id[j] = wq[qn - cnt + k];
+      bool live = false;
+      if (k < cnt) {  // the arithmetic of k_update_logodds, point by point
+        const float rx = qx[qn - cnt + k], ry = qy[qn - cnt + k], rz = qz[qn - cnt + k];
+        float wx, wy, wz;
+        sensor_to_world(P, rx, ry, rz, wx, wy, wz);
+        if (!(isnan(wx) || isnan(wy) || isnan(wz))) {
+          const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
+          if (cx < m.dx && cy < m.dy && cz >= m.z0 && cz < m.z1) {
+            live = true;
+            id[j] = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
+          }
+        }
+      }
       // equal voxels of one round fold into one saturating update (exact for same-sign deltas)
-      const unsigned peers = __match_any_sync(0xffffffffu, have_k ? id[j] : (~0ull - lane));
-      lead[j] = have_k && lane == (unsigned)(__ffs(peers) - 1);
+      const unsigned peers = __match_any_sync(0xffffffffu, live ? id[j] : (~0ull - lane));
+      lead[j] = live && lane == (unsigned)(__ffs(peers) - 1);
       tot[j] = delta * __popc(peers);
     }
     // the read-modify-writes of a lane go out together: loads of the old words, then the CAS of each, then (rare) the
@@ -402,29 +423,29 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
     __syncwarp();
   };
   unsigned long long it = 0;
-  for (unsigned long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x, ++it) {  // CTA-uniform
+  for (unsigned long long chunk = gw; chunk < n_chunks; chunk += n_warps, ++it) {  // warp-uniform
     const unsigned long long base = chunk * kChunkPts;
     float rx[U], ry[U], rz[U];
     bool have[U];
     if (chunk < n_full) {
       const int st = (int)(it % kFoldStages);
-      mbar_wait(&sh_full[st], (uint32_t)((it / kFoldStages) & 1));
-      const float* sp = sh_xyz[st];
+      mbar_wait(&sh_full[warp][st], (uint32_t)((it / kFoldStages) & 1));
+      const float* sp = sh_xyz[warp][st];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        const uint32_t k = u * kInsThreads + threadIdx.x;
+        const uint32_t k = u * 32 + lane;
         have[u] = true;
         rx[u] = sp[3 * k]; ry[u] = sp[3 * k + 1]; rz[u] = sp[3 * k + 2];
       }
-      __syncthreads();  // every thread holds its points in registers: the stage may be refilled
-      if (threadIdx.x == 0) {
-        const unsigned long long next = chunk + (unsigned long long)kFoldStages * gridDim.x;
+      __syncwarp();  // every lane holds its points in registers: the stage may be refilled
+      if (lane == 0) {
+        const unsigned long long next = chunk + (unsigned long long)kFoldStages * n_warps;
         if (next < n_full) issue(next, st);
       }
     } else {  // the partial last chunk of a frame, or an unaligned frame: plain loads
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        const unsigned long long k = base + (unsigned long long)u * kInsThreads + threadIdx.x;
+        const unsigned long long k = base + (unsigned long long)u * 32 + lane;
         have[u] = k < n;
         if (have[u]) {
           const float* p = xyz + 3 * (first + k);
@@ -432,43 +453,19 @@ k_update_logodds_frames(MapView m, const float* __restrict__ xyz, const __grid_c
         }
       }
     }
-    // Live hits are not applied where they are found: on a z-slab rank most lanes of a warp hold points of OTHER slabs,
-    // and a read-modify-write chain (DRAM miss -> CAS -> maybe the summary word) costs a warp the same latency with 4 live
-    // lanes as with 32. Every warp appends its live voxel indices to a small queue in shared memory and drains it 128 at a
-    // time -- 4 per lane, their loads issued together -- so the number of latency chains follows the number of hits.
+    // the cheap test, for every point read: a point whose world z is negative goes through the re-projection (it can end
+    // anywhere), every other point is a candidate iff z_lo <= wz < z_hi, which is (cz >= m.z0 && cz < m.z1) exactly
+    // (fold_z_bound); NaN fails both
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      bool live = false;
-      uint64_t idx = 0;
-      if (have[u]) {
-        float wz = affine_row(P + 8, rx[u], ry[u], rz[u]);
-        if (wz < 0.0f) {  // re-projection onto the floor moves x and y too: the full path
-          float wx, wy;
-          sensor_to_world(P, rx[u], ry[u], rz[u], wx, wy, wz);
-          if (!(isnan(wx) || isnan(wy) || isnan(wz))) {
-            const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side), cz = coord_to_voxel(wz, m.side);
-            if (cx < m.dx && cy < m.dy && cz >= m.z0 && cz < m.z1) {
-              live = true;
-              idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
-            }
-          }
-        } else if (wz >= z_lo && wz < z_hi) {  // == (cz >= m.z0 && cz < m.z1) for wz >= 0, exactly (fold_z_bound): the
-          const uint32_t cz = coord_to_voxel(wz, m.side);  // points of other slabs are dropped without a division
-          if (cz >= m.z0 && cz < m.z1) {  // always true (see above); kept so that no index can ever leave the slab
-            const float wx = affine_row(P, rx[u], ry[u], rz[u]), wy = affine_row(P + 4, rx[u], ry[u], rz[u]);
-            if (!(isnan(wx) || isnan(wy))) {
-              const uint32_t cx = coord_to_voxel(wx, m.side), cy = coord_to_voxel(wy, m.side);
-              if (cx < m.dx && cy < m.dy) {
-                live = true;
-                idx = (uint64_t)(cz - m.z0) * slab + (uint64_t)cy * m.dx + cx;
-              }
-            }
-          }
-        }
-      }
-      const unsigned bal = __ballot_sync(0xffffffffu, live);
+      const float wz = affine_row(P + 8, rx[u], ry[u], rz[u]);
+      const bool cand = have[u] && (wz < 0.0f || (wz >= z_lo && wz < z_hi));
+      const unsigned bal = __ballot_sync(0xffffffffu, cand);
       if (!bal) continue;  // a warp of another slab's points
-      if (live) wq[qn + __popc(bal & lt)] = idx;
+      if (cand) {
+        const int pos = qn + __popc(bal & lt);
+        qx[pos] = rx[u]; qy[pos] = ry[u]; qz[pos] = rz[u];
+      }
       qn += __popc(bal);
       if (qn >= kFoldDrain) drain(kFoldDrain);
     }
