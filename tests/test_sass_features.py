@@ -72,3 +72,23 @@ def test_scatter_kernels_use_the_reference_float_to_voxel_conversion(kernels):
     for fragment in ("k_insert", "k_update_logodds", "k_raycast_free", "k_list_keys"):
         for name, ops in _of(kernels, fragment).items():
             assert "F2I.U32.FLOOR.NTZ" in ops, name
+
+
+def test_multi_frame_fold_stages_points_with_bulk_copies_and_has_no_cta_barrier(kernels):
+    """k_update_logodds_frames: per-warp rings of point chunks filled by cp.async.bulk (UBLKCP) behind mbarriers, hits
+    queued in shared memory (STS/LDS) and applied with CAS -- and no BAR.SYNC: a warp that drains its queue must not
+    stall the other warps of its CTA"""
+    for name, ops in _of(kernels, "k_update_logodds_frames").items():
+        assert _has(ops, "UBLKCP") and _has(ops, "SYNCS.ARRIVE") and _has(ops, "SYNCS.PHASECHK"), name
+        assert _has(ops, "ATOMG.E.CAS") or _has(ops, "ATOM.E.CAS") or any("CAS" in o for o in ops), name
+        assert not _has(ops, "BAR.SYNC"), name
+        assert _has(ops, "MATCH.ANY"), name
+
+
+def test_noalloc_scratch_is_a_static_device_array():
+    """gvx_noalloc.cu: 16 MiB of .global, 256-byte aligned, inside the library (not a cudaMalloc)"""
+    from gpu_voxels_b200 import build as gvx_build
+    lib = gvx_build.build()
+    ptx_or_elf = subprocess.run([CUOBJDUMP, "-elf", lib], capture_output=True, text=True).stdout
+    hit = [l for l in ptx_or_elf.splitlines() if "g_noalloc_scratch" in l and "0x1000000" in l]
+    assert hit, "the 16 MiB scratch symbol is missing from the device ELF"
