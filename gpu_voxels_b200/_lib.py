@@ -47,6 +47,7 @@ SIGNATURES = {
     "gvx_map_upload": (C.c_int, [u64, vp]),
     "gvx_map_refresh_summary": (C.c_int, [u64]),
     "gvx_map_summary_download": (C.c_int, [u64, vp, u64, P(C.c_int)]),
+    "gvx_map_coarse_download": (C.c_int, [u64, vp, u64, P(C.c_int)]),
     "gvx_set_option": (C.c_int, [C.c_int, C.c_int]),
     "gvx_insert_points": (C.c_int, [u64, vp, u64, C.c_int, C.c_int, P(C.c_int)]),
     "gvx_insert_meta": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, u32, vp, P(C.c_int)]),

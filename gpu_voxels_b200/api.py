@@ -230,6 +230,15 @@ class GpuVoxelsMap:
         bits = np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool)
         return bits, bool(valid.value)
 
+    def coarse(self):
+        """-> (bool array, one entry per 4096 voxels of this slab; valid flag): the lazily built coarse mask"""
+        n = (self.numVoxels() + 4095) // 4096
+        words = np.zeros((n + 31) // 32, np.uint32)
+        valid = C.c_int(0)
+        _lib.check(self._L.gvx_map_coarse_download(self.handle, words.ctypes.data_as(C.c_void_p), len(words),
+                                                   C.byref(valid)))
+        return np.unpackbits(words.view(np.uint8), bitorder="little")[:n].astype(bool), bool(valid.value)
+
     # -- files (GV/voxelmap/TemplateVoxelMap.hpp:666-799): False + a logged error on failure, like the reference
     def writeToDisk(self, path):
         rc = self._L.gvx_map_write_file(self.handle, str(path).encode())
@@ -418,6 +427,7 @@ GVX_OPT_USE_SUMMARY = 1
 GVX_OPT_DH_CHECK_BITS = 2
 GVX_OPT_COLLIDE_TMA = 3
 GVX_OPT_PDL = 4
+GVX_OPT_USE_COARSE = 5
 REVOLUTE, PRISMATIC = 0, 1  # robot::DHJointType, GV/robot/dh_robot/KinematicLink.h:37-41
 
 

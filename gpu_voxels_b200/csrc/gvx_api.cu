@@ -126,6 +126,7 @@ int gvx_shutdown(void) {
   for (auto& kv : g.maps) {
     if (kv.second.owned && kv.second.data) cudaFree(kv.second.data);
     if (kv.second.occ) cudaFree(kv.second.occ);
+    if (kv.second.coarse) cudaFree(kv.second.coarse);
   }
   g.maps.clear();
   lists_free_all();
@@ -316,6 +317,8 @@ static int map_make(gvx_handle_t* h, int map_type, void* wrap, uint32_t dx, uint
       if (e != cudaSuccess) { cudaGetLastError(); cudaFree(m.data); return fail(GVX_ERR_NOMEM, "cudaMalloc(summary) failed: %s", cudaGetErrorString(e)); }
       GVX_CUDA(cudaMemsetAsync(m.occ, 0, m.occ_bytes(), g.stream));
       m.occ_valid = true;
+      // coarse mask (1 bit per 4096 voxels), allocated here so that no collide call ever allocates; built lazily
+      if (cudaMalloc((void**)&m.coarse, m.coarse_bytes()) != cudaSuccess) { cudaGetLastError(); m.coarse = nullptr; }
     }
   }
   const uint64_t id = g.next_handle++;
@@ -349,6 +352,7 @@ int gvx_map_destroy(gvx_handle_t h) {
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   if (m->owned) GVX_CUDA(cudaFree(m->data));
   if (m->occ) GVX_CUDA(cudaFree(m->occ));
+  if (m->coarse) GVX_CUDA(cudaFree(m->coarse));
   g.maps.erase(h);
   return GVX_OK;
 }
@@ -406,6 +410,7 @@ int gvx_map_device_ptr(gvx_handle_t h, void** data_d, uint64_t* first_voxel, uin
     // clearMap / clearBits / upload -- until gvx_map_refresh_summary
     m->occ_valid = false;
     m->raw_exported = true;
+    m->touch();
   }
   if (first_voxel) *first_voxel = (uint64_t)m->z0 * m->dx * m->dy;
   if (n_voxels) *n_voxels = m->n_voxels();
@@ -467,6 +472,7 @@ int gvx_map_refresh_summary(gvx_handle_t h) {
   if (!m->occ) return GVX_OK;  // wrapped memory: no summary
   GVX_CUDA(launch_env_bitmap(lctx(), m->data, m->type, m->n_voxels(), -127, m->occ));
   m->raw_exported = false;  // the caller declares its direct writes finished
+  m->touch();
   m->occ_valid = true;
   m->fallback_logged = false;
   return GVX_OK;
@@ -486,11 +492,27 @@ int gvx_map_summary_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, 
   return GVX_OK;
 }
 
+int gvx_map_coarse_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, int* valid) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(h);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
+  const bool ok = m->coarse && m->occ_valid && m->coarse_version == m->version;
+  if (valid) *valid = ok ? 1 : 0;
+  if (!ok || !words) return GVX_OK;
+  const uint64_t have = m->coarse_bytes() / 4;
+  if (n_words > have) n_words = have;
+  GVX_CUDA(cudaMemcpyAsync(words, m->coarse, n_words * 4, cudaMemcpyDeviceToHost, g.stream));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  return GVX_OK;
+}
+
 int gvx_set_option(int option, int value) {
   std::lock_guard<std::mutex> lk(g.mu);
   switch (option) {
     case GVX_OPT_USE_SUMMARY: g.use_summary = value != 0; return GVX_OK;
     case GVX_OPT_PDL: g.pdl = value != 0; return GVX_OK;
+    case GVX_OPT_USE_COARSE: g.use_coarse = value != 0; return GVX_OK;
     case GVX_OPT_COLLIDE_TMA:
       if (value < -1 || value > 5) return fail(GVX_ERR_INVALID, "GVX_OPT_COLLIDE_TMA must be in [-1, 5]");
       g.collide_tma = value; return GVX_OK;
@@ -724,8 +746,10 @@ static int collide_prepare(gvx_handle_t ha, gvx_handle_t hb, const int32_t off3[
 // lets UNKNOWN voxels of a ProbVoxelMap collide and writes 127 into them: they become known behind the summary's back.
 // Re-derive the "known" summary from the voxels on the stream (one pass; the threshold is an error case, not a path).
 static int fixup_summary_after_mark(Map* a, int8_t thr_i, bool mark) {
-  if (mark && thr_i == -128 && a->type == kMapProb && a->occ && a->occ_valid)
+  if (mark && thr_i == -128 && a->type == kMapProb && a->occ && a->occ_valid) {
     GVX_CUDA(launch_env_bitmap(lctx(), a->data, a->type, a->n_voxels(), -127, a->occ));
+    a->touch();
+  }
   return GVX_OK;
 }
 
@@ -740,9 +764,11 @@ int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32
   // inside the collide kernel when the peers' mailboxes are mapped, else through the host segment
   const bool global = shard_active() && a->sharded();
   const bool fused = global && g.shard_fused && g.peer_world > 1;
+  const uint32_t *ca = nullptr, *cb = nullptr;
+  if (off == 0 && ((rc = coarse_for_collide(a, &ca)) || (rc = coarse_for_collide(b, &cb)))) return rc;
   GVX_CUDA(launch_collide_map_map(fused ? lctx_allreduce() : lctx(), a->data, a->type, b->data, b->type, i0, i1, off,
                                   float_to_probability(thr), mark != 0, false, nullptr,
-                                  summary_for_collide(a), summary_for_collide(b)));
+                                  summary_for_collide(a), summary_for_collide(b), ca, cb));
   if ((rc = fixup_summary_after_mark(a, float_to_probability(thr), mark != 0))) return rc;
   if (count || global) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
@@ -764,9 +790,11 @@ int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const
   if (rc) return rc;
   LaunchCtx c = lctx();
   if (count_d) c.result_hmap_d = nullptr;  // the result stays on the device: nothing is written to mapped host memory
+  const uint32_t *ca = nullptr, *cb = nullptr;
+  if (off == 0 && ((rc = coarse_for_collide(a, &ca)) || (rc = coarse_for_collide(b, &cb)))) return rc;
   GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr),
                                   mark != 0, false, (unsigned long long*)count_d,
-                                  summary_for_collide(a), summary_for_collide(b)));
+                                  summary_for_collide(a), summary_for_collide(b), ca, cb));
   return fixup_summary_after_mark(a, float_to_probability(thr), mark != 0);
 }
 
@@ -797,9 +825,11 @@ int gvx_collide_map_map_allreduce(gvx_handle_t ha, gvx_handle_t hb, float thr, i
   if (rc) return rc;
   LaunchCtx c = lctx_allreduce();
   if (!count && count_d) c.result_hmap_d = nullptr;  // device-only result
+  const uint32_t *ca = nullptr, *cb = nullptr;
+  if ((rc = coarse_for_collide(a, &ca)) || (rc = coarse_for_collide(b, &cb))) return rc;
   GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, 0,
                                   float_to_probability(thr), mark != 0, false, (unsigned long long*)count_d,
-                                  summary_for_collide(a), summary_for_collide(b)));
+                                  summary_for_collide(a), summary_for_collide(b), ca, cb));
   if ((rc = fixup_summary_after_mark(a, float_to_probability(thr), mark != 0))) return rc;
   if (count) {
     GVX_CUDA(cudaStreamSynchronize(g.stream));
@@ -818,9 +848,11 @@ int gvx_collide_map_map_any(gvx_handle_t ha, gvx_handle_t hb, float thr, int* fl
   if (rc) return rc;
   LaunchCtx c = lctx();
   c.any = true;  // the kernels leave as soon as one CTA has found a collision; the count is then a lower bound
+  const uint32_t *ca = nullptr, *cb = nullptr;
+  if ((rc = coarse_for_collide(a, &ca)) || (rc = coarse_for_collide(b, &cb))) return rc;
   GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, 0, float_to_probability(thr),
                                   false, false, nullptr,
-                                  summary_for_collide(a), summary_for_collide(b)));
+                                  summary_for_collide(a), summary_for_collide(b), ca, cb));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   uint64_t any = g.result_h->count != 0;
   if (shard_active() && a->sharded() && (rc = shard_allreduce(&any, 0, 1))) return rc;  // OR over the ranks' slabs
@@ -873,6 +905,7 @@ int gvx_collide_map_map_bitcheck(gvx_handle_t ha, gvx_handle_t hb, uint32_t marg
   // contributes bits 0..3, and eBVM_FREE (not in the summary) reaches a swept-volume bit when margin + high >= 4
   const uint32_t* occ_b = summary_for_collide(b);
   const uint32_t* occ_a = (g.use_summary && occ_b && margin + high < 4) ? a->occ_if_valid() : nullptr;
+  if (mark) a->touch();  // a marked voxel that held only eBVM_FREE becomes occupied: the kernel updates a's summary
   GVX_CUDA(launch_collide_bitcheck(lctx(), a->data, b->data, i1 - i0, margin, sv_offset, mark != 0, occ_a, occ_b,
                                    a->occ_valid ? a->occ : nullptr, nullptr));
   GVX_CUDA(cudaStreamSynchronize(g.stream));

@@ -283,7 +283,8 @@ template <int AT, int BT, bool MARK, bool TYPES, bool ANY = false>
 __global__ void __launch_bounds__(kThreads, kCtasPerSm)
 k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const uint32_t* __restrict__ occ_a,
                    const uint32_t* __restrict__ occ_b, long long n, int thr, ReduceScratch* scratch, ResultBlock* out_d,
-                   ResultBlock* out_h, unsigned long long* count_out_d, PeerReduce pr) {
+                   ResultBlock* out_h, unsigned long long* count_out_d, PeerReduce pr,
+                   const uint32_t* __restrict__ coarse_a, const uint32_t* __restrict__ coarse_b) {
   constexpr int U = 4;
   pdl_wait();
   pdl_launch_dependents();  // at most kCtasPerSm CTAs per SM, all resident: the next kernel's CTAs queue up behind
@@ -319,6 +320,10 @@ k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const
     for (int u = 0; u < U; ++u) {
       const long long q = base + u * kThreads + threadIdx.x;
       ok[u] = q < n_quad;
+      // coarse masks (1 bit per 32 quads = per warp and step here, so the test is warp-uniform): a chunk that is empty in
+      // either map cannot hold a collision -- neither summary is read for it
+      if (ok[u] && coarse_a) { const long long cw = q >> 5; ok[u] = (__ldg(coarse_a + (cw >> 5)) >> (cw & 31)) & 1u; }
+      if (ok[u] && coarse_b) { const long long cw = q >> 5; ok[u] = (__ldg(coarse_b + (cw >> 5)) >> (cw & 31)) & 1u; }
       if (ok[u]) { ma[u] = ld_stream_u4(qa + q); mb[u] = ld_stream_u4(qb + q); }
     }
 #pragma unroll
@@ -413,15 +418,41 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
   finish_block<TYPES>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
 }
 
+// one warp per chunk of 32 summary quads (4096 voxels): any bit set -> the chunk's coarse bit
+__global__ void __launch_bounds__(kThreads)
+k_coarse_build(const uint4* __restrict__ occ, long long n_quads, uint32_t* __restrict__ coarse) {
+  const long long n_chunks = (n_quads + 31) >> 5;
+  const int lane = threadIdx.x & 31;
+  for (long long c = ((long long)blockIdx.x * kThreads + threadIdx.x) >> 5; c < n_chunks;
+       c += ((long long)gridDim.x * kThreads) >> 5) {
+    const long long q = (c << 5) + lane;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (q < n_quads) v = ld_stream_u4(occ + q);
+    const bool any = __any_sync(0xffffffffu, (v.x | v.y | v.z | v.w) != 0u);
+    if (any && lane == 0) atomicOr(coarse + (c >> 5), 1u << (c & 31));
+  }
+}
+
+cudaError_t launch_coarse_build(const LaunchCtx& c, const uint32_t* occ, long long n_quads, uint32_t* coarse) {
+  const long long n_chunks = (n_quads + 31) >> 5;
+  long long grid = (n_chunks * 32 + kThreads - 1) / kThreads;
+  const long long cap = (long long)c.sm_count * 8;
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  ++*c.launches;
+  k_coarse_build<<<(int)grid, kThreads, 0, c.stream>>>(reinterpret_cast<const uint4*>(occ), n_quads, coarse);
+  return cudaGetLastError();
+}
+
 template <int AT, int BT, bool ASUM, bool BSUM>
 static cudaError_t launch_summary(const LaunchCtx& c, int grid, uint8_t* a, const uint8_t* b, const uint32_t* occ_a,
                                   const uint32_t* occ_b, long long n, int thr, bool mark, bool types,
-                                  unsigned long long* out) {
+                                  unsigned long long* out, const uint32_t* coarse_a, const uint32_t* coarse_b) {
   cudaError_t err = cudaSuccess;
   if (c.any) {  // boolean collisionCheck: no write-back, no meaning mask, early exit
     if (ASUM && BSUM)
       err = pdl_launch(k_collide_summary2<AT, BT, false, false, true>, grid, kThreads, c.stream, c.pdl, a, b, occ_a, occ_b, n,
-                       thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
+                       thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer, coarse_a, coarse_b);
     else
       k_collide_summary<AT, BT, false, false, ASUM, BSUM, true><<<grid, kThreads, 0, c.stream>>>(
           a, b, occ_a, occ_b, n, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);
@@ -431,7 +462,7 @@ static cudaError_t launch_summary(const LaunchCtx& c, int grid, uint8_t* a, cons
   do {                                                                                                     \
     if (ASUM && BSUM)                                                                                      \
       err = pdl_launch(k_collide_summary2<AT, BT, M, T>, grid, kThreads, c.stream, c.pdl, a, b, occ_a, occ_b, n, thr, \
-                       c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);                             \
+                       c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer, coarse_a, coarse_b);         \
     else                                                                                                   \
       k_collide_summary<AT, BT, M, T, ASUM, BSUM><<<grid, kThreads, 0, c.stream>>>(                        \
           a, b, occ_a, occ_b, n, thr, c.scratch_d, c.result_d, c.result_hmap_d, out, c.peer);              \
@@ -470,7 +501,8 @@ static cudaError_t launch_voxelwise(const LaunchCtx& c, int grid, uint8_t* a, co
 
 cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, const void* b_, int b_type,
                                    int64_t i_begin, int64_t i_end, int64_t off, int8_t thr, bool mark, bool types,
-                                   unsigned long long* count_out_d, const uint32_t* occ_a, const uint32_t* occ_b) {
+                                   unsigned long long* count_out_d, const uint32_t* occ_a, const uint32_t* occ_b,
+                                   const uint32_t* coarse_a, const uint32_t* coarse_b) {
   uint8_t* a = (uint8_t*)a_;
   const uint8_t* b = (const uint8_t*)b_;
   if (i_end < i_begin) i_end = i_begin;
@@ -484,15 +516,15 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
   // threshold that converts to -128 (DefaultCollider::floatToProbability truncates: thr in (-0.0079, -0.0039], or a
   // wrapped value) makes UNKNOWN voxels collide in the reference (GV/voxel/DefaultCollider.hpp:51-80): stream those.
   if (thr == -128) {
-    if (!a_bit) occ_a = nullptr;
-    if (!b_bit) occ_b = nullptr;
+    if (!a_bit) occ_a = coarse_a = nullptr;
+    if (!b_bit) occ_b = coarse_b = nullptr;
   }
   const bool a_sum = occ_a != nullptr, b_sum = occ_b != nullptr;
   if (off == 0 && i_begin == 0 && (!a_bit || a_sum) && (!b_bit || b_sum) && (a_bit || b_bit || (a_sum && b_sum)) &&
       (((uintptr_t)a | (uintptr_t)b) & 15) == 0) {
     const long long units = (a_sum && b_sum) ? (n >> 7) : (n >> 5);  // quads of groups when both sides are summaries
     const int grid = balanced_grid((units + kThreads * 4 - 1) / (kThreads * 4), max_grid);
-#define GVX_SUM(AT, BT, AS, BS) return launch_summary<AT, BT, AS, BS>(c, grid, a, b, occ_a, occ_b, n, thr, mark, types, count_out_d)
+#define GVX_SUM(AT, BT, AS, BS) return launch_summary<AT, BT, AS, BS>(c, grid, a, b, occ_a, occ_b, n, thr, mark, types, count_out_d, coarse_a, coarse_b)
     if (a_bit && b_bit) GVX_SUM(kMapBit, kMapBit, true, true);
     if (a_bit) { if (b_sum) GVX_SUM(kMapBit, kMapProb, true, true); GVX_SUM(kMapBit, kMapProb, true, false); }
     if (b_bit) { if (a_sum) GVX_SUM(kMapProb, kMapBit, true, true); GVX_SUM(kMapProb, kMapBit, false, true); }

@@ -31,8 +31,17 @@ struct Map {
   // the writable raw device pointer has been handed out (gvx_map_device_ptr): the caller may write voxels at any time,
   // so NO library call re-validates the summary until gvx_map_refresh_summary says the writes are over
   bool raw_exported = false;
-  void revalidate() { if (occ && !raw_exported) occ_valid = true; }
+  void revalidate() { touch(); if (occ && !raw_exported) occ_valid = true; }
   bool fallback_logged = false;
+  // Coarse mask: 1 bit per kCoarseVoxels (4096) voxels = per 32 consecutive 128-bit words of the summary (what one warp
+  // of k_collide_summary2 loads per step); bit clear = that whole chunk of the summary is zero. Built lazily -- on the
+  // second collide of a map that has not been modified in between (a robot volume, a static environment) -- and valid
+  // only while `version` stands still: every entry point that can change the summary bumps it (touch()).
+  uint32_t* coarse = nullptr;
+  uint64_t version = 1, coarse_version = 0;
+  uint32_t quiet_collides = 0;
+  void touch() { ++version; quiet_collides = 0; }
+  size_t coarse_bytes() const { return (((occ_bytes() / 16 + 31) / 32 + 31) / 32) * 4 + 16; }
   size_t occ_bytes() const { return ((n_voxels() + 31) / 32 + 3) / 4 * 16; }  // padded to 16 B
   uint32_t* occ_if_valid() const { return occ_valid ? occ : nullptr; }
   uint64_t n_voxels() const { return (uint64_t)dx * dy * (z1 - z0); }
@@ -40,7 +49,8 @@ struct Map {
   bool sharded() const { return z0 != 0 || z1 != dz; }
   size_t voxel_bytes() const { return type == kMapProb ? 1 : kBitVoxelBytes; }
   size_t bytes() const { return n_voxels() * voxel_bytes(); }
-  MapView view() const { return MapView{data, type, dx, dy, dz, z0, z1, side, occ_valid ? occ : nullptr}; }
+  // the view handed to MUTATING kernels: taking it counts as a modification
+  MapView view() { touch(); return MapView{data, type, dx, dy, dz, z0, z1, side, occ_valid ? occ : nullptr}; }
 };
 
 // BitVectorVoxelList storage: SoA id / coord / voxel like the reference (GV/voxellist/TemplateVoxelList.h:250-252),
@@ -124,6 +134,7 @@ struct Context {
   bool pdl = true;       // GVX_OPT_PDL
   int collide_tma = -1;  // GVX_OPT_COLLIDE_TMA: -1 auto (TMA where it measured faster), 0 never, 1..5 always (shape k)
   bool use_summary = true;  // GVX_OPT_USE_SUMMARY: collide kernels may read occupancy summaries instead of voxels
+  bool use_coarse = true;   // GVX_OPT_USE_COARSE: ... and skip 4096-voxel chunks a map's coarse mask says are empty
   uint64_t launches = 0;
   uint64_t summary_fallbacks = 0;  // collides that streamed voxels because a library-owned map's summary was invalid
   uint64_t next_handle = 1;
@@ -198,6 +209,19 @@ inline const uint32_t* summary_for_collide(Map* m) {
     }
   }
   return m->occ_if_valid();
+}
+// the coarse mask a summary collide may use for map m (nullptr: none). Builds it on the stream when the map has been
+// collided twice without a modification in between; never allocates (the mask is allocated with the map).
+inline int coarse_for_collide(Map* m, const uint32_t** out) {
+  *out = nullptr;
+  if (!g.use_summary || !g.use_coarse || !m->coarse || !m->occ || !m->occ_valid) return GVX_OK;
+  if (m->coarse_version == m->version) { *out = m->coarse; return GVX_OK; }
+  if (++m->quiet_collides < 2) return GVX_OK;
+  GVX_CUDA(cudaMemsetAsync(m->coarse, 0, m->coarse_bytes(), g.stream));
+  GVX_CUDA(launch_coarse_build(lctx(), m->occ, (long long)(m->occ_bytes() / 16), m->coarse));
+  m->coarse_version = m->version;
+  *out = m->coarse;
+  return GVX_OK;
 }
 inline Map* find_map(gvx_handle_t h) {
   auto it = g.maps.find(h);

@@ -45,7 +45,10 @@ inline cudaError_t pdl_launch(void (*kernel)(KArgs...), dim3 grid, int block, cu
 cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a, int a_type, const void* b, int b_type,
                                    int64_t i_begin, int64_t i_end, int64_t off, int8_t thr, bool mark,
                                    bool types, unsigned long long* count_out_d, const uint32_t* occ_a = nullptr,
-                                   const uint32_t* occ_b = nullptr);
+                                   const uint32_t* occ_b = nullptr, const uint32_t* coarse_a = nullptr,
+                                   const uint32_t* coarse_b = nullptr);
+// coarse[c >> 5] bit c & 31 = "some bit of summary quads [32 c, 32 c + 32) is set"; coarse must be zeroed before
+cudaError_t launch_coarse_build(const LaunchCtx& c, const uint32_t* occ, long long n_quads, uint32_t* coarse);
 
 // the voxel-streaming collide fed by TMA bulk tiles (gvx_collide_tma.cu); applicable: off == 0, whole range, at least
 // one BitVectorVoxel side, 16-byte aligned bases, no meaning mask

@@ -152,6 +152,9 @@ int gvx_map_upload(gvx_handle_t h, const void* host_buf);
 int gvx_map_refresh_summary(gvx_handle_t h);
 /* test / debug: the summary words of this process's slab (bit i&31 of word i>>5 = voxel i) and whether it is valid */
 int gvx_map_summary_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, int* valid);
+/* test / debug: the coarse mask (GVX_OPT_USE_COARSE; bit c&31 of word c>>5 = voxels [4096 c, 4096 c + 4096) of this
+ * slab) and whether it is currently valid (built, and the map not modified since) */
+int gvx_map_coarse_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, int* valid);
 enum gvx_option {
   GVX_OPT_USE_SUMMARY = 1,   /* 0: always stream the voxels (the reference's access pattern) */
   GVX_OPT_DH_CHECK_BITS = 2, /* forward kinematics: sin/cos brackets of |v| * 2^-bits (default 50); smaller values send
@@ -160,10 +163,14 @@ enum gvx_option {
                                 shared-memory ring) instead of per-thread 256-bit loads; same results. -1 (default):
                                 where that measured faster (Bit x Prob on grids of >= 4 M voxels),
                                 0: never, 1..5: always, the value picks the tile x stages shape (1 = 512 voxels x 4) */
-  GVX_OPT_PDL = 4            /* 1 (default): the per-step kernels (log-odds frame update, summary collide) are started
+  GVX_OPT_PDL = 4,           /* 1 (default): the per-step kernels (log-odds frame update, summary collide) are started
                                 with programmatic dependent launch, so the launch ramp of one overlaps the tail of the
                                 kernel before it; they wait for that kernel's completion before touching memory, so
                                 results and ordering are those of a plain stream. 0: plain launches */
+  GVX_OPT_USE_COARSE = 5     /* 1 (default): a map that is collided twice without being modified in between (a robot
+                                volume, a static environment) gets a coarse mask, 1 bit per 4096 voxels, built from its
+                                summary on the stream; summary collides then skip chunks that are empty in either map
+                                without reading either summary. Any modifying call invalidates the mask. Same results */
 };
 int gvx_set_option(int option, int value);
 
