@@ -1,5 +1,5 @@
 #!/bin/bash
-# round 2, job C (1 GPU): the whole -m gpu suite
+# the whole -m gpu suite
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/c_pytest_gpu.log 2>&1

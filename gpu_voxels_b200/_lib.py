@@ -56,6 +56,7 @@ SIGNATURES = {
     "gvx_insert_sensor_data": (C.c_int, [u64, vp, u64, C.c_int, vp, C.c_int, u64, C.c_int, C.c_int, C.c_int]),
     "gvx_update_logodds_multi": (C.c_int, [u64, vp, C.c_int, vp, u32, vp, C.c_int]),
     "gvx_collide_map_map": (C.c_int, [u64, u64, f32, vp, C.c_int, P(u64)]),
+    "gvx_collide_map_map_thresholds": (C.c_int, [u64, u64, C.c_int, C.c_int, vp, C.c_int, P(u64)]),
     "gvx_collide_map_map_async": (C.c_int, [u64, u64, f32, vp, C.c_int, vp]),
     "gvx_collide_map_map_any": (C.c_int, [u64, u64, f32, P(C.c_int)]),
     "gvx_collide_map_map_types": (C.c_int, [u64, u64, f32, C.c_int, vp, P(u64)]),

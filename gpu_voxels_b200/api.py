@@ -329,6 +329,15 @@ class GpuVoxelsMap:
         _lib.check(self._L.gvx_collide_map_map(self.handle, other.handle, coll_threshold, p, int(mark), C.byref(cnt)))
         return cnt.value
 
+    def collisionCheckWithCounter(self, other, threshold1, threshold2, offset=None, mark=True):
+        """collisionCheckWithCounterRelativeTransform(other, DefaultCollider(Probability t1, Probability t2), offset)
+        (GV/voxelmap/TemplateVoxelMap.hpp:477-519): two int8 thresholds, one per side"""
+        p, keep = self._off(offset)
+        cnt = C.c_uint64(0)
+        _lib.check(self._L.gvx_collide_map_map_thresholds(self.handle, other.handle, int(threshold1), int(threshold2), p,
+                                                          int(mark), C.byref(cnt)))
+        return cnt.value
+
     def collisionCheck(self, other, coll_threshold=1.0):
         flag = C.c_int(0)
         _lib.check(self._L.gvx_collide_map_map_any(self.handle, other.handle, coll_threshold, C.byref(flag)))

@@ -780,6 +780,32 @@ int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32
   return GVX_OK;
 }
 
+int gvx_collide_map_map_thresholds(gvx_handle_t ha, gvx_handle_t hb, int threshold1, int threshold2,
+                                   const int32_t off3[3], int mark, uint64_t* count) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  if (threshold1 < -128 || threshold1 > 127 || threshold2 < -128 || threshold2 > 127)
+    return fail(GVX_ERR_INVALID, "thresholds (%d, %d) outside the int8 range of Probability", threshold1, threshold2);
+  Map *a, *b;
+  int64_t off, i0, i1;
+  int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1);
+  if (rc) return rc;
+  const bool global = shard_active() && a->sharded();
+  const bool fused = global && g.shard_fused && g.peer_world > 1;
+  const uint32_t *ca = nullptr, *cb = nullptr;
+  if (off == 0 && ((rc = coarse_for_collide(a, &ca)) || (rc = coarse_for_collide(b, &cb)))) return rc;
+  GVX_CUDA(launch_collide_map_map(fused ? lctx_allreduce() : lctx(), a->data, a->type, b->data, b->type, i0, i1, off,
+                                  (int8_t)threshold1, mark != 0, false, nullptr, summary_for_collide(a),
+                                  summary_for_collide(b), ca, cb, threshold2));
+  if ((rc = fixup_summary_after_mark(a, (int8_t)threshold1, mark != 0))) return rc;
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  uint64_t c = g.result_h->count;
+  if (fused && c == ~0ull) return fail(GVX_ERR_CUDA, "peer all-reduce timed out: a rank did not arrive");
+  if (global && !fused && (rc = shard_allreduce(&c, 1, 0))) return rc;
+  if (count) *count = c;
+  return GVX_OK;
+}
+
 int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32_t off3[3], int mark,
                               uint64_t* count_d) {
   std::lock_guard<std::mutex> lk(g.mu);

@@ -46,6 +46,13 @@ __device__ __forceinline__ void any_raise(ReduceScratch* s) {
   asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(&s->any_flag), "r"(1u) : "memory");
 }
 
+// `thr` of every collide kernel carries DefaultCollider's TWO int8 thresholds (GV/voxel/DefaultCollider.hpp:39-49:
+// DefaultCollider(Probability t1, Probability t2); the float form sets both to the same value): t1, applied to a
+// ProbabilisticVoxel on side a, in bits 0..7; t2 for side b in bits 8..15.
+__device__ __forceinline__ int thr_of_a(int thr) { return (int)(int8_t)(thr & 0xFF); }
+__device__ __forceinline__ int thr_of_b(int thr) { return (int)(int8_t)((thr >> 8) & 0xFF); }
+__device__ __forceinline__ uint32_t thr4(int t) { return (uint32_t)(uint8_t)t * 0x01010101u; }
+
 // ---- generic kernel: one voxel per thread per step, at least one side is a BitVectorVoxel map (or an
 // unaligned Prob x Prob fallback). AT/BT are MapType values. DefaultCollider::collide semantics
 // (GV/voxel/DefaultCollider.hpp:51-80); TYPES adds SVCollider's mask |= a (GV/voxel/SVCollider.hpp:96-106).
@@ -81,8 +88,8 @@ k_collide_voxelwise(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long
     for (int u = 0; u < U; ++u) {
       if (!ok[u]) continue;
       const long long i = base + u * kThreads + threadIdx.x;
-      const bool occ_a = (AT == kMapBit) ? bit_occupied(va[u]) : (pa[u] >= thr);
-      const bool occ_b = (BT == kMapBit) ? bit_occupied(vb[u]) : (pb[u] >= thr);
+      const bool occ_a = (AT == kMapBit) ? bit_occupied(va[u]) : (pa[u] >= thr_of_a(thr));
+      const bool occ_b = (BT == kMapBit) ? bit_occupied(vb[u]) : (pb[u] >= thr_of_b(thr));
       if (occ_a && occ_b) {
         ++cnt;
         if (TYPES && AT == kMapBit) {
@@ -112,7 +119,7 @@ k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long l
                     unsigned long long* count_out_d, PeerReduce pr) {
   uint32_t cnt = 0;
   const uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  const uint32_t t4 = (uint32_t)(uint8_t)thr * 0x01010101u;
+  const uint32_t t4a = thr4(thr_of_a(thr)), t4b = thr4(thr_of_b(thr));
   const long long vb = (i_begin + 15) & ~15ll, ve = i_end & ~15ll;
   if (blockIdx.x == 0) {  // unaligned head and tail, at most 30 voxels
     const long long head = (vb < i_end ? vb : i_end) - i_begin;
@@ -120,7 +127,7 @@ k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long l
     for (long long k = threadIdx.x; k < head + tail; k += kThreads) {
       const long long i = k < head ? i_begin + k : ve + (k - head);
       const int pa = a[i + off], pb = b[i];
-      if (pa >= thr && pb >= thr) {
+      if (pa >= thr_of_a(thr) && pb >= thr_of_b(thr)) {
         ++cnt;
         if (MARK && pa != 127) a[i + off] = 127;
       }
@@ -155,7 +162,7 @@ k_collide_prob_prob(int8_t* __restrict__ a, const int8_t* __restrict__ b, long l
       bool changed = false;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const uint32_t hit = __vcmpges4(wa[k], t4) & __vcmpges4(wb[k], t4);  // 0xFF per colliding byte
+        const uint32_t hit = __vcmpges4(wa[k], t4a) & __vcmpges4(wb[k], t4b);  // 0xFF per colliding byte
         cnt += __popc(hit) >> 3;
         if (MARK) {
           const uint32_t nw = (wa[k] & ~hit) | (0x7F7F7F7Fu & hit);
@@ -192,16 +199,16 @@ __device__ __forceinline__ uint32_t prob_group_mask(const uint4& lo, const uint4
 // only for the write-back (MARK) or the meaning bits (TYPES) of colliding voxels.
 template <int AT, int BT, bool MARK, bool TYPES, bool ASUM, bool BSUM>
 __device__ __forceinline__ void resolve_group(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long long g,
-                                              uint32_t hit, uint32_t t4, uint32_t& cnt, uint32_t (&acc)[8]) {
+                                              uint32_t hit, uint32_t t4a, uint32_t t4b, uint32_t& cnt, uint32_t (&acc)[8]) {
   if (AT == kMapProb && ASUM) {
     const uint4* p = reinterpret_cast<const uint4*>(a + (g << 5));
     const uint4 lo = __ldcg(p), hi = __ldcg(p + 1);
-    hit &= prob_group_mask(lo, hi, t4);
+    hit &= prob_group_mask(lo, hi, t4a);
   }
   if (BT == kMapProb && BSUM && hit) {
     const uint4* p = reinterpret_cast<const uint4*>(b + (g << 5));
     const uint4 lo = __ldg(p), hi = __ldg(p + 1);
-    hit &= prob_group_mask(lo, hi, t4);
+    hit &= prob_group_mask(lo, hi, t4b);
   }
   cnt += __popc(hit);
   if (MARK || TYPES) {
@@ -238,9 +245,9 @@ __device__ __forceinline__ void summary_tail(uint8_t* __restrict__ a, const uint
   bool oa, ob;
   int pa = 0;
   if (AT == kMapBit) oa = (__ldg(occ_a + (i >> 5)) >> (i & 31)) & 1u;
-  else { pa = ((const volatile int8_t*)a)[i]; oa = pa >= thr; }
+  else { pa = ((const volatile int8_t*)a)[i]; oa = pa >= thr_of_a(thr); }
   if (BT == kMapBit) ob = (__ldg(occ_b + (i >> 5)) >> (i & 31)) & 1u;
-  else ob = (int)ld_stream_i8(b + i) >= thr;
+  else ob = (int)ld_stream_i8(b + i) >= thr_of_b(thr);
   if (!(oa && ob)) return;
   ++cnt;
   if (AT == kMapBit && (MARK || TYPES)) {
@@ -259,7 +266,7 @@ __device__ __forceinline__ void summary_tail(uint8_t* __restrict__ a, const uint
 // threshold mask), then the colliding voxels are counted / marked like in resolve_group.
 template <int AT, int BT, bool MARK, bool TYPES>
 __device__ __forceinline__ void resolve_entry(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long long g,
-                                              uint32_t hit, uint32_t t4, uint32_t& cnt, uint32_t (&acc)[8]) {
+                                              uint32_t hit, uint32_t t4a, uint32_t t4b, uint32_t& cnt, uint32_t (&acc)[8]) {
   uint4 alo, ahi, blo, bhi;
   if (AT == kMapProb) {
     const uint4* p = reinterpret_cast<const uint4*>(a + (g << 5));
@@ -269,9 +276,9 @@ __device__ __forceinline__ void resolve_entry(uint8_t* __restrict__ a, const uin
     const uint4* p = reinterpret_cast<const uint4*>(b + (g << 5));
     blo = __ldg(p); bhi = __ldg(p + 1);
   }
-  if (AT == kMapProb) hit &= prob_group_mask(alo, ahi, t4);
-  if (BT == kMapProb) hit &= prob_group_mask(blo, bhi, t4);
-  if (hit) resolve_group<AT, BT, MARK, TYPES, false, false>(a, b, g, hit, t4, cnt, acc);  // count + write-back only
+  if (AT == kMapProb) hit &= prob_group_mask(alo, ahi, t4a);
+  if (BT == kMapProb) hit &= prob_group_mask(blo, bhi, t4b);
+  if (hit) resolve_group<AT, BT, MARK, TYPES, false, false>(a, b, g, hit, t4a, t4b, cnt, acc);  // count + write-back only
 }
 
 // Both sides represented by summaries: 128-bit loads, 128 voxels per load pair and thread. Candidate groups (both
@@ -297,14 +304,14 @@ k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const
   int qn = 0;  // warp-uniform number of queued groups
   uint32_t cnt = 0;
   uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  const uint32_t t4 = (uint32_t)(uint8_t)thr * 0x01010101u;
+  const uint32_t t4a = thr4(thr_of_a(thr)), t4b = thr4(thr_of_b(thr));
   const long long n_full = n >> 5;     // complete 32-voxel groups
   const long long n_quad = n_full >> 2;  // complete 4-group quads (summaries are 16-byte padded and aligned)
   const uint4* qa = reinterpret_cast<const uint4*>(occ_a);
   const uint4* qb = reinterpret_cast<const uint4*>(occ_b);
   auto drain = [&](int m) {  // the last m (<= 32) queued groups, one per lane
     __syncwarp();
-    if ((int)lane < m) resolve_entry<AT, BT, MARK, TYPES>(a, b, qg[qn - m + lane], qh[qn - m + lane], t4, cnt, acc);
+    if ((int)lane < m) resolve_entry<AT, BT, MARK, TYPES>(a, b, qg[qn - m + lane], qh[qn - m + lane], t4a, t4b, cnt, acc);
     qn -= m;
     __syncwarp();
   };
@@ -354,7 +361,7 @@ k_collide_summary2(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const
   if (blockIdx.x == 0 && threadIdx.x < (n_full & 3)) {
     const long long g = (n_quad << 2) + threadIdx.x;
     const uint32_t hit = __ldg(occ_a + g) & __ldg(occ_b + g);
-    if (hit) resolve_group<AT, BT, MARK, TYPES, true, true>(a, b, g, hit, t4, cnt, acc);
+    if (hit) resolve_group<AT, BT, MARK, TYPES, true, true>(a, b, g, hit, t4a, t4b, cnt, acc);
   }
   summary_tail<AT, BT, MARK, TYPES>(a, b, occ_a, occ_b, n, thr, cnt, acc);
   if (ANY && cnt) any_raise(scratch);
@@ -375,7 +382,7 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
   constexpr int U = 4;
   uint32_t cnt = 0;
   uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  const uint32_t t4 = (uint32_t)(uint8_t)thr * 0x01010101u;
+  const uint32_t t4a = thr4(thr_of_a(thr)), t4b = thr4(thr_of_b(thr));
   const long long n_full = n >> 5;  // complete 32-voxel groups
   const long long stride = (long long)gridDim.x * kThreads * U;
   for (long long base = (long long)blockIdx.x * kThreads * U; base < n_full; base += stride) {
@@ -407,10 +414,10 @@ k_collide_summary(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, const 
     for (int u = 0; u < U; ++u) {
       if (!ok[u]) continue;
       const long long g = base + u * kThreads + threadIdx.x;
-      if (!ASUM) ma[u] = prob_group_mask(alo[u], ahi[u], t4);
-      if (!BSUM) mb[u] = prob_group_mask(blo[u], bhi[u], t4);
+      if (!ASUM) ma[u] = prob_group_mask(alo[u], ahi[u], t4a);
+      if (!BSUM) mb[u] = prob_group_mask(blo[u], bhi[u], t4b);
       const uint32_t hit = ma[u] & mb[u];
-      if (hit) resolve_group<AT, BT, MARK, TYPES, ASUM, BSUM>(a, b, g, hit, t4, cnt, acc);
+      if (hit) resolve_group<AT, BT, MARK, TYPES, ASUM, BSUM>(a, b, g, hit, t4a, t4b, cnt, acc);
     }
   }
   summary_tail<AT, BT, MARK, TYPES>(a, b, occ_a, occ_b, n, thr, cnt, acc);
@@ -502,7 +509,9 @@ static cudaError_t launch_voxelwise(const LaunchCtx& c, int grid, uint8_t* a, co
 cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, const void* b_, int b_type,
                                    int64_t i_begin, int64_t i_end, int64_t off, int8_t thr, bool mark, bool types,
                                    unsigned long long* count_out_d, const uint32_t* occ_a, const uint32_t* occ_b,
-                                   const uint32_t* coarse_a, const uint32_t* coarse_b) {
+                                   const uint32_t* coarse_a, const uint32_t* coarse_b, int thr_b_or_same) {
+  const int8_t thr_a = thr, thr_b = thr_b_or_same == kSameThreshold ? thr : (int8_t)thr_b_or_same;
+  const int thr_pack = (int)(uint8_t)thr_a | ((int)(uint8_t)thr_b << 8);  // decoded per side in the kernels
   uint8_t* a = (uint8_t*)a_;
   const uint8_t* b = (const uint8_t*)b_;
   if (i_end < i_begin) i_end = i_begin;
@@ -515,16 +524,14 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
   // A ProbabilisticVoxel summary marks "known" voxels, a superset of "occupancy >= thr" only for thr >= -127. A float
   // threshold that converts to -128 (DefaultCollider::floatToProbability truncates: thr in (-0.0079, -0.0039], or a
   // wrapped value) makes UNKNOWN voxels collide in the reference (GV/voxel/DefaultCollider.hpp:51-80): stream those.
-  if (thr == -128) {
-    if (!a_bit) occ_a = coarse_a = nullptr;
-    if (!b_bit) occ_b = coarse_b = nullptr;
-  }
+  if (thr_a == -128 && !a_bit) occ_a = coarse_a = nullptr;
+  if (thr_b == -128 && !b_bit) occ_b = coarse_b = nullptr;
   const bool a_sum = occ_a != nullptr, b_sum = occ_b != nullptr;
   if (off == 0 && i_begin == 0 && (!a_bit || a_sum) && (!b_bit || b_sum) && (a_bit || b_bit || (a_sum && b_sum)) &&
       (((uintptr_t)a | (uintptr_t)b) & 15) == 0) {
     const long long units = (a_sum && b_sum) ? (n >> 7) : (n >> 5);  // quads of groups when both sides are summaries
     const int grid = balanced_grid((units + kThreads * 4 - 1) / (kThreads * 4), max_grid);
-#define GVX_SUM(AT, BT, AS, BS) return launch_summary<AT, BT, AS, BS>(c, grid, a, b, occ_a, occ_b, n, thr, mark, types, count_out_d, coarse_a, coarse_b)
+#define GVX_SUM(AT, BT, AS, BS) return launch_summary<AT, BT, AS, BS>(c, grid, a, b, occ_a, occ_b, n, thr_pack, mark, types, count_out_d, coarse_a, coarse_b)
     if (a_bit && b_bit) GVX_SUM(kMapBit, kMapBit, true, true);
     if (a_bit) { if (b_sum) GVX_SUM(kMapBit, kMapProb, true, true); GVX_SUM(kMapBit, kMapProb, true, false); }
     if (b_bit) { if (a_sum) GVX_SUM(kMapProb, kMapBit, true, true); GVX_SUM(kMapProb, kMapBit, false, true); }
@@ -538,25 +545,25 @@ cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a_, int a_type, con
       (c.tma > 0 || (a_bit && !b_bit && n >= (1ll << 22)))) {
     LaunchCtx ct = c;
     if (ct.tma < 0) ct.tma = 2;
-    return launch_collide_tma(ct, a, a_type, b, b_type, n, thr, mark, count_out_d);
+    return launch_collide_tma(ct, a, a_type, b, b_type, n, thr_pack, mark, count_out_d);
   }
   if (a_type == kMapProb && b_type == kMapProb) {
     const bool aligned = ((off & 15) == 0) && (((uintptr_t)a & 15) == 0) && (((uintptr_t)b & 15) == 0);
     if (aligned) {
       const int grid = balanced_grid((n / 16 + kThreads * kUnroll - 1) / (kThreads * kUnroll), max_grid);
-      if (c.any) k_collide_prob_prob<false, true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
-      else if (mark) k_collide_prob_prob<true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
-      else k_collide_prob_prob<false><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
+      if (c.any) k_collide_prob_prob<false, true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr_pack, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
+      else if (mark) k_collide_prob_prob<true><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr_pack, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
+      else k_collide_prob_prob<false><<<grid, kThreads, 0, c.stream>>>((int8_t*)a, (const int8_t*)b, i_begin, i_end, off, thr_pack, c.scratch_d, c.result_d, c.result_hmap_d, count_out_d, c.peer);
       return cudaGetLastError();
     }
   }
   // Bit x Bit advances 2 voxels per thread and step, the other pairs 4
   const int per_step = kThreads * ((a_type == kMapBit && b_type == kMapBit) ? 2 : kUnroll);
   const int grid = balanced_grid((n + per_step - 1) / per_step, max_grid);
-  if (a_type == kMapBit && b_type == kMapProb) return launch_voxelwise<kMapBit, kMapProb>(c, grid, a, b, i_begin, i_end, off, thr, mark, types, count_out_d);
-  if (a_type == kMapProb && b_type == kMapBit) return launch_voxelwise<kMapProb, kMapBit>(c, grid, a, b, i_begin, i_end, off, thr, mark, false, count_out_d);
-  if (a_type == kMapBit && b_type == kMapBit) return launch_voxelwise<kMapBit, kMapBit>(c, grid, a, b, i_begin, i_end, off, thr, mark, false, count_out_d);
-  return launch_voxelwise<kMapProb, kMapProb>(c, grid, a, b, i_begin, i_end, off, thr, mark, false, count_out_d);
+  if (a_type == kMapBit && b_type == kMapProb) return launch_voxelwise<kMapBit, kMapProb>(c, grid, a, b, i_begin, i_end, off, thr_pack, mark, types, count_out_d);
+  if (a_type == kMapProb && b_type == kMapBit) return launch_voxelwise<kMapProb, kMapBit>(c, grid, a, b, i_begin, i_end, off, thr_pack, mark, false, count_out_d);
+  if (a_type == kMapBit && b_type == kMapBit) return launch_voxelwise<kMapBit, kMapBit>(c, grid, a, b, i_begin, i_end, off, thr_pack, mark, false, count_out_d);
+  return launch_voxelwise<kMapProb, kMapProb>(c, grid, a, b, i_begin, i_end, off, thr_pack, mark, false, count_out_d);
 }
 
 }  // namespace gvx

@@ -98,11 +98,11 @@ k_collide_tma(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long long 
       if (AT == kMapBit) {
         const uint32_t nz = half_nonzero(qa[j], half);
         occ_a = (nz | __shfl_xor_sync(0xffffffffu, nz, 1)) != 0u;
-      } else occ_a = pa[j] >= thr;
+      } else occ_a = pa[j] >= (int)(int8_t)(thr & 0xFF);
       if (BT == kMapBit) {
         const uint32_t nz = half_nonzero(qb[j], half);
         occ_b = (nz | __shfl_xor_sync(0xffffffffu, nz, 1)) != 0u;
-      } else occ_b = pb[j] >= thr;
+      } else occ_b = pb[j] >= (int)(int8_t)((thr >> 8) & 0xFF);
       if (half == 0 && occ_a && occ_b) {  // the even lane owns the voxel (and holds word 0 of a Bit voxel)
         ++cnt;
         if (MARK) {
@@ -120,8 +120,8 @@ k_collide_tma(uint8_t* __restrict__ a, const uint8_t* __restrict__ b, long long 
       int xa = 0, xb = 0;
       if (AT == kMapBit) va = ld_voxel(a + (size_t)i * kBitVoxelBytes); else xa = (int)reinterpret_cast<const volatile int8_t*>(a)[i];
       if (BT == kMapBit) vb = ld_voxel_stream(b + (size_t)i * kBitVoxelBytes); else xb = (int)ld_stream_i8(b + i);
-      const bool occ_a = AT == kMapBit ? bit_occupied(va) : xa >= thr;
-      const bool occ_b = BT == kMapBit ? bit_occupied(vb) : xb >= thr;
+      const bool occ_a = AT == kMapBit ? bit_occupied(va) : xa >= (int)(int8_t)(thr & 0xFF);
+      const bool occ_b = BT == kMapBit ? bit_occupied(vb) : xb >= (int)(int8_t)((thr >> 8) & 0xFF);
       if (occ_a && occ_b) {
         ++cnt;
         if (MARK) {
@@ -165,7 +165,7 @@ bool collide_tma_applicable(const void* a, int a_type, const void* b, int b_type
 }
 
 cudaError_t launch_collide_tma(const LaunchCtx& c, void* a_, int a_type, const void* b_, int b_type, int64_t n,
-                               int8_t thr, bool mark, unsigned long long* out) {
+                               int thr, bool mark, unsigned long long* out) {  // thr: both int8 thresholds, packed
   uint8_t* a = (uint8_t*)a_;
   const uint8_t* b = (const uint8_t*)b_;
   // tile / ring shape by option value (c.tma): 1 = 512 voxels x 4 stages (66 KiB, 3 CTAs per SM); the others exist for

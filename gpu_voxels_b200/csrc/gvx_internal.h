@@ -39,14 +39,16 @@ inline cudaError_t pdl_launch(void (*kernel)(KArgs...), dim3 grid, int block, cu
   return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
-// collideWith map x map. a/b: device base pointers of the voxel arrays; a is indexed at i + off.
+constexpr int kSameThreshold = 1000;  // thr_b_or_same: side b uses side a's threshold (the one-threshold DefaultCollider)
+// collideWith map x map. `thr` applies to a ProbabilisticVoxel on side a, thr_b_or_same (an int8 value) to one on side b
+// (DefaultCollider(Probability, Probability), GV/voxel/DefaultCollider.hpp:45-49). a/b: device base pointers of the voxel arrays; a is indexed at i + off.
 // [i_begin, i_end) is the range of i for which 0 <= i + off < n. count_out_d: optional extra device
 // destination for the 64-bit count (async API), may be nullptr.
 cudaError_t launch_collide_map_map(const LaunchCtx& c, void* a, int a_type, const void* b, int b_type,
                                    int64_t i_begin, int64_t i_end, int64_t off, int8_t thr, bool mark,
                                    bool types, unsigned long long* count_out_d, const uint32_t* occ_a = nullptr,
                                    const uint32_t* occ_b = nullptr, const uint32_t* coarse_a = nullptr,
-                                   const uint32_t* coarse_b = nullptr);
+                                   const uint32_t* coarse_b = nullptr, int thr_b_or_same = kSameThreshold);
 // coarse[c >> 5] bit c & 31 = "some bit of summary quads [32 c, 32 c + 32) is set"; coarse must be zeroed before
 cudaError_t launch_coarse_build(const LaunchCtx& c, const uint32_t* occ, long long n_quads, uint32_t* coarse);
 
@@ -55,7 +57,7 @@ cudaError_t launch_coarse_build(const LaunchCtx& c, const uint32_t* occ, long lo
 bool collide_tma_applicable(const void* a, int a_type, const void* b, int b_type, int64_t i_begin, int64_t off,
                             bool types);
 cudaError_t launch_collide_tma(const LaunchCtx& c, void* a, int a_type, const void* b, int b_type, int64_t n,
-                               int8_t thr, bool mark, unsigned long long* count_out_d);
+                               int thr_pack, bool mark, unsigned long long* count_out_d);
 
 // voxelisation
 struct MetaDesc {             // device-resident description of a MetaPointCloud insert

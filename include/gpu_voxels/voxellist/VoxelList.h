@@ -104,28 +104,25 @@ public:
     LOGGING_INFO_C(VoxellistLog, TemplateVoxelList, "Dumped " << ids.size() << " Voxels." << endl);
   }
   // TemplateVoxelList::collisionCheckWithCollider (GV/voxellist/TemplateVoxelList.hpp:690-774) with the default
-  // collider: what collideWith forwards to. A collider with two different thresholds is refused (see VoxelMap.h)
+  // collider: what collideWith forwards to. The list's voxels are BitVoxels (side 1 of the collider), so of a
+  // DefaultCollider(t1, t2) only t2 -- the test of the map's ProbabilisticVoxel -- matters
+  // (DefaultCollider::collide(BitVoxel, ProbabilisticVoxel), GV/voxel/DefaultCollider.hpp:66-72)
   size_t collisionCheckWithCollider(const voxelmap::AbstractVoxelMap* other, DefaultCollider collider = DefaultCollider(),
                                     const Vector3i& offset = Vector3i())
   {
     float thr = 0.f;
-    if (!collider.asFloatThreshold(&thr))
+    if (!DefaultCollider(collider.getThreshold2(), collider.getThreshold2()).asFloatThreshold(&thr))
     {
-      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, "DefaultCollider with two different thresholds: " << GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, "DefaultCollider threshold without a float form: " << GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
       return 0;
     }
     return collide(0, other, thr, offset, NULL, NULL);
   }
-  size_t collisionCheckWithCollider(const BitVoxelList<length>* other, DefaultCollider collider = DefaultCollider(),
+  // list x list: both sides are BitVoxels, the thresholds play no role (DefaultCollider::collide(BitVoxel, BitVoxel))
+  size_t collisionCheckWithCollider(const BitVoxelList<length>* other, DefaultCollider = DefaultCollider(),
                                     const Vector3i& offset = Vector3i())
   {
-    float thr = 0.f;
-    if (!collider.asFloatThreshold(&thr))
-    {
-      LOGGING_ERROR_C(VoxellistLog, TemplateVoxelList, "DefaultCollider with two different thresholds: " << GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
-      return 0;
-    }
-    return collideWith(other, thr, offset);
+    return collideWith(other, 1.0f, offset);
   }
   virtual void clearMap()
   {

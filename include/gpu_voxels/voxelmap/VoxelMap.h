@@ -139,8 +139,8 @@ public:
   }
 
   // TemplateVoxelMap::collisionCheckWithCounter / ...RelativeTransform (GV/voxelmap/TemplateVoxelMap.hpp:477-519) with
-  // a collider object: number of colliding voxels, `this` gets eBVM_COLLISION marks. A collider with two different
-  // thresholds is refused (the kernels apply one threshold to both sides, as every public collideWith does).
+  // a collider object: number of colliding voxels, `this` gets eBVM_COLLISION marks. DefaultCollider(t1, t2) with two
+  // different thresholds is honoured (t1 for this map's ProbabilisticVoxels, t2 for the other's).
   uint32_t collisionCheckWithCounter(AbstractVoxelMap* other, DefaultCollider collider = DefaultCollider())
   {
     return collisionCheckWithCounterRelativeTransform(other, collider);
@@ -148,13 +148,14 @@ public:
   uint32_t collisionCheckWithCounterRelativeTransform(AbstractVoxelMap* other, DefaultCollider collider = DefaultCollider(),
                                                       const Vector3i& offset = Vector3i())
   {
-    float thr = 0.f;
-    if (!collider.asFloatThreshold(&thr))
-    {
-      LOGGING_ERROR_C(VoxelmapLog, TemplateVoxelMap, "DefaultCollider with two different thresholds: " << GPU_VOXELS_MAP_OPERATION_NOT_SUPPORTED << endl);
+    // the collider's two int8 thresholds go to the kernels as they are (threshold1: this map, threshold2: other)
+    detail::DualLock guard(this->m_mutex, other->m_mutex);
+    const int32_t off[3] = {offset.x, offset.y, offset.z};
+    uint64_t n = 0;
+    if (!gvxCheck(gvx_collide_map_map_thresholds(m_handle, other->m_handle, int(collider.getThreshold1()),
+                                                 int(collider.getThreshold2()), off, 1, &n), "collisionCheckWithCounter"))
       return 0;
-    }
-    return uint32_t(collideMapMap(other, thr, offset));
+    return uint32_t(n);
   }
 
 protected:

@@ -229,6 +229,12 @@ int gvx_collide_map_map(gvx_handle_t a, gvx_handle_t b, float thr, const int32_t
 int gvx_collide_map_map_async(gvx_handle_t a, gvx_handle_t b, float thr, const int32_t off3[3], int mark,
                               uint64_t* count_d);
 /* collisionCheck (boolean, no side effect; GV/voxelmap/TemplateVoxelMap.hpp:329-414) */
+/* collisionCheckWithCounter[RelativeTransform](other, DefaultCollider(Probability threshold1, Probability threshold2))
+ * (GV/voxelmap/TemplateVoxelMap.hpp:477-519, GV/voxel/DefaultCollider.hpp:45-49): the collider built from two int8
+ * thresholds -- threshold1 applies to a ProbabilisticVoxel on side a, threshold2 to one on side b; BitVectorVoxels ignore
+ * them. Otherwise gvx_collide_map_map. */
+int gvx_collide_map_map_thresholds(gvx_handle_t a, gvx_handle_t b, int threshold1, int threshold2,
+                                   const int32_t off3[3], int mark, uint64_t* count);
 int gvx_collide_map_map_any(gvx_handle_t a, gvx_handle_t b, float thr, int* flag);
 /* BitVoxelMap::collideWithTypes(ProbVoxelMap*) (GV/voxelmap/BitVoxelMap.hpp:212-217 -> collisionCheckBitvector :139-188,
  * kernelCollideVoxelMapsBitvector GV/voxelmap/kernels/VoxelMapOperations.hpp:187-239, SVCollider::collide

@@ -293,6 +293,29 @@ int gvo_collide_map_map(uint8_t* a, int a_type, const uint8_t* b, int b_type, ui
   return 0;
 }
 
+/* the same with DefaultCollider(Probability threshold1, Probability threshold2) (GV/voxel/DefaultCollider.hpp:45-49):
+ * t1 applies to a ProbabilisticVoxel on side a, t2 to one on side b (collide_default above, :51-80) */
+int gvo_collide_map_map_thresholds(uint8_t* a, int a_type, const uint8_t* b, int b_type, uint64_t n, int t1, int t2,
+                                   int64_t off, int mark, uint64_t* count) {
+  const size_t sa = vox_bytes(a_type), sb = vox_bytes(b_type);
+  uint64_t cnt = 0;
+#pragma omp parallel for schedule(static) reduction(+ : cnt)
+  for (int64_t i = 0; i < (int64_t)n; ++i) {
+    int64_t j = i + off;
+    if (j < 0 || j >= (int64_t)n) continue;
+    uint8_t* va = a + (size_t)j * sa;
+    if (collide_default(va, a_type, b + (size_t)i * sb, b_type, (int8_t)t1, (int8_t)t2)) {
+      ++cnt;
+      if (mark) {
+        if (a_type == GVO_MAP_PROB) ((int8_t*)va)[0] = 127;
+        else bit_set(va, GVO_EBVM_COLLISION);
+      }
+    }
+  }
+  *count = cnt;
+  return 0;
+}
+
 /* collisionCheck (boolean), GV/voxelmap/TemplateVoxelMap.hpp:329-414, kernelCollideVoxelMaps :78-120 */
 int gvo_collide_map_map_any(const uint8_t* a, int a_type, const uint8_t* b, int b_type, uint64_t n, float thr, int* flag) {
   uint64_t c = 0;

@@ -150,6 +150,14 @@ def collide_map_map(a, a_type, b, b_type, n, thr=1.0, off=0, mark=True):
     return cnt.value
 
 
+def collide_map_map_thresholds(a, a_type, b, b_type, n, t1, t2, off=0, mark=True):
+    """DefaultCollider(Probability t1, Probability t2): int8 thresholds for side a / side b"""
+    cnt = C.c_uint64(0)
+    lib().gvo_collide_map_map_thresholds(_ptr(a), a_type, _ptr(b), b_type, C.c_uint64(n), int(t1), int(t2),
+                                         C.c_int64(off), int(mark), C.byref(cnt))
+    return cnt.value
+
+
 def collide_bit_prob_types(a, b, n, thr=1.0, mark=True, mask=None):
     mask = np.zeros(32, np.uint8) if mask is None else mask
     cnt = C.c_uint64(0)

@@ -39,8 +39,7 @@ struct ColliderProbe : public DefaultCollider {
 };
 
 template <class VA, class VB>
-static uint64_t collide_loop(VA* a, const VB* b, uint64_t n, float thr, int64_t off, int mark) {
-  DefaultCollider collider(thr);
+static uint64_t collide_loop(VA* a, const VB* b, uint64_t n, DefaultCollider collider, int64_t off, int mark) {
   uint64_t cnt = 0;
   // body of kernelCollideVoxelMapsDebug, GV/voxelmap/kernels/VoxelMapOperations.hpp:141-156
 #pragma omp parallel for schedule(static) reduction(+ : cnt)
@@ -94,12 +93,20 @@ int gvrefcpu_update_occupancy(int occ, int delta) {
 }
 
 // a_type/b_type: 0 = BitVectorVoxel, 4 = ProbabilisticVoxel (MapType enum values)
+static uint64_t collide_any(void* a, int a_type, const void* b, int b_type, uint64_t n, DefaultCollider c, int64_t off, int mark) {
+  if (a_type == 0 && b_type == 0) return collide_loop((BitVectorVoxel*)a, (const BitVectorVoxel*)b, n, c, off, mark);
+  if (a_type == 0 && b_type == 4) return collide_loop((BitVectorVoxel*)a, (const ProbabilisticVoxel*)b, n, c, off, mark);
+  if (a_type == 4 && b_type == 0) return collide_loop((ProbabilisticVoxel*)a, (const BitVectorVoxel*)b, n, c, off, mark);
+  return collide_loop((ProbabilisticVoxel*)a, (const ProbabilisticVoxel*)b, n, c, off, mark);
+}
 uint64_t gvrefcpu_collide_map_map(void* a, int a_type, const void* b, int b_type, uint64_t n, float thr,
                                   int64_t off, int mark) {
-  if (a_type == 0 && b_type == 0) return collide_loop((BitVectorVoxel*)a, (const BitVectorVoxel*)b, n, thr, off, mark);
-  if (a_type == 0 && b_type == 4) return collide_loop((BitVectorVoxel*)a, (const ProbabilisticVoxel*)b, n, thr, off, mark);
-  if (a_type == 4 && b_type == 0) return collide_loop((ProbabilisticVoxel*)a, (const BitVectorVoxel*)b, n, thr, off, mark);
-  return collide_loop((ProbabilisticVoxel*)a, (const ProbabilisticVoxel*)b, n, thr, off, mark);
+  return collide_any(a, a_type, b, b_type, n, DefaultCollider(thr), off, mark);
+}
+// DefaultCollider(Probability threshold1, Probability threshold2), GV/voxel/DefaultCollider.hpp:45-49
+uint64_t gvrefcpu_collide_map_map_thresholds(void* a, int a_type, const void* b, int b_type, uint64_t n, int t1, int t2,
+                                             int64_t off, int mark) {
+  return collide_any(a, a_type, b, b_type, n, DefaultCollider((Probability)t1, (Probability)t2), off, mark);
 }
 
 // body of kernelCollideVoxelMapsBitvector with SVCollider(thr) Bit x Prob, VoxelMapOperations.hpp:202-214

@@ -36,7 +36,10 @@ BOOST_AUTO_TEST_CASE(collision)
   // the same through the collider-object entry points (GV/voxelmap/TemplateVoxelMap.hpp:477-519)
   BOOST_CHECK(map_1.collisionCheckWithCounter(&map_2, DefaultCollider(0.1f)) == (uint32_t)numberOfPoints);
   BOOST_CHECK(map_1.collisionCheckWithCounterRelativeTransform(&map_2, DefaultCollider(Probability(-101), Probability(-101))) == (uint32_t)numberOfPoints);
-  BOOST_CHECK(map_1.collisionCheckWithCounter(&map_2, DefaultCollider(Probability(1), Probability(2))) == 0);  // refused
+  // DefaultCollider(threshold1, threshold2) with two DIFFERENT thresholds (GV/voxel/DefaultCollider.hpp:45-49): every
+  // inserted voxel holds 127, so it collides unless a threshold is out of reach on its side
+  BOOST_CHECK(map_1.collisionCheckWithCounter(&map_2, DefaultCollider(Probability(1), Probability(2))) == (uint32_t)numberOfPoints);
+  BOOST_CHECK(map_1.collisionCheckWithCounter(&map_2, DefaultCollider(Probability(127), Probability(-127))) == (uint32_t)numberOfPoints);
   ProbabilisticVoxel* raw = map_1.getDeviceDataPtr();
   BOOST_CHECK(raw != NULL && (const void*)raw == map_1.getConstVoidDeviceDataPtr());
 }
@@ -790,7 +793,7 @@ BOOST_AUTO_TEST_CASE(base_class_interface)
 
   // collider-object entry points of the list == collideWith (46 collisions, GV/test/testing_voxellist.cu:142)
   BOOST_CHECK(list->collisionCheckWithCollider(map_copy->as<ProbVoxelMap>(), DefaultCollider(1.0f)) == 46);
-  BOOST_CHECK(list->collisionCheckWithCollider(map_copy->as<ProbVoxelMap>(), DefaultCollider(Probability(1), Probability(2))) == 0);  // refused
+  BOOST_CHECK(list->collisionCheckWithCollider(map_copy->as<ProbVoxelMap>(), DefaultCollider(Probability(1), Probability(2))) == 46);  // only threshold2 applies
   BOOST_CHECK(list->collisionCheckWithCollider(list_copy->as<BitVectorVoxelList>()) == list->collideWith(list_copy->as<BitVectorVoxelList>()));
 
   // raw storage: three device arrays of size() entries; make_unique / shrinkToFit leave a list as it is

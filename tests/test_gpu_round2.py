@@ -331,3 +331,41 @@ def test_fold_slab_filter_is_exact_at_layer_boundaries(gv, oracle, side):
             assert np.array_equal(m.download(), want[z0 * plane:z1 * plane]), (side, z0, z1)
             bits, valid = m.summary()
             assert valid and np.array_equal(bits, want[z0 * plane:z1 * plane] != -128)
+
+
+# ---- DefaultCollider(Probability threshold1, Probability threshold2) -----------------------------------------------------
+@pytest.mark.parametrize("pair", [(PROB, BIT), (BIT, PROB), (PROB, PROB), (BIT, BIT)])
+def test_two_threshold_collider(gv, oracle, pair):
+    """VERDICT r1 missing #7 (GV/voxel/DefaultCollider.hpp:45-49): threshold1 tests side a's ProbabilisticVoxels, threshold2
+    side b's; incl. -128 on one side only (that side's 'known' summary must be bypassed, the other side's stays in use),
+    offsets, marks, summaries on and off."""
+    dims, side = (67, 45, 39), 0.01
+    n = dims[0] * dims[1] * dims[2]
+    rng = np.random.Generator(np.random.PCG64(77))
+    vals = np.array([-128, -128, -128, -127, -60, -1, 0, 1, 40, 127], np.int8)
+    prob_a, prob_b = rng.choice(vals, size=n), rng.choice(vals, size=n)
+    bit_a = np.zeros((n, 32), np.uint8); bit_b = np.zeros((n, 32), np.uint8)
+    bit_a[rng.uniform(size=n) < 0.2, 5] = 2; bit_b[rng.uniform(size=n) < 0.2, 9] = 1
+    bit_a[rng.uniform(size=n) < 0.1, 0] |= 1; bit_b[rng.uniform(size=n) < 0.1, 0] |= 1   # eBVM_FREE does not occupy
+    src_a, src_b = (prob_a if pair[0] == PROB else bit_a), (prob_b if pair[1] == PROB else bit_b)
+    a, b = _mk(gv, pair[0], dims, side), _mk(gv, pair[1], dims, side)
+    b.upload(src_b)
+    for use_summary in (1, 0):
+        gv.set_option(gv.GVX_OPT_USE_SUMMARY, use_summary)
+        try:
+            for t1, t2 in ((0, 0), (-128, 5), (5, -128), (-127, 127), (127, -127), (-20, 90), (64, -3), (-128, -128)):
+                for off, mark in (((0, 0, 0), False), ((0, 0, 0), True), ((3, -1, 2), True)):
+                    a.upload(src_a)
+                    ra = src_a.copy().reshape(-1)
+                    lin = off[2] * dims[0] * dims[1] + off[1] * dims[0] + off[0]
+                    want = oracle.collide_map_map_thresholds(ra, pair[0], src_b.reshape(-1), pair[1], n, t1, t2, lin, mark)
+                    for rep in range(2):   # the second call also goes through the coarse mask
+                        if rep:
+                            want = oracle.collide_map_map_thresholds(ra, pair[0], src_b.reshape(-1), pair[1], n, t1, t2, lin, mark)
+                        got = a.collisionCheckWithCounter(b, t1, t2, off, mark=mark)
+                        assert got == want, (pair, t1, t2, off, mark, use_summary, rep, got, want)
+                    assert np.array_equal(a.download().reshape(-1).view(np.uint8), ra.view(np.uint8))
+        finally:
+            gv.set_option(gv.GVX_OPT_USE_SUMMARY, 1)
+    with pytest.raises(gv.GvxError):
+        a.collisionCheckWithCounter(b, 200, 0)

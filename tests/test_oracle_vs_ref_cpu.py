@@ -95,6 +95,29 @@ def test_collide_map_map(oracle, ref, ta, tb):
             assert np.array_equal(a1, a2)
 
 
+@pytest.mark.parametrize("ta,tb", [(BIT, PROB), (PROB, BIT), (PROB, PROB), (BIT, BIT)])
+def test_collide_map_map_two_thresholds(oracle, ref, ta, tb):
+    """DefaultCollider(Probability threshold1, Probability threshold2), GV/voxel/DefaultCollider.hpp:45-49"""
+    ref.gvrefcpu_collide_map_map_thresholds.restype = C.c_uint64
+    ref.gvrefcpu_collide_map_map_thresholds.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_uint64, C.c_int, C.c_int,
+                                                        C.c_int64, C.c_int]
+    n = 20011
+    bit1, prob1 = _random_maps(3, n)
+    bit2, prob2 = _random_maps(4, n)
+    for t1, t2 in ((0, 0), (-128, 5), (5, -128), (-127, 127), (127, -127), (-20, 90), (64, -3), (-128, -128)):
+        for off in (0, -1, 177):
+            a1 = (bit1 if ta == BIT else prob1).copy(); a2 = a1.copy()
+            b = bit2 if tb == BIT else prob2
+            c1 = oracle.collide_map_map_thresholds(a1, ta, b, tb, n, t1, t2, off, True)
+            c2 = ref.gvrefcpu_collide_map_map_thresholds(a2.ctypes.data, ta, b.ctypes.data, tb, n, t1, t2, off, 1)
+            assert c1 == c2, (t1, t2, off)
+            assert np.array_equal(a1, a2)
+    # the one-threshold form is the two-threshold form with t1 == t2 == floatToProbability(thr)
+    a1 = prob1.copy()
+    assert oracle.collide_map_map(a1, PROB, prob2, PROB, n, 0.5, 0, False) == \
+        oracle.collide_map_map_thresholds(a1, PROB, prob2, PROB, n, 0, 0, 0, False)
+
+
 def test_collide_types(oracle, ref):
     n = 20011
     bit1, _ = _random_maps(5, n)
