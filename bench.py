@@ -521,11 +521,17 @@ def run_c5(ctx):
     if world > 1 and not ctx.fused and not args.nccl_count:
         ctx.connect_peers(1)
 
-    def step(k):
-        """count + 256 per-meaning counts of this rank's slab, then the path's one collective (257 x u64, NCCL)"""
+    def step_nccl(k):
+        """count + 256 per-meaning counts of this rank's slab, then ONE NCCL all-reduce of the 257 words"""
         ctx.check(L.gvx_collide_list_map_per_meaning_async(lh, mh, 1.0, None, 0, out_p))
         if world > 1:
             dist.all_reduce(out_d)
+
+    def step_fused(k):
+        """the same with the 257 words all-reduced inside the kernel over NVLink peer memory (no NCCL launch)"""
+        ctx.check(L.gvx_collide_list_map_per_meaning_allreduce(lh, mh, 1.0, 0, out_p))
+
+    step = step_fused if (world > 1 and ctx.fused) else step_nccl
 
     def count_only(k):
         if world > 1 and ctx.fused:
@@ -545,7 +551,12 @@ def run_c5(ctx):
         for k in range(max(args.warmup, 3)):
             step(k); count_only(k)
         r_ = {"step": ctx.timed_reps(step, K), "count_only": ctx.timed_reps(count_only, K, reps=5),
-              "local_kernel": ctx.timed_reps(local_kernel, K, reps=5)}
+              "local_kernel": ctx.timed_reps(local_kernel, K, reps=5),
+              "allreduce": "none" if world == 1 else ("in-kernel over NVLink peer memory (257 words)" if step is step_fused else "nccl")}
+        if step is step_fused:  # A/B: the NCCL form of the same step
+            for k in range(3):
+                step_nccl(k)
+            r_["step_nccl"] = ctx.timed_reps(step_nccl, K, reps=5)
         step(0)
         torch.cuda.synchronize()
         got = out_d.cpu().numpy().astype(np.uint64)
@@ -929,6 +940,7 @@ def run_gpu_arm(args):
                 ms, kms = r["step"]["median"], r["local_kernel"]["median"]
                 line["c5"][tag] = {"entries_per_s": e / (ms * 1e-3), "ms_per_step": ms, "ms_p10_p90": [r["step"]["p10"], r["step"]["p90"]],
                                    "count_only_ms": r["count_only"]["median"], "local_kernel_ms": kms,
+                                   "allreduce": r["allreduce"], "ms_per_step_with_nccl_allreduce": r.get("step_nccl", {}).get("median"),
                                    "roofline_68B_per_entry_GBps": C5_BYTES_PER_ENTRY * e / world / (kms * 1e-3) / 1e9,
                                    "collisions": r["collisions"], "per_meaning_total": r["total"], "parity": r.get("parity")}
         if c2 is not None:

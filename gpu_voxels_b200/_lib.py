@@ -74,6 +74,7 @@ SIGNATURES = {
     "gvx_peer_dispatch_disconnect": (C.c_int, []),
     "gvx_update_logodds_dispatch": (C.c_int, [u64, vp, u64, C.c_int, vp, C.c_int, vp]),
     "gvx_collide_map_map_allreduce": (C.c_int, [u64, u64, f32, C.c_int, P(u64), vp]),
+    "gvx_collide_list_map_per_meaning_allreduce": (C.c_int, [u64, u64, f32, C.c_int, vp]),
     "gvx_collide_list_map_allreduce": (C.c_int, [u64, u64, f32, C.c_int, P(u64), vp]),
     "gvx_list_create": (C.c_int, [P(u64), u32, u32, u32, f32]),
     "gvx_list_destroy": (C.c_int, [u64]),

@@ -25,8 +25,8 @@ int mailbox_create_locked(void* ipc_handle64) {
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is exchanged as 64 bytes");
   if (!ipc_handle64) return fail(GVX_ERR_INVALID, "null handle buffer");
   if (!g.peer_mailbox) {
-    GVX_CUDA(cudaMalloc((void**)&g.peer_mailbox, 2 * kMaxPeers * sizeof(PeerSlot)));
-    GVX_CUDA(cudaMemset(g.peer_mailbox, 0, 2 * kMaxPeers * sizeof(PeerSlot)));
+    GVX_CUDA(cudaMalloc((void**)&g.peer_mailbox, kPeerMailboxBytes));
+    GVX_CUDA(cudaMemset(g.peer_mailbox, 0, kPeerMailboxBytes));
     GVX_CUDA(cudaDeviceSynchronize());
   }
   cudaIpcMemHandle_t h;

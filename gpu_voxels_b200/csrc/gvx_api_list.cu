@@ -466,6 +466,21 @@ int gvx_collide_list_map_per_meaning_async(gvx_handle_t hl, gvx_handle_t hm, flo
   return GVX_OK;
 }
 
+int gvx_collide_list_map_per_meaning_allreduce(gvx_handle_t hl, gvx_handle_t hm, float thr, int mark, uint64_t* counts257_d) {
+  std::lock_guard<std::mutex> lk(g.mu);
+  GVX_NEED_INIT();
+  if (!counts257_d) return fail(GVX_ERR_INVALID, "null result pointer");
+  ListCollideArgs a;
+  int rc = list_collide_prepare(hl, hm, nullptr, &a);
+  if (rc) return rc;
+  // a collective: every rank launches, also with an empty list or an empty slab range (size 0)
+  LaunchCtx c = lctx_allreduce();
+  c.result_hmap_d = nullptr;  // the result stays on the device
+  if ((rc = list_launch(c, 3, a, thr, mark != 0, nullptr, (unsigned long long*)counts257_d))) return rc;
+  GVX_CUDA(cudaMemcpyAsync(counts257_d + 1, g.result_d->per_meaning, 256 * sizeof(uint64_t), cudaMemcpyDeviceToDevice, g.stream));
+  return GVX_OK;
+}
+
 int gvx_collide_list_map_allreduce(gvx_handle_t hl, gvx_handle_t hm, float thr, int mark, uint64_t* count,
                                    uint64_t* count_d) {
   std::lock_guard<std::mutex> lk(g.mu);

@@ -110,6 +110,12 @@ struct ResultBlock {
 // sums them -- the collective is part of the kernel, no NCCL launch follows. world <= 1 disables it.
 constexpr int kMaxPeers = 16;
 struct PeerSlot { unsigned long long value; unsigned long long epoch; };
+// The mailbox allocation of a rank: the scalar slots [2 (epoch parity)][kMaxPeers], then a vector area
+// [2][kMaxPeers (source rank)][kPeerVecWords] of packed words (epoch16 << 48 | value48) for the 257-word all-reduce of
+// list x map per-meaning counts (total + 256 counts).
+constexpr int kPeerVecWords = 257;
+constexpr size_t kPeerVecOffset = 2 * kMaxPeers * sizeof(PeerSlot);
+constexpr size_t kPeerMailboxBytes = kPeerVecOffset + 2ull * kMaxPeers * kPeerVecWords * sizeof(unsigned long long);
 struct PeerReduce {
   PeerSlot* peers[kMaxPeers];
   int rank;

@@ -272,10 +272,17 @@ k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxel
     __syncthreads();
   }
   const bool last = finish_block<MODE == 1>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
-  if (MODE == 3 && last && out_h) {
+  if (MODE == 3 && last) {
     __threadfence();  // acquire side of the arrival ticket: the other CTAs' histogram adds are in L2
-    out_h->per_meaning[threadIdx.x] = __ldcg(&out_d->per_meaning[threadIdx.x]);
-    __threadfence_system();
+    unsigned long long h = __ldcg(&out_d->per_meaning[threadIdx.x]);
+    if (pr.world > 1) {  // sharded map: the 256 per-meaning counts are all-reduced here, over NVLink peer memory, like the
+      h = peer_allreduce_word(h, threadIdx.x + 1, pr);  // count in finish_block (word 0 of the vector area stays unused)
+      out_d->per_meaning[threadIdx.x] = h;
+    }
+    if (out_h) {
+      out_h->per_meaning[threadIdx.x] = h;
+      __threadfence_system();
+    }
   }
 }
 

@@ -38,6 +38,37 @@ __device__ __forceinline__ unsigned long long peer_allreduce_sum(unsigned long l
   return all_ok ? sum : ~0ull;
 }
 
+// The same for a vector of up to kPeerVecWords values, by ALL kThreads threads of one CTA: thread t owns word t (thread 0
+// also word 256). Every word is one packed 64-bit value (epoch16 << 48 | value48) stored into every peer's vector area
+// with a relaxed system-scope store and polled in the own area until it carries the current epoch: no flag, no fence,
+// the n_words x world stores and polls of a CTA overlap. v (in registers) is replaced by the sum over the ranks;
+// a rank that never arrives yields ~0ull (bounded spin).
+__device__ __forceinline__ unsigned long long peer_allreduce_word(unsigned long long mine, int word, const PeerReduce& pr) {
+  const int par = (int)(pr.epoch & 1ull);
+  const unsigned long long tag = (pr.epoch & 0xFFFFull) << 48;
+  const unsigned long long packed = tag | (mine & 0xFFFFFFFFFFFFull);
+  for (int r = 0; r < pr.world; ++r) {
+    unsigned long long* dst = reinterpret_cast<unsigned long long*>(reinterpret_cast<unsigned char*>(pr.peers[r]) + kPeerVecOffset) +
+                              ((size_t)par * kMaxPeers + pr.rank) * kPeerVecWords + word;
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(packed) : "memory");
+  }
+  unsigned long long sum = 0;
+  bool ok = true;
+  const long long t0 = clock64();
+  for (int r = 0; r < pr.world && ok; ++r) {
+    const unsigned long long* src = reinterpret_cast<const unsigned long long*>(reinterpret_cast<const unsigned char*>(pr.peers[pr.rank]) + kPeerVecOffset) +
+                                    ((size_t)par * kMaxPeers + r) * kPeerVecWords + word;
+    unsigned long long v;
+    for (;;) {
+      asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(src) : "memory");
+      if ((v >> 48) == (pr.epoch & 0xFFFFull)) break;
+      if (clock64() - t0 > 8000000000ll) { ok = false; break; }
+    }
+    sum += v & 0xFFFFFFFFFFFFull;
+  }
+  return ok ? sum : ~0ull;
+}
+
 // Block-level finish shared by all counting kernels: reduce (count, mask) over the CTA, add it into the context's
 // accumulator together with an arrival ticket, one atomic per CTA (8 more for a mask); the last CTA to arrive has the total,
 // optionally all-reduces the count over the peers, and publishes the result to device memory and to the mapped pinned

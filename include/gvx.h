@@ -271,6 +271,11 @@ int gvx_collide_map_map_allreduce(gvx_handle_t a, gvx_handle_t b, float thr, int
                                   uint64_t* count_d);
 int gvx_collide_list_map_allreduce(gvx_handle_t list, gvx_handle_t map, float thr, int mark, uint64_t* count,
                                    uint64_t* count_d);
+/* per-meaning counts of the list against this rank's z-slab, the total AND the 256 counts all-reduced inside the kernel
+ * over the peers' mailboxes (257 packed words per peer; no NCCL launch): counts257_d (device) receives the GLOBAL total in
+ * [0] and the global per-meaning counts in [1..256] on every rank; nothing synchronises. A collective. */
+int gvx_collide_list_map_per_meaning_allreduce(gvx_handle_t list, gvx_handle_t map, float thr, int mark,
+                                               uint64_t* counts257_d);
 
 /* ---- multi-GPU behind the drop-in API (SPMD, one process per GPU, no torch / MPI needed) ---------------------- */
 /* Start N copies of the SAME program with GVX_SHARD=z GVX_WORLD=N GVX_RANK=r in the environment ([GVX_LOCAL_RANK],
