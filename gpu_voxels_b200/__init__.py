@@ -10,6 +10,6 @@ There is no CPU fallback: every call ends in libgvx.so and fails loudly without 
 from .api import *  # noqa: F401,F403
 from .api import GpuVoxels, BitVectorVoxelMap, ProbVoxelMap, MetaPointCloud, BitVectorVoxel  # noqa: F401
 from .api import batch_robot_collide, batch_robot_collide_dh, dh_chain_transforms, transform_points  # noqa: F401
-from .api import PointcloudFileHandler  # noqa: F401
+from .api import PointcloudFileHandler, CollisionLane  # noqa: F401
 from .voxellist import BitVectorVoxelList  # noqa: F401
 from ._lib import GvxError  # noqa: F401

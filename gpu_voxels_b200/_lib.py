@@ -113,6 +113,12 @@ SIGNATURES = {
     "gvx_batch_robot_collide_noalloc": (C.c_int, [u64, vp, vp, u32, vp, vp, u32, vp, f32, vp]),
     "gvx_noalloc_scratch_bytes": (u64, []),
     "gvx_batch_set_scratch_budget": (C.c_int, [u64]),
+    "gvx_lane_create": (C.c_int, [vp]),
+    "gvx_lane_destroy": (C.c_int, [u64]),
+    "gvx_lane_count": (C.c_int, [vp]),
+    "gvx_lane_collide_map_map": (C.c_int, [u64, u64, u64, f32, vp, vp]),
+    "gvx_lane_collide_map_map_any": (C.c_int, [u64, u64, u64, f32, vp]),
+    "gvx_lane_collide_list_map": (C.c_int, [u64, u64, u64, f32, vp, vp]),
 }
 
 

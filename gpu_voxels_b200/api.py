@@ -440,6 +440,44 @@ GVX_OPT_USE_COARSE = 5
 REVOLUTE, PRISMATIC = 0, 1  # robot::DHJointType, GV/robot/dh_robot/KinematicLink.h:37-41
 
 
+class CollisionLane:
+    """A collision lane (include/gvx.h "collision lanes"): read-only collision queries on a stream and result blocks of
+    their own, so that queries issued by different host threads overlap on the GPU. The reference's counterpart is its
+    per-map locking (GV/voxelmap/TemplateVoxelMap.hpp:329-414, 477-519): threads that collide different maps run
+    concurrently. One lane per thread; results equal collideWith(..., mark=False) / collisionCheck."""
+
+    def __init__(self):
+        self._L = _lib.init()
+        h = C.c_uint64(0)
+        _lib.check(self._L.gvx_lane_create(C.byref(h)))
+        self.handle = h.value
+
+    def destroy(self):
+        if getattr(self, "handle", None):
+            self._L.gvx_lane_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+    def collideWith(self, a, b, coll_threshold=1.0, offset=None):
+        p, keep = GpuVoxelsMap._off(offset)
+        cnt = C.c_uint64(0)
+        if hasattr(a, "m_ref_map_dim"):  # BitVectorVoxelList x map
+            _lib.check(self._L.gvx_lane_collide_list_map(self.handle, a.handle, b.handle, coll_threshold, p, C.byref(cnt)))
+        else:
+            _lib.check(self._L.gvx_lane_collide_map_map(self.handle, a.handle, b.handle, coll_threshold, p, C.byref(cnt)))
+        return cnt.value
+
+    def collisionCheck(self, a, b, coll_threshold=1.0):
+        flag = C.c_int(0)
+        _lib.check(self._L.gvx_lane_collide_map_map_any(self.handle, a.handle, b.handle, coll_threshold, C.byref(flag)))
+        return bool(flag.value)
+
+
 def set_option(option, value):
     """gvx_set_option: GVX_OPT_USE_SUMMARY = 0 makes every collide stream the voxels (the reference's access pattern)"""
     _lib.check(_lib.init().gvx_set_option(int(option), int(value)))

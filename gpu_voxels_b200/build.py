@@ -11,7 +11,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgvx.so")
 SOURCES = ["gvx_api.cu", "gvx_api_list.cu", "gvx_api_batch.cu", "gvx_collide.cu", "gvx_insert.cu", "gvx_list.cu",
            "gvx_batch.cu", "gvx_kinematics.cu", "gvx_sweptvolume.cu", "gvx_listlist.cu", "gvx_api_io.cu",
-           "gvx_dispatch.cu", "gvx_api_dispatch.cu", "gvx_api_files.cu", "gvx_collide_tma.cu", "gvx_api_shard.cu", "gvx_noalloc.cu"]
+           "gvx_dispatch.cu", "gvx_api_dispatch.cu", "gvx_api_files.cu", "gvx_collide_tma.cu", "gvx_api_shard.cu", "gvx_noalloc.cu", "gvx_api_lanes.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--ftz=false", "--prec-div=true", "--prec-sqrt=true", "--fmad=true",
               "-Xcompiler", "-ffp-contract=off"]  # host code: no FMA contraction (file loaders, DH re-computation)

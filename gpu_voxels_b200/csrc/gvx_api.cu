@@ -75,8 +75,10 @@ int mailbox_disconnect_locked() {
 
 extern "C" {
 
+static int shutdown_locked(std::vector<std::shared_ptr<Lane>>* lanes);
+
 int gvx_init(int device) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   if (g.ready) return GVX_OK;
   int n_dev = 0;
   cudaError_t e = cudaGetDeviceCount(&n_dev);
@@ -119,9 +121,17 @@ int gvx_init(int device) {
 }
 
 int gvx_shutdown(void) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::vector<std::shared_ptr<Lane>> lanes;
+  const int rc = shutdown_locked(&lanes);
+  lanes_release(lanes);  // outside g.mu: lock order lane.mu -> g.mu
+  return rc;
+}
+
+static int shutdown_locked(std::vector<std::shared_ptr<Lane>>* lanes) {
+  std::lock_guard<ApiMutex> lk(g.mu);
   if (!g.ready) return GVX_OK;
   cudaDeviceSynchronize();
+  lanes_detach_all_locked(lanes);
   shard_detach();
   for (auto& kv : g.maps) {
     if (kv.second.owned && kv.second.data) cudaFree(kv.second.data);
@@ -171,7 +181,7 @@ int gvx_shutdown(void) {
 const char* gvx_last_error(void) { return t_err.c_str(); }
 
 int gvx_set_stream(void* cuda_stream) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   // NULL selects the library's own non-blocking stream; pass cudaStreamLegacy / cudaStreamPerThread (or any created
@@ -181,7 +191,7 @@ int gvx_set_stream(void* cuda_stream) {
 }
 
 int gvx_wait_event(void* cuda_event) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   if (!cuda_event) return fail(GVX_ERR_INVALID, "null event");
   GVX_CUDA(cudaStreamWaitEvent(g.stream, (cudaEvent_t)cuda_event, 0));
@@ -189,14 +199,14 @@ int gvx_wait_event(void* cuda_event) {
 }
 
 int gvx_sync(void) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   return GVX_OK;
 }
 
 int gvx_device_info(int* sm_count, uint64_t* free_bytes, uint64_t* total_bytes, char* name64) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   size_t f = 0, t = 0;
   GVX_CUDA(cudaMemGetInfo(&f, &t));
@@ -216,7 +226,7 @@ uint64_t gvx_launch_count(void) { return g.launches; }
 uint64_t gvx_summary_fallback_count(void) { return g.summary_fallbacks; }
 
 int gvx_set_l2_fetch_granularity(int bytes, int* previous) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   size_t cur = 0;
   GVX_CUDA(cudaDeviceGetLimit(&cur, cudaLimitMaxL2FetchGranularity));
@@ -230,7 +240,7 @@ int gvx_set_l2_fetch_granularity(int bytes, int* previous) {
 
 // ---- device buffers (PointCloud / MetaPointCloud storage of the C++ facade) ---------------------------------
 int gvx_buffer_create(gvx_handle_t* h, uint64_t bytes) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   if (!h) return fail(GVX_ERR_INVALID, "null handle pointer");
   Context::DevBuffer b{nullptr, bytes};
@@ -244,7 +254,7 @@ int gvx_buffer_create(gvx_handle_t* h, uint64_t bytes) {
   return GVX_OK;
 }
 int gvx_buffer_destroy(gvx_handle_t h) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   auto it = g.buffers.find(h);
   if (it == g.buffers.end()) return fail(GVX_ERR_INVALID, "unknown buffer handle %llu", (unsigned long long)h);
@@ -263,7 +273,7 @@ static int buffer_range(gvx_handle_t h, uint64_t offset, uint64_t bytes, Context
   return GVX_OK;
 }
 int gvx_buffer_upload(gvx_handle_t h, uint64_t offset, const void* host, uint64_t bytes) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Context::DevBuffer* b;
   int rc = buffer_range(h, offset, bytes, &b);
@@ -275,7 +285,7 @@ int gvx_buffer_upload(gvx_handle_t h, uint64_t offset, const void* host, uint64_
   return GVX_OK;
 }
 int gvx_buffer_download(gvx_handle_t h, uint64_t offset, void* host, uint64_t bytes) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Context::DevBuffer* b;
   int rc = buffer_range(h, offset, bytes, &b);
@@ -287,7 +297,7 @@ int gvx_buffer_download(gvx_handle_t h, uint64_t offset, void* host, uint64_t by
   return GVX_OK;
 }
 int gvx_buffer_device_ptr(gvx_handle_t h, void** data_d, uint64_t* bytes) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   auto it = g.buffers.find(h);
   if (it == g.buffers.end()) return fail(GVX_ERR_INVALID, "unknown buffer handle %llu", (unsigned long long)h);
@@ -328,24 +338,24 @@ static int map_make(gvx_handle_t* h, int map_type, void* wrap, uint32_t dx, uint
 }
 
 int gvx_map_create(gvx_handle_t* h, int map_type, uint32_t dx, uint32_t dy, uint32_t dz, float side) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   uint32_t z0 = 0, z1 = dz;
   if (shard_active() && dz >= (uint32_t)g.shard_world) shard_slab(dz, &z0, &z1);  // GVX_SHARD=z: this rank's slab
   return map_make(h, map_type, nullptr, dx, dy, dz, side, z0, z1);
 }
 int gvx_map_create_slab(gvx_handle_t* h, int map_type, uint32_t dx, uint32_t dy, uint32_t dz, float side, uint32_t z0,
                         uint32_t z1) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   return map_make(h, map_type, nullptr, dx, dy, dz, side, z0, z1);
 }
 int gvx_map_wrap(gvx_handle_t* h, int map_type, void* data_d, uint32_t dx, uint32_t dy, uint32_t dz, float side,
                  uint32_t z0, uint32_t z1) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   if (!data_d) return fail(GVX_ERR_INVALID, "null device pointer");
   return map_make(h, map_type, data_d, dx, dy, dz, side, z0, z1);
 }
 int gvx_map_destroy(gvx_handle_t h) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -365,14 +375,14 @@ static int map_clear_locked(Map* m) {
   return GVX_OK;
 }
 int gvx_map_clear(gvx_handle_t h) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
   return map_clear_locked(m);
 }
 int gvx_map_clear_bits(gvx_handle_t h, const uint8_t mask32[GVX_BITVOXEL_BYTES]) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m || !mask32) return fail(GVX_ERR_INVALID, "unknown map handle or null mask");
@@ -385,7 +395,7 @@ int gvx_map_clear_bits(gvx_handle_t h, const uint8_t mask32[GVX_BITVOXEL_BYTES])
 }
 int gvx_map_clear_meaning(gvx_handle_t h, int meaning) {
   {
-    std::lock_guard<std::mutex> lk(g.mu);
+    std::lock_guard<ApiMutex> lk(g.mu);
     GVX_NEED_INIT();
     Map* m = find_map(h);
     if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -400,7 +410,7 @@ int gvx_map_clear_meaning(gvx_handle_t h, int meaning) {
   return gvx_map_clear_bits(h, mask);
 }
 int gvx_map_device_ptr(gvx_handle_t h, void** data_d, uint64_t* first_voxel, uint64_t* n_voxels) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -417,7 +427,7 @@ int gvx_map_device_ptr(gvx_handle_t h, void** data_d, uint64_t* first_voxel, uin
   return GVX_OK;
 }
 int gvx_map_device_ptr_const(gvx_handle_t h, const void** data_d, uint64_t* first_voxel, uint64_t* n_voxels) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -428,7 +438,7 @@ int gvx_map_device_ptr_const(gvx_handle_t h, const void** data_d, uint64_t* firs
 }
 int gvx_map_info(gvx_handle_t h, int* map_type, uint32_t dims3[3], float* side, uint32_t* z0, uint32_t* z1,
                  uint64_t* bytes) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -441,7 +451,7 @@ int gvx_map_info(gvx_handle_t h, int* map_type, uint32_t dims3[3], float* side, 
   return GVX_OK;
 }
 int gvx_map_download(gvx_handle_t h, void* host_buf) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m || !host_buf) return fail(GVX_ERR_INVALID, "unknown map handle or null buffer");
@@ -450,7 +460,7 @@ int gvx_map_download(gvx_handle_t h, void* host_buf) {
   return GVX_OK;
 }
 int gvx_map_upload(gvx_handle_t h, const void* host_buf) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m || !host_buf) return fail(GVX_ERR_INVALID, "unknown map handle or null buffer");
@@ -465,7 +475,7 @@ int gvx_map_upload(gvx_handle_t h, const void* host_buf) {
 }
 
 int gvx_map_refresh_summary(gvx_handle_t h) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -479,7 +489,7 @@ int gvx_map_refresh_summary(gvx_handle_t h) {
 }
 
 int gvx_map_summary_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, int* valid) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -493,7 +503,7 @@ int gvx_map_summary_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, 
 }
 
 int gvx_map_coarse_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, int* valid) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -508,7 +518,7 @@ int gvx_map_coarse_download(gvx_handle_t h, uint32_t* words, uint64_t n_words, i
 }
 
 int gvx_set_option(int option, int value) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   switch (option) {
     case GVX_OPT_USE_SUMMARY: g.use_summary = value != 0; return GVX_OK;
     case GVX_OPT_PDL: g.pdl = value != 0; return GVX_OK;
@@ -532,7 +542,7 @@ static int read_flag(int* any_outside) {
 }
 
 int gvx_insert_points(gvx_handle_t h, const float* xyz, uint64_t n, int mem_kind, int meaning, int* any_outside) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -551,7 +561,7 @@ int gvx_insert_points(gvx_handle_t h, const float* xyz, uint64_t n, int mem_kind
 
 int gvx_insert_meta(gvx_handle_t h, const float* xyz, int mem_kind, const uint32_t* cloud_sizes, uint32_t n_clouds,
                     const int32_t* meanings, uint32_t n_meanings, const float* transforms, int* any_outside) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -595,7 +605,7 @@ int gvx_insert_meta(gvx_handle_t h, const float* xyz, int mem_kind, const uint32
 }
 
 int gvx_transform_points(const float* in_xyz, float* out_xyz, uint64_t n, int mem_kind, const float M16[16]) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   if (n == 0) return GVX_OK;
   if (!in_xyz || !out_xyz || !M16) return fail(GVX_ERR_INVALID, "null pointer");
@@ -617,7 +627,7 @@ int gvx_transform_points(const float* in_xyz, float* out_xyz, uint64_t n, int me
 
 int gvx_update_logodds(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int mem_kind, const float pose12[12],
                        int delta_occ) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -637,7 +647,7 @@ int gvx_update_logodds(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int 
 int gvx_insert_sensor_data(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int mem_kind, const float pose12[12],
                            int enable_raycasting, gvx_handle_t robot_map, int robot_bit, int delta_free,
                            int delta_occ) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -670,7 +680,7 @@ int gvx_insert_sensor_data(gvx_handle_t h, const float* xyz_sensor, uint64_t n, 
 
 int gvx_update_logodds_multi(gvx_handle_t h, const float* xyz_sensor, int mem_kind, const uint32_t* frame_sizes,
                              uint32_t n_frames, const float* poses12, int delta_occ) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -754,7 +764,7 @@ static int fixup_summary_after_mark(Map* a, int8_t thr_i, bool mark) {
 }
 
 int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32_t off3[3], int mark, uint64_t* count) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map *a, *b;
   int64_t off, i0, i1;
@@ -782,7 +792,7 @@ int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32
 
 int gvx_collide_map_map_thresholds(gvx_handle_t ha, gvx_handle_t hb, int threshold1, int threshold2,
                                    const int32_t off3[3], int mark, uint64_t* count) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   if (threshold1 < -128 || threshold1 > 127 || threshold2 < -128 || threshold2 > 127)
     return fail(GVX_ERR_INVALID, "thresholds (%d, %d) outside the int8 range of Probability", threshold1, threshold2);
@@ -808,7 +818,7 @@ int gvx_collide_map_map_thresholds(gvx_handle_t ha, gvx_handle_t hb, int thresho
 
 int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32_t off3[3], int mark,
                               uint64_t* count_d) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map *a, *b;
   int64_t off, i0, i1;
@@ -826,24 +836,24 @@ int gvx_collide_map_map_async(gvx_handle_t ha, gvx_handle_t hb, float thr, const
 
 // ---- fused all-reduce over peer memory ----------------------------------------------------------------
 int gvx_peer_mailbox_create(void* ipc_handle64) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   return mailbox_create_locked(ipc_handle64);
 }
 int gvx_peer_mailbox_connect(int rank, int world, const void* all_handles) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   return mailbox_connect_locked(rank, world, all_handles);
 }
 int gvx_peer_mailbox_disconnect(void) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   if (!g.ready) return GVX_OK;
   return mailbox_disconnect_locked();
 }
 
 int gvx_collide_map_map_allreduce(gvx_handle_t ha, gvx_handle_t hb, float thr, int mark, uint64_t* count,
                                   uint64_t* count_d) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map *a, *b;
   int64_t off, i0, i1;
@@ -866,7 +876,7 @@ int gvx_collide_map_map_allreduce(gvx_handle_t ha, gvx_handle_t hb, float thr, i
 }
 
 int gvx_collide_map_map_any(gvx_handle_t ha, gvx_handle_t hb, float thr, int* flag) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map *a, *b;
   int64_t off, i0, i1;
@@ -886,9 +896,55 @@ int gvx_collide_map_map_any(gvx_handle_t ha, gvx_handle_t hb, float thr, int* fl
   return GVX_OK;
 }
 
+// Lane variants (gvx_api_lanes.cu): the same kernels on the lane's stream and result blocks. g.mu covers validation and
+// the launch only; the wait for the result runs outside it, so queries of different lanes overlap on the GPU.
+static int lane_collide_map_map(gvx_handle_t lane, gvx_handle_t ha, gvx_handle_t hb, float thr, const int32_t off3[3],
+                                bool any, uint64_t* count) {
+  std::shared_ptr<Lane> L;
+  int rc = lane_acquire(lane, &L);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> ll(L->mu);
+  if (L->dead) return fail(GVX_ERR_INVALID, "lane %llu was destroyed", (unsigned long long)lane);
+  {
+    std::lock_guard<std::mutex> lk(g.mu.m);
+    GVX_NEED_INIT();
+    if ((rc = lane_thread_device())) return rc;
+    Map *a, *b;
+    int64_t off, i0, i1;
+    if ((rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1))) return rc;
+    if (shard_active() && a->sharded())
+      return fail(GVX_ERR_UNSUPPORTED, "lanes are per process: under GVX_SHARD the global result needs a collective, which "
+                                       "every rank must issue in the same order -- use the serial entry points");
+    const uint32_t *ca = nullptr, *cb = nullptr;
+    if (off == 0 && ((rc = coarse_for_collide(a, &ca)) || (rc = coarse_for_collide(b, &cb)))) return rc;
+    const uint32_t *sa = summary_for_collide(a), *sb = summary_for_collide(b);
+    LaunchCtx c;
+    if ((rc = lane_join_locked(*L, &c))) return rc;  // after the coarse masks: they are built on the library's stream
+    c.any = any;
+    GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->data, b->type, i0, i1, off, float_to_probability(thr), false,
+                                    false, nullptr, sa, sb, ca, cb));
+    if ((rc = lane_launched_locked(*L))) return rc;
+  }
+  GVX_CUDA(cudaStreamSynchronize(L->stream));
+  if (count) *count = L->result_h->count;
+  return GVX_OK;
+}
+
+int gvx_lane_collide_map_map(gvx_handle_t lane, gvx_handle_t ha, gvx_handle_t hb, float thr, const int32_t off3[3],
+                             uint64_t* count) {
+  return lane_collide_map_map(lane, ha, hb, thr, off3, false, count);
+}
+
+int gvx_lane_collide_map_map_any(gvx_handle_t lane, gvx_handle_t ha, gvx_handle_t hb, float thr, int* flag) {
+  uint64_t c = 0;
+  const int rc = lane_collide_map_map(lane, ha, hb, thr, nullptr, true, &c);
+  if (rc == GVX_OK && flag) *flag = c != 0;
+  return rc;
+}
+
 int gvx_collide_map_map_types(gvx_handle_t ha, gvx_handle_t hb, float thr, int mark,
                               uint8_t mask_inout32[GVX_BITVOXEL_BYTES], uint64_t* count) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map *a, *b;
   int64_t off, i0, i1;
@@ -913,7 +969,7 @@ int gvx_collide_map_map_types(gvx_handle_t ha, gvx_handle_t hb, float thr, int m
 
 int gvx_collide_map_map_bitcheck(gvx_handle_t ha, gvx_handle_t hb, uint32_t margin, uint32_t sv_offset, int mark,
                                  uint8_t types_inout32[GVX_BITVOXEL_BYTES], uint64_t* count) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map *a, *b;
   int64_t off, i0, i1;
@@ -947,7 +1003,7 @@ int gvx_collide_map_map_bitcheck(gvx_handle_t ha, gvx_handle_t hb, uint32_t marg
 }
 
 int gvx_map_shift_sv_ids(gvx_handle_t h, uint32_t shift) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);

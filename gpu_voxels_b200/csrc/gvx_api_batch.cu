@@ -7,7 +7,7 @@ using namespace gvx;
 extern "C" {
 
 int gvx_batch_set_scratch_budget(uint64_t bytes) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   if (bytes < 4096) return fail(GVX_ERR_INVALID, "scratch budget below 4 KiB");
   g.bat_seen_budget = (size_t)bytes;
   return GVX_OK;
@@ -169,7 +169,7 @@ extern "C" {
 int gvx_batch_robot_collide(gvx_handle_t env, const float* base_xyz, int mem_kind, const uint32_t* cloud_sizes,
                             uint32_t n_clouds, const int32_t* meanings, const float* transforms, uint32_t n_cfg,
                             const uint8_t* mask32, float thr, uint64_t* counts) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   return batch_core(env, base_xyz, mem_kind, cloud_sizes, n_clouds, meanings, transforms, nullptr, n_cfg, mask32, thr,
                     counts);
@@ -180,7 +180,7 @@ int gvx_batch_robot_collide_dh(gvx_handle_t env, const float* base_xyz, int mem_
                                const int32_t* joint_types, uint32_t n_links, const int32_t* link_cloud,
                                const float* joint_values, uint32_t n_cfg, const uint8_t* mask32, float thr,
                                uint64_t* counts) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   DhArgs fk{dh4, joint_types, n_links, joint_values, link_cloud};
   return batch_core(env, base_xyz, mem_kind, cloud_sizes, n_clouds, meanings, nullptr, &fk, n_cfg, mask32, thr, counts);
@@ -188,7 +188,7 @@ int gvx_batch_robot_collide_dh(gvx_handle_t env, const float* base_xyz, int mem_
 
 int gvx_dh_chain_transforms(const float* dh4, const int32_t* joint_types, uint32_t n_links, const float* joint_values,
                             uint32_t n_cfg, float* transforms_out, uint32_t* n_ambiguous) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   if (n_ambiguous) *n_ambiguous = 0;
   if (n_cfg == 0) return GVX_OK;

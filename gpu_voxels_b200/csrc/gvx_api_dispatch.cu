@@ -49,7 +49,7 @@ static int dispatch_alloc(int world, uint64_t capacity) {
 extern "C" {
 
 int gvx_peer_dispatch_create(int world, uint64_t capacity_points, void* ipc_handle64) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   if (world < 1 || world > kMaxPeers) return fail(GVX_ERR_INVALID, "world %d outside [1, %d]", world, kMaxPeers);
   if (capacity_points == 0 || capacity_points > 0xFFFFFFFFull) return fail(GVX_ERR_INVALID, "capacity must be in [1, 2^32)");
@@ -63,7 +63,7 @@ int gvx_peer_dispatch_create(int world, uint64_t capacity_points, void* ipc_hand
 }
 
 int gvx_peer_dispatch_connect(int rank, int world, const void* all_handles) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   if (!g.disp_mem) return fail(GVX_ERR_INVALID, "gvx_peer_dispatch_create has not been called");
   if (world != g.disp_world_alloc || rank < 0 || rank >= world) return fail(GVX_ERR_INVALID, "bad rank %d / world %d (created for %d)", rank, world, g.disp_world_alloc);
@@ -93,7 +93,7 @@ int gvx_peer_dispatch_connect(int rank, int world, const void* all_handles) {
 }
 
 int gvx_peer_dispatch_disconnect(void) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   if (!g.ready) return GVX_OK;
   cudaStreamSynchronize(g.stream);
   dispatch_unmap();
@@ -102,7 +102,7 @@ int gvx_peer_dispatch_disconnect(void) {
 
 int gvx_update_logodds_dispatch(gvx_handle_t h, const float* xyz_sensor, uint64_t n, int mem_kind,
                                 const float pose12[12], int delta_occ, const uint32_t* z_bounds) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);

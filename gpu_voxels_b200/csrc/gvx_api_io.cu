@@ -36,7 +36,7 @@ struct File {
 
 struct MapInfo { int type; uint32_t dx, dy, dz; float side; uint64_t bytes; bool sharded; };
 int map_info(gvx_handle_t h, MapInfo* o) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
@@ -45,7 +45,7 @@ int map_info(gvx_handle_t h, MapInfo* o) {
 }
 struct ListInfo { uint32_t dx, dy, dz; float side; uint64_t size; };
 int list_info(gvx_handle_t h, ListInfo* o) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
@@ -53,7 +53,7 @@ int list_info(gvx_handle_t h, ListInfo* o) {
   return GVX_OK;
 }
 int fail_locked(int code, const char* what, const char* path) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   return fail(code, "%s %s", what, path ? path : "(null)");
 }
 }  // namespace

@@ -180,7 +180,7 @@ int list_launch(const LaunchCtx& c, int mode, const ListCollideArgs& a, float th
 
 int list_collide(int mode, gvx_handle_t hl, gvx_handle_t hm, float thr, const int32_t off3[3], int mark,
                  const uint8_t* mask_in32, uint8_t* mask_out32, uint64_t* counts256, uint64_t* count) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   ListCollideArgs a;
   int rc = list_collide_prepare(hl, hm, off3, &a);
@@ -214,6 +214,35 @@ int list_collide(int mode, gvx_handle_t hl, gvx_handle_t hm, float thr, const in
   return GVX_OK;
 }
 
+// lane variant of the counting list x map collide (gvx_api_lanes.cu)
+int lane_list_collide(gvx_handle_t lane, gvx_handle_t hl, gvx_handle_t hm, float thr, const int32_t off3[3],
+                      uint64_t* count) {
+  std::shared_ptr<Lane> L;
+  int rc = lane_acquire(lane, &L);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> ll(L->mu);
+  if (L->dead) return fail(GVX_ERR_INVALID, "lane %llu was destroyed", (unsigned long long)lane);
+  {
+    std::lock_guard<std::mutex> lk(g.mu.m);
+    GVX_NEED_INIT();
+    if ((rc = lane_thread_device())) return rc;
+    ListCollideArgs a;
+    if ((rc = list_collide_prepare(hl, hm, off3, &a))) return rc;
+    if (shard_active() && a.m->sharded())
+      return fail(GVX_ERR_UNSUPPORTED, "lanes are per process: under GVX_SHARD use the serial entry points");
+    if (a.l->size == 0) { if (count) *count = 0; return GVX_OK; }
+    LaunchCtx c;
+    if ((rc = lane_join_locked(*L, &c))) return rc;
+    uint32_t mk[8] = {0};
+    // (explicit slab maps: list_launch finds the list's range inside the slab on the library's stream, cached after)
+    if ((rc = list_launch(c, 0, a, thr, false, mk, nullptr))) return rc;
+    if ((rc = lane_launched_locked(*L))) return rc;
+  }
+  GVX_CUDA(cudaStreamSynchronize(L->stream));
+  if (count) *count = L->result_h->count;
+  return GVX_OK;
+}
+
 // list x list: both handles, same reference dimensions, no offset (the reference refuses offsets between lists:
 // "Offset for VoxelList operation not supported", BitVoxelList.hpp:413-417)
 int list_list_prepare(gvx_handle_t ha, gvx_handle_t hb, VoxList** a, VoxList** b) {
@@ -227,7 +256,7 @@ int list_list_prepare(gvx_handle_t ha, gvx_handle_t hb, VoxList** a, VoxList** b
 
 int list_list(int mode, gvx_handle_t ha, gvx_handle_t hb, uint32_t margin, uint8_t* types_out32, uint64_t* counts256,
               uint64_t* count) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList *a, *b;
   int rc = list_list_prepare(ha, hb, &a, &b);
@@ -258,7 +287,7 @@ void lists_free_all() {
 extern "C" {
 
 int gvx_list_create(gvx_handle_t* h, uint32_t dx, uint32_t dy, uint32_t dz, float side) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   if (!h) return fail(GVX_ERR_INVALID, "null handle pointer");
   if (!dx || !dy || !dz || !(side > 0.0f)) return fail(GVX_ERR_INVALID, "bad list geometry %ux%ux%u side %g", dx, dy, dz, side);
@@ -271,7 +300,7 @@ int gvx_list_create(gvx_handle_t* h, uint32_t dx, uint32_t dy, uint32_t dz, floa
 }
 
 int gvx_list_destroy(gvx_handle_t h) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
@@ -282,7 +311,7 @@ int gvx_list_destroy(gvx_handle_t h) {
 }
 
 int gvx_list_clear(gvx_handle_t h) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
@@ -292,7 +321,7 @@ int gvx_list_clear(gvx_handle_t h) {
 }
 
 int gvx_list_size(gvx_handle_t h, uint64_t* size) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l || !size) return fail(GVX_ERR_INVALID, "unknown list handle or null pointer");
@@ -301,7 +330,7 @@ int gvx_list_size(gvx_handle_t h, uint64_t* size) {
 }
 
 int gvx_list_merge(gvx_handle_t h, gvx_handle_t other, const int32_t voxel_offset[3], int new_meaning) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   VoxList* o = find_list(other);
@@ -317,7 +346,7 @@ int gvx_list_merge(gvx_handle_t h, gvx_handle_t other, const int32_t voxel_offse
 }
 
 int gvx_list_insert_points(gvx_handle_t h, const float* xyz, uint64_t n, int mem_kind, int meaning) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
@@ -333,7 +362,7 @@ int gvx_list_insert_points(gvx_handle_t h, const float* xyz, uint64_t n, int mem
 
 int gvx_list_insert_meta(gvx_handle_t h, const float* xyz, int mem_kind, const uint32_t* cloud_sizes, uint32_t n_clouds,
                          const int32_t* meanings, uint32_t n_meanings) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
@@ -368,7 +397,7 @@ int gvx_list_insert_meta(gvx_handle_t h, const float* xyz, int mem_kind, const u
 }
 
 int gvx_list_download(gvx_handle_t h, uint32_t* ids, uint32_t* coords, uint8_t* voxels) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
@@ -382,7 +411,7 @@ int gvx_list_download(gvx_handle_t h, uint32_t* ids, uint32_t* coords, uint8_t* 
 }
 
 int gvx_list_upload(gvx_handle_t h, const uint32_t* ids, const uint32_t* coords, const uint8_t* voxels, uint64_t n) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
@@ -406,7 +435,7 @@ int gvx_list_upload(gvx_handle_t h, const uint32_t* ids, const uint32_t* coords,
 }
 
 int gvx_list_device_ptrs(gvx_handle_t h, void** ids_d, void** coords_d, void** voxels_d, uint64_t* size) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
@@ -434,7 +463,7 @@ int gvx_collide_list_map_per_meaning(gvx_handle_t l, gvx_handle_t m, float thr, 
 }
 int gvx_collide_list_map_async(gvx_handle_t hl, gvx_handle_t hm, float thr, const int32_t off3[3], int mark,
                                uint64_t* count_d) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   ListCollideArgs a;
   int rc = list_collide_prepare(hl, hm, off3, &a);
@@ -449,7 +478,7 @@ int gvx_collide_list_map_async(gvx_handle_t hl, gvx_handle_t hm, float thr, cons
 
 int gvx_collide_list_map_per_meaning_async(gvx_handle_t hl, gvx_handle_t hm, float thr, const int32_t off3[3], int mark,
                                            uint64_t* counts257_d) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   if (!counts257_d) return fail(GVX_ERR_INVALID, "null result pointer");
   ListCollideArgs a;
@@ -467,7 +496,7 @@ int gvx_collide_list_map_per_meaning_async(gvx_handle_t hl, gvx_handle_t hm, flo
 }
 
 int gvx_collide_list_map_per_meaning_allreduce(gvx_handle_t hl, gvx_handle_t hm, float thr, int mark, uint64_t* counts257_d) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   if (!counts257_d) return fail(GVX_ERR_INVALID, "null result pointer");
   ListCollideArgs a;
@@ -483,7 +512,7 @@ int gvx_collide_list_map_per_meaning_allreduce(gvx_handle_t hl, gvx_handle_t hm,
 
 int gvx_collide_list_map_allreduce(gvx_handle_t hl, gvx_handle_t hm, float thr, int mark, uint64_t* count,
                                    uint64_t* count_d) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   ListCollideArgs a;
   int rc = list_collide_prepare(hl, hm, nullptr, &a);
@@ -512,7 +541,7 @@ int gvx_collide_list_list_per_meaning(gvx_handle_t a, gvx_handle_t b, uint64_t c
 }
 
 int gvx_list_subtract(gvx_handle_t ha, gvx_handle_t hb) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList *a, *b;
   int rc = list_list_prepare(ha, hb, &a, &b);
@@ -535,7 +564,7 @@ int gvx_list_subtract(gvx_handle_t ha, gvx_handle_t hb) {
 }
 
 int gvx_list_equals(gvx_handle_t ha, gvx_handle_t hb, int* equal) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* a = find_list(ha);
   VoxList* b = find_list(hb);
@@ -551,7 +580,7 @@ int gvx_list_equals(gvx_handle_t ha, gvx_handle_t hb, int* equal) {
 }
 
 int gvx_list_shift_sv_ids(gvx_handle_t h, uint32_t shift) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   VoxList* l = find_list(h);
   if (!l) return fail(GVX_ERR_INVALID, "unknown list handle %llu", (unsigned long long)h);
@@ -559,6 +588,11 @@ int gvx_list_shift_sv_ids(gvx_handle_t h, uint32_t shift) {
   if (l->size == 0) return GVX_OK;
   GVX_CUDA(launch_shift_sv_ids(lctx(), l->voxels[l->cur], l->size, shift, nullptr));
   return GVX_OK;
+}
+
+int gvx_lane_collide_list_map(gvx_handle_t lane, gvx_handle_t list, gvx_handle_t map, float thr, const int32_t off3[3],
+                              uint64_t* count) {
+  return lane_list_collide(lane, list, map, thr, off3, count);
 }
 
 }  // extern "C"

@@ -208,13 +208,13 @@ int gvx_shard_info(int* rank, int* world, int* fused) {
 }
 
 int gvx_shard_allreduce_u64(uint64_t* values, int n_sum, int n_or) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   if (!values && n_sum + n_or > 0) return fail(GVX_ERR_INVALID, "null values");
   return shard_allreduce(values, n_sum, n_or);
 }
 
 int gvx_shard_connect_host(int rank, int world, const char* rendezvous) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   if (g.shard_world > 1) return fail(GVX_ERR_INVALID, "already part of a sharded job");
   if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return fail(GVX_ERR_INVALID, "bad rank %d / world %d", rank, world);
   if (!rendezvous || !*rendezvous) return fail(GVX_ERR_INVALID, "empty rendezvous name");
@@ -229,7 +229,7 @@ int gvx_shard_connect_host(int rank, int world, const char* rendezvous) {
 }
 
 int gvx_shard_disconnect(void) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   shard_detach();
   return GVX_OK;
 }

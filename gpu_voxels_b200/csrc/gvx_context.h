@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstring>
 #include <functional>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -78,6 +79,32 @@ struct VoxList {
   uint64_t n_total() const { return (uint64_t)dx * dy * dz; }
 };
 
+// One collision lane: its own stream, accumulators and result blocks, so that a query running on it shares nothing
+// mutable with the library's stream or another lane. `mu` serialises the callers of ONE lane (held across the wait for
+// the result); lock order lane.mu -> g.mu.
+struct Lane {
+  std::mutex mu;
+  bool dead = false;  // destroyed while a caller still held the pointer
+  cudaStream_t stream = nullptr;
+  ReduceScratch* scratch_d = nullptr;
+  ResultBlock* result_d = nullptr;
+  ResultBlock* result_h = nullptr;       // pinned, mapped
+  ResultBlock* result_hmap_d = nullptr;  // device alias of result_h
+  cudaEvent_t join_ev = nullptr;  // recorded on the library's stream at every lane launch: the lane reads what was enqueued before it
+  cudaEvent_t done_ev = nullptr;  // recorded on the lane's stream by the next serial call: what the library's stream waits for
+  bool pending = false;           // launched since the library's stream last waited for this lane (under g.mu)
+  uint64_t joined_serial_calls = ~0ull;  // g.serial_calls when the lane's stream last waited for the library's stream
+};
+
+// The library mutex. Every serial entry point takes it through std::lock_guard<ApiMutex>: lock() also orders the
+// library's stream behind the lane queries launched since the last serial call, so a mutation enqueued by the caller can
+// never overtake a lane kernel that is still reading the map. Lane entry points lock `m` directly (no fence).
+struct ApiMutex {
+  std::mutex m;
+  void lock();  // gvx_api_lanes.cu
+  void unlock() { m.unlock(); }
+};
+
 struct Context {
   bool ready = false;
   int device = 0;
@@ -142,10 +169,21 @@ struct Context {
   std::unordered_map<uint64_t, VoxList> lists;
   struct DevBuffer { void* p; uint64_t bytes; };
   std::unordered_map<uint64_t, DevBuffer> buffers;  // gvx_buffer_*: device-resident point clouds of the C++ facade
-  std::mutex mu;
+  // collision lanes (gvx_api_lanes.cu): read-only collision queries of several host threads that overlap on the GPU
+  std::unordered_map<uint64_t, std::shared_ptr<Lane>> lanes;
+  bool lanes_pending = false;  // a lane launch since the library's stream last waited for the lanes
+  uint64_t serial_calls = 0;   // serial entry points so far (ApiMutex::lock)
+  ApiMutex mu;
 };
 
 extern Context g;
+// gvx_api_lanes.cu
+int lane_thread_device();
+int lane_acquire(gvx_handle_t h, std::shared_ptr<Lane>* out);
+int lane_join_locked(Lane& L, LaunchCtx* c);
+int lane_launched_locked(Lane& L);
+void lanes_detach_all_locked(std::vector<std::shared_ptr<Lane>>* out);
+void lanes_release(std::vector<std::shared_ptr<Lane>>& v);
 // gvx_api_shard.cu
 int shard_init_from_env();
 void shard_detach();
@@ -220,6 +258,7 @@ inline int coarse_for_collide(Map* m, const uint32_t** out) {
   GVX_CUDA(cudaMemsetAsync(m->coarse, 0, m->coarse_bytes(), g.stream));
   GVX_CUDA(launch_coarse_build(lctx(), m->occ, (long long)(m->occ_bytes() / 16), m->coarse));
   m->coarse_version = m->version;
+  ++g.serial_calls;  // work on the library's stream that did not come through a serial entry point: lanes must join it
   *out = m->coarse;
   return GVX_OK;
 }

@@ -107,7 +107,7 @@ uint64_t gvx_noalloc_scratch_bytes(void) { return kNoAllocScratchBytes; }
 int gvx_batch_robot_collide_noalloc(gvx_handle_t env_map, const float* xyz_d, const uint32_t* cloud_sizes,
                                     uint32_t n_clouds, const int32_t* meanings, const float* transforms_d,
                                     uint32_t n_cfg, const uint8_t* mask32, float thr, uint64_t* counts_d) {
-  std::lock_guard<std::mutex> lk(g.mu);
+  std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map* m = find_map(env_map);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)env_map);

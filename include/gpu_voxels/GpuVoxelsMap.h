@@ -7,6 +7,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <gpu_voxels/helpers/BoostCompat.h>
@@ -114,6 +115,29 @@ struct DualLock
   ~DualLock() { m_a.unlock(); if (!m_same) m_b.unlock(); }
   std::recursive_timed_mutex& m_a; std::recursive_timed_mutex& m_b; bool m_same;
 };
+// One collision lane per WORKER thread (include/gvx.h "collision lanes"): the boolean collisionCheck of a thread other
+// than the first one to ask runs on a stream and result block of its own, so that planner threads checking disjoint
+// map pairs overlap on the GPU -- what the reference's per-map m_mutex allows (GV/voxelmap/TemplateVoxelMap.hpp:329-414).
+// The first thread keeps the serial path; 0 = no lane (first thread, or lane creation failed).
+struct ThreadLane
+{
+  gvx_handle_t handle;
+  bool tried;
+  ThreadLane() : handle(0), tried(false) {}
+  ~ThreadLane() { if (handle) gvx_lane_destroy(handle); }
+};
+inline gvx_handle_t threadLane()
+{
+  static const std::thread::id first = std::this_thread::get_id();
+  if (std::this_thread::get_id() == first) return 0;
+  thread_local ThreadLane tl;
+  if (!tl.tried)
+  {
+    tl.tried = true;
+    if (gvx_lane_create(&tl.handle) != GVX_OK) tl.handle = 0;
+  }
+  return tl.handle;
+}
 }  // namespace detail
 
 }  // namespace gpu_voxels

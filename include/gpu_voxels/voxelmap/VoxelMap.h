@@ -134,6 +134,10 @@ public:
   {
     detail::DualLock guard(this->m_mutex, other->m_mutex);
     int flag = 0;
+    // worker threads query on their own collision lane; GVX_SHARD=z (a collective) and failures fall back to the serial call
+    const gvx_handle_t lane = detail::threadLane();
+    if (lane && gvx_lane_collide_map_map_any(lane, m_handle, other->m_handle, coll_threshold, &flag) == GVX_OK)
+      return flag != 0;
     gvxCheck(gvx_collide_map_map_any(m_handle, other->m_handle, coll_threshold, &flag), "collisionCheck");
     return flag != 0;
   }

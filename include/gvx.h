@@ -483,6 +483,28 @@ int gvx_batch_robot_collide_noalloc(gvx_handle_t env_map, const float* xyz_d, co
                                     uint32_t n_cfg, const uint8_t* mask32, float thr, uint64_t* counts_d);
 uint64_t gvx_noalloc_scratch_bytes(void);
 
+/* ------------------------------------------------------------------ collision lanes: concurrent read-only queries
+ * The reference serialises per MAP: collideWith / collisionCheck lock the two maps' m_mutex
+ * (GV/voxelmap/TemplateVoxelMap.hpp:1043-1075 collisionCheckWithCounterRelativeTransform and the callers above it;
+ * GV/voxellist/TemplateVoxelList.hpp:713-760), so planner threads checking different robot maps against one environment
+ * run at the same time. The serial entry points above share one stream and one result block under one mutex. A lane is
+ * a stream + accumulators + result blocks of its own: the library mutex is held only while the query is validated and
+ * enqueued, the wait for the result runs outside it, and queries issued on different lanes (one lane per thread)
+ * overlap on the GPU. One lane serialises its own callers.
+ * Ordering against the serial API is by events: a lane query sees every insert / clear / collide-with-mark the process
+ * enqueued before the call, and any later serial call is ordered behind the lane queries still in flight. Lane queries
+ * never write voxels (no `mark`) and allocate nothing after gvx_lane_create. Under GVX_SHARD=z they are refused
+ * (GVX_ERR_UNSUPPORTED): a global result needs a collective, which every rank must issue in the same order.
+ * Results equal gvx_collide_map_map(..., mark = 0) / gvx_collide_map_map_any / gvx_collide_list_map(..., mark = 0). */
+int gvx_lane_create(gvx_handle_t* lane);
+int gvx_lane_destroy(gvx_handle_t lane); /* waits for the lane's last query */
+int gvx_lane_count(uint32_t* n);
+int gvx_lane_collide_map_map(gvx_handle_t lane, gvx_handle_t a, gvx_handle_t b, float thr, const int32_t off3[3],
+                             uint64_t* count);
+int gvx_lane_collide_map_map_any(gvx_handle_t lane, gvx_handle_t a, gvx_handle_t b, float thr, int* flag);
+int gvx_lane_collide_list_map(gvx_handle_t lane, gvx_handle_t list, gvx_handle_t map, float thr, const int32_t off3[3],
+                              uint64_t* count);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,233 @@
+"""Collision lanes (include/gvx.h "collision lanes", gvx_api_lanes.cu): read-only collision queries of
+several host threads overlap on the GPU, as the reference's per-map locking allows
+(GV/voxelmap/TemplateVoxelMap.hpp:329-414, 477-519). Checked here: lane results == serial results == oracle for every
+map pair / path, the event ordering against the serial API in both directions (a lane sees earlier inserts; a later
+clear cannot overtake a lane query in flight), many threads on their own lanes while the main thread keeps mutating
+other maps, lane lifetime, and the C++ example with the facade's per-thread lanes."""
+import ctypes as C
+import os
+import subprocess
+import threading
+import time
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+BIT, PROB = 0, 4
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def gv():
+    import gpu_voxels_b200 as g
+    g._lib.init()
+    return g
+
+
+def _cloud(seed, n, lo, hi):
+    rng = np.random.Generator(np.random.PCG64(seed))
+    return (rng.uniform(0, 1, size=(n, 3)) * (np.asarray(hi) - np.asarray(lo)) + np.asarray(lo)).astype(np.float32)
+
+
+def _mk(gv, t, dims, side):
+    return (gv.ProbVoxelMap if t == PROB else gv.BitVectorVoxelMap)(dims, side)
+
+
+@pytest.mark.parametrize("summary", [1, 0])
+@pytest.mark.parametrize("pair", [(PROB, BIT), (BIT, PROB), (BIT, BIT), (PROB, PROB)])
+def test_lane_results_equal_serial_and_oracle(gv, oracle, pair, summary):
+    dims, side = (96, 80, 72), 0.01
+    n = dims[0] * dims[1] * dims[2]
+    ext = np.asarray(dims) * side
+    gv.set_option(gv.GVX_OPT_USE_SUMMARY, summary)
+    try:
+        a, b = _mk(gv, pair[0], dims, side), _mk(gv, pair[1], dims, side)
+        ra, rb = oracle.new_map(pair[0], dims), oracle.new_map(pair[1], dims)
+        pa = _cloud(11, 30000, ext * 0.1, ext * 0.7)
+        pb = np.concatenate([pa[:9000], _cloud(12, 20000, ext * 0.4, ext * 0.95)])
+        a.insertPointCloud(pa, 1); oracle.insert_points(ra, pair[0], dims, side, pa, 1)
+        b.insertPointCloud(pb, 1); oracle.insert_points(rb, pair[1], dims, side, pb, 1)
+        lane = gv.CollisionLane()
+        for off in (None, (1, 0, 0), (-2, 3, 1), (0, 0, -4)):
+            o = 0 if off is None else off[2] * dims[0] * dims[1] + off[1] * dims[0] + off[0]
+            want = oracle.collide_map_map(ra, pair[0], rb, pair[1], n, 1.0, o, False)
+            for k in range(3):  # repeated: the coarse mask appears on the second query of an unmodified map
+                assert lane.collideWith(a, b, 1.0, off) == want, (off, k)
+            assert a.collideWith(b, 1.0, off, mark=False) == want
+        want = oracle.collide_map_map(ra, pair[0], rb, pair[1], n, 1.0, 0, False)
+        assert want > 0 and lane.collisionCheck(a, b) is True
+        empty = _mk(gv, pair[1], dims, side)
+        assert lane.collisionCheck(a, empty) is False and lane.collideWith(a, empty) == 0
+        assert lane.collisionCheck(a, b) is True  # the early-exit flag of the lane does not leak into the next query
+        assert np.array_equal(a.download().reshape(-1).view(np.uint8), ra.view(np.uint8))  # lanes never mark
+        lane.destroy()
+    finally:
+        gv.set_option(gv.GVX_OPT_USE_SUMMARY, 1)
+
+
+def test_lane_list_x_map(gv, oracle):
+    dims, side = (96, 80, 72), 0.01
+    ext = np.asarray(dims) * side
+    lane = gv.CollisionLane()
+    for t in (BIT, PROB):
+        m = _mk(gv, t, dims, side)
+        pm = _cloud(21, 40000, ext * 0.2, ext * 0.9)
+        m.insertPointCloud(pm, 1)
+        lst = gv.BitVectorVoxelList(dims, side)
+        lst.insertPointCloud(np.concatenate([pm[:5000], _cloud(22, 8000, ext * 0.0, ext * 0.5)]), 11)
+        for off in (None, (2, -1, 3)):
+            want = lst.collideWith(m, 1.0, off, mark=False)
+            assert want > 0
+            for k in range(2):
+                assert lane.collideWith(lst, m, 1.0, off) == want
+        empty = gv.BitVectorVoxelList(dims, side)
+        assert lane.collideWith(empty, m) == 0
+    lane.destroy()
+
+
+def test_lane_is_ordered_against_the_serial_api_both_ways(gv):
+    """(1) an insert enqueued on the library's stream is seen by the lane query that follows it; (2) a clear issued right
+    after a lane query -- while its kernel (a 134 M-voxel stream, ~0.6 ms) is still running -- does not overtake it"""
+    dims, side = (512, 512, 512), 0.002
+    ext = np.asarray(dims) * side
+    gv.set_option(gv.GVX_OPT_USE_SUMMARY, 0)  # voxel streaming: the lane kernel runs for hundreds of microseconds
+    try:
+        env, rob = gv.ProbVoxelMap(dims, side), gv.BitVectorVoxelMap(dims, side)
+        lane = gv.CollisionLane()
+        seen_full = seen_zero = 0
+        for it in range(12):
+            pts = _cloud(100 + it, 80000, ext * 0.1, ext * 0.9)
+            n_rob = 20000 + 1000 * it
+
+            def fill():
+                env.insertPointCloud(pts, 1)
+                rob.insertPointCloud(pts[:n_rob], 5)
+
+            fill()
+            full = rob.collideWith(env, 1.0, mark=False)
+            assert full > 15000
+            rob.clearMap(); env.clearMap()
+            # (1) inserts on the library's stream, the lane query at once: it must see all of them
+            fill()
+            assert lane.collideWith(rob, env) == full
+            # (2) a lane query from another thread; this thread clears both maps 0 .. 550 us later, i.e. before, while
+            # or after the lane's kernel runs. The query was enqueued either before the clears (-> full) or after (-> 0)
+            box = {}
+            th = threading.Thread(target=lambda: box.__setitem__("n", lane.collideWith(rob, env)))
+            th.start()
+            t_end = time.perf_counter() + 50e-6 * it
+            while time.perf_counter() < t_end:
+                pass
+            rob.clearMap(); env.clearMap()
+            th.join()
+            assert box["n"] in (full, 0), (it, box["n"], full)
+            seen_full += box["n"] == full
+            seen_zero += box["n"] == 0
+            assert lane.collideWith(rob, env) == 0
+        print("lane query vs. clear: %d saw the maps, %d saw them cleared" % (seen_full, seen_zero))
+        lane.destroy()
+    finally:
+        gv.set_option(gv.GVX_OPT_USE_SUMMARY, 1)
+
+
+def test_many_threads_on_lanes_while_the_main_thread_mutates_other_maps(gv):
+    dims, side = (128, 128, 96), 0.01
+    ext = np.asarray(dims) * side
+    env = gv.ProbVoxelMap(dims, side)
+    env.insertPointCloud(_cloud(1, 200000, ext * 0.0, ext * 1.0), 1)
+    n_thr, n_q = 6, 150
+    robots, want = [], []
+    for t in range(n_thr):
+        r = gv.BitVectorVoxelMap(dims, side)
+        r.insertPointCloud(_cloud(50 + t, 20000 + 3000 * t, ext * 0.1 * (t % 3), ext * (0.5 + 0.08 * t)), 7 + t)
+        robots.append(r)
+        want.append(r.collideWith(env, 1.0, mark=False))
+    assert len(set(want)) == n_thr and min(want) > 0
+    lanes = [gv.CollisionLane() for _ in range(n_thr)]
+    bad, errs = [], []
+    go = threading.Event()
+
+    def worker(t):
+        try:
+            go.wait()
+            for k in range(n_q):
+                got = lanes[t].collideWith(robots[t], env) if k % 3 else int(lanes[t].collisionCheck(robots[t], env)) * want[t]
+                if got != want[t]:
+                    bad.append((t, k, got, want[t]))
+        except Exception as e:  # noqa: BLE001
+            errs.append((t, repr(e)))
+
+    ths = [threading.Thread(target=worker, args=(t,)) for t in range(n_thr)]
+    for th in ths:
+        th.start()
+    # the main thread keeps the serial API busy with maps the lanes do not read
+    scratch, other = gv.BitVectorVoxelMap(dims, side), gv.ProbVoxelMap(dims, side)
+    pts = _cloud(99, 15000, ext * 0.2, ext * 0.8)
+    other.insertPointCloud(pts, 1)
+    go.set()
+    serial = []
+    for k in range(60):
+        scratch.clearMap()
+        scratch.insertPointCloud(pts[: 5000 + 100 * k], 3)
+        serial.append(scratch.collideWith(other, 1.0, mark=bool(k & 1)))
+    for th in ths:
+        th.join()
+    assert not errs, errs
+    assert not bad, bad[:5]
+    scratch2 = gv.BitVectorVoxelMap(dims, side)
+    for k in range(0, 60, 7):  # the serial results were not disturbed either
+        scratch2.clearMap()
+        scratch2.insertPointCloud(pts[: 5000 + 100 * k], 3)
+        assert scratch2.collideWith(other, 1.0, mark=False) == serial[k]
+    for ln in lanes:
+        ln.destroy()
+
+
+def test_lane_lifetime_and_errors(gv):
+    L = gv._lib.load()
+    n0 = C.c_uint32(99)
+    gv._lib.check(L.gvx_lane_count(C.byref(n0)))
+    lane = gv.CollisionLane()
+    n1 = C.c_uint32(0)
+    gv._lib.check(L.gvx_lane_count(C.byref(n1)))
+    assert n1.value == n0.value + 1
+    a, b = gv.BitVectorVoxelMap((32, 32, 32), 0.01), gv.BitVectorVoxelMap((32, 32, 16), 0.01)
+    with pytest.raises(gv._lib.GvxError):
+        lane.collideWith(a, b)                    # dimension mismatch, as on the serial path
+    cnt = C.c_uint64(0)
+    assert L.gvx_lane_collide_map_map(C.c_uint64(987654321), a.handle, a.handle, 1.0, None, C.byref(cnt)) != 0
+    assert b"lane" in L.gvx_last_error()
+    h = lane.handle
+    lane.destroy()
+    assert L.gvx_lane_collide_map_map(h, a.handle, a.handle, 1.0, None, C.byref(cnt)) != 0
+    assert L.gvx_lane_destroy(h) != 0
+    gv._lib.check(L.gvx_lane_count(C.byref(n1)))
+    assert n1.value == n0.value
+
+
+def build_lanes_example():
+    from gpu_voxels_b200 import build as gvx_build
+    gvx_build.build()
+    src = os.path.join(ROOT, "tests", "cpp", "lanes_example.cpp")
+    exe = os.path.join(ROOT, "tests", "cpp", "lanes_example")
+    deps = [src, os.path.join(ROOT, "include", "gvx.h"), os.path.join(ROOT, "gpu_voxels_b200", "libgvx.so")]
+    if not (os.path.exists(exe) and all(os.path.getmtime(exe) >= os.path.getmtime(d) for d in deps)):
+        subprocess.check_call([os.environ.get("CXX", "g++"), "-std=c++14", "-O2", "-Wall", "-Wextra", "-Werror",
+                               "-I" + os.path.join(ROOT, "include"), src, "-L" + os.path.join(ROOT, "gpu_voxels_b200"),
+                               "-lgvx", "-Wl,-rpath," + os.path.join(ROOT, "gpu_voxels_b200"),
+                               "-Wl,-rpath,$ORIGIN/../../gpu_voxels_b200", "-lpthread", "-o", exe])
+    return exe
+
+
+def test_cpp_threads_through_the_facade_and_the_c_abi():
+    exe = build_lanes_example()
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    lines = dict(l.split(" ", 1) for l in r.stdout.strip().splitlines())
+    assert lines["mismatches"] == "0" and lines["facade_mismatches"] == "0"
+    assert int(lines["facade_lanes"]) >= 2                  # the worker threads got lanes of their own
+    print(r.stdout)
+    serial, lanes = float(lines["serial_us_per_check"]), float(lines["lanes_us_per_check"])
+    assert lanes < 1.25 * serial, (serial, lanes)          # never a loss; the measured gain is in DESIGN.md 6.6
