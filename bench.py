@@ -909,7 +909,11 @@ def run_gpu_arm(args):
                                               "how": "GVX_MEM_HOST frame then a collide that returns the count, nothing in flight"}},
                 "gpu_launches": c4["launches_per_region"],
                 "roofline": {"bound": "hbm", "kernel": "k_collide_prob_prob<mark>", "achieved": achieved, "peak": peak,
-                             "unit": "GB/s", "frac": achieved / peak, "traffic": traffic_of("r2_collide_prob_prob_traffic.json"),
+                             "unit": "GB/s", "frac": achieved / peak,
+                             # the ncu capture is of the whole-grid launch (N = 1): per launch like `achieved`, so null
+                             # for the slab launches of N > 1 (same kernel, 1/N of the bytes; ratio to algorithmic 1.000)
+                             "traffic": traffic_of("r2_collide_prob_prob_traffic.json") if world == 1 else None,
+                             "traffic_captured_at": "N = 1 (profiles/r2_collide_prob_prob_traffic.json): 1.000 x algorithmic",
                              "peak_source": peak_src, "algorithmic_bytes_per_launch": C4_BYTES_PER_VOXEL * c4["n_loc"],
                              "algorithmic_bytes_per_voxel": C4_BYTES_PER_VOXEL, "kernel_ms_avg": k_ms,
                              "kernel_ms_avg_how": "%d launches back to back between one CUDA event pair on the launching "
