@@ -64,6 +64,7 @@ SIGNATURES = {
     "gvx_map_shift_sv_ids": (C.c_int, [u64, u32]),
     "gvx_shard_info": (C.c_int, [P(C.c_int), P(C.c_int), P(C.c_int)]),
     "gvx_shard_allreduce_u64": (C.c_int, [vp, C.c_int, C.c_int]),
+    "gvx_shard_allgather": (C.c_int, [vp, u32, vp]),
     "gvx_shard_connect_host": (C.c_int, [C.c_int, C.c_int, C.c_char_p]),
     "gvx_shard_disconnect": (C.c_int, []),
     "gvx_peer_mailbox_create": (C.c_int, [vp]),

@@ -132,6 +132,13 @@ static int shutdown_locked(std::vector<std::shared_ptr<Lane>>* lanes) {
   if (!g.ready) return GVX_OK;
   cudaDeviceSynchronize();
   lanes_detach_all_locked(lanes);
+  {  // peers' slabs mapped for offset collides: every rank unmaps, then a barrier, then the owners free
+    bool any_open = false;
+    for (auto& kv : g.maps)
+      if (kv.second.peers_open) { shard_map_close_peers(&kv.second); any_open = true; }
+    if (any_open) shard_barrier();
+  }
+  if (g.halo_counts_d) { cudaFree(g.halo_counts_d); g.halo_counts_d = nullptr; }
   shard_detach();
   for (auto& kv : g.maps) {
     if (kv.second.owned && kv.second.data) cudaFree(kv.second.data);
@@ -340,8 +347,11 @@ static int map_make(gvx_handle_t* h, int map_type, void* wrap, uint32_t dx, uint
 int gvx_map_create(gvx_handle_t* h, int map_type, uint32_t dx, uint32_t dy, uint32_t dz, float side) {
   std::lock_guard<ApiMutex> lk(g.mu);
   uint32_t z0 = 0, z1 = dz;
-  if (shard_active() && dz >= (uint32_t)g.shard_world) shard_slab(dz, &z0, &z1);  // GVX_SHARD=z: this rank's slab
-  return map_make(h, map_type, nullptr, dx, dy, dz, side, z0, z1);
+  const bool slab = shard_active() && dz >= (uint32_t)g.shard_world;
+  if (slab) shard_slab(dz, &z0, &z1);  // GVX_SHARD=z: this rank's slab
+  const int rc = map_make(h, map_type, nullptr, dx, dy, dz, side, z0, z1);
+  if (rc == GVX_OK && slab) find_map(*h)->shard_made = true;
+  return rc;
 }
 int gvx_map_create_slab(gvx_handle_t* h, int map_type, uint32_t dx, uint32_t dy, uint32_t dz, float side, uint32_t z0,
                         uint32_t z1) {
@@ -360,6 +370,11 @@ int gvx_map_destroy(gvx_handle_t h) {
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
   GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if (m->peers_open) {  // GVX_SHARD=z, collective like the mapping was: nobody frees a slab a peer still has mapped
+    shard_map_close_peers(m);
+    int rc = shard_barrier();
+    if (rc) return rc;
+  }
   if (m->owned) GVX_CUDA(cudaFree(m->data));
   if (m->occ) GVX_CUDA(cudaFree(m->occ));
   if (m->coarse) GVX_CUDA(cudaFree(m->coarse));
@@ -733,7 +748,7 @@ int gvx_update_logodds_multi(gvx_handle_t h, const float* xyz_sensor, int mem_ki
 
 // ---- collision counting, map x map --------------------------------------------------------------------
 static int collide_prepare(gvx_handle_t ha, gvx_handle_t hb, const int32_t off3[3], Map** a, Map** b, int64_t* off,
-                           int64_t* i0, int64_t* i1) {
+                           int64_t* i0, int64_t* i1, bool allow_halo = false) {
   *a = find_map(ha);
   *b = find_map(hb);
   if (!*a || !*b) return fail(GVX_ERR_INVALID, "unknown map handle");
@@ -742,8 +757,12 @@ static int collide_prepare(gvx_handle_t ha, gvx_handle_t hb, const int32_t off3[
     return fail(GVX_ERR_DIM_MISMATCH, "maps differ in dimensions or slab");
   int64_t o = 0;
   if (off3) o = (int64_t)off3[2] * A->dx * A->dy + (int64_t)off3[1] * A->dx + (int64_t)off3[0];  // getVoxelIndexSigned
-  if (o != 0 && A->sharded())
-    return fail(GVX_ERR_UNSUPPORTED, "offset collide on a z-slab map needs a halo exchange (replicas only)");
+  // an offset shifts the LINEAR index: on z-slab maps the partner voxel of a slab's first / last layers (any offset) or
+  // of every voxel (z offsets) lives in another rank's slab. Under GVX_SHARD=z the synchronous collides read it from the
+  // peer over CUDA IPC (collide_halo below); every other combination is refused
+  if (o != 0 && A->sharded() && !(allow_halo && shard_active() && A->shard_made && B->shard_made))
+    return fail(GVX_ERR_UNSUPPORTED, "offset collide on a z-slab map needs the peers' slabs: supported by the synchronous "
+                                     "collideWith under GVX_SHARD=z only (replicas only otherwise)");
   const int64_t n = (int64_t)A->n_voxels();
   *off = o;
   *i0 = o < 0 ? -o : 0;
@@ -763,13 +782,59 @@ static int fixup_summary_after_mark(Map* a, int8_t thr_i, bool mark) {
   return GVX_OK;
 }
 
+// Offset collide on z-slab maps under GVX_SHARD=z (collective). The reference shifts THIS map's pointer
+// (GV/voxelmap/TemplateVoxelMap.hpp:486-519: getVoxelPtrSignedOffset on m_dev_data): voxel i + off of `a` meets voxel i of
+// `b`, for every grid index i with both in range. This rank owns the a-voxels of its slab (it counts and marks them);
+// their partners i = j - off lie in some ranks' slabs of `b`. For every rank s whose b-slab holds partners: one ordinary
+// offset-collide launch over that sub-range, with b = rank s's slab mapped through CUDA IPC (loads over NVLink; own
+// slab: local) and the offset rewritten slab-to-slab. Counts land in one device word per peer slab, are summed on the
+// host and all-reduced.
+static int collide_halo(Map* a, Map* b, int64_t off, int8_t thr, int thr_b_or_same, bool mark, uint64_t* count) {
+  if (a == b && mark)
+    return fail(GVX_ERR_UNSUPPORTED, "marking a z-slab map while colliding it with a shifted copy of itself: the peers read "
+                                     "what this rank marks");
+  int rc = shard_map_open_peers(b);  // first time: collective CUDA IPC exchange
+  if (rc) return rc;
+  // what the peers are about to read must be complete on every rank, and nobody may be ahead by a whole call
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  if ((rc = shard_barrier())) return rc;
+  if (!g.halo_counts_d) GVX_CUDA(cudaMalloc((void**)&g.halo_counts_d, kMaxPeers * sizeof(unsigned long long)));
+  GVX_CUDA(cudaMemsetAsync(g.halo_counts_d, 0, kMaxPeers * sizeof(unsigned long long), g.stream));
+  const int64_t layer = (int64_t)a->dx * a->dy, n_tot = layer * a->dz;
+  const int64_t A0 = (int64_t)a->z0 * layer, A1 = (int64_t)a->z1 * layer;
+  // grid indices i of b with a partner i + off inside this rank's slab of a
+  const int64_t lo_valid = std::max<int64_t>(A0 - off, off < 0 ? -off : 0), hi_valid = std::min<int64_t>(A1 - off, off > 0 ? n_tot - off : n_tot);
+  for (int s = 0; s < g.shard_world; ++s) {
+    uint32_t zs0, zs1;
+    shard_slab_of(s, b->dz, &zs0, &zs1);
+    const int64_t B0 = (int64_t)zs0 * layer, B1 = (int64_t)zs1 * layer;
+    const int64_t lo = std::max(lo_valid, B0), hi = std::min(hi_valid, B1);
+    if (lo >= hi) continue;
+    LaunchCtx c = lctx();
+    c.result_hmap_d = nullptr;  // device-only result, one word per peer slab
+    // the kernels index b[i'] and a[i' + off'] with i' local to rank s's b-slab: a's local index is i + off - A0
+    GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->peer_data[s], b->type, lo - B0, hi - B0, B0 + off - A0, thr,
+                                    mark, false, g.halo_counts_d + s, nullptr, nullptr, nullptr, nullptr, thr_b_or_same));
+  }
+  if ((rc = fixup_summary_after_mark(a, thr, mark))) return rc;
+  unsigned long long parts[kMaxPeers];
+  GVX_CUDA(cudaMemcpyAsync(parts, g.halo_counts_d, sizeof parts, cudaMemcpyDeviceToHost, g.stream));
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  uint64_t c = 0;
+  for (int s = 0; s < g.shard_world; ++s) c += parts[s];
+  if ((rc = shard_allreduce(&c, 1, 0))) return rc;  // also: every rank's reads are done before anyone mutates `b` again
+  if (count) *count = c;
+  return GVX_OK;
+}
+
 int gvx_collide_map_map(gvx_handle_t ha, gvx_handle_t hb, float thr, const int32_t off3[3], int mark, uint64_t* count) {
   std::lock_guard<ApiMutex> lk(g.mu);
   GVX_NEED_INIT();
   Map *a, *b;
   int64_t off, i0, i1;
-  int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1);
+  int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1, true);
   if (rc) return rc;
+  if (off != 0 && a->sharded()) return collide_halo(a, b, off, float_to_probability(thr), kSameThreshold, mark != 0, count);
   // GVX_SHARD=z: the maps are this rank's slabs and the caller expects the count over the whole grid -- all-reduced
   // inside the collide kernel when the peers' mailboxes are mapped, else through the host segment
   const bool global = shard_active() && a->sharded();
@@ -798,8 +863,9 @@ int gvx_collide_map_map_thresholds(gvx_handle_t ha, gvx_handle_t hb, int thresho
     return fail(GVX_ERR_INVALID, "thresholds (%d, %d) outside the int8 range of Probability", threshold1, threshold2);
   Map *a, *b;
   int64_t off, i0, i1;
-  int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1);
+  int rc = collide_prepare(ha, hb, off3, &a, &b, &off, &i0, &i1, true);
   if (rc) return rc;
+  if (off != 0 && a->sharded()) return collide_halo(a, b, off, (int8_t)threshold1, threshold2, mark != 0, count);
   const bool global = shard_active() && a->sharded();
   const bool fused = global && g.shard_fused && g.peer_world > 1;
   const uint32_t *ca = nullptr, *cb = nullptr;

@@ -149,6 +149,88 @@ void shard_slab(uint32_t dz, uint32_t* z0, uint32_t* z1) {
   *z1 = *z0 + base + (rank < rem ? 1u : 0u);
 }
 
+void shard_slab_of(int rank_, uint32_t dz, uint32_t* z0, uint32_t* z1) {
+  const uint32_t world = (uint32_t)g.shard_world, rank = (uint32_t)rank_;
+  const uint32_t base = dz / world, rem = dz % world;
+  *z0 = rank * base + (rank < rem ? rank : rem);
+  *z1 = *z0 + base + (rank < rem ? 1u : 0u);
+}
+
+// every rank's `bytes` bytes, in rank order, on every rank (the all-reduce's buffers and sequence numbers)
+int shard_allgather(const void* mine, size_t bytes, void* all) {
+  if (g.shard_world <= 1) { memcpy(all, mine, bytes); return GVX_OK; }
+  if (!s_seg) return fail(GVX_ERR_NOT_INITIALIZED, "sharding is not connected");
+  const size_t words = (bytes + 7) / 8;
+  if (words > (size_t)kShardWords) return fail(GVX_ERR_INVALID, "host all-gather of %zu bytes (max %d)", bytes, kShardWords * 8);
+  const uint64_t e = ++s_seq;
+  const int par = (int)(e & 1);
+  uint64_t buf[kShardWords] = {};
+  memcpy(buf, mine, bytes);
+  for (size_t k = 0; k < words; ++k) s_seg->data[par][g.shard_rank][k] = buf[k];
+  __sync_synchronize();
+  s_seg->seq[g.shard_rank] = e;
+  for (int r = 0; r < g.shard_world; ++r)
+    if (!wait_until([&] { return s_seg->seq[r] >= e; }, 120.0))
+      return fail(GVX_ERR_IO, "host all-gather: rank %d did not arrive (every rank must make the same calls)", r);
+  __sync_synchronize();
+  for (int r = 0; r < g.shard_world; ++r) {
+    for (size_t k = 0; k < words; ++k) buf[k] = s_seg->data[par][r][k];
+    memcpy((unsigned char*)all + (size_t)r * bytes, buf, bytes);
+  }
+  return GVX_OK;
+}
+
+int shard_barrier() {
+  uint64_t z = 0;
+  return shard_allreduce(&z, 1, 0);
+}
+
+// Collective (every rank, same map, same order): map every peer's slab of map m into this process through CUDA IPC, so
+// that a collide with an offset can read the voxels that live in a neighbour's slab (the halo) straight over NVLink.
+// Opened on the first such collide of the map and kept until the map is destroyed.
+int shard_map_open_peers(Map* m) {
+  if (m->peers_open) return GVX_OK;
+  if (!shard_active() || !m->shard_made || !m->owned)
+    return fail(GVX_ERR_UNSUPPORTED, "offset collide on a z-slab map needs the peers' slabs: only maps made by "
+                                     "gvx_map_create under GVX_SHARD=z can be mapped (replicas only otherwise)");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+  unsigned char mine[64] = {}, all[kMaxPeers][64];
+  uint64_t bad = 0;
+  cudaIpcMemHandle_t hd;
+  if (cudaIpcGetMemHandle(&hd, m->data) != cudaSuccess) { cudaGetLastError(); bad = 1; }
+  else memcpy(mine, &hd, 64);
+  int rc = shard_allgather(mine, 64, all);
+  if (rc) return rc;
+  if ((rc = shard_allreduce(&bad, 1, 0))) return rc;
+  if (!bad) {
+    for (int r = 0; r < g.shard_world && !bad; ++r) {
+      if (r == g.shard_rank) { m->peer_data[r] = m->data; continue; }
+      cudaIpcMemHandle_t hr;
+      memcpy(&hr, all[r], 64);
+      void* p = nullptr;
+      if (cudaIpcOpenMemHandle(&p, hr, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); bad = 1; }
+      else m->peer_data[r] = p;
+    }
+    if ((rc = shard_allreduce(&bad, 1, 0))) return rc;  // all ranks agree; also: nobody proceeds before all have mapped
+  }
+  if (bad) {
+    shard_map_close_peers(m);
+    return fail(GVX_ERR_UNSUPPORTED, "a rank could not map a peer's slab through CUDA IPC (offset collides on z-slab maps "
+                                     "need peer access between the ranks' GPUs)");
+  }
+  m->peers_open = true;
+  return GVX_OK;
+}
+
+// local: drop the mappings of the peers' slabs (the owner frees its slab only after a barrier, gvx_map_destroy)
+void shard_map_close_peers(Map* m) {
+  for (int r = 0; r < kMaxPeers; ++r) {
+    if (m->peer_data[r] && m->peer_data[r] != m->data) cudaIpcCloseMemHandle(m->peer_data[r]);
+    m->peer_data[r] = nullptr;
+  }
+  m->peers_open = false;
+}
+
 void shard_detach() {
   if (s_seg) {
     munmap((void*)s_seg, sizeof(ShardSeg));
@@ -211,6 +293,12 @@ int gvx_shard_allreduce_u64(uint64_t* values, int n_sum, int n_or) {
   std::lock_guard<ApiMutex> lk(g.mu);
   if (!values && n_sum + n_or > 0) return fail(GVX_ERR_INVALID, "null values");
   return shard_allreduce(values, n_sum, n_or);
+}
+
+int gvx_shard_allgather(const void* mine, uint32_t bytes, void* all) {
+  std::lock_guard<ApiMutex> lk(g.mu);
+  if ((!mine || !all) && bytes > 0) return fail(GVX_ERR_INVALID, "null buffer");
+  return shard_allgather(mine, bytes, all);
 }
 
 int gvx_shard_connect_host(int rank, int world, const char* rendezvous) {

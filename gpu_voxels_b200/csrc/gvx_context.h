@@ -1,5 +1,6 @@
 // gvx_context.h -- process-wide context, handle tables and error plumbing shared by the gvx_api*.cu files.
 #pragma once
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -29,6 +30,11 @@ struct Map {
   // handed out.
   uint32_t* occ = nullptr;
   bool occ_valid = false;
+  // GVX_SHARD=z: made collectively by gvx_map_create (every rank holds a slab of the same grid, created in the same
+  // order); peer_data[r] = rank r's slab mapped through CUDA IPC once an offset collide needed it (gvx_api_shard.cu)
+  bool shard_made = false;
+  bool peers_open = false;
+  void* peer_data[kMaxPeers] = {};
   // the writable raw device pointer has been handed out (gvx_map_device_ptr): the caller may write voxels at any time,
   // so NO library call re-validates the summary until gvx_map_refresh_summary says the writes are over
   bool raw_exported = false;
@@ -162,6 +168,7 @@ struct Context {
   int collide_tma = -1;  // GVX_OPT_COLLIDE_TMA: -1 auto (TMA where it measured faster), 0 never, 1..5 always (shape k)
   bool use_summary = true;  // GVX_OPT_USE_SUMMARY: collide kernels may read occupancy summaries instead of voxels
   bool use_coarse = true;   // GVX_OPT_USE_COARSE: ... and skip 4096-voxel chunks a map's coarse mask says are empty
+  unsigned long long* halo_counts_d = nullptr;  // one count per peer slab of an offset collide on z-slab maps (gvx_api.cu collide_halo)
   uint64_t launches = 0;
   uint64_t summary_fallbacks = 0;  // collides that streamed voxels because a library-owned map's summary was invalid
   uint64_t next_handle = 1;
@@ -189,6 +196,11 @@ int shard_init_from_env();
 void shard_detach();
 int shard_allreduce(uint64_t* v, int n_sum, int n_or);  // host-side, through the job's shared-memory segment
 void shard_slab(uint32_t dz, uint32_t* z0, uint32_t* z1);
+void shard_slab_of(int rank, uint32_t dz, uint32_t* z0, uint32_t* z1);
+int shard_allgather(const void* mine, size_t bytes, void* all);
+int shard_barrier();
+int shard_map_open_peers(Map* m);     // collective
+void shard_map_close_peers(Map* m);   // local
 inline bool shard_active() { return g.shard_world > 1; }
 // gvx_api.cu: the peer mailbox entry points without taking g.mu
 int mailbox_create_locked(void* ipc_handle64);

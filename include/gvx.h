@@ -288,10 +288,19 @@ int gvx_collide_list_map_per_meaning_allreduce(gvx_handle_t list, gvx_handle_t m
  * collide kernel over NVLink peer memory (GVX_SHARD_FUSED=0: through the host segment), gvx_collide_map_map_any / _types /
  * _bitcheck and gvx_collide_list_map / _types / _mask / _per_meaning through the host segment (sum of counts, OR of
  * masks). Every rank must make the same calls in the same order. The *_async variants and downloads stay local to
- * the slab; offsets on slab maps are refused (GVX_ERR_UNSUPPORTED: halo exchange). */
+ * the slab.
+ * collideWith with an OFFSET (gvx_collide_map_map, gvx_collide_map_map_thresholds): the offset shifts the linear voxel
+ * index (GV/voxelmap/TemplateVoxelMap.hpp:486-519, getVoxelIndexSigned), so the partners of a slab's voxels lie in
+ * other ranks' slabs. On the first such call every rank maps the peers' slabs of the map through CUDA IPC (collective;
+ * kept until the map is destroyed, which then contains a barrier); the collide then runs one launch per peer slab that
+ * holds partners, reading them over NVLink, and returns the global count. Needs peer access between the ranks' GPUs
+ * (or ranks sharing a GPU); the *_async / *_allreduce variants, lanes and explicit gvx_map_create_slab maps still refuse
+ * offsets (GVX_ERR_UNSUPPORTED). */
 int gvx_shard_info(int* rank, int* world, int* fused);
 /* utility for callers with results of their own: sum of values[0..n_sum), OR of the next n_or words, over all ranks */
 int gvx_shard_allreduce_u64(uint64_t* values, int n_sum, int n_or);
+/* every rank's `bytes` bytes (at most 2176), in rank order, into `all` (world x bytes) on every rank */
+int gvx_shard_allgather(const void* mine, uint32_t bytes, void* all);
 /* join / leave the job's rendezvous explicitly instead of through the environment: host side only (no GPU needed, no
  * peer mailboxes: every global result then goes through the host segment). Call before gvx_init, or in a process that
  * only needs gvx_shard_allreduce_u64 (the CPU tests do). */

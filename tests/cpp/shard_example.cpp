@@ -42,6 +42,11 @@ int main()
   std::printf("bit_x_prob %zu\n", bits->collideWith(first, 1.0f));
   std::printf("prob_x_bit %zu\n", first->collideWith(bits, 1.0f));
 
+  gvl->addMap(MT_BITVECTOR_VOXELMAP, "myBitMap2");
+  voxelmap::BitVectorVoxelMap* bits2 = gvl->getMap("myBitMap2")->as<voxelmap::BitVectorVoxelMap>();
+  bits2->insertPointCloud(geometry_generation::createBoxOfPoints(Vector3f(0.1f, 0.1f, 0.55f), Vector3f(0.8f, 0.8f, 1.45f), 0.01f),
+                          BitVoxelMeaning(33));
+
   // a voxel list (replicated on every rank) against the maps
   voxellist::BitVectorVoxelList* list = gvl->getMap("myList")->as<voxellist::BitVectorVoxelList>();
   list->insertPointCloud(geometry_generation::createBoxOfPoints(Vector3f(0.3f, 0.3f, 0.05f), Vector3f(0.7f, 0.7f, 1.45f), 0.02f),
@@ -57,6 +62,19 @@ int main()
   BitVectorVoxel mask;
   mask.bitVector().setBit(12);
   std::printf("list_mask %zu\n", list->collideWithTypeMask(bits, mask, 1.0f));
+
+  // collideWith with an offset: voxel i + offset of this map meets voxel i of the other. Sharded, the partners of a slab's
+  // voxels live in other ranks' slabs (z offsets: all of them; x / y offsets: the slab's edge layers) and are read from
+  // the peers. 150 layers / 3 ranks = slabs of 50: an offset of 55 layers reaches past the neighbouring slab.
+  std::printf("off_z %zu\n", first->collideWith(second, 1.0f, Vector3i(0, 0, 7)));
+  std::printf("off_xyz %zu\n", first->collideWith(second, 1.0f, Vector3i(3, -2, -11)));
+  std::printf("off_far %zu\n", second->collideWith(first, 1.0f, Vector3i(1, 0, -55)));
+  std::printf("off_xy %zu\n", first->collideWith(second, 1.0f, Vector3i(-9, 5, 0)));
+  std::printf("off_bit_prob %zu\n", bits->collideWith(first, 1.0f, Vector3i(-5, 4, 23)));
+  std::printf("off_prob_bit %zu\n", first->collideWith(bits, 1.0f, Vector3i(2, 1, -37)));
+  std::printf("off_bit_bit %zu\n", bits->collideWith(bits2, 1.0f, Vector3i(0, -3, 52)));
+  std::printf("off_thresholds %u\n", first->collisionCheckWithCounterRelativeTransform(second, DefaultCollider(Probability(40), Probability(100)), Vector3i(4, 4, -19)));
+  std::printf("off_none %zu\n", first->collideWith(second, 1.0f, Vector3i(0, 0, 149)));
 
   gvl->clearMap("mySecondMap");
   std::printf("after_clear %zu\n", first->collideWith(second));

@@ -44,6 +44,10 @@ def test_same_caller_code_one_process_vs_three_slabs():
     assert int(lines["linkage"]) == 8000            # example_how_to_link/README.txt:21 "about 8000 collisions"
     assert lines["check"] == "1" and lines["after_clear"] == "0"
     assert lines["types"].split()[1:] == ["14", "46"] and int(lines["list_x_bit"]) > 0
+    # offset collides: non-trivial answers on one GPU (the sharded runs below must reproduce them through the peers' slabs)
+    for k in ("off_z", "off_xyz", "off_far", "off_xy", "off_bit_prob", "off_prob_bit", "off_bit_bit", "off_thresholds"):
+        assert int(lines[k]) > 0, (k, lines[k])
+    assert lines["off_none"] == "0"
     outs, errs = run_spmd(exe, 3, False, devices="0,0,0")   # 150 layers -> slabs of 50
     for rank, o in enumerate(outs):
         assert o == single[0], "rank %d of 3 prints different results:\n%s\nvs\n%s" % (rank, o, single[0])

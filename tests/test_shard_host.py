@@ -47,6 +47,13 @@ def _rank_main(rank, world, name, rounds, q):
             v[257:] = [1 << (rank + 8 * (k % 5)), 0, (0xF0 << rank) & 0xFFFF, k if rank == 0 else 0]
             _lib.check(L.gvx_shard_allreduce_u64(v.ctypes.data_as(C.c_void_p), 257, 4))
             out.append(v.copy())
+            if k % 3 == 0:  # an all-gather between the all-reduces (same buffers, same sequence): 64-byte "handles"
+                mine = np.full(64, 16 * rank + (k & 15), np.uint8)
+                mine[0] = k
+                got = np.zeros((world, 64), np.uint8)
+                _lib.check(L.gvx_shard_allgather(mine.ctypes.data_as(C.c_void_p), 64, got.ctypes.data_as(C.c_void_p)))
+                for r in range(world):
+                    assert got[r, 0] == k and (got[r, 1:] == 16 * r + (k & 15)).all(), (k, r, got[r, :4])
         one = np.array([rank == 1], np.uint64)   # an "any collision" flag: OR
         _lib.check(L.gvx_shard_allreduce_u64(one.ctypes.data_as(C.c_void_p), 0, 1))
         _lib.check(L.gvx_shard_disconnect())
