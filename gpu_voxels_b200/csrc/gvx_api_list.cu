@@ -504,6 +504,7 @@ int gvx_collide_list_map_per_meaning_allreduce(gvx_handle_t hl, gvx_handle_t hm,
   if (rc) return rc;
   // a collective: every rank launches, also with an empty list or an empty slab range (size 0)
   LaunchCtx c = lctx_allreduce();
+  if (c.peer.world > 1) c.peer.vec_epoch = ++g.peer_vec_epoch;  // the vector area keeps a sequence of its own
   c.result_hmap_d = nullptr;  // the result stays on the device
   if ((rc = list_launch(c, 3, a, thr, mark != 0, nullptr, (unsigned long long*)counts257_d))) return rc;
   GVX_CUDA(cudaMemcpyAsync(counts257_d + 1, g.result_d->per_meaning, 256 * sizeof(uint64_t), cudaMemcpyDeviceToDevice, g.stream));

@@ -152,6 +152,7 @@ struct Context {
   PeerSlot* peer_ptr[kMaxPeers] = {};
   int peer_rank = 0, peer_world = 1;
   unsigned long long peer_epoch = 0;
+  unsigned long long peer_vec_epoch = 0;  // collectives that used the mailbox's vector area (PeerReduce::vec_epoch)
   // sensor-frame dispatch over NVLink peer memory (gvx_peer_dispatch_*, gvx_dispatch.cu): this rank's head + inboxes,
   // the peers' allocations mapped through CUDA IPC, the collective sequence number, a mapped host word for time-outs
   unsigned char* disp_mem = nullptr;

@@ -121,6 +121,10 @@ struct PeerReduce {
   int rank;
   int world;
   unsigned long long epoch;  // > 0, identical on all ranks for one collective, strictly increasing
+  // the same for the collectives that use the vector area (a sequence of its own: a slot of the area is rewritten every
+  // second VECTOR collective, so its 16-bit tag can never meet a stale word of 65 536 collectives ago, however many
+  // scalar-only collectives lie in between); 0: no vector part
+  unsigned long long vec_epoch;
 };
 // Sensor-frame dispatch over NVLink peer memory (gvx_update_logodds_dispatch, gvx_dispatch.cu; one process per GPU,
 // z-slab maps). Every rank owns ONE allocation, mapped into all peers through CUDA IPC: a DispatchHead followed by

@@ -275,7 +275,7 @@ k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxel
   if (MODE == 3 && last) {
     __threadfence();  // acquire side of the arrival ticket: the other CTAs' histogram adds are in L2
     unsigned long long h = __ldcg(&out_d->per_meaning[threadIdx.x]);
-    if (pr.world > 1) {  // sharded map: the 256 per-meaning counts are all-reduced here, over NVLink peer memory, like the
+    if (pr.world > 1 && pr.vec_epoch != 0) {  // sharded map: the 256 per-meaning counts are all-reduced here, over NVLink peer memory, like the
       h = peer_allreduce_word(h, threadIdx.x + 1, pr);  // count in finish_block (word 0 of the vector area stays unused)
       out_d->per_meaning[threadIdx.x] = h;
     }

@@ -44,8 +44,8 @@ __device__ __forceinline__ unsigned long long peer_allreduce_sum(unsigned long l
 // the n_words x world stores and polls of a CTA overlap. v (in registers) is replaced by the sum over the ranks;
 // a rank that never arrives yields ~0ull (bounded spin).
 __device__ __forceinline__ unsigned long long peer_allreduce_word(unsigned long long mine, int word, const PeerReduce& pr) {
-  const int par = (int)(pr.epoch & 1ull);
-  const unsigned long long tag = (pr.epoch & 0xFFFFull) << 48;
+  const int par = (int)(pr.vec_epoch & 1ull);
+  const unsigned long long tag = (pr.vec_epoch & 0xFFFFull) << 48;
   const unsigned long long packed = tag | (mine & 0xFFFFFFFFFFFFull);
   for (int r = 0; r < pr.world; ++r) {
     unsigned long long* dst = reinterpret_cast<unsigned long long*>(reinterpret_cast<unsigned char*>(pr.peers[r]) + kPeerVecOffset) +
@@ -61,7 +61,7 @@ __device__ __forceinline__ unsigned long long peer_allreduce_word(unsigned long 
     unsigned long long v;
     for (;;) {
       asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(src) : "memory");
-      if ((v >> 48) == (pr.epoch & 0xFFFFull)) break;
+      if ((v >> 48) == (pr.vec_epoch & 0xFFFFull)) break;
       if (clock64() - t0 > 8000000000ll) { ok = false; break; }
     }
     sum += v & 0xFFFFFFFFFFFFull;

@@ -94,13 +94,18 @@ def main():
         got = out_d.cpu().numpy().astype(np.uint64)
         assert int(got[0]) == w_tot and np.array_equal(got[1:], w_per), (it, int(got[0]), w_tot)
     # ... and with the 257 words all-reduced INSIDE the kernel over the peers' mailboxes (no NCCL launch), repeated: both
-    # epoch parities of the vector area
-    for it in range(5):
+    # epoch parities of the vector area, with scalar-only collectives in between (the vector area keeps an epoch sequence
+    # of its own: 1, 2 or 0 scalar all-reduces between two vector ones shift the two sequences against each other)
+    for it in range(7):
         out_d.fill_(-1)
         _lib.check(L.gvx_collide_list_map_per_meaning_allreduce(lst.handle, env.handle, 1.0, 0, C.c_void_p(out_d.data_ptr())))
         _lib.check(L.gvx_sync())
         got = out_d.cpu().numpy().astype(np.uint64)
         assert int(got[0]) == w_tot and np.array_equal(got[1:], w_per), ("in-kernel vector all-reduce", it, int(got[0]), w_tot)
+        for k in range(it % 3):
+            host = C.c_uint64(0)
+            _lib.check(L.gvx_collide_list_map_allreduce(lst.handle, env.handle, 1.0, 0, C.byref(host), None))
+            assert host.value == l_want, ("scalar all-reduce between vector ones", it, k, host.value, l_want)
     # an offset moves the slab boundaries inside the list: ids + off must fall into the slab
     off = (3, -2, 5)
     lin = off[2] * dims[0] * dims[1] + off[1] * dims[0] + off[0]
