@@ -13,17 +13,8 @@ CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
 
 
 def _build():
-    from gpu_voxels_b200 import build as gvx_build
-    gvx_build.build()
-    deps = [SRC, os.path.join(ROOT, "tests", "cpp", "mini_boost_test.h"), os.path.join(ROOT, "include", "gvx.h")]
-    for d, _, fs in os.walk(os.path.join(ROOT, "include", "gpu_voxels")):
-        deps += [os.path.join(d, f) for f in fs]
-    if os.path.exists(EXE) and all(os.path.getmtime(EXE) >= os.path.getmtime(d) for d in deps):
-        return
-    subprocess.check_call([CXX, "-std=c++14", "-O1", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "include"),
-                           SRC, "-L" + os.path.join(ROOT, "gpu_voxels_b200"), "-lgvx",
-                           "-Wl,-rpath," + os.path.join(ROOT, "gpu_voxels_b200"),
-                           "-Wl,-rpath,$ORIGIN/../../gpu_voxels_b200", "-lpthread", "-o", EXE])
+    from _cppbuild import build_cpp, facade_headers
+    build_cpp(SRC, EXE, [os.path.join(ROOT, "tests", "cpp", "mini_boost_test.h")] + facade_headers())
 
 
 def test_facade_compiles_and_links_with_plain_gxx():

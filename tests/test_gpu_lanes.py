@@ -208,17 +208,9 @@ def test_lane_lifetime_and_errors(gv):
 
 
 def build_lanes_example():
-    from gpu_voxels_b200 import build as gvx_build
-    gvx_build.build()
-    src = os.path.join(ROOT, "tests", "cpp", "lanes_example.cpp")
-    exe = os.path.join(ROOT, "tests", "cpp", "lanes_example")
-    deps = [src, os.path.join(ROOT, "include", "gvx.h"), os.path.join(ROOT, "gpu_voxels_b200", "libgvx.so")]
-    if not (os.path.exists(exe) and all(os.path.getmtime(exe) >= os.path.getmtime(d) for d in deps)):
-        subprocess.check_call([os.environ.get("CXX", "g++"), "-std=c++14", "-O2", "-Wall", "-Wextra", "-Werror",
-                               "-I" + os.path.join(ROOT, "include"), src, "-L" + os.path.join(ROOT, "gpu_voxels_b200"),
-                               "-lgvx", "-Wl,-rpath," + os.path.join(ROOT, "gpu_voxels_b200"),
-                               "-Wl,-rpath,$ORIGIN/../../gpu_voxels_b200", "-lpthread", "-o", exe])
-    return exe
+    from _cppbuild import build_cpp, facade_headers
+    return build_cpp(os.path.join(ROOT, "tests", "cpp", "lanes_example.cpp"), os.path.join(ROOT, "tests", "cpp", "lanes_example"),
+                     facade_headers(), opt="-O2")
 
 
 def test_cpp_threads_through_the_facade_and_the_c_abi():

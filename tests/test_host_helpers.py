@@ -14,11 +14,8 @@ CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
 
 
 def _exe():
-    hdr = os.path.join(ROOT, "include", "gpu_voxels", "helpers", "MathHelpers.h")
-    if not (os.path.exists(EXE) and os.path.getmtime(EXE) >= max(os.path.getmtime(SRC), os.path.getmtime(hdr))):
-        subprocess.check_call([CXX, "-std=c++14", "-O2", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "include"),
-                               SRC, "-o", EXE])
-    return EXE
+    from _cppbuild import build_cpp, facade_headers
+    return build_cpp(SRC, EXE, facade_headers(), opt="-O2", link_gvx=False)
 
 
 def _run(mode, args):
@@ -54,9 +51,6 @@ def test_probabilistic_voxel_value_type_equals_reference():
     """include/gpu_voxels/voxel/ProbabilisticVoxel.h against the reference's header for EVERY (occupancy, delta) pair and
     every meaning (tests/golden/prob_voxel.npz, from GV/voxel/ProbabilisticVoxel.hpp compiled for the host)"""
     g = np.load(os.path.join(ROOT, "tests", "golden", "prob_voxel.npz"))
-    hdr = os.path.join(ROOT, "include", "gpu_voxels", "voxel", "ProbabilisticVoxel.h")
-    if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
-        os.remove(EXE)
     lines = subprocess.run([_exe(), "prob"], capture_output=True, text=True, check=True).stdout.split("\n")
     upd = np.array([[int(v) for v in ln.split()] for ln in lines[:256]], np.int8)
     assert np.array_equal(upd, g["update"])
@@ -68,9 +62,6 @@ def test_bitvector_window_check_and_shift_equal_reference():
     """bitMarginCollisionCheck / performLeftShift of the facade (include/gpu_voxels/voxel/BitVoxel.h) on the 1500 golden
     vectors recorded from the reference's BitVector.h (tests/golden/sweptvolume.npz): results and every output byte"""
     g = np.load(os.path.join(ROOT, "tests", "golden", "sweptvolume.npz"))
-    hdr = os.path.join(ROOT, "include", "gpu_voxels", "voxel", "BitVoxel.h")
-    if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
-        os.remove(EXE)
     hx = lambda v: bytes(v).hex()  # noqa: E731
     n = len(g["v1"])
     fresh = np.zeros(32, np.uint8)
@@ -94,10 +85,6 @@ def test_default_collider_thresholds_equal_reference():
     collider (tests/golden/conversions.npz), the Probability -> float round trip used for the C ABI, and the five
     collide() predicates"""
     g = np.load(os.path.join(ROOT, "tests", "golden", "conversions.npz"))
-    for h in ("DefaultCollider.h", "SVCollider.h"):
-        hdr = os.path.join(ROOT, "include", "gpu_voxels", "voxel", h)
-        if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
-            os.remove(EXE)
     lines = _run("f2p", g["thr"].view(np.uint32))
     got = np.array([[int(v) for v in ln.split()] for ln in lines if ln not in ("ok", "MISMATCH")])
     want = g["f2p"].astype(np.int32).astype(np.int8).astype(np.int32)   # the reference keeps the low 8 bits
@@ -134,10 +121,6 @@ def _same_bits(a, b):
 
 
 def _geometry_golden():
-    for h in ("GeometryGeneration.h", "cuda_datatypes.h"):
-        hdr = os.path.join(ROOT, "include", "gpu_voxels", "helpers", h)
-        if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
-            os.remove(EXE)
     return np.load(os.path.join(ROOT, "tests", "golden", "geometry.npz"))
 
 
@@ -247,9 +230,6 @@ def test_vector_and_matrix_value_api_equals_reference(tmp_path):
 def test_reference_bitvector_host_tests_pass_on_the_facade():
     """GV/test/testing_bitvector.cu:36-194 (logic operations, stream operators, setByte, noneButEmpty, left shift of the
     swept-volume IDs) run against include/gpu_voxels/voxel/BitVoxel.h"""
-    hdr = os.path.join(ROOT, "include", "gpu_voxels", "voxel", "BitVoxel.h")
-    if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(hdr):
-        os.remove(EXE)
     r = subprocess.run([_exe(), "bitvector"], capture_output=True, text=True, check=True)
     assert r.stdout.strip() == "ok", r.stdout
 
@@ -257,17 +237,12 @@ def test_reference_bitvector_host_tests_pass_on_the_facade():
 def test_reference_matrix_host_tests_pass_on_the_facade():
     """GV/test/testing_cudaMath.cu:33-195 (equality, approximate equality, transpose, product, inverse, roll / pitch /
     yaw round trips of 1000 random rotations) run against include/gpu_voxels/helpers/cuda_datatypes.h"""
-    _geometry_golden()  # rebuilds the helper if the headers are newer
     r = subprocess.run([_exe(), "cudamath"], capture_output=True, text=True, check=True)
     assert r.stdout.strip() == "ok", r.stdout[-2000:]
 
 
 def test_option_stand_in_and_boost_aliases():
     """include/icl_core_config/Config.h (the option handling the reference's examples use) and helpers/BoostCompat.h"""
-    for h in (os.path.join(ROOT, "include", "icl_core_config", "Config.h"),
-              os.path.join(ROOT, "include", "gpu_voxels", "helpers", "BoostCompat.h")):
-        if os.path.exists(EXE) and os.path.getmtime(EXE) < os.path.getmtime(h):
-            os.remove(EXE)
     run = lambda *a: subprocess.run([_exe(), "compat"] + list(a), capture_output=True, text=True, check=True).stdout.strip()
     assert run("--device-identifier=cam7", "--flag") == "cam7|1|1|0"
     assert run("-id", "cam9") == "cam9|1|0|0"

@@ -19,16 +19,8 @@ SHARD_EXE = os.path.join(ROOT, "tests", "cpp", "shard_example")
 
 
 def build_shard_example():
-    from gpu_voxels_b200 import build as gvx_build
-    gvx_build.build()
-    deps = [SHARD_SRC, os.path.join(ROOT, "include", "gvx.h"), os.path.join(ROOT, "gpu_voxels_b200", "libgvx.so")]
-    if os.path.exists(SHARD_EXE) and all(os.path.getmtime(SHARD_EXE) >= os.path.getmtime(d) for d in deps):
-        return SHARD_EXE
-    subprocess.check_call([CXX, "-std=c++14", "-O1", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "include"),
-                           SHARD_SRC, "-L" + os.path.join(ROOT, "gpu_voxels_b200"), "-lgvx",
-                           "-Wl,-rpath," + os.path.join(ROOT, "gpu_voxels_b200"),
-                           "-Wl,-rpath,$ORIGIN/../../gpu_voxels_b200", "-lpthread", "-o", SHARD_EXE])
-    return SHARD_EXE
+    from _cppbuild import build_cpp, facade_headers
+    return build_cpp(SHARD_SRC, SHARD_EXE, facade_headers())
 
 
 def _rank_main(rank, world, name, rounds, q):
