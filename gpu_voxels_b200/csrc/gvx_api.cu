@@ -135,7 +135,7 @@ static int shutdown_locked(std::vector<std::shared_ptr<Lane>>* lanes) {
   {  // peers' slabs mapped for offset collides: every rank unmaps, then a barrier, then the owners free
     bool any_open = false;
     for (auto& kv : g.maps)
-      if (kv.second.peers_open) { shard_map_close_peers(&kv.second); any_open = true; }
+      if (kv.second.peers_open) { any_open |= kv.second.peer_world == 0; shard_map_close_peers(&kv.second); }
     if (any_open) shard_barrier();
   }
   if (g.halo_counts_d) { cudaFree(g.halo_counts_d); g.halo_counts_d = nullptr; }
@@ -370,10 +370,12 @@ int gvx_map_destroy(gvx_handle_t h) {
   Map* m = find_map(h);
   if (!m) return fail(GVX_ERR_INVALID, "unknown map handle %llu", (unsigned long long)h);
   GVX_CUDA(cudaStreamSynchronize(g.stream));
-  if (m->peers_open) {  // GVX_SHARD=z, collective like the mapping was: nobody frees a slab a peer still has mapped
+  if (m->peers_open) {
+    const bool spmd = m->peer_world == 0;
     shard_map_close_peers(m);
-    int rc = shard_barrier();
-    if (rc) return rc;
+    // GVX_SHARD=z: collective like the mapping was -- nobody frees a slab a peer still has mapped. Explicitly connected
+    // maps (gvx_map_connect_peers): the host program disconnects on every rank and synchronises them before destroying
+    if (spmd) { int rc = shard_barrier(); if (rc) return rc; }
   }
   if (m->owned) GVX_CUDA(cudaFree(m->data));
   if (m->occ) GVX_CUDA(cudaFree(m->occ));
@@ -760,9 +762,12 @@ static int collide_prepare(gvx_handle_t ha, gvx_handle_t hb, const int32_t off3[
   // an offset shifts the LINEAR index: on z-slab maps the partner voxel of a slab's first / last layers (any offset) or
   // of every voxel (z offsets) lives in another rank's slab. Under GVX_SHARD=z the synchronous collides read it from the
   // peer over CUDA IPC (collide_halo below); every other combination is refused
-  if (o != 0 && A->sharded() && !(allow_halo && shard_active() && A->shard_made && B->shard_made))
+  const bool spmd_halo = shard_active() && A->shard_made && B->shard_made;
+  const bool explicit_halo = B->peers_open && B->peer_world > 0;  // gvx_map_connect_peers
+  if (o != 0 && A->sharded() && !(allow_halo && (spmd_halo || explicit_halo)))
     return fail(GVX_ERR_UNSUPPORTED, "offset collide on a z-slab map needs the peers' slabs: supported by the synchronous "
-                                     "collideWith under GVX_SHARD=z only (replicas only otherwise)");
+                                     "collideWith under GVX_SHARD=z, or after gvx_map_connect_peers on the other map "
+                                     "(replicas only otherwise)");
   const int64_t n = (int64_t)A->n_voxels();
   *off = o;
   *i0 = o < 0 ? -o : 0;
@@ -793,20 +798,27 @@ static int collide_halo(Map* a, Map* b, int64_t off, int8_t thr, int thr_b_or_sa
   if (a == b && mark)
     return fail(GVX_ERR_UNSUPPORTED, "marking a z-slab map while colliding it with a shifted copy of itself: the peers read "
                                      "what this rank marks");
-  int rc = shard_map_open_peers(b);  // first time: collective CUDA IPC exchange
-  if (rc) return rc;
-  // what the peers are about to read must be complete on every rank, and nobody may be ahead by a whole call
-  GVX_CUDA(cudaStreamSynchronize(g.stream));
-  if ((rc = shard_barrier())) return rc;
+  // explicit slab maps (gvx_map_connect_peers): the host program owns the communicator -- it orders the ranks around
+  // the call and all-reduces the LOCAL count this returns. GVX_SHARD=z: both happen here.
+  const bool spmd = !(b->peers_open && b->peer_world > 0);
+  int rc = GVX_OK;
+  if (spmd) {
+    if ((rc = shard_map_open_peers(b))) return rc;  // first time: collective CUDA IPC exchange
+    // what the peers are about to read must be complete on every rank, and nobody may be ahead by a whole call
+    GVX_CUDA(cudaStreamSynchronize(g.stream));
+    if ((rc = shard_barrier())) return rc;
+  }
+  const int world = spmd ? g.shard_world : b->peer_world;
   if (!g.halo_counts_d) GVX_CUDA(cudaMalloc((void**)&g.halo_counts_d, kMaxPeers * sizeof(unsigned long long)));
   GVX_CUDA(cudaMemsetAsync(g.halo_counts_d, 0, kMaxPeers * sizeof(unsigned long long), g.stream));
   const int64_t layer = (int64_t)a->dx * a->dy, n_tot = layer * a->dz;
   const int64_t A0 = (int64_t)a->z0 * layer, A1 = (int64_t)a->z1 * layer;
   // grid indices i of b with a partner i + off inside this rank's slab of a
   const int64_t lo_valid = std::max<int64_t>(A0 - off, off < 0 ? -off : 0), hi_valid = std::min<int64_t>(A1 - off, off > 0 ? n_tot - off : n_tot);
-  for (int s = 0; s < g.shard_world; ++s) {
+  for (int s = 0; s < world; ++s) {
     uint32_t zs0, zs1;
-    shard_slab_of(s, b->dz, &zs0, &zs1);
+    if (spmd) shard_slab_of(s, b->dz, &zs0, &zs1);
+    else { zs0 = b->peer_z[s]; zs1 = b->peer_z[s + 1]; }
     const int64_t B0 = (int64_t)zs0 * layer, B1 = (int64_t)zs1 * layer;
     const int64_t lo = std::max(lo_valid, B0), hi = std::min(hi_valid, B1);
     if (lo >= hi) continue;
@@ -821,8 +833,8 @@ static int collide_halo(Map* a, Map* b, int64_t off, int8_t thr, int thr_b_or_sa
   GVX_CUDA(cudaMemcpyAsync(parts, g.halo_counts_d, sizeof parts, cudaMemcpyDeviceToHost, g.stream));
   GVX_CUDA(cudaStreamSynchronize(g.stream));
   uint64_t c = 0;
-  for (int s = 0; s < g.shard_world; ++s) c += parts[s];
-  if ((rc = shard_allreduce(&c, 1, 0))) return rc;  // also: every rank's reads are done before anyone mutates `b` again
+  for (int s = 0; s < world; ++s) c += parts[s];
+  if (spmd && (rc = shard_allreduce(&c, 1, 0))) return rc;  // also: every rank's reads are done before anyone mutates `b` again
   if (count) *count = c;
   return GVX_OK;
 }

@@ -229,6 +229,7 @@ void shard_map_close_peers(Map* m) {
     m->peer_data[r] = nullptr;
   }
   m->peers_open = false;
+  m->peer_world = 0;
 }
 
 void shard_detach() {
@@ -299,6 +300,60 @@ int gvx_shard_allgather(const void* mine, uint32_t bytes, void* all) {
   std::lock_guard<ApiMutex> lk(g.mu);
   if ((!mine || !all) && bytes > 0) return fail(GVX_ERR_INVALID, "null buffer");
   return shard_allgather(mine, bytes, all);
+}
+
+// ---- explicit slab maps: the host program exchanges the handles with its own communicator -------------------------------
+int gvx_map_ipc_handle(gvx_handle_t hm, void* handle64_out) {
+  std::lock_guard<ApiMutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(hm);
+  if (!m || !handle64_out) return fail(GVX_ERR_INVALID, "unknown map handle or null output");
+  if (!m->owned) return fail(GVX_ERR_UNSUPPORTED, "wrapped (caller-owned) memory: export it with cudaIpcGetMemHandle yourself");
+  cudaIpcMemHandle_t hd;
+  GVX_CUDA(cudaIpcGetMemHandle(&hd, m->data));
+  memcpy(handle64_out, &hd, 64);
+  return GVX_OK;
+}
+
+int gvx_map_connect_peers(gvx_handle_t hm, int rank, int world, const void* all_handles, const uint32_t* z_bounds) {
+  std::lock_guard<ApiMutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(hm);
+  if (!m || !all_handles || !z_bounds) return fail(GVX_ERR_INVALID, "unknown map handle or null argument");
+  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return fail(GVX_ERR_INVALID, "bad rank %d / world %d", rank, world);
+  if (m->peers_open) return fail(GVX_ERR_INVALID, "the map's peers are connected already");
+  if (z_bounds[0] != 0 || z_bounds[world] != m->dz || z_bounds[rank] != m->z0 || z_bounds[rank + 1] != m->z1)
+    return fail(GVX_ERR_INVALID, "z_bounds do not describe this map: slab [%u,%u) of %u layers as rank %d of %d", m->z0, m->z1, m->dz, rank, world);
+  for (int r = 0; r < world; ++r)
+    if (z_bounds[r] > z_bounds[r + 1]) return fail(GVX_ERR_INVALID, "z_bounds must not decrease");
+  for (int r = 0; r < world; ++r) {
+    if (r == rank) { m->peer_data[r] = m->data; continue; }
+    cudaIpcMemHandle_t hr;
+    memcpy(&hr, (const unsigned char*)all_handles + 64 * (size_t)r, 64);
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, hr, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      shard_map_close_peers(m);
+      return fail(GVX_ERR_UNSUPPORTED, "cudaIpcOpenMemHandle(rank %d's slab) failed: %s", r, cudaGetErrorString(e));
+    }
+    m->peer_data[r] = p;
+  }
+  m->peer_world = world;
+  m->peer_rank = rank;
+  for (int r = 0; r <= world; ++r) m->peer_z[r] = z_bounds[r];
+  m->peers_open = true;
+  return GVX_OK;
+}
+
+int gvx_map_disconnect_peers(gvx_handle_t hm) {
+  std::lock_guard<ApiMutex> lk(g.mu);
+  GVX_NEED_INIT();
+  Map* m = find_map(hm);
+  if (!m) return fail(GVX_ERR_INVALID, "unknown map handle");
+  GVX_CUDA(cudaStreamSynchronize(g.stream));
+  shard_map_close_peers(m);
+  return GVX_OK;
 }
 
 int gvx_shard_connect_host(int rank, int world, const char* rendezvous) {

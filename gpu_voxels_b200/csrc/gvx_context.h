@@ -35,6 +35,10 @@ struct Map {
   bool shard_made = false;
   bool peers_open = false;
   void* peer_data[kMaxPeers] = {};
+  // ... or connected by the host program for an explicit slab map (gvx_map_connect_peers): world and slab boundaries as
+  // given there (peer_world == 0: the GVX_SHARD partition applies)
+  int peer_world = 0, peer_rank = 0;
+  uint32_t peer_z[kMaxPeers + 1] = {};
   // the writable raw device pointer has been handed out (gvx_map_device_ptr): the caller may write voxels at any time,
   // so NO library call re-validates the summary until gvx_map_refresh_summary says the writes are over
   bool raw_exported = false;

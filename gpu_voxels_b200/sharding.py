@@ -7,7 +7,8 @@ The reference is single-GPU. The partition:
     unsharded map. Every rank sees the whole cloud and keeps the points of its slab (gvx_map_create_slab).
   * collide map x map / list x map: purely local, then ONE all-reduce of (count | per-meaning counts | 256-bit mask).
   * batch of robot configurations: the environment map is replicated, the BATCH is split; counts are all-gathered.
-  * a non-zero offset.z needs a halo from the neighbour slab: not supported on slab maps (GVX_ERR_UNSUPPORTED).
+  * a collide with an offset needs voxels of other ranks' slabs: after connect_map_peers they are read from the
+    owners' GPUs through CUDA IPC mappings (collide_with_offset); refused otherwise (GVX_ERR_UNSUPPORTED).
 No CUDA code here and no voxel arithmetic: only ranges and collectives.
 """
 import numpy as np
@@ -155,6 +156,46 @@ def _exchange_ipc(create, connect, disconnect, group=None):
         return False
     dist.barrier(group=group)
     return True
+
+
+def connect_map_peers(slab_map, group=None):
+    """Offset collides on explicit z-slab maps: export this rank's slab of `slab_map` (the map that will be the OTHER side
+    of collideWith), all-gather the CUDA IPC handles, map every peer's slab (gvx_map_connect_peers). Afterwards
+    `a.collideWith(slab_map, thr, offset)` returns this rank's part of the count -- sum it over the ranks, and keep the
+    ranks ordered around the call (collide_with_offset below does both). Returns True when connected."""
+    import ctypes as C
+    from . import _lib
+    dist = _dist()
+    if not dist.is_initialized():
+        return False
+    L = _lib.init()
+    world = dist.get_world_size(group)
+    bounds = slab_bounds(slab_map.m_dim[2], world)
+
+    def create():
+        mine = (C.c_ubyte * 64)()
+        return L.gvx_map_ipc_handle(slab_map.handle, mine), mine
+
+    return _exchange_ipc(create,
+                         lambda r, w, blob: L.gvx_map_connect_peers(slab_map.handle, r, w, C.c_char_p(blob),
+                                                                    bounds.ctypes.data_as(C.c_void_p)),
+                         lambda: L.gvx_map_disconnect_peers(slab_map.handle), group)
+
+
+def collide_with_offset(a, b, coll_threshold, offset, mark=True, group=None):
+    """global count of a.collideWith(b, thr, offset) on explicit slab maps whose `b` went through connect_map_peers: every
+    rank's earlier work is complete before any rank reads a peer's slab, and every rank's collide is complete before
+    anybody continues"""
+    import torch
+    from . import _lib
+    dist = _dist()
+    L = _lib.init()
+    _lib.check(L.gvx_sync())
+    dist.barrier(group=group)
+    local = a.collideWith(b, coll_threshold, offset, mark=mark)
+    t = torch.tensor([int(local)], dtype=torch.int64, device=_device_for_backend())
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)  # also the barrier behind the reads
+    return int(t.item())
 
 
 def connect_peer_dispatch(capacity_points, group=None):

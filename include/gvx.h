@@ -299,6 +299,17 @@ int gvx_collide_list_map_per_meaning_allreduce(gvx_handle_t list, gvx_handle_t m
 int gvx_shard_info(int* rank, int* world, int* fused);
 /* utility for callers with results of their own: sum of values[0..n_sum), OR of the next n_or words, over all ranks */
 int gvx_shard_allreduce_u64(uint64_t* values, int n_sum, int n_or);
+/* Offset collides on EXPLICIT z-slab maps (gvx_map_create_slab), for host programs with a communicator of their own:
+ * every rank exports its slab of the map that will be the `other` side (gvx_map_ipc_handle: a CUDA IPC handle, 64
+ * bytes), the program all-gathers the handles and every rank connects (all_handles: world x 64 bytes in rank order;
+ * z_bounds: world + 1 slab boundaries, rank r owns layers [z_bounds[r], z_bounds[r + 1])). From then on
+ * gvx_collide_map_map / gvx_collide_map_map_thresholds with an offset read the partner voxels that lie in other ranks'
+ * slabs from the owners' GPUs and return the LOCAL count (this rank's voxels of `a`): the program sums it over the
+ * ranks, and orders the ranks around the call (every rank's earlier inserts complete before any rank collides; every
+ * rank's collide complete before any rank modifies the map again). Disconnect on every rank, synchronise, then destroy. */
+int gvx_map_ipc_handle(gvx_handle_t map, void* handle64_out);
+int gvx_map_connect_peers(gvx_handle_t map, int rank, int world, const void* all_handles, const uint32_t* z_bounds);
+int gvx_map_disconnect_peers(gvx_handle_t map);
 /* every rank's `bytes` bytes (at most 2176), in rank order, into `all` (world x bytes) on every rank */
 int gvx_shard_allgather(const void* mine, uint32_t bytes, void* all);
 /* join / leave the job's rendezvous explicitly instead of through the environment: host side only (no GPU needed, no

@@ -26,6 +26,18 @@ from oracle import gvoracle as orc  # noqa: E402
 BIT, PROB = 0, 4
 
 
+class pytest_raises:
+    """the library must refuse (GvxError) inside the block"""
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, et, ev, tb):
+        from gpu_voxels_b200 import _lib
+        assert et is not None and issubclass(et, _lib.GvxError), "expected the library to refuse the call"
+        return True
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -72,6 +84,26 @@ def main():
     _lib.check(L.gvx_collide_map_map_async(rob.handle, env.handle, 1.0, None, 0, C.c_void_p(cnt_d.data_ptr())))
     dist.all_reduce(cnt_d)
     assert int(cnt_d.item()) == want
+    # collideWith with an OFFSET on explicit slab maps: the partners in other ranks' slabs are read from the owners' GPUs
+    # (gvx_map_connect_peers on the `other` map); before the connection the call is refused
+    with pytest_raises():
+        rob.collideWith(env, 1.0, (0, 0, 3), mark=False)
+    assert sharding.connect_map_peers(env), "CUDA IPC mapping of the peers' slabs refused"
+    for off in ((0, 0, 3), (2, -1, -9), (5, 0, 0), (-1, 4, dims[2] // 2 + 1)):
+        lin = off[2] * dims[0] * dims[1] + off[1] * dims[0] + off[0]
+        w = orc.collide_map_map(r_rob.copy(), BIT, r_env, PROB, n, 1.0, lin, False)
+        got = sharding.collide_with_offset(rob, env, 1.0, off, mark=False)
+        assert got == w, ("offset collide on slab maps", off, got, w)
+    off = (1, 1, -2)   # ... and with marks: the marked slab is the slice of the oracle's marked map
+    lin = off[2] * dims[0] * dims[1] + off[1] * dims[0] + off[0]
+    r_rob_m = r_rob.copy()
+    w = orc.collide_map_map(r_rob_m, BIT, r_env, PROB, n, 1.0, lin, True)
+    rob_m = gv.BitVectorVoxelMap(dims, side, slab=slab)
+    rob_m.insertMetaPointCloud(gv.MetaPointCloud([rob_pts[:50000], rob_pts[50000:]]), [9, 70])
+    assert sharding.collide_with_offset(rob_m, env, 1.0, off, mark=True) == w and w > 0
+    assert np.array_equal(rob_m.download().reshape(-1), r_rob_m[first * 32:(first + n_loc) * 32]), "marks of an offset collide"
+    _lib.check(L.gvx_map_disconnect_peers(env.handle))
+    dist.barrier()
     # list x map: replicated list, sharded map
     lst = gv.BitVectorVoxelList(dims, side)
     lst.insertMetaPointCloud(gv.MetaPointCloud([rob_pts[:50000], rob_pts[50000:]]), [9, 70])
