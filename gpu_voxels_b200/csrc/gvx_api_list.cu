@@ -490,9 +490,7 @@ int gvx_collide_list_map_per_meaning_async(gvx_handle_t hl, gvx_handle_t hm, flo
   }
   LaunchCtx c = lctx();
   c.result_hmap_d = nullptr;  // the result stays on the device
-  if ((rc = list_launch(c, 3, a, thr, mark != 0, nullptr, (unsigned long long*)counts257_d))) return rc;
-  GVX_CUDA(cudaMemcpyAsync(counts257_d + 1, g.result_d->per_meaning, 256 * sizeof(uint64_t), cudaMemcpyDeviceToDevice, g.stream));
-  return GVX_OK;
+  return list_launch(c, 3, a, thr, mark != 0, nullptr, (unsigned long long*)counts257_d);  // the kernel writes all 257 words
 }
 
 int gvx_collide_list_map_per_meaning_allreduce(gvx_handle_t hl, gvx_handle_t hm, float thr, int mark, uint64_t* counts257_d) {
@@ -506,9 +504,7 @@ int gvx_collide_list_map_per_meaning_allreduce(gvx_handle_t hl, gvx_handle_t hm,
   LaunchCtx c = lctx_allreduce();
   if (c.peer.world > 1) c.peer.vec_epoch = ++g.peer_vec_epoch;  // the vector area keeps a sequence of its own
   c.result_hmap_d = nullptr;  // the result stays on the device
-  if ((rc = list_launch(c, 3, a, thr, mark != 0, nullptr, (unsigned long long*)counts257_d))) return rc;
-  GVX_CUDA(cudaMemcpyAsync(counts257_d + 1, g.result_d->per_meaning, 256 * sizeof(uint64_t), cudaMemcpyDeviceToDevice, g.stream));
-  return GVX_OK;
+  return list_launch(c, 3, a, thr, mark != 0, nullptr, (unsigned long long*)counts257_d);  // the kernel writes all 257 words
 }
 
 int gvx_collide_list_map_allreduce(gvx_handle_t hl, gvx_handle_t hm, float thr, int mark, uint64_t* count,

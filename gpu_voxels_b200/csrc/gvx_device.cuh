@@ -160,6 +160,9 @@ struct ReduceScratch {
   unsigned int any_flag;     // early exit of the boolean collisionCheck: raised by the first CTA that finds a collision,
                              // lowered by the last CTA of that launch (finish_block)
   unsigned int pad_[3];
+  // per-meaning histogram of list x map collides (k_collide_list_map<MODE 3>): every CTA adds its 256 bins, the last CTA
+  // reads, publishes and ZEROES them -- like `total`, so no memset precedes a launch
+  unsigned long long pm_acc[256];
 };
 
 }  // namespace gvx

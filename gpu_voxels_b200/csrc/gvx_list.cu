@@ -267,18 +267,21 @@ k_collide_list_map(const uint32_t* __restrict__ ids, uint8_t* __restrict__ voxel
   if (MODE == 3) {
     __syncthreads();
     const uint32_t h = sh_hist[threadIdx.x];
-    if (h) atomicAdd(&out_d->per_meaning[threadIdx.x], (unsigned long long)h);  // zeroed by the launcher
+    if (h) atomicAdd(&scratch->pm_acc[threadIdx.x], (unsigned long long)h);  // zero at launch: the last CTA of the launch before reset it
     __threadfence();
     __syncthreads();
   }
   const bool last = finish_block<MODE == 1>(cnt, acc, scratch, out_d, out_h, count_out_d, pr);
   if (MODE == 3 && last) {
     __threadfence();  // acquire side of the arrival ticket: the other CTAs' histogram adds are in L2
-    unsigned long long h = __ldcg(&out_d->per_meaning[threadIdx.x]);
-    if (pr.world > 1 && pr.vec_epoch != 0) {  // sharded map: the 256 per-meaning counts are all-reduced here, over NVLink peer memory, like the
+    unsigned long long h = __ldcg(&scratch->pm_acc[threadIdx.x]);
+    scratch->pm_acc[threadIdx.x] = 0ull;  // self-resetting, like the count accumulator
+    if (pr.world > 1 && pr.vec_epoch != 0)  // sharded map: the 256 per-meaning counts are all-reduced here, over NVLink peer memory, like the
       h = peer_allreduce_word(h, threadIdx.x + 1, pr);  // count in finish_block (word 0 of the vector area stays unused)
-      out_d->per_meaning[threadIdx.x] = h;
-    }
+    out_d->per_meaning[threadIdx.x] = h;
+    // a device destination holds 257 words in this mode: the count (finish_block) and the per-meaning counts behind it --
+    // no copy kernel follows the launch
+    if (count_out_d) count_out_d[1 + threadIdx.x] = h;
     if (out_h) {
       out_h->per_meaning[threadIdx.x] = h;
       __threadfence_system();
@@ -345,10 +348,8 @@ cudaError_t launch_collide_list_map(const LaunchCtx& c, int mode, const uint32_t
   const int grid = (int)(work < 1 ? 1 : (work > max_grid ? max_grid : work));
   const uint8_t* map = (const uint8_t*)map_;
   uint8_t* vx = (uint8_t*)voxels;
-  if (mode == 3) {
-    cudaError_t e = cudaMemsetAsync(c.result_d->per_meaning, 0, sizeof(c.result_d->per_meaning), c.stream);
-    if (e != cudaSuccess) return e;
-  }
+  // mode 3: count_out_d, when given, receives 257 words (count, then 256 per-meaning counts); the histogram
+  // accumulators live in ReduceScratch and reset themselves -- ONE launch, no memset before, no copy after
   ++*c.launches;
 #define GVX_LM(MT)                                                                                                      \
   switch (mode) {                                                                                                       \
