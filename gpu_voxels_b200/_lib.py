@@ -68,6 +68,7 @@ SIGNATURES = {
     "gvx_map_ipc_handle": (C.c_int, [u64, vp]),
     "gvx_map_connect_peers": (C.c_int, [u64, C.c_int, C.c_int, vp, vp]),
     "gvx_map_disconnect_peers": (C.c_int, [u64]),
+    "gvx_halo_plan": (C.c_int, [u32, u32, u32, vp, C.c_int, C.c_int, vp, vp]),
     "gvx_shard_connect_host": (C.c_int, [C.c_int, C.c_int, C.c_char_p]),
     "gvx_shard_disconnect": (C.c_int, []),
     "gvx_peer_mailbox_create": (C.c_int, [vp]),

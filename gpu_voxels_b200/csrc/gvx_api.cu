@@ -794,6 +794,38 @@ static int fixup_summary_after_mark(Map* a, int8_t thr_i, bool mark) {
 // offset-collide launch over that sub-range, with b = rank s's slab mapped through CUDA IPC (loads over NVLink; own
 // slab: local) and the offset rewritten slab-to-slab. Counts land in one device word per peer slab, are summed on the
 // host and all-reduced.
+// The launches of an offset collide for the rank that owns layers [z_bounds[rank], z_bounds[rank + 1]) of `a`: for every
+// rank s whose b-slab holds partners, segment s = {i_begin, i_end, off_local}: the kernel runs over b's LOCAL indices
+// [i_begin, i_end) of rank s's slab and meets b_s[i'] with a_local[i' + off_local]. i_begin == i_end: nothing to do with
+// rank s. Pure arithmetic (no CUDA): exported as gvx_halo_plan and pinned by brute force on the CPU
+// (tests/test_shard_host.py).
+static void halo_plan(int64_t layer, uint32_t dz, const uint32_t* z_bounds, int world, int rank, int64_t off,
+                      int64_t* seg3 /* world x {i_begin, i_end, off_local} */) {
+  const int64_t n_tot = layer * dz;
+  const int64_t A0 = (int64_t)z_bounds[rank] * layer, A1 = (int64_t)z_bounds[rank + 1] * layer;
+  // grid indices i of b with a partner i + off inside this rank's slab of a (and inside the grid)
+  const int64_t lo_valid = std::max<int64_t>(A0 - off, off < 0 ? -off : 0), hi_valid = std::min<int64_t>(A1 - off, off > 0 ? n_tot - off : n_tot);
+  for (int s = 0; s < world; ++s) {
+    const int64_t B0 = (int64_t)z_bounds[s] * layer, B1 = (int64_t)z_bounds[s + 1] * layer;
+    const int64_t lo = std::max(lo_valid, B0), hi = std::min(hi_valid, B1);
+    seg3[3 * s] = lo < hi ? lo - B0 : 0;
+    seg3[3 * s + 1] = lo < hi ? hi - B0 : 0;
+    seg3[3 * s + 2] = B0 + off - A0;  // a's local index = i + off - A0 = i' + B0 + off - A0
+  }
+}
+
+int gvx_halo_plan(uint32_t dx, uint32_t dy, uint32_t dz, const uint32_t* z_bounds, int world, int rank,
+                  const int32_t off3[3], int64_t* seg3) {
+  if (!z_bounds || !off3 || !seg3 || world < 1 || world > kMaxPeers || rank < 0 || rank >= world)
+    return fail(GVX_ERR_INVALID, "gvx_halo_plan: bad arguments");
+  if (z_bounds[0] != 0 || z_bounds[world] != dz) return fail(GVX_ERR_INVALID, "z_bounds must run from 0 to dz");
+  for (int r = 0; r < world; ++r)
+    if (z_bounds[r] > z_bounds[r + 1]) return fail(GVX_ERR_INVALID, "z_bounds must not decrease");
+  const int64_t layer = (int64_t)dx * dy;
+  halo_plan(layer, dz, z_bounds, world, rank, (int64_t)off3[2] * layer + (int64_t)off3[1] * dx + off3[0], seg3);
+  return GVX_OK;
+}
+
 static int collide_halo(Map* a, Map* b, int64_t off, int8_t thr, int thr_b_or_same, bool mark, uint64_t* count) {
   if (a == b && mark)
     return fail(GVX_ERR_UNSUPPORTED, "marking a z-slab map while colliding it with a shifted copy of itself: the peers read "
@@ -811,22 +843,23 @@ static int collide_halo(Map* a, Map* b, int64_t off, int8_t thr, int thr_b_or_sa
   const int world = spmd ? g.shard_world : b->peer_world;
   if (!g.halo_counts_d) GVX_CUDA(cudaMalloc((void**)&g.halo_counts_d, kMaxPeers * sizeof(unsigned long long)));
   GVX_CUDA(cudaMemsetAsync(g.halo_counts_d, 0, kMaxPeers * sizeof(unsigned long long), g.stream));
-  const int64_t layer = (int64_t)a->dx * a->dy, n_tot = layer * a->dz;
-  const int64_t A0 = (int64_t)a->z0 * layer, A1 = (int64_t)a->z1 * layer;
-  // grid indices i of b with a partner i + off inside this rank's slab of a
-  const int64_t lo_valid = std::max<int64_t>(A0 - off, off < 0 ? -off : 0), hi_valid = std::min<int64_t>(A1 - off, off > 0 ? n_tot - off : n_tot);
+  uint32_t zb[kMaxPeers + 1];
   for (int s = 0; s < world; ++s) {
-    uint32_t zs0, zs1;
-    if (spmd) shard_slab_of(s, b->dz, &zs0, &zs1);
-    else { zs0 = b->peer_z[s]; zs1 = b->peer_z[s + 1]; }
-    const int64_t B0 = (int64_t)zs0 * layer, B1 = (int64_t)zs1 * layer;
-    const int64_t lo = std::max(lo_valid, B0), hi = std::min(hi_valid, B1);
-    if (lo >= hi) continue;
+    uint32_t z1;
+    if (spmd) shard_slab_of(s, b->dz, &zb[s], &z1);
+    else zb[s] = b->peer_z[s];
+  }
+  zb[world] = b->dz;
+  const int rank = spmd ? g.shard_rank : b->peer_rank;
+  if (zb[rank] != a->z0 || zb[rank + 1] != a->z1) return fail(GVX_ERR_INVALID, "slab [%u,%u) is not rank %d's share of the partition", a->z0, a->z1, rank);
+  int64_t seg[3 * kMaxPeers];
+  halo_plan((int64_t)a->dx * a->dy, a->dz, zb, world, rank, off, seg);
+  for (int s = 0; s < world; ++s) {
+    if (seg[3 * s] >= seg[3 * s + 1]) continue;
     LaunchCtx c = lctx();
     c.result_hmap_d = nullptr;  // device-only result, one word per peer slab
-    // the kernels index b[i'] and a[i' + off'] with i' local to rank s's b-slab: a's local index is i + off - A0
-    GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->peer_data[s], b->type, lo - B0, hi - B0, B0 + off - A0, thr,
-                                    mark, false, g.halo_counts_d + s, nullptr, nullptr, nullptr, nullptr, thr_b_or_same));
+    GVX_CUDA(launch_collide_map_map(c, a->data, a->type, b->peer_data[s], b->type, seg[3 * s], seg[3 * s + 1], seg[3 * s + 2],
+                                    thr, mark, false, g.halo_counts_d + s, nullptr, nullptr, nullptr, nullptr, thr_b_or_same));
   }
   if ((rc = fixup_summary_after_mark(a, thr, mark))) return rc;
   unsigned long long parts[kMaxPeers];

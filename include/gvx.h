@@ -310,6 +310,12 @@ int gvx_shard_allreduce_u64(uint64_t* values, int n_sum, int n_or);
 int gvx_map_ipc_handle(gvx_handle_t map, void* handle64_out);
 int gvx_map_connect_peers(gvx_handle_t map, int rank, int world, const void* all_handles, const uint32_t* z_bounds);
 int gvx_map_disconnect_peers(gvx_handle_t map);
+/* The launches such a collide is made of, as pure arithmetic (no GPU needed; used by the library itself and pinned by
+ * brute force in the CPU tests): for the rank that owns layers [z_bounds[rank], z_bounds[rank + 1]) of `a` and every rank s,
+ * seg3[3 s .. 3 s + 2] = {i_begin, i_end, off_local}: over the LOCAL indices [i_begin, i_end) of rank s's slab of `b`,
+ * b_s[i'] meets a_local[i' + off_local]; i_begin == i_end: rank s holds no partner. */
+int gvx_halo_plan(uint32_t dx, uint32_t dy, uint32_t dz, const uint32_t* z_bounds, int world, int rank,
+                  const int32_t off3[3], int64_t* seg3);
 /* every rank's `bytes` bytes (at most 2176), in rank order, into `all` (world x bytes) on every rank */
 int gvx_shard_allgather(const void* mine, uint32_t bytes, void* all);
 /* join / leave the job's rendezvous explicitly instead of through the environment: host side only (no GPU needed, no

@@ -105,3 +105,52 @@ def test_library_slabs_equal_sharding_py():
 
 def test_shard_example_compiles_with_plain_gxx():
     assert os.path.exists(build_shard_example())
+
+
+def test_halo_plan_enumerates_every_offset_pair_exactly_once():
+    """gvx_halo_plan -- the arithmetic gvx_collide_map_map uses for an offset collide on z-slab maps (one launch per peer
+    slab holding partners) -- against brute force: over all ranks and segments, the pairs (a index, b index) the launches
+    visit must be exactly {(i + off, i) : 0 <= i < n, 0 <= i + off < n} (GV/voxelmap/TemplateVoxelMap.hpp:486-519: this
+    map's pointer is shifted by the signed linear offset), each once, with the a index inside the visiting rank's slab
+    and the b index inside rank s's slab."""
+    from gpu_voxels_b200 import _lib, sharding
+    L = _lib.load()
+    rng = np.random.Generator(np.random.PCG64(3))
+    cases = 0
+    for dims in ((5, 4, 9), (3, 3, 7), (8, 2, 16), (1, 1, 5)):
+        dx, dy, dz = dims
+        layer, n = dx * dy, dx * dy * dz
+        for world in (1, 2, 3, 4):
+            if world > dz:
+                continue
+            even = sharding.slab_bounds(dz, world)
+            cuts = np.sort(rng.choice(np.arange(0, dz + 1), size=world - 1, replace=True)).astype(np.uint32)
+            ragged = np.concatenate([[0], cuts, [dz]]).astype(np.uint32)   # may hold EMPTY slabs
+            for zb in (even, ragged):
+                offs = [(0, 0, 1), (0, 0, -1), (1, 0, 0), (-1, 0, 0), (0, 1, 0), (dx - 1, dy - 1, dz - 1), (0, 0, dz), (0, 0, -dz - 3)]
+                offs += [tuple(int(v) for v in rng.integers(-m, m + 1, 3)) for m in (1, 2, dz) for _ in range(4)]
+                for off in offs:
+                    lin = off[2] * layer + off[1] * dx + off[0]
+                    want = {(i + lin, i) for i in range(n) if 0 <= i + lin < n}
+                    got = []
+                    for rank in range(world):
+                        seg = np.zeros(3 * world, np.int64)
+                        o3 = np.asarray(off, np.int32)
+                        _lib.check(L.gvx_halo_plan(dx, dy, dz, zb.ctypes.data_as(C.c_void_p), world, rank,
+                                                   o3.ctypes.data_as(C.c_void_p), seg.ctypes.data_as(C.c_void_p)))
+                        a0, a1 = int(zb[rank]) * layer, int(zb[rank + 1]) * layer
+                        for s in range(world):
+                            b0, b1 = int(zb[s]) * layer, int(zb[s + 1]) * layer
+                            i0, i1, ol = (int(v) for v in seg[3 * s:3 * s + 3])
+                            assert 0 <= i0 <= i1 <= b1 - b0, (dims, world, zb, off, rank, s, i0, i1)
+                            for il in range(i0, i1):
+                                al = il + ol                       # what the kernel indexes: a_local[i' + off_local]
+                                assert 0 <= al < a1 - a0, (dims, world, zb, off, rank, s, il, al)
+                                got.append((a0 + al, b0 + il))
+                    assert len(got) == len(set(got)) and set(got) == want, (dims, world, zb.tolist(), off, len(got), len(want))
+                    cases += 1
+    assert cases > 400
+    bad = np.asarray([0, 5, 3, 9], np.uint32)   # decreasing bounds are refused
+    seg = np.zeros(9, np.int64)
+    o3 = np.zeros(3, np.int32)
+    assert L.gvx_halo_plan(5, 4, 9, bad.ctypes.data_as(C.c_void_p), 3, 0, o3.ctypes.data_as(C.c_void_p), seg.ctypes.data_as(C.c_void_p)) != 0
